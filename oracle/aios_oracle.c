@@ -1,0 +1,796 @@
+/*
+ * aios_oracle.c — CPU ORACLE (test infrastructure, NOT product code).
+ *
+ * Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference
+ * legs may build, load or call this file.  The product (libaios_b200.so) never links it
+ * and has no CPU fallback.
+ *
+ * PARITY UNPINNED.  The reference (MohaMehrzad/aiOS, `runtime` crate) holds no inference
+ * arithmetic; it proxies to an un-vendored, un-pinned llama.cpp `llama-server`
+ * (reference: scripts/build-llamacpp.sh:89, runtime/src/model_manager.rs:187-204,
+ * runtime/src/inference.rs:100,136-142).  llama.cpp's source is not on this machine, so
+ * this file restates the *published* ggml CPU algorithm from its documented formats:
+ *   - block formats and dequantisation: gguf-py quants.py (llama.cpp's own Python package,
+ *     gguf 0.19.0): Q8_0 :396-401, Q4_K :479-522, Q5_K :527-549, Q6_K :554-572 — the
+ *     dequantisers here are checked BIT-EXACTLY against that package in tests/.
+ *   - activation quantisation (Q8_K / Q8_0), integer block dot products, f16 KV cache,
+ *     NORM-style RoPE, RMSNorm, SwiGLU: SURVEY.md Appendix C (ggml "generic" scalar
+ *     kernels; summation order = the generic kernel's).
+ * None of the reference's own tests pin a logit/token, so there is no
+ * golden vector from the reference to check against; tests/golden/ holds vectors made
+ * with gguf-py and HF transformers fp32 by the committed generator script.
+ *
+ * Build: see oracle/Makefile (gcc -O2 -fopenmp -ffp-contract=off -shared).
+ */
+#include <math.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+#ifdef _OPENMP
+#include <omp.h>
+#endif
+
+#define QK_K 256
+#define QK8_0 32
+
+enum { T_F32 = 0, T_F16 = 1, T_Q8_0 = 8, T_Q4_K = 12, T_Q5_K = 13, T_Q6_K = 14 };
+
+/* ---------------------------------------------------------------- fp16 <-> fp32 (IEEE, RNE) */
+static inline float h2f(uint16_t h) {
+    uint32_t sign = (uint32_t)(h & 0x8000u) << 16;
+    uint32_t exp = (h >> 10) & 0x1f;
+    uint32_t man = h & 0x3ffu;
+    uint32_t bits;
+    if (exp == 0) {
+        if (man == 0) {
+            bits = sign;
+        } else { /* subnormal: normalise */
+            int e = -1;
+            do { man <<= 1; e++; } while ((man & 0x400u) == 0);
+            man &= 0x3ffu;
+            bits = sign | ((uint32_t)(127 - 15 - e) << 23) | (man << 13);
+        }
+    } else if (exp == 31) {
+        bits = sign | 0x7f800000u | (man << 13);
+    } else {
+        bits = sign | ((exp + 112) << 23) | (man << 13);
+    }
+    float f;
+    memcpy(&f, &bits, 4);
+    return f;
+}
+
+static inline uint16_t f2h(float f) {
+    uint32_t x;
+    memcpy(&x, &f, 4);
+    uint32_t sign = (x >> 16) & 0x8000u;
+    uint32_t absx = x & 0x7fffffffu;
+    if (absx >= 0x7f800000u) { /* inf / nan */
+        return (uint16_t)(sign | 0x7c00u | ((absx > 0x7f800000u) ? 0x200u : 0));
+    }
+    if (absx >= 0x477ff000u) { /* rounds to >= 65520 -> inf */
+        return (uint16_t)(sign | 0x7c00u);
+    }
+    if (absx < 0x33000001u) { /* < 2^-25 (or exactly 2^-25 -> ties to even 0) */
+        return (uint16_t)sign;
+    }
+    int32_t e = (int32_t)(absx >> 23) - 127;
+    uint32_t m = (absx & 0x7fffffu) | 0x800000u;
+    if (e < -14) { /* subnormal half */
+        int shift = (-14 - e) + 13; /* 14..24 */
+        uint32_t q = m >> shift;
+        uint32_t rem = m & ((1u << shift) - 1);
+        uint32_t half = 1u << (shift - 1);
+        if (rem > half || (rem == half && (q & 1))) q++;
+        return (uint16_t)(sign | q);
+    }
+    uint32_t q = ((uint32_t)(e + 15) << 10) | ((m >> 13) & 0x3ffu);
+    uint32_t rem = m & 0x1fffu;
+    if (rem > 0x1000u || (rem == 0x1000u && (q & 1))) q++;
+    return (uint16_t)(sign | q);
+}
+
+float oracle_h2f(uint16_t h) { return h2f(h); }
+uint16_t oracle_f2h(float f) { return f2h(f); }
+
+/* ---------------------------------------------------------------- block layouts */
+#pragma pack(push, 1)
+typedef struct { uint16_t d; int8_t qs[QK8_0]; } block_q8_0;                              /* 34 B  */
+typedef struct { uint16_t d; uint16_t dmin; uint8_t scales[12]; uint8_t qs[QK_K / 2]; } block_q4_K; /* 144 B */
+typedef struct { uint16_t d; uint16_t dmin; uint8_t scales[12]; uint8_t qh[QK_K / 8]; uint8_t qs[QK_K / 2]; } block_q5_K; /* 176 B */
+typedef struct { uint8_t ql[QK_K / 2]; uint8_t qh[QK_K / 4]; int8_t scales[QK_K / 16]; uint16_t d; } block_q6_K; /* 210 B */
+typedef struct { float d; int8_t qs[QK_K]; int16_t bsums[QK_K / 16]; } block_q8_K;       /* 292 B */
+#pragma pack(pop)
+
+static size_t type_block_bytes(int type) {
+    switch (type) {
+        case T_F32: return 4;
+        case T_F16: return 2;
+        case T_Q8_0: return sizeof(block_q8_0);
+        case T_Q4_K: return sizeof(block_q4_K);
+        case T_Q5_K: return sizeof(block_q5_K);
+        case T_Q6_K: return sizeof(block_q6_K);
+    }
+    return 0;
+}
+static int type_block_elems(int type) {
+    switch (type) {
+        case T_F32: case T_F16: return 1;
+        case T_Q8_0: return QK8_0;
+        case T_Q4_K: case T_Q5_K: case T_Q6_K: return QK_K;
+    }
+    return 0;
+}
+static size_t row_bytes(int type, int64_t k) { return (size_t)(k / type_block_elems(type)) * type_block_bytes(type); }
+
+/* 6-bit (scale, min) unpack — gguf-py quants.py:479-501 (Q4_K.get_scale_min) */
+static inline void get_scale_min_k4(int j, const uint8_t *q, uint8_t *d, uint8_t *m) {
+    if (j < 4) {
+        *d = q[j] & 63;
+        *m = q[j + 4] & 63;
+    } else {
+        *d = (q[j + 4] & 0xF) | ((q[j - 4] >> 6) << 4);
+        *m = (q[j + 4] >> 4) | ((q[j] >> 6) << 4);
+    }
+}
+
+/* ---------------------------------------------------------------- dequantize_row_* (bit-exact tier)
+ * Each product is rounded to f32 on its own; -ffp-contract=off keeps `d*q - m` un-fused,
+ * matching gguf-py (numpy has no FMA).  quants.py:396-401, :504-522, :527-549, :554-572. */
+static void dequantize_row_q8_0(const block_q8_0 *x, float *y, int64_t k) {
+    for (int64_t i = 0; i < k / QK8_0; i++) {
+        const float d = h2f(x[i].d);
+        for (int j = 0; j < QK8_0; j++) y[i * QK8_0 + j] = (float)x[i].qs[j] * d;
+    }
+}
+
+static void dequantize_row_q4_K(const block_q4_K *x, float *y, int64_t k) {
+    for (int64_t i = 0; i < k / QK_K; i++) {
+        const float d = h2f(x[i].d), dmin = h2f(x[i].dmin);
+        const uint8_t *q = x[i].qs;
+        for (int p = 0; p < 4; p++) {
+            uint8_t sc, m;
+            get_scale_min_k4(2 * p, x[i].scales, &sc, &m);
+            const float d1 = d * (float)sc, m1 = dmin * (float)m;
+            get_scale_min_k4(2 * p + 1, x[i].scales, &sc, &m);
+            const float d2 = d * (float)sc, m2 = dmin * (float)m;
+            for (int l = 0; l < 32; l++) *y++ = d1 * (float)(q[l] & 0xF) - m1;
+            for (int l = 0; l < 32; l++) *y++ = d2 * (float)(q[l] >> 4) - m2;
+            q += 32;
+        }
+    }
+}
+
+static void dequantize_row_q5_K(const block_q5_K *x, float *y, int64_t k) {
+    for (int64_t i = 0; i < k / QK_K; i++) {
+        const float d = h2f(x[i].d), dmin = h2f(x[i].dmin);
+        const uint8_t *ql = x[i].qs, *qh = x[i].qh;
+        for (int p = 0; p < 4; p++) {
+            uint8_t sc, m;
+            get_scale_min_k4(2 * p, x[i].scales, &sc, &m);
+            const float d1 = d * (float)sc, m1 = dmin * (float)m;
+            get_scale_min_k4(2 * p + 1, x[i].scales, &sc, &m);
+            const float d2 = d * (float)sc, m2 = dmin * (float)m;
+            for (int l = 0; l < 32; l++)
+                *y++ = d1 * (float)((ql[l] & 0xF) | (((qh[l] >> (2 * p)) & 1) << 4)) - m1;
+            for (int l = 0; l < 32; l++)
+                *y++ = d2 * (float)((ql[l] >> 4) | (((qh[l] >> (2 * p + 1)) & 1) << 4)) - m2;
+            ql += 32;
+        }
+    }
+}
+
+static void dequantize_row_q6_K(const block_q6_K *x, float *y, int64_t k) {
+    for (int64_t i = 0; i < k / QK_K; i++) {
+        const float d = h2f(x[i].d);
+        const uint8_t *ql = x[i].ql, *qh = x[i].qh;
+        const int8_t *sc = x[i].scales;
+        for (int h = 0; h < 2; h++) {
+            for (int l = 0; l < 32; l++) {
+                const int is = l / 16;
+                const int8_t q1 = (int8_t)((ql[l] & 0xF) | (((qh[l] >> 0) & 3) << 4)) - 32;
+                const int8_t q2 = (int8_t)((ql[l + 32] & 0xF) | (((qh[l] >> 2) & 3) << 4)) - 32;
+                const int8_t q3 = (int8_t)((ql[l] >> 4) | (((qh[l] >> 4) & 3) << 4)) - 32;
+                const int8_t q4 = (int8_t)((ql[l + 32] >> 4) | (((qh[l] >> 6) & 3) << 4)) - 32;
+                y[l + 0] = (d * (float)sc[is + 0]) * (float)q1;
+                y[l + 32] = (d * (float)sc[is + 2]) * (float)q2;
+                y[l + 64] = (d * (float)sc[is + 4]) * (float)q3;
+                y[l + 96] = (d * (float)sc[is + 6]) * (float)q4;
+            }
+            y += 128; ql += 64; qh += 32; sc += 8;
+        }
+    }
+}
+
+/* public: dequantise n elements (n multiple of the block size) of `type` */
+int oracle_dequantize(int type, const void *blocks, int64_t n, float *out) {
+    switch (type) {
+        case T_F32: memcpy(out, blocks, (size_t)n * 4); return 0;
+        case T_F16: for (int64_t i = 0; i < n; i++) out[i] = h2f(((const uint16_t *)blocks)[i]); return 0;
+        case T_Q8_0: dequantize_row_q8_0((const block_q8_0 *)blocks, out, n); return 0;
+        case T_Q4_K: dequantize_row_q4_K((const block_q4_K *)blocks, out, n); return 0;
+        case T_Q5_K: dequantize_row_q5_K((const block_q5_K *)blocks, out, n); return 0;
+        case T_Q6_K: dequantize_row_q6_K((const block_q6_K *)blocks, out, n); return 0;
+    }
+    return -1;
+}
+
+/* ---------------------------------------------------------------- activation quantisation
+ * SURVEY.md Appendix C.1 (ggml quantize_row_q8_K / quantize_row_q8_0 reference versions). */
+static inline int nearest_int(float fval) { /* round-to-nearest-even via the 1.5*2^23 trick */
+    float val = fval + 12582912.f;
+    int i;
+    memcpy(&i, &val, sizeof(int));
+    return (i & 0x007fffff) - 0x00400000;
+}
+
+void oracle_quantize_row_q8_K(const float *x, void *vy, int64_t k) {
+    block_q8_K *y = (block_q8_K *)vy;
+    for (int64_t i = 0; i < k / QK_K; i++) {
+        float max = 0, amax = 0;
+        for (int j = 0; j < QK_K; j++) {
+            const float ax = fabsf(x[j]);
+            if (ax > amax) { amax = ax; max = x[j]; }
+        }
+        if (!amax) {
+            y[i].d = 0;
+            memset(y[i].qs, 0, QK_K);
+            memset(y[i].bsums, 0, sizeof(y[i].bsums));
+            x += QK_K;
+            continue;
+        }
+        const float iscale = -127.f / max;
+        for (int j = 0; j < QK_K; j++) {
+            int v = nearest_int(iscale * x[j]);
+            y[i].qs[j] = (int8_t)(v < 127 ? v : 127);
+        }
+        for (int j = 0; j < QK_K / 16; j++) {
+            int sum = 0;
+            for (int ii = 0; ii < 16; ii++) sum += y[i].qs[j * 16 + ii];
+            y[i].bsums[j] = (int16_t)sum;
+        }
+        y[i].d = 1 / iscale;
+        x += QK_K;
+    }
+}
+
+void oracle_quantize_row_q8_0(const float *x, void *vy, int64_t k) {
+    block_q8_0 *y = (block_q8_0 *)vy;
+    for (int64_t i = 0; i < k / QK8_0; i++) {
+        float amax = 0;
+        for (int j = 0; j < QK8_0; j++) {
+            const float v = fabsf(x[i * QK8_0 + j]);
+            if (v > amax) amax = v;
+        }
+        const float d = amax / 127;
+        const float id = d ? 1.0f / d : 0.0f;
+        y[i].d = f2h(d);
+        for (int j = 0; j < QK8_0; j++) y[i].qs[j] = (int8_t)roundf(x[i * QK8_0 + j] * id);
+    }
+}
+
+/* ---------------------------------------------------------------- integer block dot products
+ * "generic" scalar kernels, 8 float lanes summed at the end. */
+static float vec_dot_q4_K_q8_K(int64_t n, const block_q4_K *x, const block_q8_K *y) {
+    const int64_t nb = n / QK_K;
+    int8_t aux8[QK_K];
+    float sums[8] = {0};
+    float sumf = 0;
+    for (int64_t i = 0; i < nb; i++) {
+        const uint8_t *q4 = x[i].qs;
+        const int8_t *q8 = y[i].qs;
+        int32_t aux32[8] = {0};
+        int8_t *a = aux8;
+        for (int j = 0; j < QK_K / 64; j++) {
+            for (int l = 0; l < 32; l++) a[l] = (int8_t)(q4[l] & 0xF);
+            a += 32;
+            for (int l = 0; l < 32; l++) a[l] = (int8_t)(q4[l] >> 4);
+            a += 32; q4 += 32;
+        }
+        uint8_t sc[8], mn[8];
+        for (int j = 0; j < 8; j++) get_scale_min_k4(j, x[i].scales, &sc[j], &mn[j]);
+        int sumi = 0;
+        for (int j = 0; j < QK_K / 16; j++) sumi += y[i].bsums[j] * mn[j / 2];
+        a = aux8;
+        for (int j = 0; j < QK_K / 32; j++) {
+            const int32_t scale = sc[j];
+            for (int r = 0; r < 4; r++) {
+                for (int l = 0; l < 8; l++) aux32[l] += scale * ((int16_t)q8[l] * (int16_t)a[l]);
+                q8 += 8; a += 8;
+            }
+        }
+        const float d = h2f(x[i].d) * y[i].d;
+        for (int l = 0; l < 8; l++) sums[l] += d * (float)aux32[l];
+        const float dmin = h2f(x[i].dmin) * y[i].d;
+        sumf -= dmin * (float)sumi;
+    }
+    for (int l = 0; l < 8; l++) sumf += sums[l];
+    return sumf;
+}
+
+static float vec_dot_q5_K_q8_K(int64_t n, const block_q5_K *x, const block_q8_K *y) {
+    const int64_t nb = n / QK_K;
+    int8_t aux8[QK_K];
+    float sums[8] = {0};
+    float sumf = 0;
+    for (int64_t i = 0; i < nb; i++) {
+        const uint8_t *q4 = x[i].qs, *hm = x[i].qh;
+        const int8_t *q8 = y[i].qs;
+        int32_t aux32[8] = {0};
+        int8_t *a = aux8;
+        uint8_t m = 1;
+        for (int j = 0; j < QK_K / 64; j++) {
+            for (int l = 0; l < 32; l++) a[l] = (int8_t)((q4[l] & 0xF) + ((hm[l] & m) ? 16 : 0));
+            a += 32; m <<= 1;
+            for (int l = 0; l < 32; l++) a[l] = (int8_t)((q4[l] >> 4) + ((hm[l] & m) ? 16 : 0));
+            a += 32; m <<= 1;
+            q4 += 32;
+        }
+        uint8_t sc[8], mn[8];
+        for (int j = 0; j < 8; j++) get_scale_min_k4(j, x[i].scales, &sc[j], &mn[j]);
+        int sumi = 0;
+        for (int j = 0; j < QK_K / 16; j++) sumi += y[i].bsums[j] * mn[j / 2];
+        a = aux8;
+        for (int j = 0; j < QK_K / 32; j++) {
+            const int32_t scale = sc[j];
+            for (int r = 0; r < 4; r++) {
+                for (int l = 0; l < 8; l++) aux32[l] += scale * ((int16_t)q8[l] * (int16_t)a[l]);
+                q8 += 8; a += 8;
+            }
+        }
+        const float d = h2f(x[i].d) * y[i].d;
+        for (int l = 0; l < 8; l++) sums[l] += d * (float)aux32[l];
+        const float dmin = h2f(x[i].dmin) * y[i].d;
+        sumf -= dmin * (float)sumi;
+    }
+    for (int l = 0; l < 8; l++) sumf += sums[l];
+    return sumf;
+}
+
+static float vec_dot_q6_K_q8_K(int64_t n, const block_q6_K *x, const block_q8_K *y) {
+    const int64_t nb = n / QK_K;
+    int8_t aux8[QK_K];
+    float sums[8] = {0};
+    float sumf = 0;
+    for (int64_t i = 0; i < nb; i++) {
+        const uint8_t *q4 = x[i].ql, *qh = x[i].qh;
+        const int8_t *q8 = y[i].qs;
+        int32_t aux32[8] = {0};
+        int8_t *a = aux8;
+        for (int j = 0; j < QK_K; j += 128) {
+            for (int l = 0; l < 32; l++) {
+                a[l + 0] = (int8_t)((q4[l + 0] & 0xF) | (((qh[l] >> 0) & 3) << 4)) - 32;
+                a[l + 32] = (int8_t)((q4[l + 32] & 0xF) | (((qh[l] >> 2) & 3) << 4)) - 32;
+                a[l + 64] = (int8_t)((q4[l + 0] >> 4) | (((qh[l] >> 4) & 3) << 4)) - 32;
+                a[l + 96] = (int8_t)((q4[l + 32] >> 4) | (((qh[l] >> 6) & 3) << 4)) - 32;
+            }
+            a += 128; q4 += 64; qh += 32;
+        }
+        a = aux8;
+        for (int j = 0; j < QK_K / 16; j++) {
+            const int scale = x[i].scales[j];
+            for (int r = 0; r < 2; r++) {
+                for (int l = 0; l < 8; l++) aux32[l] += scale * ((int16_t)q8[l] * (int16_t)a[l]);
+                q8 += 8; a += 8;
+            }
+        }
+        const float d = h2f(x[i].d) * y[i].d;
+        for (int l = 0; l < 8; l++) sums[l] += d * (float)aux32[l];
+    }
+    for (int l = 0; l < 8; l++) sumf += sums[l];
+    return sumf;
+}
+
+static float vec_dot_q8_0_q8_0(int64_t n, const block_q8_0 *x, const block_q8_0 *y) {
+    const int64_t nb = n / QK8_0;
+    float sumf = 0;
+    for (int64_t ib = 0; ib < nb; ib++) {
+        int sumi = 0;
+        for (int j = 0; j < QK8_0; j++) sumi += x[ib].qs[j] * y[ib].qs[j];
+        sumf += (float)sumi * (h2f(x[ib].d) * h2f(y[ib].d));
+    }
+    return sumf;
+}
+
+static float vec_dot_f32(int64_t n, const float *x, const float *y) {
+    float s = 0;
+    for (int64_t i = 0; i < n; i++) s += x[i] * y[i];
+    return s;
+}
+
+/* ---------------------------------------------------------------- AVX2 dot kernels (timed CPU baseline)
+ * Same integer arithmetic as the generic kernels above; only the float summation order
+ * differs (as it does between ggml's own generic/AVX2 kernels).  Validated against the
+ * generic versions in tests/.  Selected with oracle_set_simd(1). */
+static int g_simd = 0;
+void oracle_set_simd(int on) { g_simd = on; }
+#if defined(__AVX2__)
+#include <immintrin.h>
+static inline float hsum8(__m256 v) {
+    __m128 lo = _mm256_castps256_ps128(v), hi = _mm256_extractf128_ps(v, 1);
+    lo = _mm_add_ps(lo, hi);
+    lo = _mm_add_ps(lo, _mm_movehl_ps(lo, lo));
+    lo = _mm_add_ss(lo, _mm_movehdup_ps(lo));
+    return _mm_cvtss_f32(lo);
+}
+static inline int hsum8_i32(__m256i v) {
+    __m128i s = _mm_add_epi32(_mm256_castsi256_si128(v), _mm256_extracti128_si256(v, 1));
+    s = _mm_add_epi32(s, _mm_shuffle_epi32(s, 0x4e));
+    s = _mm_add_epi32(s, _mm_shuffle_epi32(s, 0xb1));
+    return _mm_cvtsi128_si32(s);
+}
+/* u8 x i8 -> i32 lanes (8 lanes, each the sum of 4 products) */
+static inline __m256i dot_u8_i8(__m256i u, __m256i s) {
+    const __m256i p16 = _mm256_maddubs_epi16(u, s);
+    return _mm256_madd_epi16(p16, _mm256_set1_epi16(1));
+}
+static float vec_dot_q4_K_q8_K_avx2(int64_t n, const block_q4_K *x, const block_q8_K *y) {
+    const int64_t nb = n / QK_K;
+    const __m256i m4 = _mm256_set1_epi8(0xF);
+    float acc = 0, accm = 0;
+    for (int64_t i = 0; i < nb; i++) {
+        uint8_t sc[8], mn[8];
+        for (int j = 0; j < 8; j++) get_scale_min_k4(j, x[i].scales, &sc[j], &mn[j]);
+        int summ = 0;
+        for (int j = 0; j < 8; j++) summ += mn[j] * (y[i].bsums[2 * j] + y[i].bsums[2 * j + 1]);
+        __m256i sumi = _mm256_setzero_si256();
+        for (int p = 0; p < 4; p++) {
+            const __m256i q4 = _mm256_loadu_si256((const __m256i *)(x[i].qs + 32 * p));
+            const __m256i lo = _mm256_and_si256(q4, m4);
+            const __m256i hi = _mm256_and_si256(_mm256_srli_epi16(q4, 4), m4);
+            const __m256i a0 = _mm256_loadu_si256((const __m256i *)(y[i].qs + 64 * p));
+            const __m256i a1 = _mm256_loadu_si256((const __m256i *)(y[i].qs + 64 * p + 32));
+            sumi = _mm256_add_epi32(sumi, _mm256_mullo_epi32(dot_u8_i8(lo, a0), _mm256_set1_epi32(sc[2 * p])));
+            sumi = _mm256_add_epi32(sumi, _mm256_mullo_epi32(dot_u8_i8(hi, a1), _mm256_set1_epi32(sc[2 * p + 1])));
+        }
+        acc += (h2f(x[i].d) * y[i].d) * (float)hsum8_i32(sumi);
+        accm += (h2f(x[i].dmin) * y[i].d) * (float)summ;
+    }
+    return acc - accm;
+}
+static float vec_dot_q6_K_q8_K_avx2(int64_t n, const block_q6_K *x, const block_q8_K *y) {
+    const int64_t nb = n / QK_K;
+    const __m256i m4 = _mm256_set1_epi8(0xF), m2 = _mm256_set1_epi8(0x30);
+    float acc = 0;
+    for (int64_t i = 0; i < nb; i++) {
+        int32_t tot = 0;
+        for (int h = 0; h < 2; h++) {
+            const __m256i qla = _mm256_loadu_si256((const __m256i *)(x[i].ql + 64 * h));
+            const __m256i qlb = _mm256_loadu_si256((const __m256i *)(x[i].ql + 64 * h + 32));
+            const __m256i qh = _mm256_loadu_si256((const __m256i *)(x[i].qh + 32 * h));
+            __m256i q[4];
+            q[0] = _mm256_or_si256(_mm256_and_si256(qla, m4), _mm256_and_si256(_mm256_slli_epi16(qh, 4), m2));
+            q[1] = _mm256_or_si256(_mm256_and_si256(qlb, m4), _mm256_and_si256(_mm256_slli_epi16(qh, 2), m2));
+            q[2] = _mm256_or_si256(_mm256_and_si256(_mm256_srli_epi16(qla, 4), m4), _mm256_and_si256(qh, m2));
+            q[3] = _mm256_or_si256(_mm256_and_si256(_mm256_srli_epi16(qlb, 4), m4), _mm256_and_si256(_mm256_srli_epi16(qh, 2), m2));
+            for (int g = 0; g < 4; g++) {
+                const __m256i a = _mm256_loadu_si256((const __m256i *)(y[i].qs + 128 * h + 32 * g));
+                const __m256i d32 = dot_u8_i8(q[g], a); /* 8 lanes: lanes 0-3 = first 16, 4-7 = second 16 */
+                const __m128i l = _mm256_castsi256_si128(d32), u = _mm256_extracti128_si256(d32, 1);
+                __m128i sl = _mm_add_epi32(l, _mm_shuffle_epi32(l, 0x4e));
+                sl = _mm_add_epi32(sl, _mm_shuffle_epi32(sl, 0xb1));
+                __m128i su = _mm_add_epi32(u, _mm_shuffle_epi32(u, 0x4e));
+                su = _mm_add_epi32(su, _mm_shuffle_epi32(su, 0xb1));
+                const int is = 8 * h + 2 * g;
+                const int d0 = _mm_cvtsi128_si32(sl) - 32 * y[i].bsums[is];
+                const int d1 = _mm_cvtsi128_si32(su) - 32 * y[i].bsums[is + 1];
+                tot += x[i].scales[is] * d0 + x[i].scales[is + 1] * d1;
+            }
+        }
+        acc += (h2f(x[i].d) * y[i].d) * (float)tot;
+    }
+    return acc;
+}
+static float vec_dot_q8_0_q8_0_avx2(int64_t n, const block_q8_0 *x, const block_q8_0 *y) {
+    const int64_t nb = n / QK8_0;
+    __m256 acc = _mm256_setzero_ps();
+    for (int64_t ib = 0; ib < nb; ib++) {
+        const __m256i qx = _mm256_loadu_si256((const __m256i *)x[ib].qs);
+        const __m256i qy = _mm256_loadu_si256((const __m256i *)y[ib].qs);
+        const __m256i ax = _mm256_sign_epi8(qx, qx);
+        const __m256i sy = _mm256_sign_epi8(qy, qx);
+        const __m256 p = _mm256_cvtepi32_ps(dot_u8_i8(ax, sy));
+        acc = _mm256_add_ps(acc, _mm256_mul_ps(p, _mm256_set1_ps(h2f(x[ib].d) * h2f(y[ib].d))));
+    }
+    return hsum8(acc);
+}
+#define HAVE_AVX2_DOTS 1
+#else
+#define HAVE_AVX2_DOTS 0
+#endif
+
+/* one row dot: x row of `type` against pre-quantised activation `yq` (or f32 `yf`) */
+static float row_dot(int type, int64_t k, const void *row, const void *yq, const float *yf) {
+#if HAVE_AVX2_DOTS
+    if (g_simd) {
+        switch (type) {
+            case T_Q4_K: return vec_dot_q4_K_q8_K_avx2(k, (const block_q4_K *)row, (const block_q8_K *)yq);
+            case T_Q6_K: return vec_dot_q6_K_q8_K_avx2(k, (const block_q6_K *)row, (const block_q8_K *)yq);
+            case T_Q8_0: return vec_dot_q8_0_q8_0_avx2(k, (const block_q8_0 *)row, (const block_q8_0 *)yq);
+            default: break;
+        }
+    }
+#endif
+    switch (type) {
+        case T_Q4_K: return vec_dot_q4_K_q8_K(k, (const block_q4_K *)row, (const block_q8_K *)yq);
+        case T_Q5_K: return vec_dot_q5_K_q8_K(k, (const block_q5_K *)row, (const block_q8_K *)yq);
+        case T_Q6_K: return vec_dot_q6_K_q8_K(k, (const block_q6_K *)row, (const block_q8_K *)yq);
+        case T_Q8_0: return vec_dot_q8_0_q8_0(k, (const block_q8_0 *)row, (const block_q8_0 *)yq);
+        case T_F32: return vec_dot_f32(k, (const float *)row, yf);
+    }
+    return NAN;
+}
+
+/* y[N] = W[N,K] . x[K]   (ggml mul_mat with src1 quantised to the weight type's vec_dot_type) */
+int oracle_matvec(int type, const void *w, int64_t n_rows, int64_t k, const float *x, float *y) {
+    void *yq = NULL;
+    if (type == T_Q4_K || type == T_Q5_K || type == T_Q6_K) {
+        yq = malloc((size_t)(k / QK_K) * sizeof(block_q8_K));
+        oracle_quantize_row_q8_K(x, yq, k);
+    } else if (type == T_Q8_0) {
+        yq = malloc((size_t)(k / QK8_0) * sizeof(block_q8_0));
+        oracle_quantize_row_q8_0(x, yq, k);
+    } else if (type != T_F32) {
+        return -1;
+    }
+    const size_t rb = row_bytes(type, k);
+#pragma omp parallel for schedule(static)
+    for (int64_t r = 0; r < n_rows; r++) y[r] = row_dot(type, k, (const char *)w + (size_t)r * rb, yq, x);
+    free(yq);
+    return 0;
+}
+
+/* ---------------------------------------------------------------- model (arch "llama") */
+typedef struct { int32_t type; int64_t ne0, ne1; const void *data; } otensor;
+typedef struct {
+    otensor attn_norm, wq, wk, wv, wo, ffn_norm, w_gate, w_up, w_down;
+} olayer;
+
+typedef struct {
+    int32_t n_layer, n_embd, n_head, n_head_kv, head_dim, n_ff, n_vocab, n_ctx, n_rot;
+    float rms_eps, rope_freq_base;
+} oracle_hparams;
+
+typedef struct oracle_model {
+    oracle_hparams hp;
+    otensor tok_embd, output_norm, output;
+    olayer *layers;
+    uint16_t *k_cache, *v_cache; /* f16 [L][n_ctx][n_head_kv*head_dim] */
+    /* scratch */
+    float *x, *xn, *q, *k, *v, *att_out, *scores, *gate, *up, *h, *tmp;
+    float *logits;
+} oracle_model;
+
+oracle_model *oracle_model_new(const oracle_hparams *hp) {
+    oracle_model *m = (oracle_model *)calloc(1, sizeof(*m));
+    m->hp = *hp;
+    m->layers = (olayer *)calloc((size_t)hp->n_layer, sizeof(olayer));
+    const size_t kvd = (size_t)hp->n_head_kv * hp->head_dim;
+    m->k_cache = (uint16_t *)calloc((size_t)hp->n_layer * hp->n_ctx * kvd, 2);
+    m->v_cache = (uint16_t *)calloc((size_t)hp->n_layer * hp->n_ctx * kvd, 2);
+    const size_t qd = (size_t)hp->n_head * hp->head_dim;
+    m->x = (float *)calloc((size_t)hp->n_embd, 4);
+    m->xn = (float *)calloc((size_t)hp->n_embd, 4);
+    m->q = (float *)calloc(qd, 4);
+    m->k = (float *)calloc(kvd, 4);
+    m->v = (float *)calloc(kvd, 4);
+    m->att_out = (float *)calloc(qd, 4);
+    m->scores = (float *)calloc((size_t)hp->n_head * hp->n_ctx, 4);
+    m->gate = (float *)calloc((size_t)hp->n_ff, 4);
+    m->up = (float *)calloc((size_t)hp->n_ff, 4);
+    m->h = (float *)calloc((size_t)hp->n_ff, 4);
+    m->tmp = (float *)calloc((size_t)hp->n_embd, 4);
+    m->logits = (float *)calloc((size_t)hp->n_vocab, 4);
+    return m;
+}
+
+void oracle_model_free(oracle_model *m) {
+    if (!m) return;
+    free(m->layers); free(m->k_cache); free(m->v_cache);
+    free(m->x); free(m->xn); free(m->q); free(m->k); free(m->v); free(m->att_out);
+    free(m->scores); free(m->gate); free(m->up); free(m->h); free(m->tmp); free(m->logits);
+    free(m);
+}
+
+/* name follows GGUF tensor names for arch llama (gguf-py constants.py:1550-1569) */
+int oracle_model_set_tensor(oracle_model *m, const char *name, int type, int64_t ne0, int64_t ne1, const void *data) {
+    otensor t = {type, ne0, ne1, data};
+    if (!strcmp(name, "token_embd.weight")) { m->tok_embd = t; return 0; }
+    if (!strcmp(name, "output_norm.weight")) { m->output_norm = t; return 0; }
+    if (!strcmp(name, "output.weight")) { m->output = t; return 0; }
+    int il;
+    char rest[64];
+    if (sscanf(name, "blk.%d.%63s", &il, rest) == 2 && il >= 0 && il < m->hp.n_layer) {
+        olayer *l = &m->layers[il];
+        if (!strcmp(rest, "attn_norm.weight")) l->attn_norm = t;
+        else if (!strcmp(rest, "attn_q.weight")) l->wq = t;
+        else if (!strcmp(rest, "attn_k.weight")) l->wk = t;
+        else if (!strcmp(rest, "attn_v.weight")) l->wv = t;
+        else if (!strcmp(rest, "attn_output.weight")) l->wo = t;
+        else if (!strcmp(rest, "ffn_norm.weight")) l->ffn_norm = t;
+        else if (!strcmp(rest, "ffn_gate.weight")) l->w_gate = t;
+        else if (!strcmp(rest, "ffn_up.weight")) l->w_up = t;
+        else if (!strcmp(rest, "ffn_down.weight")) l->w_down = t;
+        else return -1;
+        return 0;
+    }
+    return -1;
+}
+
+/* RMSNorm: sum of squares in double (ggml_float), scale = 1/sqrtf(mean+eps); then the
+ * separate elementwise multiply by the norm weight (Appendix C.4). */
+static void rms_norm_mul(const float *x, const float *w, float *y, int n, float eps) {
+    double sum = 0.0;
+    for (int i = 0; i < n; i++) sum += (double)(x[i] * x[i]);
+    const float mean = (float)(sum / n);
+    const float scale = 1.0f / sqrtf(mean + eps);
+    for (int i = 0; i < n; i++) y[i] = (x[i] * scale) * w[i];
+}
+
+/* RoPE, NORM flavour: adjacent pairs, theta_i = pos * base^(-2i/n_rot) built by repeated
+ * multiplication in f32 (Appendix C.3). */
+void oracle_rope_table(int pos, int n_rot, float freq_base, float *cos_out, float *sin_out) {
+    const float theta_scale = powf(freq_base, -2.0f / (float)n_rot);
+    float theta = (float)pos;
+    for (int i = 0; i < n_rot / 2; i++) {
+        cos_out[i] = cosf(theta);
+        sin_out[i] = sinf(theta);
+        theta *= theta_scale;
+    }
+}
+static void rope_inplace(float *v, int n_heads, int head_dim, int n_rot, const float *c, const float *s) {
+    for (int h = 0; h < n_heads; h++) {
+        float *p = v + (size_t)h * head_dim;
+        for (int i = 0; i < n_rot / 2; i++) {
+            const float x0 = p[2 * i], x1 = p[2 * i + 1];
+            p[2 * i] = x0 * c[i] - x1 * s[i];
+            p[2 * i + 1] = x0 * s[i] + x1 * c[i];
+        }
+    }
+}
+
+static void embed_row(const otensor *t, int tok, float *out) {
+    const size_t rb = row_bytes(t->type, t->ne0);
+    oracle_dequantize(t->type, (const char *)t->data + (size_t)tok * rb, t->ne0, out);
+}
+
+/* one token through the whole stack at position `pos`; logits (if non-NULL) get n_vocab floats */
+static int eval_token(oracle_model *m, int tok, int pos, float *logits) {
+    const oracle_hparams *hp = &m->hp;
+    const int E = hp->n_embd, H = hp->n_head, G = hp->n_head_kv, D = hp->head_dim, FF = hp->n_ff;
+    const int kvd = G * D, rep = H / G;
+    if (pos >= hp->n_ctx || tok < 0 || tok >= hp->n_vocab) return -1;
+    float cs[512], sn[512];
+    oracle_rope_table(pos, hp->n_rot, hp->rope_freq_base, cs, sn);
+    embed_row(&m->tok_embd, tok, m->x);
+    const float kq_scale = 1.0f / sqrtf((float)D);
+    for (int il = 0; il < hp->n_layer; il++) {
+        const olayer *l = &m->layers[il];
+        rms_norm_mul(m->x, (const float *)l->attn_norm.data, m->xn, E, hp->rms_eps);
+        oracle_matvec(l->wq.type, l->wq.data, (int64_t)H * D, E, m->xn, m->q);
+        oracle_matvec(l->wk.type, l->wk.data, kvd, E, m->xn, m->k);
+        oracle_matvec(l->wv.type, l->wv.data, kvd, E, m->xn, m->v);
+        rope_inplace(m->q, H, D, hp->n_rot, cs, sn);
+        rope_inplace(m->k, G, D, hp->n_rot, cs, sn);
+        uint16_t *kc = m->k_cache + ((size_t)il * hp->n_ctx) * kvd;
+        uint16_t *vc = m->v_cache + ((size_t)il * hp->n_ctx) * kvd;
+        for (int i = 0; i < kvd; i++) {
+            kc[(size_t)pos * kvd + i] = f2h(m->k[i]);
+            vc[(size_t)pos * kvd + i] = f2h(m->v[i]);
+        }
+        const int n_kv = pos + 1;
+#pragma omp parallel for schedule(static)
+        for (int h = 0; h < H; h++) {
+            const int g = h / rep;
+            float *sc = m->scores + (size_t)h * hp->n_ctx;
+            float qh[512];
+            for (int d = 0; d < D; d++) qh[d] = h2f(f2h(m->q[(size_t)h * D + d])); /* q -> f16 (vec_dot_type of an f16 K) */
+            float mx = -INFINITY;
+            for (int j = 0; j < n_kv; j++) {
+                const uint16_t *kr = kc + (size_t)j * kvd + (size_t)g * D;
+                float s = 0;
+                for (int d = 0; d < D; d++) s += qh[d] * h2f(kr[d]);
+                s *= kq_scale;
+                sc[j] = s;
+                if (s > mx) mx = s;
+            }
+            double sum = 0.0;
+            for (int j = 0; j < n_kv; j++) {
+                const float e = expf(sc[j] - mx);
+                sc[j] = e;
+                sum += (double)e;
+            }
+            const float inv = (float)(1.0 / sum);
+            float *o = m->att_out + (size_t)h * D;
+            for (int d = 0; d < D; d++) o[d] = 0;
+            for (int j = 0; j < n_kv; j++) {
+                const float p = h2f(f2h(sc[j] * inv)); /* P -> f16 before the f16 V mat-mul */
+                const uint16_t *vr = vc + (size_t)j * kvd + (size_t)g * D;
+                for (int d = 0; d < D; d++) o[d] += p * h2f(vr[d]);
+            }
+        }
+        oracle_matvec(l->wo.type, l->wo.data, E, (int64_t)H * D, m->att_out, m->tmp);
+        for (int i = 0; i < E; i++) m->x[i] += m->tmp[i];
+        rms_norm_mul(m->x, (const float *)l->ffn_norm.data, m->xn, E, hp->rms_eps);
+        oracle_matvec(l->w_gate.type, l->w_gate.data, FF, E, m->xn, m->gate);
+        oracle_matvec(l->w_up.type, l->w_up.data, FF, E, m->xn, m->up);
+        for (int i = 0; i < FF; i++) {
+            const float gx = m->gate[i];
+            m->h[i] = (gx / (1.0f + expf(-gx))) * m->up[i];
+        }
+        oracle_matvec(l->w_down.type, l->w_down.data, E, FF, m->h, m->tmp);
+        for (int i = 0; i < E; i++) m->x[i] += m->tmp[i];
+    }
+    if (logits) {
+        rms_norm_mul(m->x, (const float *)m->output_norm.data, m->xn, E, hp->rms_eps);
+        const otensor *out = m->output.data ? &m->output : &m->tok_embd; /* tied embeddings */
+        oracle_matvec(out->type, out->data, hp->n_vocab, E, m->xn, logits);
+    }
+    return 0;
+}
+
+/* evaluate n tokens at positions n_past..n_past+n-1; logits of the LAST token -> logits_out */
+int oracle_eval(oracle_model *m, const int32_t *tokens, int n, int n_past, float *logits_out) {
+    for (int i = 0; i < n; i++) {
+        const int last = (i == n - 1);
+        int rc = eval_token(m, tokens[i], n_past + i, last ? (logits_out ? logits_out : m->logits) : NULL);
+        if (rc) return rc;
+    }
+    return 0;
+}
+
+/* logits of every token (for per-position parity checks): logits_out[n][n_vocab] */
+int oracle_eval_all(oracle_model *m, const int32_t *tokens, int n, int n_past, float *logits_out) {
+    for (int i = 0; i < n; i++) {
+        int rc = eval_token(m, tokens[i], n_past + i, logits_out + (size_t)i * m->hp.n_vocab);
+        if (rc) return rc;
+    }
+    return 0;
+}
+
+static int argmax_first(const float *v, int n, float *margin) {
+    int best = 0;
+    for (int i = 1; i < n; i++) if (v[i] > v[best]) best = i; /* lowest index wins ties */
+    if (margin) {
+        float second = -INFINITY;
+        for (int i = 0; i < n; i++) if (i != best && v[i] > second) second = v[i];
+        *margin = v[best] - second;
+    }
+    return best;
+}
+
+/* greedy: prefill prompt, then n_gen argmax tokens; margins[i] = top1-top2 logit gap at step i */
+int oracle_greedy(oracle_model *m, const int32_t *prompt, int n_prompt, int n_gen, int32_t *out, float *margins) {
+    int rc = oracle_eval(m, prompt, n_prompt, 0, m->logits);
+    if (rc) return rc;
+    int pos = n_prompt;
+    for (int i = 0; i < n_gen; i++) {
+        float mg;
+        const int t = argmax_first(m->logits, m->hp.n_vocab, &mg);
+        out[i] = t;
+        if (margins) margins[i] = mg;
+        if (i + 1 < n_gen) {
+            rc = eval_token(m, t, pos++, m->logits);
+            if (rc) return rc;
+        }
+    }
+    return 0;
+}
+
+const uint16_t *oracle_k_cache(const oracle_model *m) { return m->k_cache; }
+const uint16_t *oracle_v_cache(const oracle_model *m) { return m->v_cache; }
+int oracle_num_threads(void) {
+#ifdef _OPENMP
+    return omp_get_max_threads();
+#else
+    return 1;
+#endif
+}
+void oracle_set_threads(int n) {
+#ifdef _OPENMP
+    if (n > 0) omp_set_num_threads(n);
+#else
+    (void)n;
+#endif
+}
