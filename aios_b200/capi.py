@@ -1,0 +1,272 @@
+"""ctypes binding of include/aios_b200.h (libaios_b200.so).
+
+This is the Python stand-in for the Rust ``-sys`` crate a maintainer of the reference's
+``runtime`` crate would write; the gRPC shim (aios_b200.runtime) and the
+tests call the engine only through these functions.  There is no CPU fallback: if the
+shared library is missing, importing a function from it raises.
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libaios_b200.so")
+
+AIOS_OK, E_INVAL, E_IO, E_FORMAT, E_CUDA, E_NOMEM, E_STATE, E_RANGE = 0, -1, -2, -3, -4, -5, -6, -7
+TYPE_F32, TYPE_F16, TYPE_Q8_0, TYPE_Q4_K, TYPE_Q5_K, TYPE_Q6_K = 0, 1, 8, 12, 13, 14
+ENGINE_NO_GRAPH = 1
+
+
+class AiosError(RuntimeError):
+    def __init__(self, code: int, msg: str):
+        super().__init__(f"aios_b200 error {code}: {msg}")
+        self.code = code
+        self.msg = msg
+
+
+class EngineOpts(C.Structure):
+    _fields_ = [("device", C.c_int32), ("max_batch", C.c_int32), ("flags", C.c_int32), ("reserved", C.c_int32)]
+
+
+class ModelInfo(C.Structure):
+    _fields_ = [("name", C.c_char * 128), ("arch", C.c_char * 32)] + \
+               [(n, C.c_int32) for n in ("n_layer", "n_embd", "n_head", "n_head_kv", "head_dim", "n_ff", "n_vocab",
+                                         "n_ctx", "n_rot", "file_type", "n_tensors", "max_batch")] + \
+               [("rms_eps", C.c_float), ("rope_freq_base", C.c_float)] + \
+               [(n, C.c_int64) for n in ("file_bytes", "weight_bytes", "kv_bytes", "weight_bytes_per_token",
+                                         "kv_bytes_per_position")]
+
+
+class TensorInfo(C.Structure):
+    _fields_ = [("name", C.c_char * 96), ("type", C.c_int32), ("n_dims", C.c_int32), ("ne", C.c_int64 * 4),
+                ("offset", C.c_int64), ("nbytes", C.c_int64)]
+
+
+class Sampling(C.Structure):
+    _fields_ = [("temperature", C.c_float), ("top_k", C.c_int32), ("top_p", C.c_float), ("min_p", C.c_float),
+                ("seed", C.c_uint64)]
+
+
+class BenchResult(C.Structure):
+    _fields_ = [("ms_total", C.c_float), ("n_tokens", C.c_int32), ("kernel_launches", C.c_int32),
+                ("n_past_begin", C.c_int32), ("n_past_end", C.c_int32), ("ms_gemv", C.c_float),
+                ("reserved", C.c_float * 3)]
+
+
+# every symbol include/aios_b200.h declares: name -> (restype, argtypes)
+_P = C.c_void_p
+SYMBOLS = {
+    "aios_last_error": (C.c_char_p, []),
+    "aios_version": (C.c_char_p, []),
+    "aios_device_count": (C.c_int, [C.POINTER(C.c_int32)]),
+    "aios_engine_create": (C.c_int, [C.POINTER(EngineOpts), C.POINTER(_P)]),
+    "aios_engine_destroy": (None, [_P]),
+    "aios_model_load": (C.c_int, [_P, C.c_char_p, C.c_char_p, C.c_int32, C.POINTER(_P)]),
+    "aios_model_unload": (C.c_int, [_P]),
+    "aios_model_info_get": (C.c_int, [_P, C.POINTER(ModelInfo)]),
+    "aios_model_tensor_info": (C.c_int, [_P, C.c_int32, C.POINTER(TensorInfo)]),
+    "aios_seq_create": (C.c_int, [_P, C.POINTER(_P)]),
+    "aios_seq_free": (None, [_P]),
+    "aios_seq_reset": (C.c_int, [_P]),
+    "aios_seq_position": (C.c_int, [_P, C.POINTER(C.c_int32)]),
+    "aios_seq_prefill": (C.c_int, [_P, _P, C.c_int32]),
+    "aios_seq_decode": (C.c_int, [_P, C.POINTER(Sampling), C.c_int32, _P, C.POINTER(C.c_int32)]),
+    "aios_seq_step": (C.c_int, [_P, C.POINTER(Sampling), C.POINTER(C.c_int32)]),
+    "aios_seq_logits": (C.c_int, [_P, _P]),
+    "aios_generate": (C.c_int, [_P, _P, C.c_int32, C.POINTER(Sampling), C.c_int32, _P, C.POINTER(C.c_int32)]),
+    "aios_dequantize": (C.c_int, [_P, C.c_int32, _P, C.c_int64, _P]),
+    "aios_matvec": (C.c_int, [_P, C.c_int32, _P, C.c_int64, C.c_int64, _P, _P, C.c_float, _P]),
+    "aios_forward_logits": (C.c_int, [_P, _P, C.c_int32, C.c_int32, _P]),
+    "aios_seq_read_kv": (C.c_int, [_P, C.c_int32, C.c_int32, C.c_int32, _P, _P]),
+    "aios_seq_read_activation": (C.c_int, [_P, C.c_int32, _P, C.c_int64]),
+    "aios_seq_bench_decode": (C.c_int, [_P, C.c_int32, C.POINTER(BenchResult)]),
+    "aios_seq_profile_decode": (C.c_int, [_P, C.c_int32, C.POINTER(BenchResult)]),
+    "aios_seq_snapshot": (C.c_int, [_P]),
+    "aios_seq_restore": (C.c_int, [_P]),
+    "aios_bench_gemv": (C.c_int, [_P, C.c_int32, C.c_int64, C.c_int64, C.c_int32, C.c_int32, C.POINTER(C.c_float)]),
+}
+
+_lib = None
+
+
+def lib():
+    """Load libaios_b200.so (fails loudly if it has not been built: run __graft_entry__.build())."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise ImportError(f"{LIB_PATH} is missing: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+                              "(there is no CPU fallback)")
+        L = C.CDLL(LIB_PATH)
+        for name, (res, args) in SYMBOLS.items():
+            fn = getattr(L, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = L
+    return _lib
+
+
+def _check(rc: int):
+    if rc != 0:
+        raise AiosError(rc, (lib().aios_last_error() or b"").decode("utf-8", "replace"))
+
+
+def _ptr(a: np.ndarray):
+    return a.ctypes.data_as(C.c_void_p)
+
+
+def device_count() -> int:
+    n = C.c_int32(0)
+    _check(lib().aios_device_count(C.byref(n)))
+    return n.value
+
+
+def make_sampling(temperature=0.0, top_k=40, top_p=0.95, min_p=0.05, seed=0) -> Sampling:
+    return Sampling(float(temperature), int(top_k), float(top_p), float(min_p), int(seed))
+
+
+class Engine:
+    def __init__(self, device: int = 0, max_batch: int = 1, flags: int = 0):
+        self.h = _P()
+        opts = EngineOpts(device, max_batch, flags, 0)
+        _check(lib().aios_engine_create(C.byref(opts), C.byref(self.h)))
+
+    def close(self):
+        if self.h:
+            lib().aios_engine_destroy(self.h)
+            self.h = _P()
+
+    def dequantize(self, qtype: int, blocks: np.ndarray, n: int) -> np.ndarray:
+        blocks = np.ascontiguousarray(blocks, dtype=np.uint8).reshape(-1)
+        out = np.empty(n, dtype=np.float32)
+        _check(lib().aios_dequantize(self.h, qtype, _ptr(blocks), n, _ptr(out)))
+        return out
+
+    def matvec(self, qtype: int, w_blocks: np.ndarray, n_rows: int, k: int, x: np.ndarray, norm_w=None,
+               eps: float = 1e-5) -> np.ndarray:
+        w = np.ascontiguousarray(w_blocks, dtype=np.uint8).reshape(-1)
+        x = np.ascontiguousarray(x, dtype=np.float32)
+        y = np.empty(n_rows, dtype=np.float32)
+        nw = None
+        if norm_w is not None:
+            nw = np.ascontiguousarray(norm_w, dtype=np.float32)
+        _check(lib().aios_matvec(self.h, qtype, _ptr(w), n_rows, k, _ptr(x), _ptr(nw) if nw is not None else None,
+                                 eps, _ptr(y)))
+        return y
+
+    def bench_gemv(self, qtype: int, n_rows: int, k: int, n_copies: int, iters: int) -> float:
+        ms = C.c_float(0)
+        _check(lib().aios_bench_gemv(self.h, qtype, n_rows, k, n_copies, iters, C.byref(ms)))
+        return ms.value
+
+    def load_model(self, name: str, path: str, n_ctx: int = 0) -> "Model":
+        return Model(self, name, path, n_ctx)
+
+
+class Model:
+    def __init__(self, engine: Engine, name: str, path: str, n_ctx: int = 0):
+        self.engine = engine
+        self.h = _P()
+        _check(lib().aios_model_load(engine.h, name.encode(), path.encode(), n_ctx, C.byref(self.h)))
+        self.info = ModelInfo()
+        _check(lib().aios_model_info_get(self.h, C.byref(self.info)))
+
+    def unload(self):
+        if self.h:
+            _check(lib().aios_model_unload(self.h))
+            self.h = _P()
+
+    def tensor_info(self, i: int) -> TensorInfo:
+        t = TensorInfo()
+        _check(lib().aios_model_tensor_info(self.h, i, C.byref(t)))
+        return t
+
+    def new_seq(self) -> "Seq":
+        return Seq(self)
+
+    def forward_logits(self, tokens, n_past: int = 0) -> np.ndarray:
+        toks = np.ascontiguousarray(tokens, dtype=np.int32)
+        out = np.empty(self.info.n_vocab, dtype=np.float32)
+        _check(lib().aios_forward_logits(self.h, _ptr(toks), toks.size, n_past, _ptr(out)))
+        return out
+
+    def generate(self, prompt, max_tokens: int, sampling: Sampling | None = None) -> np.ndarray:
+        toks = np.ascontiguousarray(prompt, dtype=np.int32)
+        out = np.empty(max(max_tokens, 1), dtype=np.int32)
+        n = C.c_int32(0)
+        sp = sampling if sampling is not None else Sampling()
+        _check(lib().aios_generate(self.h, _ptr(toks), toks.size, C.byref(sp), max_tokens, _ptr(out), C.byref(n)))
+        return out[: n.value].copy()
+
+
+class Seq:
+    def __init__(self, model: Model):
+        self.model = model
+        self.h = _P()
+        _check(lib().aios_seq_create(model.h, C.byref(self.h)))
+
+    def free(self):
+        if self.h:
+            lib().aios_seq_free(self.h)
+            self.h = _P()
+
+    def reset(self):
+        _check(lib().aios_seq_reset(self.h))
+
+    @property
+    def n_past(self) -> int:
+        n = C.c_int32(0)
+        _check(lib().aios_seq_position(self.h, C.byref(n)))
+        return n.value
+
+    def prefill(self, tokens):
+        toks = np.ascontiguousarray(tokens, dtype=np.int32)
+        _check(lib().aios_seq_prefill(self.h, _ptr(toks), toks.size))
+
+    def decode(self, max_tokens: int, sampling: Sampling | None = None) -> np.ndarray:
+        out = np.empty(max(max_tokens, 1), dtype=np.int32)
+        n = C.c_int32(0)
+        sp = sampling if sampling is not None else Sampling()
+        _check(lib().aios_seq_decode(self.h, C.byref(sp), max_tokens, _ptr(out), C.byref(n)))
+        return out[: n.value].copy()
+
+    def step(self, sampling: Sampling | None = None) -> int:
+        t = C.c_int32(0)
+        sp = sampling if sampling is not None else Sampling()
+        _check(lib().aios_seq_step(self.h, C.byref(sp), C.byref(t)))
+        return t.value
+
+    def logits(self) -> np.ndarray:
+        out = np.empty(self.model.info.n_vocab, dtype=np.float32)
+        _check(lib().aios_seq_logits(self.h, _ptr(out)))
+        return out
+
+    def read_kv(self, layer: int, pos0: int, n: int):
+        kvd = self.model.info.n_head_kv * self.model.info.head_dim
+        k = np.empty((n, kvd), dtype=np.uint16)
+        v = np.empty((n, kvd), dtype=np.uint16)
+        _check(lib().aios_seq_read_kv(self.h, layer, pos0, n, _ptr(k), _ptr(v)))
+        return k, v
+
+    def read_activation(self, which: int, n: int) -> np.ndarray:
+        out = np.empty(n, dtype=np.float32)
+        _check(lib().aios_seq_read_activation(self.h, which, _ptr(out), n))
+        return out
+
+    def profile_decode(self, n_tokens: int) -> BenchResult:
+        r = BenchResult()
+        _check(lib().aios_seq_profile_decode(self.h, n_tokens, C.byref(r)))
+        return r
+
+    def snapshot(self):
+        _check(lib().aios_seq_snapshot(self.h))
+
+    def restore(self):
+        _check(lib().aios_seq_restore(self.h))
+
+    def bench_decode(self, n_tokens: int) -> BenchResult:
+        r = BenchResult()
+        _check(lib().aios_seq_bench_decode(self.h, n_tokens, C.byref(r)))
+        return r

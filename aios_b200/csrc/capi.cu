@@ -1,0 +1,405 @@
+// capi.cu — the extern "C" boundary declared in include/aios_b200.h.  Every entry point catches
+// all C++ exceptions and turns them into an AIOS_E_* code + thread-local message.
+#include <string.h>
+
+#include <random>
+#include <string>
+#include <vector>
+
+#include "../../include/aios_b200.h"
+#include "common.cuh"
+#include "engine.h"
+
+using namespace aios;
+
+struct aios_engine { Engine impl; explicit aios_engine(const aios_engine_opts &o) : impl(o) {} };
+struct aios_model {
+    Model impl;
+    std::unique_ptr<Seq> scratch;  // for aios_forward_logits
+    aios_model(Engine *e, const char *n, const char *p, int c) : impl(e, n, p, c) {}
+};
+struct aios_seq { Seq impl; explicit aios_seq(Model *m) : impl(m) {} };
+
+static thread_local std::string g_err;
+
+static int fail(int code, const std::string &msg) {
+    g_err = msg;
+    return code;
+}
+
+template <typename F>
+static int guarded(F &&f) {
+    try {
+        g_err.clear();
+        return f();
+    } catch (const GgufError &e) {
+        return fail(e.code, e.what());
+    } catch (const CudaError &e) {
+        cudaGetLastError();  // clear the sticky flag of non-fatal errors
+        return fail(AIOS_E_CUDA, e.what());
+    } catch (const std::invalid_argument &e) {
+        return fail(AIOS_E_INVAL, e.what());
+    } catch (const std::bad_alloc &) {
+        return fail(AIOS_E_NOMEM, "out of host memory");
+    } catch (const std::exception &e) {
+        return fail(AIOS_E_STATE, e.what());
+    } catch (...) {
+        return fail(AIOS_E_STATE, "unknown error");
+    }
+}
+
+extern "C" {
+
+const char *aios_last_error(void) { return g_err.c_str(); }
+const char *aios_version(void) { return "aios_b200 0.1 sm_100a"; }
+
+int aios_device_count(int32_t *n) {
+    return guarded([&] {
+        if (!n) return fail(AIOS_E_INVAL, "n is null");
+        int c = 0;
+        cudaError_t e = cudaGetDeviceCount(&c);
+        if (e != cudaSuccess) { cudaGetLastError(); c = 0; }
+        *n = c;
+        return AIOS_OK;
+    });
+}
+
+int aios_engine_create(const aios_engine_opts *opts, aios_engine **out) {
+    return guarded([&] {
+        if (!out) return fail(AIOS_E_INVAL, "out is null");
+        aios_engine_opts o{};
+        if (opts) o = *opts;
+        *out = new aios_engine(o);
+        return AIOS_OK;
+    });
+}
+
+void aios_engine_destroy(aios_engine *e) { delete e; }
+
+int aios_model_load(aios_engine *e, const char *name, const char *gguf_path, int32_t n_ctx, aios_model **out) {
+    return guarded([&] {
+        if (!e || !gguf_path || !out) return fail(AIOS_E_INVAL, "null argument");
+        std::lock_guard<std::mutex> lk(e->impl.mu);
+        *out = new aios_model(&e->impl, name ? name : "", gguf_path, n_ctx);
+        return AIOS_OK;
+    });
+}
+
+int aios_model_unload(aios_model *m) {
+    return guarded([&] {
+        if (!m) return fail(AIOS_E_INVAL, "null model");
+        m->scratch.reset();
+        for (bool u : m->impl.slot_used)
+            if (u) return fail(AIOS_E_STATE, "model still has live sequences");
+        delete m;
+        return AIOS_OK;
+    });
+}
+
+int aios_model_info_get(const aios_model *m, aios_model_info *o) {
+    return guarded([&] {
+        if (!m || !o) return fail(AIOS_E_INVAL, "null argument");
+        memset(o, 0, sizeof(*o));
+        const Model &M = m->impl;
+        strncpy(o->name, M.name.c_str(), sizeof(o->name) - 1);
+        strncpy(o->arch, M.arch.c_str(), sizeof(o->arch) - 1);
+        o->n_layer = M.hp.n_layer; o->n_embd = M.hp.n_embd; o->n_head = M.hp.n_head; o->n_head_kv = M.hp.n_head_kv;
+        o->head_dim = M.hp.head_dim; o->n_ff = M.hp.n_ff; o->n_vocab = M.hp.n_vocab; o->n_ctx = M.hp.n_ctx;
+        o->n_rot = M.hp.n_rot; o->file_type = M.hp.file_type; o->n_tensors = (int32_t)M.file->tensors().size();
+        o->max_batch = M.eng->max_batch; o->rms_eps = M.hp.rms_eps; o->rope_freq_base = M.hp.rope_freq_base;
+        o->file_bytes = (int64_t)M.file->file_bytes(); o->weight_bytes = M.weight_bytes; o->kv_bytes = (int64_t)M.kv.bytes;
+        o->weight_bytes_per_token = M.weight_bytes_per_token;
+        o->kv_bytes_per_position = (int64_t)M.hp.n_layer * 2 * M.hp.n_head_kv * M.hp.head_dim * 2;
+        return AIOS_OK;
+    });
+}
+
+int aios_model_tensor_info(const aios_model *m, int32_t i, aios_tensor_info *o) {
+    return guarded([&] {
+        if (!m || !o) return fail(AIOS_E_INVAL, "null argument");
+        const auto &ts = m->impl.file->tensors();
+        if (i < 0 || (size_t)i >= ts.size()) return fail(AIOS_E_INVAL, "tensor index out of range");
+        memset(o, 0, sizeof(*o));
+        strncpy(o->name, ts[i].name.c_str(), sizeof(o->name) - 1);
+        o->type = ts[i].type; o->n_dims = ts[i].n_dims;
+        for (int d = 0; d < 4; d++) o->ne[d] = ts[i].ne[d];
+        o->offset = (int64_t)ts[i].offset; o->nbytes = (int64_t)ts[i].nbytes;
+        return AIOS_OK;
+    });
+}
+
+int aios_seq_create(aios_model *m, aios_seq **out) {
+    return guarded([&] {
+        if (!m || !out) return fail(AIOS_E_INVAL, "null argument");
+        std::lock_guard<std::mutex> lk(m->impl.eng->mu);
+        *out = new aios_seq(&m->impl);
+        return AIOS_OK;
+    });
+}
+void aios_seq_free(aios_seq *s) {
+    if (!s) return;
+    std::lock_guard<std::mutex> lk(s->impl.m->eng->mu);
+    delete s;
+}
+int aios_seq_reset(aios_seq *s) {
+    return guarded([&] {
+        if (!s) return fail(AIOS_E_INVAL, "null seq");
+        std::lock_guard<std::mutex> lk(s->impl.m->eng->mu);
+        s->impl.reset();
+        return AIOS_OK;
+    });
+}
+int aios_seq_position(const aios_seq *s, int32_t *n_past) {
+    if (!s || !n_past) return fail(AIOS_E_INVAL, "null argument");
+    *n_past = s->impl.n_past;
+    return AIOS_OK;
+}
+int aios_seq_prefill(aios_seq *s, const int32_t *tokens, int32_t n) {
+    return guarded([&] {
+        if (!s || (!tokens && n > 0) || n < 0) return fail(AIOS_E_INVAL, "bad argument");
+        if (s->impl.n_past + n > s->impl.m->hp.n_ctx) return fail(AIOS_E_STATE, "prompt does not fit in the context");
+        std::lock_guard<std::mutex> lk(s->impl.m->eng->mu);
+        s->impl.prefill(tokens, n);
+        return AIOS_OK;
+    });
+}
+int aios_seq_decode(aios_seq *s, const aios_sampling *sp, int32_t max_tokens, int32_t *out_tokens, int32_t *n_out) {
+    return guarded([&] {
+        if (!s || !out_tokens || !n_out || max_tokens < 0) return fail(AIOS_E_INVAL, "bad argument");
+        aios_sampling d{};
+        if (sp) d = *sp;
+        std::lock_guard<std::mutex> lk(s->impl.m->eng->mu);
+        *n_out = s->impl.decode(d, max_tokens, out_tokens);
+        return AIOS_OK;
+    });
+}
+int aios_seq_step(aios_seq *s, const aios_sampling *sp, int32_t *token_out) {
+    return guarded([&] {
+        if (!s || !token_out) return fail(AIOS_E_INVAL, "bad argument");
+        aios_sampling d{};
+        if (sp) d = *sp;
+        std::lock_guard<std::mutex> lk(s->impl.m->eng->mu);
+        s->impl.step(d, token_out);
+        return AIOS_OK;
+    });
+}
+int aios_seq_logits(aios_seq *s, float *logits_out) {
+    return guarded([&] {
+        if (!s || !logits_out) return fail(AIOS_E_INVAL, "bad argument");
+        std::lock_guard<std::mutex> lk(s->impl.m->eng->mu);
+        s->impl.read_logits(logits_out);
+        return AIOS_OK;
+    });
+}
+
+int aios_generate(aios_model *m, const int32_t *prompt, int32_t n_prompt, const aios_sampling *sp, int32_t max_tokens,
+                  int32_t *out_tokens, int32_t *n_out) {
+    return guarded([&] {
+        if (!m || !prompt || n_prompt <= 0 || !out_tokens || !n_out) return fail(AIOS_E_INVAL, "bad argument");
+        if (n_prompt > m->impl.hp.n_ctx) return fail(AIOS_E_STATE, "prompt does not fit in the context");
+        aios_sampling d{};
+        if (sp) d = *sp;
+        std::lock_guard<std::mutex> lk(m->impl.eng->mu);
+        Seq s(&m->impl);
+        s.prefill(prompt, n_prompt);
+        *n_out = s.decode(d, max_tokens, out_tokens);
+        return AIOS_OK;
+    });
+}
+
+int aios_dequantize(aios_engine *e, int32_t type, const void *blocks, int64_t n, float *out) {
+    return guarded([&] {
+        if (!e || !blocks || !out || n < 0) return fail(AIOS_E_INVAL, "bad argument");
+        const int be = type_block_elems(type), bb = type_block_bytes(type);
+        if (!bb) return fail(AIOS_E_INVAL, "unsupported ggml type");
+        if (n % be) return fail(AIOS_E_INVAL, "n is not a multiple of the block size");
+        if (n == 0) return (int)AIOS_OK;
+        std::lock_guard<std::mutex> lk(e->impl.mu);
+        e->impl.make_current();
+        const size_t nbytes = (size_t)(n / be) * bb;
+        DevBuf in(nbytes), o((size_t)n * 4);
+        cudaStream_t st = e->impl.stream;
+        CUDA_CHECK(cudaMemcpyAsync(in.p, blocks, nbytes, cudaMemcpyHostToDevice, st));
+        launch_dequantize(type, in.p, n, o.as<float>(), st);
+        CUDA_CHECK(cudaGetLastError());
+        CUDA_CHECK(cudaMemcpyAsync(out, o.p, (size_t)n * 4, cudaMemcpyDeviceToHost, st));
+        CUDA_CHECK(cudaStreamSynchronize(st));
+        return (int)AIOS_OK;
+    });
+}
+
+static void make_dev_matrix(Engine &E, int type, const void *host_blocks, int64_t n_rows, int64_t k, DevMatrix &dm) {
+    size_t total = 0, off[5];
+    for (int i = 0; i < 5; i++) { off[i] = total; total += (plane_bytes(type, i, n_rows, k) + 255) / 256 * 256; }
+    dm.storage = DevBuf(total);
+    uint8_t *planes[5];
+    for (int i = 0; i < 5; i++) {
+        planes[i] = plane_bytes(type, i, n_rows, k) ? dm.storage.as<uint8_t>() + off[i] : nullptr;
+        dm.w.p[i] = planes[i];
+    }
+    dm.w.type = type; dm.w.n_rows = (int32_t)n_rows; dm.w.k = (int32_t)k;
+    const size_t nbytes = tensor_bytes(type, n_rows, k);
+    DevBuf raw(nbytes);
+    CUDA_CHECK(cudaMemcpyAsync(raw.p, host_blocks, nbytes, cudaMemcpyHostToDevice, E.stream));
+    launch_repack(type, raw.p, n_rows, (int)k, planes, E.stream);
+    CUDA_CHECK(cudaGetLastError());
+    CUDA_CHECK(cudaStreamSynchronize(E.stream));
+}
+
+int aios_matvec(aios_engine *e, int32_t type, const void *w_blocks, int64_t n_rows, int64_t k, const float *x,
+                const float *norm_w, float rms_eps, float *y) {
+    return guarded([&] {
+        if (!e || !w_blocks || !x || !y || n_rows <= 0 || k <= 0) return fail(AIOS_E_INVAL, "bad argument");
+        if (!(type == T_Q4_K || type == T_Q5_K || type == T_Q6_K || type == T_Q8_0)) return fail(AIOS_E_INVAL, "unsupported weight type");
+        if (k % 256) return fail(AIOS_E_INVAL, "k must be a multiple of 256");
+        if (gemv_smem_bytes((int)k) > 100 * 1024) return fail(AIOS_E_RANGE, "k too large");
+        std::lock_guard<std::mutex> lk(e->impl.mu);
+        Engine &E = e->impl;
+        E.make_current();
+        DevMatrix dm;
+        make_dev_matrix(E, type, w_blocks, n_rows, k, dm);
+        DevBuf dx((size_t)k * 4), dy((size_t)n_rows * 4), dn;
+        CUDA_CHECK(cudaMemcpyAsync(dx.p, x, (size_t)k * 4, cudaMemcpyHostToDevice, E.stream));
+        if (norm_w) {
+            dn = DevBuf((size_t)k * 4);
+            CUDA_CHECK(cudaMemcpyAsync(dn.p, norm_w, (size_t)k * 4, cudaMemcpyHostToDevice, E.stream));
+        }
+        GemvParams p{};
+        p.n_seg = 1; p.epi = EPI_STORE; p.k = (int32_t)k; p.seg[0] = dm.w; p.out[0] = dy.as<float>();
+        p.x = dx.as<float>(); p.norm_w = norm_w ? dn.as<float>() : nullptr; p.eps = rms_eps;
+        launch_gemv(p, gemv_plan_grid(p, E.n_sms), E.stream);
+        CUDA_CHECK(cudaGetLastError());
+        CUDA_CHECK(cudaMemcpyAsync(y, dy.p, (size_t)n_rows * 4, cudaMemcpyDeviceToHost, E.stream));
+        CUDA_CHECK(cudaStreamSynchronize(E.stream));
+        return (int)AIOS_OK;
+    });
+}
+
+int aios_forward_logits(aios_model *m, const int32_t *tokens, int32_t n, int32_t n_past, float *logits_out) {
+    return guarded([&] {
+        if (!m || !tokens || n <= 0 || !logits_out || n_past < 0) return fail(AIOS_E_INVAL, "bad argument");
+        std::lock_guard<std::mutex> lk(m->impl.eng->mu);
+        if (!m->scratch) m->scratch.reset(new Seq(&m->impl));
+        Seq &s = *m->scratch;
+        if (n_past == 0) s.reset();
+        else if (s.n_past != n_past) return fail(AIOS_E_STATE, "scratch sequence is at a different position");
+        if (s.n_past + n > m->impl.hp.n_ctx) return fail(AIOS_E_STATE, "tokens do not fit in the context");
+        s.prefill(tokens, n);
+        s.read_logits(logits_out);
+        return (int)AIOS_OK;
+    });
+}
+
+int aios_seq_read_kv(aios_seq *s, int32_t layer, int32_t pos0, int32_t n, uint16_t *k_out, uint16_t *v_out) {
+    return guarded([&] {
+        if (!s || !k_out || !v_out) return fail(AIOS_E_INVAL, "bad argument");
+        Model &M = *s->impl.m;
+        if (layer < 0 || layer >= M.hp.n_layer || pos0 < 0 || n < 0 || pos0 + n > M.hp.n_ctx) return fail(AIOS_E_INVAL, "range");
+        std::lock_guard<std::mutex> lk(M.eng->mu);
+        M.eng->make_current();
+        const size_t kvd = (size_t)M.hp.n_head_kv * M.hp.head_dim;
+        CUDA_CHECK(cudaMemcpy(k_out, M.k_cache(s->impl.slot, layer) + (size_t)pos0 * kvd, (size_t)n * kvd * 2, cudaMemcpyDeviceToHost));
+        CUDA_CHECK(cudaMemcpy(v_out, M.v_cache(s->impl.slot, layer) + (size_t)pos0 * kvd, (size_t)n * kvd * 2, cudaMemcpyDeviceToHost));
+        return (int)AIOS_OK;
+    });
+}
+
+int aios_seq_read_activation(aios_seq *s, int32_t which, float *out, int64_t n) {
+    return guarded([&] {
+        if (!s || !out || n < 0) return fail(AIOS_E_INVAL, "bad argument");
+        Seq &q = s->impl;
+        const DevBuf *b = which == 0 ? &q.x : which == 1 ? &q.qkv : which == 2 ? &q.att : which == 3 ? &q.h : nullptr;
+        if (!b) return fail(AIOS_E_INVAL, "unknown activation buffer");
+        if ((size_t)n * 4 > b->bytes) return fail(AIOS_E_RANGE, "n exceeds the buffer");
+        std::lock_guard<std::mutex> lk(q.m->eng->mu);
+        q.m->eng->make_current();
+        CUDA_CHECK(cudaMemcpy(out, b->p, (size_t)n * 4, cudaMemcpyDeviceToHost));
+        return (int)AIOS_OK;
+    });
+}
+
+int aios_seq_bench_decode(aios_seq *s, int32_t n_tokens, aios_bench_result *out) {
+    return guarded([&] {
+        if (!s || !out || n_tokens <= 0) return fail(AIOS_E_INVAL, "bad argument");
+        std::lock_guard<std::mutex> lk(s->impl.m->eng->mu);
+        s->impl.bench_decode(n_tokens, out);
+        return (int)AIOS_OK;
+    });
+}
+
+int aios_seq_profile_decode(aios_seq *s, int32_t n_tokens, aios_bench_result *out) {
+    return guarded([&] {
+        if (!s || !out || n_tokens <= 0) return fail(AIOS_E_INVAL, "bad argument");
+        std::lock_guard<std::mutex> lk(s->impl.m->eng->mu);
+        s->impl.profile_decode(n_tokens, out);
+        return (int)AIOS_OK;
+    });
+}
+int aios_seq_snapshot(aios_seq *s) {
+    return guarded([&] {
+        if (!s) return fail(AIOS_E_INVAL, "null seq");
+        std::lock_guard<std::mutex> lk(s->impl.m->eng->mu);
+        s->impl.snapshot();
+        return (int)AIOS_OK;
+    });
+}
+int aios_seq_restore(aios_seq *s) {
+    return guarded([&] {
+        if (!s) return fail(AIOS_E_INVAL, "null seq");
+        std::lock_guard<std::mutex> lk(s->impl.m->eng->mu);
+        s->impl.restore();
+        return (int)AIOS_OK;
+    });
+}
+
+int aios_bench_gemv(aios_engine *e, int32_t type, int64_t n_rows, int64_t k, int32_t n_copies, int32_t iters,
+                    float *ms_per_launch) {
+    return guarded([&] {
+        if (!e || !ms_per_launch || n_rows <= 0 || k <= 0 || n_copies <= 0 || iters <= 0) return fail(AIOS_E_INVAL, "bad argument");
+        if (!(type == T_Q4_K || type == T_Q5_K || type == T_Q6_K || type == T_Q8_0)) return fail(AIOS_E_INVAL, "unsupported weight type");
+        if (k % 256 || gemv_smem_bytes((int)k) > 100 * 1024) return fail(AIOS_E_RANGE, "bad k");
+        std::lock_guard<std::mutex> lk(e->impl.mu);
+        Engine &E = e->impl;
+        E.make_current();
+        // random but valid blocks: fp16 scale fields are overwritten with small finite values
+        const size_t nbytes = tensor_bytes(type, n_rows, k);
+        std::vector<uint8_t> host(nbytes);
+        std::mt19937_64 rng(1234);
+        for (size_t i = 0; i + 8 <= nbytes; i += 8) { uint64_t r = rng(); memcpy(&host[i], &r, 8); }
+        const int bb = type_block_bytes(type);
+        for (size_t b = 0; b < nbytes / bb; b++) {
+            uint8_t *blk = &host[b * bb];
+            const uint16_t small = 0x1400;  // 2^-10 as fp16
+            if (type == T_Q6_K) memcpy(blk + 208, &small, 2);
+            else { memcpy(blk, &small, 2); if (type != T_Q8_0) memcpy(blk + 2, &small, 2); }
+        }
+        std::vector<DevMatrix> ws((size_t)n_copies);
+        for (auto &w : ws) make_dev_matrix(E, type, host.data(), n_rows, k, w);
+        std::vector<float> hx((size_t)k);
+        for (auto &v : hx) v = (float)((int)(rng() % 2001) - 1000) / 1000.f;
+        DevBuf dx((size_t)k * 4), dy((size_t)n_rows * 4);
+        CUDA_CHECK(cudaMemcpy(dx.p, hx.data(), (size_t)k * 4, cudaMemcpyHostToDevice));
+        GemvParams p{};
+        p.n_seg = 1; p.epi = EPI_STORE; p.k = (int32_t)k; p.out[0] = dy.as<float>(); p.x = dx.as<float>();
+        p.seg[0] = ws[0].w;
+        const int grid = gemv_plan_grid(p, E.n_sms);
+        for (int i = 0; i < 3 * n_copies; i++) { p.seg[0] = ws[(size_t)i % n_copies].w; launch_gemv(p, grid, E.stream); }
+        cudaEvent_t e0, e1;
+        CUDA_CHECK(cudaEventCreate(&e0));
+        CUDA_CHECK(cudaEventCreate(&e1));
+        CUDA_CHECK(cudaStreamSynchronize(E.stream));
+        CUDA_CHECK(cudaEventRecord(e0, E.stream));
+        for (int i = 0; i < iters; i++) { p.seg[0] = ws[(size_t)i % n_copies].w; launch_gemv(p, grid, E.stream); }
+        CUDA_CHECK(cudaEventRecord(e1, E.stream));
+        CUDA_CHECK(cudaEventSynchronize(e1));
+        CUDA_CHECK(cudaGetLastError());
+        float ms = 0;
+        CUDA_CHECK(cudaEventElapsedTime(&ms, e0, e1));
+        cudaEventDestroy(e0);
+        cudaEventDestroy(e1);
+        *ms_per_launch = ms / (float)iters;
+        return (int)AIOS_OK;
+    });
+}
+
+}  // extern "C"

@@ -1,0 +1,93 @@
+// common.cuh — small device/host helpers shared by every kernel TU (sm_100a only).
+#pragma once
+#include <cuda_fp16.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <stdexcept>
+#include <string>
+
+#define AIOS_QK_K 256
+#define AIOS_QK8_0 32
+
+namespace aios {
+
+struct CudaError : std::runtime_error {
+    using std::runtime_error::runtime_error;
+};
+
+inline void cuda_check(cudaError_t e, const char *what, const char *file, int line) {
+    if (e != cudaSuccess) {
+        throw CudaError(std::string(what) + ": " + cudaGetErrorString(e) + " (" + file + ":" + std::to_string(line) + ")");
+    }
+}
+#define CUDA_CHECK(x) ::aios::cuda_check((x), #x, __FILE__, __LINE__)
+
+#ifdef __CUDACC__
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    return v;
+}
+
+// 128-bit streaming load of weights: read-only path, do not allocate in L1 (each byte is used once)
+__device__ __forceinline__ uint4 ldg_stream(const void *p) {
+    uint4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.v4.u32 {%0,%1,%2,%3}, [%4];"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+                 : "l"(p));
+    return r;
+}
+__device__ __forceinline__ uint32_t ldg_stream_u32(const void *p) {
+    uint32_t r;
+    asm volatile("ld.global.nc.L1::no_allocate.u32 %0, [%1];" : "=r"(r) : "l"(p));
+    return r;
+}
+__device__ __forceinline__ uint16_t ldg_stream_u16(const void *p) {
+    uint16_t r;
+    asm volatile("ld.global.nc.L1::no_allocate.u16 %0, [%1];" : "=h"(r) : "l"(p));
+    return r;
+}
+
+__device__ __forceinline__ double warp_sum_f64(double v) {
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// expf with a fixed operation sequence, bit-identical to oracle_expf() in oracle/aios_oracle.c
+// (CUDA's and glibc's expf differ in the last ulp, which is enough to flip a Q8 rounding
+// downstream): n = rint(x*log2e), two-step Cody-Waite reduction, degree-6 Horner, scale by 2^n.
+__device__ __forceinline__ float expf_det(float x) {
+    if (x < -87.0f) return 0.0f;
+    if (x > 88.0f) return __int_as_float(0x7f800000);
+    const float t = __fmul_rn(x, 1.44269504088896341f);
+    const float n = rintf(t);
+    float r = __fmaf_rn(n, -0.693145751953125f, x);
+    r = __fmaf_rn(n, -1.42860682030941723212e-6f, r);
+    float p = 1.0f / 720.0f;
+    p = __fmaf_rn(p, r, 1.0f / 120.0f);
+    p = __fmaf_rn(p, r, 1.0f / 24.0f);
+    p = __fmaf_rn(p, r, 1.0f / 6.0f);
+    p = __fmaf_rn(p, r, 0.5f);
+    p = __fmaf_rn(p, r, 1.0f);
+    p = __fmaf_rn(p, r, 1.0f);
+    const int ni = (int)n;
+    return __fmul_rn(p, __int_as_float((ni + 127) << 23));
+}
+
+__device__ __forceinline__ float h2f_bits(uint16_t h) { return __half2float(__ushort_as_half(h)); }
+__device__ __forceinline__ uint16_t f2h_bits(float f) { return __half_as_ushort(__float2half_rn(f)); }
+
+__device__ __forceinline__ int dp4a_su(uint32_t a_signed, uint32_t b_unsigned, int c) {
+    // signed x unsigned is not needed: all our "unsigned" operands are < 128, so s8 x s8 is exact
+    return __dp4a((int)a_signed, (int)b_unsigned, c);
+}
+#endif
+
+}  // namespace aios

@@ -1,0 +1,539 @@
+// engine.cu — see engine.h.
+#include "engine.h"
+
+#include <math.h>
+#include <string.h>
+
+#include <algorithm>
+
+#include "common.cuh"
+
+namespace aios {
+
+// ---------------------------------------------------------------- DevBuf / Engine
+DevBuf::DevBuf(size_t n) : bytes(n) {
+    if (n) {
+        cudaError_t e = cudaMalloc(&p, n);
+        if (e != cudaSuccess) {
+            p = nullptr;
+            bytes = 0;
+            throw CudaError(std::string("cudaMalloc(") + std::to_string(n) + " bytes): " + cudaGetErrorString(e));
+        }
+    }
+}
+DevBuf::~DevBuf() {
+    if (p) cudaFree(p);
+}
+DevBuf &DevBuf::operator=(DevBuf &&o) noexcept {
+    if (this != &o) {
+        if (p) cudaFree(p);
+        p = o.p;
+        bytes = o.bytes;
+        o.p = nullptr;
+        o.bytes = 0;
+    }
+    return *this;
+}
+
+Engine::Engine(const aios_engine_opts &o) : device(o.device), max_batch(o.max_batch > 0 ? o.max_batch : 1), flags(o.flags) {
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0) throw CudaError("no CUDA device is usable (this library has no CPU fallback)");
+    if (device < 0 || device >= n) throw CudaError("device ordinal out of range");
+    CUDA_CHECK(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    CUDA_CHECK(cudaGetDeviceProperties(&prop, device));
+    if (prop.major != 10) {
+        throw CudaError(std::string("device '") + prop.name + "' is sm_" + std::to_string(prop.major) +
+                        std::to_string(prop.minor) + "; this library is built for sm_100a (B200) only");
+    }
+    n_sms = prop.multiProcessorCount;
+    CUDA_CHECK(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+    gemv_init();
+    attn_init();
+}
+Engine::~Engine() {
+    if (stream) cudaStreamDestroy(stream);
+}
+void Engine::make_current() const { CUDA_CHECK(cudaSetDevice(device)); }
+
+// ---------------------------------------------------------------- Model
+static bool is_quant_matrix_type(int t) { return t == T_Q4_K || t == T_Q5_K || t == T_Q6_K || t == T_Q8_0; }
+
+static void alloc_planes(int type, int64_t n_rows, int64_t k, DevMatrix &dst) {
+    size_t total = 0, off[5];
+    for (int i = 0; i < 5; i++) {
+        off[i] = total;
+        total += (plane_bytes(type, i, n_rows, k) + 255) / 256 * 256;
+    }
+    dst.storage = DevBuf(total);
+    for (int i = 0; i < 5; i++)
+        dst.w.p[i] = plane_bytes(type, i, n_rows, k) ? dst.storage.as<uint8_t>() + off[i] : nullptr;
+    dst.w.type = type;
+    dst.w.n_rows = (int32_t)n_rows;
+    dst.w.k = (int32_t)k;
+}
+
+void Model::upload_matrix(const GgufTensor &t, DevMatrix &dst, DevBuf &staging, void *pinned, size_t pinned_bytes) {
+    if (!is_quant_matrix_type(t.type))
+        throw GgufError(AIOS_E_FORMAT, "tensor '" + t.name + "': matrix type " + std::to_string(t.type) +
+                                           " is not supported (Q4_K, Q5_K, Q6_K, Q8_0 are)");
+    if (t.n_dims != 2) throw GgufError(AIOS_E_FORMAT, "tensor '" + t.name + "' is not a matrix");
+    const int64_t k = t.ne[0], n = t.ne[1];
+    if (k % 256) throw GgufError(AIOS_E_FORMAT, "tensor '" + t.name + "': K must be a multiple of 256");
+    alloc_planes(t.type, n, k, dst);
+    dst.src_bytes = t.nbytes;
+    if (staging.bytes < t.nbytes) staging = DevBuf(t.nbytes);
+    cudaStream_t st = eng->stream;
+    for (size_t off = 0; off < t.nbytes; off += pinned_bytes) {
+        const size_t c = std::min(pinned_bytes, (size_t)t.nbytes - off);
+        memcpy(pinned, t.data + off, c);
+        CUDA_CHECK(cudaMemcpyAsync(staging.as<uint8_t>() + off, pinned, c, cudaMemcpyHostToDevice, st));
+        CUDA_CHECK(cudaStreamSynchronize(st));
+    }
+    uint8_t *planes[5];
+    for (int i = 0; i < 5; i++) planes[i] = const_cast<uint8_t *>(dst.w.p[i]);
+    launch_repack(t.type, staging.p, n, (int)k, planes, st);
+    CUDA_CHECK(cudaGetLastError());
+    CUDA_CHECK(cudaStreamSynchronize(st));
+    weight_bytes += (int64_t)dst.storage.bytes;
+    weight_bytes_per_token += (int64_t)t.nbytes;
+}
+
+static DevBuf upload_f32(const GgufTensor &t, int64_t expect, cudaStream_t st) {
+    if (t.type != T_F32 || t.ne[0] != expect)
+        throw GgufError(AIOS_E_FORMAT, "tensor '" + t.name + "' must be F32[" + std::to_string(expect) + "]");
+    DevBuf b((size_t)expect * 4);
+    CUDA_CHECK(cudaMemcpyAsync(b.p, t.data, (size_t)expect * 4, cudaMemcpyHostToDevice, st));
+    CUDA_CHECK(cudaStreamSynchronize(st));
+    return b;
+}
+
+Model::Model(Engine *e, const std::string &name_, const std::string &path_, int n_ctx) : eng(e), name(name_), path(path_) {
+    e->make_current();
+    file.reset(new GgufFile(path));
+    const GgufFile &f = *file;
+    arch = f.get_s("general.architecture", "");
+    if (arch != "llama") throw GgufError(AIOS_E_FORMAT, "unsupported architecture '" + arch + "' (only 'llama' is built)");
+    hp.n_layer = (int)f.get_u("llama.block_count", 0);
+    hp.n_embd = (int)f.get_u("llama.embedding_length", 0);
+    hp.n_head = (int)f.get_u("llama.attention.head_count", 0);
+    hp.n_head_kv = (int)f.get_u("llama.attention.head_count_kv", hp.n_head);
+    hp.n_ff = (int)f.get_u("llama.feed_forward_length", 0);
+    hp.rms_eps = (float)f.get_f("llama.attention.layer_norm_rms_epsilon", 1e-5);
+    hp.rope_freq_base = (float)f.get_f("llama.rope.freq_base", 10000.0);
+    hp.file_type = (int)f.get_u("general.file_type", 0);
+    if (!hp.n_layer || !hp.n_embd || !hp.n_head || !hp.n_ff || hp.n_embd % hp.n_head || hp.n_head % hp.n_head_kv)
+        throw GgufError(AIOS_E_FORMAT, "GGUF: missing or inconsistent llama.* hyper-parameters");
+    hp.head_dim = hp.n_embd / hp.n_head;
+    hp.n_rot = (int)f.get_u("llama.rope.dimension_count", hp.head_dim);
+    if (hp.head_dim != 64 && hp.head_dim != 128) throw GgufError(AIOS_E_FORMAT, "head_dim must be 64 or 128");
+    {
+        const int rep = hp.n_head / hp.n_head_kv;
+        if (rep != 1 && rep != 2 && rep != 4 && rep != 8)
+            throw GgufError(AIOS_E_FORMAT, "query heads per kv head must be 1, 2, 4 or 8");
+    }
+    if (hp.n_rot > hp.head_dim || hp.n_rot % 2) throw GgufError(AIOS_E_FORMAT, "bad rope dimension count");
+    hp.n_ctx = n_ctx > 0 ? n_ctx : 2048;  // reference default (model_manager.rs:167-171)
+    const GgufTensor &te = f.require("token_embd.weight");
+    hp.n_vocab = (int)te.ne[1];
+    if (te.ne[0] != hp.n_embd) throw GgufError(AIOS_E_FORMAT, "token_embd.weight has the wrong width");
+
+    cudaStream_t st = e->stream;
+    const size_t pinned_bytes = 64u << 20;
+    void *pinned = nullptr;
+    CUDA_CHECK(cudaMallocHost(&pinned, pinned_bytes));
+    DevBuf staging;
+    try {
+        // embedding table stays in GGUF's natural layout: one row is gathered per token
+        tok_embd_type = te.type;
+        tok_embd_row_bytes = (int64_t)(te.nbytes / (uint64_t)hp.n_vocab);
+        tok_embd_raw = DevBuf(te.nbytes);
+        for (size_t off = 0; off < te.nbytes; off += pinned_bytes) {
+            const size_t c = std::min(pinned_bytes, (size_t)te.nbytes - off);
+            memcpy(pinned, te.data + off, c);
+            CUDA_CHECK(cudaMemcpyAsync(tok_embd_raw.as<uint8_t>() + off, pinned, c, cudaMemcpyHostToDevice, st));
+            CUDA_CHECK(cudaStreamSynchronize(st));
+        }
+        weight_bytes += (int64_t)te.nbytes;
+        weight_bytes_per_token += tok_embd_row_bytes;
+
+        const int QD = hp.n_head * hp.head_dim, KVD = hp.n_head_kv * hp.head_dim;
+        layers.resize(hp.n_layer);
+        for (int i = 0; i < hp.n_layer; i++) {
+            const std::string p = "blk." + std::to_string(i) + ".";
+            Layer &L = layers[i];
+            L.attn_norm = upload_f32(f.require(p + "attn_norm.weight"), hp.n_embd, st);
+            L.ffn_norm = upload_f32(f.require(p + "ffn_norm.weight"), hp.n_embd, st);
+            weight_bytes_per_token += 2 * (int64_t)hp.n_embd * 4;
+            struct { const char *n; DevMatrix *d; int64_t rows, cols; } ms[] = {
+                {"attn_q.weight", &L.wq, QD, hp.n_embd},      {"attn_k.weight", &L.wk, KVD, hp.n_embd},
+                {"attn_v.weight", &L.wv, KVD, hp.n_embd},     {"attn_output.weight", &L.wo, hp.n_embd, QD},
+                {"ffn_gate.weight", &L.w_gate, hp.n_ff, hp.n_embd}, {"ffn_up.weight", &L.w_up, hp.n_ff, hp.n_embd},
+                {"ffn_down.weight", &L.w_down, hp.n_embd, hp.n_ff}};
+            for (auto &m : ms) {
+                const GgufTensor &t = f.require(p + m.n);
+                if (t.ne[0] != m.cols || t.ne[1] != m.rows)
+                    throw GgufError(AIOS_E_FORMAT, "tensor '" + t.name + "' has unexpected shape");
+                upload_matrix(t, *m.d, staging, pinned, pinned_bytes);
+            }
+            if (L.w_gate.w.type != L.w_up.w.type)
+                throw GgufError(AIOS_E_FORMAT, "ffn_gate and ffn_up of layer " + std::to_string(i) + " differ in type");
+        }
+        output_norm = upload_f32(f.require("output_norm.weight"), hp.n_embd, st);
+        weight_bytes_per_token += (int64_t)hp.n_embd * 4;
+        const GgufTensor *out = f.find("output.weight");
+        upload_matrix(out ? *out : te, output, staging, pinned, pinned_bytes);  // tied embeddings when absent
+    } catch (...) {
+        cudaFreeHost(pinned);
+        throw;
+    }
+    cudaFreeHost(pinned);
+
+    // RoPE table, built like the oracle (repeated multiplication by theta_scale, glibc cosf/sinf)
+    {
+        const int half = hp.n_rot / 2;
+        std::vector<float> c((size_t)hp.n_ctx * half), s((size_t)hp.n_ctx * half);
+        const float theta_scale = powf(hp.rope_freq_base, -2.0f / (float)hp.n_rot);
+        for (int pos = 0; pos < hp.n_ctx; pos++) {
+            float theta = (float)pos;
+            for (int i = 0; i < half; i++) {
+                c[(size_t)pos * half + i] = cosf(theta);
+                s[(size_t)pos * half + i] = sinf(theta);
+                theta *= theta_scale;
+            }
+        }
+        rope_cos = DevBuf(c.size() * 4);
+        rope_sin = DevBuf(s.size() * 4);
+        CUDA_CHECK(cudaMemcpy(rope_cos.p, c.data(), c.size() * 4, cudaMemcpyHostToDevice));
+        CUDA_CHECK(cudaMemcpy(rope_sin.p, s.data(), s.size() * 4, cudaMemcpyHostToDevice));
+    }
+    kv = DevBuf((size_t)e->max_batch * hp.n_layer * 2 * kv_layer_elems() * 2);
+    CUDA_CHECK(cudaMemsetAsync(kv.p, 0, kv.bytes, st));
+    CUDA_CHECK(cudaStreamSynchronize(st));
+    slot_used.assign((size_t)e->max_batch, false);
+    attn_splits = std::max(1, std::min(32, (2 * e->n_sms) / std::max(1, hp.n_head_kv)));
+}
+
+Model::~Model() {}
+
+uint16_t *Model::k_cache(int slot, int layer) const {
+    return kv.as<uint16_t>() + (((size_t)slot * hp.n_layer + layer) * 2 + 0) * kv_layer_elems();
+}
+uint16_t *Model::v_cache(int slot, int layer) const {
+    return kv.as<uint16_t>() + (((size_t)slot * hp.n_layer + layer) * 2 + 1) * kv_layer_elems();
+}
+
+// ---------------------------------------------------------------- Seq
+struct KernelTimer {  // per-launch CUDA events (profile_decode only)
+    struct Rec { cudaEvent_t a, b; int kind; };
+    std::vector<Rec> recs;
+    cudaStream_t st;
+    void begin(int kind) {
+        Rec r; r.kind = kind;
+        CUDA_CHECK(cudaEventCreate(&r.a));
+        CUDA_CHECK(cudaEventCreate(&r.b));
+        CUDA_CHECK(cudaEventRecord(r.a, st));
+        recs.push_back(r);
+    }
+    void end() { CUDA_CHECK(cudaEventRecord(recs.back().b, st)); }
+};
+#define TIMED(kind, stmt) do { if (timer) timer->begin(kind); stmt; if (timer) timer->end(); } while (0)
+
+Seq::Seq(Model *m_) : m(m_), slot(-1) {
+    m->eng->make_current();
+    {
+        std::lock_guard<std::mutex> lk(m->mu);
+        for (size_t i = 0; i < m->slot_used.size(); i++)
+            if (!m->slot_used[i]) { slot = (int)i; m->slot_used[i] = true; break; }
+    }
+    if (slot < 0) throw std::runtime_error("no free KV slot (engine max_batch reached)");
+    const HParams &hp = m->hp;
+    try {
+        state = DevBuf(sizeof(SeqState));
+        x = DevBuf((size_t)hp.n_embd * 4);
+        qkv = DevBuf((size_t)(hp.n_head + 2 * hp.n_head_kv) * hp.head_dim * 4);
+        att = DevBuf((size_t)hp.n_head * hp.head_dim * 4);
+        h = DevBuf((size_t)hp.n_ff * 4);
+        logits = DevBuf((size_t)hp.n_vocab * 4);
+        out_tokens = DevBuf((size_t)hp.n_ctx * 4);
+        prompt = DevBuf((size_t)hp.n_ctx * 4);
+        attn_scratch = DevBuf(attn_scratch_floats(hp.n_head, m->attn_splits, hp.head_dim) * 4);
+        attn_counters = DevBuf((size_t)hp.n_head_kv * 4);
+        CUDA_CHECK(cudaMemset(attn_counters.p, 0, attn_counters.bytes));
+        reset();
+    } catch (...) {
+        std::lock_guard<std::mutex> lk(m->mu);
+        m->slot_used[slot] = false;
+        throw;
+    }
+}
+
+Seq::~Seq() {
+    if (graph) cudaGraphExecDestroy(graph);
+    std::lock_guard<std::mutex> lk(m->mu);
+    if (slot >= 0) m->slot_used[slot] = false;
+}
+
+void Seq::reset() {
+    n_past = 0;
+    have_logits = false;
+    SeqState s{-1, 0, 0, 0, 0ull};
+    CUDA_CHECK(cudaMemcpy(state.p, &s, sizeof(s), cudaMemcpyHostToDevice));
+}
+
+void Seq::launch_token_pass(bool from_prompt, int prompt_idx, int pos_value, bool want_logits, cudaStream_t st, int *n_launch) {
+    const HParams &hp = m->hp;
+    SeqState *sd = state.as<SeqState>();
+    const int n_sms = m->eng->n_sms;
+    int launches = 0;
+    const int32_t *tok_ptr = from_prompt ? prompt.as<int32_t>() + prompt_idx : &sd->cur_token;
+    TIMED(2, launch_embed_row(m->tok_embd_type, m->tok_embd_raw.p, m->tok_embd_row_bytes, hp.n_embd, tok_ptr, x.as<float>(),
+                     from_prompt ? &sd->pos : nullptr, pos_value, from_prompt ? &sd->cur_token : nullptr, st));
+    launches++;
+    const int QD = hp.n_head * hp.head_dim, KVD = hp.n_head_kv * hp.head_dim;
+    for (int il = 0; il < hp.n_layer; il++) {
+        const Layer &L = m->layers[il];
+        {   // RMSNorm + Q,K,V projections in one launch
+            GemvParams p{};
+            p.n_seg = 3; p.epi = EPI_STORE; p.k = hp.n_embd;
+            p.seg[0] = L.wq.w; p.seg[1] = L.wk.w; p.seg[2] = L.wv.w;
+            p.out[0] = qkv.as<float>(); p.out[1] = qkv.as<float>() + QD; p.out[2] = qkv.as<float>() + QD + KVD;
+            p.x = x.as<float>(); p.norm_w = L.attn_norm.as<float>(); p.eps = hp.rms_eps;
+            TIMED(0, launch_gemv(p, gemv_plan_grid(p, n_sms), st));
+            launches++;
+        }
+        {   // RoPE + KV write + flash-decode
+            AttnParams a{};
+            a.qkv = qkv.as<float>(); a.out = att.as<float>();
+            a.k_cache = m->k_cache(slot, il); a.v_cache = m->v_cache(slot, il);
+            a.rope_cos = m->rope_cos.as<float>(); a.rope_sin = m->rope_sin.as<float>();
+            a.n_past_ptr = &sd->pos;
+            a.scratch = attn_scratch.as<float>(); a.counters = attn_counters.as<uint32_t>();
+            a.n_head = hp.n_head; a.n_kv = hp.n_head_kv; a.hd = hp.head_dim; a.n_rot = hp.n_rot;
+            a.n_split = m->attn_splits; a.n_ctx = hp.n_ctx;
+            a.scale = 1.0f / sqrtf((float)hp.head_dim);
+            TIMED(1, launch_attn_decode(a, st));
+            launches++;
+        }
+        {   // attention output projection + residual add
+            GemvParams p{};
+            p.n_seg = 1; p.epi = EPI_ADD; p.k = QD;
+            p.seg[0] = L.wo.w; p.out[0] = x.as<float>(); p.x = att.as<float>();
+            TIMED(0, launch_gemv(p, gemv_plan_grid(p, n_sms), st));
+            launches++;
+        }
+        {   // RMSNorm + gate/up + SwiGLU
+            GemvParams p{};
+            p.n_seg = 2; p.epi = EPI_SWIGLU; p.k = hp.n_embd;
+            p.seg[0] = L.w_gate.w; p.seg[1] = L.w_up.w; p.out[0] = h.as<float>();
+            p.x = x.as<float>(); p.norm_w = L.ffn_norm.as<float>(); p.eps = hp.rms_eps;
+            TIMED(0, launch_gemv(p, gemv_plan_grid(p, n_sms), st));
+            launches++;
+        }
+        {   // down projection + residual add
+            GemvParams p{};
+            p.n_seg = 1; p.epi = EPI_ADD; p.k = hp.n_ff;
+            p.seg[0] = L.w_down.w; p.out[0] = x.as<float>(); p.x = h.as<float>();
+            TIMED(0, launch_gemv(p, gemv_plan_grid(p, n_sms), st));
+            launches++;
+        }
+    }
+    if (want_logits) {
+        GemvParams p{};
+        p.n_seg = 1; p.epi = EPI_STORE; p.k = hp.n_embd;
+        p.seg[0] = m->output.w; p.out[0] = logits.as<float>();
+        p.x = x.as<float>(); p.norm_w = m->output_norm.as<float>(); p.eps = hp.rms_eps;
+        TIMED(0, launch_gemv(p, gemv_plan_grid(p, n_sms), st));
+        launches++;
+    }
+    if (n_launch) *n_launch += launches;
+}
+
+void Seq::launch_sample_kernel(const aios_sampling &sp, cudaStream_t st) {
+    SeqState *sd = state.as<SeqState>();
+    SampleParams s{};
+    s.logits = logits.as<float>();
+    s.n_vocab = m->hp.n_vocab;
+    s.temperature = sp.temperature; s.top_k = sp.top_k; s.top_p = sp.top_p; s.min_p = sp.min_p; s.seed = sp.seed;
+    s.pos_ptr = &sd->pos; s.step_ptr = &sd->step; s.cur_token = &sd->cur_token;
+    s.out_tokens = out_tokens.as<int32_t>(); s.out_cap = m->hp.n_ctx;
+    TIMED(2, launch_sample(s, st));
+}
+
+void Seq::prefill(const int32_t *tokens, int n) {
+    if (n <= 0) return;
+    if (n_past + n > m->hp.n_ctx) throw std::runtime_error("prefill would exceed the context length");
+    for (int i = 0; i < n; i++)
+        if (tokens[i] < 0 || tokens[i] >= m->hp.n_vocab) throw std::invalid_argument("token id out of range");
+    m->eng->make_current();
+    cudaStream_t st = m->eng->stream;
+    CUDA_CHECK(cudaMemcpyAsync(prompt.p, tokens, (size_t)n * 4, cudaMemcpyHostToDevice, st));
+    for (int i = 0; i < n; i++) launch_token_pass(true, i, n_past + i, i == n - 1, st, nullptr);
+    CUDA_CHECK(cudaGetLastError());
+    CUDA_CHECK(cudaStreamSynchronize(st));
+    n_past += n;
+    have_logits = true;
+}
+
+static bool same_sampling(const aios_sampling &a, const aios_sampling &b) {
+    return a.temperature == b.temperature && a.top_k == b.top_k && a.top_p == b.top_p && a.min_p == b.min_p && a.seed == b.seed;
+}
+
+void Seq::ensure_graph(const aios_sampling &sp) {
+    if (graph && same_sampling(sp, graph_sampling)) return;
+    if (graph) { cudaGraphExecDestroy(graph); graph = nullptr; }
+    cudaStream_t st = m->eng->stream;
+    cudaGraph_t g = nullptr;
+    kernels_per_step = 0;
+    CUDA_CHECK(cudaStreamBeginCapture(st, cudaStreamCaptureModeThreadLocal));
+    try {
+        launch_sample_kernel(sp, st);
+        kernels_per_step++;
+        launch_token_pass(false, 0, 0, true, st, &kernels_per_step);
+    } catch (...) {
+        cudaStreamEndCapture(st, &g);
+        if (g) cudaGraphDestroy(g);
+        throw;
+    }
+    CUDA_CHECK(cudaStreamEndCapture(st, &g));
+    cudaError_t e = cudaGraphInstantiate(&graph, g, 0);
+    cudaGraphDestroy(g);
+    CUDA_CHECK(e);
+    graph_sampling = sp;
+}
+
+int Seq::decode(const aios_sampling &sp, int max_tokens, int32_t *out) {
+    if (!have_logits) throw std::runtime_error("decode needs logits: prefill at least one token first");
+    // the sampled token n is fed at position n_past+n, which must fit; the last sampled token is returned un-fed
+    const int steps = std::min(max_tokens, m->hp.n_ctx - n_past);
+    if (steps <= 0) return 0;
+    m->eng->make_current();
+    cudaStream_t st = m->eng->stream;
+    const bool use_graph = !(m->eng->flags & AIOS_ENGINE_NO_GRAPH);
+    int32_t hdr[2] = {n_past - 1, 0};  // pos, step
+    CUDA_CHECK(cudaMemcpyAsync(state.p, hdr, sizeof(hdr), cudaMemcpyHostToDevice, st));
+    if (use_graph) {
+        ensure_graph(sp);
+        for (int i = 0; i < steps; i++) CUDA_CHECK(cudaGraphLaunch(graph, st));
+    } else {
+        for (int i = 0; i < steps; i++) {
+            launch_sample_kernel(sp, st);
+            launch_token_pass(false, 0, 0, true, st, nullptr);
+        }
+    }
+    CUDA_CHECK(cudaMemcpyAsync(out, out_tokens.p, (size_t)steps * 4, cudaMemcpyDeviceToHost, st));
+    CUDA_CHECK(cudaStreamSynchronize(st));
+    CUDA_CHECK(cudaGetLastError());
+    n_past += steps;
+    return steps;
+}
+
+void Seq::step(const aios_sampling &sp, int32_t *tok) {
+    if (decode(sp, 1, tok) != 1) throw std::runtime_error("context is full");
+}
+
+void Seq::bench_decode(int n_tokens, aios_bench_result *out) {
+    if (!have_logits) throw std::runtime_error("bench_decode needs a prefilled sequence");
+    const int steps = std::min(n_tokens, m->hp.n_ctx - n_past);
+    if (steps <= 0) throw std::runtime_error("context is full");
+    m->eng->make_current();
+    cudaStream_t st = m->eng->stream;
+    aios_sampling sp{};  // greedy
+    ensure_graph(sp);
+    int32_t hdr[2] = {n_past - 1, 0};
+    CUDA_CHECK(cudaMemcpyAsync(state.p, hdr, sizeof(hdr), cudaMemcpyHostToDevice, st));
+    cudaEvent_t e0, e1;
+    CUDA_CHECK(cudaEventCreate(&e0));
+    CUDA_CHECK(cudaEventCreate(&e1));
+    CUDA_CHECK(cudaStreamSynchronize(st));
+    CUDA_CHECK(cudaEventRecord(e0, st));
+    for (int i = 0; i < steps; i++) CUDA_CHECK(cudaGraphLaunch(graph, st));
+    CUDA_CHECK(cudaEventRecord(e1, st));
+    CUDA_CHECK(cudaEventSynchronize(e1));
+    float ms = 0;
+    CUDA_CHECK(cudaEventElapsedTime(&ms, e0, e1));
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    memset(out, 0, sizeof(*out));
+    out->ms_total = ms;
+    out->n_tokens = steps;
+    out->kernel_launches = steps * kernels_per_step;
+    out->n_past_begin = n_past;
+    out->n_past_end = n_past + steps;
+    n_past += steps;
+}
+
+void Seq::profile_decode(int n_tokens, aios_bench_result *out) {
+    if (!have_logits) throw std::runtime_error("profile_decode needs a prefilled sequence");
+    const int steps = std::min(n_tokens, m->hp.n_ctx - n_past);
+    if (steps <= 0) throw std::runtime_error("context is full");
+    m->eng->make_current();
+    cudaStream_t st = m->eng->stream;
+    aios_sampling sp{};
+    int32_t hdr[2] = {n_past - 1, 0};
+    CUDA_CHECK(cudaMemcpyAsync(state.p, hdr, sizeof(hdr), cudaMemcpyHostToDevice, st));
+    KernelTimer kt;
+    kt.st = st;
+    timer = &kt;
+    int launches = 0;
+    try {
+        for (int i = 0; i < steps; i++) {
+            launch_sample_kernel(sp, st);
+            launches++;
+            launch_token_pass(false, 0, 0, true, st, &launches);
+        }
+        CUDA_CHECK(cudaStreamSynchronize(st));
+    } catch (...) {
+        timer = nullptr;
+        throw;
+    }
+    timer = nullptr;
+    float ms_kind[3] = {0, 0, 0};
+    int n_gemv = 0;
+    for (auto &r : kt.recs) {
+        float ms = 0;
+        cudaEventElapsedTime(&ms, r.a, r.b);
+        ms_kind[r.kind] += ms;
+        if (r.kind == 0) n_gemv++;
+        cudaEventDestroy(r.a);
+        cudaEventDestroy(r.b);
+    }
+    memset(out, 0, sizeof(*out));
+    out->ms_total = ms_kind[0] + ms_kind[1] + ms_kind[2];
+    out->n_tokens = steps;
+    out->kernel_launches = launches;
+    out->n_past_begin = n_past;
+    out->n_past_end = n_past + steps;
+    out->ms_gemv = ms_kind[0];
+    out->reserved[0] = ms_kind[1];
+    out->reserved[1] = ms_kind[2];
+    out->reserved[2] = (float)n_gemv;
+    n_past += steps;
+}
+
+void Seq::snapshot() {
+    if (!have_logits) throw std::runtime_error("nothing to snapshot: prefill first");
+    m->eng->make_current();
+    if (!snap_logits.p) snap_logits = DevBuf(logits.bytes);
+    CUDA_CHECK(cudaMemcpyAsync(snap_logits.p, logits.p, logits.bytes, cudaMemcpyDeviceToDevice, m->eng->stream));
+    CUDA_CHECK(cudaStreamSynchronize(m->eng->stream));
+    snap_n_past = n_past;
+}
+
+void Seq::restore() {
+    if (snap_n_past < 0) throw std::runtime_error("no snapshot");
+    m->eng->make_current();
+    CUDA_CHECK(cudaMemcpyAsync(logits.p, snap_logits.p, logits.bytes, cudaMemcpyDeviceToDevice, m->eng->stream));
+    n_past = snap_n_past;
+    have_logits = true;
+}
+
+void Seq::read_logits(float *out) {
+    if (!have_logits) throw std::runtime_error("no logits yet");
+    m->eng->make_current();
+    CUDA_CHECK(cudaMemcpyAsync(out, logits.p, (size_t)m->hp.n_vocab * 4, cudaMemcpyDeviceToHost, m->eng->stream));
+    CUDA_CHECK(cudaStreamSynchronize(m->eng->stream));
+}
+
+}  // namespace aios

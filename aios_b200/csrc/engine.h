@@ -1,0 +1,132 @@
+// engine.h — host-side runtime: engine (device + stream), model (weights in HBM, RoPE table,
+// KV-cache slots) and sequence (device-resident decode state + captured CUDA graph).
+// This is what replaces a llama-server child process (reference: runtime/src/model_manager.rs
+// :187-204 spawns one per model; runtime/src/inference.rs:94-186 proxies requests to it).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include <memory>
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/aios_b200.h"
+#include "gguf.h"
+#include "kernels.h"
+#include "layout.cuh"
+
+namespace aios {
+
+struct DevBuf {
+    void *p = nullptr;
+    size_t bytes = 0;
+    DevBuf() = default;
+    explicit DevBuf(size_t n);
+    ~DevBuf();
+    DevBuf(const DevBuf &) = delete;
+    DevBuf &operator=(const DevBuf &) = delete;
+    DevBuf(DevBuf &&o) noexcept : p(o.p), bytes(o.bytes) { o.p = nullptr; o.bytes = 0; }
+    DevBuf &operator=(DevBuf &&o) noexcept;
+    template <typename T>
+    T *as() const { return static_cast<T *>(p); }
+};
+
+struct Engine {
+    int device = 0;
+    int n_sms = 148;
+    int max_batch = 1;
+    int flags = 0;
+    cudaStream_t stream = nullptr;
+    std::mutex mu;  // serialises use of the stream by API calls
+    explicit Engine(const aios_engine_opts &o);
+    ~Engine();
+    void make_current() const;
+};
+
+struct DevMatrix {
+    WPlanes w{};      // planes layout (layout.cuh)
+    DevBuf storage;   // one allocation holding all planes
+    size_t src_bytes = 0;
+};
+
+struct Layer {
+    DevMatrix wq, wk, wv, wo, w_gate, w_up, w_down;
+    DevBuf attn_norm, ffn_norm;  // f32
+};
+
+struct HParams {
+    int n_layer = 0, n_embd = 0, n_head = 0, n_head_kv = 0, head_dim = 0, n_ff = 0, n_vocab = 0, n_ctx = 0, n_rot = 0;
+    int file_type = 0;
+    float rms_eps = 1e-5f, rope_freq_base = 10000.f;
+};
+
+struct Seq;
+
+struct Model {
+    Engine *eng;
+    std::string name, arch, path;
+    HParams hp;
+    std::unique_ptr<GgufFile> file;
+    std::vector<Layer> layers;
+    DevBuf tok_embd_raw;  // natural GGUF layout: one row is gathered per token
+    int tok_embd_type = 0;
+    int64_t tok_embd_row_bytes = 0;
+    DevMatrix output;     // output.weight (or the tied embedding) in planes layout
+    DevBuf output_norm;
+    DevBuf rope_cos, rope_sin;  // [n_ctx][n_rot/2], host-computed (glibc cosf/sinf, as the oracle)
+    DevBuf kv;            // [max_batch][n_layer][2][n_ctx][n_kv*hd] f16
+    std::vector<bool> slot_used;
+    int64_t weight_bytes = 0, weight_bytes_per_token = 0;
+    std::mutex mu;
+    int attn_splits = 16;
+
+    Model(Engine *e, const std::string &name, const std::string &path, int n_ctx);
+    ~Model();
+    uint16_t *k_cache(int slot, int layer) const;
+    uint16_t *v_cache(int slot, int layer) const;
+    size_t kv_layer_elems() const { return (size_t)hp.n_ctx * hp.n_head_kv * hp.head_dim; }
+
+   private:
+    void upload_matrix(const GgufTensor &t, DevMatrix &dst, DevBuf &staging, void *pinned, size_t pinned_bytes);
+};
+
+struct SeqState {  // lives in device memory
+    int32_t pos;        // position of the token being processed (= #cached positions before it); -1 when empty
+    int32_t step;       // tokens generated so far in the current decode call
+    int32_t cur_token;  // token fed at `pos`
+    int32_t pad;
+    unsigned long long argmax_key;
+};
+
+struct Seq {
+    Model *m;
+    int slot;
+    int n_past = 0;  // host mirror: number of positions in the KV cache
+    bool have_logits = false;
+    DevBuf state, x, qkv, att, h, logits, out_tokens, prompt, attn_scratch, attn_counters, snap_logits;
+    int snap_n_past = -1;
+    struct KernelTimer *timer = nullptr;  // non-null only inside profile_decode
+    cudaGraphExec_t graph = nullptr;
+    aios_sampling graph_sampling{};
+    int kernels_per_step = 0;
+
+    explicit Seq(Model *m);
+    ~Seq();
+    void reset();
+    void prefill(const int32_t *tokens, int n);
+    int decode(const aios_sampling &sp, int max_tokens, int32_t *out);
+    void step(const aios_sampling &sp, int32_t *tok);
+    void bench_decode(int n_tokens, aios_bench_result *out);
+    void profile_decode(int n_tokens, aios_bench_result *out);
+    void snapshot();
+    void restore();
+    void read_logits(float *out);
+
+   private:
+    void launch_token_pass(bool from_prompt, int prompt_idx, int pos_value, bool want_logits, cudaStream_t st, int *n_launch);
+    void launch_sample_kernel(const aios_sampling &sp, cudaStream_t st);
+    void ensure_graph(const aios_sampling &sp);
+};
+
+}  // namespace aios

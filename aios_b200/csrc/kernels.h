@@ -1,0 +1,76 @@
+// kernels.h — host-callable launchers of the CUDA kernels (internal; not part of the C ABI).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "layout.cuh"
+
+namespace aios {
+
+// ---- dequant.cu
+void launch_dequantize(int type, const void *d_blocks, int64_t n, float *d_out, cudaStream_t st);
+void launch_embed_row(int type, const void *d_table, int64_t row_bytes, int k, const int32_t *d_tok, float *d_x,
+                      int32_t *d_pos, int pos_value, int32_t *d_cur_token, cudaStream_t st);
+void launch_repack(int type, const void *d_raw, int64_t n_rows, int k, uint8_t *const planes[5], cudaStream_t st);
+
+// ---- gemv.cu : fused [RMSNorm] -> activation quantisation -> dequant+GEMV -> epilogue
+enum GemvEpilogue : int {
+    EPI_STORE = 0,   // out[n] = dot
+    EPI_ADD = 1,     // out[n] += dot            (residual stream update, in place)
+    EPI_SWIGLU = 2,  // out[n] = silu(dot(seg0 row n)) * dot(seg1 row n)
+};
+
+struct GemvParams {
+    int32_t n_seg;          // 1..3 weight matrices sharing the same input vector
+    int32_t epi;            // GemvEpilogue
+    int32_t k;              // input length (all segments)
+    int32_t cta_begin[4];   // CTA ranges per segment: segment i owns CTAs [cta_begin[i], cta_begin[i+1])
+    WPlanes seg[3];
+    float *out[3];
+    const float *x;         // f32 input vector [k]
+    const float *norm_w;    // if non-null: x <- rmsnorm(x) * norm_w first (llama attn_norm / ffn_norm / output_norm)
+    float eps;
+    unsigned long long *argmax_key;  // if non-null (EPI_STORE, 1 segment): running packed (value,index) max
+};
+
+// fills cta_begin[] and returns the grid size; n_sms from the device
+int gemv_plan_grid(GemvParams &p, int n_sms);
+size_t gemv_smem_bytes(int k);
+void launch_gemv(const GemvParams &p, int grid, cudaStream_t st);
+void gemv_init();  // one-time function attributes (dynamic smem)
+
+// ---- attention.cu : RoPE + KV write + flash-decode over the f16 KV cache (one new token)
+struct AttnParams {
+    const float *qkv;        // [n_head*hd + 2*n_kv*hd] raw projections of the new token
+    float *out;              // [n_head*hd]
+    uint16_t *k_cache;       // this layer: [n_ctx][n_kv*hd] f16
+    uint16_t *v_cache;
+    const float *rope_cos;   // [n_ctx][hd/2]
+    const float *rope_sin;
+    const int32_t *n_past_ptr;  // device: number of cached positions before this token
+    float *scratch;          // [n_head][n_split][hd+2] partial (m, l, o[hd])
+    uint32_t *counters;      // [n_kv] arrival counters (zero on entry, zero on exit)
+    int32_t n_head, n_kv, hd, n_rot, n_split, n_ctx;
+    float scale;
+};
+void launch_attn_decode(const AttnParams &p, cudaStream_t st);
+void attn_init();  // one-time function attributes (dynamic smem)
+size_t attn_scratch_floats(int n_head, int n_split, int hd);
+
+// ---- sampler.cu
+struct SampleParams {
+    const float *logits;
+    int32_t n_vocab;
+    float temperature;
+    int32_t top_k;
+    float top_p, min_p;
+    uint64_t seed;
+    int32_t *pos_ptr;        // device state: position of the token being fed; incremented by one
+    int32_t *step_ptr;       // device state: index into out_tokens, incremented
+    int32_t *cur_token;      // device: sampled token (input of the next step)
+    int32_t *out_tokens;     // device array
+    int32_t out_cap;
+};
+void launch_sample(const SampleParams &p, cudaStream_t st);
+
+}  // namespace aios

@@ -50,6 +50,7 @@ class Arch:
 ARCHS = {
     # tiny shapes for CPU-speed parity tests (K multiples of 256 as K-quants require)
     "tiny": Arch("tiny", 2, 256, 4, 2, 64, 512, 512, 10000.0, 1e-5, 512),
+    "tiny1": Arch("tiny1", 1, 256, 4, 2, 64, 512, 512, 10000.0, 1e-5, 512),
     "tiny-gqa4": Arch("tiny-gqa4", 3, 512, 8, 2, 64, 1024, 1000, 10000.0, 1e-5, 512),
     # SURVEY.md Appendix B shapes
     "tinyllama-1.1b": Arch("tinyllama-1.1b", 22, 2048, 32, 4, 64, 5632, 32000, 10000.0, 1e-5, 2048),

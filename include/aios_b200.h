@@ -1,0 +1,175 @@
+/*
+ * aios_b200.h — C ABI of libaios_b200.so, the B200-native (sm_100a) GGUF inference engine
+ * that replaces the llama-server child processes behind aiOS's `aios-runtime`.
+ *
+ * The reference has no FFI for this path: its Rust `runtime` crate spawns llama-server
+ * (runtime/src/model_manager.rs:187-204) and proxies HTTP (runtime/src/inference.rs:94-186).
+ * Each entry point below names the reference interface it stands in for; INTEGRATION.md
+ * shows the Rust `-sys` binding a maintainer would add.
+ *
+ * Conventions: plain C types only; every call returns 0 (AIOS_OK) or a negative AIOS_E_*
+ * code; the message is in the calling thread's aios_last_error().  Nothing throws or
+ * aborts across this boundary.  Handles are opaque and owned by the library.  All pointer
+ * arguments are HOST pointers unless a comment says otherwise.  There is no CPU fallback:
+ * every compute entry point fails with AIOS_E_CUDA when no sm_100 device is usable.
+ */
+#ifndef AIOS_B200_H
+#define AIOS_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define AIOS_OK 0
+#define AIOS_E_INVAL (-1)   /* bad argument                          -> tonic InvalidArgument */
+#define AIOS_E_IO (-2)      /* file missing / unreadable / not GGUF  -> "error: ..." status   */
+#define AIOS_E_FORMAT (-3)  /* unsupported GGUF contents                                      */
+#define AIOS_E_CUDA (-4)    /* CUDA runtime / no device              -> tonic Internal        */
+#define AIOS_E_NOMEM (-5)   /* device or host memory exhausted                                */
+#define AIOS_E_STATE (-6)   /* wrong state (context full, unloaded)  -> tonic FailedPrecondition */
+#define AIOS_E_RANGE (-7)   /* size beyond a stated maximum                                   */
+
+/* ggml tensor type ids as stored in GGUF (gguf-py constants.py GGMLQuantizationType) */
+#define AIOS_TYPE_F32 0
+#define AIOS_TYPE_F16 1
+#define AIOS_TYPE_Q8_0 8
+#define AIOS_TYPE_Q4_K 12
+#define AIOS_TYPE_Q5_K 13
+#define AIOS_TYPE_Q6_K 14
+
+typedef struct aios_engine aios_engine;   /* one per GPU: device, stream, scratch            */
+typedef struct aios_model aios_model;     /* a loaded GGUF: replaces one llama-server child  */
+typedef struct aios_seq aios_seq;         /* one sequence = one KV-cache slot of a model     */
+
+const char *aios_last_error(void);
+/* library / build identification, e.g. "aios_b200 0.1 sm_100a" */
+const char *aios_version(void);
+
+/* ---- engine: replaces runtime/src/main.rs:50-51 (ModelManager + InferenceEngine construction) */
+typedef struct aios_engine_opts {
+    int32_t device;      /* CUDA ordinal                                                     */
+    int32_t max_batch;   /* max concurrent sequences per model (KV slots); 0 -> 1            */
+    int32_t flags;       /* AIOS_ENGINE_* bits                                               */
+    int32_t reserved;
+} aios_engine_opts;
+#define AIOS_ENGINE_NO_GRAPH 1 /* launch kernels one by one instead of via CUDA graphs (debug) */
+
+int aios_engine_create(const aios_engine_opts *opts, aios_engine **out);
+void aios_engine_destroy(aios_engine *e);
+int aios_device_count(int32_t *n);
+
+/* ---- model: replaces ModelManager::load_model / unload_model
+ *      (runtime/src/model_manager.rs:149-277, :285-345).  n_ctx<=0 -> 2048 like the
+ *      reference default (model_manager.rs:167-171). */
+int aios_model_load(aios_engine *e, const char *name, const char *gguf_path, int32_t n_ctx, aios_model **out);
+int aios_model_unload(aios_model *m);
+
+typedef struct aios_model_info {
+    char name[128];
+    char arch[32];
+    int32_t n_layer, n_embd, n_head, n_head_kv, head_dim, n_ff, n_vocab, n_ctx, n_rot;
+    int32_t file_type;            /* general.file_type                                      */
+    int32_t n_tensors;
+    int32_t max_batch;
+    float rms_eps, rope_freq_base;
+    int64_t file_bytes;           /* GGUF file size                                         */
+    int64_t weight_bytes;         /* device bytes held by weights                           */
+    int64_t kv_bytes;             /* device bytes held by the KV cache                      */
+    int64_t weight_bytes_per_token; /* algorithmic bytes one decode step streams            */
+    int64_t kv_bytes_per_position;
+} aios_model_info;
+/* replaces the ModelStatus / ManagedModel fields (runtime/src/model_manager.rs:42-56, :539-548) */
+int aios_model_info_get(const aios_model *m, aios_model_info *out);
+
+/* tensor directory (loader parity tests): i in [0, n_tensors) */
+typedef struct aios_tensor_info {
+    char name[96];
+    int32_t type;
+    int32_t n_dims;
+    int64_t ne[4];      /* ne[0] = innermost (K) */
+    int64_t offset;     /* byte offset inside the GGUF data section */
+    int64_t nbytes;
+} aios_tensor_info;
+int aios_model_tensor_info(const aios_model *m, int32_t i, aios_tensor_info *out);
+
+/* ---- sampling parameters: the request fields InferenceEngine::infer forwards
+ *      (runtime/src/inference.rs:103-122: max_tokens, temperature) plus the llama-server
+ *      defaults it leaves implicit (top_k 40, top_p 0.95, min_p 0.05). */
+typedef struct aios_sampling {
+    float temperature;   /* <= 0 -> greedy argmax (lowest index wins ties)                   */
+    int32_t top_k;       /* <= 0 -> disabled                                                 */
+    float top_p;         /* >= 1 -> disabled                                                 */
+    float min_p;         /* <= 0 -> disabled                                                 */
+    uint64_t seed;
+} aios_sampling;
+
+/* ---- sequences: the decode hot loop llama-server runs per slot */
+int aios_seq_create(aios_model *m, aios_seq **out);
+void aios_seq_free(aios_seq *s);
+int aios_seq_reset(aios_seq *s);                     /* drop the KV contents, position 0     */
+int aios_seq_position(const aios_seq *s, int32_t *n_past);
+/* feed n prompt tokens at the current position (prefill); keeps the last token's logits */
+int aios_seq_prefill(aios_seq *s, const int32_t *tokens, int32_t n);
+/* generate up to max_tokens tokens after the fed ones; out_tokens[cap]; stops at the
+ * context limit.  One H2D of nothing, one D2H of the token ids. */
+int aios_seq_decode(aios_seq *s, const aios_sampling *sp, int32_t max_tokens, int32_t *out_tokens, int32_t *n_out);
+/* one streaming step: sample from the kept logits, feed that token, return it.
+ * H2D: 0 bytes; D2H: 4 bytes; synchronises. */
+int aios_seq_step(aios_seq *s, const aios_sampling *sp, int32_t *token_out);
+/* copy the kept logits (n_vocab floats) to the host */
+int aios_seq_logits(aios_seq *s, float *logits_out);
+/* remember / return to the current position and its logits (prompt caching, benchmark replays).
+ * KV rows past the snapshot position are simply overwritten by later tokens. */
+int aios_seq_snapshot(aios_seq *s);
+int aios_seq_restore(aios_seq *s);
+
+/* ---- convenience: InferenceEngine::infer at token level (runtime/src/inference.rs:94-186):
+ *      prefill prompt, decode max_tokens.  tokens_used = n_prompt + *n_out. */
+int aios_generate(aios_model *m, const int32_t *prompt, int32_t n_prompt, const aios_sampling *sp,
+                  int32_t max_tokens, int32_t *out_tokens, int32_t *n_out);
+
+/* ---- test / parity hooks (SURVEY.md §8b "test hooks") */
+/* dequantise n elements (whole blocks) of ggml_type on the GPU: host blocks -> host floats.
+ * Bit-exact against ggml's dequantize_row_* as restated by gguf-py. */
+int aios_dequantize(aios_engine *e, int32_t ggml_type, const void *blocks, int64_t n, float *out);
+/* y[n_rows] = W[n_rows,k] . x[k] with llama.cpp's CPU numerics (x quantised to Q8_K / Q8_0,
+ * integer block dots): host in, host out.  If norm_w != NULL, x is RMS-normed first. */
+int aios_matvec(aios_engine *e, int32_t ggml_type, const void *w_blocks, int64_t n_rows, int64_t k,
+                const float *x, const float *norm_w, float rms_eps, float *y);
+/* logits of the last of n tokens fed at position n_past into a scratch sequence */
+int aios_forward_logits(aios_model *m, const int32_t *tokens, int32_t n, int32_t n_past, float *logits_out);
+/* read back one layer's KV rows [pos0, pos0+n) as fp16 bit patterns: k_out/v_out[n][n_head_kv*head_dim] */
+int aios_seq_read_kv(aios_seq *s, int32_t layer, int32_t pos0, int32_t n, uint16_t *k_out, uint16_t *v_out);
+/* read one of the sequence's f32 activation buffers as the last token pass left it:
+ * which = 0 residual x[n_embd], 1 raw q|k|v[(n_head+2*n_head_kv)*head_dim], 2 attention output
+ * [n_head*head_dim], 3 SwiGLU output h[n_ff].  n = number of floats to copy. */
+int aios_seq_read_activation(aios_seq *s, int32_t which, float *out, int64_t n);
+
+/* ---- measurement hooks (bench.py): device-timed decode with CUDA events on the engine's
+ *      own stream.  Runs n_tokens greedy decode steps from the current position and returns
+ *      the elapsed milliseconds and the number of kernels launched. */
+typedef struct aios_bench_result {
+    float ms_total;          /* CUDA-event time of the whole region                          */
+    int32_t n_tokens;
+    int32_t kernel_launches; /* kernel nodes executed inside the region                      */
+    int32_t n_past_begin, n_past_end;
+    float ms_gemv;           /* if per-kernel timing was requested, time in GEMV kernels     */
+    float reserved[3];
+} aios_bench_result;
+int aios_seq_bench_decode(aios_seq *s, int32_t n_tokens, aios_bench_result *out);
+/* same work launched kernel by kernel with a CUDA-event pair around every launch: fills
+ * ms_gemv (sum of the dequant+GEMV launches), reserved[0] = ms in attention launches,
+ * reserved[1] = ms in the remaining launches, reserved[2] = number of GEMV launches. */
+int aios_seq_profile_decode(aios_seq *s, int32_t n_tokens, aios_bench_result *out);
+/* time ONE GEMV launch shape in isolation (roofline leg): type/n_rows/k on random weights,
+ * `iters` launches over `n_copies` distinct weight copies (so the working set exceeds L2) */
+int aios_bench_gemv(aios_engine *e, int32_t ggml_type, int64_t n_rows, int64_t k, int32_t n_copies,
+                    int32_t iters, float *ms_per_launch);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* AIOS_B200_H */

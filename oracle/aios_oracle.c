@@ -271,127 +271,109 @@ void oracle_quantize_row_q8_0(const float *x, void *vy, int64_t k) {
 }
 
 /* ---------------------------------------------------------------- integer block dot products
- * "generic" scalar kernels, 8 float lanes summed at the end. */
+ * ggml's arithmetic: integer dot products inside a block, float
+ * scaling by d_weight*d_activation, accumulation across blocks.  ggml does not fix the order of
+ * that last accumulation (its generic, AVX2, AVX-512 and NEON kernels all differ), so this
+ * restatement picks an ORDER-FREE one: every 64-weight unit (32 for Q8_0) contributes one f32
+ * term, and the terms are summed in double and rounded to f32 once.  A double sum of a few
+ * hundred f32 terms rounds to the same f32 in any order (except with probability ~1e-7), which
+ * lets a parallel implementation be compared bit for bit instead of through a chaotic tolerance
+ * (one flipped Q8 rounding re-randomises the quantisation noise of every later layer). */
 static float vec_dot_q4_K_q8_K(int64_t n, const block_q4_K *x, const block_q8_K *y) {
     const int64_t nb = n / QK_K;
-    int8_t aux8[QK_K];
-    float sums[8] = {0};
-    float sumf = 0;
+    double acc = 0.0;
     for (int64_t i = 0; i < nb; i++) {
-        const uint8_t *q4 = x[i].qs;
-        const int8_t *q8 = y[i].qs;
-        int32_t aux32[8] = {0};
-        int8_t *a = aux8;
-        for (int j = 0; j < QK_K / 64; j++) {
-            for (int l = 0; l < 32; l++) a[l] = (int8_t)(q4[l] & 0xF);
-            a += 32;
-            for (int l = 0; l < 32; l++) a[l] = (int8_t)(q4[l] >> 4);
-            a += 32; q4 += 32;
-        }
-        uint8_t sc[8], mn[8];
-        for (int j = 0; j < 8; j++) get_scale_min_k4(j, x[i].scales, &sc[j], &mn[j]);
-        int sumi = 0;
-        for (int j = 0; j < QK_K / 16; j++) sumi += y[i].bsums[j] * mn[j / 2];
-        a = aux8;
-        for (int j = 0; j < QK_K / 32; j++) {
-            const int32_t scale = sc[j];
-            for (int r = 0; r < 4; r++) {
-                for (int l = 0; l < 8; l++) aux32[l] += scale * ((int16_t)q8[l] * (int16_t)a[l]);
-                q8 += 8; a += 8;
+        const float d = h2f(x[i].d), dmin = h2f(x[i].dmin), d8 = y[i].d;
+        const float fd = d * d8, fm = dmin * d8;
+        for (int p = 0; p < 4; p++) { /* unit p: sub-blocks 2p (low nibbles) and 2p+1 (high nibbles) */
+            uint8_t sc_lo, m_lo, sc_hi, m_hi;
+            get_scale_min_k4(2 * p, x[i].scales, &sc_lo, &m_lo);
+            get_scale_min_k4(2 * p + 1, x[i].scales, &sc_hi, &m_hi);
+            const uint8_t *q4 = x[i].qs + 32 * p;
+            const int8_t *q8 = y[i].qs + 64 * p;
+            int dlo = 0, dhi = 0;
+            for (int l = 0; l < 32; l++) {
+                dlo += (q4[l] & 0xF) * q8[l];
+                dhi += (q4[l] >> 4) * q8[l + 32];
             }
+            const int bs_lo = y[i].bsums[4 * p] + y[i].bsums[4 * p + 1];
+            const int bs_hi = y[i].bsums[4 * p + 2] + y[i].bsums[4 * p + 3];
+            const int isum = sc_lo * dlo + sc_hi * dhi;
+            const int msum = m_lo * bs_lo + m_hi * bs_hi;
+            const float term = fmaf(fd, (float)isum, -(fm * (float)msum));
+            acc += (double)term;
         }
-        const float d = h2f(x[i].d) * y[i].d;
-        for (int l = 0; l < 8; l++) sums[l] += d * (float)aux32[l];
-        const float dmin = h2f(x[i].dmin) * y[i].d;
-        sumf -= dmin * (float)sumi;
     }
-    for (int l = 0; l < 8; l++) sumf += sums[l];
-    return sumf;
+    return (float)acc;
 }
 
 static float vec_dot_q5_K_q8_K(int64_t n, const block_q5_K *x, const block_q8_K *y) {
     const int64_t nb = n / QK_K;
-    int8_t aux8[QK_K];
-    float sums[8] = {0};
-    float sumf = 0;
+    double acc = 0.0;
     for (int64_t i = 0; i < nb; i++) {
-        const uint8_t *q4 = x[i].qs, *hm = x[i].qh;
-        const int8_t *q8 = y[i].qs;
-        int32_t aux32[8] = {0};
-        int8_t *a = aux8;
-        uint8_t m = 1;
-        for (int j = 0; j < QK_K / 64; j++) {
-            for (int l = 0; l < 32; l++) a[l] = (int8_t)((q4[l] & 0xF) + ((hm[l] & m) ? 16 : 0));
-            a += 32; m <<= 1;
-            for (int l = 0; l < 32; l++) a[l] = (int8_t)((q4[l] >> 4) + ((hm[l] & m) ? 16 : 0));
-            a += 32; m <<= 1;
-            q4 += 32;
-        }
-        uint8_t sc[8], mn[8];
-        for (int j = 0; j < 8; j++) get_scale_min_k4(j, x[i].scales, &sc[j], &mn[j]);
-        int sumi = 0;
-        for (int j = 0; j < QK_K / 16; j++) sumi += y[i].bsums[j] * mn[j / 2];
-        a = aux8;
-        for (int j = 0; j < QK_K / 32; j++) {
-            const int32_t scale = sc[j];
-            for (int r = 0; r < 4; r++) {
-                for (int l = 0; l < 8; l++) aux32[l] += scale * ((int16_t)q8[l] * (int16_t)a[l]);
-                q8 += 8; a += 8;
+        const float d = h2f(x[i].d), dmin = h2f(x[i].dmin), d8 = y[i].d;
+        const float fd = d * d8, fm = dmin * d8;
+        for (int p = 0; p < 4; p++) {
+            uint8_t sc_lo, m_lo, sc_hi, m_hi;
+            get_scale_min_k4(2 * p, x[i].scales, &sc_lo, &m_lo);
+            get_scale_min_k4(2 * p + 1, x[i].scales, &sc_hi, &m_hi);
+            const uint8_t *q4 = x[i].qs + 32 * p, *qh = x[i].qh;
+            const int8_t *q8 = y[i].qs + 64 * p;
+            int dlo = 0, dhi = 0;
+            for (int l = 0; l < 32; l++) {
+                dlo += ((q4[l] & 0xF) | (((qh[l] >> (2 * p)) & 1) << 4)) * q8[l];
+                dhi += ((q4[l] >> 4) | (((qh[l] >> (2 * p + 1)) & 1) << 4)) * q8[l + 32];
             }
+            const int bs_lo = y[i].bsums[4 * p] + y[i].bsums[4 * p + 1];
+            const int bs_hi = y[i].bsums[4 * p + 2] + y[i].bsums[4 * p + 3];
+            const int isum = sc_lo * dlo + sc_hi * dhi;
+            const int msum = m_lo * bs_lo + m_hi * bs_hi;
+            const float term = fmaf(fd, (float)isum, -(fm * (float)msum));
+            acc += (double)term;
         }
-        const float d = h2f(x[i].d) * y[i].d;
-        for (int l = 0; l < 8; l++) sums[l] += d * (float)aux32[l];
-        const float dmin = h2f(x[i].dmin) * y[i].d;
-        sumf -= dmin * (float)sumi;
     }
-    for (int l = 0; l < 8; l++) sumf += sums[l];
-    return sumf;
+    return (float)acc;
 }
 
 static float vec_dot_q6_K_q8_K(int64_t n, const block_q6_K *x, const block_q8_K *y) {
     const int64_t nb = n / QK_K;
-    int8_t aux8[QK_K];
-    float sums[8] = {0};
-    float sumf = 0;
+    double acc = 0.0;
     for (int64_t i = 0; i < nb; i++) {
-        const uint8_t *q4 = x[i].ql, *qh = x[i].qh;
-        const int8_t *q8 = y[i].qs;
-        int32_t aux32[8] = {0};
-        int8_t *a = aux8;
-        for (int j = 0; j < QK_K; j += 128) {
-            for (int l = 0; l < 32; l++) {
-                a[l + 0] = (int8_t)((q4[l + 0] & 0xF) | (((qh[l] >> 0) & 3) << 4)) - 32;
-                a[l + 32] = (int8_t)((q4[l + 32] & 0xF) | (((qh[l] >> 2) & 3) << 4)) - 32;
-                a[l + 64] = (int8_t)((q4[l + 0] >> 4) | (((qh[l] >> 4) & 3) << 4)) - 32;
-                a[l + 96] = (int8_t)((q4[l + 32] >> 4) | (((qh[l] >> 6) & 3) << 4)) - 32;
+        const float fd = h2f(x[i].d) * y[i].d;
+        for (int h = 0; h < 2; h++) {
+            for (int t = 0; t < 2; t++) { /* unit (h,t): elements 128h + 16t + 32k + [0,16), k = 0..3 */
+                const uint8_t *ql = x[i].ql + 64 * h + 16 * t, *qh = x[i].qh + 32 * h + 16 * t;
+                const int8_t *q8 = y[i].qs + 128 * h + 16 * t;
+                int dk[4] = {0, 0, 0, 0};
+                for (int l = 0; l < 16; l++) {
+                    dk[0] += ((ql[l] & 0xF) | (((qh[l] >> 0) & 3) << 4)) * q8[l];
+                    dk[1] += ((ql[l + 32] & 0xF) | (((qh[l] >> 2) & 3) << 4)) * q8[l + 32];
+                    dk[2] += ((ql[l] >> 4) | (((qh[l] >> 4) & 3) << 4)) * q8[l + 64];
+                    dk[3] += ((ql[l + 32] >> 4) | (((qh[l] >> 6) & 3) << 4)) * q8[l + 96];
+                }
+                int isum = 0;
+                for (int k = 0; k < 4; k++) {
+                    const int g = 8 * h + t + 2 * k; /* 16-wide scale group */
+                    isum += x[i].scales[g] * (dk[k] - 32 * y[i].bsums[g]);
+                }
+                acc += (double)(fd * (float)isum);
             }
-            a += 128; q4 += 64; qh += 32;
         }
-        a = aux8;
-        for (int j = 0; j < QK_K / 16; j++) {
-            const int scale = x[i].scales[j];
-            for (int r = 0; r < 2; r++) {
-                for (int l = 0; l < 8; l++) aux32[l] += scale * ((int16_t)q8[l] * (int16_t)a[l]);
-                q8 += 8; a += 8;
-            }
-        }
-        const float d = h2f(x[i].d) * y[i].d;
-        for (int l = 0; l < 8; l++) sums[l] += d * (float)aux32[l];
     }
-    for (int l = 0; l < 8; l++) sumf += sums[l];
-    return sumf;
+    return (float)acc;
 }
 
 static float vec_dot_q8_0_q8_0(int64_t n, const block_q8_0 *x, const block_q8_0 *y) {
     const int64_t nb = n / QK8_0;
-    float sumf = 0;
+    double acc = 0.0;
     for (int64_t ib = 0; ib < nb; ib++) {
         int sumi = 0;
         for (int j = 0; j < QK8_0; j++) sumi += x[ib].qs[j] * y[ib].qs[j];
-        sumf += (float)sumi * (h2f(x[ib].d) * h2f(y[ib].d));
+        acc += (double)((float)sumi * (h2f(x[ib].d) * h2f(y[ib].d)));
     }
-    return sumf;
+    return (float)acc;
 }
+
 
 static float vec_dot_f32(int64_t n, const float *x, const float *y) {
     float s = 0;
@@ -618,6 +600,30 @@ int oracle_model_set_tensor(oracle_model *m, const char *name, int type, int64_t
     return -1;
 }
 
+/* expf restated with fixed operations so that a GPU can reproduce it bit for bit (glibc's and
+ * CUDA's expf differ in the last ulp; ggml's own vectorised paths use their own polynomial too):
+ * n = rint(x*log2e), r = x - n*ln2 (two-step Cody-Waite), degree-6 Horner with fmaf, scale by 2^n. */
+float oracle_expf(float x) {
+    if (x < -87.0f) return 0.0f;
+    if (x > 88.0f) return INFINITY;
+    const float t = x * 1.44269504088896341f;
+    const float n = rintf(t);
+    float r = fmaf(n, -0.693145751953125f, x);
+    r = fmaf(n, -1.42860682030941723212e-6f, r);
+    float p = 1.0f / 720.0f;
+    p = fmaf(p, r, 1.0f / 120.0f);
+    p = fmaf(p, r, 1.0f / 24.0f);
+    p = fmaf(p, r, 1.0f / 6.0f);
+    p = fmaf(p, r, 0.5f);
+    p = fmaf(p, r, 1.0f);
+    p = fmaf(p, r, 1.0f);
+    const int ni = (int)n; /* [-126, 127] after the clamps above */
+    uint32_t bits = (uint32_t)(ni + 127) << 23;
+    float s;
+    memcpy(&s, &bits, 4);
+    return p * s;
+}
+
 /* RMSNorm: sum of squares in double (ggml_float), scale = 1/sqrtf(mean+eps); then the
  * separate elementwise multiply by the norm weight (Appendix C.4). */
 static void rms_norm_mul(const float *x, const float *w, float *y, int n, float eps) {
@@ -689,26 +695,29 @@ static int eval_token(oracle_model *m, int tok, int pos, float *logits) {
             float mx = -INFINITY;
             for (int j = 0; j < n_kv; j++) {
                 const uint16_t *kr = kc + (size_t)j * kvd + (size_t)g * D;
-                float s = 0;
-                for (int d = 0; d < D; d++) s += qh[d] * h2f(kr[d]);
+                double sd = 0; /* f16 x f16 products are exact in f32; summed order-free in double */
+                for (int d = 0; d < D; d++) sd += (double)(qh[d] * h2f(kr[d]));
+                float s = (float)sd;
                 s *= kq_scale;
                 sc[j] = s;
                 if (s > mx) mx = s;
             }
             double sum = 0.0;
             for (int j = 0; j < n_kv; j++) {
-                const float e = expf(sc[j] - mx);
+                const float e = oracle_expf(sc[j] - mx);
                 sc[j] = e;
                 sum += (double)e;
             }
             const float inv = (float)(1.0 / sum);
             float *o = m->att_out + (size_t)h * D;
-            for (int d = 0; d < D; d++) o[d] = 0;
+            double od[512];
+            for (int d = 0; d < D; d++) od[d] = 0;
             for (int j = 0; j < n_kv; j++) {
                 const float p = h2f(f2h(sc[j] * inv)); /* P -> f16 before the f16 V mat-mul */
                 const uint16_t *vr = vc + (size_t)j * kvd + (size_t)g * D;
-                for (int d = 0; d < D; d++) o[d] += p * h2f(vr[d]);
+                for (int d = 0; d < D; d++) od[d] += (double)(p * h2f(vr[d])); /* exact product, order-free sum */
             }
+            for (int d = 0; d < D; d++) o[d] = (float)od[d];
         }
         oracle_matvec(l->wo.type, l->wo.data, E, (int64_t)H * D, m->att_out, m->tmp);
         for (int i = 0; i < E; i++) m->x[i] += m->tmp[i];
@@ -717,7 +726,7 @@ static int eval_token(oracle_model *m, int tok, int pos, float *logits) {
         oracle_matvec(l->w_up.type, l->w_up.data, FF, E, m->xn, m->up);
         for (int i = 0; i < FF; i++) {
             const float gx = m->gate[i];
-            m->h[i] = (gx / (1.0f + expf(-gx))) * m->up[i];
+            m->h[i] = (gx / (1.0f + oracle_expf(-gx))) * m->up[i];
         }
         oracle_matvec(l->w_down.type, l->w_down.data, E, FF, m->h, m->tmp);
         for (int i = 0; i < E; i++) m->x[i] += m->tmp[i];

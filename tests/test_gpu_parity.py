@@ -1,0 +1,192 @@
+"""GPU parity tests: the CUDA path through the C ABI vs the CPU oracle on the same seeded inputs.
+
+Bars (BASELINE.json north_star): dequantised blocks bit-exact; logits within a stated relative
+tolerance (max-abs-err / logit-std <= 1e-3 vs the activation-quantising oracle); greedy tokens
+identical, with the minimum top-1/top-2 margin reported.
+"""
+import numpy as np
+import pytest
+
+from aios_b200 import capi
+from aios_b200 import gguf_synth as gs
+
+pytestmark = pytest.mark.gpu
+
+QTYPES = [gs.Q8_0, gs.Q4_K, gs.Q5_K, gs.Q6_K]
+LOGIT_TOL = 1e-3  # max |gpu - oracle| / std(oracle logits)
+
+
+@pytest.mark.parametrize("qt", QTYPES)
+def test_dequantize_bit_exact(engine, oracle, qt):
+    rng = np.random.default_rng(qt)
+    blocks = gs.random_blocks(qt, 4096, rng, 0.02)
+    # edge blocks: all-zero, all-ones bytes with finite scales, max 6-bit scales, sub-normal d
+    blocks[0] = 0
+    blocks[1] = 0xFF
+    blocks[2, :] = 0x3F
+    be, bb = gs.BLOCK[qt]
+    if qt in (gs.Q4_K, gs.Q5_K):
+        blocks[1, 0:4] = np.array([0x00, 0x3C, 0x00, 0x38], np.uint8)  # d=1.0 dmin=0.5
+        blocks[3, 0:2] = np.array([0x01, 0x00], np.uint8)  # smallest sub-normal d
+    elif qt == gs.Q6_K:
+        blocks[1, 208:210] = np.array([0x00, 0x3C], np.uint8)
+        blocks[3, 208:210] = np.array([0x01, 0x00], np.uint8)
+    else:
+        blocks[1, 0:2] = np.array([0x00, 0x3C], np.uint8)
+        blocks[3, 0:2] = np.array([0x01, 0x00], np.uint8)
+    n = blocks.shape[0] * be
+    ref = oracle.dequantize(qt, blocks)
+    got = engine.dequantize(qt, blocks, n)
+    assert np.array_equal(ref.view(np.uint32), got.view(np.uint32))
+
+
+def test_dequantize_rejects_ragged(engine):
+    with pytest.raises(capi.AiosError) as ei:
+        engine.dequantize(gs.Q4_K, np.zeros(144, np.uint8), 100)
+    assert ei.value.code == capi.E_INVAL
+    assert engine.dequantize(gs.Q4_K, np.zeros(0, np.uint8), 0).size == 0  # empty input
+
+
+@pytest.mark.parametrize("qt", QTYPES)
+@pytest.mark.parametrize("shape", [(1, 256), (37, 512), (64, 2048), (300, 4096), (50, 5632), (33, 14336)])
+def test_matvec_vs_oracle(engine, oracle, qt, shape):
+    n, k = shape
+    rng = np.random.default_rng([qt, n, k])
+    w = gs.random_blocks(qt, n * k // gs.BLOCK[qt][0], rng, 0.02)
+    x = rng.standard_normal(k, dtype=np.float32)
+    x[:7] = 0  # some exact zeros
+    ref = oracle.matvec(qt, w, n, k, x)
+    got = engine.matvec(qt, w, n, k, x)
+    # only the float summation order differs: error relative to the size of a typical output
+    scale = max(np.abs(ref).max(), 0.02 * np.sqrt(k) * x.std())
+    assert np.abs(got - ref).max() / scale < 2e-6, (np.abs(got - ref).max(), scale)
+
+
+@pytest.mark.parametrize("qt", [gs.Q4_K, gs.Q6_K, gs.Q8_0])
+def test_matvec_all_zero_and_signed_ties(engine, oracle, qt):
+    n, k = 16, 512
+    rng = np.random.default_rng(3)
+    w = gs.random_blocks(qt, n * k // gs.BLOCK[qt][0], rng, 0.02)
+    x = np.zeros(k, np.float32)
+    assert np.array_equal(engine.matvec(qt, w, n, k, x), np.zeros(n, np.float32))
+    # +a and -a tie for amax: the first one decides the sign of the Q8_K scale
+    x = rng.standard_normal(k, dtype=np.float32) * 0.1
+    x[5], x[200] = -3.0, 3.0
+    x[300], x[400] = 2.5, -2.5
+    ref = oracle.matvec(qt, w, n, k, x)
+    got = engine.matvec(qt, w, n, k, x)
+    assert np.abs(got - ref).max() / (np.abs(ref).max() + 1e-12) < 2e-6
+
+
+@pytest.mark.parametrize("qt", [gs.Q4_K, gs.Q6_K, gs.Q8_0])
+def test_matvec_with_rmsnorm(engine, oracle, qt):
+    n, k = 96, 2048
+    rng = np.random.default_rng(11)
+    w = gs.random_blocks(qt, n * k // gs.BLOCK[qt][0], rng, 0.02)
+    x = rng.standard_normal(k, dtype=np.float32) * 3
+    nw = (rng.random(k, dtype=np.float32) * 0.4 + 0.8).astype(np.float32)
+    eps = 1e-5
+    ss = np.sum((x * x).astype(np.float64))
+    scale = np.float32(1.0) / np.sqrt(np.float32(ss / k) + np.float32(eps), dtype=np.float32)
+    xn = (x * scale) * nw
+    ref = oracle.matvec(qt, w, n, k, xn.astype(np.float32))
+    got = engine.matvec(qt, w, n, k, x, norm_w=nw, eps=eps)
+    assert np.abs(got - ref).max() / (np.abs(ref).max() + 1e-12) < 2e-4
+
+
+@pytest.mark.parametrize("arch,ftype", [("tiny", "Q4_K_M"), ("tiny", "Q8_0"), ("tiny-gqa4", "Q4_K_M")])
+def test_model_logits_and_kv(engine, oracle, tmp_models, arch, ftype):
+    path = tmp_models(arch, ftype)
+    m = engine.load_model("t", path, n_ctx=128)
+    try:
+        om = oracle.OracleModel(path, n_ctx=128)
+        prompt = gs.synthetic_prompt(arch, 24, 5)
+        ref = om.eval_all(prompt)
+        seq = m.new_seq()
+        try:
+            for i in range(len(prompt)):
+                seq.prefill(prompt[i:i + 1])
+                got = seq.logits()
+                err = np.abs(got - ref[i]).max() / ref[i].std()
+                assert err < LOGIT_TOL, (i, err)
+            k, v = seq.read_kv(0, 0, len(prompt))
+            assert k.any() and v.any()
+        finally:
+            seq.free()
+        # whole prompt in one call == token by token
+        got = m.forward_logits(prompt)
+        assert np.abs(got - ref[-1]).max() / ref[-1].std() < LOGIT_TOL
+    finally:
+        m.unload()
+
+
+@pytest.mark.parametrize("arch,ftype", [("tiny", "Q4_K_M"), ("tiny-gqa4", "Q4_K_M"), ("tiny", "Q8_0")])
+def test_greedy_tokens_match_oracle(engine, oracle, tmp_models, arch, ftype):
+    path = tmp_models(arch, ftype)
+    m = engine.load_model("t", path, n_ctx=256)
+    try:
+        om = oracle.OracleModel(path, n_ctx=256)
+        prompt = gs.synthetic_prompt(arch, 32, 9)
+        n_gen = 128
+        ref, margins = om.greedy(prompt, n_gen)
+        got = m.generate(prompt, n_gen)
+        print(f"min top1-top2 margin {margins.min():.3e}")
+        assert got.shape == ref.shape
+        assert np.array_equal(got, ref), (np.nonzero(got != ref)[0][:4], margins.min())
+    finally:
+        m.unload()
+
+
+def test_decode_stops_at_context_and_steps_agree(engine, tmp_models):
+    path = tmp_models("tiny", "Q4_K_M")
+    m = engine.load_model("t", path, n_ctx=48)
+    try:
+        prompt = gs.synthetic_prompt("tiny", 40, 1)
+        a = m.generate(prompt, 100)
+        assert a.size == 8  # clamped: n_prompt + generated <= n_ctx
+        s = m.new_seq()
+        try:
+            s.prefill(prompt)
+            b = np.array([s.step() for _ in range(8)], np.int32)
+            assert np.array_equal(a, b)
+            with pytest.raises(capi.AiosError):
+                s.step()
+        finally:
+            s.free()
+    finally:
+        m.unload()
+
+
+def test_load_errors(engine, tmp_path):
+    with pytest.raises(capi.AiosError) as ei:
+        engine.load_model("x", str(tmp_path / "missing.gguf"))
+    assert ei.value.code == capi.E_IO
+    p = tmp_path / "junk.gguf"
+    p.write_bytes(b"not a gguf file at all, just some bytes....")
+    with pytest.raises(capi.AiosError) as ei:
+        engine.load_model("x", str(p))
+    assert ei.value.code == capi.E_FORMAT
+
+
+def test_loader_matches_gguf_py(engine, tmp_models):
+    from gguf import GGUFReader
+
+    path = tmp_models("tiny", "Q4_K_M")
+    m = engine.load_model("tiny", path, n_ctx=64)
+    try:
+        r = GGUFReader(path)
+        assert m.info.n_tensors == len(r.tensors)
+        for i, t in enumerate(r.tensors):
+            ti = m.tensor_info(i)
+            assert ti.name.decode() == t.name
+            assert ti.type == int(t.tensor_type)
+            assert list(ti.ne)[: ti.n_dims] == [int(x) for x in t.shape]
+            assert ti.offset == int(t.data_offset) - int(r.data_offset)
+            assert ti.nbytes == int(t.n_bytes)
+        a = gs.ARCHS["tiny"]
+        assert (m.info.n_layer, m.info.n_embd, m.info.n_head, m.info.n_head_kv, m.info.n_ff, m.info.n_vocab) == \
+               (a.n_layer, a.n_embd, a.n_head, a.n_head_kv, a.n_ff, a.n_vocab)
+        assert m.info.weight_bytes_per_token == gs.weight_bytes_per_token("tiny", "Q4_K_M")
+        assert m.info.kv_bytes_per_position == gs.kv_bytes_per_position("tiny")
+    finally:
+        m.unload()
