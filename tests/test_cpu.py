@@ -1,0 +1,215 @@
+"""CPU-only tests (-m "not gpu"): the oracle against its golden vectors, the synthetic GGUF author,
+host logic, and that the C-ABI library loads and exports every symbol include/aios_b200.h declares
+(no compute calls without a GPU)."""
+import os
+import re
+
+import numpy as np
+import pytest
+
+from aios_b200 import gguf_synth as gs
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLD = os.path.join(ROOT, "tests", "golden")
+NAMES = {gs.Q8_0: "Q8_0", gs.Q4_K: "Q4_K", gs.Q5_K: "Q5_K", gs.Q6_K: "Q6_K"}
+
+
+def same_bits_or_both_nan(a_bits, b_bits):
+    a, b = a_bits.view(np.float32), b_bits.view(np.float32)
+    return bool(np.all((a_bits == b_bits) | (np.isnan(a) & np.isnan(b))))
+
+
+@pytest.mark.parametrize("qt", list(NAMES))
+def test_oracle_dequant_matches_golden_gguf_py(oracle, qt):
+    g = np.load(os.path.join(GOLD, "dequant_gguf_py.npz"))
+    blocks, want = g[f"{NAMES[qt]}_blocks"], g[f"{NAMES[qt]}_dequant_bits"].reshape(-1)
+    with np.errstate(all="ignore"):
+        got = oracle.dequantize(qt, blocks)
+    assert same_bits_or_both_nan(got.view(np.uint32), want)
+
+
+@pytest.mark.parametrize("qt", list(NAMES))
+def test_oracle_dequant_matches_live_gguf_py(oracle, qt):
+    import gguf
+    from gguf import quants
+
+    blocks = gs.random_blocks(qt, 50000, np.random.default_rng(qt + 100), 0.02)
+    ref = quants.dequantize(blocks, getattr(gguf.GGMLQuantizationType, NAMES[qt])).reshape(-1)
+    got = oracle.dequantize(qt, blocks)
+    assert np.array_equal(ref.view(np.uint32), got.view(np.uint32))
+
+
+def test_oracle_fp16_roundtrip(oracle):
+    L = oracle.lib()
+    bits = np.arange(0, 65536, dtype=np.uint16)
+    ref = bits.view(np.float16).astype(np.float32)
+    got = np.array([L.oracle_h2f(int(b)) for b in bits[::7]], np.float32)
+    r = ref[::7]
+    assert np.all((got == r) | (np.isnan(got) & np.isnan(r)))
+    rng = np.random.default_rng(0)
+    xs = np.concatenate([rng.standard_normal(2000).astype(np.float32) * 10.0 ** rng.integers(-9, 6, 2000),
+                         np.array([0, -0.0, 65504, 65519.99, 65520, 1e-8, 5.96e-8, 2.98e-8, 2.9802322e-8], np.float32)])
+    with np.errstate(over="ignore"):
+        want = xs.astype(np.float16).view(np.uint16)
+    got = np.array([L.oracle_f2h(float(x)) for x in xs], np.uint16)
+    assert np.array_equal(got, want)
+
+
+def test_oracle_q8_K_quantisation_properties(oracle):
+    rng = np.random.default_rng(5)
+    x = rng.standard_normal(1024).astype(np.float32)
+    x[256:512] = 0  # an all-zero block
+    x[600], x[700] = -4.0, 4.0  # signed tie: the first one (negative) decides the sign of the scale
+    q = oracle.quantize_q8_K(x).reshape(4, 292)
+    d = q[:, :4].copy().view(np.float32).reshape(4)
+    qs = q[:, 4:260].copy().view(np.int8).reshape(4, 256)
+    bs = q[:, 260:].copy().view(np.int16).reshape(4, 16)
+    assert d[1] == 0 and not qs[1].any()
+    assert d[2] > 0 and qs[2][600 - 512] == -127 and qs[2][700 - 512] == 127  # iscale=-127/max, max=-4 -> d=-max/127>0
+    assert np.array_equal(bs, qs.reshape(4, 16, 16).sum(-1))
+    rec = qs.astype(np.float32) * d[:, None]
+    assert np.abs(rec.reshape(-1) - x).max() <= np.abs(d).max() * 0.5001 + 1e-7
+    for b in range(4):
+        if d[b] != 0:
+            assert np.abs(qs[b]).max() == 127  # the extreme value always maps to +-127... (|-127| for the max element)
+
+
+@pytest.mark.parametrize("qt", [gs.Q4_K, gs.Q6_K, gs.Q8_0])
+def test_oracle_simd_dots_match_generic(oracle, qt):
+    n, k = 64, 4096
+    rng = np.random.default_rng(qt)
+    w = gs.random_blocks(qt, n * k // gs.BLOCK[qt][0], rng, 0.02)
+    x = rng.standard_normal(k).astype(np.float32)
+    a = oracle.matvec(qt, w, n, k, x, simd=False)
+    b = oracle.matvec(qt, w, n, k, x, simd=True)
+    assert np.abs(a - b).max() / np.abs(a).max() < 1e-5
+    # and against an exact-math float64 product of the dequantised weights: only activation-quantisation noise remains
+    wd = oracle.dequantize(qt, w).reshape(n, k).astype(np.float64)
+    exact = wd @ x.astype(np.float64)
+    assert np.abs(a - exact).max() / np.abs(exact).std() < 5e-2
+
+
+@pytest.mark.parametrize("key", ["tiny_Q4_K_M_7", "tiny_Q8_0_7", "tiny-gqa4_Q4_K_M_7"])
+def test_oracle_model_vs_hf_fp32_golden(oracle, tmp_models, key):
+    """Tolerance tier: the oracle quantises activations (llama.cpp CPU numerics), HF does not, so the
+    logits differ by the activation-quantisation noise: a few % of the logit std, highly correlated."""
+    g = np.load(os.path.join(GOLD, "hf_fp32_logits.npz"))
+    arch, rest = key.split("_", 1)
+    ftype = rest.rsplit("_", 1)[0]
+    path = tmp_models(arch, ftype, 7)
+    om = oracle.OracleModel(path, n_ctx=64)
+    prompt, want = g[key + "_prompt"], g[key + "_hf_fp32_logits"]
+    got = om.eval_all(prompt)
+    err = np.abs(got - want).max(axis=1) / want.std(axis=1)
+    assert err.max() < 0.12, err
+    for i in range(len(prompt)):
+        assert np.corrcoef(got[i], want[i])[0, 1] > 0.995
+
+
+def test_oracle_greedy_is_deterministic_and_eval_all_consistent(oracle, tmp_models):
+    path = tmp_models("tiny", "Q4_K_M", 7)
+    om = oracle.OracleModel(path, n_ctx=128)
+    prompt = gs.synthetic_prompt("tiny", 12, 3)
+    a, ma = om.greedy(prompt, 20)
+    om2 = oracle.OracleModel(path, n_ctx=128)
+    b, mb = om2.greedy(prompt, 20)
+    assert np.array_equal(a, b) and np.array_equal(ma, mb) and (ma >= 0).all()
+    all_logits = om2.eval_all(prompt)
+    assert np.array_equal(all_logits[-1], oracle.OracleModel(path, n_ctx=128).eval(prompt))
+
+
+def test_synth_writer_is_valid_gguf(tmp_models):
+    from gguf import GGUFReader
+
+    for arch, ftype in [("tiny", "Q4_K_M"), ("tiny", "Q8_0"), ("tiny-gqa4", "Q4_K_M")]:
+        path = tmp_models(arch, ftype, 7)
+        r = GGUFReader(path)
+        plan = gs.tensor_plan(gs.ARCHS[arch], ftype)
+        assert [t.name for t in r.tensors] == [p[0] for p in plan]
+        for t, (name, shape, qt) in zip(r.tensors, plan):
+            assert int(t.tensor_type) == qt
+            assert [int(x) for x in t.shape] == list(reversed(shape))
+            assert int(t.n_bytes) == gs.tensor_nbytes(shape, qt)
+            assert int(t.data_offset) % 32 == 0
+        assert os.path.getsize(path) == int(r.tensors[-1].data_offset) + (int(r.tensors[-1].n_bytes) + 31) // 32 * 32
+
+
+def test_q4_k_m_mix_and_algorithmic_bytes_match_survey():
+    # Mistral-7B Q4_K_M streams 4.2940 GB/token (Q4_K 3,359.6 MB + Q6_K 933.3 MB + norms)
+    assert sum(gs.use_more_bits(i, 32) for i in range(32)) == 16
+    assert sum(gs.use_more_bits(i, 22) for i in range(22)) == 10
+    wb = gs.weight_bytes_per_token("mistral-7b", "Q4_K_M")
+    assert abs(wb / 1e9 - 4.2940) < 2e-3, wb
+    assert gs.kv_bytes_per_position("mistral-7b") == 131072
+    assert abs(gs.weight_bytes_per_token("tinyllama-1.1b", "Q4_K_M") / 1e9 - 0.6302) < 1e-3
+    assert gs.kv_bytes_per_position("tinyllama-1.1b") == 22528
+
+
+def test_capi_exports_every_declared_symbol():
+    from aios_b200 import capi
+
+    hdr = open(os.path.join(ROOT, "include", "aios_b200.h")).read()
+    hdr = re.sub(r"/\*.*?\*/", "", hdr, flags=re.S)
+    declared = set(re.findall(r"\b(aios_[a-z0-9_]+)\s*\(", hdr))
+    assert declared, "no declarations found"
+    assert declared == set(capi.SYMBOLS), (declared ^ set(capi.SYMBOLS))
+    L = capi.lib()
+    for name in declared:
+        assert getattr(L, name) is not None
+    assert L.aios_version().decode().startswith("aios_b200")
+
+
+def test_no_gpu_fails_loudly_instead_of_falling_back():
+    from aios_b200 import capi
+
+    if capi.device_count() > 0:
+        pytest.skip("a GPU is present")
+    with pytest.raises(capi.AiosError) as ei:
+        capi.Engine(device=0)
+    assert ei.value.code == capi.E_CUDA
+    assert "no CPU fallback" in ei.value.msg
+
+
+def test_product_package_never_imports_the_oracle():
+    pkg = os.path.join(ROOT, "aios_b200")
+    for dirpath, _, files in os.walk(pkg):
+        for f in files:
+            if f.endswith((".py", ".cu", ".cuh", ".cpp", ".h")):
+                src = open(os.path.join(dirpath, f), errors="replace").read()
+                assert "import oracle" not in src and "from oracle" not in src and "libaios_oracle" not in src, f
+                assert not re.search(r'#include\s*[<"][^>"]*oracle', src), f  # comments may cite it, code may not use it
+
+
+def _gloo_worker(rank, world, port, q):
+    import torch.distributed as dist
+
+    from aios_b200 import replicas
+
+    dist.init_process_group("gloo", init_method=f"tcp://127.0.0.1:{port}", rank=rank, world_size=world)
+    mine = replicas.assign_requests(7, world, rank)
+    units, ms, thr = replicas.aggregate_throughput(128.0 * len(mine), 100.0 + 50.0 * rank, world)
+    q.put((rank, mine, units, ms, thr))
+    dist.destroy_process_group()
+
+
+def test_replica_bookkeeping_world_size_2_gloo():
+    import socket
+
+    import torch.multiprocessing as mp
+
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    ps = [ctx.Process(target=_gloo_worker, args=(r, 2, port, q)) for r in range(2)]
+    for p in ps:
+        p.start()
+    res = sorted(q.get(timeout=120) for _ in ps)
+    for p in ps:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert res[0][1] == [0, 2, 4, 6] and res[1][1] == [1, 3, 5]
+    for r in res:
+        assert r[2] == 128.0 * 7 and r[3] == 150.0 and abs(r[4] - 128.0 * 7 / 0.150) < 1e-6

@@ -1,9 +1,17 @@
 """GPU parity tests: the CUDA path through the C ABI vs the CPU oracle on the same seeded inputs.
 
 Bars (BASELINE.json north_star): dequantised blocks bit-exact; logits within a stated relative
-tolerance (max-abs-err / logit-std <= 1e-3 vs the activation-quantising oracle); greedy tokens
-identical, with the minimum top-1/top-2 margin reported.
+tolerance; greedy tokens identical, with the minimum top-1/top-2 margin reported.
+
+The stated logit tolerance is LOGIT_TOL = 1e-6 (max-abs-err / logit-std), and in practice the
+logits are BIT-IDENTICAL: the engine mirrors the oracle's order-free numerics (one f32 term per
+64-weight unit summed in double; deterministic expf; exact f16 products summed in double), so the
+only possible difference is a double-rounding event of probability ~1e-7 per value.  A loose
+tolerance would be meaningless here anyway: one flipped Q8 rounding re-randomises the activation
+quantisation noise of all later layers (~4e-2 of the logit std on the tiny models).
 """
+import os
+
 import numpy as np
 import pytest
 
@@ -13,7 +21,8 @@ from aios_b200 import gguf_synth as gs
 pytestmark = pytest.mark.gpu
 
 QTYPES = [gs.Q8_0, gs.Q4_K, gs.Q5_K, gs.Q6_K]
-LOGIT_TOL = 1e-3  # max |gpu - oracle| / std(oracle logits)
+LOGIT_TOL = 1e-6  # max |gpu - oracle| / std(oracle logits)
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 
 
 @pytest.mark.parametrize("qt", QTYPES)
@@ -40,6 +49,18 @@ def test_dequantize_bit_exact(engine, oracle, qt):
     assert np.array_equal(ref.view(np.uint32), got.view(np.uint32))
 
 
+@pytest.mark.parametrize("qt", QTYPES)
+def test_dequantize_golden_gguf_py(engine, qt):
+    """Committed fixture made by gguf-py (scripts/make_golden.py): edge blocks incl. max-finite and sub-normal
+    fp16 scales, where the result overflows to inf / nan; NaN payloads are not compared."""
+    name = {gs.Q8_0: "Q8_0", gs.Q4_K: "Q4_K", gs.Q5_K: "Q5_K", gs.Q6_K: "Q6_K"}[qt]
+    g = np.load(os.path.join(GOLD, "dequant_gguf_py.npz"))
+    blocks, want = g[f"{name}_blocks"], g[f"{name}_dequant_bits"].reshape(-1)
+    got = engine.dequantize(qt, blocks, want.size).view(np.uint32)
+    gf, wf = got.view(np.float32), want.view(np.float32)
+    assert np.all((got == want) | (np.isnan(gf) & np.isnan(wf)))
+
+
 def test_dequantize_rejects_ragged(engine):
     with pytest.raises(capi.AiosError) as ei:
         engine.dequantize(gs.Q4_K, np.zeros(144, np.uint8), 100)
@@ -57,9 +78,7 @@ def test_matvec_vs_oracle(engine, oracle, qt, shape):
     x[:7] = 0  # some exact zeros
     ref = oracle.matvec(qt, w, n, k, x)
     got = engine.matvec(qt, w, n, k, x)
-    # only the float summation order differs: error relative to the size of a typical output
-    scale = max(np.abs(ref).max(), 0.02 * np.sqrt(k) * x.std())
-    assert np.abs(got - ref).max() / scale < 2e-6, (np.abs(got - ref).max(), scale)
+    assert np.array_equal(got.view(np.uint32), ref.view(np.uint32)), np.abs(got - ref).max()
 
 
 @pytest.mark.parametrize("qt", [gs.Q4_K, gs.Q6_K, gs.Q8_0])
@@ -75,7 +94,7 @@ def test_matvec_all_zero_and_signed_ties(engine, oracle, qt):
     x[300], x[400] = 2.5, -2.5
     ref = oracle.matvec(qt, w, n, k, x)
     got = engine.matvec(qt, w, n, k, x)
-    assert np.abs(got - ref).max() / (np.abs(ref).max() + 1e-12) < 2e-6
+    assert np.array_equal(got.view(np.uint32), ref.view(np.uint32))
 
 
 @pytest.mark.parametrize("qt", [gs.Q4_K, gs.Q6_K, gs.Q8_0])
@@ -86,12 +105,12 @@ def test_matvec_with_rmsnorm(engine, oracle, qt):
     x = rng.standard_normal(k, dtype=np.float32) * 3
     nw = (rng.random(k, dtype=np.float32) * 0.4 + 0.8).astype(np.float32)
     eps = 1e-5
-    ss = np.sum((x * x).astype(np.float64))
+    ss = np.sum((x * x).astype(np.float64))  # f32 squares summed in double, like ggml_rms_norm
     scale = np.float32(1.0) / np.sqrt(np.float32(ss / k) + np.float32(eps), dtype=np.float32)
-    xn = (x * scale) * nw
-    ref = oracle.matvec(qt, w, n, k, xn.astype(np.float32))
+    xn = ((x * scale).astype(np.float32) * nw).astype(np.float32)
+    ref = oracle.matvec(qt, w, n, k, xn)
     got = engine.matvec(qt, w, n, k, x, norm_w=nw, eps=eps)
-    assert np.abs(got - ref).max() / (np.abs(ref).max() + 1e-12) < 2e-4
+    assert np.array_equal(got.view(np.uint32), ref.view(np.uint32)), np.abs(got - ref).max()
 
 
 @pytest.mark.parametrize("arch,ftype", [("tiny", "Q4_K_M"), ("tiny", "Q8_0"), ("tiny-gqa4", "Q4_K_M")])
@@ -109,8 +128,20 @@ def test_model_logits_and_kv(engine, oracle, tmp_models, arch, ftype):
                 got = seq.logits()
                 err = np.abs(got - ref[i]).max() / ref[i].std()
                 assert err < LOGIT_TOL, (i, err)
-            k, v = seq.read_kv(0, 0, len(prompt))
-            assert k.any() and v.any()
+            # the f16 KV cache must hold exactly the oracle's bits
+            import ctypes as C
+            L = oracle.lib()
+            L.oracle_k_cache.restype = C.POINTER(C.c_uint16)
+            L.oracle_k_cache.argtypes = [C.c_void_p]
+            L.oracle_v_cache.restype = C.POINTER(C.c_uint16)
+            L.oracle_v_cache.argtypes = [C.c_void_p]
+            a = gs.ARCHS[arch]
+            kvd = a.n_head_kv * a.head_dim
+            ok = np.ctypeslib.as_array(L.oracle_k_cache(om.h), shape=(a.n_layer, 128, kvd))
+            ov = np.ctypeslib.as_array(L.oracle_v_cache(om.h), shape=(a.n_layer, 128, kvd))
+            for il in range(a.n_layer):
+                k, v = seq.read_kv(il, 0, len(prompt))
+                assert np.array_equal(k, ok[il, :len(prompt)]) and np.array_equal(v, ov[il, :len(prompt)])
         finally:
             seq.free()
         # whole prompt in one call == token by token
