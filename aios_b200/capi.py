@@ -18,6 +18,9 @@ LIB_PATH = os.path.join(_HERE, "libaios_b200.so")
 AIOS_OK, E_INVAL, E_IO, E_FORMAT, E_CUDA, E_NOMEM, E_STATE, E_RANGE = 0, -1, -2, -3, -4, -5, -6, -7
 TYPE_F32, TYPE_F16, TYPE_Q8_0, TYPE_Q4_K, TYPE_Q5_K, TYPE_Q6_K = 0, 1, 8, 12, 13, 14
 ENGINE_NO_GRAPH = 1
+ENGINE_NO_PDL = 2
+ENGINE_NO_PFD = 4
+ENGINE_USE_PFD = 8
 
 
 class AiosError(RuntimeError):
@@ -84,6 +87,7 @@ SYMBOLS = {
     "aios_seq_read_activation": (C.c_int, [_P, C.c_int32, _P, C.c_int64]),
     "aios_seq_bench_decode": (C.c_int, [_P, C.c_int32, C.POINTER(BenchResult)]),
     "aios_seq_profile_decode": (C.c_int, [_P, C.c_int32, C.POINTER(BenchResult)]),
+    "aios_seq_phase_timing": (C.c_int, [_P, _P, C.c_int32, C.POINTER(C.c_int32)]),
     "aios_seq_snapshot": (C.c_int, [_P]),
     "aios_seq_restore": (C.c_int, [_P]),
     "aios_bench_gemv": (C.c_int, [_P, C.c_int32, C.c_int64, C.c_int64, C.c_int32, C.c_int32, C.POINTER(C.c_float)]),
@@ -259,6 +263,12 @@ class Seq:
         r = BenchResult()
         _check(lib().aios_seq_profile_decode(self.h, n_tokens, C.byref(r)))
         return r
+
+    def phase_timing(self) -> np.ndarray:
+        out = np.zeros((4096, 4), dtype=np.uint64)
+        n = C.c_int32(0)
+        _check(lib().aios_seq_phase_timing(self.h, _ptr(out), 4096, C.byref(n)))
+        return out[: n.value].copy()
 
     def snapshot(self):
         _check(lib().aios_seq_snapshot(self.h))

@@ -335,6 +335,19 @@ int aios_seq_profile_decode(aios_seq *s, int32_t n_tokens, aios_bench_result *ou
         return (int)AIOS_OK;
     });
 }
+int aios_seq_phase_timing(aios_seq *s, uint64_t *out, int32_t cap, int32_t *n_phases) {
+    return guarded([&] {
+        if (!s || !out || !n_phases) return fail(AIOS_E_INVAL, "bad argument");
+        Seq &q = s->impl;
+        const int n = q.pfd.n_phases;
+        *n_phases = n;
+        if (cap < n) return fail(AIOS_E_RANGE, "out is too small");
+        std::lock_guard<std::mutex> lk(q.m->eng->mu);
+        q.m->eng->make_current();
+        CUDA_CHECK(cudaMemcpy(out, q.pfd_timing.p, (size_t)n * 4 * sizeof(uint64_t), cudaMemcpyDeviceToHost));
+        return (int)AIOS_OK;
+    });
+}
 int aios_seq_snapshot(aios_seq *s) {
     return guarded([&] {
         if (!s) return fail(AIOS_E_INVAL, "null seq");

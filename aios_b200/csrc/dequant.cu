@@ -67,7 +67,21 @@ __global__ void repack_q4k_kernel(const uint8_t *raw, int64_t n_rows, int k, uin
     const uint8_t *qs = blk + (is_q5 ? 48 : 16);
     reinterpret_cast<uint4 *>(qsa)[idx] = load16_bytes(qs + 32 * p);
     reinterpret_cast<uint4 *>(qsb)[idx] = load16_bytes(qs + 32 * p + 16);
-    if (p == 0) reinterpret_cast<uint4 *>(meta)[row * nb + b] = load16_bytes(blk);
+    if (p == 0) {
+        // META word j (one per unit): sc(2j) | sc(2j+1)<<6 | m(2j)<<12 | m(2j+1)<<18 | byte j of (d | dmin<<16) << 24.
+        // The 6-bit fields are unpacked here once (gguf-py quants.py:479-501) so the GEMV needs no bit surgery;
+        // the block still costs exactly 16 bytes.
+        const uint32_t ddm = (uint32_t)blk[0] | ((uint32_t)blk[1] << 8) | ((uint32_t)blk[2] << 16) | ((uint32_t)blk[3] << 24);
+        uint32_t w[4];
+        for (int j = 0; j < 4; j++) {
+            int s0, m0, s1, m1;
+            scale_min_k4(2 * j, blk + 4, s0, m0);
+            scale_min_k4(2 * j + 1, blk + 4, s1, m1);
+            w[j] = (uint32_t)s0 | ((uint32_t)s1 << 6) | ((uint32_t)m0 << 12) | ((uint32_t)m1 << 18) |
+                   (((ddm >> (8 * j)) & 0xffu) << 24);
+        }
+        reinterpret_cast<uint4 *>(meta)[row * nb + b] = make_uint4(w[0], w[1], w[2], w[3]);
+    }
     if (is_q5) {
         const uint8_t *qh = blk + 16;
         uint32_t lo = 0, hi = 0;

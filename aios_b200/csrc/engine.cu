@@ -261,7 +261,14 @@ Seq::Seq(Model *m_) : m(m_), slot(-1) {
         attn_scratch = DevBuf(attn_scratch_floats(hp.n_head, m->attn_splits, hp.head_dim) * 4);
         attn_counters = DevBuf((size_t)hp.n_head_kv * 4);
         CUDA_CHECK(cudaMemset(attn_counters.p, 0, attn_counters.bytes));
+        pfd_att_max = DevBuf((size_t)hp.n_head_kv * 16 * 8 * sizeof(float));
+        pfd_att_sum = DevBuf((size_t)hp.n_head_kv * 16 * 8 * sizeof(double));
+        pfd_att_acc = DevBuf((size_t)hp.n_head * hp.head_dim * sizeof(double));
+        pfd_counters = DevBuf(32 * sizeof(unsigned));
+        CUDA_CHECK(cudaMemset(pfd_att_acc.p, 0, pfd_att_acc.bytes));
+        CUDA_CHECK(cudaMemset(pfd_counters.p, 0, pfd_counters.bytes));
         reset();
+        build_pfd();
     } catch (...) {
         std::lock_guard<std::mutex> lk(m->mu);
         m->slot_used[slot] = false;
@@ -287,6 +294,7 @@ void Seq::launch_token_pass(bool from_prompt, int prompt_idx, int pos_value, boo
     SeqState *sd = state.as<SeqState>();
     const int n_sms = m->eng->n_sms;
     int launches = 0;
+    const bool pdl = !(m->eng->flags & AIOS_ENGINE_NO_PDL);
     const int32_t *tok_ptr = from_prompt ? prompt.as<int32_t>() + prompt_idx : &sd->cur_token;
     TIMED(2, launch_embed_row(m->tok_embd_type, m->tok_embd_raw.p, m->tok_embd_row_bytes, hp.n_embd, tok_ptr, x.as<float>(),
                      from_prompt ? &sd->pos : nullptr, pos_value, from_prompt ? &sd->cur_token : nullptr, st));
@@ -294,14 +302,23 @@ void Seq::launch_token_pass(bool from_prompt, int prompt_idx, int pos_value, boo
     const int QD = hp.n_head * hp.head_dim, KVD = hp.n_head_kv * hp.head_dim;
     for (int il = 0; il < hp.n_layer; il++) {
         const Layer &L = m->layers[il];
-        {   // RMSNorm + Q,K,V projections in one launch
+        {   // RMSNorm + Q,K,V projections: one launch when the three matrices share a type (else q,k + v)
             GemvParams p{};
-            p.n_seg = 3; p.epi = EPI_STORE; p.k = hp.n_embd;
+            const bool same = L.wv.w.type == L.wq.w.type;
+            p.n_seg = same ? 3 : 2; p.epi = EPI_STORE; p.k = hp.n_embd;
             p.seg[0] = L.wq.w; p.seg[1] = L.wk.w; p.seg[2] = L.wv.w;
             p.out[0] = qkv.as<float>(); p.out[1] = qkv.as<float>() + QD; p.out[2] = qkv.as<float>() + QD + KVD;
             p.x = x.as<float>(); p.norm_w = L.attn_norm.as<float>(); p.eps = hp.rms_eps;
-            TIMED(0, launch_gemv(p, gemv_plan_grid(p, n_sms), st));
+            TIMED(0, launch_gemv(p, gemv_plan_grid(p, n_sms), st, pdl));
             launches++;
+            if (!same) {
+                GemvParams v{};
+                v.n_seg = 1; v.epi = EPI_STORE; v.k = hp.n_embd;
+                v.seg[0] = L.wv.w; v.out[0] = qkv.as<float>() + QD + KVD;
+                v.x = x.as<float>(); v.norm_w = L.attn_norm.as<float>(); v.eps = hp.rms_eps;
+                TIMED(0, launch_gemv(v, gemv_plan_grid(v, n_sms), st, pdl));
+                launches++;
+            }
         }
         {   // RoPE + KV write + flash-decode
             AttnParams a{};
@@ -320,7 +337,7 @@ void Seq::launch_token_pass(bool from_prompt, int prompt_idx, int pos_value, boo
             GemvParams p{};
             p.n_seg = 1; p.epi = EPI_ADD; p.k = QD;
             p.seg[0] = L.wo.w; p.out[0] = x.as<float>(); p.x = att.as<float>();
-            TIMED(0, launch_gemv(p, gemv_plan_grid(p, n_sms), st));
+            TIMED(0, launch_gemv(p, gemv_plan_grid(p, n_sms), st, pdl));
             launches++;
         }
         {   // RMSNorm + gate/up + SwiGLU
@@ -328,14 +345,14 @@ void Seq::launch_token_pass(bool from_prompt, int prompt_idx, int pos_value, boo
             p.n_seg = 2; p.epi = EPI_SWIGLU; p.k = hp.n_embd;
             p.seg[0] = L.w_gate.w; p.seg[1] = L.w_up.w; p.out[0] = h.as<float>();
             p.x = x.as<float>(); p.norm_w = L.ffn_norm.as<float>(); p.eps = hp.rms_eps;
-            TIMED(0, launch_gemv(p, gemv_plan_grid(p, n_sms), st));
+            TIMED(0, launch_gemv(p, gemv_plan_grid(p, n_sms), st, pdl));
             launches++;
         }
         {   // down projection + residual add
             GemvParams p{};
             p.n_seg = 1; p.epi = EPI_ADD; p.k = hp.n_ff;
             p.seg[0] = L.w_down.w; p.out[0] = x.as<float>(); p.x = h.as<float>();
-            TIMED(0, launch_gemv(p, gemv_plan_grid(p, n_sms), st));
+            TIMED(0, launch_gemv(p, gemv_plan_grid(p, n_sms), st, pdl));
             launches++;
         }
     }
@@ -344,7 +361,10 @@ void Seq::launch_token_pass(bool from_prompt, int prompt_idx, int pos_value, boo
         p.n_seg = 1; p.epi = EPI_STORE; p.k = hp.n_embd;
         p.seg[0] = m->output.w; p.out[0] = logits.as<float>();
         p.x = x.as<float>(); p.norm_w = m->output_norm.as<float>(); p.eps = hp.rms_eps;
-        TIMED(0, launch_gemv(p, gemv_plan_grid(p, n_sms), st));
+        // the lm_head epilogue keeps the packed (value, index) arg-max of the logits it writes
+        CUDA_CHECK(cudaMemsetAsync(&sd->argmax_key, 0, sizeof(unsigned long long), st));
+        p.argmax_key = &sd->argmax_key;
+        TIMED(0, launch_gemv(p, gemv_plan_grid(p, n_sms), st, false));
         launches++;
     }
     if (n_launch) *n_launch += launches;
@@ -413,7 +433,9 @@ int Seq::decode(const aios_sampling &sp, int max_tokens, int32_t *out) {
     const bool use_graph = !(m->eng->flags & AIOS_ENGINE_NO_GRAPH);
     int32_t hdr[2] = {n_past - 1, 0};  // pos, step
     CUDA_CHECK(cudaMemcpyAsync(state.p, hdr, sizeof(hdr), cudaMemcpyHostToDevice, st));
-    if (use_graph) {
+    if (use_pfd(sp)) {
+        launch_pfd_tokens(steps, st);  // one cooperative launch for all the tokens
+    } else if (use_graph) {
         ensure_graph(sp);
         for (int i = 0; i < steps; i++) CUDA_CHECK(cudaGraphLaunch(graph, st));
     } else {
@@ -440,7 +462,8 @@ void Seq::bench_decode(int n_tokens, aios_bench_result *out) {
     m->eng->make_current();
     cudaStream_t st = m->eng->stream;
     aios_sampling sp{};  // greedy
-    ensure_graph(sp);
+    const bool fused = use_pfd(sp);
+    if (!fused) ensure_graph(sp);
     int32_t hdr[2] = {n_past - 1, 0};
     CUDA_CHECK(cudaMemcpyAsync(state.p, hdr, sizeof(hdr), cudaMemcpyHostToDevice, st));
     cudaEvent_t e0, e1;
@@ -448,7 +471,8 @@ void Seq::bench_decode(int n_tokens, aios_bench_result *out) {
     CUDA_CHECK(cudaEventCreate(&e1));
     CUDA_CHECK(cudaStreamSynchronize(st));
     CUDA_CHECK(cudaEventRecord(e0, st));
-    for (int i = 0; i < steps; i++) CUDA_CHECK(cudaGraphLaunch(graph, st));
+    if (fused) launch_pfd_tokens(steps, st);
+    else for (int i = 0; i < steps; i++) CUDA_CHECK(cudaGraphLaunch(graph, st));
     CUDA_CHECK(cudaEventRecord(e1, st));
     CUDA_CHECK(cudaEventSynchronize(e1));
     float ms = 0;
@@ -458,7 +482,7 @@ void Seq::bench_decode(int n_tokens, aios_bench_result *out) {
     memset(out, 0, sizeof(*out));
     out->ms_total = ms;
     out->n_tokens = steps;
-    out->kernel_launches = steps * kernels_per_step;
+    out->kernel_launches = fused ? 1 : steps * kernels_per_step;
     out->n_past_begin = n_past;
     out->n_past_end = n_past + steps;
     n_past += steps;
@@ -515,8 +539,10 @@ void Seq::profile_decode(int n_tokens, aios_bench_result *out) {
 void Seq::snapshot() {
     if (!have_logits) throw std::runtime_error("nothing to snapshot: prefill first");
     m->eng->make_current();
-    if (!snap_logits.p) snap_logits = DevBuf(logits.bytes);
+    if (!snap_logits.p) snap_logits = DevBuf(logits.bytes + sizeof(unsigned long long));
     CUDA_CHECK(cudaMemcpyAsync(snap_logits.p, logits.p, logits.bytes, cudaMemcpyDeviceToDevice, m->eng->stream));
+    CUDA_CHECK(cudaMemcpyAsync(snap_logits.as<uint8_t>() + logits.bytes, &state.as<SeqState>()->argmax_key,
+                               sizeof(unsigned long long), cudaMemcpyDeviceToDevice, m->eng->stream));  // the logits' arg-max key
     CUDA_CHECK(cudaStreamSynchronize(m->eng->stream));
     snap_n_past = n_past;
 }
@@ -525,8 +551,117 @@ void Seq::restore() {
     if (snap_n_past < 0) throw std::runtime_error("no snapshot");
     m->eng->make_current();
     CUDA_CHECK(cudaMemcpyAsync(logits.p, snap_logits.p, logits.bytes, cudaMemcpyDeviceToDevice, m->eng->stream));
+    CUDA_CHECK(cudaMemcpyAsync(&state.as<SeqState>()->argmax_key, snap_logits.as<uint8_t>() + logits.bytes,
+                               sizeof(unsigned long long), cudaMemcpyDeviceToDevice, m->eng->stream));
     n_past = snap_n_past;
     have_logits = true;
+}
+
+// ---------------------------------------------------------------- persistent fused decode (pfd.cu)
+static int perm_bit(int type) { return type == T_Q6_K ? 2 : (type == T_Q8_0 ? 4 : 1); }
+
+void Seq::build_pfd() {
+    const HParams &hp = m->hp;
+    const int QD = hp.n_head * hp.head_dim, KVD = hp.n_head_kv * hp.head_dim;
+    std::vector<PfdPhase> ph;
+    auto gemv = [&](int n_seg, const WPlanes *segs, float *const *outs, int epi, int k, const float *xin, const double *x64,
+                    const float *norm_w) {
+        PfdPhase P{};
+        P.kind = PH_GEMV; P.n_seg = n_seg; P.epi = epi; P.k = k;
+        P.x = xin; P.x64 = x64; P.norm_w = norm_w; P.eps = hp.rms_eps;
+        int units = 0;
+        for (int i = 0; i < n_seg; i++) {
+            P.seg[i] = segs[i]; P.out[i] = outs[i];
+            P.perm_mask |= perm_bit(segs[i].type);
+            if (epi != EPI_SWIGLU) { P.unit_begin[i] = units; units += (segs[i].n_rows + 1) / 2; }
+        }
+        if (epi == EPI_SWIGLU) { P.unit_begin[0] = 0; units = segs[0].n_rows; P.out[0] = outs[0]; }
+        for (int i = n_seg; i < 4; i++) P.unit_begin[i] = units;
+        P.units_total = units;
+        ph.push_back(P);
+        return ph.size() - 1;
+    };
+    float *xq = x.as<float>(), *qk = qkv.as<float>(), *hh = h.as<float>();
+    for (int il = 0; il < hp.n_layer; il++) {
+        const Layer &L = m->layers[il];
+        {
+            const WPlanes s[3] = {L.wq.w, L.wk.w, L.wv.w};
+            float *o[3] = {qk, qk + QD, qk + QD + KVD};
+            const size_t i = gemv(3, s, o, EPI_STORE, hp.n_embd, xq, nullptr, L.attn_norm.as<float>());
+            if (il == 0) ph[i].embed = 1;
+        }
+        {
+            PfdPhase P{};
+            P.kind = PH_ATTN;
+            P.k_cache = m->k_cache(slot, il); P.v_cache = m->v_cache(slot, il);
+            ph.push_back(P);
+        }
+        {
+            const WPlanes s[1] = {L.wo.w};
+            float *o[1] = {xq};
+            gemv(1, s, o, EPI_ADD, QD, nullptr, pfd_att_acc.as<double>(), nullptr);
+        }
+        {
+            const WPlanes s[2] = {L.w_gate.w, L.w_up.w};
+            float *o[2] = {hh, hh};
+            const size_t i = gemv(2, s, o, EPI_SWIGLU, hp.n_embd, xq, nullptr, L.ffn_norm.as<float>());
+            ph[i].zero_att = 1;
+        }
+        {
+            const WPlanes s[1] = {L.w_down.w};
+            float *o[1] = {xq};
+            gemv(1, s, o, EPI_ADD, hp.n_ff, hh, nullptr, nullptr);
+        }
+    }
+    {
+        const WPlanes s[1] = {m->output.w};
+        float *o[1] = {logits.as<float>()};
+        const size_t i = gemv(1, s, o, EPI_STORE, hp.n_embd, xq, nullptr, m->output_norm.as<float>());
+        ph[i].argmax = 1;
+    }
+    pfd_phases = DevBuf(ph.size() * sizeof(PfdPhase));
+    CUDA_CHECK(cudaMemcpy(pfd_phases.p, ph.data(), ph.size() * sizeof(PfdPhase), cudaMemcpyHostToDevice));
+
+    SeqState *sd = state.as<SeqState>();
+    PfdParams &p = pfd;
+    p = PfdParams{};
+    p.phases = pfd_phases.as<PfdPhase>();
+    p.n_phases = (int)ph.size();
+    p.out_tokens = out_tokens.as<int32_t>();
+    p.state = reinterpret_cast<int32_t *>(sd);
+    p.argmax_key = &sd->argmax_key;
+    p.x = xq; p.qkv = qk;
+    p.tok_embd = m->tok_embd_raw.as<uint8_t>();
+    p.tok_embd_row_bytes = m->tok_embd_row_bytes; p.tok_embd_type = m->tok_embd_type; p.n_embd = hp.n_embd;
+    p.rope_cos = m->rope_cos.as<float>(); p.rope_sin = m->rope_sin.as<float>();
+    p.n_head = hp.n_head; p.n_kv = hp.n_head_kv; p.hd = hp.head_dim; p.n_rot = hp.n_rot;
+    p.att_scale = 1.0f / sqrtf((float)hp.head_dim);
+    const int n_sms = m->eng->n_sms;
+    p.att_group = std::max(1, std::min(16, n_sms / hp.n_head_kv));
+    p.att_per_cap = ((hp.n_ctx + p.att_group - 1) / p.att_group + 1) & ~1;
+    p.att_max = pfd_att_max.as<float>(); p.att_sum = pfd_att_sum.as<double>(); p.att_acc = pfd_att_acc.as<double>();
+    p.att_counters = pfd_counters.as<unsigned>(); p.bar_counter = pfd_counters.as<unsigned>() + 16;
+    p.k_max = std::max(std::max(hp.n_embd, hp.n_ff), QD);
+    pfd_timing = DevBuf(ph.size() * 4 * sizeof(unsigned long long));
+    CUDA_CHECK(cudaMemset(pfd_timing.p, 0, pfd_timing.bytes));
+    p.timing = pfd_timing.as<unsigned long long>();
+    pfd_grid = (hp.n_head_kv <= n_sms) ? pfd_max_grid(n_sms, p) : 0;
+}
+
+bool Seq::use_pfd(const aios_sampling &sp) const {
+    // opt-in until it beats the per-op path (AIOS_ENGINE_USE_PFD); AIOS_ENGINE_NO_PFD always wins
+    const int f = m->eng->flags;
+    return pfd_grid > 0 && !(sp.temperature > 0.f) && (f & AIOS_ENGINE_USE_PFD) && !(f & AIOS_ENGINE_NO_PFD);
+}
+
+// n greedy tokens after the current position; device state (pos, step) must already be set
+void Seq::launch_pfd_tokens(int n, cudaStream_t st) {
+    PfdParams p = pfd;
+    p.n_tokens = n;
+    p.pos0 = n_past - 1;
+    p.step0 = 0;
+    CUDA_CHECK(cudaMemsetAsync(pfd_counters.p, 0, pfd_counters.bytes, st));
+    launch_pfd(p, pfd_grid, st);
 }
 
 void Seq::read_logits(float *out) {

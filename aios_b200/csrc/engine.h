@@ -15,6 +15,7 @@
 #include "gguf.h"
 #include "kernels.h"
 #include "layout.cuh"
+#include "pfd.h"
 
 namespace aios {
 
@@ -110,6 +111,10 @@ struct Seq {
     cudaGraphExec_t graph = nullptr;
     aios_sampling graph_sampling{};
     int kernels_per_step = 0;
+    // persistent fused decode (pfd.cu): phase table + global exchange buffers; pfd_grid == 0 -> not usable
+    DevBuf pfd_phases, pfd_att_max, pfd_att_sum, pfd_att_acc, pfd_counters, pfd_timing;
+    PfdParams pfd{};
+    int pfd_grid = 0;
 
     explicit Seq(Model *m);
     ~Seq();
@@ -127,6 +132,9 @@ struct Seq {
     void launch_token_pass(bool from_prompt, int prompt_idx, int pos_value, bool want_logits, cudaStream_t st, int *n_launch);
     void launch_sample_kernel(const aios_sampling &sp, cudaStream_t st);
     void ensure_graph(const aios_sampling &sp);
+    void build_pfd();
+    bool use_pfd(const aios_sampling &sp) const;
+    void launch_pfd_tokens(int n, cudaStream_t st);
 };
 
 }  // namespace aios

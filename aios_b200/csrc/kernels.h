@@ -36,7 +36,7 @@ struct GemvParams {
 // fills cta_begin[] and returns the grid size; n_sms from the device
 int gemv_plan_grid(GemvParams &p, int n_sms);
 size_t gemv_smem_bytes(int k);
-void launch_gemv(const GemvParams &p, int grid, cudaStream_t st);
+void launch_gemv(const GemvParams &p, int grid, cudaStream_t st, bool pdl = false);
 void gemv_init();  // one-time function attributes (dynamic smem)
 
 // ---- attention.cu : RoPE + KV write + flash-decode over the f16 KV cache (one new token)

@@ -12,7 +12,9 @@
 //  Q4_K  unit (b,p), p=0..3   = sub-blocks 2p (low nibbles) and 2p+1 (high nibbles) of block b
 //        plane QSa[N][U][16] = qs[32p    .. 32p+16)      U = K/64
 //        plane QSb[N][U][16] = qs[32p+16 .. 32p+32)
-//        plane META[N][nb][16] = {d, dmin, scales[12]}   nb = K/256 (original packing kept)
+//        plane META[N][nb][16] = 4 words, one per unit j of the block (nb = K/256):
+//                                sc(2j) | sc(2j+1)<<6 | m(2j)<<12 | m(2j+1)<<18 | byte j of (d | dmin<<16) << 24
+//                                (the twelve packed 6-bit scale bytes, re-ordered per unit; still 16 bytes)
 //        activations used: a_k = q8[64p+16k .. +16), k=0..3  (lo: a0,a1  hi: a2,a3)
 //
 //  Q6_K  unit (b,h,t), h,t in {0,1}; unit index = 4b + 2h + t

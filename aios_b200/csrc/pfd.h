@@ -1,0 +1,66 @@
+// pfd.h — descriptors of the persistent fused decode kernel (pfd.cu), built on the host per sequence.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "kernels.h"
+#include "layout.cuh"
+
+namespace aios {
+
+enum : int { PH_GEMV = 0, PH_ATTN = 1 };
+
+struct PfdPhase {
+    int32_t kind;            // PH_GEMV or PH_ATTN
+    // ---- GEMV phase
+    int32_t n_seg, epi, k;
+    WPlanes seg[3];
+    float *out[3];
+    const float *x;          // f32 input vector [k] ...
+    const double *x64;       // ... or the f64 attention accumulators [k] (attn_output projection)
+    const float *norm_w;     // RMSNorm weight or null
+    float eps;
+    int32_t embed;           // 1: the input is the embedding row of the current token (first phase of a token)
+    int32_t argmax;          // 1: lm_head — the epilogue updates the running arg-max key
+    int32_t zero_att;        // 1: zero the f64 attention accumulators at the start of this phase
+    int32_t perm_mask;       // activation images needed: 1 Q4_K/Q5_K order, 2 Q6_K order, 4 Q8_0
+    int32_t units_total;     // work units (row pairs) over all segments
+    int32_t unit_begin[4];   // prefix sums per segment
+    // ---- attention phase
+    uint16_t *k_cache, *v_cache;
+};
+
+struct PfdParams {
+    const PfdPhase *phases;
+    int32_t n_phases, n_tokens;
+    int32_t pos0;            // position of the last token already fed (SeqState.pos at launch)
+    int32_t step0;           // first index of out_tokens to write
+    int32_t *out_tokens;
+    int32_t *state;          // SeqState: {pos, step, cur_token}
+    unsigned long long *argmax_key;
+    float *x;                // residual stream [n_embd]
+    const float *qkv;        // raw projections of the current token
+    const uint8_t *tok_embd; // embedding table, GGUF natural layout
+    int64_t tok_embd_row_bytes;
+    int32_t tok_embd_type;
+    int32_t n_embd;
+    const float *rope_cos, *rope_sin;
+    int32_t n_head, n_kv, hd, n_rot;
+    float att_scale;
+    int32_t att_group;       // CTAs per kv-head
+    int32_t att_per_cap;     // max cached positions per CTA
+    float *att_max;          // [n_kv][att_group][8]
+    double *att_sum;         // [n_kv][att_group][8]
+    double *att_acc;         // [n_head*hd] f64 accumulators, zero between uses
+    unsigned *att_counters;  // [n_kv] monotonic group barriers (zeroed by the host before the launch)
+    unsigned *bar_counter;   // grid barrier (zeroed by the host before the launch)
+    int32_t k_max;           // largest GEMV input length (sizes the activation images)
+    unsigned long long *timing;  // optional [n_phases][4] ns stamps of CTA 0 for the last token: start, after prologue,
+                                 // after compute, after barrier (null = off)
+};
+
+size_t pfd_smem_bytes(const PfdParams &p);
+int pfd_max_grid(int n_sms, const PfdParams &p);   // 0 if the kernel cannot be made resident
+void launch_pfd(const PfdParams &p, int grid, cudaStream_t st);
+
+}  // namespace aios

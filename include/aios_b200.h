@@ -56,6 +56,9 @@ typedef struct aios_engine_opts {
     int32_t reserved;
 } aios_engine_opts;
 #define AIOS_ENGINE_NO_GRAPH 1 /* launch kernels one by one instead of via CUDA graphs (debug) */
+#define AIOS_ENGINE_NO_PDL 2   /* no programmatic dependent launch between the GEMV kernels (debug) */
+#define AIOS_ENGINE_NO_PFD 4   /* greedy decode through per-op kernels instead of the persistent fused kernel */
+#define AIOS_ENGINE_USE_PFD 8  /* greedy decode through the persistent fused decode kernel (pfd.cu) */
 
 int aios_engine_create(const aios_engine_opts *opts, aios_engine **out);
 void aios_engine_destroy(aios_engine *e);
@@ -164,6 +167,10 @@ int aios_seq_bench_decode(aios_seq *s, int32_t n_tokens, aios_bench_result *out)
  * ms_gemv (sum of the dequant+GEMV launches), reserved[0] = ms in attention launches,
  * reserved[1] = ms in the remaining launches, reserved[2] = number of GEMV launches. */
 int aios_seq_profile_decode(aios_seq *s, int32_t n_tokens, aios_bench_result *out);
+/* per-phase time stamps (ns) that CTA 0 of the persistent fused decode kernel took for the last token of the last
+ * fused launch: out[n_phases][4] = phase start, after the activation prologue, after the compute loop, after the grid
+ * barrier.  *n_phases returns the phase count; cap = capacity of out in phases. */
+int aios_seq_phase_timing(aios_seq *s, uint64_t *out, int32_t cap, int32_t *n_phases);
 /* time ONE GEMV launch shape in isolation (roofline leg): type/n_rows/k on random weights,
  * `iters` launches over `n_copies` distinct weight copies (so the working set exceeds L2) */
 int aios_bench_gemv(aios_engine *e, int32_t ggml_type, int64_t n_rows, int64_t k, int32_t n_copies,

@@ -46,3 +46,13 @@ def engine():
     e = capi.Engine(device=0, max_batch=4)
     yield e
     e.close()
+
+
+@pytest.fixture(scope="session")
+def engine_pfd():
+    """Engine whose greedy decode goes through the persistent fused decode kernel (pfd.cu)."""
+    from aios_b200 import capi
+
+    e = capi.Engine(device=0, max_batch=2, flags=capi.ENGINE_USE_PFD)
+    yield e
+    e.close()

@@ -221,3 +221,40 @@ def test_loader_matches_gguf_py(engine, tmp_models):
         assert m.info.kv_bytes_per_position == gs.kv_bytes_per_position("tiny")
     finally:
         m.unload()
+
+
+@pytest.mark.parametrize("arch,ftype", [("tiny", "Q4_K_M"), ("tiny-gqa4", "Q4_K_M"), ("tiny", "Q8_0")])
+def test_fused_decode_kernel_matches_oracle_and_per_op_path(engine, engine_pfd, oracle, tmp_models, arch, ftype):
+    """The persistent fused decode kernel (one cooperative launch for all tokens) must give the oracle's tokens,
+    the same logits bit for bit as the per-op kernels, and leave the sequence usable for further steps."""
+    path = tmp_models(arch, ftype)
+    om = oracle.OracleModel(path, n_ctx=256)
+    prompt = gs.synthetic_prompt(arch, 20, 11)
+    ref, margins = om.greedy(prompt, 96)
+    m1 = engine.load_model("a", path, n_ctx=256)
+    m2 = engine_pfd.load_model("b", path, n_ctx=256)
+    try:
+        s1, s2 = m1.new_seq(), m2.new_seq()
+        try:
+            s1.prefill(prompt)
+            s2.prefill(prompt)
+            a = s1.decode(64)
+            b = s2.decode(64)            # one fused launch, 64 tokens
+            r = s2.bench_decode(8)       # another fused launch continuing from there
+            assert r.kernel_launches == 1, "the fused kernel was not used"
+            s1.decode(8)
+            assert np.array_equal(a, ref[:64]) and np.array_equal(b, ref[:64]), margins.min()
+            assert np.array_equal(s1.logits().view(np.uint32), s2.logits().view(np.uint32))
+            c1 = np.array([s1.step() for _ in range(4)])
+            c2 = np.array([s2.step() for _ in range(4)])  # single-token fused launches
+            assert np.array_equal(c1, ref[72:76]) and np.array_equal(c2, ref[72:76])
+            for il in range(gs.ARCHS[arch].n_layer):
+                k1, v1 = s1.read_kv(il, 0, 96)
+                k2, v2 = s2.read_kv(il, 0, 96)
+                assert np.array_equal(k1, k2) and np.array_equal(v1, v2)
+        finally:
+            s1.free()
+            s2.free()
+    finally:
+        m1.unload()
+        m2.unload()
