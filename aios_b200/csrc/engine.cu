@@ -564,30 +564,30 @@ void Seq::build_pfd() {
     const HParams &hp = m->hp;
     const int QD = hp.n_head * hp.head_dim, KVD = hp.n_head_kv * hp.head_dim;
     std::vector<PfdPhase> ph;
-    auto gemv = [&](int n_seg, const WPlanes *segs, float *const *outs, int epi, int k, const float *xin, const double *x64,
-                    const float *norm_w) {
+    // one phase per matrix (or gate/up pair); matrices sharing an input form a group: the first builds the
+    // activation image(s) for all of them, only the last is followed by a grid barrier
+    auto gemv = [&](const WPlanes &w0, const WPlanes *w1, float *out, int epi, int k, const float *xin, const double *x64,
+                    const float *norm_w, bool prologue, bool barrier_after, int group_mask) {
         PfdPhase P{};
-        P.kind = PH_GEMV; P.n_seg = n_seg; P.epi = epi; P.k = k;
+        P.kind = PH_GEMV; P.type = w0.type; P.epi = epi; P.k = k;
+        P.w0 = w0; P.w1 = w1 ? *w1 : w0; P.out = out;
         P.x = xin; P.x64 = x64; P.norm_w = norm_w; P.eps = hp.rms_eps;
-        int units = 0;
-        for (int i = 0; i < n_seg; i++) {
-            P.seg[i] = segs[i]; P.out[i] = outs[i];
-            P.perm_mask |= perm_bit(segs[i].type);
-            if (epi != EPI_SWIGLU) { P.unit_begin[i] = units; units += (segs[i].n_rows + 1) / 2; }
-        }
-        if (epi == EPI_SWIGLU) { P.unit_begin[0] = 0; units = segs[0].n_rows; P.out[0] = outs[0]; }
-        for (int i = n_seg; i < 4; i++) P.unit_begin[i] = units;
-        P.units_total = units;
+        P.prologue = prologue; P.barrier_after = barrier_after; P.perm_mask = group_mask;
+        P.units_total = epi == EPI_SWIGLU ? w0.n_rows : (w0.n_rows + 1) / 2;
         ph.push_back(P);
         return ph.size() - 1;
     };
     float *xq = x.as<float>(), *qk = qkv.as<float>(), *hh = h.as<float>();
+    bool mixed80 = false;
     for (int il = 0; il < hp.n_layer; il++) {
         const Layer &L = m->layers[il];
         {
-            const WPlanes s[3] = {L.wq.w, L.wk.w, L.wv.w};
-            float *o[3] = {qk, qk + QD, qk + QD + KVD};
-            const size_t i = gemv(3, s, o, EPI_STORE, hp.n_embd, xq, nullptr, L.attn_norm.as<float>());
+            const int mask = perm_bit(L.wq.w.type) | perm_bit(L.wk.w.type) | perm_bit(L.wv.w.type);
+            if ((mask & 4) && (mask & 3)) mixed80 = true;
+            const float *nw = L.attn_norm.as<float>();
+            const size_t i = gemv(L.wq.w, nullptr, qk, EPI_STORE, hp.n_embd, xq, nullptr, nw, true, false, mask);
+            gemv(L.wk.w, nullptr, qk + QD, EPI_STORE, hp.n_embd, xq, nullptr, nw, false, false, mask);
+            gemv(L.wv.w, nullptr, qk + QD + KVD, EPI_STORE, hp.n_embd, xq, nullptr, nw, false, true, mask);
             if (il == 0) ph[i].embed = 1;
         }
         {
@@ -596,27 +596,17 @@ void Seq::build_pfd() {
             P.k_cache = m->k_cache(slot, il); P.v_cache = m->v_cache(slot, il);
             ph.push_back(P);
         }
+        gemv(L.wo.w, nullptr, xq, EPI_ADD, QD, nullptr, pfd_att_acc.as<double>(), nullptr, true, true, perm_bit(L.wo.w.type));
         {
-            const WPlanes s[1] = {L.wo.w};
-            float *o[1] = {xq};
-            gemv(1, s, o, EPI_ADD, QD, nullptr, pfd_att_acc.as<double>(), nullptr);
-        }
-        {
-            const WPlanes s[2] = {L.w_gate.w, L.w_up.w};
-            float *o[2] = {hh, hh};
-            const size_t i = gemv(2, s, o, EPI_SWIGLU, hp.n_embd, xq, nullptr, L.ffn_norm.as<float>());
+            const size_t i = gemv(L.w_gate.w, &L.w_up.w, hh, EPI_SWIGLU, hp.n_embd, xq, nullptr, L.ffn_norm.as<float>(), true,
+                                  true, perm_bit(L.w_gate.w.type));
             ph[i].zero_att = 1;
         }
-        {
-            const WPlanes s[1] = {L.w_down.w};
-            float *o[1] = {xq};
-            gemv(1, s, o, EPI_ADD, hp.n_ff, hh, nullptr, nullptr);
-        }
+        gemv(L.w_down.w, nullptr, xq, EPI_ADD, hp.n_ff, hh, nullptr, nullptr, true, true, perm_bit(L.w_down.w.type));
     }
     {
-        const WPlanes s[1] = {m->output.w};
-        float *o[1] = {logits.as<float>()};
-        const size_t i = gemv(1, s, o, EPI_STORE, hp.n_embd, xq, nullptr, m->output_norm.as<float>());
+        const size_t i = gemv(m->output.w, nullptr, logits.as<float>(), EPI_STORE, hp.n_embd, xq, nullptr,
+                              m->output_norm.as<float>(), true, true, perm_bit(m->output.w.type));
         ph[i].argmax = 1;
     }
     pfd_phases = DevBuf(ph.size() * sizeof(PfdPhase));
@@ -645,7 +635,7 @@ void Seq::build_pfd() {
     pfd_timing = DevBuf(ph.size() * 4 * sizeof(unsigned long long));
     CUDA_CHECK(cudaMemset(pfd_timing.p, 0, pfd_timing.bytes));
     p.timing = pfd_timing.as<unsigned long long>();
-    pfd_grid = (hp.n_head_kv <= n_sms) ? pfd_max_grid(n_sms, p) : 0;
+    pfd_grid = (hp.n_head_kv <= n_sms && !mixed80) ? pfd_max_grid(n_sms, p) : 0;
 }
 
 bool Seq::use_pfd(const aios_sampling &sp) const {

@@ -244,10 +244,10 @@ __device__ __forceinline__ int dp4a_us(uint32_t a, uint32_t b, int c) {
 }
 
 // FULL: the pass is known to be entirely in range (no per-lane predicates)
-template <int TYPE, bool FULL>
-__device__ __forceinline__ void load_pass(PassRegs<TYPE> &g, const RowPtrs (&rp)[GEMV_R], int u0, int nu) {
+template <int TYPE, bool FULL, typename Regs>
+__device__ __forceinline__ void load_pass(Regs &g, const RowPtrs (&rp)[GEMV_R], int u0, int nu) {
     const int lane = threadIdx.x & 31;
-    constexpr int ITS = PassCfg<TYPE>::ITS;
+    constexpr int ITS = Regs::ITS;
 #pragma unroll
     for (int it = 0; it < ITS; it++) {
         const int u = u0 + it * 32 + lane;
@@ -274,11 +274,11 @@ __device__ __forceinline__ void load_pass(PassRegs<TYPE> &g, const RowPtrs (&rp)
     }
 }
 
-template <int TYPE, bool FULL>
-__device__ __forceinline__ void compute_pass(const PassRegs<TYPE> &g, int u0, int nu, int k, const ActSmem &s,
+template <int TYPE, bool FULL, typename Regs>
+__device__ __forceinline__ void compute_pass(const Regs &g, int u0, int nu, int k, const ActSmem &s,
                                              double (&acc)[GEMV_R]) {
     const int lane = threadIdx.x & 31;
-    constexpr int ITS = PassCfg<TYPE>::ITS;
+    constexpr int ITS = Regs::ITS;
 #pragma unroll
     for (int it = 0; it < ITS; it++) {
         const int u = u0 + it * 32 + lane;

@@ -4,7 +4,7 @@
 // by one, every kernel pays a drain + launch + activation prologue + one exposed memory latency, and
 // HBM idles for more than half of the step (profiles/r01_v1_summary.md).  Here one CTA per SM stays
 // resident for the whole decode loop and walks a host-built table of phases
-//   [QKV gemv] [attention] [O gemv + residual] [gate/up gemv + SwiGLU] [down gemv + residual] x L, [lm_head]
+//   [q][k][v] [attention] [o + residual] [gate/up + SwiGLU] [down + residual] x L, [lm_head]
 // separated by grid barriers (a global counter; the launch is cooperative, so all CTAs are resident).
 // Weights never depend on activations, so every warp keeps the NEXT item's weights in flight in a
 // second register image while it computes the current one — across phase boundaries and grid barriers
@@ -35,11 +35,6 @@ __device__ __forceinline__ unsigned long long globaltimer_ns() {
 }
 
 // ---------------------------------------------------------------- barriers
-__device__ __forceinline__ unsigned ld_acquire_u32(const unsigned *p) {
-    unsigned v;
-    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-    return v;
-}
 __device__ __forceinline__ void red_release_add(unsigned *p, unsigned v) {
     asm volatile("red.release.gpu.global.add.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
 }
@@ -56,163 +51,142 @@ __device__ __forceinline__ void counter_barrier(unsigned *counter, unsigned targ
     __syncthreads();
 }
 
-// ---------------------------------------------------------------- item cursor
-struct Item {
-    int tok, ph;      // token index within the launch, phase index (always a GEMV phase)
-    int unit, chunk;  // work unit (row pair) inside the phase; K-chunk (pass) inside the unit
-    int ue, nchunks;  // end of this CTA's unit range in the phase; passes per unit
+// ---------------------------------------------------------------- the weight loader of one warp
+// Walks this warp's items (work unit x K-pass) in order across phases and tokens.  Inside a phase it only
+// adds strides; the phase table is read once per phase.
+struct AnyRegs {  // one register image for every weight type (fields a type does not use stay dead)
+    static constexpr int ITS = 2;
+    uint4 a[GEMV_R][2], b[GEMV_R][2], c[GEMV_R][2];
+    uint32_t e[GEMV_R][2], f[GEMV_R][2];
+};
+
+struct Loader {
+    int tok, ph;
+    bool valid;
+    int type, nu, nchunks, pair, n_rows;
+    int unit, chunk, ue;
+    RowPtrs rp[GEMV_R];  // plane pointers of the unit's two rows
+};
+
+struct Light {  // what the compute side needs to know about an item
+    int tok, ph, unit, chunk, nchunks;
     bool valid;
 };
 
+__device__ __forceinline__ Light light(const Loader &L) {
+    Light l;
+    l.tok = L.tok; l.ph = L.ph; l.unit = L.unit; l.chunk = L.chunk; l.nchunks = L.nchunks; l.valid = L.valid;
+    return l;
+}
+
 __device__ __forceinline__ int unit_elems(int type) { return type == T_Q8_0 ? 32 : 64; }
 
+// bytes of one row inside plane i
+__device__ __forceinline__ int plane_row_bytes(int type, int i, int nu) {
+    switch (type) {
+        case T_Q4_K: return i < 2 ? nu * 16 : (i == 2 ? nu * 4 : 0);
+        case T_Q5_K: return i < 2 ? nu * 16 : (i == 2 ? nu * 4 : (i == 3 ? nu * 8 : 0));
+        case T_Q6_K: return i < 3 ? nu * 16 : (i == 3 ? nu * 4 : nu / 2);
+        default: return i < 2 ? nu * 16 : (i == 2 ? nu * 2 : 0);
+    }
+}
+
 // this CTA's contiguous share of a phase's work units (32-bit: units_total * gridDim.x < 2^31)
-__device__ __forceinline__ void cta_range(const PfdPhase &P, int &ub, int &ue) {
-    const unsigned tot = (unsigned)P.units_total, g = gridDim.x, b = blockIdx.x;
+__device__ __forceinline__ void cta_range(int units_total, int &ub, int &ue) {
+    const unsigned tot = (unsigned)units_total, g = gridDim.x, b = blockIdx.x;
     ub = (int)(tot * b / g);
     ue = (int)(tot * (b + 1) / g);
 }
 
-// passes per work unit: a pass covers 2 lane-iterations x 32 lanes = 64 units of each row.  All segments of
-// a phase share k; the host refuses to mix Q8_0 (32-weight units) with K-quants inside one phase.
-__device__ __forceinline__ int n_chunks(const PfdPhase &P) {
-    const int nu = P.k / unit_elems(P.seg[0].type);
-    return (nu + 63) / 64;
+__device__ __forceinline__ void loader_set_rows(Loader &L, const PfdPhase &P) {
+    const int row0 = L.pair ? L.unit : 2 * L.unit;
+#pragma unroll
+    for (int i = 0; i < 5; i++) {
+        const int rb = plane_row_bytes(L.type, i, L.nu);
+        L.rp[0].p[i] = P.w0.p[i] ? P.w0.p[i] + (size_t)row0 * rb : nullptr;
+        if (L.pair) L.rp[1].p[i] = P.w1.p[i] ? P.w1.p[i] + (size_t)row0 * rb : nullptr;
+        else L.rp[1].p[i] = (row0 + 1 < L.n_rows) ? L.rp[0].p[i] + rb : L.rp[0].p[i];
+    }
 }
 
-// first item of this warp at or after phase ph of token tok
-__device__ __forceinline__ Item first_item_from(const PfdParams &p, int tok, int ph) {
+// position the loader on this warp's first item at or after (tok, ph)
+__device__ __forceinline__ void loader_seek(const PfdParams &p, Loader &L, int tok, int ph) {
     const int warp = threadIdx.x >> 5;
-    Item it;
-    it.valid = false; it.tok = tok; it.ph = ph; it.unit = 0; it.chunk = 0;
+    L.valid = false;
     while (tok < p.n_tokens) {
         for (; ph < p.n_phases; ph++) {
             const PfdPhase &P = p.phases[ph];
             if (P.kind != PH_GEMV) continue;
             int ub, ue;
-            cta_range(P, ub, ue);
+            cta_range(P.units_total, ub, ue);
             if (ub + warp < ue) {
-                it.valid = true; it.tok = tok; it.ph = ph; it.unit = ub + warp; it.chunk = 0;
-                it.ue = ue; it.nchunks = n_chunks(P);
-                return it;
+                L.valid = true; L.tok = tok; L.ph = ph;
+                L.type = P.type; L.nu = P.k / unit_elems(P.type); L.nchunks = (L.nu + 63) / 64;
+                L.pair = P.epi == EPI_SWIGLU; L.n_rows = P.w0.n_rows;
+                L.unit = ub + warp; L.chunk = 0; L.ue = ue;
+                loader_set_rows(L, P);
+                return;
             }
         }
         tok++; ph = 0;
     }
-    it.tok = tok;
-    return it;
+    L.tok = tok; L.ph = 0;
 }
 
-__device__ __forceinline__ Item next_item(const PfdParams &p, const Item &c) {
-    Item n = c;
-    if (c.chunk + 1 < c.nchunks) { n.chunk = c.chunk + 1; return n; }
-    if (c.unit + PFD_WARPS < c.ue) { n.unit = c.unit + PFD_WARPS; n.chunk = 0; return n; }
-    return first_item_from(p, c.tok, c.ph + 1);
-}
-
-// rows of a work unit -> plane pointers
-template <int TYPE>
-__device__ __forceinline__ void rows_typed(const PfdPhase &P, int unit, int seg, int row0, RowPtrs (&rp)[GEMV_R]) {
-    if (P.epi == EPI_SWIGLU) {
-        rp[0] = row_ptrs<TYPE>(P.seg[0], row0);
-        rp[1] = row_ptrs<TYPE>(P.seg[1], row0);
-    } else {
-        const WPlanes &W = P.seg[seg];
-        rp[0] = row_ptrs<TYPE>(W, row0);
-        rp[1] = row_ptrs<TYPE>(W, min(row0 + 1, W.n_rows - 1));
-    }
-}
-
-__device__ __forceinline__ void unit_to_rows(const PfdPhase &P, int unit, int &seg, int &row0) {
-    if (P.epi == EPI_SWIGLU) { seg = 0; row0 = unit; return; }
-    seg = 0;
-    while (seg + 1 < P.n_seg && unit >= P.unit_begin[seg + 1]) seg++;
-    row0 = (unit - P.unit_begin[seg]) * 2;
-}
-
-// one register image for every weight type (fields a type does not use stay dead)
-struct AnyRegs {
-    uint4 a[GEMV_R][2], b[GEMV_R][2], c[GEMV_R][2];
-    uint32_t e[GEMV_R][2], f[GEMV_R][2];
-};
-
-template <int TYPE>
-__device__ __forceinline__ void pfd_load(AnyRegs &g, const RowPtrs (&rp)[GEMV_R], int u0, int nu) {
-    const int lane = threadIdx.x & 31;
+__device__ __forceinline__ void loader_advance(const PfdParams &p, Loader &L) {
+    if (L.chunk + 1 < L.nchunks) { L.chunk++; return; }
+    if (L.unit + PFD_WARPS < L.ue) {
+        L.unit += PFD_WARPS; L.chunk = 0;
+        const int rows = L.pair ? PFD_WARPS : 2 * PFD_WARPS;
+        const bool last_odd = !L.pair && (2 * L.unit + 1 >= L.n_rows);
 #pragma unroll
-    for (int it = 0; it < 2; it++) {
-        const int u = u0 + it * 32 + lane;
-        if (u < nu) {
-#pragma unroll
-            for (int r = 0; r < GEMV_R; r++) {
-                g.a[r][it] = ldg_stream(rp[r].p[0] + (size_t)u * 16);
-                g.b[r][it] = ldg_stream(rp[r].p[1] + (size_t)u * 16);
-                if (TYPE == T_Q4_K || TYPE == T_Q5_K) {
-                    g.c[r][it] = ldg_stream(rp[r].p[2] + (size_t)(u >> 2) * 16);
-                    if (TYPE == T_Q5_K) {
-                        const uint2 h = *reinterpret_cast<const uint2 *>(rp[r].p[3] + (size_t)u * 8);
-                        g.e[r][it] = h.x; g.f[r][it] = h.y;
-                    }
-                } else if (TYPE == T_Q6_K) {
-                    g.c[r][it] = ldg_stream(rp[r].p[2] + (size_t)u * 16);
-                    g.e[r][it] = ldg_stream_u32(rp[r].p[3] + (size_t)u * 4);
-                    g.f[r][it] = ldg_stream_u16(rp[r].p[4] + (size_t)(u >> 2) * 2);
-                } else {
-                    g.e[r][it] = ldg_stream_u16(rp[r].p[2] + (size_t)u * 2);
-                }
+        for (int i = 0; i < 5; i++) {
+            const size_t step = (size_t)rows * plane_row_bytes(L.type, i, L.nu);
+            if (L.rp[0].p[i]) {
+                L.rp[0].p[i] += step;
+                L.rp[1].p[i] = last_odd ? L.rp[0].p[i] : L.rp[1].p[i] + step;
             }
         }
+        return;
+    }
+    loader_seek(p, L, L.tok, L.ph + 1);
+}
+
+__device__ __forceinline__ void issue_load(const Loader &L, AnyRegs &g) {
+    const int u0 = L.chunk * 64;
+    switch (L.type) {
+        case T_Q4_K: load_pass<T_Q4_K, false>(g, L.rp, u0, L.nu); break;
+        case T_Q5_K: load_pass<T_Q5_K, false>(g, L.rp, u0, L.nu); break;
+        case T_Q6_K: load_pass<T_Q6_K, false>(g, L.rp, u0, L.nu); break;
+        default: load_pass<T_Q8_0, false>(g, L.rp, u0, L.nu); break;
     }
 }
 
-__device__ __forceinline__ void load_item(const PfdParams &p, const Item &it, AnyRegs &g) {
-    const PfdPhase &P = p.phases[it.ph];
-    int seg, row0;
-    unit_to_rows(P, it.unit, seg, row0);
-    const int type = P.seg[seg].type;
-    const int nu = P.k / unit_elems(type);
-    const int u0 = it.chunk * 64;
-    RowPtrs rp[GEMV_R];
-    switch (type) {
-        case T_Q4_K: rows_typed<T_Q4_K>(P, it.unit, seg, row0, rp); pfd_load<T_Q4_K>(g, rp, u0, nu); break;
-        case T_Q5_K: rows_typed<T_Q5_K>(P, it.unit, seg, row0, rp); pfd_load<T_Q5_K>(g, rp, u0, nu); break;
-        case T_Q6_K: rows_typed<T_Q6_K>(P, it.unit, seg, row0, rp); pfd_load<T_Q6_K>(g, rp, u0, nu); break;
-        default: rows_typed<T_Q8_0>(P, it.unit, seg, row0, rp); pfd_load<T_Q8_0>(g, rp, u0, nu); break;
+// Ask L2 to fetch this CTA's slice of the NEXT GEMV phase's weights (cp.async.bulk.prefetch.L2): HBM keeps
+// streaming one phase ahead of the compute, through barriers and prologues, and the demand loads hit L2.
+__device__ __forceinline__ void l2_prefetch_range(const uint8_t *base, size_t bytes) {
+    const uintptr_t a0 = reinterpret_cast<uintptr_t>(base) & ~(uintptr_t)15;
+    const uintptr_t a1 = (reinterpret_cast<uintptr_t>(base) + bytes + 15) & ~(uintptr_t)15;
+    constexpr size_t PIECE = 8192;
+    for (uintptr_t a = a0 + (size_t)threadIdx.x * PIECE; a < a1; a += (size_t)PFD_THREADS * PIECE) {
+        const unsigned sz = (unsigned)(a1 - a < PIECE ? a1 - a : PIECE);
+        asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(a), "r"(sz) : "memory");
     }
 }
 
-template <int TYPE>
-__device__ __forceinline__ void pfd_compute(const AnyRegs &g, int u0, int nu, int k, const ActSmem &s, double (&acc)[GEMV_R]) {
-    if (TYPE == T_Q8_0) {
-        const int lane = threadIdx.x & 31;
-        const int U8 = k / 32;
+__device__ __forceinline__ void l2_prefetch_phase(const PfdPhase &P) {
+    int ub, ue;
+    cta_range(P.units_total, ub, ue);
+    if (ub >= ue) return;
+    const int pair = P.epi == EPI_SWIGLU;
+    const int nu = P.k / unit_elems(P.type);
+    const int r0 = pair ? ub : 2 * ub, r1 = pair ? ue : min(2 * ue, P.w0.n_rows);
 #pragma unroll
-        for (int it = 0; it < 2; it++) {
-            const int u = u0 + it * 32 + lane;
-            if (u < nu) {
-                const uint4 a0 = s.act[u], a1 = s.act[U8 + u];
-                const float d8 = s.d8[u];
-#pragma unroll
-                for (int r = 0; r < GEMV_R; r++) {
-                    int d = 0;
-                    d = __dp4a((int)g.a[r][it].x, (int)a0.x, d); d = __dp4a((int)g.a[r][it].y, (int)a0.y, d);
-                    d = __dp4a((int)g.a[r][it].z, (int)a0.z, d); d = __dp4a((int)g.a[r][it].w, (int)a0.w, d);
-                    d = __dp4a((int)g.b[r][it].x, (int)a1.x, d); d = __dp4a((int)g.b[r][it].y, (int)a1.y, d);
-                    d = __dp4a((int)g.b[r][it].z, (int)a1.z, d); d = __dp4a((int)g.b[r][it].w, (int)a1.w, d);
-                    acc[r] += (double)__fmul_rn((float)d, __fmul_rn(h2f_bits((uint16_t)g.e[r][it]), d8));
-                }
-            }
-        }
-    } else {
-        PassRegs<TYPE> t;  // same field names; ITS == 2 for the K-quants
-#pragma unroll
-        for (int r = 0; r < GEMV_R; r++)
-#pragma unroll
-            for (int it = 0; it < 2; it++) {
-                t.a[r][it] = g.a[r][it]; t.b[r][it] = g.b[r][it]; t.c[r][it] = g.c[r][it];
-                t.e[r][it] = g.e[r][it]; t.f[r][it] = g.f[r][it];
-            }
-        compute_pass<TYPE, false>(t, u0, nu, k, s, acc);
+    for (int i = 0; i < 5; i++) {
+        const int rb = plane_row_bytes(P.type, i, nu);
+        if (rb == 0 || !P.w0.p[i]) continue;
+        l2_prefetch_range(P.w0.p[i] + (size_t)r0 * rb, (size_t)(r1 - r0) * rb);
+        if (pair) l2_prefetch_range(P.w1.p[i] + (size_t)r0 * rb, (size_t)(r1 - r0) * rb);
     }
 }
 
@@ -224,35 +198,17 @@ struct PfdSmem {
     double *red;       // [PFD_WARPS]
 };
 
-__device__ __forceinline__ void compute_item(const PfdPhase &P, const Item &it, const AnyRegs &g, const PfdSmem &sm,
-                                             double (&acc)[GEMV_R]) {
-    int seg, row0;
-    unit_to_rows(P, it.unit, seg, row0);
-    const int type = P.seg[seg].type;
-    const int nu = P.k / unit_elems(type);
-    const int u0 = it.chunk * 64;
-    switch (type) {
-        case T_Q4_K: pfd_compute<T_Q4_K>(g, u0, nu, P.k, carve(sm.act_a, P.k), acc); break;
-        case T_Q5_K: pfd_compute<T_Q5_K>(g, u0, nu, P.k, carve(sm.act_a, P.k), acc); break;
-        case T_Q6_K: pfd_compute<T_Q6_K>(g, u0, nu, P.k, carve(sm.act_b, P.k), acc); break;
-        default: pfd_compute<T_Q8_0>(g, u0, nu, P.k, carve(sm.act_a, P.k), acc); break;
-    }
-}
-
-// reduction + fused epilogue of a finished work unit (same code path as gemv_kernel's)
-__device__ __forceinline__ void finish_unit(const PfdParams &p, const PfdPhase &P, const Item &it, double (&acc)[GEMV_R],
-                                            unsigned long long &best) {
+// reduction + fused epilogue of a finished work unit (same arithmetic as gemv_kernel's)
+__device__ __forceinline__ void finish_unit(const PfdPhase &P, int unit, double (&acc)[GEMV_R], unsigned long long &best) {
     const int lane = threadIdx.x & 31;
-    int seg, row0;
-    unit_to_rows(P, it.unit, seg, row0);
     const double tot = warp_sum2_f64(acc[0], acc[1]);  // lanes 0-15: row 0, lanes 16-31: row 1
-    float *out = P.out[seg];
+    float *out = P.out;
     if (P.epi == EPI_SWIGLU) {
         const float gte = (float)__shfl_sync(0xffffffffu, tot, 0), up = (float)__shfl_sync(0xffffffffu, tot, 16);
-        if (lane == 0) out[row0] = __fmul_rn(__fdiv_rn(gte, __fadd_rn(1.0f, expf_det(-gte))), up);
+        if (lane == 0) out[unit] = __fmul_rn(__fdiv_rn(gte, __fadd_rn(1.0f, expf_det(-gte))), up);
     } else if ((lane & 15) == 0) {
-        const int row = row0 + (lane >> 4);
-        if (row < P.seg[seg].n_rows) {
+        const int row = 2 * unit + (lane >> 4);
+        if (row < P.w0.n_rows) {
             const float v = (float)tot;
             if (P.epi == EPI_ADD) out[row] = __fadd_rn(__ldcg(out + row), v);
             else out[row] = v;
@@ -266,15 +222,41 @@ __device__ __forceinline__ void finish_unit(const PfdParams &p, const PfdPhase &
     acc[1] = 0.0;
 }
 
+__device__ __forceinline__ void compute_any(int type, const AnyRegs &g, int u0, int nu, int k, const PfdSmem &sm,
+                                            double (&acc)[GEMV_R]) {
+    switch (type) {
+        case T_Q4_K: compute_pass<T_Q4_K, false>(g, u0, nu, k, carve(sm.act_a, k), acc); break;
+        case T_Q5_K: compute_pass<T_Q5_K, false>(g, u0, nu, k, carve(sm.act_a, k), acc); break;
+        case T_Q6_K: compute_pass<T_Q6_K, false>(g, u0, nu, k, carve(sm.act_b, k), acc); break;
+        default: compute_pass<T_Q8_0, false>(g, u0, nu, k, carve(sm.act_a, k), acc); break;
+    }
+}
+
+// All of this warp's items of one GEMV phase.  `C` holds the weights of the current item; the next item's
+// (possibly of a later phase or token) are fetched into `N` while C is being consumed, then N becomes C.
+__device__ __forceinline__ void gemv_phase(const PfdParams &p, const PfdPhase &P, int tok, int ph, Loader &L, Light &cur,
+                                           AnyRegs &C, AnyRegs &N, const PfdSmem &sm, unsigned long long &best) {
+    const int type = P.type;
+    const int nu = P.k / unit_elems(type);
+    double acc[GEMV_R] = {0.0, 0.0};
+    while (cur.valid && cur.tok == tok && cur.ph == ph) {
+        loader_advance(p, L);
+        const Light nxt = light(L);
+        if (nxt.valid) issue_load(L, N);
+        compute_any(type, C, cur.chunk * 64, nu, P.k, sm, acc);
+        if (cur.chunk + 1 == cur.nchunks) finish_unit(P, cur.unit, acc, best);
+        cur = nxt;
+        C = N;
+    }
+}
+
+__device__ __noinline__ float dequant_elem_nl(int type, const uint8_t *row, int64_t i) { return dequant_elem(type, row, i); }
+
 // ---------------------------------------------------------------- activation prologue of a GEMV phase
 __device__ __forceinline__ void src_load8(const PfdParams &p, const PfdPhase &P, int token, int idx, float (&v)[8]) {
     if (P.x64) {
 #pragma unroll
         for (int i = 0; i < 8; i++) v[i] = (float)__ldcg(P.x64 + idx + i);
-    } else if (P.embed) {
-        const uint8_t *row = p.tok_embd + (int64_t)token * p.tok_embd_row_bytes;
-#pragma unroll
-        for (int i = 0; i < 8; i++) v[i] = dequant_elem(p.tok_embd_type, row, idx + i);
     } else {
         const float4 a = __ldcg(reinterpret_cast<const float4 *>(P.x + idx));
         const float4 b = __ldcg(reinterpret_cast<const float4 *>(P.x + idx) + 1);
@@ -282,37 +264,101 @@ __device__ __forceinline__ void src_load8(const PfdParams &p, const PfdPhase &P,
     }
 }
 
+// Q8_K-quantise the lane's 8 values of slab b once and store them in the lane order(s) the phase group needs
+__device__ __forceinline__ void quant_slab_k(const float (&v)[8], int b, int k, int mask, const ActSmem &sa, const ActSmem &sb) {
+    const int lane = threadIdx.x & 31;
+    float am = 0.f;
+    int ai = 0;
+#pragma unroll
+    for (int i = 0; i < 8; i++) {
+        const float ax = fabsf(v[i]);
+        if (ax > am) { am = ax; ai = i; }
+    }
+    int idx = lane * 8 + ai;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        const float am2 = __shfl_xor_sync(0xffffffffu, am, o);
+        const int idx2 = __shfl_xor_sync(0xffffffffu, idx, o);
+        if (am2 > am || (am2 == am && idx2 < idx)) { am = am2; idx = idx2; }
+    }
+    float cand = 0.f;
+#pragma unroll
+    for (int i = 0; i < 8; i++) if (i == (idx & 7)) cand = v[i];
+    const float mv = __shfl_sync(0xffffffffu, cand, idx >> 3);
+    int q[8];
+    float d = 0.f;
+    if (am == 0.f) {
+#pragma unroll
+        for (int i = 0; i < 8; i++) q[i] = 0;
+    } else {
+        const float iscale = __fdiv_rn(-127.f, mv);
+#pragma unroll
+        for (int i = 0; i < 8; i++) q[i] = min(127, __float2int_rn(__fmul_rn(iscale, v[i])));
+        d = __fdiv_rn(1.0f, iscale);
+    }
+    int s8 = 0;
+#pragma unroll
+    for (int i = 0; i < 8; i++) s8 += q[i];
+    const int s16 = s8 + __shfl_xor_sync(0xffffffffu, s8, 1);
+    const int s32 = s16 + __shfl_xor_sync(0xffffffffu, s16, 2);
+    const int U = k / 64;
+    uint2 pk;
+    pk.x = (q[0] & 0xff) | ((q[1] & 0xff) << 8) | ((q[2] & 0xff) << 16) | ((q[3] & 0xff) << 24);
+    pk.y = (q[4] & 0xff) | ((q[5] & 0xff) << 8) | ((q[6] & 0xff) << 16) | ((q[7] & 0xff) << 24);
+    if (mask & 1) {
+        const int unit = b * 4 + (lane >> 3), kk = (lane & 7) >> 1;
+        *reinterpret_cast<uint2 *>(reinterpret_cast<uint8_t *>(sa.act + kk * U + unit) + (lane & 1) * 8) = pk;
+        if ((lane & 3) == 0) sa.bs32[b * 8 + (lane >> 2)] = s32;
+        if (lane == 0) sa.d8[b] = d;
+    }
+    if (mask & 2) {
+        const int h = lane >> 4, kk = (lane & 15) >> 2, t = (lane >> 1) & 1;
+        const int unit = b * 4 + h * 2 + t;
+        *reinterpret_cast<uint2 *>(reinterpret_cast<uint8_t *>(sb.act + kk * U + unit) + (lane & 1) * 8) = pk;
+        if ((lane & 1) == 0) sb.bs16[unit * 4 + kk] = (int16_t)s16;
+        if (lane == 0) sb.d8[b] = d;
+    }
+}
+
 __device__ void pfd_prologue(const PfdParams &p, const PfdPhase &P, const PfdSmem &sm, int token) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int k = P.k, nslab = k / 256;
     const ActSmem sa = carve(sm.act_a, k), sb = carve(sm.act_b, k);
-    auto emit = [&](float (&v)[8], int b, float scale) {
-        if (P.embed && blockIdx.x == 0) {  // one CTA publishes the residual stream's starting value
-            float4 *dst = reinterpret_cast<float4 *>(p.x + b * 256 + lane * 8);
-            dst[0] = make_float4(v[0], v[1], v[2], v[3]);
-            dst[1] = make_float4(v[4], v[5], v[6], v[7]);
-        }
-        if (P.norm_w) norm8(v, P.norm_w + b * 256 + lane * 8, scale);
-        if (P.perm_mask & 1) quant_slab<PERM_Q4>(v, b, k, sa);
-        if (P.perm_mask & 2) quant_slab<PERM_Q6>(v, b, k, sb);
-        if (P.perm_mask & 4) quant_slab<PERM_Q80>(v, b, k, sa);
-    };
-    if (nslab <= 2 * PFD_WARPS) {
-        // k <= 512*warps: each lane keeps its (up to) 16 values in registers — one trip to L2 per phase
-        const int b0 = warp, b1 = warp + PFD_WARPS;
-        float v0[8], v1[8];
+    const int mask = P.perm_mask;
+    auto emit = [&](float (&v)[8], const float (&w)[8], int b, float scale) {
+        if (P.norm_w) {
 #pragma unroll
-        for (int i = 0; i < 8; i++) v0[i] = v1[i] = 0.f;
-        if (b0 < nslab) src_load8(p, P, token, b0 * 256 + lane * 8, v0);
-        if (b1 < nslab) src_load8(p, P, token, b1 * 256 + lane * 8, v1);
+            for (int i = 0; i < 8; i++) v[i] = __fmul_rn(__fmul_rn(v[i], scale), w[i]);
+        }
+        if (mask & 4) quant_slab<PERM_Q80>(v, b, k, sa);
+        else quant_slab_k(v, b, k, mask, sa, sb);
+    };
+    constexpr int NB = 4;  // slabs fetched per trip to L2 on the long-vector path
+    if (nslab <= 2 * PFD_WARPS) {
+        // k <= 4096: every lane keeps its (up to) 16 values in registers: one trip to L2 for x and, concurrently,
+        // one for the norm weight
+        float v[2][8], w[2][8];
+#pragma unroll
+        for (int j = 0; j < 2; j++) {
+            const int b = warp + j * PFD_WARPS;
+#pragma unroll
+            for (int i = 0; i < 8; i++) { v[j][i] = 0.f; w[j][i] = 0.f; }
+            if (b < nslab) {
+                src_load8(p, P, token, b * 256 + lane * 8, v[j]);
+                if (P.norm_w) load8(P.norm_w + b * 256 + lane * 8, w[j]);
+            }
+        }
         float scale = 1.f;
         if (P.norm_w) {
-            const double ss = block_sum(sumsq8(v0) + sumsq8(v1), sm.red);
+            const double ss = block_sum(sumsq8(v[0]) + sumsq8(v[1]), sm.red);
             const float mean = (float)(ss / (double)k);
             scale = __fdiv_rn(1.0f, __fsqrt_rn(__fadd_rn(mean, P.eps)));
         }
-        if (b0 < nslab) emit(v0, b0, scale);
-        if (b1 < nslab) emit(v1, b1, scale);
+#pragma unroll
+        for (int j = 0; j < 2; j++) {
+            const int b = warp + j * PFD_WARPS;
+            if (b < nslab) emit(v[j], w[j], b, scale);
+        }
     } else {
         float scale = 1.f;
         if (P.norm_w) {
@@ -326,16 +372,24 @@ __device__ void pfd_prologue(const PfdParams &p, const PfdPhase &P, const PfdSme
             const float mean = (float)(ss / (double)k);
             scale = __fdiv_rn(1.0f, __fsqrt_rn(__fadd_rn(mean, P.eps)));
         }
-        // three slabs per trip to L2
-        for (int b = warp; b < nslab; b += 3 * PFD_WARPS) {
-            const int b1 = b + PFD_WARPS, b2 = b + 2 * PFD_WARPS;
-            float v0[8], v1[8], v2[8];
-            src_load8(p, P, token, b * 256 + lane * 8, v0);
-            if (b1 < nslab) src_load8(p, P, token, b1 * 256 + lane * 8, v1);
-            if (b2 < nslab) src_load8(p, P, token, b2 * 256 + lane * 8, v2);
-            emit(v0, b, scale);
-            if (b1 < nslab) emit(v1, b1, scale);
-            if (b2 < nslab) emit(v2, b2, scale);
+        for (int b0 = warp; b0 < nslab; b0 += NB * PFD_WARPS) {
+            float v[NB][8];
+#pragma unroll
+            for (int j = 0; j < NB; j++) {
+                const int b = b0 + j * PFD_WARPS;
+                if (b < nslab) src_load8(p, P, token, b * 256 + lane * 8, v[j]);
+            }
+#pragma unroll
+            for (int j = 0; j < NB; j++) {
+                const int b = b0 + j * PFD_WARPS;
+                if (b < nslab) {
+                    float w[8];
+#pragma unroll
+                    for (int i = 0; i < 8; i++) w[i] = 0.f;
+                    if (P.norm_w) load8(P.norm_w + b * 256 + lane * 8, w);
+                    emit(v[j], w, b, scale);
+                }
+            }
         }
     }
     __syncthreads();
@@ -565,10 +619,11 @@ __global__ void __launch_bounds__(PFD_THREADS, 1) pfd_kernel(const PfdParams p) 
     int att_count = 0;
     int pos = p.pos0;
 
-    Item cur = first_item_from(p, 0, 0);
-    AnyRegs A, B;
-    bool in_b = false;
-    if (cur.valid) load_item(p, cur, A);  // weights of my first item: in flight before anything else happens
+    Loader L;
+    loader_seek(p, L, 0, 0);
+    Light cur = light(L);
+    AnyRegs C, N;
+    if (cur.valid) issue_load(L, C);  // weights of my first item: in flight before anything else happens
 
     for (int tok = 0; tok < p.n_tokens; tok++) {
         // the token to feed = arg-max of the logits kept from the previous pass
@@ -576,6 +631,17 @@ __global__ void __launch_bounds__(PFD_THREADS, 1) pfd_kernel(const PfdParams p) 
         const int token = key_to_index(key);
         pos += 1;
         if (blockIdx.x == 0 && threadIdx.x == 0) p.out_tokens[p.step0 + tok] = token;
+        bool key_cleared = false;
+        {
+            // residual stream <- embedding row of the token (bit-exact dequantisation), spread over the grid
+            const uint8_t *row = p.tok_embd + (int64_t)token * p.tok_embd_row_bytes;
+            for (int i = blockIdx.x * PFD_THREADS + threadIdx.x; i < p.n_embd; i += gridDim.x * PFD_THREADS)
+                p.x[i] = dequant_elem_nl(p.tok_embd_type, row, i);
+            bar++;
+            counter_barrier(p.bar_counter, bar * gridDim.x);
+            if (blockIdx.x == 0 && threadIdx.x == 0) *p.argmax_key = 0ull;  // every CTA has read the key by now
+            key_cleared = true;
+        }
 
         for (int ph = 0; ph < p.n_phases; ph++) {
             const PfdPhase &P = p.phases[ph];
@@ -587,23 +653,19 @@ __global__ void __launch_bounds__(PFD_THREADS, 1) pfd_kernel(const PfdParams p) 
                     const int n = p.n_head * p.hd;
                     for (int i = blockIdx.x * PFD_THREADS + threadIdx.x; i < n; i += gridDim.x * PFD_THREADS) p.att_acc[i] = 0.0;
                 }
-                pfd_prologue(p, P, sm, token);
-                if (tm) tm[1] = globaltimer_ns();
-                double acc[GEMV_R] = {0.0, 0.0};
-                unsigned long long best = 0ull;
-                while (cur.valid && cur.tok == tok && cur.ph == ph) {
-                    const Item nxt = next_item(p, cur);
-                    if (!in_b) {
-                        if (nxt.valid) load_item(p, nxt, B);
-                        compute_item(P, cur, A, sm, acc);
-                    } else {
-                        if (nxt.valid) load_item(p, nxt, A);
-                        compute_item(P, cur, B, sm, acc);
+                {
+                    // weights of the next GEMV phase (of this or the next token) start moving HBM -> L2 now
+                    int nph = ph + 1;
+                    for (int s = 0; s < p.n_phases; s++, nph++) {
+                        if (nph >= p.n_phases) nph = 0;
+                        if (p.phases[nph].kind == PH_GEMV) break;
                     }
-                    if (cur.chunk + 1 == cur.nchunks) finish_unit(p, P, cur, acc, best);
-                    cur = nxt;
-                    in_b = !in_b;
+                    if (nph > ph || tok + 1 < p.n_tokens) l2_prefetch_phase(p.phases[nph]);
                 }
+                if (P.prologue) pfd_prologue(p, P, sm, token);
+                if (tm) tm[1] = globaltimer_ns();
+                unsigned long long best = 0ull;
+                gemv_phase(p, P, tok, ph, L, cur, C, N, sm, best);
                 if (P.argmax) {
                     const unsigned long long other = __shfl_sync(0xffffffffu, best, 16);
                     best = other > best ? other : best;
@@ -613,13 +675,18 @@ __global__ void __launch_bounds__(PFD_THREADS, 1) pfd_kernel(const PfdParams p) 
                 const int epoch = att_count++;  // ordinal of this attention phase within the launch
                 if (p.hd == 128) pfd_attention<4>(p, P, sm, pos, epoch);
                 else pfd_attention<2>(p, P, sm, pos, epoch);
+                if (tm) tm[1] = tm[0];
             }
             if (tm) tm[2] = globaltimer_ns();
-            bar++;
-            counter_barrier(p.bar_counter, bar * gridDim.x);
+            if (P.kind == PH_ATTN || P.barrier_after) {
+                bar++;
+                counter_barrier(p.bar_counter, bar * gridDim.x);
+                // every CTA has read this token's key before arriving at the token's first barrier:
+                // clear it for the next lm_head
+                if (!key_cleared && blockIdx.x == 0 && threadIdx.x == 0) *p.argmax_key = 0ull;
+                key_cleared = true;
+            }
             if (tm) tm[3] = globaltimer_ns();
-            // every CTA has read this token's key before arriving at the first barrier: clear it for the next lm_head
-            if (ph == 0 && blockIdx.x == 0 && threadIdx.x == 0) *p.argmax_key = 0ull;
         }
     }
     if (blockIdx.x == 0 && threadIdx.x == 0) {

@@ -10,22 +10,28 @@ namespace aios {
 
 enum : int { PH_GEMV = 0, PH_ATTN = 1 };
 
+// One phase = one weight matrix (or the gate/up pair) streamed against one input vector, or one attention.
+// Matrices that share an input (q,k,v) are consecutive phases: the first carries `prologue`, the last
+// `barrier_after`.
 struct PfdPhase {
     int32_t kind;            // PH_GEMV or PH_ATTN
     // ---- GEMV phase
-    int32_t n_seg, epi, k;
-    WPlanes seg[3];
-    float *out[3];
+    int32_t type;            // ggml type of w0 (and w1)
+    int32_t epi;             // GemvEpilogue; EPI_SWIGLU: unit u = (row u of w0, row u of w1)
+    int32_t k;               // input length
+    WPlanes w0, w1;
+    float *out;
     const float *x;          // f32 input vector [k] ...
     const double *x64;       // ... or the f64 attention accumulators [k] (attn_output projection)
     const float *norm_w;     // RMSNorm weight or null
     float eps;
+    int32_t prologue;        // 1: build the activation image(s) at the start of this phase
+    int32_t barrier_after;   // 1: grid barrier at the end of this phase
     int32_t embed;           // 1: the input is the embedding row of the current token (first phase of a token)
     int32_t argmax;          // 1: lm_head — the epilogue updates the running arg-max key
     int32_t zero_att;        // 1: zero the f64 attention accumulators at the start of this phase
-    int32_t perm_mask;       // activation images needed: 1 Q4_K/Q5_K order, 2 Q6_K order, 4 Q8_0
-    int32_t units_total;     // work units (row pairs) over all segments
-    int32_t unit_begin[4];   // prefix sums per segment
+    int32_t perm_mask;       // images the prologue builds: 1 Q4_K/Q5_K order, 2 Q6_K order, 4 Q8_0
+    int32_t units_total;     // work units: row pairs (rows 2u, 2u+1), or rows for EPI_SWIGLU
     // ---- attention phase
     uint16_t *k_cache, *v_cache;
 };

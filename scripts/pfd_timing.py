@@ -14,10 +14,10 @@ for _ in range(2):
     seq.restore(); r = seq.bench_decode(32)
 print("ms/token", r.ms_total / r.n_tokens)
 t = seq.phase_timing().astype(np.int64)
-names = ["qkv", "attn", "o", "gateup", "down"]
+names = ["q", "k", "v", "attn", "o", "gateup", "down"]
 tot = {}
 for ph in range(len(t)):
-    nm = names[ph % 5] if ph < len(t) - 1 else "lm_head"
+    nm = names[ph % 7] if ph < len(t) - 1 else "lm_head"
     pro, comp, bar = t[ph, 1] - t[ph, 0], t[ph, 2] - t[ph, 1], t[ph, 3] - t[ph, 2]
     if nm == "attn": pro, comp = 0, t[ph, 2] - t[ph, 0]
     a = tot.setdefault(nm, [0, 0, 0, 0]); a[0] += pro; a[1] += comp; a[2] += bar; a[3] += 1
