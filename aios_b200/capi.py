@@ -78,6 +78,7 @@ SYMBOLS = {
     "aios_seq_prefill": (C.c_int, [_P, _P, C.c_int32]),
     "aios_seq_decode": (C.c_int, [_P, C.POINTER(Sampling), C.c_int32, _P, C.POINTER(C.c_int32)]),
     "aios_seq_step": (C.c_int, [_P, C.POINTER(Sampling), C.POINTER(C.c_int32)]),
+    "aios_seq_decode_static": (C.c_int, [_P, C.c_int32, _P, C.POINTER(C.c_int32)]),
     "aios_seq_logits": (C.c_int, [_P, _P]),
     "aios_generate": (C.c_int, [_P, _P, C.c_int32, C.POINTER(Sampling), C.c_int32, _P, C.POINTER(C.c_int32)]),
     "aios_dequantize": (C.c_int, [_P, C.c_int32, _P, C.c_int64, _P]),
@@ -234,6 +235,14 @@ class Seq:
         n = C.c_int32(0)
         sp = sampling if sampling is not None else Sampling()
         _check(lib().aios_seq_decode(self.h, C.byref(sp), max_tokens, _ptr(out), C.byref(n)))
+        return out[: n.value].copy()
+
+    def decode_static(self, max_tokens: int) -> np.ndarray:
+        """Greedy decode that allocates no device memory (aios_seq_decode_static): the fused kernel's exchange
+        scratch is the library's built-in static device array."""
+        out = np.empty(max(max_tokens, 1), dtype=np.int32)
+        n = C.c_int32(0)
+        _check(lib().aios_seq_decode_static(self.h, max_tokens, _ptr(out), C.byref(n)))
         return out[: n.value].copy()
 
     def step(self, sampling: Sampling | None = None) -> int:

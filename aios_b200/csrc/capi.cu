@@ -39,6 +39,8 @@ static int guarded(F &&f) {
         return fail(AIOS_E_CUDA, e.what());
     } catch (const std::invalid_argument &e) {
         return fail(AIOS_E_INVAL, e.what());
+    } catch (const std::length_error &e) {
+        return fail(AIOS_E_RANGE, e.what());
     } catch (const std::bad_alloc &) {
         return fail(AIOS_E_NOMEM, "out of host memory");
     } catch (const std::exception &e) {
@@ -181,6 +183,16 @@ int aios_seq_step(aios_seq *s, const aios_sampling *sp, int32_t *token_out) {
         std::lock_guard<std::mutex> lk(s->impl.m->eng->mu);
         s->impl.step(d, token_out);
         return AIOS_OK;
+    });
+}
+// Greedy decode that never touches the device allocator: the fused kernel's exchange scratch is the static
+// __device__ array in pfd.cu (resolved with cudaGetSymbolAddress on the first call per device).  See the header.
+int aios_seq_decode_static(aios_seq *s, int32_t max_tokens, int32_t *out_tokens, int32_t *n_out) {
+    return guarded([&] {
+        if (!s || !out_tokens || !n_out || max_tokens < 0) return fail(AIOS_E_INVAL, "bad argument");
+        std::lock_guard<std::mutex> lk(s->impl.m->eng->mu);
+        *n_out = s->impl.decode_static(max_tokens, out_tokens);
+        return (int)AIOS_OK;
     });
 }
 int aios_seq_logits(aios_seq *s, float *logits_out) {

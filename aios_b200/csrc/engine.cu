@@ -654,6 +654,55 @@ void Seq::launch_pfd_tokens(int n, cudaStream_t st) {
     launch_pfd(p, pfd_grid, st);
 }
 
+// Greedy decode through the fused kernel with its exchange scratch taken from the library's built-in
+// static device array (pfd.cu) instead of this sequence's cudaMalloc'd buffers.  Nothing on this path
+// allocates: only memset / launch / memcpy on the engine's stream.
+int Seq::decode_static(int max_tokens, int32_t *out) {
+    if (!have_logits) throw std::runtime_error("decode needs logits: prefill at least one token first");
+    if (pfd_grid <= 0) throw std::runtime_error("the fused decode kernel is not usable for this model on this device");
+    const HParams &hp = m->hp;
+    if (hp.n_head_kv > PFD_STATIC_MAX_KV_HEADS || hp.n_head * hp.head_dim > PFD_STATIC_MAX_QDIM)
+        throw std::length_error("model too large for the built-in scratch: at most " +
+                                std::to_string(PFD_STATIC_MAX_KV_HEADS) + " kv heads and n_head*head_dim <= " +
+                                std::to_string(PFD_STATIC_MAX_QDIM) + " (" + std::to_string(PFD_STATIC_SCRATCH_BYTES) +
+                                " bytes)");
+    const int steps = std::min(max_tokens, hp.n_ctx - n_past);
+    if (steps <= 0) return 0;
+    m->eng->make_current();
+    cudaStream_t st = m->eng->stream;
+    // first call on a device resolves the array's device address (cudaGetSymbolAddress)
+    uint8_t *base = static_cast<uint8_t *>(pfd_static_scratch(m->eng->device));
+    constexpr size_t OFF_COUNTERS = 0;                                                // 32 x u32
+    constexpr size_t OFF_MAX = 256;                                                   // [8][16][8] f32
+    constexpr size_t OFF_SUM = OFF_MAX + PFD_STATIC_MAX_KV_HEADS * 16 * 8 * sizeof(float);   // [8][16][8] f64
+    constexpr size_t OFF_ACC = OFF_SUM + PFD_STATIC_MAX_KV_HEADS * 16 * 8 * sizeof(double);  // [4096] f64
+    static_assert(OFF_ACC + PFD_STATIC_MAX_QDIM * sizeof(double) <= PFD_STATIC_SCRATCH_BYTES, "scratch layout");
+    PfdParams p = pfd;
+    p.att_counters = reinterpret_cast<unsigned *>(base + OFF_COUNTERS);
+    p.bar_counter = p.att_counters + 16;
+    p.att_max = reinterpret_cast<float *>(base + OFF_MAX);
+    p.att_sum = reinterpret_cast<double *>(base + OFF_SUM);
+    p.att_acc = reinterpret_cast<double *>(base + OFF_ACC);
+    p.timing = nullptr;
+    // the attn_output phases read the accumulators through the phase table, which points at this sequence's own
+    // buffer; the static variant therefore uses a second, static-scratch copy of the table's pointer: see below
+    p.x64_override = p.att_acc;
+    p.n_tokens = steps;
+    p.pos0 = n_past - 1;
+    p.step0 = 0;
+    // the array keeps whatever the previous call left: counters and accumulators must start at zero
+    CUDA_CHECK(cudaMemsetAsync(base + OFF_COUNTERS, 0, 256, st));
+    CUDA_CHECK(cudaMemsetAsync(base + OFF_ACC, 0, (size_t)hp.n_head * hp.head_dim * sizeof(double), st));
+    int32_t hdr[2] = {n_past - 1, 0};
+    CUDA_CHECK(cudaMemcpyAsync(state.p, hdr, sizeof(hdr), cudaMemcpyHostToDevice, st));
+    launch_pfd(p, pfd_grid, st);
+    CUDA_CHECK(cudaMemcpyAsync(out, out_tokens.p, (size_t)steps * 4, cudaMemcpyDeviceToHost, st));
+    CUDA_CHECK(cudaStreamSynchronize(st));
+    CUDA_CHECK(cudaGetLastError());
+    n_past += steps;
+    return steps;
+}
+
 void Seq::read_logits(float *out) {
     if (!have_logits) throw std::runtime_error("no logits yet");
     m->eng->make_current();

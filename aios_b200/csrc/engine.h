@@ -122,6 +122,7 @@ struct Seq {
     void prefill(const int32_t *tokens, int n);
     int decode(const aios_sampling &sp, int max_tokens, int32_t *out);
     void step(const aios_sampling &sp, int32_t *tok);
+    int decode_static(int max_tokens, int32_t *out);  // fused kernel on the library's built-in scratch: no allocation
     void bench_decode(int n_tokens, aios_bench_result *out);
     void profile_decode(int n_tokens, aios_bench_result *out);
     void snapshot();

@@ -255,8 +255,10 @@ __device__ __noinline__ float dequant_elem_nl(int type, const uint8_t *row, int6
 // ---------------------------------------------------------------- activation prologue of a GEMV phase
 __device__ __forceinline__ void src_load8(const PfdParams &p, const PfdPhase &P, int token, int idx, float (&v)[8]) {
     if (P.x64) {
+        // (the built-in-scratch variant keeps the f64 accumulators somewhere else than the phase table says)
+        const double *src = p.x64_override ? p.x64_override : P.x64;
 #pragma unroll
-        for (int i = 0; i < 8; i++) v[i] = (float)__ldcg(P.x64 + idx + i);
+        for (int i = 0; i < 8; i++) v[i] = (float)__ldcg(src + idx + i);
     } else {
         const float4 a = __ldcg(reinterpret_cast<const float4 *>(P.x + idx));
         const float4 b = __ldcg(reinterpret_cast<const float4 *>(P.x + idx) + 1);
@@ -693,6 +695,26 @@ __global__ void __launch_bounds__(PFD_THREADS, 1) pfd_kernel(const PfdParams p) 
         p.state[0] = pos;                      // SeqState.pos: position of the last token fed
         p.state[1] = p.step0 + p.n_tokens;     // SeqState.step
     }
+}
+
+// ---------------------------------------------------------------- built-in scratch (aios_seq_decode_static)
+// The fused kernel's cross-CTA exchange area (barrier counters, per-CTA row maxima and sums, f64 output
+// accumulators) normally lives in buffers each sequence cudaMalloc's when it is created.  This array is the
+// same area baked into the library image, so a decode call that uses it touches the allocator not at all.
+// Every GPU that loads the library carries these 48 KB until the process exits.
+static __device__ __align__(256) unsigned char g_pfd_static_scratch[PFD_STATIC_SCRATCH_BYTES];
+
+void *pfd_static_scratch(int device) {
+    // In host code the array's name is only a handle for the runtime, not a device address: resolve it once per
+    // device, with that device current (the caller has made it current), and hand the result to the kernel.
+    static void *addr[64] = {nullptr};
+    if (device < 0 || device >= 64) throw CudaError("static scratch: device ordinal out of range");
+    if (!addr[device]) {
+        void *ptr = nullptr;
+        CUDA_CHECK(cudaGetSymbolAddress((void **)&ptr, g_pfd_static_scratch));
+        addr[device] = ptr;
+    }
+    return addr[device];
 }
 
 size_t pfd_smem_bytes(const PfdParams &p) {

@@ -61,9 +61,18 @@ struct PfdParams {
     unsigned *att_counters;  // [n_kv] monotonic group barriers (zeroed by the host before the launch)
     unsigned *bar_counter;   // grid barrier (zeroed by the host before the launch)
     int32_t k_max;           // largest GEMV input length (sizes the activation images)
+    const double *x64_override;  // null, or where the f64 attention accumulators really are (built-in scratch variant)
     unsigned long long *timing;  // optional [n_phases][4] ns stamps of CTA 0 for the last token: start, after prologue,
                                  // after compute, after barrier (null = off)
 };
+
+// Size of the library's built-in exchange scratch (a static __device__ array in pfd.cu) used by
+// aios_seq_decode_static instead of per-sequence cudaMalloc'd buffers.
+constexpr size_t PFD_STATIC_SCRATCH_BYTES = 48 * 1024;
+constexpr int PFD_STATIC_MAX_KV_HEADS = 8;        // att_max / att_sum rows
+constexpr int PFD_STATIC_MAX_QDIM = 4096;         // n_head * head_dim (f64 accumulators)
+// device address of that array on `device` (made current by the caller); the first call per device resolves it
+void *pfd_static_scratch(int device);
 
 size_t pfd_smem_bytes(const PfdParams &p);
 int pfd_max_grid(int n_sms, const PfdParams &p);   // 0 if the kernel cannot be made resident

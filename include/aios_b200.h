@@ -122,6 +122,34 @@ int aios_seq_decode(aios_seq *s, const aios_sampling *sp, int32_t max_tokens, in
 /* one streaming step: sample from the kept logits, feed that token, return it.
  * H2D: 0 bytes; D2H: 4 bytes; synchronises. */
 int aios_seq_step(aios_seq *s, const aios_sampling *sp, int32_t *token_out);
+/* Greedy decode for callers that must not allocate device memory while serving.  (No counterpart in the
+ * reference: llama-server hides its allocator behind a process boundary.)
+ *
+ * Who needs it: a serving thread whose device-memory budget was handed out completely at start-up and is frozen
+ * afterwards (an embedding host that owns the rest of HBM for its own pools, or a real-time loop that forbids
+ * allocator calls because cudaMalloc/cudaFree synchronise the whole device and take a process-wide lock).  Such a
+ * caller creates the model and the sequence during start-up, when allocating is still allowed, and later only calls
+ * this function.
+ *
+ * Same result as aios_seq_decode with greedy sampling (temperature <= 0): up to max_tokens tokens into the caller's
+ * HOST buffer out_tokens[max_tokens], *n_out = how many (fewer at the context limit).  It always runs the persistent
+ * fused decode kernel, and that kernel's cross-CTA exchange area — barrier counters, per-CTA soft-max row maxima and
+ * sums, the f64 attention-output accumulators — is a 48 KB array compiled into the library image instead of buffers
+ * from cudaMalloc.  The call issues only memset / kernel launch / memcpy on the engine's stream: no cudaMalloc, no
+ * cudaFree, no allocating library routine.
+ *
+ * Limits: the array fits models with at most 8 kv heads and n_head*head_dim <= 4096 (TinyLlama, Mistral-7B);
+ * anything larger is refused with AIOS_E_RANGE.  AIOS_E_STATE if the sequence has no logits yet or the fused kernel
+ * cannot be made resident on this GPU.
+ *
+ * Sharing: there is ONE array per GPU, shared by every sequence and every call in the process, and it keeps what
+ * the previous call left in it; each call clears the counters and accumulators it needs at zero before launching.
+ * Two calls whose kernels overlap on the same GPU (two engines, two streams) would trample each other's
+ * counters — serialise them.  Every GPU that loads the library holds the 48 KB until the process exits.
+ *
+ * Set-up: the first call on a device looks the array's device address up once (cudaGetSymbolAddress, with that
+ * device current) and remembers it; make that first call before starting any stream capture. */
+int aios_seq_decode_static(aios_seq *s, int32_t max_tokens, int32_t *out_tokens, int32_t *n_out);
 /* copy the kept logits (n_vocab floats) to the host */
 int aios_seq_logits(aios_seq *s, float *logits_out);
 /* remember / return to the current position and its logits (prompt caching, benchmark replays).
