@@ -271,6 +271,10 @@ void attn_init() {
 }
 
 void launch_attn_decode(const AttnParams &p, cudaStream_t st) {
+    if (attn_head_usable(p.n_ctx, p.hd)) {  // short context: skip the cluster launch and its barriers
+        launch_attn_decode_head(p, st);
+        return;
+    }
     const int rep = p.n_head / p.n_kv;
     const int per_cap = ((p.n_ctx + ATT_CLUSTER - 1) / ATT_CLUSTER + 1) & ~1;  // even: keeps the f64 area aligned
     const size_t smem = attn_dyn_smem(rep, p.hd, per_cap);

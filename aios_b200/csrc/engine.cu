@@ -51,6 +51,7 @@ Engine::Engine(const aios_engine_opts &o) : device(o.device), max_batch(o.max_ba
     CUDA_CHECK(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
     gemv_init();
     attn_init();
+    attn_head_init();
 }
 Engine::~Engine() {
     if (stream) cudaStreamDestroy(stream);

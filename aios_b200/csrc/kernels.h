@@ -55,6 +55,10 @@ struct AttnParams {
 };
 void launch_attn_decode(const AttnParams &p, cudaStream_t st);
 void attn_init();  // one-time function attributes (dynamic smem)
+// short contexts: one CTA per query head, no cross-CTA exchange (attention_head.cu)
+bool attn_head_usable(int n_ctx, int hd);
+void launch_attn_decode_head(const AttnParams &p, cudaStream_t st);
+void attn_head_init();
 size_t attn_scratch_floats(int n_head, int n_split, int hd);
 
 // ---- sampler.cu

@@ -258,3 +258,25 @@ def test_fused_decode_kernel_matches_oracle_and_per_op_path(engine, engine_pfd, 
     finally:
         m1.unload()
         m2.unload()
+
+
+def test_long_context_attention_path_matches_oracle(engine, oracle, tmp_models):
+    """n_ctx > 1024 selects the cluster/DSMEM attention kernel (attention.cu) instead of the one-CTA-per-head kernel
+    (attention_head.cu); both must give the oracle's logits bit for bit."""
+    path = tmp_models("tiny-gqa4", "Q4_K_M")
+    m = engine.load_model("t", path, n_ctx=1536)
+    try:
+        om = oracle.OracleModel(path, n_ctx=1536)
+        prompt = gs.synthetic_prompt("tiny-gqa4", 40, 2)
+        ref = om.eval_all(prompt)
+        seq = m.new_seq()
+        try:
+            for i in range(len(prompt)):
+                seq.prefill(prompt[i:i + 1])
+                if i % 5 == 4 or i == len(prompt) - 1:
+                    got = seq.logits()
+                    assert np.abs(got - ref[i]).max() / ref[i].std() < LOGIT_TOL, i
+        finally:
+            seq.free()
+    finally:
+        m.unload()
