@@ -21,6 +21,7 @@ ENGINE_NO_GRAPH = 1
 ENGINE_NO_PDL = 2
 ENGINE_NO_PFD = 4
 ENGINE_USE_PFD = 8
+ENGINE_L2_PREFETCH = 16
 
 
 class AiosError(RuntimeError):
@@ -48,6 +49,11 @@ class TensorInfo(C.Structure):
                 ("offset", C.c_int64), ("nbytes", C.c_int64)]
 
 
+class VocabInfo(C.Structure):
+    _fields_ = [("n_tokens", C.c_int32), ("bos", C.c_int32), ("eos", C.c_int32), ("add_bos", C.c_int32),
+                ("model", C.c_char * 32)]
+
+
 class Sampling(C.Structure):
     _fields_ = [("temperature", C.c_float), ("top_k", C.c_int32), ("top_p", C.c_float), ("min_p", C.c_float),
                 ("seed", C.c_uint64)]
@@ -71,6 +77,9 @@ SYMBOLS = {
     "aios_model_unload": (C.c_int, [_P]),
     "aios_model_info_get": (C.c_int, [_P, C.POINTER(ModelInfo)]),
     "aios_model_tensor_info": (C.c_int, [_P, C.c_int32, C.POINTER(TensorInfo)]),
+    "aios_model_vocab": (C.c_int, [_P, C.POINTER(VocabInfo)]),
+    "aios_model_token_piece": (C.c_int, [_P, C.c_int32, _P, C.c_int32, C.POINTER(C.c_int32), C.POINTER(C.c_int32),
+                                        C.POINTER(C.c_float)]),
     "aios_seq_create": (C.c_int, [_P, C.POINTER(_P)]),
     "aios_seq_free": (None, [_P]),
     "aios_seq_reset": (C.c_int, [_P]),
@@ -187,6 +196,22 @@ class Model:
         t = TensorInfo()
         _check(lib().aios_model_tensor_info(self.h, i, C.byref(t)))
         return t
+
+    def vocab_info(self) -> VocabInfo:
+        v = VocabInfo()
+        _check(lib().aios_model_vocab(self.h, C.byref(v)))
+        return v
+
+    def vocab(self):
+        """[(piece bytes, token_type, score)] for every token id."""
+        n = self.vocab_info().n_tokens
+        out = []
+        buf = C.create_string_buffer(512)
+        ln, ty, sc = C.c_int32(0), C.c_int32(0), C.c_float(0)
+        for i in range(n):
+            _check(lib().aios_model_token_piece(self.h, i, buf, 512, C.byref(ln), C.byref(ty), C.byref(sc)))
+            out.append((buf.raw[: ln.value], ty.value, sc.value))
+        return out
 
     def new_seq(self) -> "Seq":
         return Seq(self)

@@ -16,6 +16,18 @@ struct aios_engine { Engine impl; explicit aios_engine(const aios_engine_opts &o
 struct aios_model {
     Model impl;
     std::unique_ptr<Seq> scratch;  // for aios_forward_logits
+    // tokenizer.ggml.* arrays, materialised on first use (aios_model_vocab / aios_model_token_piece)
+    bool vocab_loaded = false;
+    std::vector<std::string> vocab;
+    std::vector<int32_t> vtype;
+    std::vector<float> vscore;
+    void load_vocab() {
+        if (vocab_loaded) return;
+        vocab = impl.file->get_str_array("tokenizer.ggml.tokens");
+        vtype = impl.file->get_i32_array("tokenizer.ggml.token_type");
+        vscore = impl.file->get_f32_array("tokenizer.ggml.scores");
+        vocab_loaded = true;
+    }
     aios_model(Engine *e, const char *n, const char *p, int c) : impl(e, n, p, c) {}
 };
 struct aios_seq { Seq impl; explicit aios_seq(Model *m) : impl(m) {} };
@@ -127,6 +139,40 @@ int aios_model_tensor_info(const aios_model *m, int32_t i, aios_tensor_info *o) 
         for (int d = 0; d < 4; d++) o->ne[d] = ts[i].ne[d];
         o->offset = (int64_t)ts[i].offset; o->nbytes = (int64_t)ts[i].nbytes;
         return AIOS_OK;
+    });
+}
+
+int aios_model_vocab(aios_model *m, aios_vocab_info *o) {
+    return guarded([&] {
+        if (!m || !o) return fail(AIOS_E_INVAL, "null argument");
+        std::lock_guard<std::mutex> lk(m->impl.mu);
+        m->load_vocab();
+        memset(o, 0, sizeof(*o));
+        const GgufFile &f = *m->impl.file;
+        o->n_tokens = (int32_t)m->vocab.size();
+        o->bos = (int32_t)f.get_u("tokenizer.ggml.bos_token_id", (uint64_t)-1);
+        o->eos = (int32_t)f.get_u("tokenizer.ggml.eos_token_id", (uint64_t)-1);
+        o->add_bos = f.has("tokenizer.ggml.add_bos_token") ? (int32_t)f.get_u("tokenizer.ggml.add_bos_token", 1) : 1;
+        strncpy(o->model, f.get_s("tokenizer.ggml.model", "").c_str(), sizeof(o->model) - 1);
+        return (int)AIOS_OK;
+    });
+}
+
+int aios_model_token_piece(aios_model *m, int32_t id, char *buf, int32_t cap, int32_t *len, int32_t *type, float *score) {
+    return guarded([&] {
+        if (!m || !len) return fail(AIOS_E_INVAL, "null argument");
+        std::lock_guard<std::mutex> lk(m->impl.mu);
+        m->load_vocab();
+        if (id < 0 || (size_t)id >= m->vocab.size()) return fail(AIOS_E_INVAL, "token id out of range");
+        const std::string &s = m->vocab[id];
+        *len = (int32_t)s.size();
+        if (type) *type = (size_t)id < m->vtype.size() ? m->vtype[id] : 1;
+        if (score) *score = (size_t)id < m->vscore.size() ? m->vscore[id] : 0.f;
+        if (buf && cap > 0) {
+            if ((size_t)cap < s.size()) return fail(AIOS_E_RANGE, "buffer too small for the token piece");
+            memcpy(buf, s.data(), s.size());
+        }
+        return (int)AIOS_OK;
     });
 }
 

@@ -290,8 +290,30 @@ void Seq::reset() {
     CUDA_CHECK(cudaMemcpy(state.p, &s, sizeof(s), cudaMemcpyHostToDevice));
 }
 
+// next launch's weight planes -> L2 prefetch ranges of this launch (capped: two big matrices must share L2)
+static void set_prefetch(GemvParams &p, std::initializer_list<const WPlanes *> next, bool on) {
+    p.n_pf = 0;
+    if (!on) return;
+    size_t budget = 72u << 20;
+    for (const WPlanes *w : next) {
+        if (!w) continue;
+        for (int i = 0; i < 5 && p.n_pf < 12; i++) {
+            const size_t b = plane_bytes(w->type, i, w->n_rows, w->k);
+            if (!b || !w->p[i]) continue;
+            const size_t take = std::min(b, budget);
+            if (take < 4096) continue;
+            p.pf_ptr[p.n_pf] = w->p[i];
+            p.pf_bytes[p.n_pf] = (uint32_t)take;
+            p.n_pf++;
+            budget -= take;
+        }
+    }
+}
+
 void Seq::launch_token_pass(bool from_prompt, int prompt_idx, int pos_value, bool want_logits, cudaStream_t st, int *n_launch) {
     const HParams &hp = m->hp;
+    // opt-in: measured 6 % SLOWER on Mistral-7B (2.10 vs 1.97 ms/token, profiles/r01_v3_summary.md)
+    const bool pf = (m->eng->flags & AIOS_ENGINE_L2_PREFETCH) != 0;
     SeqState *sd = state.as<SeqState>();
     const int n_sms = m->eng->n_sms;
     int launches = 0;
@@ -310,6 +332,8 @@ void Seq::launch_token_pass(bool from_prompt, int prompt_idx, int pos_value, boo
             p.seg[0] = L.wq.w; p.seg[1] = L.wk.w; p.seg[2] = L.wv.w;
             p.out[0] = qkv.as<float>(); p.out[1] = qkv.as<float>() + QD; p.out[2] = qkv.as<float>() + QD + KVD;
             p.x = x.as<float>(); p.norm_w = L.attn_norm.as<float>(); p.eps = hp.rms_eps;
+            if (same) set_prefetch(p, {&L.wo.w}, pf);
+            else set_prefetch(p, {&L.wv.w, &L.wo.w}, pf);
             TIMED(0, launch_gemv(p, gemv_plan_grid(p, n_sms), st, pdl));
             launches++;
             if (!same) {
@@ -317,6 +341,7 @@ void Seq::launch_token_pass(bool from_prompt, int prompt_idx, int pos_value, boo
                 v.n_seg = 1; v.epi = EPI_STORE; v.k = hp.n_embd;
                 v.seg[0] = L.wv.w; v.out[0] = qkv.as<float>() + QD + KVD;
                 v.x = x.as<float>(); v.norm_w = L.attn_norm.as<float>(); v.eps = hp.rms_eps;
+                set_prefetch(v, {&L.w_gate.w}, pf);  // (attn_output was requested by the q,k launch)
                 TIMED(0, launch_gemv(v, gemv_plan_grid(v, n_sms), st, pdl));
                 launches++;
             }
@@ -338,6 +363,7 @@ void Seq::launch_token_pass(bool from_prompt, int prompt_idx, int pos_value, boo
             GemvParams p{};
             p.n_seg = 1; p.epi = EPI_ADD; p.k = QD;
             p.seg[0] = L.wo.w; p.out[0] = x.as<float>(); p.x = att.as<float>();
+            set_prefetch(p, {&L.w_gate.w, &L.w_up.w}, pf);
             TIMED(0, launch_gemv(p, gemv_plan_grid(p, n_sms), st, pdl));
             launches++;
         }
@@ -346,6 +372,7 @@ void Seq::launch_token_pass(bool from_prompt, int prompt_idx, int pos_value, boo
             p.n_seg = 2; p.epi = EPI_SWIGLU; p.k = hp.n_embd;
             p.seg[0] = L.w_gate.w; p.seg[1] = L.w_up.w; p.out[0] = h.as<float>();
             p.x = x.as<float>(); p.norm_w = L.ffn_norm.as<float>(); p.eps = hp.rms_eps;
+            set_prefetch(p, {&L.w_down.w}, pf);
             TIMED(0, launch_gemv(p, gemv_plan_grid(p, n_sms), st, pdl));
             launches++;
         }
@@ -353,6 +380,8 @@ void Seq::launch_token_pass(bool from_prompt, int prompt_idx, int pos_value, boo
             GemvParams p{};
             p.n_seg = 1; p.epi = EPI_ADD; p.k = hp.n_ff;
             p.seg[0] = L.w_down.w; p.out[0] = x.as<float>(); p.x = h.as<float>();
+            if (il + 1 < hp.n_layer) set_prefetch(p, {&m->layers[il + 1].wq.w, &m->layers[il + 1].wk.w, &m->layers[il + 1].wv.w}, pf);
+            else if (want_logits) set_prefetch(p, {&m->output.w}, pf);
             TIMED(0, launch_gemv(p, gemv_plan_grid(p, n_sms), st, pdl));
             launches++;
         }

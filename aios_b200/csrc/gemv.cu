@@ -64,6 +64,7 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) gemv_kernel(const GemvParams 
         if (full) load_pass<TYPE, true>(g, rp, 0, nu);
         else load_pass<TYPE, false>(g, rp, 0, nu);
     }
+    l2_prefetch_next(p);  // and the NEXT launch's weights start moving HBM -> L2
     // programmatic dependent launch: everything above overlapped the previous kernel's tail
     asm volatile("griddepcontrol.wait;" ::: "memory");
 
@@ -147,6 +148,10 @@ int gemv_plan_grid(GemvParams &p, int n_sms) {
     return begin;
 }
 
+static int g_n_sms = 148;
+static bool g_use_staged = false;  // measured slower than the register pipeline so far (profiles/r01_v3_gemv.md)
+void gemv_set_staged(bool on) { g_use_staged = on; }
+
 void gemv_init() {
     static bool done = false;
     if (done) return;
@@ -154,6 +159,10 @@ void gemv_init() {
     CUDA_CHECK(cudaFuncSetAttribute(gemv_kernel<T_Q5_K>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
     CUDA_CHECK(cudaFuncSetAttribute(gemv_kernel<T_Q6_K>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
     CUDA_CHECK(cudaFuncSetAttribute(gemv_kernel<T_Q8_0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+    int dev = 0;
+    CUDA_CHECK(cudaGetDevice(&dev));
+    CUDA_CHECK(cudaDeviceGetAttribute(&g_n_sms, cudaDevAttrMultiProcessorCount, dev));
+    gemv_staged_init();
     done = true;
 }
 
@@ -162,6 +171,10 @@ void launch_gemv(const GemvParams &p, int grid, cudaStream_t st, bool pdl) {
     const int t = p.seg[0].type;
     for (int i = 1; i < p.n_seg; i++)
         if (p.seg[i].type != t) throw CudaError("launch_gemv: segments of one launch must share a weight type");
+    if (g_use_staged && gemv_staged_usable(p, g_n_sms)) {  // big matrix: the cp.async ring keeps more bytes in flight
+        launch_gemv_staged(p, g_n_sms, st, pdl);
+        return;
+    }
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(grid);
     cfg.blockDim = dim3(GEMV_THREADS);

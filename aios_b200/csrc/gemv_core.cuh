@@ -201,6 +201,21 @@ __device__ void prep_activations(const float *__restrict__ x, const float *__res
 }
 
 // ---------------------------------------------------------------- weight registers of one pass
+// L2 prefetch of the next launch's weight planes: CTA b of g takes the b-th slice of every range
+__device__ __forceinline__ void l2_prefetch_next(const GemvParams &p) {
+    constexpr uint32_t PIECE = 4096;
+    for (int i = 0; i < p.n_pf; i++) {
+        const uint32_t bytes = p.pf_bytes[i];
+        const uint32_t per = ((bytes + gridDim.x - 1) / gridDim.x + 15u) & ~15u;
+        const uint32_t lo = blockIdx.x * per;
+        const uint32_t hi = lo + per < bytes ? lo + per : bytes;
+        for (uint32_t o = lo + threadIdx.x * PIECE; o < hi; o += GEMV_THREADS * PIECE) {
+            const uint32_t sz = ((hi - o < PIECE ? hi - o : PIECE) + 15u) & ~15u;  // planes are padded to 256 B
+            asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p.pf_ptr[i] + o), "r"(sz) : "memory");
+        }
+    }
+}
+
 struct RowPtrs {
     const uint8_t *p[5];  // row starts inside each plane
 };

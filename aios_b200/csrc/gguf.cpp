@@ -200,5 +200,21 @@ std::vector<std::string> GgufFile::get_str_array(const std::string &key) const {
     for (uint64_t i = 0; i < v->arr_n; i++) out.push_back(c.str());
     return out;
 }
+std::vector<int32_t> GgufFile::get_i32_array(const std::string &key) const {
+    std::vector<int32_t> out;
+    const GgufValue *v = get(key);
+    if (!v || v->kind != GgufValue::ARRAY || (v->arr_type != GT_I32 && v->arr_type != GT_U32)) return out;
+    out.resize((size_t)v->arr_n);
+    memcpy(out.data(), v->arr_data, out.size() * 4);
+    return out;
+}
+std::vector<float> GgufFile::get_f32_array(const std::string &key) const {
+    std::vector<float> out;
+    const GgufValue *v = get(key);
+    if (!v || v->kind != GgufValue::ARRAY || v->arr_type != GT_F32) return out;
+    out.resize((size_t)v->arr_n);
+    memcpy(out.data(), v->arr_data, out.size() * 4);
+    return out;
+}
 
 }  // namespace aios

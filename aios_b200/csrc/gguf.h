@@ -61,6 +61,8 @@ class GgufFile {
     std::string get_s(const std::string &key, const std::string &dflt) const;
     // string array element access (tokenizer.ggml.tokens)
     std::vector<std::string> get_str_array(const std::string &key) const;
+    std::vector<int32_t> get_i32_array(const std::string &key) const;
+    std::vector<float> get_f32_array(const std::string &key) const;
 
    private:
     void parse();

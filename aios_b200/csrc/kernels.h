@@ -31,6 +31,11 @@ struct GemvParams {
     const float *norm_w;    // if non-null: x <- rmsnorm(x) * norm_w first (llama attn_norm / ffn_norm / output_norm)
     float eps;
     unsigned long long *argmax_key;  // if non-null (EPI_STORE, 1 segment): running packed (value,index) max
+    // weights of the NEXT launch of the token pass: every CTA asks L2 to fetch its slice of them
+    // (cp.async.bulk.prefetch.L2), so HBM keeps streaming through this launch's tail and the next one's start
+    int32_t n_pf;
+    const uint8_t *pf_ptr[12];
+    uint32_t pf_bytes[12];
 };
 
 // fills cta_begin[] and returns the grid size; n_sms from the device
@@ -38,6 +43,10 @@ int gemv_plan_grid(GemvParams &p, int n_sms);
 size_t gemv_smem_bytes(int k);
 void launch_gemv(const GemvParams &p, int grid, cudaStream_t st, bool pdl = false);
 void gemv_init();  // one-time function attributes (dynamic smem)
+// large matrices: per-warp cp.async ring in shared memory (gemv_staged.cu); launch_gemv picks it when usable
+bool gemv_staged_usable(const GemvParams &p, int n_sms);
+void launch_gemv_staged(const GemvParams &p, int n_sms, cudaStream_t st, bool pdl);
+void gemv_staged_init();
 
 // ---- attention.cu : RoPE + KV write + flash-decode over the f16 KV cache (one new token)
 struct AttnParams {

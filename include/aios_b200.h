@@ -59,6 +59,7 @@ typedef struct aios_engine_opts {
 #define AIOS_ENGINE_NO_PDL 2   /* no programmatic dependent launch between the GEMV kernels (debug) */
 #define AIOS_ENGINE_NO_PFD 4   /* greedy decode through per-op kernels instead of the persistent fused kernel */
 #define AIOS_ENGINE_USE_PFD 8  /* greedy decode through the persistent fused decode kernel (pfd.cu) */
+#define AIOS_ENGINE_L2_PREFETCH 16 /* GEMV launches prefetch the next launch's weights into L2 (experiment; slower so far) */
 
 int aios_engine_create(const aios_engine_opts *opts, aios_engine **out);
 void aios_engine_destroy(aios_engine *e);
@@ -97,6 +98,19 @@ typedef struct aios_tensor_info {
     int64_t nbytes;
 } aios_tensor_info;
 int aios_model_tensor_info(const aios_model *m, int32_t i, aios_tensor_info *out);
+
+/* ---- vocabulary (tokenizer.ggml.* metadata): what llama-server's tokenizer / detokenizer stage reads from the
+ *      GGUF; the host-side tokenizer (aios_b200/runtime/tokenizer.py) is built on these. */
+typedef struct aios_vocab_info {
+    int32_t n_tokens;    /* length of tokenizer.ggml.tokens (0 if the file carries no vocabulary)          */
+    int32_t bos, eos;    /* tokenizer.ggml.{bos,eos}_token_id, -1 if absent                               */
+    int32_t add_bos;     /* tokenizer.ggml.add_bos_token (default 1)                                      */
+    char model[32];      /* tokenizer.ggml.model: "llama" (SPM), "gpt2" (BPE), ...                        */
+} aios_vocab_info;
+int aios_model_vocab(aios_model *m, aios_vocab_info *out);
+/* piece bytes (not NUL-terminated) of token id; *len = its length even when buf is NULL; type = token_type
+ * (1 normal, 2 unknown, 3 control, 6 byte), score = tokenizer.ggml.scores[id] */
+int aios_model_token_piece(aios_model *m, int32_t id, char *buf, int32_t cap, int32_t *len, int32_t *type, float *score);
 
 /* ---- sampling parameters: the request fields InferenceEngine::infer forwards
  *      (runtime/src/inference.rs:103-122: max_tokens, temperature) plus the llama-server
