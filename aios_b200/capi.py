@@ -15,7 +15,7 @@ import numpy as np
 _HERE = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_HERE, "libaios_b200.so")
 
-AIOS_OK, E_INVAL, E_IO, E_FORMAT, E_CUDA, E_NOMEM, E_STATE, E_RANGE = 0, -1, -2, -3, -4, -5, -6, -7
+AIOS_OK, E_INVAL, E_IO, E_FORMAT, E_CUDA, E_NOMEM, E_STATE, E_RANGE, E_UNSUPPORTED = 0, -1, -2, -3, -4, -5, -6, -7, -8
 TYPE_F32, TYPE_F16, TYPE_Q8_0, TYPE_Q4_K, TYPE_Q5_K, TYPE_Q6_K = 0, 1, 8, 12, 13, 14
 ENGINE_NO_GRAPH = 1
 ENGINE_NO_PDL = 2
@@ -51,7 +51,7 @@ class TensorInfo(C.Structure):
 
 class VocabInfo(C.Structure):
     _fields_ = [("n_tokens", C.c_int32), ("bos", C.c_int32), ("eos", C.c_int32), ("add_bos", C.c_int32),
-                ("model", C.c_char * 32)]
+                ("chat_format", C.c_int32), ("model", C.c_char * 32)]
 
 
 class Sampling(C.Structure):
@@ -65,6 +65,8 @@ class BenchResult(C.Structure):
                 ("reserved", C.c_float * 3)]
 
 
+TOK_ADD_SPECIAL, TOK_PARSE_SPECIAL, TOK_RENDER_SPECIAL, TOK_STRIP_SPACE = 1, 2, 4, 8
+
 # every symbol include/aios_b200.h declares: name -> (restype, argtypes)
 _P = C.c_void_p
 SYMBOLS = {
@@ -77,9 +79,17 @@ SYMBOLS = {
     "aios_model_unload": (C.c_int, [_P]),
     "aios_model_info_get": (C.c_int, [_P, C.POINTER(ModelInfo)]),
     "aios_model_tensor_info": (C.c_int, [_P, C.c_int32, C.POINTER(TensorInfo)]),
-    "aios_model_vocab": (C.c_int, [_P, C.POINTER(VocabInfo)]),
-    "aios_model_token_piece": (C.c_int, [_P, C.c_int32, _P, C.c_int32, C.POINTER(C.c_int32), C.POINTER(C.c_int32),
+    "aios_model_meta_str": (C.c_int, [_P, C.c_char_p, _P, C.c_int32, C.POINTER(C.c_int32)]),
+    "aios_vocab_open": (C.c_int, [C.c_char_p, C.POINTER(_P)]),
+    "aios_vocab_close": (None, [_P]),
+    "aios_model_vocab": (C.c_int, [_P, C.POINTER(_P)]),
+    "aios_vocab_info_get": (C.c_int, [_P, C.POINTER(VocabInfo)]),
+    "aios_vocab_token_piece": (C.c_int, [_P, C.c_int32, _P, C.c_int32, C.POINTER(C.c_int32), C.POINTER(C.c_int32),
                                         C.POINTER(C.c_float)]),
+    "aios_tokenize": (C.c_int, [_P, C.c_char_p, C.c_int32, C.c_int32, _P, C.c_int32, C.POINTER(C.c_int32)]),
+    "aios_detokenize": (C.c_int, [_P, _P, C.c_int32, C.c_int32, _P, C.c_int32, C.POINTER(C.c_int32)]),
+    "aios_chat_prompt": (C.c_int, [_P, C.c_char_p, C.c_char_p, _P, C.c_int32, C.POINTER(C.c_int32)]),
+    "aios_token_is_eog": (C.c_int, [_P, C.c_int32, C.POINTER(C.c_int32)]),
     "aios_seq_create": (C.c_int, [_P, C.POINTER(_P)]),
     "aios_seq_free": (None, [_P]),
     "aios_seq_reset": (C.c_int, [_P]),
@@ -141,6 +151,74 @@ def make_sampling(temperature=0.0, top_k=40, top_p=0.95, min_p=0.05, seed=0) -> 
     return Sampling(float(temperature), int(top_k), float(top_p), float(min_p), int(seed))
 
 
+def _bytes_out(call) -> bytes:
+    """Run a (buf, cap, len*) style entry point: size query first, then the copy."""
+    ln = C.c_int32(0)
+    _check(call(None, 0, C.byref(ln)))
+    if ln.value == 0:
+        return b""
+    buf = C.create_string_buffer(ln.value)
+    _check(call(buf, ln.value, C.byref(ln)))
+    return buf.raw[: ln.value]
+
+
+class Vocab:
+    """A GGUF file's tokenizer (host only).  ``Vocab.open(path)`` needs no GPU; ``Model.vocab()`` borrows the
+    loaded model's."""
+
+    def __init__(self, handle, owned: bool, keep=None):
+        self.h, self.owned, self._keep = handle, owned, keep
+        self.info = VocabInfo()
+        _check(lib().aios_vocab_info_get(self.h, C.byref(self.info)))
+
+    @classmethod
+    def open(cls, path: str) -> "Vocab":
+        h = _P()
+        _check(lib().aios_vocab_open(path.encode(), C.byref(h)))
+        return cls(h, owned=True)
+
+    def close(self):
+        if self.h and self.owned:
+            lib().aios_vocab_close(self.h)
+        self.h = _P()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def piece(self, i: int):
+        """(piece bytes, token_type, score) of token id i."""
+        ln, ty, sc = C.c_int32(0), C.c_int32(0), C.c_float(0)
+        buf = C.create_string_buffer(512)
+        _check(lib().aios_vocab_token_piece(self.h, i, buf, 512, C.byref(ln), C.byref(ty), C.byref(sc)))
+        return buf.raw[: ln.value], ty.value, sc.value
+
+    def tokenize(self, text: str | bytes, add_special: bool = True, parse_special: bool = False) -> np.ndarray:
+        raw = text.encode("utf-8") if isinstance(text, str) else bytes(text)
+        flags = (TOK_ADD_SPECIAL if add_special else 0) | (TOK_PARSE_SPECIAL if parse_special else 0)
+        n = C.c_int32(0)
+        _check(lib().aios_tokenize(self.h, raw, len(raw), flags, None, 0, C.byref(n)))
+        out = np.empty(max(n.value, 1), dtype=np.int32)
+        _check(lib().aios_tokenize(self.h, raw, len(raw), flags, _ptr(out), out.size, C.byref(n)))
+        return out[: n.value].copy()
+
+    def detokenize(self, tokens, render_special: bool = False, strip_space: bool = False) -> bytes:
+        toks = np.ascontiguousarray(tokens, dtype=np.int32)
+        flags = (TOK_RENDER_SPECIAL if render_special else 0) | (TOK_STRIP_SPACE if strip_space else 0)
+        return _bytes_out(lambda b, c, l: lib().aios_detokenize(self.h, _ptr(toks), toks.size, flags, b, c, l))
+
+    def chat_prompt(self, system_prompt: str, user_prompt: str) -> str:
+        return _bytes_out(lambda b, c, l: lib().aios_chat_prompt(
+            self.h, (system_prompt or "").encode("utf-8"), user_prompt.encode("utf-8"), b, c, l)).decode("utf-8", "replace")
+
+    def is_eog(self, token: int) -> bool:
+        r = C.c_int32(0)
+        _check(lib().aios_token_is_eog(self.h, int(token), C.byref(r)))
+        return bool(r.value)
+
+
 class Engine:
     def __init__(self, device: int = 0, max_batch: int = 1, flags: int = 0):
         self.h = _P()
@@ -197,21 +275,18 @@ class Model:
         _check(lib().aios_model_tensor_info(self.h, i, C.byref(t)))
         return t
 
-    def vocab_info(self) -> VocabInfo:
-        v = VocabInfo()
-        _check(lib().aios_model_vocab(self.h, C.byref(v)))
-        return v
+    def meta_str(self, key: str, default: str | None = None) -> str | None:
+        try:
+            return _bytes_out(lambda b, c, l: lib().aios_model_meta_str(self.h, key.encode(), b, c, l)).decode(
+                "utf-8", "replace")
+        except AiosError:
+            return default
 
-    def vocab(self):
-        """[(piece bytes, token_type, score)] for every token id."""
-        n = self.vocab_info().n_tokens
-        out = []
-        buf = C.create_string_buffer(512)
-        ln, ty, sc = C.c_int32(0), C.c_int32(0), C.c_float(0)
-        for i in range(n):
-            _check(lib().aios_model_token_piece(self.h, i, buf, 512, C.byref(ln), C.byref(ty), C.byref(sc)))
-            out.append((buf.raw[: ln.value], ty.value, sc.value))
-        return out
+    def vocab(self) -> "Vocab":
+        """The model's tokenizer (borrowed handle: lives as long as the model)."""
+        h = _P()
+        _check(lib().aios_model_vocab(self.h, C.byref(h)))
+        return Vocab(h, owned=False, keep=self)
 
     def new_seq(self) -> "Seq":
         return Seq(self)

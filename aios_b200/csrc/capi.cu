@@ -9,24 +9,28 @@
 #include "../../include/aios_b200.h"
 #include "common.cuh"
 #include "engine.h"
+#include "tokenizer.h"
 
 using namespace aios;
 
 struct aios_engine { Engine impl; explicit aios_engine(const aios_engine_opts &o) : impl(o) {} };
+// host-only: the tokenizer of one GGUF file; either owns its file (aios_vocab_open) or borrows the model's
+struct aios_vocab {
+    std::unique_ptr<GgufFile> own;
+    Tokenizer tok;
+    explicit aios_vocab(const char *path) : own(new GgufFile(path)), tok(*own) {}
+    explicit aios_vocab(const GgufFile &f) : tok(f) {}
+};
 struct aios_model {
     Model impl;
     std::unique_ptr<Seq> scratch;  // for aios_forward_logits
-    // tokenizer.ggml.* arrays, materialised on first use (aios_model_vocab / aios_model_token_piece)
-    bool vocab_loaded = false;
-    std::vector<std::string> vocab;
-    std::vector<int32_t> vtype;
-    std::vector<float> vscore;
-    void load_vocab() {
-        if (vocab_loaded) return;
-        vocab = impl.file->get_str_array("tokenizer.ggml.tokens");
-        vtype = impl.file->get_i32_array("tokenizer.ggml.token_type");
-        vscore = impl.file->get_f32_array("tokenizer.ggml.scores");
-        vocab_loaded = true;
+    // built from the tokenizer.ggml.* metadata on first use, under tok_mu (not the engine's GPU lock)
+    std::mutex tok_mu;
+    std::unique_ptr<aios_vocab> vocab_;
+    aios_vocab *vocab() {
+        std::lock_guard<std::mutex> lk(tok_mu);
+        if (!vocab_) vocab_.reset(new aios_vocab(*impl.file));
+        return vocab_.get();
     }
     aios_model(Engine *e, const char *n, const char *p, int c) : impl(e, n, p, c) {}
 };
@@ -142,36 +146,118 @@ int aios_model_tensor_info(const aios_model *m, int32_t i, aios_tensor_info *o) 
     });
 }
 
-int aios_model_vocab(aios_model *m, aios_vocab_info *o) {
+// copy a std::string into a caller buffer: *len always gets the full length; AIOS_E_RANGE if it does not fit
+static int put_bytes(const std::string &s, char *buf, int32_t cap, int32_t *len) {
+    *len = (int32_t)s.size();
+    if (buf && cap > 0) {
+        if ((size_t)cap < s.size()) return fail(AIOS_E_RANGE, "output buffer too small");
+        memcpy(buf, s.data(), s.size());
+    } else if (buf == nullptr) {
+        return (int)AIOS_OK;  // length query
+    } else if (!s.empty()) {
+        return fail(AIOS_E_RANGE, "output buffer too small");
+    }
+    return (int)AIOS_OK;
+}
+
+int aios_vocab_open(const char *gguf_path, aios_vocab **out) {
     return guarded([&] {
-        if (!m || !o) return fail(AIOS_E_INVAL, "null argument");
-        std::lock_guard<std::mutex> lk(m->impl.mu);
-        m->load_vocab();
-        memset(o, 0, sizeof(*o));
-        const GgufFile &f = *m->impl.file;
-        o->n_tokens = (int32_t)m->vocab.size();
-        o->bos = (int32_t)f.get_u("tokenizer.ggml.bos_token_id", (uint64_t)-1);
-        o->eos = (int32_t)f.get_u("tokenizer.ggml.eos_token_id", (uint64_t)-1);
-        o->add_bos = f.has("tokenizer.ggml.add_bos_token") ? (int32_t)f.get_u("tokenizer.ggml.add_bos_token", 1) : 1;
-        strncpy(o->model, f.get_s("tokenizer.ggml.model", "").c_str(), sizeof(o->model) - 1);
+        if (!gguf_path || !out) return fail(AIOS_E_INVAL, "null argument");
+        *out = new aios_vocab(gguf_path);
         return (int)AIOS_OK;
     });
 }
 
-int aios_model_token_piece(aios_model *m, int32_t id, char *buf, int32_t cap, int32_t *len, int32_t *type, float *score) {
+void aios_vocab_close(aios_vocab *v) { delete v; }
+
+int aios_model_vocab(aios_model *m, aios_vocab **out) {
     return guarded([&] {
-        if (!m || !len) return fail(AIOS_E_INVAL, "null argument");
-        std::lock_guard<std::mutex> lk(m->impl.mu);
-        m->load_vocab();
-        if (id < 0 || (size_t)id >= m->vocab.size()) return fail(AIOS_E_INVAL, "token id out of range");
-        const std::string &s = m->vocab[id];
-        *len = (int32_t)s.size();
-        if (type) *type = (size_t)id < m->vtype.size() ? m->vtype[id] : 1;
-        if (score) *score = (size_t)id < m->vscore.size() ? m->vscore[id] : 0.f;
-        if (buf && cap > 0) {
-            if ((size_t)cap < s.size()) return fail(AIOS_E_RANGE, "buffer too small for the token piece");
-            memcpy(buf, s.data(), s.size());
-        }
+        if (!m || !out) return fail(AIOS_E_INVAL, "null argument");
+        *out = m->vocab();
+        return (int)AIOS_OK;
+    });
+}
+
+int aios_vocab_info_get(aios_vocab *v, aios_vocab_info *o) {
+    return guarded([&] {
+        if (!v || !o) return fail(AIOS_E_INVAL, "null argument");
+        const Tokenizer &t = v->tok;
+        memset(o, 0, sizeof(*o));
+        o->n_tokens = t.n_tokens();
+        o->bos = t.bos();
+        o->eos = t.eos();
+        o->add_bos = t.add_bos() ? 1 : 0;
+        o->chat_format = (int32_t)t.chat_format();
+        strncpy(o->model, t.model().c_str(), sizeof(o->model) - 1);
+        return (int)AIOS_OK;
+    });
+}
+
+int aios_vocab_token_piece(aios_vocab *v, int32_t id, char *buf, int32_t cap, int32_t *len, int32_t *type, float *score) {
+    return guarded([&] {
+        if (!v || !len) return fail(AIOS_E_INVAL, "null argument");
+        const Tokenizer &t = v->tok;
+        if (id < 0 || id >= t.n_tokens()) return fail(AIOS_E_INVAL, "token id out of range");
+        if (type) *type = t.type(id);
+        if (score) *score = t.score(id);
+        return put_bytes(t.piece(id), buf, cap, len);
+    });
+}
+
+int aios_model_meta_str(aios_model *m, const char *key, char *buf, int32_t cap, int32_t *len) {
+    return guarded([&] {
+        if (!m || !key || !len) return fail(AIOS_E_INVAL, "null argument");
+        const GgufValue *v = m->impl.file->get(key);
+        if (!v || v->kind != GgufValue::STRING) return fail(AIOS_E_INVAL, std::string("no string metadata key ") + key);
+        return put_bytes(v->s, buf, cap, len);
+    });
+}
+
+static int need_vocab(const Tokenizer &t) {
+    if (t.n_tokens() == 0) return fail(AIOS_E_STATE, "the GGUF file carries no tokenizer.ggml.tokens");
+    if (t.model() != "llama")
+        return fail(AIOS_E_UNSUPPORTED, "tokenizer.ggml.model '" + t.model() + "' is not supported (only 'llama' / SentencePiece)");
+    return (int)AIOS_OK;
+}
+
+int aios_tokenize(aios_vocab *v, const char *text, int32_t text_len, int32_t flags, int32_t *out, int32_t cap, int32_t *n_out) {
+    return guarded([&] {
+        if (!v || (!text && text_len != 0) || !n_out) return fail(AIOS_E_INVAL, "null argument");
+        const Tokenizer &t = v->tok;
+        if (int rc = need_vocab(t)) return rc;
+        std::string s = text_len < 0 ? std::string(text) : std::string(text, (size_t)text_len);
+        std::vector<int32_t> ids = t.encode(s, (flags & AIOS_TOK_ADD_SPECIAL) != 0, (flags & AIOS_TOK_PARSE_SPECIAL) != 0);
+        *n_out = (int32_t)ids.size();
+        if (!out) return (int)AIOS_OK;  // count query
+        if ((size_t)cap < ids.size()) return fail(AIOS_E_RANGE, "token buffer too small");
+        if (!ids.empty()) memcpy(out, ids.data(), ids.size() * sizeof(int32_t));
+        return (int)AIOS_OK;
+    });
+}
+
+int aios_detokenize(aios_vocab *v, const int32_t *tokens, int32_t n, int32_t flags, char *buf, int32_t cap, int32_t *len) {
+    return guarded([&] {
+        if (!v || (!tokens && n > 0) || !len || n < 0) return fail(AIOS_E_INVAL, "bad argument");
+        const Tokenizer &t = v->tok;
+        if (t.n_tokens() == 0) return fail(AIOS_E_STATE, "the GGUF file carries no tokenizer.ggml.tokens");
+        for (int32_t i = 0; i < n; i++)
+            if (tokens[i] < 0 || tokens[i] >= t.n_tokens()) return fail(AIOS_E_INVAL, "token id out of range");
+        return put_bytes(t.decode(tokens, n, (flags & AIOS_TOK_RENDER_SPECIAL) != 0, (flags & AIOS_TOK_STRIP_SPACE) != 0),
+                         buf, cap, len);
+    });
+}
+
+int aios_chat_prompt(aios_vocab *v, const char *system_prompt, const char *user_prompt, char *buf, int32_t cap, int32_t *len) {
+    return guarded([&] {
+        if (!v || !user_prompt || !len) return fail(AIOS_E_INVAL, "null argument");
+        return put_bytes(v->tok.chat_prompt(system_prompt ? system_prompt : "", user_prompt), buf, cap, len);
+    });
+}
+
+int aios_token_is_eog(aios_vocab *v, int32_t id, int32_t *is_eog) {
+    return guarded([&] {
+        if (!v || !is_eog) return fail(AIOS_E_INVAL, "null argument");
+        *is_eog = v->tok.is_eog(id) ? 1 : 0;
         return (int)AIOS_OK;
     });
 }

@@ -188,7 +188,10 @@ class SynthInfo:
 
 
 def write_synthetic_gguf(path: str, arch: Arch | str, ftype: str = "Q4_K_M", seed: int = 0xA105,
-                         w_std: float = 0.02, with_vocab: bool = True) -> SynthInfo:
+                         w_std: float = 0.02, with_vocab: bool = True, vocab: list | None = None,
+                         chat_template: str | None = None, tokenizer_model: str = "llama") -> SynthInfo:
+    """``vocab`` = [(piece, score, token_type)] replaces the generated placeholder vocabulary (padded with unused
+    entries up to ``arch.n_vocab``); ``chat_template`` is stored as ``tokenizer.chat_template``."""
     if isinstance(arch, str):
         arch = ARCHS[arch]
     plan = tensor_plan(arch, ftype)
@@ -207,11 +210,22 @@ def write_synthetic_gguf(path: str, arch: Arch | str, ftype: str = "Q4_K_M", see
         _kv("llama.attention.layer_norm_rms_epsilon", _F32, arch.rms_eps),
         _kv("llama.rope.dimension_count", _U32, arch.head_dim),
         _kv("llama.rope.freq_base", _F32, arch.rope_freq_base),
-        _kv("tokenizer.ggml.model", _STR, "llama"),
+        _kv("tokenizer.ggml.model", _STR, tokenizer_model),
         _kv("tokenizer.ggml.bos_token_id", _U32, 1),
         _kv("tokenizer.ggml.eos_token_id", _U32, 2),
     ]
-    if with_vocab:
+    if chat_template is not None:
+        kvs.append(_kv("tokenizer.chat_template", _STR, chat_template))
+    if vocab is not None:
+        if len(vocab) > arch.n_vocab:
+            raise ValueError(f"vocabulary of {len(vocab)} pieces exceeds n_vocab {arch.n_vocab}")
+        pad = arch.n_vocab - len(vocab)
+        kvs += [
+            _kv("tokenizer.ggml.tokens", _ARR, (_STR, [p for p, _, _ in vocab] + [f"<unused{i}>" for i in range(pad)])),
+            _kv("tokenizer.ggml.scores", _ARR, (_F32, [float(s) for _, s, _ in vocab] + [0.0] * pad)),
+            _kv("tokenizer.ggml.token_type", _ARR, (_I32, [int(t) for _, _, t in vocab] + [5] * pad)),
+        ]
+    elif with_vocab:
         toks = ["<unk>", "<s>", "</s>"] + [f"<0x{i:02X}>" for i in range(256)]
         toks += [f"▁t{i}" for i in range(arch.n_vocab - len(toks))]
         toks = toks[: arch.n_vocab]

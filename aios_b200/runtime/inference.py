@@ -1,0 +1,180 @@
+"""InferenceEngine — host-side mirror of ``runtime/src/inference.rs`` whose HTTP call to llama-server is replaced
+by the B200 engine behind the C ABI (``aios_b200.capi``).
+
+Reference behaviour kept (file:line): defaults ``max_tokens <= 0 -> 512`` and ``temperature <= 0 -> 0.7``
+(inference.rs:103-112, :203-212); messages = optional system + user (``build_messages`` :363-376);
+``tokens_used = prompt + completion`` (llama-server's ``usage.total_tokens`` read at :167-171); ``latency_ms`` =
+wall milliseconds around the whole call (:138, :158); ``model_used`` = the resolved name (:180-185); the stream
+ends with ``done: true`` (:290-299, :345-352).  What the llama-server child did per request — chat template,
+tokenizer, prefill, the decode loop, the sampler chain (top-k 40, top-p 0.95, min-p 0.05, temperature; SURVEY.md
+§8a D2-D5) — happens in the engine; the sampler runs on the device so a decode step moves 4 bytes to the host.
+
+Differences, on purpose: ``stream_infer`` really streams (the reference buffers the whole SSE body first,
+inference.rs:261); JSON-mode constrained sampling (``response_format: json_object``, :119-121) is not built yet
+ — unary ``infer`` samples unconstrained.
+
+There is no CPU fallback: ``EngineBackend`` needs libaios_b200.so and a B200.
+"""
+from __future__ import annotations
+
+import codecs
+import logging
+import os
+import threading
+import time
+from dataclasses import dataclass
+from typing import Iterator, Optional
+
+import numpy as np
+
+log = logging.getLogger("aios_b200.runtime")
+
+DEFAULT_MAX_TOKENS = 512  # inference.rs:103-107
+DEFAULT_TEMPERATURE = 0.7  # inference.rs:108-112
+STREAM_CHUNK_TOKENS = 8  # tokens per device round trip while streaming
+
+
+@dataclass
+class InferParams:
+    """The fields of InferRequest (runtime.proto:41-50) the engine consumes."""
+    prompt: str
+    system_prompt: str = ""
+    max_tokens: int = 0
+    temperature: float = 0.0
+    requesting_agent: str = ""
+    task_id: str = ""
+    seed: Optional[int] = None  # not on the wire; tests pin it
+
+
+@dataclass
+class InferResult:
+    """InferResponse (runtime.proto:52-57)."""
+    text: str
+    tokens_used: int
+    latency_ms: int
+    model_used: str
+
+
+def build_messages(system_prompt: str, user_prompt: str) -> list[dict]:
+    """inference.rs:363-376"""
+    msgs = []
+    if system_prompt:
+        msgs.append({"role": "system", "content": system_prompt})
+    msgs.append({"role": "user", "content": user_prompt})
+    return msgs
+
+
+def effective_max_tokens(v: int) -> int:
+    return v if v > 0 else DEFAULT_MAX_TOKENS
+
+
+def effective_temperature(v: float) -> float:
+    return v if v > 0.0 else DEFAULT_TEMPERATURE
+
+
+class LoadedModel:
+    """One model resident in HBM: what a llama-server child was for the reference."""
+
+    def __init__(self, engine, name: str, path: str, context_length: int):
+        self.name = name
+        self.model = engine.load_model(name, path, context_length)
+        self.vocab = self.model.vocab()
+        self.n_ctx = self.model.info.n_ctx
+        self.seq = self.model.new_seq()
+        self.lock = threading.Lock()  # one KV slot: requests of one model run one after another
+
+    def close(self):
+        with self.lock:
+            self.seq.free()
+            self.model.unload()
+
+
+class EngineBackend:
+    """``Backend`` of ModelManager on the real engine: one ``aios_engine`` per process / GPU."""
+
+    def __init__(self, device: int = 0, flags: int = 0):
+        from .. import capi
+        self.capi = capi
+        self.engine = capi.Engine(device=device, flags=flags)
+
+    def load(self, name: str, path: str, context_length: int) -> LoadedModel:
+        if not os.path.isfile(path):
+            raise FileNotFoundError(f"model file {path} not found")
+        return LoadedModel(self.engine, name, path, context_length)
+
+    def unload(self, handle: LoadedModel) -> None:
+        handle.close()
+
+    def alive(self, handle: LoadedModel) -> bool:
+        return bool(handle.model.h)
+
+    def close(self):
+        self.engine.close()
+
+
+class InferenceEngine:
+    """Stateless, shared by all handlers, like the reference's ``Arc<InferenceEngine>`` (main.rs:51)."""
+
+    def __init__(self, stream_chunk_tokens: int = STREAM_CHUNK_TOKENS):
+        self.stream_chunk_tokens = stream_chunk_tokens
+
+    # -- what llama-server did before the forward passes: template + tokenize
+    def _prepare(self, lm: LoadedModel, p: InferParams):
+        text = lm.vocab.chat_prompt(p.system_prompt, p.prompt)
+        tokens = lm.vocab.tokenize(text, add_special=True, parse_special=True)
+        if tokens.size >= lm.n_ctx:
+            raise RuntimeError(f"the request exceeds the available context size ({tokens.size} prompt tokens, "
+                               f"context {lm.n_ctx})")
+        max_tokens = min(effective_max_tokens(p.max_tokens), lm.n_ctx - int(tokens.size))
+        from ..capi import make_sampling
+        seed = p.seed if p.seed is not None else int.from_bytes(os.urandom(8), "little")
+        sampling = make_sampling(temperature=effective_temperature(p.temperature), seed=seed)
+        return tokens, max_tokens, sampling
+
+    def _generate(self, lm: LoadedModel, p: InferParams, chunk: int) -> Iterator[tuple[np.ndarray, int, bool]]:
+        """Yields (new completion tokens without the end-of-generation token, n_prompt, finished)."""
+        tokens, max_tokens, sampling = self._prepare(lm, p)
+        with lm.lock:
+            lm.seq.reset()
+            lm.seq.prefill(tokens)
+            left = max_tokens
+            while left > 0:
+                out = lm.seq.decode(min(chunk, left), sampling)
+                if out.size == 0:
+                    break
+                left -= int(out.size)
+                stop = next((i for i, t in enumerate(out) if lm.vocab.is_eog(int(t))), None)
+                if stop is not None:
+                    yield out[:stop], int(tokens.size), True
+                    return
+                yield out, int(tokens.size), left <= 0
+            yield np.empty(0, np.int32), int(tokens.size), True
+
+    def infer(self, lm: LoadedModel, model_name: str, p: InferParams) -> InferResult:
+        """inference.rs:94-186"""
+        start = time.monotonic()
+        log.info("Sending inference request model=%s max_tokens=%d temperature=%.3g agent=%s task=%s", model_name,
+                 effective_max_tokens(p.max_tokens), effective_temperature(p.temperature), p.requesting_agent, p.task_id)
+        done_tokens, n_prompt = [], 0
+        for toks, n_prompt, finished in self._generate(lm, p, chunk=64):
+            done_tokens.append(toks)
+            if finished:
+                break
+        comp = np.concatenate(done_tokens) if done_tokens else np.empty(0, np.int32)
+        text = lm.vocab.detokenize(comp).decode("utf-8", "replace")
+        latency_ms = int((time.monotonic() - start) * 1000)
+        return InferResult(text=text, tokens_used=n_prompt + int(comp.size), latency_ms=latency_ms, model_used=model_name)
+
+    def stream_infer(self, lm: LoadedModel, model_name: str, p: InferParams) -> Iterator[tuple[str, bool]]:
+        """inference.rs:194-356: yields (text, done); the last item is always done=True."""
+        utf8 = codecs.getincrementaldecoder("utf-8")("replace")
+        for toks, _, finished in self._generate(lm, p, chunk=self.stream_chunk_tokens):
+            text = utf8.decode(lm.vocab.detokenize(toks), final=finished) if toks.size or finished else ""
+            if finished:
+                if text:
+                    yield text, False
+                yield "", True
+                return
+            if text:
+                yield text, False
+        yield "", True

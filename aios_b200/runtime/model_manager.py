@@ -1,0 +1,256 @@
+"""ModelManager — host-side mirror of ``runtime/src/model_manager.rs`` with the llama-server child replaced by an
+in-process model handle on the B200 engine.
+
+Same public surface and observable behaviour as the reference (file:line cited per method); what changes is what
+a "managed model" is: the reference spawns ``llama-server --model … --port …`` and polls ``/health``
+(model_manager.rs:187-277), here ``backend.load(name, path, ctx)`` maps the GGUF into HBM through the C ABI
+(``aios_model_load``) and returns a handle.  ``port`` stays in ``ModelStatus`` (model_manager.rs:543) as a stable
+pseudo-port from the same allocator (BASE_PORT 8080, :69, :137-144) — nothing listens on it.
+
+Differences, on purpose (SURVEY.md §8b "Threading"): the table lock is NOT held while a model loads, so routing
+and inference on other models keep running during a load (the reference blocks them for up to 120 s,
+grpc_service.rs:40-41); a second LoadModel for a name that is still loading gets ``status: "loading"`` back,
+which is what the reference's idempotence rule (:152-157) says for that state.
+"""
+from __future__ import annotations
+
+import logging
+import os
+import threading
+import time
+from dataclasses import dataclass, field
+from typing import Any, Optional, Protocol
+
+log = logging.getLogger("aios_b200.runtime")
+
+BASE_PORT = 8080  # model_manager.rs:69
+DEFAULT_MODEL_DIR = "/var/lib/aios/models/"  # model_manager.rs:118-120
+DEFAULT_CONTEXT = 2048  # model_manager.rs:167-171
+DEFAULT_THREADS = 4  # model_manager.rs:173 (kept in the record; the GPU engine has no use for it)
+
+
+def now_epoch_ms() -> int:
+    """model_manager.rs:100-105"""
+    return int(time.time() * 1000)
+
+
+class ModelState:
+    """model_manager.rs:24-40: the four states and their display strings."""
+    LOADING, READY, ERROR, UNLOADING = "loading", "ready", "error", "unloading"
+
+    def __init__(self, kind: str, msg: str = ""):
+        self.kind, self.msg = kind, msg
+
+    def __str__(self) -> str:
+        return f"error: {self.msg}" if self.kind == self.ERROR else self.kind
+
+    @property
+    def ready(self) -> bool:
+        return self.kind == self.READY
+
+
+@dataclass
+class ManagedModel:
+    """model_manager.rs:42-56, with ``process: Option<Child>`` replaced by ``handle``."""
+    name: str
+    path: str
+    port: int
+    status: ModelState
+    loaded_at: int
+    last_used: int
+    request_count: int = 0
+    context_length: int = DEFAULT_CONTEXT
+    gpu_layers: int = 0
+    threads: int = DEFAULT_THREADS
+    handle: Any = None
+    loaded_evt: threading.Event = field(default_factory=threading.Event, repr=False)
+
+
+@dataclass
+class ModelStatusRecord:
+    """Plain-data ModelStatus (runtime.proto:28-35); ``model_to_status`` at model_manager.rs:539-548."""
+    model_name: str
+    status: str
+    port: int
+    loaded_at: int
+    last_used: int
+    request_count: int
+
+
+@dataclass
+class LoadRequest:
+    """LoadModelRequest (runtime.proto:15-22)."""
+    model_name: str
+    model_path: str = ""
+    context_length: int = 0
+    gpu_layers: int = 0
+    threads: int = 0
+    port: int = 0
+
+
+class Backend(Protocol):
+    """What stands where the llama-server child stood."""
+
+    def load(self, name: str, path: str, context_length: int) -> Any: ...
+    def unload(self, handle: Any) -> None: ...
+    def alive(self, handle: Any) -> bool: ...
+
+
+def model_to_status(m: ManagedModel) -> ModelStatusRecord:
+    return ModelStatusRecord(m.name, str(m.status), int(m.port), m.loaded_at, m.last_used, m.request_count)
+
+
+class ModelManager:
+    def __init__(self, backend: Backend, model_dir: Optional[str] = None):
+        # model_manager.rs:115-131
+        self.backend = backend
+        self.model_dir = model_dir or os.environ.get("AIOS_MODEL_DIR", DEFAULT_MODEL_DIR)
+        self.models: dict[str, ManagedModel] = {}
+        self.next_port = BASE_PORT
+        self.lock = threading.RLock()
+        log.info("ModelManager initialised model_dir=%s", self.model_dir)
+
+    # ------------------------------------------------------------------ port allocation (model_manager.rs:134-144)
+    def allocate_port(self, requested: int) -> int:
+        if requested > 0:
+            return requested
+        port = self.next_port
+        self.next_port += 1
+        return port
+
+    # ------------------------------------------------------------------ load (model_manager.rs:149-277)
+    def load_model(self, req: LoadRequest) -> ModelStatusRecord:
+        name = req.model_name
+        with self.lock:
+            existing = self.models.get(name)
+            if existing is not None and existing.status.kind in (ModelState.READY, ModelState.LOADING):
+                log.info("Model %s already loaded, returning current status", name)
+                return model_to_status(existing)
+            path = req.model_path if req.model_path else os.path.join(self.model_dir, name)
+            port = self.allocate_port(req.port & 0xFFFF)  # `req.port as u16`
+            ctx = req.context_length if req.context_length > 0 else DEFAULT_CONTEXT
+            threads = req.threads if req.threads > 0 else DEFAULT_THREADS
+            now = now_epoch_ms()
+            managed = ManagedModel(name=name, path=path, port=port, status=ModelState(ModelState.LOADING),
+                                   loaded_at=now, last_used=now, context_length=ctx, gpu_layers=req.gpu_layers,
+                                   threads=threads)
+            self.models[name] = managed
+        log.info("Loading model %s path=%s port=%d ctx=%d", name, path, port, ctx)
+        try:
+            handle = self.backend.load(name, path, ctx)
+        except Exception as e:  # the reference's "exited early" branch: recorded in-band AND returned as Err
+            msg = str(e)
+            with self.lock:
+                managed.status = ModelState(ModelState.ERROR, msg)
+                managed.loaded_evt.set()
+            log.error("Model %s failed to load: %s", name, msg)
+            raise RuntimeError(msg) from e
+        with self.lock:
+            if managed.status.kind == ModelState.UNLOADING or self.models.get(name) is not managed:
+                # unloaded while it was loading: drop the fresh handle
+                self.backend.unload(handle)
+                managed.loaded_evt.set()
+                return model_to_status(managed)
+            managed.handle = handle
+            managed.status = ModelState(ModelState.READY)
+            managed.loaded_evt.set()
+            log.info("Model %s is ready", name)
+            return model_to_status(managed)
+
+    # ------------------------------------------------------------------ unload (model_manager.rs:285-345)
+    def unload_model(self, name: str) -> None:
+        with self.lock:
+            model = self.models.get(name)
+            if model is None:
+                raise KeyError(f"Model '{name}' not found")
+            model.status = ModelState(ModelState.UNLOADING)
+            handle, model.handle = model.handle, None
+            del self.models[name]
+        log.info("Unloading model %s", name)
+        if handle is not None:
+            self.backend.unload(handle)
+        log.info("Model %s unloaded", name)
+
+    # ------------------------------------------------------------------ list / get (model_manager.rs:352-376)
+    def list_models(self) -> list[ModelStatusRecord]:
+        with self.lock:
+            return [model_to_status(m) for m in self.models.values()]
+
+    def get_model(self, name: str) -> Optional[ManagedModel]:
+        with self.lock:
+            m = self.models.get(name)
+            if m is not None:
+                m.last_used = now_epoch_ms()
+            return m
+
+    def model_port(self, name: str) -> Optional[int]:
+        """Ready check, ``last_used`` stamp, ``request_count += 1`` (model_manager.rs:367-376)."""
+        with self.lock:
+            m = self.get_model(name)
+            if m is not None and m.status.ready:
+                m.request_count += 1
+                return m.port
+            return None
+
+    def model_handle(self, name: str) -> Any:
+        """The engine handle that replaces the port as the coupling to the backend."""
+        with self.lock:
+            m = self.models.get(name)
+            return m.handle if m is not None and m.status.ready else None
+
+    # ------------------------------------------------------------------ health (model_manager.rs:393-447)
+    def health_check_all(self) -> None:
+        """Reference: child liveness + GET /health per model, flipping Ready <-> Error.  Here: ask the backend
+        whether the handle is still usable (a sticky CUDA error is the in-process version of a dead child)."""
+        with self.lock:
+            for m in self.models.values():
+                if m.status.kind in (ModelState.LOADING, ModelState.UNLOADING) or m.handle is None:
+                    continue
+                try:
+                    ok = self.backend.alive(m.handle)
+                except Exception as e:
+                    ok, why = False, str(e)
+                else:
+                    why = "engine handle no longer usable"
+                if ok and m.status.kind == ModelState.ERROR:
+                    log.info("Model %s recovered", m.name)
+                    m.status = ModelState(ModelState.READY)
+                elif not ok and m.status.kind != ModelState.ERROR:
+                    log.warning("Model %s health check failed: %s", m.name, why)
+                    m.status = ModelState(ModelState.ERROR, why)
+
+    # ------------------------------------------------------------------ level routing (model_manager.rs:462-518)
+    LEVELS = {
+        "operational": ["tinyllama-1.1b", "DeepSeek-R1-Distill-Qwen-8B", "mistral-7b"],
+        "tactical": ["DeepSeek-R1-Distill-Qwen-8B", "Qwen3-14B", "mistral-7b", "tinyllama-1.1b"],
+        "strategic": ["Qwen3-14B", "DeepSeek-R1-Distill-Qwen-8B", "mistral-7b"],
+    }
+
+    def select_model_for_level(self, level: str) -> Optional[str]:
+        if level == "reactive":
+            return None  # heuristics, no LLM
+        if level in self.LEVELS:
+            return self.first_ready_from(self.LEVELS[level])
+        log.warning("Unknown intelligence level %r, falling back to first ready model", level)
+        return self.first_ready_model()
+
+    def first_ready_from(self, candidates: list[str]) -> Optional[str]:
+        with self.lock:
+            for cand in candidates:
+                c = cand.lower()
+                for name, m in self.models.items():
+                    if m.status.ready and c in name.lower():
+                        return name
+        return None
+
+    def is_model_ready(self, name: str) -> bool:
+        with self.lock:
+            m = self.models.get(name)
+            return m is not None and m.status.ready
+
+    def first_ready_model(self) -> Optional[str]:
+        with self.lock:
+            for m in self.models.values():
+                if m.status.ready:
+                    return m.name
+        return None

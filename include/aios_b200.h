@@ -31,6 +31,7 @@ extern "C" {
 #define AIOS_E_NOMEM (-5)   /* device or host memory exhausted                                */
 #define AIOS_E_STATE (-6)   /* wrong state (context full, unloaded)  -> tonic FailedPrecondition */
 #define AIOS_E_RANGE (-7)   /* size beyond a stated maximum                                   */
+#define AIOS_E_UNSUPPORTED (-8) /* valid input this build does not implement (e.g. BPE vocab) */
 
 /* ggml tensor type ids as stored in GGUF (gguf-py constants.py GGMLQuantizationType) */
 #define AIOS_TYPE_F32 0
@@ -43,6 +44,7 @@ extern "C" {
 typedef struct aios_engine aios_engine;   /* one per GPU: device, stream, scratch            */
 typedef struct aios_model aios_model;     /* a loaded GGUF: replaces one llama-server child  */
 typedef struct aios_seq aios_seq;         /* one sequence = one KV-cache slot of a model     */
+typedef struct aios_vocab aios_vocab;     /* a GGUF's tokenizer (host only, needs no GPU)    */
 
 const char *aios_last_error(void);
 /* library / build identification, e.g. "aios_b200 0.1 sm_100a" */
@@ -99,18 +101,44 @@ typedef struct aios_tensor_info {
 } aios_tensor_info;
 int aios_model_tensor_info(const aios_model *m, int32_t i, aios_tensor_info *out);
 
-/* ---- vocabulary (tokenizer.ggml.* metadata): what llama-server's tokenizer / detokenizer stage reads from the
- *      GGUF; the host-side tokenizer (aios_b200/runtime/tokenizer.py) is built on these. */
+/* a string-valued GGUF metadata key ("general.name", "tokenizer.chat_template", ...): AIOS_E_INVAL if absent.
+ * Output-buffer convention here and below: *len / *n_out always receives the full size; pass buf/out = NULL to
+ * query it; AIOS_E_RANGE if cap is too short. */
+int aios_model_meta_str(aios_model *m, const char *key, char *buf, int32_t cap, int32_t *len);
+
+/* ---- vocabulary, tokenizer and chat prompt: the stage llama-server runs on the {system,user} messages the
+ *      reference posts (runtime/src/inference.rs:363-376 build_messages), read from the
+ *      GGUF's tokenizer.ggml.* metadata.  Host-only: a vocabulary can be opened straight from a file without a GPU
+ *      (aios_vocab_open / aios_vocab_close), or borrowed from a loaded model (aios_model_vocab: owned by the model,
+ *      valid until aios_model_unload, never closed by the caller).  SentencePiece-style ("llama") vocabularies
+ *      only; encoding with a "gpt2"/BPE vocabulary answers AIOS_E_UNSUPPORTED. */
+int aios_vocab_open(const char *gguf_path, aios_vocab **out);
+void aios_vocab_close(aios_vocab *v);
+int aios_model_vocab(aios_model *m, aios_vocab **out);
 typedef struct aios_vocab_info {
     int32_t n_tokens;    /* length of tokenizer.ggml.tokens (0 if the file carries no vocabulary)          */
     int32_t bos, eos;    /* tokenizer.ggml.{bos,eos}_token_id, -1 if absent                               */
     int32_t add_bos;     /* tokenizer.ggml.add_bos_token (default 1)                                      */
+    int32_t chat_format; /* 0 chatml, 1 llama-2, 2 mistral, 3 zephyr, 4 llama-3 (see aios_chat_prompt)    */
     char model[32];      /* tokenizer.ggml.model: "llama" (SPM), "gpt2" (BPE), ...                        */
 } aios_vocab_info;
-int aios_model_vocab(aios_model *m, aios_vocab_info *out);
-/* piece bytes (not NUL-terminated) of token id; *len = its length even when buf is NULL; type = token_type
- * (1 normal, 2 unknown, 3 control, 6 byte), score = tokenizer.ggml.scores[id] */
-int aios_model_token_piece(aios_model *m, int32_t id, char *buf, int32_t cap, int32_t *len, int32_t *type, float *score);
+int aios_vocab_info_get(aios_vocab *v, aios_vocab_info *out);
+/* piece bytes (not NUL-terminated) of token id; type = token_type (1 normal, 2 unknown, 3 control,
+ * 4 user-defined, 6 byte), score = tokenizer.ggml.scores[id] */
+int aios_vocab_token_piece(aios_vocab *v, int32_t id, char *buf, int32_t cap, int32_t *len, int32_t *type, float *score);
+#define AIOS_TOK_ADD_SPECIAL 1     /* tokenize: prepend BOS when the vocabulary asks for it                  */
+#define AIOS_TOK_PARSE_SPECIAL 2   /* tokenize: control-token strings in the text become their single ids    */
+#define AIOS_TOK_RENDER_SPECIAL 4  /* detokenize: emit control tokens' strings instead of skipping them      */
+#define AIOS_TOK_STRIP_SPACE 8     /* detokenize: drop the leading space of the SentencePiece prefix         */
+/* text_len < 0: text is NUL-terminated */
+int aios_tokenize(aios_vocab *v, const char *text, int32_t text_len, int32_t flags, int32_t *out, int32_t cap, int32_t *n_out);
+int aios_detokenize(aios_vocab *v, const int32_t *tokens, int32_t n, int32_t flags, char *buf, int32_t cap, int32_t *len);
+/* [system?, user] rendered in the model's chat format (recognised from tokenizer.chat_template by its marker
+ * strings: chatml, llama-2, mistral, zephyr, llama-3; chatml when there is none) and ending with the assistant
+ * header, ready for aios_tokenize(ADD_SPECIAL|PARSE_SPECIAL).  system_prompt may be NULL or "". */
+int aios_chat_prompt(aios_vocab *v, const char *system_prompt, const char *user_prompt, char *buf, int32_t cap, int32_t *len);
+/* 1 if id ends generation: tokenizer.ggml.eos_token_id or a turn terminator (<|im_end|>, <|eot_id|>, ...) */
+int aios_token_is_eog(aios_vocab *v, int32_t id, int32_t *is_eog);
 
 /* ---- sampling parameters: the request fields InferenceEngine::infer forwards
  *      (runtime/src/inference.rs:103-122: max_tokens, temperature) plus the llama-server
