@@ -22,6 +22,8 @@ ENGINE_NO_PDL = 2
 ENGINE_NO_PFD = 4
 ENGINE_USE_PFD = 8
 ENGINE_L2_PREFETCH = 16
+ENGINE_ATTN_HEAD = 32
+ENGINE_ATTN_CLUSTER = 64
 
 
 class AiosError(RuntimeError):

@@ -270,8 +270,12 @@ void attn_init() {
     done = true;
 }
 
-void launch_attn_decode(const AttnParams &p, cudaStream_t st) {
-    if (attn_head_usable(p.n_ctx, p.hd)) {  // short context: skip the cluster launch and its barriers
+void launch_attn_decode(const AttnParams &p, cudaStream_t st, bool pdl, int mode) {
+    if (mode == 0 && attn_split_usable(p.n_ctx, p.hd)) {  // one wave of independent CTAs, PDL
+        launch_attn_decode_split(p, st, pdl);
+        return;
+    }
+    if (mode != 2 && attn_head_usable(p.n_ctx, p.hd)) {  // short context: skip the cluster launch and its barriers
         launch_attn_decode_head(p, st);
         return;
     }

@@ -356,7 +356,8 @@ void Seq::launch_token_pass(bool from_prompt, int prompt_idx, int pos_value, boo
             a.n_head = hp.n_head; a.n_kv = hp.n_head_kv; a.hd = hp.head_dim; a.n_rot = hp.n_rot;
             a.n_split = m->attn_splits; a.n_ctx = hp.n_ctx;
             a.scale = 1.0f / sqrtf((float)hp.head_dim);
-            TIMED(1, launch_attn_decode(a, st));
+            const int amode = (m->eng->flags & AIOS_ENGINE_ATTN_CLUSTER) ? 2 : (m->eng->flags & AIOS_ENGINE_ATTN_HEAD) ? 1 : 0;
+            TIMED(1, launch_attn_decode(a, st, pdl, amode));
             launches++;
         }
         {   // attention output projection + residual add

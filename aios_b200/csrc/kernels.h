@@ -62,7 +62,11 @@ struct AttnParams {
     int32_t n_head, n_kv, hd, n_rot, n_split, n_ctx;
     float scale;
 };
-void launch_attn_decode(const AttnParams &p, cudaStream_t st);
+// mode: 0 = pick (split kernel when usable, else per-head, else cluster); 1 = per-head kernel; 2 = cluster kernel
+void launch_attn_decode(const AttnParams &p, cudaStream_t st, bool pdl = false, int mode = 0);
+// one wave of independent (query head, head-dim slice) CTAs, launched with PDL (attention_split.cu)
+bool attn_split_usable(int n_ctx, int hd);
+void launch_attn_decode_split(const AttnParams &p, cudaStream_t st, bool pdl);
 void attn_init();  // one-time function attributes (dynamic smem)
 // short contexts: one CTA per query head, no cross-CTA exchange (attention_head.cu)
 bool attn_head_usable(int n_ctx, int hd);

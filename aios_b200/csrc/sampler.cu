@@ -81,7 +81,9 @@ __global__ void __launch_bounds__(SAMP_THREADS) sample_kernel(const SampleParams
     if (threadIdx.x == 0) {
         int tok = key_index(top[0]);
         if (!greedy) {
-            const int step = *p.step_ptr;
+            // the random draw is a function of (seed, absolute position): the same whether the caller decodes in
+            // one call or in chunks
+            const int step = p.pos_ptr ? *p.pos_ptr : *p.step_ptr;
             // softmax over the k candidates (sorted descending), then top-p / min-p cut, then temperature
             const float mx = key_value(top[0]);
             float probs[SAMP_MAX_K];

@@ -62,6 +62,8 @@ typedef struct aios_engine_opts {
 #define AIOS_ENGINE_NO_PFD 4   /* greedy decode through per-op kernels instead of the persistent fused kernel */
 #define AIOS_ENGINE_USE_PFD 8  /* greedy decode through the persistent fused decode kernel (pfd.cu) */
 #define AIOS_ENGINE_L2_PREFETCH 16 /* GEMV launches prefetch the next launch's weights into L2 (experiment; slower so far) */
+#define AIOS_ENGINE_ATTN_HEAD 32    /* decode attention: one CTA per query head (attention_head.cu) instead of the split kernel */
+#define AIOS_ENGINE_ATTN_CLUSTER 64 /* decode attention: the cluster / DSMEM kernel (attention.cu) at every context length */
 
 int aios_engine_create(const aios_engine_opts *opts, aios_engine **out);
 void aios_engine_destroy(aios_engine *e);

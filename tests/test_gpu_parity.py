@@ -260,11 +260,16 @@ def test_fused_decode_kernel_matches_oracle_and_per_op_path(engine, engine_pfd, 
         m2.unload()
 
 
-def test_long_context_attention_path_matches_oracle(engine, oracle, tmp_models):
-    """n_ctx > 1024 selects the cluster/DSMEM attention kernel (attention.cu) instead of the one-CTA-per-head kernel
-    (attention_head.cu); both must give the oracle's logits bit for bit."""
+@pytest.mark.parametrize("attn", ["split", "head", "cluster"])
+def test_long_context_attention_path_matches_oracle(oracle, tmp_models, attn):
+    """The three decode-attention kernels — one wave of (head, dim-slice) CTAs (attention_split.cu, the default),
+    one CTA per query head (attention_head.cu, n_ctx <= 1024) and the cluster/DSMEM kernel (attention.cu) — must all
+    give the oracle's logits."""
+    from aios_b200 import capi
     path = tmp_models("tiny-gqa4", "Q4_K_M")
-    m = engine.load_model("t", path, n_ctx=1536)
+    flags = {"split": 0, "head": capi.ENGINE_ATTN_HEAD, "cluster": capi.ENGINE_ATTN_CLUSTER}[attn]
+    engine = capi.Engine(device=0, max_batch=1, flags=flags)
+    m = engine.load_model("t", path, n_ctx=1024 if attn == "head" else 1536)
     try:
         om = oracle.OracleModel(path, n_ctx=1536)
         prompt = gs.synthetic_prompt("tiny-gqa4", 40, 2)
@@ -275,8 +280,9 @@ def test_long_context_attention_path_matches_oracle(engine, oracle, tmp_models):
                 seq.prefill(prompt[i:i + 1])
                 if i % 5 == 4 or i == len(prompt) - 1:
                     got = seq.logits()
-                    assert np.abs(got - ref[i]).max() / ref[i].std() < LOGIT_TOL, i
+                    assert np.array_equal(got.view(np.uint32), ref[i].view(np.uint32)), i  # bit for bit
         finally:
             seq.free()
     finally:
         m.unload()
+        engine.close()
