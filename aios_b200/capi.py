@@ -24,6 +24,7 @@ ENGINE_USE_PFD = 8
 ENGINE_L2_PREFETCH = 16
 ENGINE_ATTN_HEAD = 32
 ENGINE_ATTN_CLUSTER = 64
+ENGINE_USE_RING = 128
 
 
 class AiosError(RuntimeError):
@@ -109,6 +110,7 @@ SYMBOLS = {
     "aios_seq_read_activation": (C.c_int, [_P, C.c_int32, _P, C.c_int64]),
     "aios_seq_bench_decode": (C.c_int, [_P, C.c_int32, C.POINTER(BenchResult)]),
     "aios_seq_profile_decode": (C.c_int, [_P, C.c_int32, C.POINTER(BenchResult)]),
+    "aios_seq_trace_decode": (C.c_int, [_P, _P, C.c_int32, C.POINTER(C.c_int32)]),
     "aios_seq_phase_timing": (C.c_int, [_P, _P, C.c_int32, C.POINTER(C.c_int32)]),
     "aios_seq_snapshot": (C.c_int, [_P]),
     "aios_seq_restore": (C.c_int, [_P]),
@@ -374,6 +376,13 @@ class Seq:
         r = BenchResult()
         _check(lib().aios_seq_profile_decode(self.h, n_tokens, C.byref(r)))
         return r
+
+    def trace_decode(self, cap: int = 4096) -> np.ndarray:
+        """[launch][8] u64 %globaltimer marks of one greedy token (see aios_seq_trace_decode)."""
+        out = np.zeros((cap, 8), dtype=np.uint64)
+        n = C.c_int32(0)
+        _check(lib().aios_seq_trace_decode(self.h, _ptr(out), cap, C.byref(n)))
+        return out[: n.value].copy()
 
     def phase_timing(self) -> np.ndarray:
         out = np.zeros((4096, 4), dtype=np.uint64)

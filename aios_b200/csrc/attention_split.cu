@@ -104,12 +104,32 @@ __global__ void __launch_bounds__(AS_THREADS, 2) attn_split_kernel(const AttnPar
     __shared__ float sh_f[AS_WARPS];
     __shared__ double sh_d[AS_WARPS];
 
+    unsigned long long *tr = (blockIdx.x == 0 && threadIdx.x == 0) ? p.trace : nullptr;
+    trace_mark(tr, 0);
     // the successor only prefetches weights until this grid has completed: let it start now
     asm volatile("griddepcontrol.launch_dependents;");
+
+    // Before the dependency wait: the cache rows of earlier tokens are final, so ask L2 for them now (they were
+    // last touched a whole token pass — 4 GB of weight traffic — ago and would otherwise come from DRAM in two to
+    // four dependent round trips).  The position counter read here may in principle be one token old; it is only
+    // used for this hint and re-read after the wait.
+    {
+        const int n_hint = *reinterpret_cast<const volatile int32_t *>(p.n_past_ptr);
+        if (h % rep == 0 && n_hint > 0 && n_hint < p.n_ctx) {
+            const size_t head_off = (size_t)g * HD;
+            for (int j = part_id * AS_THREADS + threadIdx.x; j < n_hint; j += SPLIT * AS_THREADS) {
+                const uint16_t *kr = p.k_cache + (size_t)j * kvd + head_off;
+                const uint16_t *vr = p.v_cache + (size_t)j * kvd + head_off;
+                asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(kr), "r"(HD * 2) : "memory");
+                asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(vr), "r"(HD * 2) : "memory");
+            }
+        }
+    }
     // qkv, the position counter and the cache rows of earlier tokens are all final once the predecessor is done
     asm volatile("griddepcontrol.wait;" ::: "memory");
+    trace_mark(tr, 1);
 
-    const int n_past = *p.n_past_ptr;
+    const int n_past = __ldcg(p.n_past_ptr);
     const int n_pos = n_past + 1;
     const float *cs = p.rope_cos + (size_t)n_past * (p.n_rot / 2);
     const float *sn = p.rope_sin + (size_t)n_past * (p.n_rot / 2);
@@ -219,6 +239,7 @@ __global__ void __launch_bounds__(AS_THREADS, 2) attn_split_kernel(const AttnPar
         }
     }
 
+    trace_mark(tr, 2);
     // ---- request the first V batch now: it does not depend on the scores
     const int vsub = lane / VL, vdl = part_id * DPC + (lane % VL) * 8;
     const uint16_t *vbase = p.v_cache + (size_t)g * HD + vdl;
@@ -287,6 +308,7 @@ __global__ void __launch_bounds__(AS_THREADS, 2) attn_split_kernel(const AttnPar
         for (int w = 0; w < AS_WARPS; w++) s += part[(size_t)w * DPC + d];
         p.out[(size_t)h * HD + part_id * DPC + d] = (float)s;
     }
+    trace_mark(tr, 4);
 }
 
 static size_t as_smem(int n_ctx, int hd, int split) {
@@ -295,6 +317,15 @@ static size_t as_smem(int n_ctx, int hd, int split) {
 }
 
 constexpr int AS_SPLIT = 4;
+
+void attn_split_init() {
+    static bool done = false;
+    if (done) return;
+    // same shared-memory carve-out as the ring GEMV it sits between (an SM cannot host two carve-outs at once)
+    CUDA_CHECK(cudaFuncSetAttribute(attn_split_kernel<128, AS_SPLIT>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    CUDA_CHECK(cudaFuncSetAttribute(attn_split_kernel<64, AS_SPLIT>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    done = true;
+}
 
 bool attn_split_usable(int n_ctx, int hd) {
     return (hd == 64 || hd == 128) && n_ctx <= 4096 && as_smem(n_ctx, hd, AS_SPLIT) <= 40 * 1024;

@@ -479,6 +479,15 @@ int aios_seq_profile_decode(aios_seq *s, int32_t n_tokens, aios_bench_result *ou
         return (int)AIOS_OK;
     });
 }
+int aios_seq_trace_decode(aios_seq *s, uint64_t *out, int32_t cap_launches, int32_t *n_launches) {
+    return guarded([&] {
+        if (!s || !out || !n_launches || cap_launches <= 0) return fail(AIOS_E_INVAL, "bad argument");
+        std::lock_guard<std::mutex> lk(s->impl.m->eng->mu);
+        *n_launches = s->impl.trace_decode(reinterpret_cast<unsigned long long *>(out), cap_launches);
+        return (int)AIOS_OK;
+    });
+}
+
 int aios_seq_phase_timing(aios_seq *s, uint64_t *out, int32_t cap, int32_t *n_phases) {
     return guarded([&] {
         if (!s || !out || !n_phases) return fail(AIOS_E_INVAL, "bad argument");

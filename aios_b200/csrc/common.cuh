@@ -81,6 +81,14 @@ __device__ __forceinline__ float expf_det(float x) {
     return __fmul_rn(p, __int_as_float((ni + 127) << 23));
 }
 
+// launch timeline (aios_seq_trace): 8 u64 per launch, nanoseconds of %globaltimer, written by CTA 0 only
+__device__ __forceinline__ void trace_mark(unsigned long long *trace, int slot) {
+    if (trace) {
+        unsigned long long t;
+        asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+        trace[slot] = t;
+    }
+}
 __device__ __forceinline__ float h2f_bits(uint16_t h) { return __half2float(__ushort_as_half(h)); }
 __device__ __forceinline__ uint16_t f2h_bits(float f) { return __half_as_ushort(__float2half_rn(f)); }
 

@@ -50,6 +50,8 @@ Engine::Engine(const aios_engine_opts &o) : device(o.device), max_batch(o.max_ba
     n_sms = prop.multiProcessorCount;
     CUDA_CHECK(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
     gemv_init();
+    gemv_ring_init();
+    attn_split_init();
     attn_init();
     attn_head_init();
 }
@@ -101,6 +103,15 @@ void Model::upload_matrix(const GgufTensor &t, DevMatrix &dst, DevBuf &staging, 
     weight_bytes_per_token += (int64_t)t.nbytes;
 }
 
+// stream tiles for the TMA-ring GEMV: a second copy of the matrix bytes, cut into bulk-copy blobs (layout.cuh)
+void Model::build_tiles(DevMatrix &m) {
+    if (!ring || tile_bytes(m.w.type) == 0) return;
+    m.tile_storage = DevBuf(tiles_total_bytes(m.w.type, m.w.n_rows, m.w.k, false));
+    launch_build_tiles(m.w, nullptr, m.tile_storage.as<uint8_t>(), &m.t, eng->stream);
+    CUDA_CHECK(cudaStreamSynchronize(eng->stream));
+    weight_bytes += (int64_t)m.tile_storage.bytes;
+}
+
 static DevBuf upload_f32(const GgufTensor &t, int64_t expect, cudaStream_t st) {
     if (t.type != T_F32 || t.ne[0] != expect)
         throw GgufError(AIOS_E_FORMAT, "tensor '" + t.name + "' must be F32[" + std::to_string(expect) + "]");
@@ -140,6 +151,9 @@ Model::Model(Engine *e, const std::string &name_, const std::string &path_, int 
     hp.n_vocab = (int)te.ne[1];
     if (te.ne[0] != hp.n_embd) throw GgufError(AIOS_E_FORMAT, "token_embd.weight has the wrong width");
 
+    // opt-in: correct (bit-identical results) but 2.41 vs 1.92 ms/token — its 8 consumer warps per SM process a tile
+    // in ~0.55 us where HBM delivers one in 0.42 (profiles/r01_v4_ring.md)
+    ring = (e->flags & AIOS_ENGINE_USE_RING) != 0;
     cudaStream_t st = e->stream;
     const size_t pinned_bytes = 64u << 20;
     void *pinned = nullptr;
@@ -180,11 +194,21 @@ Model::Model(Engine *e, const std::string &name_, const std::string &path_, int 
             }
             if (L.w_gate.w.type != L.w_up.w.type)
                 throw GgufError(AIOS_E_FORMAT, "ffn_gate and ffn_up of layer " + std::to_string(i) + " differ in type");
+            if (ring) {
+                for (DevMatrix *dm : {&L.wq, &L.wk, &L.wv, &L.wo, &L.w_down}) build_tiles(*dm);
+                if (tile_bytes(L.w_gate.w.type)) {
+                    L.gate_up_storage = DevBuf(tiles_total_bytes(L.w_gate.w.type, L.w_gate.w.n_rows, L.w_gate.w.k, true));
+                    launch_build_tiles(L.w_gate.w, &L.w_up.w, L.gate_up_storage.as<uint8_t>(), &L.gate_up, st);
+                    CUDA_CHECK(cudaStreamSynchronize(st));
+                    weight_bytes += (int64_t)L.gate_up_storage.bytes;
+                }
+            }
         }
         output_norm = upload_f32(f.require("output_norm.weight"), hp.n_embd, st);
         weight_bytes_per_token += (int64_t)hp.n_embd * 4;
         const GgufTensor *out = f.find("output.weight");
         upload_matrix(out ? *out : te, output, staging, pinned, pinned_bytes);  // tied embeddings when absent
+        build_tiles(output);
     } catch (...) {
         cudaFreeHost(pinned);
         throw;
@@ -323,8 +347,30 @@ void Seq::launch_token_pass(bool from_prompt, int prompt_idx, int pos_value, boo
                      from_prompt ? &sd->pos : nullptr, pos_value, from_prompt ? &sd->cur_token : nullptr, st));
     launches++;
     const int QD = hp.n_head * hp.head_dim, KVD = hp.n_head_kv * hp.head_dim;
+    // TMA-ring GEMV (gemv_ring.cu) when every matrix of the launch has stream tiles; false -> caller takes gemv.cu
+    auto ring_launch = [&](std::initializer_list<const WTiles *> segs, std::initializer_list<float *> outs, int epi, int k,
+                           const float *xin, const float *norm, unsigned long long *amax, bool use_pdl) -> bool {
+        if (!m->ring) return false;
+        RingParams r{};
+        r.n_seg = (int)segs.size(); r.epi = epi; r.k = k;
+        int i = 0;
+        for (const WTiles *w : segs) {
+            if (!w->base) return false;
+            r.seg[i++] = *w;
+        }
+        i = 0;
+        for (float *o : outs) r.out[i++] = o;
+        r.x = xin; r.norm_w = norm; r.eps = hp.rms_eps; r.argmax_key = amax;
+        r.trace = trace_base && launches < 4096 ? trace_base + (size_t)launches * 8 : nullptr;
+        if (!gemv_ring_usable(r)) return false;
+        TIMED(0, launch_gemv_ring(r, n_sms, st, use_pdl));
+        launches++;
+        return true;
+    };
     for (int il = 0; il < hp.n_layer; il++) {
         const Layer &L = m->layers[il];
+        if (!ring_launch({&L.wq.t, &L.wk.t, &L.wv.t}, {qkv.as<float>(), qkv.as<float>() + QD, qkv.as<float>() + QD + KVD},
+                         EPI_STORE, hp.n_embd, x.as<float>(), L.attn_norm.as<float>(), nullptr, pdl))
         {   // RMSNorm + Q,K,V projections: one launch when the three matrices share a type (else q,k + v)
             GemvParams p{};
             const bool same = L.wv.w.type == L.wq.w.type;
@@ -356,10 +402,12 @@ void Seq::launch_token_pass(bool from_prompt, int prompt_idx, int pos_value, boo
             a.n_head = hp.n_head; a.n_kv = hp.n_head_kv; a.hd = hp.head_dim; a.n_rot = hp.n_rot;
             a.n_split = m->attn_splits; a.n_ctx = hp.n_ctx;
             a.scale = 1.0f / sqrtf((float)hp.head_dim);
+            a.trace = trace_base && launches < 4096 ? trace_base + (size_t)launches * 8 : nullptr;
             const int amode = (m->eng->flags & AIOS_ENGINE_ATTN_CLUSTER) ? 2 : (m->eng->flags & AIOS_ENGINE_ATTN_HEAD) ? 1 : 0;
             TIMED(1, launch_attn_decode(a, st, pdl, amode));
             launches++;
         }
+        if (!ring_launch({&L.wo.t}, {x.as<float>()}, EPI_ADD, QD, att.as<float>(), nullptr, nullptr, pdl))
         {   // attention output projection + residual add
             GemvParams p{};
             p.n_seg = 1; p.epi = EPI_ADD; p.k = QD;
@@ -368,6 +416,7 @@ void Seq::launch_token_pass(bool from_prompt, int prompt_idx, int pos_value, boo
             TIMED(0, launch_gemv(p, gemv_plan_grid(p, n_sms), st, pdl));
             launches++;
         }
+        if (!ring_launch({&L.gate_up}, {h.as<float>()}, EPI_SWIGLU, hp.n_embd, x.as<float>(), L.ffn_norm.as<float>(), nullptr, pdl))
         {   // RMSNorm + gate/up + SwiGLU
             GemvParams p{};
             p.n_seg = 2; p.epi = EPI_SWIGLU; p.k = hp.n_embd;
@@ -377,6 +426,7 @@ void Seq::launch_token_pass(bool from_prompt, int prompt_idx, int pos_value, boo
             TIMED(0, launch_gemv(p, gemv_plan_grid(p, n_sms), st, pdl));
             launches++;
         }
+        if (!ring_launch({&L.w_down.t}, {x.as<float>()}, EPI_ADD, hp.n_ff, h.as<float>(), nullptr, nullptr, pdl))
         {   // down projection + residual add
             GemvParams p{};
             p.n_seg = 1; p.epi = EPI_ADD; p.k = hp.n_ff;
@@ -388,15 +438,18 @@ void Seq::launch_token_pass(bool from_prompt, int prompt_idx, int pos_value, boo
         }
     }
     if (want_logits) {
-        GemvParams p{};
-        p.n_seg = 1; p.epi = EPI_STORE; p.k = hp.n_embd;
-        p.seg[0] = m->output.w; p.out[0] = logits.as<float>();
-        p.x = x.as<float>(); p.norm_w = m->output_norm.as<float>(); p.eps = hp.rms_eps;
         // the lm_head epilogue keeps the packed (value, index) arg-max of the logits it writes
         CUDA_CHECK(cudaMemsetAsync(&sd->argmax_key, 0, sizeof(unsigned long long), st));
-        p.argmax_key = &sd->argmax_key;
-        TIMED(0, launch_gemv(p, gemv_plan_grid(p, n_sms), st, false));
-        launches++;
+        if (!ring_launch({&m->output.t}, {logits.as<float>()}, EPI_STORE, hp.n_embd, x.as<float>(),
+                         m->output_norm.as<float>(), &sd->argmax_key, false)) {
+            GemvParams p{};
+            p.n_seg = 1; p.epi = EPI_STORE; p.k = hp.n_embd;
+            p.seg[0] = m->output.w; p.out[0] = logits.as<float>();
+            p.x = x.as<float>(); p.norm_w = m->output_norm.as<float>(); p.eps = hp.rms_eps;
+            p.argmax_key = &sd->argmax_key;
+            TIMED(0, launch_gemv(p, gemv_plan_grid(p, n_sms), st, false));
+            launches++;
+        }
     }
     if (n_launch) *n_launch += launches;
 }
@@ -565,6 +618,38 @@ void Seq::profile_decode(int n_tokens, aios_bench_result *out) {
     out->reserved[1] = ms_kind[2];
     out->reserved[2] = (float)n_gemv;
     n_past += steps;
+}
+
+// Two greedy tokens launched kernel by kernel on the stream (PDL attributes as in the graph); during the second one
+// CTA 0 of every ring-GEMV / split-attention launch writes its %globaltimer marks (kernels.h) into `trace`.
+int Seq::trace_decode(unsigned long long *out, int cap_launches) {
+    if (!have_logits) throw std::runtime_error("trace_decode needs a prefilled sequence");
+    if (m->hp.n_ctx - n_past < 2) throw std::runtime_error("context is full");
+    m->eng->make_current();
+    cudaStream_t st = m->eng->stream;
+    aios_sampling sp{};
+    int32_t hdr[2] = {n_past - 1, 0};
+    CUDA_CHECK(cudaMemcpyAsync(state.p, hdr, sizeof(hdr), cudaMemcpyHostToDevice, st));
+    const size_t cap = 4096;
+    if (trace.bytes < cap * 8 * sizeof(unsigned long long)) trace = DevBuf(cap * 8 * sizeof(unsigned long long));
+    CUDA_CHECK(cudaMemsetAsync(trace.p, 0, trace.bytes, st));
+    int launches = 0;
+    launch_sample_kernel(sp, st);
+    launch_token_pass(false, 0, 0, true, st, nullptr);
+    launch_sample_kernel(sp, st);
+    trace_base = trace.as<unsigned long long>();
+    try {
+        launch_token_pass(false, 0, 0, true, st, &launches);
+        CUDA_CHECK(cudaStreamSynchronize(st));
+    } catch (...) {
+        trace_base = nullptr;
+        throw;
+    }
+    trace_base = nullptr;
+    n_past += 2;
+    const int n = std::min(launches, cap_launches);
+    CUDA_CHECK(cudaMemcpy(out, trace.p, (size_t)n * 8 * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+    return n;
 }
 
 void Seq::snapshot() {

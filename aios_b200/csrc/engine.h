@@ -49,10 +49,14 @@ struct DevMatrix {
     WPlanes w{};      // planes layout (layout.cuh)
     DevBuf storage;   // one allocation holding all planes
     size_t src_bytes = 0;
+    WTiles t{};       // stream tiles for the TMA-ring GEMV (layout.cuh); t.base == nullptr when not built
+    DevBuf tile_storage;
 };
 
 struct Layer {
     DevMatrix wq, wk, wv, wo, w_gate, w_up, w_down;
+    WTiles gate_up{};            // PAIR tiles of (ffn_gate, ffn_up)
+    DevBuf gate_up_storage;
     DevBuf attn_norm, ffn_norm;  // f32
 };
 
@@ -88,8 +92,11 @@ struct Model {
     uint16_t *v_cache(int slot, int layer) const;
     size_t kv_layer_elems() const { return (size_t)hp.n_ctx * hp.n_head_kv * hp.head_dim; }
 
+    bool ring = false;    // stream tiles were built: token passes use the TMA-ring GEMV (gemv_ring.cu)
+
    private:
     void upload_matrix(const GgufTensor &t, DevMatrix &dst, DevBuf &staging, void *pinned, size_t pinned_bytes);
+    void build_tiles(DevMatrix &m);
 };
 
 struct SeqState {  // lives in device memory
@@ -108,6 +115,8 @@ struct Seq {
     DevBuf state, x, qkv, att, h, logits, out_tokens, prompt, attn_scratch, attn_counters, snap_logits;
     int snap_n_past = -1;
     struct KernelTimer *timer = nullptr;  // non-null only inside profile_decode
+    DevBuf trace;
+    unsigned long long *trace_base = nullptr;  // non-null only inside trace_decode
     cudaGraphExec_t graph = nullptr;
     aios_sampling graph_sampling{};
     int kernels_per_step = 0;
@@ -125,6 +134,7 @@ struct Seq {
     int decode_static(int max_tokens, int32_t *out);  // fused kernel on the library's built-in scratch: no allocation
     void bench_decode(int n_tokens, aios_bench_result *out);
     void profile_decode(int n_tokens, aios_bench_result *out);
+    int trace_decode(unsigned long long *out, int cap_launches);  // per-launch timeline of one token (kernels.h marks)
     void snapshot();
     void restore();
     void read_logits(float *out);

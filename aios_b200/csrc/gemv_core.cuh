@@ -13,6 +13,11 @@ namespace aios {
 #ifndef GEMV_CORE_WARPS
 #error "define GEMV_CORE_WARPS (warps per CTA taking part in the activation prologue) before including gemv_core.cuh"
 #endif
+// barrier over the GEMV_WARPS warps that take part in the activation prologue: the whole CTA by default; a kernel
+// with extra (producer) warps overrides it with a named barrier
+#ifndef GEMV_CORE_SYNC
+#define GEMV_CORE_SYNC() __syncthreads()
+#endif
 constexpr int GEMV_WARPS = GEMV_CORE_WARPS;
 constexpr int GEMV_THREADS = GEMV_WARPS * 32;
 constexpr int GEMV_R = 2;  // rows per warp per pass
@@ -44,11 +49,11 @@ __device__ __forceinline__ double block_sum(double v, double *red) {
     v = warp_sum_f64(v);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     if (lane == 0) red[warp] = v;
-    __syncthreads();
+    GEMV_CORE_SYNC();
     double t = 0.0;
 #pragma unroll
     for (int i = 0; i < GEMV_WARPS; i++) t += red[i];
-    __syncthreads();
+    GEMV_CORE_SYNC();
     return t;
 }
 
@@ -84,24 +89,23 @@ __device__ __forceinline__ void quant_slab(const float (&v)[8], int b, int k, co
         return;
     }
     // amax with ggml's "first element whose |x| is strictly larger" rule
-    float am = 0.f;
+    // (the signed value travels with its index through the reduction: selecting v[idx & 7] afterwards makes the
+    // compiler spill v[] to local memory for an indexed load)
+    float mv = 0.f;
     int ai = 0;
 #pragma unroll
     for (int i = 0; i < 8; i++) {
-        const float ax = fabsf(v[i]);
-        if (ax > am) { am = ax; ai = i; }
+        if (fabsf(v[i]) > fabsf(mv)) { mv = v[i]; ai = i; }
     }
     int idx = lane * 8 + ai;
 #pragma unroll
     for (int o = 16; o > 0; o >>= 1) {
-        const float am2 = __shfl_xor_sync(0xffffffffu, am, o);
+        const float mv2 = __shfl_xor_sync(0xffffffffu, mv, o);
         const int idx2 = __shfl_xor_sync(0xffffffffu, idx, o);
-        if (am2 > am || (am2 == am && idx2 < idx)) { am = am2; idx = idx2; }
+        const float a = fabsf(mv), a2 = fabsf(mv2);
+        if (a2 > a || (a2 == a && idx2 < idx)) { mv = mv2; idx = idx2; }
     }
-    float cand = 0.f;
-#pragma unroll
-    for (int i = 0; i < 8; i++) if (i == (idx & 7)) cand = v[i];
-    const float mv = __shfl_sync(0xffffffffu, cand, idx >> 3);
+    const float am = fabsf(mv);
     float d = 0.f;
     if (am == 0.f) {
 #pragma unroll
@@ -197,7 +201,60 @@ __device__ void prep_activations(const float *__restrict__ x, const float *__res
             if (b1 < nslab) quant_slab<PERM>(v1, b1, k, s);
         }
     }
-    __syncthreads();
+    GEMV_CORE_SYNC();
+}
+
+// The norm weights are weights: a kernel can fetch them BEFORE its dependency wait (K <= 4096: 16 per lane) ...
+__device__ __forceinline__ void preload_norm(const float *__restrict__ norm_w, int k, float (&nw0)[8], float (&nw1)[8]) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int nslab = k / 256;
+    if (norm_w && nslab <= 2 * GEMV_WARPS) {
+        if (warp < nslab) load8(norm_w + warp * 256 + lane * 8, nw0);
+        if (warp + GEMV_WARPS < nslab) load8(norm_w + (warp + GEMV_WARPS) * 256 + lane * 8, nw1);
+    }
+}
+
+// ... and hand them to this variant of prep_activations.  Same values; two differences in latency: no trip to L2 for
+// the norm weights after the wait, and for a big un-normed K (ffn_down) four slabs of x in flight per lane, not two.
+template <int PERM>
+__device__ void prep_activations_pre(const float *__restrict__ x, const float *__restrict__ norm_w, float eps, int k,
+                                     const ActSmem &s, double *red, const float (&nw0)[8], const float (&nw1)[8]) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int nslab = k / 256;
+    if (nslab <= 2 * GEMV_WARPS) {
+        const int b0 = warp, b1 = warp + GEMV_WARPS;
+        float v0[8], v1[8];
+#pragma unroll
+        for (int i = 0; i < 8; i++) v0[i] = v1[i] = 0.f;
+        if (b0 < nslab) load8(x + b0 * 256 + lane * 8, v0);
+        if (b1 < nslab) load8(x + b1 * 256 + lane * 8, v1);
+        if (norm_w) {
+            const double ss = block_sum(sumsq8(v0) + sumsq8(v1), red);
+            const float mean = (float)(ss / (double)k);
+            const float scale = __fdiv_rn(1.0f, __fsqrt_rn(__fadd_rn(mean, eps)));
+#pragma unroll
+            for (int i = 0; i < 8; i++) {
+                v0[i] = __fmul_rn(__fmul_rn(v0[i], scale), nw0[i]);
+                v1[i] = __fmul_rn(__fmul_rn(v1[i], scale), nw1[i]);
+            }
+        }
+        if (b0 < nslab) quant_slab<PERM>(v0, b0, k, s);
+        if (b1 < nslab) quant_slab<PERM>(v1, b1, k, s);
+        GEMV_CORE_SYNC();
+    } else if (norm_w) {
+        prep_activations<PERM>(x, norm_w, eps, k, s, red);
+    } else {
+        for (int b = warp; b < nslab; b += 4 * GEMV_WARPS) {
+            float v[4][8];
+#pragma unroll
+            for (int j = 0; j < 4; j++)
+                if (b + j * GEMV_WARPS < nslab) load8(x + (b + j * GEMV_WARPS) * 256 + lane * 8, v[j]);
+#pragma unroll
+            for (int j = 0; j < 4; j++)
+                if (b + j * GEMV_WARPS < nslab) quant_slab<PERM>(v[j], b + j * GEMV_WARPS, k, s);
+        }
+        GEMV_CORE_SYNC();
+    }
 }
 
 // ---------------------------------------------------------------- weight registers of one pass

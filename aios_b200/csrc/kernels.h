@@ -48,6 +48,31 @@ bool gemv_staged_usable(const GemvParams &p, int n_sms);
 void launch_gemv_staged(const GemvParams &p, int n_sms, cudaStream_t st, bool pdl);
 void gemv_staged_init();
 
+// ---- gemv_ring.cu : the same fused op fed by a TMA ring (stream tiles of layout.cuh)
+// build the tiles of a [N][K] matrix (b == nullptr) or the PAIR tiles of two matrices from their planes
+size_t tiles_total_bytes(int type, int n_rows, int k, bool pair);
+void launch_build_tiles(const WPlanes &a, const WPlanes *b, uint8_t *dst, WTiles *out, cudaStream_t st);
+struct RingParams {
+    int32_t n_seg;          // 1..3 tile streams sharing the same input vector
+    int32_t epi;            // GemvEpilogue; EPI_SWIGLU wants one PAIR stream
+    int32_t k;
+    int32_t ct;             // K tiles per row tile (same for all segments)
+    int32_t rt_begin[4];    // row-tile ranges per segment
+    WTiles seg[3];
+    float *out[3];
+    const float *x;
+    const float *norm_w;
+    float eps;
+    unsigned long long *argmax_key;
+    int32_t n_slots, slot_bytes;  // shared-memory ring geometry (host-chosen)
+    // timeline of CTA 0 (null = off): [0] entry [1] dependency wait over [2] activations ready [3] first tile landed
+    // [4] consumers done [5] producer's first copy issued [6] producer's last copy issued
+    unsigned long long *trace;
+};
+bool gemv_ring_usable(const RingParams &p);
+void launch_gemv_ring(RingParams &p, int n_sms, cudaStream_t st, bool pdl);
+void gemv_ring_init();
+
 // ---- attention.cu : RoPE + KV write + flash-decode over the f16 KV cache (one new token)
 struct AttnParams {
     const float *qkv;        // [n_head*hd + 2*n_kv*hd] raw projections of the new token
@@ -61,11 +86,13 @@ struct AttnParams {
     uint32_t *counters;      // [n_kv] arrival counters (zero on entry, zero on exit)
     int32_t n_head, n_kv, hd, n_rot, n_split, n_ctx;
     float scale;
+    unsigned long long *trace;  // split kernel, CTA 0 (null = off): [0] entry [1] wait over [2] scores done [4] end
 };
 // mode: 0 = pick (split kernel when usable, else per-head, else cluster); 1 = per-head kernel; 2 = cluster kernel
 void launch_attn_decode(const AttnParams &p, cudaStream_t st, bool pdl = false, int mode = 0);
 // one wave of independent (query head, head-dim slice) CTAs, launched with PDL (attention_split.cu)
 bool attn_split_usable(int n_ctx, int hd);
+void attn_split_init();
 void launch_attn_decode_split(const AttnParams &p, cudaStream_t st, bool pdl);
 void attn_init();  // one-time function attributes (dynamic smem)
 // short contexts: one CTA per query head, no cross-CTA exchange (attention_head.cu)

@@ -64,6 +64,8 @@ typedef struct aios_engine_opts {
 #define AIOS_ENGINE_L2_PREFETCH 16 /* GEMV launches prefetch the next launch's weights into L2 (experiment; slower so far) */
 #define AIOS_ENGINE_ATTN_HEAD 32    /* decode attention: one CTA per query head (attention_head.cu) instead of the split kernel */
 #define AIOS_ENGINE_ATTN_CLUSTER 64 /* decode attention: the cluster / DSMEM kernel (attention.cu) at every context length */
+#define AIOS_ENGINE_USE_RING 128    /* GEMV through the TMA-ring kernel (gemv_ring.cu): a second, tile-ordered copy of the
+                                       Q4_K/Q6_K weights is built at load; experiment, slower than gemv.cu so far */
 
 int aios_engine_create(const aios_engine_opts *opts, aios_engine **out);
 void aios_engine_destroy(aios_engine *e);
@@ -239,6 +241,12 @@ int aios_seq_bench_decode(aios_seq *s, int32_t n_tokens, aios_bench_result *out)
  * ms_gemv (sum of the dequant+GEMV launches), reserved[0] = ms in attention launches,
  * reserved[1] = ms in the remaining launches, reserved[2] = number of GEMV launches. */
 int aios_seq_profile_decode(aios_seq *s, int32_t n_tokens, aios_bench_result *out);
+/* Launch timeline of one greedy token: two tokens are decoded kernel by kernel on the engine's stream (same
+ * programmatic-dependent-launch attributes as in the captured graph); during the second one, CTA 0 of every TMA-ring
+ * GEMV / split-attention launch records %globaltimer nanoseconds.  out[launch][8]: [0] kernel entry, [1] dependency
+ * wait over, [2] activations ready (GEMV) / scores done (attention), [3] first weight tile landed, [4] CTA done,
+ * [5] first / [6] last bulk copy issued by the producer warp; zeros for launches of other kernels. */
+int aios_seq_trace_decode(aios_seq *s, uint64_t *out, int32_t cap_launches, int32_t *n_launches);
 /* per-phase time stamps (ns) that CTA 0 of the persistent fused decode kernel took for the last token of the last
  * fused launch: out[n_phases][4] = phase start, after the activation prologue, after the compute loop, after the grid
  * barrier.  *n_phases returns the phase count; cap = capacity of out in phases. */
