@@ -5,17 +5,19 @@
 // the HBM peak but pays ~6 us per launch in which HBM idles — the dependency wait on the previous kernel, the
 // activation prologue (RMSNorm + Q8 quantisation), the tail.  145 launches per token make that 0.9 of 1.4 ms.  The
 // weights do not depend on any of it.  So here:
-//   * one CTA per SM, sized to HALF an SM (9 warps x <=112 registers, <=~100 KB shared memory), so that the CTA of
+//   * one CTA per SM, sized to HALF an SM (8 warps x <=128 registers, <=100 KB shared memory), so that the CTA of
 //     the NEXT launch is co-resident with the current one (programmatic dependent launch, triggered at kernel entry);
-//   * a producer warp walks the CTA's static list of weight tiles (layout.cuh "stream tiles": one contiguous blob
-//     per 16 rows x 2048 weights) and issues one cp.async.bulk per tile into a ring of shared-memory slots guarded by
-//     full/empty mbarriers.  It never waits for the previous kernel — only for a free slot.  While the previous
-//     kernel finishes, while this kernel waits for it and quantises its activations, HBM keeps streaming: up to
-//     ~80-90 KB per SM (12-13 MB per GPU) are already on chip when the consumers start;
-//   * 8 consumer warps wait for the dependency, build the activation image (gemv_core.cuh, same code as gemv.cu),
-//     then take slot after slot: warp w owns tile rows w and w+8 for the whole K, so the only reduction is the
-//     warp-level one; the unit arithmetic is gemv_core.cuh's compute_pass on registers loaded from the slot.
+//   * the CTA's list of weight tiles is static (layout.cuh "stream tiles": one contiguous blob per 16 rows x 2048
+//     weights).  Thread 0 issues one cp.async.bulk per ring slot at kernel entry — before the dependency wait — and
+//     from then on the LAST warp to copy its rows out of a slot re-arms it with the tile S ahead (shared-memory
+//     counter + full mbarrier per slot): no producer warp, no waiting.  While the previous kernel finishes, while
+//     this kernel waits for it and quantises its activations, 80-92 KB per SM (12-13 MB per GPU) are already on chip;
+//   * the 8 warps wait for the dependency, build the activation image (gemv_core.cuh, same arithmetic as gemv.cu),
+//     then take the slots two at a time: warp w owns tile rows w and w+8 for the whole K, so the only reduction is
+//     the warp-level one; the unit arithmetic is gemv_core.cuh's compute_pass on registers loaded from the slot.
 // Numerics are those of gemv.cu (bit-identical results: one f32 term per 64-weight unit, summed in double).
+// Status: correct, but slower than gemv.cu (2.41 vs 1.92 ms/token) — the consumers, not the ring, are the limit
+// (profiles/r01_v4_ring.md) — so the engine uses it only with AIOS_ENGINE_USE_RING.
 //
 // Q4_K and Q6_K streams (the Q4_K_M mix); a launch may mix both types (attn_q/k Q4_K + attn_v Q6_K).
 #define GEMV_CORE_WARPS 8
