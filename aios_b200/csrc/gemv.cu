@@ -116,6 +116,122 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) gemv_kernel(const GemvParams 
     l2_prefetch_next(p);
 }
 
+// ---------------------------------------------------------------- double-buffered variant
+// Same work split, prologue, arithmetic and epilogues as gemv_kernel; the difference is the weight pipeline inside a
+// warp.  gemv_kernel loads a pass (2 rows x 2 units per lane, 12 loads), waits for it, computes it, loads the next:
+// while a warp computes, none of its loads are in flight.  Here a pass is half as big (2 rows x 1 unit, 6 loads) and
+// there are two register images: compute(A), refill A, compute(B), refill B — so every warp always has 6-12 loads in
+// flight, through its own arithmetic as well.  Same register budget (2 x 24 instead of 1 x 48 weight registers).
+// K must be a whole number of passes (K % 2048 == 0); launch_gemv falls back to gemv_kernel otherwise.
+template <int TYPE>
+struct PassRegs1 {
+    static constexpr int ITS = TYPE == T_Q8_0 ? 2 : 1;
+    uint4 a[GEMV_R][ITS], b[GEMV_R][ITS], c[GEMV_R][ITS];
+    uint32_t e[GEMV_R][ITS], f[GEMV_R][ITS];
+};
+
+template <int TYPE, int NB>
+__global__ void __launch_bounds__(GEMV_THREADS, 2) gemv_db_kernel(const GemvParams p) {
+    extern __shared__ __align__(16) uint8_t smem[];
+    __shared__ double red[GEMV_WARPS];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    constexpr int UNIT = TYPE == T_Q8_0 ? 32 : 64;
+    using Regs = PassRegs1<TYPE>;
+    constexpr int PU = Regs::ITS * 32;
+    int seg = 0;
+    if (p.epi != EPI_SWIGLU) {
+        while (seg + 1 < p.n_seg && (int)blockIdx.x >= p.cta_begin[seg + 1]) seg++;
+    }
+    const WPlanes &W = p.seg[seg];
+    const WPlanes &W1 = p.seg[p.epi == EPI_SWIGLU ? 1 : seg];
+    const int cta_local = (int)blockIdx.x - p.cta_begin[seg];
+    const int cta_count = p.cta_begin[seg + 1] - p.cta_begin[seg];
+    const ActSmem s = carve(smem, p.k);
+    const int N = W.n_rows;
+    const int nu = p.k / UNIT;
+    const bool pair = p.epi == EPI_SWIGLU;
+    const int rows_per_pass = pair ? 1 : GEMV_R;
+    const int row_first = (cta_local * GEMV_WARPS + warp) * rows_per_pass;
+    const int row_step = cta_count * GEMV_WARPS * rows_per_pass;
+
+    auto ptrs = [&](int row0, RowPtrs (&rp)[GEMV_R]) {
+        if (pair) {
+            rp[0] = row_ptrs<TYPE>(W, row0);
+            rp[1] = row_ptrs<TYPE>(W1, row0);
+        } else {
+            rp[0] = row_ptrs<TYPE>(W, row0);
+            rp[1] = row_ptrs<TYPE>(W, min(row0 + 1, N - 1));
+        }
+    };
+
+    // load cursor: the pass that will be requested next
+    int lrow = row_first, lu = 0;
+    RowPtrs lrp[GEMV_R];
+    if (lrow < N) ptrs(lrow, lrp);
+    auto load_next = [&](Regs &g) {
+        if (lrow < N) {
+            load_pass<TYPE, true>(g, lrp, lu, nu);
+            lu += PU;
+            if (lu >= nu) {
+                lu = 0;
+                lrow += row_step;
+                if (lrow < N) ptrs(lrow, lrp);
+            }
+        }
+    };
+    Regs g[NB];
+#pragma unroll
+    for (int b = 0; b < NB; b++) load_next(g[b]);  // all images are requested before the dependency wait
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+
+    if (TYPE == T_Q6_K) prep_activations<PERM_Q6>(p.x, p.norm_w, p.eps, p.k, s, red);
+    else if (TYPE == T_Q8_0) prep_activations<PERM_Q80>(p.x, p.norm_w, p.eps, p.k, s, red);
+    else prep_activations<PERM_Q4>(p.x, p.norm_w, p.eps, p.k, s, red);
+    asm volatile("griddepcontrol.launch_dependents;");
+
+    float *out = p.out[seg];
+    unsigned long long best = 0ull;
+    int crow = row_first, cu = 0;  // compute cursor
+    double acc[GEMV_R] = {0.0, 0.0};
+    auto step = [&](Regs &g) {
+        compute_pass<TYPE, true>(g, cu, nu, p.k, s, acc);
+        load_next(g);  // refill this image; the loads fly while the other image is computed
+        cu += PU;
+        if (cu >= nu) {
+            const double tot = warp_sum2_f64(acc[0], acc[1]);  // lanes 0-15: row 0, lanes 16-31: row 1
+            if (pair) {
+                const float gte = (float)__shfl_sync(0xffffffffu, tot, 0), up = (float)__shfl_sync(0xffffffffu, tot, 16);
+                if (lane == 0) out[crow] = __fmul_rn(__fdiv_rn(gte, __fadd_rn(1.0f, expf_det(-gte))), up);
+            } else if ((lane & 15) == 0) {
+                const int row = crow + (lane >> 4);
+                if (row < N) {
+                    const float v = (float)tot;
+                    if (p.epi == EPI_ADD) out[row] = __fadd_rn(out[row], v);
+                    else out[row] = v;
+                    if (p.argmax_key) {
+                        const unsigned long long key = argmax_key(v, row);
+                        best = key > best ? key : best;
+                    }
+                }
+            }
+            acc[0] = acc[1] = 0.0;
+            cu = 0;
+            crow += row_step;
+        }
+    };
+    while (crow < N) {
+#pragma unroll
+        for (int b = 0; b < NB; b++) {
+            if (crow < N) step(g[b]);
+        }
+    }
+    if (p.argmax_key) {
+        const unsigned long long other = __shfl_sync(0xffffffffu, best, 16);
+        best = other > best ? other : best;
+        if (lane == 0 && best) atomicMax(p.argmax_key, best);
+    }
+}
+
 size_t gemv_smem_bytes(int k) { return act_image_bytes(k); }
 
 static size_t seg_row_bytes(const WPlanes &w) { return tensor_bytes(w.type, 1, w.k); }
@@ -153,6 +269,9 @@ int gemv_plan_grid(GemvParams &p, int n_sms) {
 }
 
 static int g_n_sms = 148;
+// N-buffered register pipeline (gemv_db_kernel): 2 = default (1.92 -> 1.79 ms/token), 3 spills (2.01), 0 = gemv_kernel.
+// AIOS_GEMV_DB=0/2/3 overrides for A/B runs.
+static int g_use_db = 2;
 static bool g_use_staged = false;  // measured slower than the register pipeline so far (profiles/r01_v3_gemv.md)
 void gemv_set_staged(bool on) { g_use_staged = on; }
 
@@ -169,6 +288,13 @@ void gemv_init() {
     CUDA_CHECK(cudaFuncSetAttribute(gemv_kernel<T_Q5_K>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
     CUDA_CHECK(cudaFuncSetAttribute(gemv_kernel<T_Q6_K>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
     CUDA_CHECK(cudaFuncSetAttribute(gemv_kernel<T_Q8_0>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    auto prep = [](auto kern) {
+        CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+        CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    };
+    prep(gemv_db_kernel<T_Q4_K, 2>); prep(gemv_db_kernel<T_Q5_K, 2>); prep(gemv_db_kernel<T_Q6_K, 2>); prep(gemv_db_kernel<T_Q8_0, 2>);
+    prep(gemv_db_kernel<T_Q4_K, 3>); prep(gemv_db_kernel<T_Q6_K, 3>);
+    if (const char *e = getenv("AIOS_GEMV_DB")) g_use_db = atoi(e);
     int dev = 0;
     CUDA_CHECK(cudaGetDevice(&dev));
     CUDA_CHECK(cudaDeviceGetAttribute(&g_n_sms, cudaDevAttrMultiProcessorCount, dev));
@@ -195,6 +321,18 @@ void launch_gemv(const GemvParams &p, int grid, cudaStream_t st, bool pdl) {
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = pdl ? 1 : 0;
+    const int pass_units = t == T_Q8_0 ? 64 : 32, unit = t == T_Q8_0 ? 32 : 64;
+    if (g_use_db && (p.k / unit) % pass_units == 0) {
+        if (g_use_db == 3 && t == T_Q4_K) { CUDA_CHECK(cudaLaunchKernelEx(&cfg, gemv_db_kernel<T_Q4_K, 3>, p)); return; }
+        if (g_use_db == 3 && t == T_Q6_K) { CUDA_CHECK(cudaLaunchKernelEx(&cfg, gemv_db_kernel<T_Q6_K, 3>, p)); return; }
+        switch (t) {
+            case T_Q4_K: CUDA_CHECK(cudaLaunchKernelEx(&cfg, gemv_db_kernel<T_Q4_K, 2>, p)); return;
+            case T_Q5_K: CUDA_CHECK(cudaLaunchKernelEx(&cfg, gemv_db_kernel<T_Q5_K, 2>, p)); return;
+            case T_Q6_K: CUDA_CHECK(cudaLaunchKernelEx(&cfg, gemv_db_kernel<T_Q6_K, 2>, p)); return;
+            case T_Q8_0: CUDA_CHECK(cudaLaunchKernelEx(&cfg, gemv_db_kernel<T_Q8_0, 2>, p)); return;
+            default: break;
+        }
+    }
     switch (t) {
         case T_Q4_K: CUDA_CHECK(cudaLaunchKernelEx(&cfg, gemv_kernel<T_Q4_K>, p)); break;
         case T_Q5_K: CUDA_CHECK(cudaLaunchKernelEx(&cfg, gemv_kernel<T_Q5_K>, p)); break;
