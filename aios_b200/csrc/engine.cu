@@ -373,13 +373,16 @@ void Seq::launch_token_pass(bool from_prompt, int prompt_idx, int pos_value, boo
                          EPI_STORE, hp.n_embd, x.as<float>(), L.attn_norm.as<float>(), nullptr, pdl))
         {   // RMSNorm + Q,K,V projections: one launch when the three matrices share a type (else q,k + v)
             GemvParams p{};
-            const bool same = L.wv.w.type == L.wq.w.type;
-            p.n_seg = same ? 3 : 2; p.epi = EPI_STORE; p.k = hp.n_embd;
+            bool same = L.wv.w.type == L.wq.w.type && L.wk.w.type == L.wq.w.type;
+            p.n_seg = 3; p.epi = EPI_STORE; p.k = hp.n_embd;
             p.seg[0] = L.wq.w; p.seg[1] = L.wk.w; p.seg[2] = L.wv.w;
+            if (!same && gemv_can_mix(p)) same = true;  // Q4_K + Q6_K: one launch, the type is per CTA
+            p.n_seg = same ? 3 : 2;
             p.out[0] = qkv.as<float>(); p.out[1] = qkv.as<float>() + QD; p.out[2] = qkv.as<float>() + QD + KVD;
             p.x = x.as<float>(); p.norm_w = L.attn_norm.as<float>(); p.eps = hp.rms_eps;
             if (same) set_prefetch(p, {&L.wo.w}, pf);
             else set_prefetch(p, {&L.wv.w, &L.wo.w}, pf);
+            p.trace = trace_base && launches < 4096 ? trace_base + (size_t)launches * 8 : nullptr;
             TIMED(0, launch_gemv(p, gemv_plan_grid(p, n_sms), st, pdl));
             launches++;
             if (!same) {
@@ -388,6 +391,7 @@ void Seq::launch_token_pass(bool from_prompt, int prompt_idx, int pos_value, boo
                 v.seg[0] = L.wv.w; v.out[0] = qkv.as<float>() + QD + KVD;
                 v.x = x.as<float>(); v.norm_w = L.attn_norm.as<float>(); v.eps = hp.rms_eps;
                 set_prefetch(v, {&L.w_gate.w}, pf);  // (attn_output was requested by the q,k launch)
+                v.trace = trace_base && launches < 4096 ? trace_base + (size_t)launches * 8 : nullptr;
                 TIMED(0, launch_gemv(v, gemv_plan_grid(v, n_sms), st, pdl));
                 launches++;
             }
@@ -413,6 +417,7 @@ void Seq::launch_token_pass(bool from_prompt, int prompt_idx, int pos_value, boo
             p.n_seg = 1; p.epi = EPI_ADD; p.k = QD;
             p.seg[0] = L.wo.w; p.out[0] = x.as<float>(); p.x = att.as<float>();
             set_prefetch(p, {&L.w_gate.w, &L.w_up.w}, pf);
+            p.trace = trace_base && launches < 4096 ? trace_base + (size_t)launches * 8 : nullptr;
             TIMED(0, launch_gemv(p, gemv_plan_grid(p, n_sms), st, pdl));
             launches++;
         }
@@ -423,6 +428,7 @@ void Seq::launch_token_pass(bool from_prompt, int prompt_idx, int pos_value, boo
             p.seg[0] = L.w_gate.w; p.seg[1] = L.w_up.w; p.out[0] = h.as<float>();
             p.x = x.as<float>(); p.norm_w = L.ffn_norm.as<float>(); p.eps = hp.rms_eps;
             set_prefetch(p, {&L.w_down.w}, pf);
+            p.trace = trace_base && launches < 4096 ? trace_base + (size_t)launches * 8 : nullptr;
             TIMED(0, launch_gemv(p, gemv_plan_grid(p, n_sms), st, pdl));
             launches++;
         }
@@ -433,6 +439,7 @@ void Seq::launch_token_pass(bool from_prompt, int prompt_idx, int pos_value, boo
             p.seg[0] = L.w_down.w; p.out[0] = x.as<float>(); p.x = h.as<float>();
             if (il + 1 < hp.n_layer) set_prefetch(p, {&m->layers[il + 1].wq.w, &m->layers[il + 1].wk.w, &m->layers[il + 1].wv.w}, pf);
             else if (want_logits) set_prefetch(p, {&m->output.w}, pf);
+            p.trace = trace_base && launches < 4096 ? trace_base + (size_t)launches * 8 : nullptr;
             TIMED(0, launch_gemv(p, gemv_plan_grid(p, n_sms), st, pdl));
             launches++;
         }
@@ -447,6 +454,7 @@ void Seq::launch_token_pass(bool from_prompt, int prompt_idx, int pos_value, boo
             p.seg[0] = m->output.w; p.out[0] = logits.as<float>();
             p.x = x.as<float>(); p.norm_w = m->output_norm.as<float>(); p.eps = hp.rms_eps;
             p.argmax_key = &sd->argmax_key;
+            p.trace = trace_base && launches < 4096 ? trace_base + (size_t)launches * 8 : nullptr;
             TIMED(0, launch_gemv(p, gemv_plan_grid(p, n_sms), st, false));
             launches++;
         }

@@ -131,17 +131,13 @@ struct PassRegs1 {
 };
 
 template <int TYPE, int NB>
-__global__ void __launch_bounds__(GEMV_THREADS, 2) gemv_db_kernel(const GemvParams p) {
-    extern __shared__ __align__(16) uint8_t smem[];
-    __shared__ double red[GEMV_WARPS];
+__device__ __forceinline__ void gemv_db_body(const GemvParams &p, int seg, uint8_t *smem, double *red) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     constexpr int UNIT = TYPE == T_Q8_0 ? 32 : 64;
     using Regs = PassRegs1<TYPE>;
     constexpr int PU = Regs::ITS * 32;
-    int seg = 0;
-    if (p.epi != EPI_SWIGLU) {
-        while (seg + 1 < p.n_seg && (int)blockIdx.x >= p.cta_begin[seg + 1]) seg++;
-    }
+    unsigned long long *tr = (blockIdx.x == 0 && threadIdx.x == 0) ? p.trace : nullptr;
+    trace_mark(tr, 0);
     const WPlanes &W = p.seg[seg];
     const WPlanes &W1 = p.seg[p.epi == EPI_SWIGLU ? 1 : seg];
     const int cta_local = (int)blockIdx.x - p.cta_begin[seg];
@@ -180,14 +176,17 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) gemv_db_kernel(const GemvPara
         }
     };
     Regs g[NB];
+    // (Tried instead: hold nothing through the prologue, only pull the first passes into L2, and use the freed
+    // registers for a prologue with more loads in flight — 1.81 vs 1.72 ms/token: the held images win.)
 #pragma unroll
     for (int b = 0; b < NB; b++) load_next(g[b]);  // all images are requested before the dependency wait
     asm volatile("griddepcontrol.wait;" ::: "memory");
-
+    trace_mark(tr, 1);
     if (TYPE == T_Q6_K) prep_activations<PERM_Q6>(p.x, p.norm_w, p.eps, p.k, s, red);
     else if (TYPE == T_Q8_0) prep_activations<PERM_Q80>(p.x, p.norm_w, p.eps, p.k, s, red);
     else prep_activations<PERM_Q4>(p.x, p.norm_w, p.eps, p.k, s, red);
     asm volatile("griddepcontrol.launch_dependents;");
+    trace_mark(tr, 2);
 
     float *out = p.out[seg];
     unsigned long long best = 0ull;
@@ -225,11 +224,43 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) gemv_db_kernel(const GemvPara
             if (crow < N) step(g[b]);
         }
     }
+    trace_mark(tr, 4);
+    if (p.trace && threadIdx.x == 0) {
+        unsigned long long now;
+        asm volatile("mov.u64 %0, %globaltimer;" : "=l"(now));
+        atomicMax(p.trace + 7, now);
+    }
     if (p.argmax_key) {
         const unsigned long long other = __shfl_sync(0xffffffffu, best, 16);
         best = other > best ? other : best;
         if (lane == 0 && best) atomicMax(p.argmax_key, best);
     }
+}
+
+__device__ __forceinline__ int gemv_my_segment(const GemvParams &p) {
+    int seg = 0;
+    if (p.epi != EPI_SWIGLU) {
+        while (seg + 1 < p.n_seg && (int)blockIdx.x >= p.cta_begin[seg + 1]) seg++;
+    }
+    return seg;
+}
+
+template <int TYPE, int NB>
+__global__ void __launch_bounds__(GEMV_THREADS, 2) gemv_db_kernel(const GemvParams p) {
+    extern __shared__ __align__(16) uint8_t smem[];
+    __shared__ double red[GEMV_WARPS];
+    gemv_db_body<TYPE, NB>(p, gemv_my_segment(p), smem, red);
+}
+
+// attn_q / attn_k (Q4_K) and attn_v (Q6_K in half of the layers of a Q4_K_M file) in ONE launch: a CTA serves one
+// matrix, so the type is CTA-uniform and each CTA builds only the activation image its type needs.  Saves a launch
+// (hand-over + a second RMSNorm/quantisation prologue) in every such layer.
+__global__ void __launch_bounds__(GEMV_THREADS, 2) gemv_db_mixed_kernel(const GemvParams p) {
+    extern __shared__ __align__(16) uint8_t smem[];
+    __shared__ double red[GEMV_WARPS];
+    const int seg = gemv_my_segment(p);
+    if (p.seg[seg].type == T_Q6_K) gemv_db_body<T_Q6_K, 2>(p, seg, smem, red);
+    else gemv_db_body<T_Q4_K, 2>(p, seg, smem, red);
 }
 
 size_t gemv_smem_bytes(int k) { return act_image_bytes(k); }
@@ -294,6 +325,7 @@ void gemv_init() {
     };
     prep(gemv_db_kernel<T_Q4_K, 2>); prep(gemv_db_kernel<T_Q5_K, 2>); prep(gemv_db_kernel<T_Q6_K, 2>); prep(gemv_db_kernel<T_Q8_0, 2>);
     prep(gemv_db_kernel<T_Q4_K, 3>); prep(gemv_db_kernel<T_Q6_K, 3>);
+    prep(gemv_db_mixed_kernel);
     if (const char *e = getenv("AIOS_GEMV_DB")) g_use_db = atoi(e);
     int dev = 0;
     CUDA_CHECK(cudaGetDevice(&dev));
@@ -302,11 +334,21 @@ void gemv_init() {
     done = true;
 }
 
-// All segments of a launch must have one type (the engine splits mixed q/k/v into two launches).
-void launch_gemv(const GemvParams &p, int grid, cudaStream_t st, bool pdl) {
+// Q4_K and Q6_K matrices may share a launch (gemv_db_mixed_kernel) when K is a whole number of 2048-weight passes
+bool gemv_can_mix(const GemvParams &p) {
+    if (g_use_db != 2 || p.epi == EPI_SWIGLU || (p.k / 64) % 32 != 0) return false;
+    for (int i = 0; i < p.n_seg; i++)
+        if (p.seg[i].type != T_Q4_K && p.seg[i].type != T_Q6_K) return false;
+    return true;
+}
+
+// All segments of a launch must have one type, except for the Q4_K + Q6_K mix gemv_can_mix() allows.
+void launch_gemv(const GemvParams &p_in, int grid, cudaStream_t st, bool pdl) {
+    const GemvParams &p = p_in;
     const int t = p.seg[0].type;
-    for (int i = 1; i < p.n_seg; i++)
-        if (p.seg[i].type != t) throw CudaError("launch_gemv: segments of one launch must share a weight type");
+    bool mixed = false;
+    for (int i = 1; i < p.n_seg; i++) mixed |= p.seg[i].type != t;
+    if (mixed && !gemv_can_mix(p)) throw CudaError("launch_gemv: segments of one launch must share a weight type");
     if (g_use_staged && gemv_staged_usable(p, g_n_sms)) {  // big matrix: the cp.async ring keeps more bytes in flight
         launch_gemv_staged(p, g_n_sms, st, pdl);
         return;
@@ -321,6 +363,10 @@ void launch_gemv(const GemvParams &p, int grid, cudaStream_t st, bool pdl) {
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     cfg.attrs = attr;
     cfg.numAttrs = pdl ? 1 : 0;
+    if (mixed) {
+        CUDA_CHECK(cudaLaunchKernelEx(&cfg, gemv_db_mixed_kernel, p));
+        return;
+    }
     const int pass_units = t == T_Q8_0 ? 64 : 32, unit = t == T_Q8_0 ? 32 : 64;
     if (g_use_db && (p.k / unit) % pass_units == 0) {
         if (g_use_db == 3 && t == T_Q4_K) { CUDA_CHECK(cudaLaunchKernelEx(&cfg, gemv_db_kernel<T_Q4_K, 3>, p)); return; }

@@ -36,12 +36,16 @@ struct GemvParams {
     int32_t n_pf;
     const uint8_t *pf_ptr[12];
     uint32_t pf_bytes[12];
+    // timeline of CTA 0 (null = off; gemv_db_kernel): [0] entry [1] dependency wait over [2] activations ready
+    // [4] CTA 0 done [7] last CTA done
+    unsigned long long *trace;
 };
 
 // fills cta_begin[] and returns the grid size; n_sms from the device
 int gemv_plan_grid(GemvParams &p, int n_sms);
 size_t gemv_smem_bytes(int k);
 void launch_gemv(const GemvParams &p, int grid, cudaStream_t st, bool pdl = false);
+bool gemv_can_mix(const GemvParams &p);  // may Q4_K and Q6_K segments of p ride in one launch?
 void gemv_init();  // one-time function attributes (dynamic smem)
 // large matrices: per-warp cp.async ring in shared memory (gemv_staged.cu); launch_gemv picks it when usable
 bool gemv_staged_usable(const GemvParams &p, int n_sms);
