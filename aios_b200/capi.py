@@ -25,6 +25,7 @@ ENGINE_L2_PREFETCH = 16
 ENGINE_ATTN_HEAD = 32
 ENGINE_ATTN_CLUSTER = 64
 ENGINE_USE_RING = 128
+ENGINE_NO_ROPE_EPILOGUE = 256
 
 
 class AiosError(RuntimeError):

@@ -21,6 +21,8 @@
 //
 // Same arithmetic as attention.cu / attention_head.cu / oracle/aios_oracle.c: rope from the host table, q, K and V
 // rounded to f16, exact f16 x f16 products summed in double (order-free), deterministic expf, P rounded to f16.
+#include <algorithm>
+
 #include "common.cuh"
 #include "kernels.h"
 
@@ -101,6 +103,9 @@ __global__ void __launch_bounds__(AS_THREADS, 2) attn_split_kernel(const AttnPar
     double *part = reinterpret_cast<double *>(dyn + (size_t)sc_cap * 4);
     uint16_t *knew = reinterpret_cast<uint16_t *>(part + (size_t)AS_WARPS * DPC);
     uint16_t *vnew = knew + HD;
+    // staged rows (kv_ready launches): K[stage_cap][HD] f16 | V[stage_cap][DPC] f16
+    uint16_t *kst = vnew + HD;
+    uint16_t *vst = kst + (size_t)p.stage_cap * HD;
     __shared__ float sh_f[AS_WARPS];
     __shared__ double sh_d[AS_WARPS];
 
@@ -109,21 +114,31 @@ __global__ void __launch_bounds__(AS_THREADS, 2) attn_split_kernel(const AttnPar
     // the successor only prefetches weights until this grid has completed: let it start now
     asm volatile("griddepcontrol.launch_dependents;");
 
-    // Before the dependency wait: the cache rows of earlier tokens are final, so ask L2 for them now (they were
-    // last touched a whole token pass — 4 GB of weight traffic — ago and would otherwise come from DRAM in two to
-    // four dependent round trips).  The position counter read here may in principle be one token old; it is only
-    // used for this hint and re-read after the wait.
-    {
-        const int n_hint = *reinterpret_cast<const volatile int32_t *>(p.n_past_ptr);
-        if (h % rep == 0 && n_hint > 0 && n_hint < p.n_ctx) {
-            const size_t head_off = (size_t)g * HD;
-            for (int j = part_id * AS_THREADS + threadIdx.x; j < n_hint; j += SPLIT * AS_THREADS) {
-                const uint16_t *kr = p.k_cache + (size_t)j * kvd + head_off;
-                const uint16_t *vr = p.v_cache + (size_t)j * kvd + head_off;
-                asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(kr), "r"(HD * 2) : "memory");
-                asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(vr), "r"(HD * 2) : "memory");
-            }
+    // Before the dependency wait: the cache rows of earlier tokens are final — they were last touched a whole token
+    // pass (4 GB of weight traffic) ago, so they come from DRAM.  Copy them into shared memory NOW, all at once
+    // (cp.async, 16 B per thread-instruction), while the previous kernel is still finishing: one DRAM round trip
+    // that overlaps the dependency wait instead of two to four dependent ones after it.  The position counter read
+    // here may in principle be stale; rows at or above the true position are (re)copied after the wait.
+    const bool kv_ready = p.kv_ready != 0;
+    const size_t head_off = (size_t)g * HD;
+    auto stage_rows = [&](int lo, int hi) {  // rows [lo, hi) of K (whole head) and V (my DPC dims) -> shared memory
+        for (int c = lo * LPR + threadIdx.x; c < hi * LPR; c += AS_THREADS) {
+            const int j = c / LPR, ch = c % LPR;
+            const uint32_t dst = (uint32_t)__cvta_generic_to_shared(kst + (size_t)j * HD + ch * 8);
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(p.k_cache + (size_t)j * kvd + head_off + ch * 8) : "memory");
         }
+        for (int c = lo * VL + threadIdx.x; c < hi * VL; c += AS_THREADS) {
+            const int j = c / VL, ch = c % VL;
+            const uint32_t dst = (uint32_t)__cvta_generic_to_shared(vst + (size_t)j * DPC + ch * 8);
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(p.v_cache + (size_t)j * kvd + head_off + part_id * DPC + ch * 8) : "memory");
+        }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    int n_stage0 = 0;
+    if (kv_ready && p.stage_cap > 0) {
+        const int n_hint = *reinterpret_cast<const volatile int32_t *>(p.n_past_ptr);
+        n_stage0 = max(0, min(n_hint, p.stage_cap));
+        stage_rows(0, n_stage0);
     }
     // qkv, the position counter and the cache rows of earlier tokens are all final once the predecessor is done
     asm volatile("griddepcontrol.wait;" ::: "memory");
@@ -131,6 +146,10 @@ __global__ void __launch_bounds__(AS_THREADS, 2) attn_split_kernel(const AttnPar
 
     const int n_past = __ldcg(p.n_past_ptr);
     const int n_pos = n_past + 1;
+    // kv_ready: the q/k/v GEMV's epilogue already roped q, and appended this token's K/V rows to the cache
+    const int n_cached = kv_ready ? n_pos : n_past;  // rows that come from the cache
+    const int n_stage = kv_ready ? min(n_pos, p.stage_cap) : 0;  // rows served from shared memory
+    if (n_stage > 0) stage_rows(min(n_stage0, n_past), n_stage);  // this token's row (and anything a stale hint missed)
     const float *cs = p.rope_cos + (size_t)n_past * (p.n_rot / 2);
     const float *sn = p.rope_sin + (size_t)n_past * (p.n_rot / 2);
 
@@ -143,11 +162,11 @@ __global__ void __launch_bounds__(AS_THREADS, 2) attn_split_kernel(const AttnPar
     for (int t = 0; t < AS_BATCH; t++) {
         const int j = warp * RPW + t * kstep + ksub;
         kk[0][t] = make_uint4(0, 0, 0, 0);
-        if (j < n_past) kk[0][t] = __ldcg(reinterpret_cast<const uint4 *>(kbase + (size_t)j * kvd));
+        if (j >= n_stage && j < n_cached) kk[0][t] = __ldcg(reinterpret_cast<const uint4 *>(kbase + (size_t)j * kvd));
     }
 
     // ---- new token's k (roped) and v, rounded to f16; one CTA of the kv group appends the cache rows
-    {
+    if (!kv_ready) {
         const float *kraw = p.qkv + (size_t)p.n_head * HD + (size_t)g * HD;
         const float *vraw = kraw + kvd;
         const bool writer = (h % rep == 0) && part_id == 0;
@@ -179,7 +198,7 @@ __global__ void __launch_bounds__(AS_THREADS, 2) attn_split_kernel(const AttnPar
         for (int e = 0; e < 8; e += 2) {
             float x0 = qraw[e], x1 = qraw[e + 1];
             const int i = (kdl + e) / 2;
-            if (2 * i < p.n_rot) {
+            if (!kv_ready && 2 * i < p.n_rot) {
                 const float c = cs[i], s = sn[i];
                 const float r0 = __fsub_rn(__fmul_rn(x0, c), __fmul_rn(x1, s));
                 const float r1 = __fadd_rn(__fmul_rn(x0, s), __fmul_rn(x1, c));
@@ -189,9 +208,11 @@ __global__ void __launch_bounds__(AS_THREADS, 2) attn_split_kernel(const AttnPar
             q[e + 1] = (double)__half2float(__float2half_rn(x1));
         }
     }
-    __syncthreads();  // knew / vnew visible
+    asm volatile("cp.async.wait_all;" ::: "memory");
+    __syncthreads();  // staged rows landed; knew / vnew visible
 
-    // ---- scores of ALL positions (every CTA of the head repeats them): cached rows from L2, row n_past from smem
+    // ---- scores of ALL positions (every CTA of the head repeats them): staged rows from shared memory, the rest
+    // of the cache from L2/DRAM, (without kv_ready) row n_past from knew
     float wmax = -INFINITY;
     const int kbstride = kstep * AS_BATCH;
     auto kload = [&](uint4 (&dst)[AS_BATCH], int jb) {
@@ -199,16 +220,24 @@ __global__ void __launch_bounds__(AS_THREADS, 2) attn_split_kernel(const AttnPar
         for (int t = 0; t < AS_BATCH; t++) {
             const int j = jb + t * kstep + ksub;
             dst[t] = make_uint4(0, 0, 0, 0);
-            if (j < n_past) dst[t] = __ldcg(reinterpret_cast<const uint4 *>(kbase + (size_t)j * kvd));
+            if (j < n_stage) dst[t] = *reinterpret_cast<const uint4 *>(kst + (size_t)j * HD + kdl);
+            else if (j < n_cached) dst[t] = __ldcg(reinterpret_cast<const uint4 *>(kbase + (size_t)j * kvd));
         }
     };
+    if (n_stage > 0) {  // the first batch was requested before the staged rows had landed
+#pragma unroll
+        for (int t = 0; t < AS_BATCH; t++) {
+            const int j = warp * RPW + t * kstep + ksub;
+            if (j < n_stage) kk[0][t] = *reinterpret_cast<const uint4 *>(kst + (size_t)j * HD + kdl);
+        }
+    }
     auto kscore = [&](const uint4 (&src)[AS_BATCH], int jb) {
         double sd[AS_BATCH];
 #pragma unroll
         for (int t = 0; t < AS_BATCH; t++) {
             const int j = jb + t * kstep + ksub;
             uint4 row = src[t];
-            if (j == n_past) row = *reinterpret_cast<const uint4 *>(knew + kdl);
+            if (!kv_ready && j == n_past) row = *reinterpret_cast<const uint4 *>(knew + kdl);
             sd[t] = dot8(row, q);
         }
         // fold the LPR lanes of each row; lane ends up with the total of row-group `e`
@@ -250,7 +279,8 @@ __global__ void __launch_bounds__(AS_THREADS, 2) attn_split_kernel(const AttnPar
         for (int t = 0; t < AS_BATCH; t++) {
             const int j = jb + t * vstep + vsub;
             vv[t] = make_uint4(0, 0, 0, 0);
-            if (j < n_past) vv[t] = __ldcg(reinterpret_cast<const uint4 *>(vbase + (size_t)j * kvd));
+            if (j < n_stage) vv[t] = *reinterpret_cast<const uint4 *>(vst + (size_t)j * DPC + (lane % VL) * 8);
+            else if (j < n_cached) vv[t] = __ldcg(reinterpret_cast<const uint4 *>(vbase + (size_t)j * kvd));
         }
     };
     vload(warp * RPV);
@@ -290,7 +320,7 @@ __global__ void __launch_bounds__(AS_THREADS, 2) attn_split_kernel(const AttnPar
             const int j = jb + t * vstep + vsub;
             if (j < n_pos) {
                 uint4 row = vv[t];
-                if (j == n_past) row = *reinterpret_cast<const uint4 *>(vnew + vdl);
+                if (!kv_ready && j == n_past) row = *reinterpret_cast<const uint4 *>(vnew + vdl);
                 const double pj = (double)__half2float(__float2half_rn(__fmul_rn(sc[j], inv)));
                 axpy8(row, pj, o);
             }
@@ -324,6 +354,8 @@ void attn_split_init() {
     // same shared-memory carve-out as the ring GEMV it sits between (an SM cannot host two carve-outs at once)
     CUDA_CHECK(cudaFuncSetAttribute(attn_split_kernel<128, AS_SPLIT>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
     CUDA_CHECK(cudaFuncSetAttribute(attn_split_kernel<64, AS_SPLIT>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+    CUDA_CHECK(cudaFuncSetAttribute(attn_split_kernel<128, AS_SPLIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 208 * 1024));
+    CUDA_CHECK(cudaFuncSetAttribute(attn_split_kernel<64, AS_SPLIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 208 * 1024));
     done = true;
 }
 
@@ -331,11 +363,15 @@ bool attn_split_usable(int n_ctx, int hd) {
     return (hd == 64 || hd == 128) && n_ctx <= 4096 && as_smem(n_ctx, hd, AS_SPLIT) <= 40 * 1024;
 }
 
-void launch_attn_decode_split(const AttnParams &p, cudaStream_t st, bool pdl) {
+constexpr int AS_STAGE_ROWS = 512;  // cache rows copied into shared memory before the dependency wait (kv_ready)
+
+void launch_attn_decode_split(const AttnParams &p_in, cudaStream_t st, bool pdl) {
+    AttnParams p = p_in;
+    p.stage_cap = p.kv_ready ? std::min(p.n_ctx, AS_STAGE_ROWS) : 0;
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(p.n_head * AS_SPLIT);
     cfg.blockDim = dim3(AS_THREADS);
-    cfg.dynamicSmemBytes = as_smem(p.n_ctx, p.hd, AS_SPLIT);
+    cfg.dynamicSmemBytes = as_smem(p.n_ctx, p.hd, AS_SPLIT) + (size_t)p.stage_cap * (p.hd + p.hd / AS_SPLIT) * 2;
     cfg.stream = st;
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;

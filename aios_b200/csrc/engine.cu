@@ -367,8 +367,13 @@ void Seq::launch_token_pass(bool from_prompt, int prompt_idx, int pos_value, boo
         launches++;
         return true;
     };
+    const int amode = (m->eng->flags & AIOS_ENGINE_ATTN_CLUSTER) ? 2 : (m->eng->flags & AIOS_ENGINE_ATTN_HEAD) ? 1 : 0;
+    // with the split attention kernel, RoPE + f16 rounding + KV append move into the q/k/v GEMV's epilogue
+    // (EPI_QKV_ROPE): the attention kernel then starts on final data, with no dependent table loads of its own
+    const bool rope_in_gemv = amode == 0 && attn_split_usable(hp.n_ctx, hp.head_dim) && !(m->eng->flags & AIOS_ENGINE_NO_ROPE_EPILOGUE);
     for (int il = 0; il < hp.n_layer; il++) {
         const Layer &L = m->layers[il];
+        bool kv_ready = false;
         if (!ring_launch({&L.wq.t, &L.wk.t, &L.wv.t}, {qkv.as<float>(), qkv.as<float>() + QD, qkv.as<float>() + QD + KVD},
                          EPI_STORE, hp.n_embd, x.as<float>(), L.attn_norm.as<float>(), nullptr, pdl))
         {   // RMSNorm + Q,K,V projections: one launch when the three matrices share a type (else q,k + v)
@@ -380,6 +385,14 @@ void Seq::launch_token_pass(bool from_prompt, int prompt_idx, int pos_value, boo
             p.n_seg = same ? 3 : 2;
             p.out[0] = qkv.as<float>(); p.out[1] = qkv.as<float>() + QD; p.out[2] = qkv.as<float>() + QD + KVD;
             p.x = x.as<float>(); p.norm_w = L.attn_norm.as<float>(); p.eps = hp.rms_eps;
+            if (same && rope_in_gemv) {  // RoPE, f16 rounding and the KV append ride in this launch's epilogue
+                p.epi = EPI_QKV_ROPE;
+                p.rope.cos = m->rope_cos.as<float>(); p.rope.sin = m->rope_sin.as<float>();
+                p.rope.n_past_ptr = &sd->pos;
+                p.rope.k_cache = m->k_cache(slot, il); p.rope.v_cache = m->v_cache(slot, il);
+                p.rope.n_rot = hp.n_rot; p.rope.hd = hp.head_dim; p.rope.kvd = KVD;
+                kv_ready = true;
+            }
             if (same) set_prefetch(p, {&L.wo.w}, pf);
             else set_prefetch(p, {&L.wv.w, &L.wo.w}, pf);
             p.trace = trace_base && launches < 4096 ? trace_base + (size_t)launches * 8 : nullptr;
@@ -407,7 +420,7 @@ void Seq::launch_token_pass(bool from_prompt, int prompt_idx, int pos_value, boo
             a.n_split = m->attn_splits; a.n_ctx = hp.n_ctx;
             a.scale = 1.0f / sqrtf((float)hp.head_dim);
             a.trace = trace_base && launches < 4096 ? trace_base + (size_t)launches * 8 : nullptr;
-            const int amode = (m->eng->flags & AIOS_ENGINE_ATTN_CLUSTER) ? 2 : (m->eng->flags & AIOS_ENGINE_ATTN_HEAD) ? 1 : 0;
+            a.kv_ready = kv_ready ? 1 : 0;
             TIMED(1, launch_attn_decode(a, st, pdl, amode));
             launches++;
         }

@@ -78,6 +78,7 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) gemv_kernel(const GemvParams 
 
     float *out = p.out[seg];
     unsigned long long best = 0ull;
+    const int rope_pos = p.epi == EPI_QKV_ROPE ? __ldcg(p.rope.n_past_ptr) : 0;
     for (int row0 = row_first; row0 < N; row0 += row_step) {
         double acc[GEMV_R] = {0.0, 0.0};
         if (row0 != row_first) ptrs(row0, rp);
@@ -90,7 +91,9 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) gemv_kernel(const GemvParams 
             else compute_pass<TYPE, false>(g, u0, nu, p.k, s, acc);
         }
         const double tot = warp_sum2_f64(acc[0], acc[1]);  // lanes 0-15: row 0, lanes 16-31: row 1
-        if (pair) {
+        if (p.epi == EPI_QKV_ROPE) {
+            qkv_rope_store(p, seg, row0, tot, rope_pos);
+        } else if (pair) {
             const float gte = (float)__shfl_sync(0xffffffffu, tot, 0), up = (float)__shfl_sync(0xffffffffu, tot, 16);
             if (lane == 0) out[row0] = __fmul_rn(__fdiv_rn(gte, __fadd_rn(1.0f, expf_det(-gte))), up);
         } else if ((lane & 15) == 0) {
@@ -190,6 +193,7 @@ __device__ __forceinline__ void gemv_db_body(const GemvParams &p, int seg, uint8
 
     float *out = p.out[seg];
     unsigned long long best = 0ull;
+    const int rope_pos = p.epi == EPI_QKV_ROPE ? __ldcg(p.rope.n_past_ptr) : 0;
     int crow = row_first, cu = 0;  // compute cursor
     double acc[GEMV_R] = {0.0, 0.0};
     auto step = [&](Regs &g) {
@@ -198,7 +202,9 @@ __device__ __forceinline__ void gemv_db_body(const GemvParams &p, int seg, uint8
         cu += PU;
         if (cu >= nu) {
             const double tot = warp_sum2_f64(acc[0], acc[1]);  // lanes 0-15: row 0, lanes 16-31: row 1
-            if (pair) {
+            if (p.epi == EPI_QKV_ROPE) {
+                qkv_rope_store(p, seg, crow, tot, rope_pos);
+            } else if (pair) {
                 const float gte = (float)__shfl_sync(0xffffffffu, tot, 0), up = (float)__shfl_sync(0xffffffffu, tot, 16);
                 if (lane == 0) out[crow] = __fmul_rn(__fdiv_rn(gte, __fadd_rn(1.0f, expf_det(-gte))), up);
             } else if ((lane & 15) == 0) {

@@ -473,6 +473,32 @@ __device__ __forceinline__ double warp_sum2_f64(double a0, double a1) {
     return v;
 }
 
+// EPI_QKV_ROPE: the warp holds the dots of rows row0 (lanes 0-15) and row0+1 (lanes 16-31) of segment seg — an
+// adjacent (even, odd) pair, which is what GGML's NORM-style RoPE rotates.  Same operations, in the same order, as
+// the attention kernels' own prologue (attention_split.cu) and the oracle: rotate (q, k), round to f16.
+__device__ __forceinline__ void qkv_rope_store(const GemvParams &p, int seg, int row0, double tot, int n_past) {
+    const float x0 = (float)__shfl_sync(0xffffffffu, tot, 0), x1 = (float)__shfl_sync(0xffffffffu, tot, 16);
+    if ((threadIdx.x & 31) != 0) return;
+    const RopeKv &r = p.rope;
+    float a = x0, b = x1;
+    if (seg < 2) {
+        const int d = row0 % r.hd;
+        if (d < r.n_rot) {
+            const int i = d >> 1;
+            const float c = r.cos[(size_t)n_past * (r.n_rot / 2) + i], s = r.sin[(size_t)n_past * (r.n_rot / 2) + i];
+            a = __fsub_rn(__fmul_rn(x0, c), __fmul_rn(x1, s));
+            b = __fadd_rn(__fmul_rn(x0, s), __fmul_rn(x1, c));
+        }
+    }
+    const uint16_t ha = f2h_bits(a), hb = f2h_bits(b);
+    if (seg == 0) {
+        *reinterpret_cast<float2 *>(p.out[0] + row0) = make_float2(h2f_bits(ha), h2f_bits(hb));
+    } else {
+        uint16_t *dst = (seg == 1 ? r.k_cache : r.v_cache) + (size_t)n_past * r.kvd + row0;
+        *reinterpret_cast<uint32_t *>(dst) = (uint32_t)ha | ((uint32_t)hb << 16);
+    }
+}
+
 // order-preserving float -> u32 so that packed (value, ~index) keys can be atomicMax-ed
 __device__ __forceinline__ unsigned long long argmax_key(float v, int idx) {
     uint32_t b = __float_as_uint(v);

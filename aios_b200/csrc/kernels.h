@@ -18,6 +18,16 @@ enum GemvEpilogue : int {
     EPI_STORE = 0,   // out[n] = dot
     EPI_ADD = 1,     // out[n] += dot            (residual stream update, in place)
     EPI_SWIGLU = 2,  // out[n] = silu(dot(seg0 row n)) * dot(seg1 row n)
+    // segments = (attn_q, attn_k, attn_v): RoPE + f16 rounding in the epilogue; q -> out[0] (f32 holding f16 values),
+    // k and v -> row *n_past_ptr of the layer's KV cache.  Attention then reads every position from the cache.
+    EPI_QKV_ROPE = 3,
+};
+
+struct RopeKv {              // EPI_QKV_ROPE only
+    const float *cos, *sin;  // [n_ctx][n_rot/2]
+    const int32_t *n_past_ptr;
+    uint16_t *k_cache, *v_cache;  // this layer, this sequence: [n_ctx][kvd] f16
+    int32_t n_rot, hd, kvd, pad;
 };
 
 struct GemvParams {
@@ -39,6 +49,7 @@ struct GemvParams {
     // timeline of CTA 0 (null = off; gemv_db_kernel): [0] entry [1] dependency wait over [2] activations ready
     // [4] CTA 0 done [7] last CTA done
     unsigned long long *trace;
+    RopeKv rope;
 };
 
 // fills cta_begin[] and returns the grid size; n_sms from the device
@@ -91,6 +102,10 @@ struct AttnParams {
     int32_t n_head, n_kv, hd, n_rot, n_split, n_ctx;
     float scale;
     unsigned long long *trace;  // split kernel, CTA 0 (null = off): [0] entry [1] wait over [2] scores done [4] end
+    // split kernel: the q/k/v GEMV already applied RoPE, rounded to f16 and appended this token's K/V rows
+    // (EPI_QKV_ROPE): qkv holds the final q only, every position comes from the cache
+    int32_t kv_ready;
+    int32_t stage_cap;  // set by launch_attn_decode_split: cache rows staged in shared memory (kv_ready launches)
 };
 // mode: 0 = pick (split kernel when usable, else per-head, else cluster); 1 = per-head kernel; 2 = cluster kernel
 void launch_attn_decode(const AttnParams &p, cudaStream_t st, bool pdl = false, int mode = 0);
