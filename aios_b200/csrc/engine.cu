@@ -280,6 +280,9 @@ Seq::Seq(Model *m_) : m(m_), slot(-1) {
         qkv = DevBuf((size_t)(hp.n_head + 2 * hp.n_head_kv) * hp.head_dim * 4);
         att = DevBuf((size_t)hp.n_head * hp.head_dim * 4);
         h = DevBuf((size_t)hp.n_ff * 4);
+        h_image = DevBuf((size_t)hp.n_ff + (size_t)hp.n_ff / 4 + 64);  // = act_image_bytes(n_ff), gemv_core.cuh
+        h_counters = DevBuf((size_t)(hp.n_ff / 256 + 1) * 128);  // one 128-byte line per slab counter
+        CUDA_CHECK(cudaMemset(h_counters.p, 0, h_counters.bytes));
         logits = DevBuf((size_t)hp.n_vocab * 4);
         out_tokens = DevBuf((size_t)hp.n_ctx * 4);
         prompt = DevBuf((size_t)hp.n_ctx * 4);
@@ -373,7 +376,7 @@ void Seq::launch_token_pass(bool from_prompt, int prompt_idx, int pos_value, boo
     const bool rope_in_gemv = amode == 0 && attn_split_usable(hp.n_ctx, hp.head_dim) && !(m->eng->flags & AIOS_ENGINE_NO_ROPE_EPILOGUE);
     for (int il = 0; il < hp.n_layer; il++) {
         const Layer &L = m->layers[il];
-        bool kv_ready = false;
+        bool kv_ready = false, h_quantised = false;
         if (!ring_launch({&L.wq.t, &L.wk.t, &L.wv.t}, {qkv.as<float>(), qkv.as<float>() + QD, qkv.as<float>() + QD + KVD},
                          EPI_STORE, hp.n_embd, x.as<float>(), L.attn_norm.as<float>(), nullptr, pdl))
         {   // RMSNorm + Q,K,V projections: one launch when the three matrices share a type (else q,k + v)
@@ -440,6 +443,15 @@ void Seq::launch_token_pass(bool from_prompt, int prompt_idx, int pos_value, boo
             p.n_seg = 2; p.epi = EPI_SWIGLU; p.k = hp.n_embd;
             p.seg[0] = L.w_gate.w; p.seg[1] = L.w_up.w; p.out[0] = h.as<float>();
             p.x = x.as<float>(); p.norm_w = L.ffn_norm.as<float>(); p.eps = hp.rms_eps;
+            if ((m->eng->flags & AIOS_ENGINE_PRODUCER_QUANT) && !(m->ring && L.w_down.t.base)) {
+                // opt-in: the SwiGLU epilogue also quantises h, slab by slab, for ffn_down (whose prologue becomes a
+                // copy).  Bit-identical, but the fence / count / quantise chain lands on the tail of the gate/up
+                // launch and costs more than ffn_down's 4.7 us prologue saves: 1.83 vs 1.71 ms/token.
+                const int dt = L.w_down.w.type;
+                p.q_image = h_image.as<uint8_t>(); p.q_counters = h_counters.as<uint32_t>();
+                p.q_perm = dt == T_Q6_K ? 1 : dt == T_Q8_0 ? 2 : 0; p.q_k = hp.n_ff;
+                h_quantised = true;
+            }
             set_prefetch(p, {&L.w_down.w}, pf);
             p.trace = trace_base && launches < 4096 ? trace_base + (size_t)launches * 8 : nullptr;
             TIMED(0, launch_gemv(p, gemv_plan_grid(p, n_sms), st, pdl));
@@ -450,6 +462,7 @@ void Seq::launch_token_pass(bool from_prompt, int prompt_idx, int pos_value, boo
             GemvParams p{};
             p.n_seg = 1; p.epi = EPI_ADD; p.k = hp.n_ff;
             p.seg[0] = L.w_down.w; p.out[0] = x.as<float>(); p.x = h.as<float>();
+            if (h_quantised) p.x_image = h_image.as<uint8_t>();
             if (il + 1 < hp.n_layer) set_prefetch(p, {&m->layers[il + 1].wq.w, &m->layers[il + 1].wk.w, &m->layers[il + 1].wv.w}, pf);
             else if (want_logits) set_prefetch(p, {&m->output.w}, pf);
             p.trace = trace_base && launches < 4096 ? trace_base + (size_t)launches * 8 : nullptr;

@@ -115,6 +115,7 @@ struct Seq {
     DevBuf state, x, qkv, att, h, logits, out_tokens, prompt, attn_scratch, attn_counters, snap_logits;
     int snap_n_past = -1;
     struct KernelTimer *timer = nullptr;  // non-null only inside profile_decode
+    DevBuf h_image, h_counters;  // ffn_down's activation image, quantised by the SwiGLU epilogue (GemvParams::q_image)
     DevBuf trace;
     unsigned long long *trace_base = nullptr;  // non-null only inside trace_decode
     cudaGraphExec_t graph = nullptr;

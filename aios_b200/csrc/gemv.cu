@@ -69,7 +69,8 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) gemv_kernel(const GemvParams 
 
     // (fetching the norm weights before the wait was tried: it costs 16 registers across the held first pass, spills,
     // and gains nothing measurable — 1.915 vs 1.912 ms/token)
-    if (TYPE == T_Q6_K) prep_activations<PERM_Q6>(p.x, p.norm_w, p.eps, p.k, s, red);
+    if (p.x_image) copy_activation_image(p.x_image, p.k, smem);
+    else if (TYPE == T_Q6_K) prep_activations<PERM_Q6>(p.x, p.norm_w, p.eps, p.k, s, red);
     else if (TYPE == T_Q8_0) prep_activations<PERM_Q80>(p.x, p.norm_w, p.eps, p.k, s, red);
     else prep_activations<PERM_Q4>(p.x, p.norm_w, p.eps, p.k, s, red);
     // let the next kernel's CTAs be scheduled as soon as SM resources free up: until this grid has
@@ -108,6 +109,10 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) gemv_kernel(const GemvParams 
                 }
             }
         }
+    }
+    if (pair && p.q_image) {
+        __threadfence();
+        report_rows_and_quantise(p, out, row_first, row_step, N);
     }
     if (p.argmax_key) {
         const unsigned long long other = __shfl_sync(0xffffffffu, best, 16);
@@ -185,7 +190,8 @@ __device__ __forceinline__ void gemv_db_body(const GemvParams &p, int seg, uint8
     for (int b = 0; b < NB; b++) load_next(g[b]);  // all images are requested before the dependency wait
     asm volatile("griddepcontrol.wait;" ::: "memory");
     trace_mark(tr, 1);
-    if (TYPE == T_Q6_K) prep_activations<PERM_Q6>(p.x, p.norm_w, p.eps, p.k, s, red);
+    if (p.x_image) copy_activation_image(p.x_image, p.k, smem);  // quantised by the previous launch's epilogue
+    else if (TYPE == T_Q6_K) prep_activations<PERM_Q6>(p.x, p.norm_w, p.eps, p.k, s, red);
     else if (TYPE == T_Q8_0) prep_activations<PERM_Q80>(p.x, p.norm_w, p.eps, p.k, s, red);
     else prep_activations<PERM_Q4>(p.x, p.norm_w, p.eps, p.k, s, red);
     asm volatile("griddepcontrol.launch_dependents;");
@@ -229,6 +235,10 @@ __device__ __forceinline__ void gemv_db_body(const GemvParams &p, int seg, uint8
         for (int b = 0; b < NB; b++) {
             if (crow < N) step(g[b]);
         }
+    }
+    if (pair && p.q_image) {  // report this warp's rows; the warp that completes a slab quantises it for ffn_down
+        __threadfence();
+        report_rows_and_quantise(p, out, row_first, row_step, N);
     }
     trace_mark(tr, 4);
     if (p.trace && threadIdx.x == 0) {

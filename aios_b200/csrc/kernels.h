@@ -50,6 +50,14 @@ struct GemvParams {
     // [4] CTA 0 done [7] last CTA done
     unsigned long long *trace;
     RopeKv rope;
+    // Producer-side activation quantisation (EPI_SWIGLU launches): the warp whose row completes a 256-slab of the
+    // output (per-slab arrival counter) quantises that slab for the NEXT launch and writes it, in that launch's
+    // shared-memory image layout, to q_image.  The consumer then gets x_image = the same buffer and its prologue is
+    // a 17 KB copy instead of 4-5 us of loads + quantisation (ffn_down, K = 14336).  Counters are zero between tokens.
+    uint8_t *q_image;
+    uint32_t *q_counters;
+    int32_t q_perm, q_k;      // image permutation (PERM_* of the consumer's weight type) and the consumer's K
+    const uint8_t *x_image;   // consumer side: ready-made activation image (x is not read)
 };
 
 // fills cta_begin[] and returns the grid size; n_sms from the device

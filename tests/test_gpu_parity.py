@@ -320,3 +320,37 @@ def test_ring_gemv_matches_oracle_and_register_path(engine, oracle, tmp_models, 
         m1.unload()
         m2.unload()
         ring.close()
+
+
+@pytest.mark.parametrize("flag", ["ENGINE_NO_ROPE_EPILOGUE", "ENGINE_PRODUCER_QUANT", "ENGINE_NO_PDL", "ENGINE_NO_GRAPH"])
+def test_engine_variants_are_bit_identical(engine, oracle, tmp_models, flag):
+    """Every switchable variant of the token pass — RoPE / KV append in the attention kernel instead of the q/k/v
+    GEMV's epilogue, ffn_down's input quantised by the SwiGLU epilogue, no programmatic dependent launch, no CUDA
+    graph — computes the same arithmetic: oracle tokens, logits equal bit for bit to the default engine's."""
+    from aios_b200 import capi
+    arch = "tiny-gqa4"
+    path = tmp_models(arch, "Q4_K_M")
+    om = oracle.OracleModel(path, n_ctx=128)
+    prompt = gs.synthetic_prompt(arch, 10, 21)
+    ref, margins = om.greedy(prompt, 32)
+    other = capi.Engine(device=0, max_batch=1, flags=getattr(capi, flag))
+    m1, m2 = engine.load_model("a", path, n_ctx=128), other.load_model("b", path, n_ctx=128)
+    try:
+        s1, s2 = m1.new_seq(), m2.new_seq()
+        try:
+            s1.prefill(prompt)
+            s2.prefill(prompt)
+            a, b = s1.decode(32), s2.decode(32)
+            assert np.array_equal(a, ref) and np.array_equal(b, ref), margins.min()
+            assert np.array_equal(s1.logits().view(np.uint32), s2.logits().view(np.uint32))
+            for il in range(gs.ARCHS[arch].n_layer):
+                k1, v1 = s1.read_kv(il, 0, 42)
+                k2, v2 = s2.read_kv(il, 0, 42)
+                assert np.array_equal(k1, k2) and np.array_equal(v1, v2)
+        finally:
+            s1.free()
+            s2.free()
+    finally:
+        m1.unload()
+        m2.unload()
+        other.close()
