@@ -105,6 +105,11 @@ SYMBOLS = {
     "aios_seq_decode_static": (C.c_int, [_P, C.c_int32, _P, C.POINTER(C.c_int32)]),
     "aios_seq_logits": (C.c_int, [_P, _P]),
     "aios_generate": (C.c_int, [_P, _P, C.c_int32, C.POINTER(Sampling), C.c_int32, _P, C.POINTER(C.c_int32)]),
+    "aios_request_submit": (C.c_int, [_P, _P, C.c_int32, C.POINTER(Sampling), C.c_int32, C.c_int32, C.POINTER(_P)]),
+    "aios_request_poll": (C.c_int, [_P, _P, C.c_int32, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
+    "aios_request_wait": (C.c_int, [_P, C.c_int32, C.POINTER(C.c_int32)]),
+    "aios_request_cancel": (C.c_int, [_P]),
+    "aios_request_free": (None, [_P]),
     "aios_dequantize": (C.c_int, [_P, C.c_int32, _P, C.c_int64, _P]),
     "aios_matvec": (C.c_int, [_P, C.c_int32, _P, C.c_int64, C.c_int64, _P, _P, C.c_float, _P]),
     "aios_forward_logits": (C.c_int, [_P, _P, C.c_int32, C.c_int32, _P]),
@@ -297,6 +302,15 @@ class Model:
     def new_seq(self) -> "Seq":
         return Seq(self)
 
+    def submit(self, prompt, max_tokens: int, sampling: Sampling | None = None, stop_at_eog: bool = False) -> "Request":
+        """Queue a generation on the engine's scheduler thread (aios_request_submit); returns at once."""
+        toks = np.ascontiguousarray(prompt, dtype=np.int32)
+        sp = sampling if sampling is not None else Sampling()
+        h = _P()
+        _check(lib().aios_request_submit(self.h, _ptr(toks), toks.size, C.byref(sp), max_tokens,
+                                         REQ_STOP_AT_EOG if stop_at_eog else 0, C.byref(h)))
+        return Request(h, self)
+
     def forward_logits(self, tokens, n_past: int = 0) -> np.ndarray:
         toks = np.ascontiguousarray(tokens, dtype=np.int32)
         out = np.empty(self.info.n_vocab, dtype=np.float32)
@@ -310,6 +324,47 @@ class Model:
         sp = sampling if sampling is not None else Sampling()
         _check(lib().aios_generate(self.h, _ptr(toks), toks.size, C.byref(sp), max_tokens, _ptr(out), C.byref(n)))
         return out[: n.value].copy()
+
+
+REQ_STOP_AT_EOG = 1
+
+
+class Request:
+    """A queued generation: poll() never blocks, wait() blocks until there is something to poll."""
+
+    def __init__(self, handle, model: Model):
+        self.h, self.model = handle, model
+
+    def poll(self, cap: int = 256):
+        """-> (new tokens, done).  Raises AiosError if the request failed (after its tokens were taken)."""
+        out = np.empty(max(cap, 1), dtype=np.int32)
+        n, done = C.c_int32(0), C.c_int32(0)
+        _check(lib().aios_request_poll(self.h, _ptr(out), cap, C.byref(n), C.byref(done)))
+        return out[: n.value].copy(), bool(done.value)
+
+    def wait(self, timeout_ms: int = -1) -> bool:
+        r = C.c_int32(0)
+        _check(lib().aios_request_wait(self.h, timeout_ms, C.byref(r)))
+        return bool(r.value)
+
+    def cancel(self):
+        _check(lib().aios_request_cancel(self.h))
+
+    def result(self, timeout_ms: int = 60000) -> np.ndarray:
+        """Block until the request is finished; all its tokens."""
+        parts = []
+        while True:
+            if not self.wait(timeout_ms):
+                raise TimeoutError("request did not make progress")
+            toks, done = self.poll()
+            parts.append(toks)
+            if done:
+                return np.concatenate(parts) if parts else np.empty(0, np.int32)
+
+    def free(self):
+        if self.h:
+            lib().aios_request_free(self.h)
+            self.h = _P()
 
 
 class Seq:

@@ -2,8 +2,13 @@
 // all C++ exceptions and turns them into an AIOS_E_* code + thread-local message.
 #include <string.h>
 
+#include <atomic>
+#include <chrono>
+#include <condition_variable>
+#include <deque>
 #include <random>
 #include <string>
+#include <thread>
 #include <vector>
 
 #include "../../include/aios_b200.h"
@@ -13,7 +18,35 @@
 
 using namespace aios;
 
-struct aios_engine { Engine impl; explicit aios_engine(const aios_engine_opts &o) : impl(o) {} };
+// One queued generation (aios_request_submit).  The engine's scheduler thread fills `out`; the owner polls it.
+struct aios_request {
+    aios_model *m = nullptr;
+    std::vector<int32_t> prompt;
+    aios_sampling sp{};
+    int32_t max_tokens = 0, flags = 0;
+    std::mutex mu;
+    std::condition_variable cv;
+    std::vector<int32_t> out;   // generated tokens so far
+    size_t read = 0;            // how many of them the owner has taken
+    bool done = false, cancel = false, orphan = false;
+    int err = AIOS_OK;
+    std::string msg;
+};
+
+struct aios_engine {
+    Engine impl;
+    // scheduler thread: requests of all models of this engine, first come first served (one GPU stream)
+    std::thread worker;
+    std::mutex qmu;
+    std::condition_variable qcv;
+    std::deque<aios_request *> queue;
+    bool stop = false;
+    explicit aios_engine(const aios_engine_opts &o) : impl(o) {}
+    ~aios_engine();
+    void ensure_worker();
+    void run();
+    void serve(aios_request *r);
+};
 // host-only: the tokenizer of one GGUF file; either owns its file (aios_vocab_open) or borrows the model's
 struct aios_vocab {
     std::unique_ptr<GgufFile> own;
@@ -32,9 +65,112 @@ struct aios_model {
         if (!vocab_) vocab_.reset(new aios_vocab(*impl.file));
         return vocab_.get();
     }
+    aios_engine *owner = nullptr;
+    std::unique_ptr<Seq> req_seq;        // the KV slot queued requests run in (created on first use)
+    std::atomic<int> inflight{0};        // queued or running requests
     aios_model(Engine *e, const char *n, const char *p, int c) : impl(e, n, p, c) {}
 };
 struct aios_seq { Seq impl; explicit aios_seq(Model *m) : impl(m) {} };
+
+// ---------------------------------------------------------------- request scheduler (one thread per engine)
+static void finish_request(aios_request *r, int err, const std::string &msg) {
+    aios_model *m = r->m;
+    bool orphan;
+    {
+        std::lock_guard<std::mutex> lk(r->mu);
+        r->err = err;
+        r->msg = msg;
+        r->done = true;
+        orphan = r->orphan;
+        r->cv.notify_all();
+    }
+    // from here on the owner may free r at any moment (it sees done): do not touch it unless it is ours
+    m->inflight.fetch_sub(1);
+    if (orphan) delete r;  // the owner freed it while it was queued or running
+}
+
+void aios_engine::serve(aios_request *r) {
+    int err = AIOS_OK;
+    std::string msg;
+    try {
+        impl.make_current();
+        Model &M = r->m->impl;
+        const Tokenizer *tok = (r->flags & AIOS_REQ_STOP_AT_EOG) ? &r->m->vocab()->tok : nullptr;
+        {
+            std::lock_guard<std::mutex> lk(impl.mu);
+            if (!r->m->req_seq) r->m->req_seq.reset(new Seq(&M));
+            r->m->req_seq->reset();
+            r->m->req_seq->prefill(r->prompt.data(), (int)r->prompt.size());
+        }
+        Seq &s = *r->m->req_seq;
+        int left = r->max_tokens;
+        int32_t buf[16];
+        while (left > 0) {
+            {
+                std::lock_guard<std::mutex> lk(r->mu);
+                if (r->cancel) break;
+            }
+            int n;
+            {
+                std::lock_guard<std::mutex> lk(impl.mu);  // other API calls of this engine interleave between chunks
+                n = s.decode(r->sp, std::min(left, 16), buf);
+            }
+            if (n <= 0) break;  // context full
+            left -= n;
+            int keep = n;
+            bool stop = false;
+            if (tok)
+                for (int i = 0; i < n; i++)
+                    if (tok->is_eog(buf[i])) { keep = i; stop = true; break; }
+            {
+                std::lock_guard<std::mutex> lk(r->mu);
+                r->out.insert(r->out.end(), buf, buf + keep);
+            }
+            r->cv.notify_all();
+            if (stop) break;
+        }
+    } catch (const GgufError &e) {
+        err = e.code; msg = e.what();
+    } catch (const CudaError &e) {
+        cudaGetLastError();
+        err = AIOS_E_CUDA; msg = e.what();
+    } catch (const std::exception &e) {
+        err = AIOS_E_STATE; msg = e.what();
+    }
+    finish_request(r, err, msg);
+}
+
+void aios_engine::run() {
+    for (;;) {
+        aios_request *r;
+        {
+            std::unique_lock<std::mutex> lk(qmu);
+            qcv.wait(lk, [&] { return stop || !queue.empty(); });
+            if (queue.empty()) return;  // stop requested and nothing left
+            r = queue.front();
+            queue.pop_front();
+            if (stop) {
+                lk.unlock();
+                finish_request(r, AIOS_E_STATE, "engine destroyed before the request ran");
+                continue;
+            }
+        }
+        serve(r);
+    }
+}
+
+void aios_engine::ensure_worker() {
+    if (!worker.joinable()) worker = std::thread([this] { run(); });
+}
+
+aios_engine::~aios_engine() {
+    {
+        std::lock_guard<std::mutex> lk(qmu);
+        stop = true;
+    }
+    qcv.notify_all();
+    if (worker.joinable()) worker.join();
+}
 
 static thread_local std::string g_err;
 
@@ -99,6 +235,7 @@ int aios_model_load(aios_engine *e, const char *name, const char *gguf_path, int
         if (!e || !gguf_path || !out) return fail(AIOS_E_INVAL, "null argument");
         std::lock_guard<std::mutex> lk(e->impl.mu);
         *out = new aios_model(&e->impl, name ? name : "", gguf_path, n_ctx);
+        (*out)->owner = e;
         return AIOS_OK;
     });
 }
@@ -106,7 +243,9 @@ int aios_model_load(aios_engine *e, const char *name, const char *gguf_path, int
 int aios_model_unload(aios_model *m) {
     return guarded([&] {
         if (!m) return fail(AIOS_E_INVAL, "null model");
+        if (m->inflight.load() > 0) return fail(AIOS_E_STATE, "model still has queued or running requests");
         m->scratch.reset();
+        m->req_seq.reset();
         for (bool u : m->impl.slot_used)
             if (u) return fail(AIOS_E_STATE, "model still has live sequences");
         delete m;
@@ -349,6 +488,81 @@ int aios_generate(aios_model *m, const int32_t *prompt, int32_t n_prompt, const 
         *n_out = s.decode(d, max_tokens, out_tokens);
         return AIOS_OK;
     });
+}
+
+int aios_request_submit(aios_model *m, const int32_t *tokens, int32_t n, const aios_sampling *sp, int32_t max_tokens,
+                        int32_t flags, aios_request **out) {
+    return guarded([&] {
+        if (!m || !tokens || n <= 0 || !out || max_tokens < 0) return fail(AIOS_E_INVAL, "bad argument");
+        if (!m->owner) return fail(AIOS_E_STATE, "model has no engine");
+        if (n >= m->impl.hp.n_ctx) return fail(AIOS_E_STATE, "prompt does not fit in the context");
+        for (int32_t i = 0; i < n; i++)
+            if (tokens[i] < 0 || tokens[i] >= m->impl.hp.n_vocab) return fail(AIOS_E_INVAL, "token id out of range");
+        aios_request *r = new aios_request();
+        r->m = m;
+        r->prompt.assign(tokens, tokens + n);  // copied: the caller's buffer is free again when this returns
+        if (sp) r->sp = *sp;
+        r->max_tokens = std::min(max_tokens, m->impl.hp.n_ctx - n);
+        r->flags = flags;
+        m->inflight.fetch_add(1);
+        aios_engine *e = m->owner;
+        {
+            std::lock_guard<std::mutex> lk(e->qmu);
+            e->ensure_worker();
+            e->queue.push_back(r);
+        }
+        e->qcv.notify_one();
+        *out = r;
+        return (int)AIOS_OK;
+    });
+}
+
+int aios_request_poll(aios_request *r, int32_t *out, int32_t cap, int32_t *n_out, int32_t *done) {
+    return guarded([&] {
+        if (!r || !n_out || !done || cap < 0 || (cap > 0 && !out)) return fail(AIOS_E_INVAL, "bad argument");
+        std::lock_guard<std::mutex> lk(r->mu);
+        const size_t avail = r->out.size() - r->read;
+        const size_t take = std::min(avail, (size_t)cap);
+        if (take) memcpy(out, r->out.data() + r->read, take * sizeof(int32_t));
+        r->read += take;
+        *n_out = (int32_t)take;
+        *done = (r->done && r->read == r->out.size()) ? 1 : 0;
+        if (*done && r->err != AIOS_OK) return fail(r->err, r->msg);  // a failed request reports its error last
+        return (int)AIOS_OK;
+    });
+}
+
+int aios_request_wait(aios_request *r, int32_t timeout_ms, int32_t *ready) {
+    return guarded([&] {
+        if (!r || !ready) return fail(AIOS_E_INVAL, "bad argument");
+        std::unique_lock<std::mutex> lk(r->mu);
+        auto pred = [&] { return r->done || r->read < r->out.size(); };
+        if (timeout_ms < 0) r->cv.wait(lk, pred);
+        else r->cv.wait_for(lk, std::chrono::milliseconds(timeout_ms), pred);
+        *ready = pred() ? 1 : 0;
+        return (int)AIOS_OK;
+    });
+}
+
+int aios_request_cancel(aios_request *r) {
+    return guarded([&] {
+        if (!r) return fail(AIOS_E_INVAL, "null request");
+        std::lock_guard<std::mutex> lk(r->mu);
+        r->cancel = true;
+        return (int)AIOS_OK;
+    });
+}
+
+void aios_request_free(aios_request *r) {
+    if (!r) return;
+    bool del;
+    {
+        std::lock_guard<std::mutex> lk(r->mu);
+        r->cancel = true;
+        r->orphan = true;
+        del = r->done;  // finished: nobody else holds it.  Otherwise the scheduler deletes it when it is done with it.
+    }
+    if (del) delete r;
 }
 
 int aios_dequantize(aios_engine *e, int32_t type, const void *blocks, int64_t n, float *out) {

@@ -80,8 +80,12 @@ class LoadedModel:
         self.model = engine.load_model(name, path, context_length)
         self.vocab = self.model.vocab()
         self.n_ctx = self.model.info.n_ctx
-        self.seq = self.model.new_seq()
-        self.lock = threading.Lock()  # one KV slot: requests of one model run one after another
+        self.seq = self.model.new_seq()  # for direct (non-queued) use: tests, prompt caching
+        self.lock = threading.Lock()
+
+    def submit(self, tokens, max_tokens: int, sampling):
+        """Queue a generation on the engine's scheduler; stops at the first end-of-generation token."""
+        return self.model.submit(tokens, max_tokens, sampling, stop_at_eog=True)
 
     def close(self):
         with self.lock:
@@ -95,7 +99,8 @@ class EngineBackend:
     def __init__(self, device: int = 0, flags: int = 0):
         from .. import capi
         self.capi = capi
-        self.engine = capi.Engine(device=device, flags=flags)
+        # KV slots per model: one for the scheduler's queued requests, one for direct use, one spare
+        self.engine = capi.Engine(device=device, max_batch=3, flags=flags)
 
     def load(self, name: str, path: str, context_length: int) -> LoadedModel:
         if not os.path.isfile(path):
@@ -134,6 +139,21 @@ class InferenceEngine:
     def _generate(self, lm: LoadedModel, p: InferParams, chunk: int) -> Iterator[tuple[np.ndarray, int, bool]]:
         """Yields (new completion tokens without the end-of-generation token, n_prompt, finished)."""
         tokens, max_tokens, sampling = self._prepare(lm, p)
+        if hasattr(lm, "submit"):
+            # the engine's own scheduler thread (aios_request_*): handlers of concurrent RPCs queue up there, like
+            # concurrent HTTP requests did on llama-server's slot, and none of them blocks another one's polling
+            req = lm.submit(tokens, max_tokens, sampling)
+            try:
+                while True:
+                    if not req.wait(120000):  # the reference's HTTP timeout (inference.rs:81)
+                        raise TimeoutError("generation made no progress for 120 s")
+                    out, done = req.poll(chunk)
+                    if out.size or done:
+                        yield out, int(tokens.size), done
+                    if done:
+                        return
+            finally:
+                req.free()
         with lm.lock:
             lm.seq.reset()
             lm.seq.prefill(tokens)

@@ -210,6 +210,26 @@ int aios_seq_restore(aios_seq *s);
 int aios_generate(aios_model *m, const int32_t *prompt, int32_t n_prompt, const aios_sampling *sp,
                   int32_t max_tokens, int32_t *out_tokens, int32_t *n_out);
 
+/* ---- queued requests: what concurrent tonic handlers need (SURVEY.md §8b "Threading": the reference lets Infer calls
+ *      run in parallel against llama-server, runtime/src/main.rs:50-51, grpc_service.rs:86-141).  submit / poll /
+ *      wait / cancel / free are thread-safe and submit / poll / cancel never block on the GPU: one scheduler thread
+ *      per engine runs the requests first come first served in a KV slot of their model (the model needs one free
+ *      slot, see aios_engine_opts.max_batch), in chunks of 16 tokens between which other calls on the engine interleave.
+ *      The prompt is copied on submit.  max_tokens is clipped to the context. */
+typedef struct aios_request aios_request;
+#define AIOS_REQ_STOP_AT_EOG 1  /* stop at (and do not return) the first end-of-generation token, see aios_token_is_eog */
+int aios_request_submit(aios_model *m, const int32_t *tokens, int32_t n, const aios_sampling *sp, int32_t max_tokens,
+                        int32_t flags, aios_request **out);
+/* take up to cap new tokens; *done = 1 once the request has finished AND everything was taken.  A request that
+ * failed returns its error code (message in aios_last_error) from the poll that would have set *done. */
+int aios_request_poll(aios_request *r, int32_t *out_tokens, int32_t cap, int32_t *n_out, int32_t *done);
+/* block until there is something to poll or the request is finished (timeout_ms < 0: no timeout); *ready = 0 on timeout */
+int aios_request_wait(aios_request *r, int32_t timeout_ms, int32_t *ready);
+/* ask the scheduler to stop at the next chunk boundary; tokens already generated stay pollable */
+int aios_request_cancel(aios_request *r);
+/* may be called at any time; a request that is still queued or running is cancelled and reclaimed by the scheduler */
+void aios_request_free(aios_request *r);
+
 /* ---- test / parity hooks (SURVEY.md §8b "test hooks") */
 /* dequantise n elements (whole blocks) of ggml_type on the GPU: host blocks -> host floats.
  * Bit-exact against ggml's dequantize_row_* as restated by gguf-py. */

@@ -90,6 +90,33 @@ def test_infer_engine_on_device(backend, chat_gguf):
         backend.unload(lm)
 
 
+def test_concurrent_infer_rpcs(backend, chat_gguf):
+    """Eight Infer / StreamInfer RPCs at once (tonic handlers run concurrently in the reference): all are served, and a
+    pinned seed gives every caller the same text as a lone call."""
+    import threading
+    lm = backend.load("c", chat_gguf, 256)
+    try:
+        eng = InferenceEngine(stream_chunk_tokens=4)
+        p = InferParams(prompt="Hello, world!", max_tokens=20, temperature=0.9, seed=11)
+        alone = eng.infer(lm, "c", p)
+        results = [None] * 8
+
+        def run(i):
+            if i % 2:
+                results[i] = "".join(t for t, _ in eng.stream_infer(lm, "c", p))
+            else:
+                results[i] = eng.infer(lm, "c", p).text
+
+        ts = [threading.Thread(target=run, args=(i,)) for i in range(8)]
+        for t in ts:
+            t.start()
+        for t in ts:
+            t.join(60)
+        assert results == [alone.text] * 8
+    finally:
+        backend.unload(lm)
+
+
 def test_grpc_service_on_device(backend, chat_gguf):
     srv = RuntimeServer(backend, addr="127.0.0.1:0", model_dir=os.path.dirname(chat_gguf), health_interval_s=3600.0)
     srv.start(do_autoload=True)  # main.rs:65-132: picks the .gguf up by itself
