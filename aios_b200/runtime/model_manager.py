@@ -63,6 +63,7 @@ class ManagedModel:
     gpu_layers: int = 0
     threads: int = DEFAULT_THREADS
     handle: Any = None
+    http: Any = None  # the model's OpenAI-compatible endpoint on `port`, when the manager was given an http_factory
     loaded_evt: threading.Event = field(default_factory=threading.Event, repr=False)
 
 
@@ -101,7 +102,10 @@ def model_to_status(m: ManagedModel) -> ModelStatusRecord:
 
 
 class ModelManager:
-    def __init__(self, backend: Backend, model_dir: Optional[str] = None):
+    def __init__(self, backend: Backend, model_dir: Optional[str] = None, http_factory=None):
+        # http_factory(name, handle, port) -> object with .close(): serves the loaded model on its port the way the
+        # llama-server child did; None = the port stays a pseudo-port
+        self.http_factory = http_factory
         # model_manager.rs:115-131
         self.backend = backend
         self.model_dir = model_dir or os.environ.get("AIOS_MODEL_DIR", DEFAULT_MODEL_DIR)
@@ -136,8 +140,15 @@ class ModelManager:
                                    threads=threads)
             self.models[name] = managed
         log.info("Loading model %s path=%s port=%d ctx=%d", name, path, port, ctx)
+        http = None
         try:
             handle = self.backend.load(name, path, ctx)
+            if self.http_factory is not None:
+                try:
+                    http = self.http_factory(name, handle, port)
+                except Exception:
+                    self.backend.unload(handle)
+                    raise
         except Exception as e:  # the reference's "exited early" branch: recorded in-band AND returned as Err
             msg = str(e)
             with self.lock:
@@ -148,10 +159,13 @@ class ModelManager:
         with self.lock:
             if managed.status.kind == ModelState.UNLOADING or self.models.get(name) is not managed:
                 # unloaded while it was loading: drop the fresh handle
+                if http is not None:
+                    http.close()
                 self.backend.unload(handle)
                 managed.loaded_evt.set()
                 return model_to_status(managed)
             managed.handle = handle
+            managed.http = http
             managed.status = ModelState(ModelState.READY)
             managed.loaded_evt.set()
             log.info("Model %s is ready", name)
@@ -165,8 +179,11 @@ class ModelManager:
                 raise KeyError(f"Model '{name}' not found")
             model.status = ModelState(ModelState.UNLOADING)
             handle, model.handle = model.handle, None
+            http, model.http = model.http, None
             del self.models[name]
         log.info("Unloading model %s", name)
+        if http is not None:
+            http.close()
         if handle is not None:
             self.backend.unload(handle)
         log.info("Model %s unloaded", name)

@@ -208,9 +208,15 @@ class RuntimeServer:
     """The running process of main.rs: service + health task + listener."""
 
     def __init__(self, backend, addr: str = LISTEN_ADDR, model_dir: Optional[str] = None, max_workers: int = 16,
-                 health_interval_s: float = HEALTH_CHECK_INTERVAL_S, inference_engine: Optional[InferenceEngine] = None):
-        self.manager = ModelManager(backend, model_dir)
-        self.service = AIRuntimeService(self.manager, inference_engine or InferenceEngine())
+                 health_interval_s: float = HEALTH_CHECK_INTERVAL_S, inference_engine: Optional[InferenceEngine] = None,
+                 openai_http: bool = False):
+        engine = inference_engine or InferenceEngine()
+        factory = None
+        if openai_http:  # every loaded model also answers OpenAI-compatible HTTP on its ModelStatus.port
+            from .openai_http import OpenAIServer
+            factory = lambda name, handle, port: OpenAIServer(handle, name, port, engine).start()  # noqa: E731
+        self.manager = ModelManager(backend, model_dir, http_factory=factory)
+        self.service = AIRuntimeService(self.manager, engine)
         self.server = grpc.server(futures.ThreadPoolExecutor(max_workers=max_workers))
         self.server.add_generic_rpc_handlers((generic_handler(self.service),))
         self.port = self.server.add_insecure_port(addr)
@@ -246,11 +252,14 @@ def main(argv=None):
     ap.add_argument("--addr", default=LISTEN_ADDR)
     ap.add_argument("--device", type=int, default=int(os.environ.get("LOCAL_RANK", "0")))
     ap.add_argument("--model-dir", default=None)
+    ap.add_argument("--openai-http", action="store_true",
+                    help="serve every loaded model on its port (8080, 8081, ...) with the OpenAI-compatible HTTP API")
     args = ap.parse_args(argv)
     logging.basicConfig(level=logging.INFO, format="%(asctime)s %(levelname)s %(message)s")
     from .inference import EngineBackend
     log.info("aiOS AI Runtime starting...")
-    srv = RuntimeServer(EngineBackend(device=args.device), addr=args.addr, model_dir=args.model_dir).start()
+    srv = RuntimeServer(EngineBackend(device=args.device), addr=args.addr, model_dir=args.model_dir,
+                        openai_http=args.openai_http).start()
     try:
         srv.server.wait_for_termination()
     except KeyboardInterrupt:
