@@ -14,13 +14,13 @@
 // kernel) + a double-precision warp-shuffle reduction + a fused epilogue (store / residual add /
 // SwiGLU / running arg-max).  Matrices of one type that share the input (attn_q/k/v; ffn_gate/up)
 // ride in one launch; CTAs are split between them by byte share.
-#define GEMV_CORE_WARPS 8
+#define GEMV_CORE_WARPS 16
 #include "gemv_core.cuh"
 
 namespace aios {
 
 template <int TYPE>
-__global__ void __launch_bounds__(GEMV_THREADS, 2) gemv_kernel(const GemvParams p) {
+__global__ void __launch_bounds__(GEMV_THREADS, 1) gemv_kernel(const GemvParams p) {
     extern __shared__ __align__(16) uint8_t smem[];
     __shared__ double red[GEMV_WARPS];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -262,7 +262,7 @@ __device__ __forceinline__ int gemv_my_segment(const GemvParams &p) {
 }
 
 template <int TYPE, int NB>
-__global__ void __launch_bounds__(GEMV_THREADS, 2) gemv_db_kernel(const GemvParams p) {
+__global__ void __launch_bounds__(GEMV_THREADS, 1) gemv_db_kernel(const GemvParams p) {
     extern __shared__ __align__(16) uint8_t smem[];
     __shared__ double red[GEMV_WARPS];
     gemv_db_body<TYPE, NB>(p, gemv_my_segment(p), smem, red);
@@ -271,7 +271,7 @@ __global__ void __launch_bounds__(GEMV_THREADS, 2) gemv_db_kernel(const GemvPara
 // attn_q / attn_k (Q4_K) and attn_v (Q6_K in half of the layers of a Q4_K_M file) in ONE launch: a CTA serves one
 // matrix, so the type is CTA-uniform and each CTA builds only the activation image its type needs.  Saves a launch
 // (hand-over + a second RMSNorm/quantisation prologue) in every such layer.
-__global__ void __launch_bounds__(GEMV_THREADS, 2) gemv_db_mixed_kernel(const GemvParams p) {
+__global__ void __launch_bounds__(GEMV_THREADS, 1) gemv_db_mixed_kernel(const GemvParams p) {
     extern __shared__ __align__(16) uint8_t smem[];
     __shared__ double red[GEMV_WARPS];
     const int seg = gemv_my_segment(p);
@@ -284,7 +284,7 @@ size_t gemv_smem_bytes(int k) { return act_image_bytes(k); }
 static size_t seg_row_bytes(const WPlanes &w) { return tensor_bytes(w.type, 1, w.k); }
 
 int gemv_plan_grid(GemvParams &p, int n_sms) {
-    const int target = n_sms * 2;  // two resident CTAs per SM (launch bounds)
+    const int target = n_sms;  // one 16-warp CTA per SM
     if (p.epi == EPI_SWIGLU) {
         const int groups = (p.seg[0].n_rows + GEMV_WARPS - 1) / GEMV_WARPS;
         const int g = groups < target ? groups : target;
