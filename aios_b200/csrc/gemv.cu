@@ -6,14 +6,21 @@
 // 64-weight unit (dp4a); every unit contributes one f32 term, and the terms are summed in double —
 // an order-free sum, so the result is bit-identical to the oracle's for any work split.
 //
-// One launch = [optional RMSNorm] + activation quantisation (done redundantly by every CTA into
-// shared memory: K bytes, so no separate launch and no HBM round trip) + the weight stream
-// (128-bit coalesced no-allocate loads from the planes of layout.cuh, two rows x two lane-iterations
-// = up to 12 loads in flight per lane; the first pass is issued BEFORE the activation prologue, and
-// before the programmatic-dependent-launch wait, because weights do not depend on the previous
-// kernel) + a double-precision warp-shuffle reduction + a fused epilogue (store / residual add /
-// SwiGLU / running arg-max).  Matrices of one type that share the input (attn_q/k/v; ffn_gate/up)
-// ride in one launch; CTAs are split between them by byte share.
+// One launch = [optional RMSNorm] + activation quantisation (done by every CTA into its own shared
+// memory: K bytes, so no separate launch and no HBM round trip) + the weight stream (128-bit coalesced
+// no-allocate loads from the planes of layout.cuh; the first passes are issued BEFORE the activation
+// prologue, and before the programmatic-dependent-launch wait, because weights do not depend on the
+// previous kernel) + a double-precision warp-shuffle reduction + a fused epilogue (store / residual
+// add / SwiGLU / running arg-max / RoPE + f16 KV append for q,k,v).  Matrices that share the input
+// (attn_q/k/v, also when attn_v is Q6_K next to Q4_K q/k; ffn_gate/up) ride in one launch; CTAs are
+// split between them by byte share.
+//
+// Two kernels: gemv_db_kernel (default; K a multiple of 2048) keeps two half-size weight images per
+// warp so loads stay in flight through the warp's own arithmetic; gemv_kernel is the single-image
+// original and the fallback for other K.  One 16-warp CTA per SM: the activation image is built once
+// per SM.  Measured steps, Mistral-7B Q4_K_M ms/token: 1.92 single image -> 1.79 double buffered ->
+// 1.72 q/k/v in one launch -> 1.68 RoPE epilogue + staged attention -> 1.66 one CTA per SM
+// (profiles/r01_v5_summary.md).
 #define GEMV_CORE_WARPS 16
 #include "gemv_core.cuh"
 

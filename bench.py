@@ -319,7 +319,7 @@ def main():
                        "wall_ms_per_step": wall_ms_max / args.steps},
             "roofline": {"bound": "hbm", "achieved": gemv_gbs, "peak": peak, "unit": "GB/s", "frac": gemv_gbs / peak,
                          "traffic": traffic, "peak_source": peak_src,
-                         "kernel": "gemv_kernel (fused norm + act-quant + dequant-GEMV)", "launches_per_token": n_gemv // prof.n_tokens,
+                         "kernel": "gemv_db_kernel / gemv_db_mixed_kernel (fused norm + act-quant + dequant-GEMV + epilogue)", "launches_per_token": n_gemv // prof.n_tokens,
                          "algorithmic_bytes_per_token": gemv_bytes_per_token,
                          "avg_launch_us": prof.ms_gemv * 1e3 / max(1, n_gemv),
                          "whole_token_frac_of_peak": bytes_per_token * value / world / 1e9 / peak,
