@@ -28,7 +28,7 @@
 
 namespace aios {
 
-constexpr int AS_THREADS = 256;
+constexpr int AS_THREADS = 512;
 constexpr int AS_WARPS = AS_THREADS / 32;
 constexpr int AS_BATCH = 8;  // row-groups in flight per lane (and the width of the butterfly)
 
@@ -86,7 +86,7 @@ __device__ __forceinline__ int butterfly_index(int lane) {
 
 // dynamic smem: sc[n_ctx] f32 | part[AS_WARPS][DPC] f64 | knew[HD] f16 | vnew[HD] f16
 template <int HD, int SPLIT>
-__global__ void __launch_bounds__(AS_THREADS, 2) attn_split_kernel(const AttnParams p) {
+__global__ void __launch_bounds__(AS_THREADS, 1) attn_split_kernel(const AttnParams p) {
     constexpr int LPR = HD / 8, RPW = 32 / LPR;       // K: lanes per row, rows per warp-load
     constexpr int DPC = HD / SPLIT;                   // output dims of this CTA
     constexpr int VL = DPC / 8, RPV = 32 / VL;        // V: lanes per row slice, rows per warp-load

@@ -158,8 +158,28 @@ __device__ void prep_activations(const float *__restrict__ x, const float *__res
                                  const ActSmem &s, double *red) {
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int nslab = k / 256;
-    if (nslab <= 2 * GEMV_WARPS) {
-        // K <= 4096: each lane keeps its (up to) 16 values in registers — one trip to L2
+    if (nslab <= GEMV_WARPS) {
+        // one slab per warp (K <= 4096 with 16 warps): x and the norm weights are requested together, so the norm
+        // weights do not cost a second trip to L2 after the sum of squares
+        float v0[8], w0[8];
+#pragma unroll
+        for (int i = 0; i < 8; i++) v0[i] = 0.f;
+        if (warp < nslab) {
+            load8(x + warp * 256 + lane * 8, v0);
+            if (norm_w) load8(norm_w + warp * 256 + lane * 8, w0);
+        }
+        if (norm_w) {
+            const double ss = block_sum(sumsq8(v0), red);
+            const float mean = (float)(ss / (double)k);
+            const float scale = __fdiv_rn(1.0f, __fsqrt_rn(__fadd_rn(mean, eps)));
+            if (warp < nslab) {
+#pragma unroll
+                for (int i = 0; i < 8; i++) v0[i] = __fmul_rn(__fmul_rn(v0[i], scale), w0[i]);
+            }
+        }
+        if (warp < nslab) quant_slab<PERM>(v0, warp, k, s);
+    } else if (nslab <= 2 * GEMV_WARPS) {
+        // each lane keeps its (up to) 16 values in registers — one trip to L2
         const int b0 = warp, b1 = warp + GEMV_WARPS;
         float v0[8], v1[8];
 #pragma unroll
