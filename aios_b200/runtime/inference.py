@@ -10,8 +10,10 @@ tokenizer, prefill, the decode loop, the sampler chain (top-k 40, top-p 0.95, mi
 §8a D2-D5) — happens in the engine; the sampler runs on the device so a decode step moves 4 bytes to the host.
 
 Differences, on purpose: ``stream_infer`` really streams (the reference buffers the whole SSE body first,
-inference.rs:261); JSON-mode constrained sampling (``response_format: json_object``, :119-121) is not built yet
- — unary ``infer`` samples unconstrained.
+inference.rs:261).  JSON mode (``response_format: json_object``, :119-121): requests with
+``json_mode`` are sampled under ``json_grammar.JsonPrefix`` — the candidates come back to the host every step
+(128 KB of logits) and only pieces that keep the text a prefix of one JSON object survive; the sampler chain
+(top-k 40, top-p, min-p, temperature) then runs on the survivors.
 
 There is no CPU fallback: ``EngineBackend`` needs libaios_b200.so and a B200.
 """
@@ -44,6 +46,7 @@ class InferParams:
     requesting_agent: str = ""
     task_id: str = ""
     seed: Optional[int] = None  # not on the wire; tests pin it
+    json_mode: bool = False     # response_format json_object: what unary Infer always asks for (inference.rs:119-121)
 
 
 @dataclass
@@ -170,9 +173,66 @@ class InferenceEngine:
                 yield out, int(tokens.size), left <= 0
             yield np.empty(0, np.int32), int(tokens.size), True
 
+    # -- JSON mode: llama-server turns response_format json_object into a grammar that masks the sampler's candidates
+    #    (SURVEY.md §8f-3).  Here the sampler chain runs on the host for these requests: per step the logits come back
+    #    (128 KB D2H), candidates are walked best first and kept only if json_grammar accepts their piece.
+    @staticmethod
+    def _pieces(lm) -> list:
+        pieces = getattr(lm, "_piece_bytes", None)
+        if pieces is None:
+            n = lm.vocab.info.n_tokens
+            pieces = [lm.vocab.detokenize([i]) for i in range(n)]
+            lm._piece_bytes = pieces
+        return pieces
+
+    def _generate_json(self, lm, p: InferParams):
+        """-> (completion tokens, n_prompt).  Stops when the JSON object closes, at max_tokens, or when nothing fits."""
+        from .json_grammar import JsonPrefix
+        tokens, max_tokens, sampling = self._prepare(lm, p)
+        pieces = self._pieces(lm)
+        rng = np.random.default_rng(sampling.seed & 0xFFFFFFFF)
+        temp, top_k, top_p, min_p = float(sampling.temperature), int(sampling.top_k), float(sampling.top_p), float(sampling.min_p)
+        state, out = JsonPrefix(), []
+        with lm.lock:
+            lm.seq.reset()
+            lm.seq.prefill(tokens)
+            for _ in range(max_tokens):
+                logits = lm.seq.logits()
+                n_look = min(256, logits.size)
+                order = np.argpartition(-logits, n_look - 1)[:n_look]
+                order = order[np.argsort(-logits[order], kind="stable")]
+                cand = [int(t) for t in order if state.accepts(pieces[int(t)])][: max(top_k, 1)]
+                if not cand:  # rare: nothing in the best 256 fits — look at the whole vocabulary
+                    for t in np.argsort(-logits, kind="stable"):
+                        if state.accepts(pieces[int(t)]):
+                            cand = [int(t)]
+                            break
+                if not cand:
+                    break
+                lg = logits[cand].astype(np.float64)
+                pr = np.exp(lg - lg[0])
+                keep = len(cand)
+                if top_p < 1.0:
+                    keep = min(keep, int(np.searchsorted(np.cumsum(pr / pr.sum()), top_p) + 1))
+                if min_p > 0.0:
+                    keep = min(keep, max(1, int((pr >= min_p * pr[0]).sum())))
+                pr = np.exp((lg[:keep] - lg[0]) / max(temp, 1e-6))
+                tok = cand[int(rng.choice(keep, p=pr / pr.sum()))]
+                state.feed(pieces[tok])
+                out.append(tok)
+                if state.complete:
+                    break
+                lm.seq.prefill(np.array([tok], np.int32))
+        return np.asarray(out, np.int32), int(tokens.size)
+
     def infer(self, lm: LoadedModel, model_name: str, p: InferParams) -> InferResult:
         """inference.rs:94-186"""
         start = time.monotonic()
+        if p.json_mode and hasattr(lm.seq, "logits"):
+            comp, n_prompt = self._generate_json(lm, p)
+            text = lm.vocab.detokenize(comp).decode("utf-8", "replace")
+            return InferResult(text=text, tokens_used=n_prompt + int(comp.size),
+                               latency_ms=int((time.monotonic() - start) * 1000), model_used=model_name)
         log.info("Sending inference request model=%s max_tokens=%d temperature=%.3g agent=%s task=%s", model_name,
                  effective_max_tokens(p.max_tokens), effective_temperature(p.temperature), p.requesting_agent, p.task_id)
         done_tokens, n_prompt = [], 0

@@ -13,8 +13,8 @@ shape ``ChatCompletionRequest`` runtime/src/inference.rs:20-36, response fields 
   ``finish_reason`` is set, then ``data: [DONE]``.
 
 The first ``system`` message and the last ``user`` message are rendered through the model's chat format (one turn,
-like the reference sends, inference.rs:363-376).  ``response_format: json_object`` is accepted and ignored (constrained
-sampling is not built yet).  Binds 127.0.0.1 only, like the reference's ``--host 127.0.0.1`` (model_manager.rs:197-198).
+like the reference sends, inference.rs:363-376).  ``response_format: {"type": "json_object"}`` switches the non-streaming call to
+grammar-constrained sampling (``json_grammar.py``).  Binds 127.0.0.1 only, like the reference's ``--host 127.0.0.1`` (model_manager.rs:197-198).
 """
 from __future__ import annotations
 
@@ -38,8 +38,10 @@ def _messages_to_params(body: dict) -> InferParams:
     users = [m.get("content", "") for m in msgs if m.get("role") == "user"]
     if not users:
         raise ValueError("no message with role 'user'")
+    rf = body.get("response_format")
     return InferParams(prompt=str(users[-1]), system_prompt=str(system or ""), max_tokens=int(body.get("max_tokens") or 0),
-                       temperature=float(body.get("temperature") or 0.0), seed=body.get("seed"))
+                       temperature=float(body.get("temperature") or 0.0), seed=body.get("seed"),
+                       json_mode=isinstance(rf, dict) and rf.get("type") == "json_object")
 
 
 class OpenAIServer:
@@ -106,11 +108,16 @@ class OpenAIServer:
         try:
             pieces, n_prompt, n_comp = [], 0, 0
             limit = params.max_tokens if params.max_tokens > 0 else 512
-            for toks, n_prompt, finished in self.engine._generate(self.handle, params, chunk=64):
+            if params.json_mode and hasattr(self.handle.seq, "logits"):  # grammar-constrained (json_grammar.py)
+                toks, n_prompt = self.engine._generate_json(self.handle, params)
                 pieces.append(toks)
-                n_comp += int(toks.size)
-                if finished:
-                    break
+                n_comp = int(toks.size)
+            else:
+                for toks, n_prompt, finished in self.engine._generate(self.handle, params, chunk=64):
+                    pieces.append(toks)
+                    n_comp += int(toks.size)
+                    if finished:
+                        break
             import numpy as np
             comp = np.concatenate(pieces) if pieces else np.empty(0, np.int32)
             text = self.handle.vocab.detokenize(comp).decode("utf-8", "replace")

@@ -114,7 +114,9 @@ class AIRuntimeService:
                  req.requesting_agent, req.task_id)
         handle, name = self.resolve_model(req, context)
         try:
-            r = self.inference_engine.infer(handle, name, self._params(req))
+            params = self._params(req)
+            params.json_mode = True  # the reference's unary call always sets response_format json_object (inference.rs:119-121)
+            r = self.inference_engine.infer(handle, name, params)
         except Exception as e:
             log.error("Inference failed model=%s: %s", name, e)
             context.abort(grpc.StatusCode.INTERNAL, f"Inference failed: {e}")
