@@ -633,6 +633,33 @@ int aios_matvec(aios_engine *e, int32_t type, const void *w_blocks, int64_t n_ro
     });
 }
 
+int aios_matmul(aios_engine *e, int32_t type, const void *w_blocks, int64_t n_rows, int64_t k, const float *x, int32_t n_tok,
+                const float *norm_w, float rms_eps, float *y) {
+    return guarded([&] {
+        if (!e || !w_blocks || !x || !y || n_rows <= 0 || k <= 0 || n_tok <= 0) return fail(AIOS_E_INVAL, "bad argument");
+        if (!gemm_q_usable(type, (int)k)) return fail(AIOS_E_UNSUPPORTED, "aios_matmul: Q4_K / Q8_0 weights, k a multiple of 256");
+        if (n_tok > 32) return fail(AIOS_E_RANGE, "aios_matmul: at most 32 tokens per call");
+        std::lock_guard<std::mutex> lk(e->impl.mu);
+        Engine &E = e->impl;
+        E.make_current();
+        DevMatrix dm;
+        make_dev_matrix(E, type, w_blocks, n_rows, k, dm);
+        const int T8 = (n_tok + 7) / 8 * 8;
+        DevBuf dx((size_t)T8 * k * 4), dy((size_t)n_tok * n_rows * 4), dn, img(gemm_images_bytes((int)k, T8));
+        CUDA_CHECK(cudaMemsetAsync(dx.p, 0, dx.bytes, E.stream));  // padding tokens: zeros
+        CUDA_CHECK(cudaMemcpyAsync(dx.p, x, (size_t)n_tok * k * 4, cudaMemcpyHostToDevice, E.stream));
+        if (norm_w) {
+            dn = DevBuf((size_t)k * 4);
+            CUDA_CHECK(cudaMemcpyAsync(dn.p, norm_w, (size_t)k * 4, cudaMemcpyHostToDevice, E.stream));
+        }
+        launch_quant_rows(type, dx.as<float>(), k, norm_w ? dn.as<float>() : nullptr, rms_eps, (int)k, T8, img.as<uint8_t>(), E.stream);
+        launch_gemm_q(dm.w, img.as<uint8_t>(), n_tok, dy.as<float>(), n_rows, EPI_STORE, E.stream);
+        CUDA_CHECK(cudaMemcpyAsync(y, dy.p, dy.bytes, cudaMemcpyDeviceToHost, E.stream));
+        CUDA_CHECK(cudaStreamSynchronize(E.stream));
+        return (int)AIOS_OK;
+    });
+}
+
 int aios_forward_logits(aios_model *m, const int32_t *tokens, int32_t n, int32_t n_past, float *logits_out) {
     return guarded([&] {
         if (!m || !tokens || n <= 0 || !logits_out || n_past < 0) return fail(AIOS_E_INVAL, "bad argument");

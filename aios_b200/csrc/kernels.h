@@ -71,6 +71,15 @@ bool gemv_staged_usable(const GemvParams &p, int n_sms);
 void launch_gemv_staged(const GemvParams &p, int n_sms, cudaStream_t st, bool pdl);
 void gemv_staged_init();
 
+// ---- gemm_q.cu : multi-token (prompt chunk) dequant GEMM on int8 tensor cores, bit-identical to T GEMV calls
+// per-token Q8_K / Q8_0 activation images in global memory (optionally RMS-normed first); x row stride ldx floats
+void launch_quant_rows(int weight_type, const float *x, int64_t ldx, const float *norm_w, float eps, int k, int T,
+                       uint8_t *images, cudaStream_t st);
+size_t gemm_images_bytes(int k, int T);  // allocate for T rounded up to a multiple of 8
+bool gemm_q_usable(int type, int k);     // Q4_K / Q8_0
+// out[t][row] (row stride ldo floats) = or += dot, t < T <= 32; epi = EPI_STORE or EPI_ADD
+void launch_gemm_q(const WPlanes &w, const uint8_t *images, int T, float *out, int64_t ldo, int epi, cudaStream_t st);
+
 // ---- gemv_ring.cu : the same fused op fed by a TMA ring (stream tiles of layout.cuh)
 // build the tiles of a [N][K] matrix (b == nullptr) or the PAIR tiles of two matrices from their planes
 size_t tiles_total_bytes(int type, int n_rows, int k, bool pair);

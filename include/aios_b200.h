@@ -238,6 +238,11 @@ int aios_dequantize(aios_engine *e, int32_t ggml_type, const void *blocks, int64
  * integer block dots): host in, host out.  If norm_w != NULL, x is RMS-normed first. */
 int aios_matvec(aios_engine *e, int32_t ggml_type, const void *w_blocks, int64_t n_rows, int64_t k,
                 const float *x, const float *norm_w, float rms_eps, float *y);
+/* Y[n_tok][n_rows] = X[n_tok][k] . W[n_rows,k]^T for a chunk of 1..32 tokens through the tensor-core kernel
+ * (gemm_q.cu: int8 MMA on the 32-weight sub-block dots, weights streamed once for all tokens).  Same numerics as
+ * n_tok calls of aios_matvec, bit for bit.  Q4_K and Q8_0 weights (AIOS_E_UNSUPPORTED otherwise); host in, host out. */
+int aios_matmul(aios_engine *e, int32_t ggml_type, const void *w_blocks, int64_t n_rows, int64_t k, const float *x,
+                int32_t n_tok, const float *norm_w, float rms_eps, float *y);
 /* logits of the last of n tokens fed at position n_past into a scratch sequence */
 int aios_forward_logits(aios_model *m, const int32_t *tokens, int32_t n, int32_t n_past, float *logits_out);
 /* read back one layer's KV rows [pos0, pos0+n) as fp16 bit patterns: k_out/v_out[n][n_head_kv*head_dim] */

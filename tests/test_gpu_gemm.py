@@ -1,0 +1,50 @@
+"""GPU parity of the multi-token tensor-core GEMM (gemm_q.cu, aios_matmul): Y[T][N] must equal T oracle mat-vecs
+bit for bit — the int8 MMA only changes HOW the 32-weight integer dots are formed, not their values, and the scale
+arithmetic and the double-precision sums around them are the GEMV's."""
+import numpy as np
+import pytest
+
+from aios_b200 import capi
+from aios_b200 import gguf_synth as gs
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("qt", [gs.Q4_K, gs.Q8_0])
+@pytest.mark.parametrize("shape", [(16, 256, 8), (37, 512, 3), (64, 2048, 32), (130, 4096, 17), (70, 5632, 9), (48, 14336, 24)])
+def test_matmul_equals_oracle_matvecs(engine, oracle, qt, shape):
+    n, k, t = shape
+    rng = np.random.default_rng([qt, n, k, t])
+    w = gs.random_blocks(qt, n * k // gs.BLOCK[qt][0], rng, 0.02)
+    x = rng.standard_normal((t, k), dtype=np.float32)
+    x[0, :9] = 0
+    if t > 2:
+        x[2] = 0  # an all-zero token
+    got = engine.matmul(qt, w, n, k, x)
+    assert got.shape == (t, n)
+    for i in range(t):
+        ref = oracle.matvec(qt, w, n, k, x[i])
+        assert np.array_equal(got[i].view(np.uint32), ref.view(np.uint32)), (i, np.abs(got[i] - ref).max())
+
+
+@pytest.mark.parametrize("qt", [gs.Q4_K, gs.Q8_0])
+def test_matmul_with_rmsnorm_equals_matvec(engine, qt):
+    n, k, t = 96, 2048, 12
+    rng = np.random.default_rng(5)
+    w = gs.random_blocks(qt, n * k // gs.BLOCK[qt][0], rng, 0.02)
+    x = rng.standard_normal((t, k), dtype=np.float32) * 2
+    nw = (rng.random(k, dtype=np.float32) * 0.4 + 0.8).astype(np.float32)
+    got = engine.matmul(qt, w, n, k, x, norm_w=nw, eps=1e-5)
+    for i in range(t):
+        ref = engine.matvec(qt, w, n, k, x[i], norm_w=nw, eps=1e-5)
+        assert np.array_equal(got[i].view(np.uint32), ref.view(np.uint32)), i
+
+
+def test_matmul_argument_errors(engine):
+    w = np.zeros(210 * 4, np.uint8)
+    with pytest.raises(capi.AiosError) as e:
+        engine.matmul(gs.Q6_K, w, 4, 256, np.zeros((2, 256), np.float32))
+    assert e.value.code == capi.E_UNSUPPORTED
+    with pytest.raises(capi.AiosError) as e:
+        engine.matmul(gs.Q4_K, np.zeros(144 * 4, np.uint8), 4, 256, np.zeros((33, 256), np.float32))
+    assert e.value.code == capi.E_RANGE
