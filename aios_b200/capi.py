@@ -27,6 +27,7 @@ ENGINE_ATTN_CLUSTER = 64
 ENGINE_USE_RING = 128
 ENGINE_NO_ROPE_EPILOGUE = 256
 ENGINE_PRODUCER_QUANT = 512
+ENGINE_NO_GEMM = 1024
 
 
 class AiosError(RuntimeError):

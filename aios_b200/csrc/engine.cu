@@ -507,7 +507,15 @@ void Seq::prefill(const int32_t *tokens, int n) {
     m->eng->make_current();
     cudaStream_t st = m->eng->stream;
     CUDA_CHECK(cudaMemcpyAsync(prompt.p, tokens, (size_t)n * 4, cudaMemcpyHostToDevice, st));
-    for (int i = 0; i < n; i++) launch_token_pass(true, i, n_past + i, i == n - 1, st, nullptr);
+    if (n >= 4 && !(m->eng->flags & AIOS_ENGINE_NO_GEMM)) {
+        // prompt chunks of up to 32 tokens: every Q4_K / Q8_0 matrix is streamed once per chunk (gemm_q.cu)
+        for (int i = 0; i < n; i += 32) {
+            const int T = std::min(32, n - i);
+            prefill_chunk(i, T, n_past + i, i + T == n, st);
+        }
+    } else {
+        for (int i = 0; i < n; i++) launch_token_pass(true, i, n_past + i, i == n - 1, st, nullptr);
+    }
     CUDA_CHECK(cudaGetLastError());
     CUDA_CHECK(cudaStreamSynchronize(st));
     n_past += n;
@@ -539,6 +547,89 @@ void Seq::ensure_graph(const aios_sampling &sp) {
     cudaGraphDestroy(g);
     CUDA_CHECK(e);
     graph_sampling = sp;
+}
+
+// One prompt chunk of T <= 32 tokens at positions pos0 .. pos0+T-1.  Same arithmetic as T token passes (the logits and
+// the KV rows come out bit-identical); what changes is the weight traffic: every Q4_K / Q8_0 matrix is streamed once
+// for the whole chunk by the tensor-core GEMM (gemm_q.cu).  Matrices of other types (Q6_K, Q5_K) and attention still
+// go token by token through the decode kernels.
+void Seq::prefill_chunk(int idx0, int T, int pos0, bool want_logits, cudaStream_t st) {
+    const HParams &hp = m->hp;
+    const int E = hp.n_embd, FF = hp.n_ff, QD = hp.n_head * hp.head_dim, KVD = hp.n_head_kv * hp.head_dim;
+    const int LQ = QD + 2 * KVD, T8 = (T + 7) / 8 * 8, n_sms = m->eng->n_sms;
+    SeqState *sd = state.as<SeqState>();
+    if (!cx.p) {  // first chunk of this sequence: room for 32 tokens side by side
+        cx = DevBuf((size_t)32 * E * 4); cqkv = DevBuf((size_t)32 * LQ * 4); catt = DevBuf((size_t)32 * QD * 4);
+        ch = DevBuf((size_t)32 * FF * 4); cgu = DevBuf((size_t)32 * 2 * FF * 4);
+        cimg = DevBuf(gemm_images_bytes(std::max(std::max(E, QD), FF), 32)); cpos = DevBuf(32 * 4);
+        CUDA_CHECK(cudaMemsetAsync(cx.p, 0, cx.bytes, st)); CUDA_CHECK(cudaMemsetAsync(catt.p, 0, catt.bytes, st));
+        CUDA_CHECK(cudaMemsetAsync(ch.p, 0, ch.bytes, st));  // rows of padding tokens stay zero (finite images)
+    }
+    float *X = cx.as<float>(), *QKV = cqkv.as<float>(), *ATT = catt.as<float>(), *H = ch.as<float>(), *GU = cgu.as<float>();
+    uint8_t *IMG = cimg.as<uint8_t>();
+    int32_t *POS = cpos.as<int32_t>();
+    const int32_t *toks = prompt.as<int32_t>() + idx0;
+    for (int t = 0; t < T; t++)  // the last token also leaves its position / id in the sequence state
+        launch_embed_row(m->tok_embd_type, m->tok_embd_raw.p, m->tok_embd_row_bytes, E, toks + t, X + (size_t)t * E,
+                         t == T - 1 ? &sd->pos : POS + t, pos0 + t, t == T - 1 ? &sd->cur_token : nullptr, st);
+    CUDA_CHECK(cudaMemcpyAsync(POS + (T - 1), &sd->pos, 4, cudaMemcpyDeviceToDevice, st));
+
+    auto gemv1 = [&](const WPlanes &w, const float *xin, const float *norm, float *out, int epi) {
+        GemvParams p{};
+        p.n_seg = 1; p.epi = epi; p.k = w.k; p.seg[0] = w; p.out[0] = out; p.x = xin; p.norm_w = norm; p.eps = hp.rms_eps;
+        launch_gemv(p, gemv_plan_grid(p, n_sms), st, false);
+    };
+    // Y[t] (=|+=) W . act(in[t]) for all tokens of the chunk; `img_type` remembers which image permutation IMG holds
+    auto matmul = [&](const WPlanes &w, const float *in, int64_t ldin, const float *norm, float *out, int64_t ldo, int epi,
+                      int &img_type) {
+        if (gemm_q_usable(w.type, w.k)) {
+            const int perm_class = w.type == T_Q8_0 ? T_Q8_0 : T_Q4_K;
+            if (img_type != perm_class) {
+                launch_quant_rows(w.type, in, ldin, norm, hp.rms_eps, w.k, T8, IMG, st);
+                img_type = perm_class;
+            }
+            launch_gemm_q(w, IMG, T, out, ldo, epi, st);
+        } else {
+            for (int t = 0; t < T; t++) gemv1(w, in + (size_t)t * ldin, norm, out + (size_t)t * ldo, epi);
+        }
+    };
+    for (int il = 0; il < hp.n_layer; il++) {
+        const Layer &L = m->layers[il];
+        int img = -1;
+        matmul(L.wq.w, X, E, L.attn_norm.as<float>(), QKV, LQ, EPI_STORE, img);
+        matmul(L.wk.w, X, E, L.attn_norm.as<float>(), QKV + QD, LQ, EPI_STORE, img);
+        matmul(L.wv.w, X, E, L.attn_norm.as<float>(), QKV + QD + KVD, LQ, EPI_STORE, img);
+        for (int t = 0; t < T; t++) {  // RoPE + KV append + attention, token by token (each sees the rows before it)
+            AttnParams a{};
+            a.qkv = QKV + (size_t)t * LQ; a.out = ATT + (size_t)t * QD;
+            a.k_cache = m->k_cache(slot, il); a.v_cache = m->v_cache(slot, il);
+            a.rope_cos = m->rope_cos.as<float>(); a.rope_sin = m->rope_sin.as<float>();
+            a.n_past_ptr = POS + t;
+            a.scratch = attn_scratch.as<float>(); a.counters = attn_counters.as<uint32_t>();
+            a.n_head = hp.n_head; a.n_kv = hp.n_head_kv; a.hd = hp.head_dim; a.n_rot = hp.n_rot;
+            a.n_split = m->attn_splits; a.n_ctx = hp.n_ctx;
+            a.scale = 1.0f / sqrtf((float)hp.head_dim);
+            const int amode = (m->eng->flags & AIOS_ENGINE_ATTN_CLUSTER) ? 2 : (m->eng->flags & AIOS_ENGINE_ATTN_HEAD) ? 1 : 0;
+            launch_attn_decode(a, st, false, amode);
+        }
+        img = -1;
+        matmul(L.wo.w, ATT, QD, nullptr, X, E, EPI_ADD, img);
+        img = -1;
+        matmul(L.w_gate.w, X, E, L.ffn_norm.as<float>(), GU, 2 * FF, EPI_STORE, img);
+        matmul(L.w_up.w, X, E, L.ffn_norm.as<float>(), GU + FF, 2 * FF, EPI_STORE, img);
+        launch_swiglu_rows(GU, 2 * FF, FF, T, H, FF, st);
+        img = -1;
+        matmul(L.w_down.w, H, FF, nullptr, X, E, EPI_ADD, img);
+    }
+    if (want_logits) {
+        CUDA_CHECK(cudaMemsetAsync(&sd->argmax_key, 0, sizeof(unsigned long long), st));
+        GemvParams p{};
+        p.n_seg = 1; p.epi = EPI_STORE; p.k = E;
+        p.seg[0] = m->output.w; p.out[0] = logits.as<float>();
+        p.x = X + (size_t)(T - 1) * E; p.norm_w = m->output_norm.as<float>(); p.eps = hp.rms_eps;
+        p.argmax_key = &sd->argmax_key;
+        launch_gemv(p, gemv_plan_grid(p, n_sms), st, false);
+    }
 }
 
 int Seq::decode(const aios_sampling &sp, int max_tokens, int32_t *out) {

@@ -116,6 +116,8 @@ struct Seq {
     int snap_n_past = -1;
     struct KernelTimer *timer = nullptr;  // non-null only inside profile_decode
     DevBuf h_image, h_counters;  // ffn_down's activation image, quantised by the SwiGLU epilogue (GemvParams::q_image)
+    // prompt chunks (prefill_chunk): activations of up to 32 tokens side by side, their quantised images, positions
+    DevBuf cx, cqkv, catt, ch, cgu, cimg, cpos;
     DevBuf trace;
     unsigned long long *trace_base = nullptr;  // non-null only inside trace_decode
     cudaGraphExec_t graph = nullptr;
@@ -143,6 +145,7 @@ struct Seq {
    private:
     void launch_token_pass(bool from_prompt, int prompt_idx, int pos_value, bool want_logits, cudaStream_t st, int *n_launch);
     void launch_sample_kernel(const aios_sampling &sp, cudaStream_t st);
+    void prefill_chunk(int idx0, int T, int pos0, bool want_logits, cudaStream_t st);  // tokens prompt[idx0 .. idx0+T)
     void ensure_graph(const aios_sampling &sp);
     void build_pfd();
     bool use_pfd(const aios_sampling &sp) const;

@@ -213,6 +213,21 @@ __global__ void __launch_bounds__(GEMM_THREADS) gemm_q_kernel(const GemmParams p
         }
 }
 
+// h[t][i] = silu(gate[t][i]) * up[t][i] for a chunk: gu[t] = gate[ff] | up[ff].  Same expression, operation by
+// operation, as the GEMV's fused SwiGLU epilogue.
+__global__ void swiglu_rows_kernel(const float *gu, int64_t ldgu, int ff, int T, float *h, int64_t ldh) {
+    const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= (int64_t)T * ff) return;
+    const int t = (int)(i / ff), c = (int)(i % ff);
+    const float gte = gu[(size_t)t * ldgu + c], up = gu[(size_t)t * ldgu + ff + c];
+    h[(size_t)t * ldh + c] = __fmul_rn(__fdiv_rn(gte, __fadd_rn(1.0f, expf_det(-gte))), up);
+}
+void launch_swiglu_rows(const float *gu, int64_t ldgu, int ff, int T, float *h, int64_t ldh, cudaStream_t st) {
+    const int64_t n = (int64_t)T * ff;
+    swiglu_rows_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(gu, ldgu, ff, T, h, ldh);
+    CUDA_CHECK(cudaGetLastError());
+}
+
 bool gemm_q_usable(int type, int k) { return (type == T_Q4_K || type == T_Q8_0) && k % 256 == 0; }
 
 // T in 1..32: the images of tokens T..8*NT-1 (padding) must exist (any finite contents); their outputs are not stored.

@@ -79,6 +79,8 @@ size_t gemm_images_bytes(int k, int T);  // allocate for T rounded up to a multi
 bool gemm_q_usable(int type, int k);     // Q4_K / Q8_0
 // out[t][row] (row stride ldo floats) = or += dot, t < T <= 32; epi = EPI_STORE or EPI_ADD
 void launch_gemm_q(const WPlanes &w, const uint8_t *images, int T, float *out, int64_t ldo, int epi, cudaStream_t st);
+// h[t][0..ff) = silu(gu[t][0..ff)) * gu[t][ff..2ff)
+void launch_swiglu_rows(const float *gu, int64_t ldgu, int ff, int T, float *h, int64_t ldh, cudaStream_t st);
 
 // ---- gemv_ring.cu : the same fused op fed by a TMA ring (stream tiles of layout.cuh)
 // build the tiles of a [N][K] matrix (b == nullptr) or the PAIR tiles of two matrices from their planes

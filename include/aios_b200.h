@@ -64,6 +64,7 @@ typedef struct aios_engine_opts {
 #define AIOS_ENGINE_L2_PREFETCH 16 /* GEMV launches prefetch the next launch's weights into L2 (experiment; slower so far) */
 #define AIOS_ENGINE_ATTN_HEAD 32    /* decode attention: one CTA per query head (attention_head.cu) instead of the split kernel */
 #define AIOS_ENGINE_ATTN_CLUSTER 64 /* decode attention: the cluster / DSMEM kernel (attention.cu) at every context length */
+#define AIOS_ENGINE_NO_GEMM 1024 /* prefill token by token through the decode kernels instead of 32-token chunks through the tensor-core GEMM */
 #define AIOS_ENGINE_PRODUCER_QUANT 512 /* the SwiGLU epilogue quantises ffn_down's input slab by slab (experiment; slower so far) */
 #define AIOS_ENGINE_NO_ROPE_EPILOGUE 256/* RoPE / KV append in the attention kernel instead of the q/k/v GEMV's epilogue */
 #define AIOS_ENGINE_USE_RING 128   /* GEMV through the TMA-ring kernel (gemv_ring.cu): a second, tile-ordered copy of the

@@ -40,6 +40,40 @@ def test_matmul_with_rmsnorm_equals_matvec(engine, qt):
         assert np.array_equal(got[i].view(np.uint32), ref.view(np.uint32)), i
 
 
+@pytest.mark.parametrize("arch,ftype", [("tiny", "Q4_K_M"), ("tiny-gqa4", "Q4_K_M"), ("tiny", "Q8_0")])
+@pytest.mark.parametrize("n_prompt", [4, 33, 70])
+def test_chunked_prefill_is_bit_identical_to_token_by_token(engine, oracle, tmp_models, arch, ftype, n_prompt):
+    """Seq::prefill feeds prompts in 32-token chunks through the GEMM; logits, KV rows and the continuation must be
+    those of the token-by-token path (AIOS_ENGINE_NO_GEMM) and of the oracle."""
+    path = tmp_models(arch, ftype)
+    prompt = gs.synthetic_prompt(arch, n_prompt, 31)
+    slow = capi.Engine(device=0, max_batch=1, flags=capi.ENGINE_NO_GEMM)
+    m1, m2 = engine.load_model("a", path, n_ctx=128), slow.load_model("b", path, n_ctx=128)
+    try:
+        s1, s2 = m1.new_seq(), m2.new_seq()
+        try:
+            s1.prefill(prompt[:3])      # a short first call (token path), then chunks starting at position 3
+            s1.prefill(prompt[3:])
+            s2.prefill(prompt)
+            assert s1.n_past == s2.n_past == n_prompt
+            assert np.array_equal(s1.logits().view(np.uint32), s2.logits().view(np.uint32))
+            om = oracle.OracleModel(path, n_ctx=128)
+            ref = om.eval(prompt)
+            assert np.array_equal(s1.logits().view(np.uint32), ref.view(np.uint32))
+            for il in range(gs.ARCHS[arch].n_layer):
+                k1, v1 = s1.read_kv(il, 0, n_prompt)
+                k2, v2 = s2.read_kv(il, 0, n_prompt)
+                assert np.array_equal(k1, k2) and np.array_equal(v1, v2)
+            assert np.array_equal(s1.decode(16), s2.decode(16))
+        finally:
+            s1.free()
+            s2.free()
+    finally:
+        m1.unload()
+        m2.unload()
+        slow.close()
+
+
 def test_matmul_argument_errors(engine):
     w = np.zeros(210 * 4, np.uint8)
     with pytest.raises(capi.AiosError) as e:
