@@ -44,7 +44,7 @@ void launch_quant_rows(int weight_type, const float *x, int64_t ldx, const float
 size_t gemm_images_bytes(int k, int T) { return gemm_image_stride(k) * (size_t)T; }
 
 // ---------------------------------------------------------------- the GEMM
-constexpr int GEMM_WARPS = 4, GEMM_THREADS = GEMM_WARPS * 32, GEMM_ROWS = GEMM_WARPS * 16;
+constexpr int GEMM_WARPS = 2, GEMM_THREADS = GEMM_WARPS * 32, GEMM_ROWS = GEMM_WARPS * 16;
 constexpr int GEMM_TOK_STRIDE = 17;  // uint4 per token in the staged chunk: 16 used + 1 pad (bank spread over tokens)
 
 __device__ __forceinline__ void mma_s8(int (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
@@ -92,7 +92,8 @@ __device__ __forceinline__ void gemm_stage(const GemmSmem &s, const uint8_t *ima
     if (TYPE != T_Q8_0) {
         for (int t = threadIdx.x; t < T; t += GEMM_THREADS) {
             const uint8_t *aux = images + (size_t)t * img_stride + k;
-            s.d8[t] = *reinterpret_cast<const float *>(aux + k / 8 + (size_t)b * 4);
+            const uint32_t d = (uint32_t)__cvta_generic_to_shared(s.d8 + t);
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d), "l"(aux + k / 8 + (size_t)b * 4) : "memory");
         }
     }
     asm volatile("cp.async.commit_group;" ::: "memory");
@@ -106,20 +107,55 @@ struct GemmParams {
     int32_t T, epi;         // epi: EPI_STORE or EPI_ADD
 };
 
-// grid = ceil(N / 64); warp w of a CTA owns rows [64*cta + 16*w, +16) for the whole K and all T = 8*NT tokens.
-// Thread (g = lane/4, q = lane%4) ends up with the sums of rows g and g+8 for tokens 8j+2q and 8j+2q+1, j < NT.
+// Weight side of a stage: the 256-weight block b of GEMM_ROWS rows, copied plane by plane with 16-byte cp.async
+// (a row's bytes of one block are contiguous inside a plane), padded per row so that the fragment reads of the eight
+// row groups of a warp fall into different banks.
+//   Q4_K: qa[rows][5] uint4 (4 units + pad) | qb[rows][5] | meta[rows] uint4
+//   Q8_0: qa[rows][9] uint4 (8 blocks + pad) | qb[rows][9] | d[rows][8] f16
+template <int TYPE> struct GemmA;
+template <> struct GemmA<T_Q4_K> {
+    static constexpr int RS = 5;
+    static constexpr size_t bytes = (size_t)GEMM_ROWS * (2 * RS + 1) * 16;
+};
+template <> struct GemmA<T_Q8_0> {
+    static constexpr int RS = 9;
+    static constexpr size_t bytes = (size_t)GEMM_ROWS * (2 * RS + 1) * 16;
+};
+
+template <int TYPE>
+__device__ __forceinline__ void gemm_stage_a(uint8_t *sa, const WPlanes &w, int row0, int b) {
+    constexpr int RS = GemmA<TYPE>::RS, UPB = TYPE == T_Q8_0 ? 8 : 4;  // units (blocks of 32) per 256-weight block
+    const size_t U = (size_t)w.k / (TYPE == T_Q8_0 ? 32 : 64), nb = (size_t)w.k / 256;
+    uint4 *qa = reinterpret_cast<uint4 *>(sa), *qb = qa + GEMM_ROWS * RS, *ex = qb + GEMM_ROWS * RS;
+    for (int idx = threadIdx.x; idx < GEMM_ROWS * UPB; idx += GEMM_THREADS) {
+        const int r = idx / UPB, u = idx % UPB;
+        const size_t row = (size_t)min(row0 + r, w.n_rows - 1);
+        cp16(qa + r * RS + u, w.p[0] + (row * U + (size_t)UPB * b + u) * 16);
+        cp16(qb + r * RS + u, w.p[1] + (row * U + (size_t)UPB * b + u) * 16);
+    }
+    for (int r = threadIdx.x; r < GEMM_ROWS; r += GEMM_THREADS) {
+        const size_t row = (size_t)min(row0 + r, w.n_rows - 1);
+        if (TYPE == T_Q8_0) cp16(ex + r, w.p[2] + (row * U + (size_t)8 * b) * 2);   // eight f16 scales = 16 bytes
+        else cp16(ex + r, w.p[2] + (row * nb + b) * 16);                            // META of the block
+    }
+}
+
+// grid = ceil(N / GEMM_ROWS); warp w of a CTA owns rows [GEMM_ROWS*cta + 16*w, +16) for the whole K and all T = 8*NT
+// tokens.  Thread (g = lane/4, q = lane%4) ends up with the sums of rows g and g+8 for tokens 8j+2q, 8j+2q+1, j < NT.
+// Three-stage cp.async pipeline over the 256-weight blocks of K: weights and activation images of block b+2 are in
+// flight while block b is multiplied.
 template <int TYPE, int NT>
 __global__ void __launch_bounds__(GEMM_THREADS) gemm_q_kernel(const GemmParams p) {
     extern __shared__ __align__(16) uint8_t smem[];
-    constexpr int T = 8 * NT;
+    constexpr int T = 8 * NT, RS = GemmA<TYPE>::RS, STAGES = 3;
+    const size_t stage_bytes = GemmA<TYPE>::bytes + gemm_chunk_bytes(T);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int g = lane >> 2, q = lane & 3;
     const int k = p.w.k, N = p.w.n_rows;
     const int nb = k / 256;
     const size_t img_stride = gemm_image_stride(k);
-
-    const int row_a = blockIdx.x * GEMM_ROWS + warp * 16 + g, row_b = row_a + 8;
-    const size_t ra = (size_t)min(row_a, N - 1), rb = (size_t)min(row_b, N - 1);  // clamped for loads; stores are guarded
+    const int row0 = blockIdx.x * GEMM_ROWS;
+    const int ra = warp * 16 + g, rb = ra + 8;  // my two rows inside the CTA's tile
 
     double acc[NT][4];
 #pragma unroll
@@ -127,27 +163,35 @@ __global__ void __launch_bounds__(GEMM_THREADS) gemm_q_kernel(const GemmParams p
 #pragma unroll
         for (int e = 0; e < 4; e++) acc[j][e] = 0.0;
 
-    gemm_stage<TYPE>(gemm_carve(smem, T), p.images, img_stride, k, T, 0);
+    auto stage = [&](int b) {
+        uint8_t *base = smem + (size_t)(b % STAGES) * stage_bytes;
+        gemm_stage_a<TYPE>(base, p.w, row0, b);
+        gemm_stage<TYPE>(gemm_carve(base + GemmA<TYPE>::bytes, T), p.images, img_stride, k, T, b);  // commits the group
+    };
+    stage(0);
+    if (nb > 1) stage(1);
     for (int b = 0; b < nb; b++) {
-        const GemmSmem s = gemm_carve(smem + (size_t)(b & 1) * gemm_chunk_bytes(T), T);
-        if (b + 1 < nb) {
-            gemm_stage<TYPE>(gemm_carve(smem + (size_t)((b + 1) & 1) * gemm_chunk_bytes(T), T), p.images, img_stride, k, T, b + 1);
+        if (b + 2 < nb) {
+            stage(b + 2);
+            asm volatile("cp.async.wait_group 2;" ::: "memory");
+        } else if (b + 1 < nb) {
             asm volatile("cp.async.wait_group 1;" ::: "memory");
         } else {
             asm volatile("cp.async.wait_group 0;" ::: "memory");
         }
         __syncthreads();
+        const uint8_t *base = smem + (size_t)(b % STAGES) * stage_bytes;
+        const uint4 *qa = reinterpret_cast<const uint4 *>(base), *qb = qa + GEMM_ROWS * RS, *ex = qb + GEMM_ROWS * RS;
+        const GemmSmem s = gemm_carve(const_cast<uint8_t *>(base) + GemmA<TYPE>::bytes, T);
         if (TYPE == T_Q8_0) {
-            const size_t U8 = (size_t)k / 32;
+            const __half *dha = reinterpret_cast<const __half *>(ex + ra), *dhb = reinterpret_cast<const __half *>(ex + rb);
 #pragma unroll 2
             for (int u = 0; u < 8; u++) {
-                const size_t ua = ra * U8 + 8 * b + u, ub = rb * U8 + 8 * b + u;
-                const uint32_t a0 = *reinterpret_cast<const uint32_t *>(p.w.p[0] + ua * 16 + q * 4);
-                const uint32_t a1 = *reinterpret_cast<const uint32_t *>(p.w.p[0] + ub * 16 + q * 4);
-                const uint32_t a2 = *reinterpret_cast<const uint32_t *>(p.w.p[1] + ua * 16 + q * 4);
-                const uint32_t a3 = *reinterpret_cast<const uint32_t *>(p.w.p[1] + ub * 16 + q * 4);
-                const float dwa = h2f_bits(*reinterpret_cast<const uint16_t *>(p.w.p[2] + ua * 2));
-                const float dwb = h2f_bits(*reinterpret_cast<const uint16_t *>(p.w.p[2] + ub * 2));
+                const uint32_t a0 = reinterpret_cast<const uint32_t *>(qa + ra * RS + u)[q];
+                const uint32_t a1 = reinterpret_cast<const uint32_t *>(qa + rb * RS + u)[q];
+                const uint32_t a2 = reinterpret_cast<const uint32_t *>(qb + ra * RS + u)[q];
+                const uint32_t a3 = reinterpret_cast<const uint32_t *>(qb + rb * RS + u)[q];
+                const float dwa = __half2float(dha[u]), dwb = __half2float(dhb[u]);
 #pragma unroll
                 for (int j = 0; j < NT; j++) {
                     const uint32_t *bt = reinterpret_cast<const uint32_t *>(s.act + (8 * j + g) * GEMM_TOK_STRIDE + u * 2);
@@ -161,9 +205,7 @@ __global__ void __launch_bounds__(GEMM_THREADS) gemm_q_kernel(const GemmParams p
                 }
             }
         } else {  // Q4_K
-            const size_t U = (size_t)k / 64;
-            const uint4 mta = *reinterpret_cast<const uint4 *>(p.w.p[2] + (ra * nb + b) * 16);
-            const uint4 mtb = *reinterpret_cast<const uint4 *>(p.w.p[2] + (rb * nb + b) * 16);
+            const uint4 mta = ex[ra], mtb = ex[rb];
             const uint32_t dda = __byte_perm(__byte_perm(mta.x, mta.y, 0x0073), __byte_perm(mta.z, mta.w, 0x0073), 0x5410);
             const uint32_t ddb = __byte_perm(__byte_perm(mtb.x, mtb.y, 0x0073), __byte_perm(mtb.z, mtb.w, 0x0073), 0x5410);
             const float2 da = __half22float2(*reinterpret_cast<const __half2 *>(&dda));  // (d, dmin) of row a
@@ -171,11 +213,10 @@ __global__ void __launch_bounds__(GEMM_THREADS) gemm_q_kernel(const GemmParams p
             const uint32_t mwa[4] = {mta.x, mta.y, mta.z, mta.w}, mwb[4] = {mtb.x, mtb.y, mtb.z, mtb.w};
 #pragma unroll
             for (int u = 0; u < 4; u++) {
-                const size_t ua = ra * U + 4 * b + u, ub = rb * U + 4 * b + u;
-                const uint32_t qa0 = *reinterpret_cast<const uint32_t *>(p.w.p[0] + ua * 16 + q * 4);
-                const uint32_t qa1 = *reinterpret_cast<const uint32_t *>(p.w.p[0] + ub * 16 + q * 4);
-                const uint32_t qb0 = *reinterpret_cast<const uint32_t *>(p.w.p[1] + ua * 16 + q * 4);
-                const uint32_t qb1 = *reinterpret_cast<const uint32_t *>(p.w.p[1] + ub * 16 + q * 4);
+                const uint32_t qa0 = reinterpret_cast<const uint32_t *>(qa + ra * RS + u)[q];
+                const uint32_t qa1 = reinterpret_cast<const uint32_t *>(qa + rb * RS + u)[q];
+                const uint32_t qb0 = reinterpret_cast<const uint32_t *>(qb + ra * RS + u)[q];
+                const uint32_t qb1 = reinterpret_cast<const uint32_t *>(qb + rb * RS + u)[q];
                 const int sa_lo = mwa[u] & 63, sa_hi = (mwa[u] >> 6) & 63, ma_lo = (mwa[u] >> 12) & 63, ma_hi = (mwa[u] >> 18) & 63;
                 const int sb_lo = mwb[u] & 63, sb_hi = (mwb[u] >> 6) & 63, mb_lo = (mwb[u] >> 12) & 63, mb_hi = (mwb[u] >> 18) & 63;
 #pragma unroll
@@ -198,8 +239,9 @@ __global__ void __launch_bounds__(GEMM_THREADS) gemm_q_kernel(const GemmParams p
                 }
             }
         }
-        __syncthreads();  // everyone is done with this buffer before it is staged again
+        __syncthreads();  // everyone is done with this stage before it is refilled
     }
+    const int row_a = row0 + ra, row_b = row0 + rb;
 #pragma unroll
     for (int j = 0; j < NT; j++)
 #pragma unroll
@@ -212,6 +254,9 @@ __global__ void __launch_bounds__(GEMM_THREADS) gemm_q_kernel(const GemmParams p
             }
         }
 }
+
+template <int TYPE>
+static size_t gemm_smem_bytes(int T) { return 3 * (GemmA<TYPE>::bytes + gemm_chunk_bytes(T)); }
 
 // h[t][i] = silu(gate[t][i]) * up[t][i] for a chunk: gu[t] = gate[ff] | up[ff].  Same expression, operation by
 // operation, as the GEMV's fused SwiGLU epilogue.
@@ -238,8 +283,16 @@ void launch_gemm_q(const WPlanes &w, const uint8_t *images, int T, float *out, i
     p.w = w; p.images = images; p.out = out; p.ldo = ldo; p.T = T; p.epi = epi;
     const int nt = (T + 7) / 8;
     const dim3 grid((w.n_rows + GEMM_ROWS - 1) / GEMM_ROWS);
-    const size_t smem = 2 * gemm_chunk_bytes(8 * nt);
-#define GEMM_LAUNCH(TY, NTV) gemm_q_kernel<TY, NTV><<<grid, GEMM_THREADS, smem, st>>>(p)
+    const size_t smem = w.type == T_Q4_K ? gemm_smem_bytes<T_Q4_K>(8 * nt) : gemm_smem_bytes<T_Q8_0>(8 * nt);
+#define GEMM_LAUNCH(TY, NTV)                                                                                          \
+    do {                                                                                                              \
+        static bool attr_set = false;                                                                                 \
+        if (!attr_set) {                                                                                              \
+            CUDA_CHECK(cudaFuncSetAttribute(gemm_q_kernel<TY, NTV>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024)); \
+            attr_set = true;                                                                                          \
+        }                                                                                                             \
+        gemm_q_kernel<TY, NTV><<<grid, GEMM_THREADS, smem, st>>>(p);                                                  \
+    } while (0)
     if (w.type == T_Q4_K) {
         if (nt == 1) GEMM_LAUNCH(T_Q4_K, 1); else if (nt == 2) GEMM_LAUNCH(T_Q4_K, 2); else if (nt == 3) GEMM_LAUNCH(T_Q4_K, 3); else GEMM_LAUNCH(T_Q4_K, 4);
     } else {
