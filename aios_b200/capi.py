@@ -21,12 +21,8 @@ ENGINE_NO_GRAPH = 1
 ENGINE_NO_PDL = 2
 ENGINE_NO_PFD = 4
 ENGINE_USE_PFD = 8
-ENGINE_L2_PREFETCH = 16
-ENGINE_ATTN_HEAD = 32
 ENGINE_ATTN_CLUSTER = 64
-ENGINE_USE_RING = 128
 ENGINE_NO_ROPE_EPILOGUE = 256
-ENGINE_PRODUCER_QUANT = 512
 ENGINE_NO_GEMM = 1024
 
 

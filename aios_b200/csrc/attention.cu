@@ -263,20 +263,16 @@ static size_t attn_dyn_smem(int rep, int hd, int per_cap) {
 }
 
 void attn_init() {
-    static bool done = false;
-    if (done) return;
-    CUDA_CHECK(cudaFuncSetAttribute(attn_decode_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
-    CUDA_CHECK(cudaFuncSetAttribute(attn_decode_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
-    done = true;
+    static PerDeviceOnce once;
+    once.run([] {
+        CUDA_CHECK(cudaFuncSetAttribute(attn_decode_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+        CUDA_CHECK(cudaFuncSetAttribute(attn_decode_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+    });
 }
 
 void launch_attn_decode(const AttnParams &p, cudaStream_t st, bool pdl, int mode) {
     if (mode == 0 && attn_split_usable(p.n_ctx, p.hd)) {  // one wave of independent CTAs, PDL
         launch_attn_decode_split(p, st, pdl);
-        return;
-    }
-    if (mode != 2 && attn_head_usable(p.n_ctx, p.hd)) {  // short context: skip the cluster launch and its barriers
-        launch_attn_decode_head(p, st);
         return;
     }
     const int rep = p.n_head / p.n_kv;

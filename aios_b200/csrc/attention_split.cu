@@ -349,14 +349,14 @@ static size_t as_smem(int n_ctx, int hd, int split) {
 constexpr int AS_SPLIT = 4;
 
 void attn_split_init() {
-    static bool done = false;
-    if (done) return;
-    // same shared-memory carve-out as the ring GEMV it sits between (an SM cannot host two carve-outs at once)
-    CUDA_CHECK(cudaFuncSetAttribute(attn_split_kernel<128, AS_SPLIT>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
-    CUDA_CHECK(cudaFuncSetAttribute(attn_split_kernel<64, AS_SPLIT>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
-    CUDA_CHECK(cudaFuncSetAttribute(attn_split_kernel<128, AS_SPLIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 208 * 1024));
-    CUDA_CHECK(cudaFuncSetAttribute(attn_split_kernel<64, AS_SPLIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 208 * 1024));
-    done = true;
+    static PerDeviceOnce once;
+    once.run([] {
+        // same shared-memory carve-out as the GEMVs it sits between (an SM cannot host two carve-outs at once)
+        CUDA_CHECK(cudaFuncSetAttribute(attn_split_kernel<128, AS_SPLIT>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+        CUDA_CHECK(cudaFuncSetAttribute(attn_split_kernel<64, AS_SPLIT>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+        CUDA_CHECK(cudaFuncSetAttribute(attn_split_kernel<128, AS_SPLIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 208 * 1024));
+        CUDA_CHECK(cudaFuncSetAttribute(attn_split_kernel<64, AS_SPLIT>, cudaFuncAttributeMaxDynamicSharedMemorySize, 208 * 1024));
+    });
 }
 
 bool attn_split_usable(int n_ctx, int hd) {

@@ -98,7 +98,7 @@ void aios_engine::serve(aios_request *r) {
         const Tokenizer *tok = (r->flags & AIOS_REQ_STOP_AT_EOG) ? &r->m->vocab()->tok : nullptr;
         {
             std::lock_guard<std::mutex> lk(impl.mu);
-            if (!r->m->req_seq) r->m->req_seq.reset(new Seq(&M));
+            if (!r->m->req_seq) r->m->req_seq.reset(new Seq(&M, true));  // a hidden slot, not one of the caller's
             r->m->req_seq->reset();
             r->m->req_seq->prefill(r->prompt.data(), (int)r->prompt.size());
         }
@@ -664,7 +664,7 @@ int aios_forward_logits(aios_model *m, const int32_t *tokens, int32_t n, int32_t
     return guarded([&] {
         if (!m || !tokens || n <= 0 || !logits_out || n_past < 0) return fail(AIOS_E_INVAL, "bad argument");
         std::lock_guard<std::mutex> lk(m->impl.eng->mu);
-        if (!m->scratch) m->scratch.reset(new Seq(&m->impl));
+        if (!m->scratch) m->scratch.reset(new Seq(&m->impl, true));  // a hidden slot, not one of the caller's
         Seq &s = *m->scratch;
         if (n_past == 0) s.reset();
         else if (s.n_past != n_past) return fail(AIOS_E_STATE, "scratch sequence is at a different position");

@@ -4,6 +4,7 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include <mutex>
 #include <stdexcept>
 #include <string>
 
@@ -22,6 +23,22 @@ inline void cuda_check(cudaError_t e, const char *what, const char *file, int li
     }
 }
 #define CUDA_CHECK(x) ::aios::cuda_check((x), #x, __FILE__, __LINE__)
+
+// Function attributes (dynamic shared-memory limit, carve-out) are per-DEVICE settings: a process that drives several
+// GPUs (one engine each) must set them once on each.  run(f) calls f the first time it is reached with a given
+// device current; thread-safe.
+struct PerDeviceOnce {
+    std::mutex mu;
+    bool done[64] = {};
+    template <typename F>
+    void run(F &&f) {
+        int dev = 0;
+        CUDA_CHECK(cudaGetDevice(&dev));
+        std::lock_guard<std::mutex> lk(mu);
+        if (dev < 0 || dev >= 64) { f(); return; }
+        if (!done[dev]) { f(); done[dev] = true; }
+    }
+};
 
 #ifdef __CUDACC__
 __device__ __forceinline__ float warp_sum(float v) {

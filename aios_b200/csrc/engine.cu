@@ -49,11 +49,10 @@ Engine::Engine(const aios_engine_opts &o) : device(o.device), max_batch(o.max_ba
     }
     n_sms = prop.multiProcessorCount;
     CUDA_CHECK(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+    // function attributes are per-device settings: every engine sets them for its own device
     gemv_init();
-    gemv_ring_init();
     attn_split_init();
     attn_init();
-    attn_head_init();
 }
 Engine::~Engine() {
     if (stream) cudaStreamDestroy(stream);
@@ -103,15 +102,6 @@ void Model::upload_matrix(const GgufTensor &t, DevMatrix &dst, DevBuf &staging, 
     weight_bytes_per_token += (int64_t)t.nbytes;
 }
 
-// stream tiles for the TMA-ring GEMV: a second copy of the matrix bytes, cut into bulk-copy blobs (layout.cuh)
-void Model::build_tiles(DevMatrix &m) {
-    if (!ring || tile_bytes(m.w.type) == 0) return;
-    m.tile_storage = DevBuf(tiles_total_bytes(m.w.type, m.w.n_rows, m.w.k, false));
-    launch_build_tiles(m.w, nullptr, m.tile_storage.as<uint8_t>(), &m.t, eng->stream);
-    CUDA_CHECK(cudaStreamSynchronize(eng->stream));
-    weight_bytes += (int64_t)m.tile_storage.bytes;
-}
-
 static DevBuf upload_f32(const GgufTensor &t, int64_t expect, cudaStream_t st) {
     if (t.type != T_F32 || t.ne[0] != expect)
         throw GgufError(AIOS_E_FORMAT, "tensor '" + t.name + "' must be F32[" + std::to_string(expect) + "]");
@@ -151,9 +141,6 @@ Model::Model(Engine *e, const std::string &name_, const std::string &path_, int 
     hp.n_vocab = (int)te.ne[1];
     if (te.ne[0] != hp.n_embd) throw GgufError(AIOS_E_FORMAT, "token_embd.weight has the wrong width");
 
-    // opt-in: correct (bit-identical results) but 2.41 vs 1.92 ms/token — its 8 consumer warps per SM process a tile
-    // in ~0.55 us where HBM delivers one in 0.42 (profiles/r01_v4_ring.md)
-    ring = (e->flags & AIOS_ENGINE_USE_RING) != 0;
     cudaStream_t st = e->stream;
     const size_t pinned_bytes = 64u << 20;
     void *pinned = nullptr;
@@ -194,21 +181,11 @@ Model::Model(Engine *e, const std::string &name_, const std::string &path_, int 
             }
             if (L.w_gate.w.type != L.w_up.w.type)
                 throw GgufError(AIOS_E_FORMAT, "ffn_gate and ffn_up of layer " + std::to_string(i) + " differ in type");
-            if (ring) {
-                for (DevMatrix *dm : {&L.wq, &L.wk, &L.wv, &L.wo, &L.w_down}) build_tiles(*dm);
-                if (tile_bytes(L.w_gate.w.type)) {
-                    L.gate_up_storage = DevBuf(tiles_total_bytes(L.w_gate.w.type, L.w_gate.w.n_rows, L.w_gate.w.k, true));
-                    launch_build_tiles(L.w_gate.w, &L.w_up.w, L.gate_up_storage.as<uint8_t>(), &L.gate_up, st);
-                    CUDA_CHECK(cudaStreamSynchronize(st));
-                    weight_bytes += (int64_t)L.gate_up_storage.bytes;
-                }
-            }
         }
         output_norm = upload_f32(f.require("output_norm.weight"), hp.n_embd, st);
         weight_bytes_per_token += (int64_t)hp.n_embd * 4;
         const GgufTensor *out = f.find("output.weight");
         upload_matrix(out ? *out : te, output, staging, pinned, pinned_bytes);  // tied embeddings when absent
-        build_tiles(output);
     } catch (...) {
         cudaFreeHost(pinned);
         throw;
@@ -233,10 +210,11 @@ Model::Model(Engine *e, const std::string &name_, const std::string &path_, int 
         CUDA_CHECK(cudaMemcpy(rope_cos.p, c.data(), c.size() * 4, cudaMemcpyHostToDevice));
         CUDA_CHECK(cudaMemcpy(rope_sin.p, s.data(), s.size() * 4, cudaMemcpyHostToDevice));
     }
-    kv = DevBuf((size_t)e->max_batch * hp.n_layer * 2 * kv_layer_elems() * 2);
+    const size_t n_slots = (size_t)e->max_batch + HIDDEN_SLOTS;
+    kv = DevBuf(n_slots * hp.n_layer * 2 * kv_layer_elems() * 2);
     CUDA_CHECK(cudaMemsetAsync(kv.p, 0, kv.bytes, st));
     CUDA_CHECK(cudaStreamSynchronize(st));
-    slot_used.assign((size_t)e->max_batch, false);
+    slot_used.assign(n_slots, false);
     attn_splits = std::max(1, std::min(32, (2 * e->n_sms) / std::max(1, hp.n_head_kv)));
 }
 
@@ -265,14 +243,17 @@ struct KernelTimer {  // per-launch CUDA events (profile_decode only)
 };
 #define TIMED(kind, stmt) do { if (timer) timer->begin(kind); stmt; if (timer) timer->end(); } while (0)
 
-Seq::Seq(Model *m_) : m(m_), slot(-1) {
+Seq::Seq(Model *m_, bool internal) : m(m_), slot(-1) {
     m->eng->make_current();
     {
+        // caller-visible sequences own slots [0, max_batch); the library's own live in the hidden slots behind them
         std::lock_guard<std::mutex> lk(m->mu);
-        for (size_t i = 0; i < m->slot_used.size(); i++)
+        const size_t lo = internal ? (size_t)m->eng->max_batch : 0;
+        const size_t hi = internal ? m->slot_used.size() : (size_t)m->eng->max_batch;
+        for (size_t i = lo; i < hi; i++)
             if (!m->slot_used[i]) { slot = (int)i; m->slot_used[i] = true; break; }
     }
-    if (slot < 0) throw std::runtime_error("no free KV slot (engine max_batch reached)");
+    if (slot < 0) throw std::runtime_error(internal ? "no free internal KV slot" : "no free KV slot (engine max_batch reached)");
     const HParams &hp = m->hp;
     try {
         state = DevBuf(sizeof(SeqState));
@@ -280,9 +261,6 @@ Seq::Seq(Model *m_) : m(m_), slot(-1) {
         qkv = DevBuf((size_t)(hp.n_head + 2 * hp.n_head_kv) * hp.head_dim * 4);
         att = DevBuf((size_t)hp.n_head * hp.head_dim * 4);
         h = DevBuf((size_t)hp.n_ff * 4);
-        h_image = DevBuf((size_t)hp.n_ff + (size_t)hp.n_ff / 4 + 64);  // = act_image_bytes(n_ff), gemv_core.cuh
-        h_counters = DevBuf((size_t)(hp.n_ff / 256 + 1) * 128);  // one 128-byte line per slab counter
-        CUDA_CHECK(cudaMemset(h_counters.p, 0, h_counters.bytes));
         logits = DevBuf((size_t)hp.n_vocab * 4);
         out_tokens = DevBuf((size_t)hp.n_ctx * 4);
         prompt = DevBuf((size_t)hp.n_ctx * 4);
@@ -292,7 +270,7 @@ Seq::Seq(Model *m_) : m(m_), slot(-1) {
         pfd_att_max = DevBuf((size_t)hp.n_head_kv * 16 * 8 * sizeof(float));
         pfd_att_sum = DevBuf((size_t)hp.n_head_kv * 16 * 8 * sizeof(double));
         pfd_att_acc = DevBuf((size_t)hp.n_head * hp.head_dim * sizeof(double));
-        pfd_counters = DevBuf(32 * sizeof(unsigned));
+        pfd_counters = DevBuf(((size_t)hp.n_head_kv + 16) * sizeof(unsigned));  // [n_kv] group barriers, then the grid barrier
         CUDA_CHECK(cudaMemset(pfd_att_acc.p, 0, pfd_att_acc.bytes));
         CUDA_CHECK(cudaMemset(pfd_counters.p, 0, pfd_counters.bytes));
         reset();
@@ -317,30 +295,8 @@ void Seq::reset() {
     CUDA_CHECK(cudaMemcpy(state.p, &s, sizeof(s), cudaMemcpyHostToDevice));
 }
 
-// next launch's weight planes -> L2 prefetch ranges of this launch (capped: two big matrices must share L2)
-static void set_prefetch(GemvParams &p, std::initializer_list<const WPlanes *> next, bool on) {
-    p.n_pf = 0;
-    if (!on) return;
-    size_t budget = 72u << 20;
-    for (const WPlanes *w : next) {
-        if (!w) continue;
-        for (int i = 0; i < 5 && p.n_pf < 12; i++) {
-            const size_t b = plane_bytes(w->type, i, w->n_rows, w->k);
-            if (!b || !w->p[i]) continue;
-            const size_t take = std::min(b, budget);
-            if (take < 4096) continue;
-            p.pf_ptr[p.n_pf] = w->p[i];
-            p.pf_bytes[p.n_pf] = (uint32_t)take;
-            p.n_pf++;
-            budget -= take;
-        }
-    }
-}
-
 void Seq::launch_token_pass(bool from_prompt, int prompt_idx, int pos_value, bool want_logits, cudaStream_t st, int *n_launch) {
     const HParams &hp = m->hp;
-    // opt-in: measured 6 % SLOWER on Mistral-7B (2.10 vs 1.97 ms/token, profiles/r01_v3_summary.md)
-    const bool pf = (m->eng->flags & AIOS_ENGINE_L2_PREFETCH) != 0;
     SeqState *sd = state.as<SeqState>();
     const int n_sms = m->eng->n_sms;
     int launches = 0;
@@ -350,35 +306,14 @@ void Seq::launch_token_pass(bool from_prompt, int prompt_idx, int pos_value, boo
                      from_prompt ? &sd->pos : nullptr, pos_value, from_prompt ? &sd->cur_token : nullptr, st));
     launches++;
     const int QD = hp.n_head * hp.head_dim, KVD = hp.n_head_kv * hp.head_dim;
-    // TMA-ring GEMV (gemv_ring.cu) when every matrix of the launch has stream tiles; false -> caller takes gemv.cu
-    auto ring_launch = [&](std::initializer_list<const WTiles *> segs, std::initializer_list<float *> outs, int epi, int k,
-                           const float *xin, const float *norm, unsigned long long *amax, bool use_pdl) -> bool {
-        if (!m->ring) return false;
-        RingParams r{};
-        r.n_seg = (int)segs.size(); r.epi = epi; r.k = k;
-        int i = 0;
-        for (const WTiles *w : segs) {
-            if (!w->base) return false;
-            r.seg[i++] = *w;
-        }
-        i = 0;
-        for (float *o : outs) r.out[i++] = o;
-        r.x = xin; r.norm_w = norm; r.eps = hp.rms_eps; r.argmax_key = amax;
-        r.trace = trace_base && launches < 4096 ? trace_base + (size_t)launches * 8 : nullptr;
-        if (!gemv_ring_usable(r)) return false;
-        TIMED(0, launch_gemv_ring(r, n_sms, st, use_pdl));
-        launches++;
-        return true;
-    };
-    const int amode = (m->eng->flags & AIOS_ENGINE_ATTN_CLUSTER) ? 2 : (m->eng->flags & AIOS_ENGINE_ATTN_HEAD) ? 1 : 0;
+    auto trace_slot = [&]() { return trace_base && launches < 4096 ? trace_base + (size_t)launches * 8 : nullptr; };
+    const int amode = (m->eng->flags & AIOS_ENGINE_ATTN_CLUSTER) ? 2 : 0;
     // with the split attention kernel, RoPE + f16 rounding + KV append move into the q/k/v GEMV's epilogue
     // (EPI_QKV_ROPE): the attention kernel then starts on final data, with no dependent table loads of its own
     const bool rope_in_gemv = amode == 0 && attn_split_usable(hp.n_ctx, hp.head_dim) && !(m->eng->flags & AIOS_ENGINE_NO_ROPE_EPILOGUE);
     for (int il = 0; il < hp.n_layer; il++) {
         const Layer &L = m->layers[il];
-        bool kv_ready = false, h_quantised = false;
-        if (!ring_launch({&L.wq.t, &L.wk.t, &L.wv.t}, {qkv.as<float>(), qkv.as<float>() + QD, qkv.as<float>() + QD + KVD},
-                         EPI_STORE, hp.n_embd, x.as<float>(), L.attn_norm.as<float>(), nullptr, pdl))
+        bool kv_ready = false;
         {   // RMSNorm + Q,K,V projections: one launch when the three matrices share a type (else q,k + v)
             GemvParams p{};
             bool same = L.wv.w.type == L.wq.w.type && L.wk.w.type == L.wq.w.type;
@@ -396,9 +331,7 @@ void Seq::launch_token_pass(bool from_prompt, int prompt_idx, int pos_value, boo
                 p.rope.n_rot = hp.n_rot; p.rope.hd = hp.head_dim; p.rope.kvd = KVD;
                 kv_ready = true;
             }
-            if (same) set_prefetch(p, {&L.wo.w}, pf);
-            else set_prefetch(p, {&L.wv.w, &L.wo.w}, pf);
-            p.trace = trace_base && launches < 4096 ? trace_base + (size_t)launches * 8 : nullptr;
+            p.trace = trace_slot();
             TIMED(0, launch_gemv(p, gemv_plan_grid(p, n_sms), st, pdl));
             launches++;
             if (!same) {
@@ -406,8 +339,7 @@ void Seq::launch_token_pass(bool from_prompt, int prompt_idx, int pos_value, boo
                 v.n_seg = 1; v.epi = EPI_STORE; v.k = hp.n_embd;
                 v.seg[0] = L.wv.w; v.out[0] = qkv.as<float>() + QD + KVD;
                 v.x = x.as<float>(); v.norm_w = L.attn_norm.as<float>(); v.eps = hp.rms_eps;
-                set_prefetch(v, {&L.w_gate.w}, pf);  // (attn_output was requested by the q,k launch)
-                v.trace = trace_base && launches < 4096 ? trace_base + (size_t)launches * 8 : nullptr;
+                v.trace = trace_slot();
                 TIMED(0, launch_gemv(v, gemv_plan_grid(v, n_sms), st, pdl));
                 launches++;
             }
@@ -422,50 +354,33 @@ void Seq::launch_token_pass(bool from_prompt, int prompt_idx, int pos_value, boo
             a.n_head = hp.n_head; a.n_kv = hp.n_head_kv; a.hd = hp.head_dim; a.n_rot = hp.n_rot;
             a.n_split = m->attn_splits; a.n_ctx = hp.n_ctx;
             a.scale = 1.0f / sqrtf((float)hp.head_dim);
-            a.trace = trace_base && launches < 4096 ? trace_base + (size_t)launches * 8 : nullptr;
+            a.trace = trace_slot();
             a.kv_ready = kv_ready ? 1 : 0;
             TIMED(1, launch_attn_decode(a, st, pdl, amode));
             launches++;
         }
-        if (!ring_launch({&L.wo.t}, {x.as<float>()}, EPI_ADD, QD, att.as<float>(), nullptr, nullptr, pdl))
         {   // attention output projection + residual add
             GemvParams p{};
             p.n_seg = 1; p.epi = EPI_ADD; p.k = QD;
             p.seg[0] = L.wo.w; p.out[0] = x.as<float>(); p.x = att.as<float>();
-            set_prefetch(p, {&L.w_gate.w, &L.w_up.w}, pf);
-            p.trace = trace_base && launches < 4096 ? trace_base + (size_t)launches * 8 : nullptr;
+            p.trace = trace_slot();
             TIMED(0, launch_gemv(p, gemv_plan_grid(p, n_sms), st, pdl));
             launches++;
         }
-        if (!ring_launch({&L.gate_up}, {h.as<float>()}, EPI_SWIGLU, hp.n_embd, x.as<float>(), L.ffn_norm.as<float>(), nullptr, pdl))
         {   // RMSNorm + gate/up + SwiGLU
             GemvParams p{};
             p.n_seg = 2; p.epi = EPI_SWIGLU; p.k = hp.n_embd;
             p.seg[0] = L.w_gate.w; p.seg[1] = L.w_up.w; p.out[0] = h.as<float>();
             p.x = x.as<float>(); p.norm_w = L.ffn_norm.as<float>(); p.eps = hp.rms_eps;
-            if ((m->eng->flags & AIOS_ENGINE_PRODUCER_QUANT) && !(m->ring && L.w_down.t.base)) {
-                // opt-in: the SwiGLU epilogue also quantises h, slab by slab, for ffn_down (whose prologue becomes a
-                // copy).  Bit-identical, but the fence / count / quantise chain lands on the tail of the gate/up
-                // launch and costs more than ffn_down's 4.7 us prologue saves: 1.83 vs 1.71 ms/token.
-                const int dt = L.w_down.w.type;
-                p.q_image = h_image.as<uint8_t>(); p.q_counters = h_counters.as<uint32_t>();
-                p.q_perm = dt == T_Q6_K ? 1 : dt == T_Q8_0 ? 2 : 0; p.q_k = hp.n_ff;
-                h_quantised = true;
-            }
-            set_prefetch(p, {&L.w_down.w}, pf);
-            p.trace = trace_base && launches < 4096 ? trace_base + (size_t)launches * 8 : nullptr;
+            p.trace = trace_slot();
             TIMED(0, launch_gemv(p, gemv_plan_grid(p, n_sms), st, pdl));
             launches++;
         }
-        if (!ring_launch({&L.w_down.t}, {x.as<float>()}, EPI_ADD, hp.n_ff, h.as<float>(), nullptr, nullptr, pdl))
         {   // down projection + residual add
             GemvParams p{};
             p.n_seg = 1; p.epi = EPI_ADD; p.k = hp.n_ff;
             p.seg[0] = L.w_down.w; p.out[0] = x.as<float>(); p.x = h.as<float>();
-            if (h_quantised) p.x_image = h_image.as<uint8_t>();
-            if (il + 1 < hp.n_layer) set_prefetch(p, {&m->layers[il + 1].wq.w, &m->layers[il + 1].wk.w, &m->layers[il + 1].wv.w}, pf);
-            else if (want_logits) set_prefetch(p, {&m->output.w}, pf);
-            p.trace = trace_base && launches < 4096 ? trace_base + (size_t)launches * 8 : nullptr;
+            p.trace = trace_slot();
             TIMED(0, launch_gemv(p, gemv_plan_grid(p, n_sms), st, pdl));
             launches++;
         }
@@ -473,17 +388,14 @@ void Seq::launch_token_pass(bool from_prompt, int prompt_idx, int pos_value, boo
     if (want_logits) {
         // the lm_head epilogue keeps the packed (value, index) arg-max of the logits it writes
         CUDA_CHECK(cudaMemsetAsync(&sd->argmax_key, 0, sizeof(unsigned long long), st));
-        if (!ring_launch({&m->output.t}, {logits.as<float>()}, EPI_STORE, hp.n_embd, x.as<float>(),
-                         m->output_norm.as<float>(), &sd->argmax_key, false)) {
-            GemvParams p{};
-            p.n_seg = 1; p.epi = EPI_STORE; p.k = hp.n_embd;
-            p.seg[0] = m->output.w; p.out[0] = logits.as<float>();
-            p.x = x.as<float>(); p.norm_w = m->output_norm.as<float>(); p.eps = hp.rms_eps;
-            p.argmax_key = &sd->argmax_key;
-            p.trace = trace_base && launches < 4096 ? trace_base + (size_t)launches * 8 : nullptr;
-            TIMED(0, launch_gemv(p, gemv_plan_grid(p, n_sms), st, false));
-            launches++;
-        }
+        GemvParams p{};
+        p.n_seg = 1; p.epi = EPI_STORE; p.k = hp.n_embd;
+        p.seg[0] = m->output.w; p.out[0] = logits.as<float>();
+        p.x = x.as<float>(); p.norm_w = m->output_norm.as<float>(); p.eps = hp.rms_eps;
+        p.argmax_key = &sd->argmax_key;
+        p.trace = trace_slot();
+        TIMED(0, launch_gemv(p, gemv_plan_grid(p, n_sms), st, false));
+        launches++;
     }
     if (n_launch) *n_launch += launches;
 }
@@ -609,8 +521,7 @@ void Seq::prefill_chunk(int idx0, int T, int pos0, bool want_logits, cudaStream_
             a.n_head = hp.n_head; a.n_kv = hp.n_head_kv; a.hd = hp.head_dim; a.n_rot = hp.n_rot;
             a.n_split = m->attn_splits; a.n_ctx = hp.n_ctx;
             a.scale = 1.0f / sqrtf((float)hp.head_dim);
-            const int amode = (m->eng->flags & AIOS_ENGINE_ATTN_CLUSTER) ? 2 : (m->eng->flags & AIOS_ENGINE_ATTN_HEAD) ? 1 : 0;
-            launch_attn_decode(a, st, false, amode);
+            launch_attn_decode(a, st, false, (m->eng->flags & AIOS_ENGINE_ATTN_CLUSTER) ? 2 : 0);
         }
         img = -1;
         matmul(L.wo.w, ATT, QD, nullptr, X, E, EPI_ADD, img);
@@ -871,7 +782,7 @@ void Seq::build_pfd() {
     p.att_group = std::max(1, std::min(16, n_sms / hp.n_head_kv));
     p.att_per_cap = ((hp.n_ctx + p.att_group - 1) / p.att_group + 1) & ~1;
     p.att_max = pfd_att_max.as<float>(); p.att_sum = pfd_att_sum.as<double>(); p.att_acc = pfd_att_acc.as<double>();
-    p.att_counters = pfd_counters.as<unsigned>(); p.bar_counter = pfd_counters.as<unsigned>() + 16;
+    p.att_counters = pfd_counters.as<unsigned>(); p.bar_counter = pfd_counters.as<unsigned>() + hp.n_head_kv;
     p.k_max = std::max(std::max(hp.n_embd, hp.n_ff), QD);
     pfd_timing = DevBuf(ph.size() * 4 * sizeof(unsigned long long));
     CUDA_CHECK(cudaMemset(pfd_timing.p, 0, pfd_timing.bytes));

@@ -49,14 +49,10 @@ struct DevMatrix {
     WPlanes w{};      // planes layout (layout.cuh)
     DevBuf storage;   // one allocation holding all planes
     size_t src_bytes = 0;
-    WTiles t{};       // stream tiles for the TMA-ring GEMV (layout.cuh); t.base == nullptr when not built
-    DevBuf tile_storage;
 };
 
 struct Layer {
     DevMatrix wq, wk, wv, wo, w_gate, w_up, w_down;
-    WTiles gate_up{};            // PAIR tiles of (ffn_gate, ffn_up)
-    DevBuf gate_up_storage;
     DevBuf attn_norm, ffn_norm;  // f32
 };
 
@@ -80,7 +76,11 @@ struct Model {
     DevMatrix output;     // output.weight (or the tied embedding) in planes layout
     DevBuf output_norm;
     DevBuf rope_cos, rope_sin;  // [n_ctx][n_rot/2], host-computed (glibc cosf/sinf, as the oracle)
-    DevBuf kv;            // [max_batch][n_layer][2][n_ctx][n_kv*hd] f16
+    // KV slots: max_batch for the caller's sequences (aios_seq_create, aios_generate) plus HIDDEN_SLOTS the library
+    // keeps for itself (aios_forward_logits' scratch sequence, the request scheduler's sequence), so that internal
+    // sequences never eat into the budget the caller was promised
+    static constexpr int HIDDEN_SLOTS = 2;
+    DevBuf kv;            // [max_batch + HIDDEN_SLOTS][n_layer][2][n_ctx][n_kv*hd] f16
     std::vector<bool> slot_used;
     int64_t weight_bytes = 0, weight_bytes_per_token = 0;
     std::mutex mu;
@@ -92,11 +92,8 @@ struct Model {
     uint16_t *v_cache(int slot, int layer) const;
     size_t kv_layer_elems() const { return (size_t)hp.n_ctx * hp.n_head_kv * hp.head_dim; }
 
-    bool ring = false;    // stream tiles were built: token passes use the TMA-ring GEMV (gemv_ring.cu)
-
    private:
     void upload_matrix(const GgufTensor &t, DevMatrix &dst, DevBuf &staging, void *pinned, size_t pinned_bytes);
-    void build_tiles(DevMatrix &m);
 };
 
 struct SeqState {  // lives in device memory
@@ -115,7 +112,6 @@ struct Seq {
     DevBuf state, x, qkv, att, h, logits, out_tokens, prompt, attn_scratch, attn_counters, snap_logits;
     int snap_n_past = -1;
     struct KernelTimer *timer = nullptr;  // non-null only inside profile_decode
-    DevBuf h_image, h_counters;  // ffn_down's activation image, quantised by the SwiGLU epilogue (GemvParams::q_image)
     // prompt chunks (prefill_chunk): activations of up to 32 tokens side by side, their quantised images, positions
     DevBuf cx, cqkv, catt, ch, cgu, cimg, cpos;
     DevBuf trace;
@@ -128,7 +124,8 @@ struct Seq {
     PfdParams pfd{};
     int pfd_grid = 0;
 
-    explicit Seq(Model *m);
+    // internal = true: one of the library's own sequences (takes a hidden slot, never a caller's)
+    explicit Seq(Model *m, bool internal = false);
     ~Seq();
     void reset();
     void prefill(const int32_t *tokens, int n);

@@ -286,11 +286,8 @@ void launch_gemm_q(const WPlanes &w, const uint8_t *images, int T, float *out, i
     const size_t smem = w.type == T_Q4_K ? gemm_smem_bytes<T_Q4_K>(8 * nt) : gemm_smem_bytes<T_Q8_0>(8 * nt);
 #define GEMM_LAUNCH(TY, NTV)                                                                                          \
     do {                                                                                                              \
-        static bool attr_set = false;                                                                                 \
-        if (!attr_set) {                                                                                              \
-            CUDA_CHECK(cudaFuncSetAttribute(gemm_q_kernel<TY, NTV>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024)); \
-            attr_set = true;                                                                                          \
-        }                                                                                                             \
+        static PerDeviceOnce once;                                                                                    \
+        once.run([] { CUDA_CHECK(cudaFuncSetAttribute(gemm_q_kernel<TY, NTV>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024)); }); \
         gemm_q_kernel<TY, NTV><<<grid, GEMM_THREADS, smem, st>>>(p);                                                  \
     } while (0)
     if (w.type == T_Q4_K) {

@@ -117,18 +117,11 @@ __global__ void __launch_bounds__(GEMV_THREADS, 1) gemv_kernel(const GemvParams 
             }
         }
     }
-    if (pair && p.q_image) {
-        __threadfence();
-        report_rows_and_quantise(p, out, row_first, row_step, N);
-    }
     if (p.argmax_key) {
         const unsigned long long other = __shfl_sync(0xffffffffu, best, 16);
         best = other > best ? other : best;
         if (lane == 0 && best) atomicMax(p.argmax_key, best);
     }
-    // This CTA's rows are done: HBM is about to idle through this launch's tail, the dependency hand-over and the
-    // next launch's activation prologue.  Ask L2 to fetch the next launch's weights through that hole (opt-in).
-    l2_prefetch_next(p);
 }
 
 // ---------------------------------------------------------------- double-buffered variant
@@ -197,7 +190,7 @@ __device__ __forceinline__ void gemv_db_body(const GemvParams &p, int seg, uint8
     for (int b = 0; b < NB; b++) load_next(g[b]);  // all images are requested before the dependency wait
     asm volatile("griddepcontrol.wait;" ::: "memory");
     trace_mark(tr, 1);
-    if (p.x_image) copy_activation_image(p.x_image, p.k, smem);  // quantised by the previous launch's epilogue
+    if (p.x_image) copy_activation_image(p.x_image, p.k, smem);
     else if (TYPE == T_Q6_K) prep_activations<PERM_Q6>(p.x, p.norm_w, p.eps, p.k, s, red);
     else if (TYPE == T_Q8_0) prep_activations<PERM_Q80>(p.x, p.norm_w, p.eps, p.k, s, red);
     else prep_activations<PERM_Q4>(p.x, p.norm_w, p.eps, p.k, s, red);
@@ -242,10 +235,6 @@ __device__ __forceinline__ void gemv_db_body(const GemvParams &p, int seg, uint8
         for (int b = 0; b < NB; b++) {
             if (crow < N) step(g[b]);
         }
-    }
-    if (pair && p.q_image) {  // report this warp's rows; the warp that completes a slab quantises it for ffn_down
-        __threadfence();
-        report_rows_and_quantise(p, out, row_first, row_step, N);
     }
     trace_mark(tr, 4);
     if (p.trace && threadIdx.x == 0) {
@@ -322,39 +311,25 @@ int gemv_plan_grid(GemvParams &p, int n_sms) {
     return begin;
 }
 
-static int g_n_sms = 148;
 // N-buffered register pipeline (gemv_db_kernel): 2 = default (1.92 -> 1.79 ms/token), 3 spills (2.01), 0 = gemv_kernel.
 // AIOS_GEMV_DB=0/2/3 overrides for A/B runs.
 static int g_use_db = 2;
-static bool g_use_staged = false;  // measured slower than the register pipeline so far (profiles/r01_v3_gemv.md)
-void gemv_set_staged(bool on) { g_use_staged = on; }
 
 void gemv_init() {
-    static bool done = false;
-    if (done) return;
-    CUDA_CHECK(cudaFuncSetAttribute(gemv_kernel<T_Q4_K>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
-    CUDA_CHECK(cudaFuncSetAttribute(gemv_kernel<T_Q5_K>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
-    CUDA_CHECK(cudaFuncSetAttribute(gemv_kernel<T_Q6_K>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
-    CUDA_CHECK(cudaFuncSetAttribute(gemv_kernel<T_Q8_0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
-    // one shared-memory carve-out for every kernel of the token pass: kernels with different carve-outs cannot share
-    // an SM, which would serialise the programmatic-dependent-launch overlap (measured: 1.89 -> 2.07 ms/token)
-    CUDA_CHECK(cudaFuncSetAttribute(gemv_kernel<T_Q4_K>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
-    CUDA_CHECK(cudaFuncSetAttribute(gemv_kernel<T_Q5_K>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
-    CUDA_CHECK(cudaFuncSetAttribute(gemv_kernel<T_Q6_K>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
-    CUDA_CHECK(cudaFuncSetAttribute(gemv_kernel<T_Q8_0>, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
-    auto prep = [](auto kern) {
-        CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
-        CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
-    };
-    prep(gemv_db_kernel<T_Q4_K, 2>); prep(gemv_db_kernel<T_Q5_K, 2>); prep(gemv_db_kernel<T_Q6_K, 2>); prep(gemv_db_kernel<T_Q8_0, 2>);
-    prep(gemv_db_kernel<T_Q4_K, 3>); prep(gemv_db_kernel<T_Q6_K, 3>);
-    prep(gemv_db_mixed_kernel);
-    if (const char *e = getenv("AIOS_GEMV_DB")) g_use_db = atoi(e);
-    int dev = 0;
-    CUDA_CHECK(cudaGetDevice(&dev));
-    CUDA_CHECK(cudaDeviceGetAttribute(&g_n_sms, cudaDevAttrMultiProcessorCount, dev));
-    gemv_staged_init();
-    done = true;
+    static PerDeviceOnce once;
+    once.run([] {
+        // one shared-memory carve-out for every kernel of the token pass: kernels with different carve-outs cannot
+        // share an SM, which would serialise the programmatic-dependent-launch overlap (measured: 1.89 -> 2.07 ms/token)
+        auto prep = [](auto kern) {
+            CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, 100 * 1024));
+            CUDA_CHECK(cudaFuncSetAttribute(kern, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared));
+        };
+        prep(gemv_kernel<T_Q4_K>); prep(gemv_kernel<T_Q5_K>); prep(gemv_kernel<T_Q6_K>); prep(gemv_kernel<T_Q8_0>);
+        prep(gemv_db_kernel<T_Q4_K, 2>); prep(gemv_db_kernel<T_Q5_K, 2>); prep(gemv_db_kernel<T_Q6_K, 2>); prep(gemv_db_kernel<T_Q8_0, 2>);
+        prep(gemv_db_kernel<T_Q4_K, 3>); prep(gemv_db_kernel<T_Q6_K, 3>);
+        prep(gemv_db_mixed_kernel);
+        if (const char *e = getenv("AIOS_GEMV_DB")) g_use_db = atoi(e);
+    });
 }
 
 // Q4_K and Q6_K matrices may share a launch (gemv_db_mixed_kernel) when K is a whole number of 2048-weight passes
@@ -372,10 +347,6 @@ void launch_gemv(const GemvParams &p_in, int grid, cudaStream_t st, bool pdl) {
     bool mixed = false;
     for (int i = 1; i < p.n_seg; i++) mixed |= p.seg[i].type != t;
     if (mixed && !gemv_can_mix(p)) throw CudaError("launch_gemv: segments of one launch must share a weight type");
-    if (g_use_staged && gemv_staged_usable(p, g_n_sms)) {  // big matrix: the cp.async ring keeps more bytes in flight
-        launch_gemv_staged(p, g_n_sms, st, pdl);
-        return;
-    }
     cudaLaunchConfig_t cfg{};
     cfg.gridDim = dim3(grid);
     cfg.blockDim = dim3(GEMV_THREADS);

@@ -280,21 +280,6 @@ __device__ void prep_activations_pre(const float *__restrict__ x, const float *_
 }
 
 // ---------------------------------------------------------------- weight registers of one pass
-// L2 prefetch of the next launch's weight planes: CTA b of g takes the b-th slice of every range
-__device__ __forceinline__ void l2_prefetch_next(const GemvParams &p) {
-    constexpr uint32_t PIECE = 4096;
-    for (int i = 0; i < p.n_pf; i++) {
-        const uint32_t bytes = p.pf_bytes[i];
-        const uint32_t per = ((bytes + gridDim.x - 1) / gridDim.x + 15u) & ~15u;
-        const uint32_t lo = blockIdx.x * per;
-        const uint32_t hi = lo + per < bytes ? lo + per : bytes;
-        for (uint32_t o = lo + threadIdx.x * PIECE; o < hi; o += GEMV_THREADS * PIECE) {
-            const uint32_t sz = ((hi - o < PIECE ? hi - o : PIECE) + 15u) & ~15u;  // planes are padded to 256 B
-            asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;" ::"l"(p.pf_ptr[i] + o), "r"(sz) : "memory");
-        }
-    }
-}
-
 struct RowPtrs {
     const uint8_t *p[5];  // row starts inside each plane
 };
@@ -493,46 +478,7 @@ __device__ __forceinline__ double warp_sum2_f64(double a0, double a1) {
     return v;
 }
 
-// Producer side of GemvParams::q_image: called by a whole warp after its lane 0 has stored out[row].  The warp whose
-// row is the 256th of its slab quantises the slab (same quant_slab as every consumer-side prologue) into the global
-// image and re-arms the counter.
-// The caller has fenced (__threadfence) after its last store to out[] and before the first call: a fence per row would
-// drain the warp's in-flight weight loads every time (measured: +0.23 ms/token), so a warp reports all its rows at
-// the end of its loop.
-// A returning atomic is a round trip to L2: the warp's rows are therefore reported by one lane each, all at once
-// (lane i: row_first + i * row_step), not one after the other.
-__device__ __forceinline__ void quantise_slab_to_image(const GemvParams &p, const float *out, int b);
-
-__device__ __forceinline__ void report_rows_and_quantise(const GemvParams &p, const float *out, int row_first, int row_step, int n) {
-    const int lane = threadIdx.x & 31;
-    for (int base = row_first; base < n; base += 32 * row_step) {
-        const int row = base + lane * row_step;
-        unsigned old = 0;
-        if (row < n) old = atomicAdd(p.q_counters + (size_t)(row >> 8) * 32, 1u);  // one 128-byte line per counter
-        unsigned done = __ballot_sync(0xffffffffu, row < n && old == 255u);
-        while (done) {  // (rare) this warp's row was the 256th of a slab
-            const int src = __ffs(done) - 1;
-            done &= done - 1;
-            quantise_slab_to_image(p, out, (base + src * row_step) >> 8);
-        }
-    }
-}
-
-__device__ __forceinline__ void quantise_slab_to_image(const GemvParams &p, const float *out, int b) {
-    const int lane = threadIdx.x & 31;
-    __threadfence();  // the count before the other warps' rows
-    float v[8];
-    const float4 lo = __ldcg(reinterpret_cast<const float4 *>(out + b * 256 + lane * 8));
-    const float4 hi = __ldcg(reinterpret_cast<const float4 *>(out + b * 256 + lane * 8 + 4));
-    v[0] = lo.x; v[1] = lo.y; v[2] = lo.z; v[3] = lo.w; v[4] = hi.x; v[5] = hi.y; v[6] = hi.z; v[7] = hi.w;
-    const ActSmem g = carve(p.q_image, p.q_k);
-    if (p.q_perm == PERM_Q6) quant_slab<PERM_Q6>(v, b, p.q_k, g);
-    else if (p.q_perm == PERM_Q80) quant_slab<PERM_Q80>(v, b, p.q_k, g);
-    else quant_slab<PERM_Q4>(v, b, p.q_k, g);
-    if (lane == 0) p.q_counters[(size_t)b * 32] = 0;
-}
-
-// Consumer side: the activation image was built by the previous launch — copy it into shared memory.
+// The activation image was built by an earlier launch (quant_rows_kernel) — copy it into shared memory.
 __device__ __forceinline__ void copy_activation_image(const uint8_t *__restrict__ image, int k, uint8_t *smem) {
     const int n16 = (int)(act_image_bytes(k) / 16);
     for (int i = threadIdx.x; i < n16; i += GEMV_THREADS)

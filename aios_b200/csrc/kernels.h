@@ -41,23 +41,13 @@ struct GemvParams {
     const float *norm_w;    // if non-null: x <- rmsnorm(x) * norm_w first (llama attn_norm / ffn_norm / output_norm)
     float eps;
     unsigned long long *argmax_key;  // if non-null (EPI_STORE, 1 segment): running packed (value,index) max
-    // weights of the NEXT launch of the token pass: every CTA asks L2 to fetch its slice of them
-    // (cp.async.bulk.prefetch.L2), so HBM keeps streaming through this launch's tail and the next one's start
-    int32_t n_pf;
-    const uint8_t *pf_ptr[12];
-    uint32_t pf_bytes[12];
     // timeline of CTA 0 (null = off; gemv_db_kernel): [0] entry [1] dependency wait over [2] activations ready
     // [4] CTA 0 done [7] last CTA done
     unsigned long long *trace;
     RopeKv rope;
-    // Producer-side activation quantisation (EPI_SWIGLU launches): the warp whose row completes a 256-slab of the
-    // output (per-slab arrival counter) quantises that slab for the NEXT launch and writes it, in that launch's
-    // shared-memory image layout, to q_image.  The consumer then gets x_image = the same buffer and its prologue is
-    // a 17 KB copy instead of 4-5 us of loads + quantisation (ffn_down, K = 14336).  Counters are zero between tokens.
-    uint8_t *q_image;
-    uint32_t *q_counters;
-    int32_t q_perm, q_k;      // image permutation (PERM_* of the consumer's weight type) and the consumer's K
-    const uint8_t *x_image;   // consumer side: ready-made activation image (x is not read)
+    // ready-made activation image in global memory (quant_rows_kernel, gemm_q.cu), in this launch's shared-memory
+    // image layout: the prologue becomes a copy and x / norm_w are not read
+    const uint8_t *x_image;
 };
 
 // fills cta_begin[] and returns the grid size; n_sms from the device
@@ -66,10 +56,6 @@ size_t gemv_smem_bytes(int k);
 void launch_gemv(const GemvParams &p, int grid, cudaStream_t st, bool pdl = false);
 bool gemv_can_mix(const GemvParams &p);  // may Q4_K and Q6_K segments of p ride in one launch?
 void gemv_init();  // one-time function attributes (dynamic smem)
-// large matrices: per-warp cp.async ring in shared memory (gemv_staged.cu); launch_gemv picks it when usable
-bool gemv_staged_usable(const GemvParams &p, int n_sms);
-void launch_gemv_staged(const GemvParams &p, int n_sms, cudaStream_t st, bool pdl);
-void gemv_staged_init();
 
 // ---- gemm_q.cu : multi-token (prompt chunk) dequant GEMM on int8 tensor cores, bit-identical to T GEMV calls
 // per-token Q8_K / Q8_0 activation images in global memory (optionally RMS-normed first); x row stride ldx floats
@@ -81,31 +67,6 @@ bool gemm_q_usable(int type, int k);     // Q4_K / Q8_0
 void launch_gemm_q(const WPlanes &w, const uint8_t *images, int T, float *out, int64_t ldo, int epi, cudaStream_t st);
 // h[t][0..ff) = silu(gu[t][0..ff)) * gu[t][ff..2ff)
 void launch_swiglu_rows(const float *gu, int64_t ldgu, int ff, int T, float *h, int64_t ldh, cudaStream_t st);
-
-// ---- gemv_ring.cu : the same fused op fed by a TMA ring (stream tiles of layout.cuh)
-// build the tiles of a [N][K] matrix (b == nullptr) or the PAIR tiles of two matrices from their planes
-size_t tiles_total_bytes(int type, int n_rows, int k, bool pair);
-void launch_build_tiles(const WPlanes &a, const WPlanes *b, uint8_t *dst, WTiles *out, cudaStream_t st);
-struct RingParams {
-    int32_t n_seg;          // 1..3 tile streams sharing the same input vector
-    int32_t epi;            // GemvEpilogue; EPI_SWIGLU wants one PAIR stream
-    int32_t k;
-    int32_t ct;             // K tiles per row tile (same for all segments)
-    int32_t rt_begin[4];    // row-tile ranges per segment
-    WTiles seg[3];
-    float *out[3];
-    const float *x;
-    const float *norm_w;
-    float eps;
-    unsigned long long *argmax_key;
-    int32_t n_slots, slot_bytes;  // shared-memory ring geometry (host-chosen)
-    // timeline of CTA 0 (null = off): [0] entry [1] dependency wait over [2] activations ready [3] first tile landed
-    // [4] consumers done [5] producer's first copy issued [6] producer's last copy issued
-    unsigned long long *trace;
-};
-bool gemv_ring_usable(const RingParams &p);
-void launch_gemv_ring(RingParams &p, int n_sms, cudaStream_t st, bool pdl);
-void gemv_ring_init();
 
 // ---- attention.cu : RoPE + KV write + flash-decode over the f16 KV cache (one new token)
 struct AttnParams {
@@ -126,17 +87,13 @@ struct AttnParams {
     int32_t kv_ready;
     int32_t stage_cap;  // set by launch_attn_decode_split: cache rows staged in shared memory (kv_ready launches)
 };
-// mode: 0 = pick (split kernel when usable, else per-head, else cluster); 1 = per-head kernel; 2 = cluster kernel
+// mode: 0 = pick (split kernel when usable, else cluster); 2 = cluster kernel
 void launch_attn_decode(const AttnParams &p, cudaStream_t st, bool pdl = false, int mode = 0);
 // one wave of independent (query head, head-dim slice) CTAs, launched with PDL (attention_split.cu)
 bool attn_split_usable(int n_ctx, int hd);
 void attn_split_init();
 void launch_attn_decode_split(const AttnParams &p, cudaStream_t st, bool pdl);
 void attn_init();  // one-time function attributes (dynamic smem)
-// short contexts: one CTA per query head, no cross-CTA exchange (attention_head.cu)
-bool attn_head_usable(int n_ctx, int hd);
-void launch_attn_decode_head(const AttnParams &p, cudaStream_t st);
-void attn_head_init();
 size_t attn_scratch_floats(int n_head, int n_split, int hd);
 
 // ---- sampler.cu

@@ -72,32 +72,4 @@ inline size_t plane_bytes(int t, int i, int64_t n_rows, int64_t k) {
     return 0;
 }
 
-// ---------------------------------------------------------------- stream tiles (gemv_ring.cu)
-// The same bytes once more, cut for TMA bulk copies: a TILE is 16 rows x 32 units (2048 weights per row), stored as
-// one contiguous blob, plane after plane, so that ONE cp.async.bulk moves it into a shared-memory ring slot:
-//   Q4_K tile (18432 B): QSa[16][32][16] | QSb[16][32][16] | META[16][8][16]
-//   Q6_K tile (26880 B): QLa[16][32][16] | QLb[16][32][16] | QH[16][32][16] | SC[16][32][4] | D[16][8][2]
-// Tiles are ordered [row tile][K tile]: the CT = ceil(U/32) tiles of a row tile are consecutive.  Rows beyond N and
-// units beyond U are zero bytes (zero quants and zero scales: they contribute exactly 0).
-// Tile row r of row tile rt is matrix row 16*rt + r; warp w of the consumer CTA takes tile rows w and w+8.
-// PAIR tiles fuse two matrices that feed one SwiGLU (ffn_gate, ffn_up): tile rows 0..7 are rows 8*rt + (0..7) of the
-// first matrix, tile rows 8..15 the same rows of the second one — so warp w holds gate row and up row 8*rt + w.
-constexpr int TILE_ROWS = 16, TILE_UNITS = 32;
-inline size_t tile_bytes(int t) {
-    switch (t) {
-        case T_Q4_K: return 16 * 32 * 32 + 16 * 8 * 16;
-        case T_Q6_K: return 16 * 32 * 48 + 16 * 32 * 4 + 16 * 8 * 2;
-    }
-    return 0;
-}
-struct WTiles {
-    const uint8_t *base = nullptr;
-    int32_t type = 0;
-    int32_t n_out = 0;   // output rows (N; for PAIR tiles N of each of the two matrices)
-    int32_t k = 0;
-    int32_t n_rt = 0;    // row tiles: ceil(N/16), PAIR: ceil(N/8)
-    int32_t ct = 0;      // K tiles per row tile
-    int32_t pair = 0;
-};
-
 }  // namespace aios

@@ -53,7 +53,9 @@ const char *aios_version(void);
 /* ---- engine: replaces runtime/src/main.rs:50-51 (ModelManager + InferenceEngine construction) */
 typedef struct aios_engine_opts {
     int32_t device;      /* CUDA ordinal                                                     */
-    int32_t max_batch;   /* max concurrent sequences per model (KV slots); 0 -> 1            */
+    int32_t max_batch;   /* max concurrent sequences per model the CALLER may hold (aios_seq_create,
+                            aios_generate); 0 -> 1.  The library's own sequences (aios_forward_logits' scratch,
+                            the request scheduler's) live in extra hidden KV slots and never count against it */
     int32_t flags;       /* AIOS_ENGINE_* bits                                               */
     int32_t reserved;
 } aios_engine_opts;
@@ -61,14 +63,12 @@ typedef struct aios_engine_opts {
 #define AIOS_ENGINE_NO_PDL 2   /* no programmatic dependent launch between the GEMV kernels (debug) */
 #define AIOS_ENGINE_NO_PFD 4   /* greedy decode through per-op kernels instead of the persistent fused kernel */
 #define AIOS_ENGINE_USE_PFD 8  /* greedy decode through the persistent fused decode kernel (pfd.cu) */
-#define AIOS_ENGINE_L2_PREFETCH 16 /* GEMV launches prefetch the next launch's weights into L2 (experiment; slower so far) */
-#define AIOS_ENGINE_ATTN_HEAD 32    /* decode attention: one CTA per query head (attention_head.cu) instead of the split kernel */
 #define AIOS_ENGINE_ATTN_CLUSTER 64 /* decode attention: the cluster / DSMEM kernel (attention.cu) at every context length */
-#define AIOS_ENGINE_NO_GEMM 1024 /* prefill token by token through the decode kernels instead of 32-token chunks through the tensor-core GEMM */
-#define AIOS_ENGINE_PRODUCER_QUANT 512 /* the SwiGLU epilogue quantises ffn_down's input slab by slab (experiment; slower so far) */
 #define AIOS_ENGINE_NO_ROPE_EPILOGUE 256/* RoPE / KV append in the attention kernel instead of the q/k/v GEMV's epilogue */
-#define AIOS_ENGINE_USE_RING 128   /* GEMV through the TMA-ring kernel (gemv_ring.cu): a second, tile-ordered copy of the
-                                       Q4_K/Q6_K weights is built at load; experiment, slower than gemv.cu so far */
+#define AIOS_ENGINE_NO_GEMM 1024 /* prefill token by token through the decode kernels instead of prompt chunks through the tensor-core GEMM */
+/* (bits 16, 32, 128 and 512 selected round-1 experiments — L2 prefetch, per-head attention, TMA-ring GEMV, producer-side
+ * quantisation — that measured slower than the default path and were removed; their profiles are under profiles/r01_*.
+ * The bits are ignored.) */
 
 int aios_engine_create(const aios_engine_opts *opts, aios_engine **out);
 void aios_engine_destroy(aios_engine *e);
