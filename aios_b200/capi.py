@@ -101,6 +101,8 @@ SYMBOLS = {
     "aios_seq_step": (C.c_int, [_P, C.POINTER(Sampling), C.POINTER(C.c_int32)]),
     "aios_seq_decode_static": (C.c_int, [_P, C.c_int32, _P, C.POINTER(C.c_int32)]),
     "aios_seq_logits": (C.c_int, [_P, _P]),
+    "aios_seq_set_mask": (C.c_int, [_P, _P, C.c_int32]),
+    "aios_sample_logits": (C.c_int, [_P, _P, C.c_int32, _P, C.POINTER(Sampling), C.c_uint64, C.POINTER(C.c_int32), _P, _P]),
     "aios_generate": (C.c_int, [_P, _P, C.c_int32, C.POINTER(Sampling), C.c_int32, _P, C.POINTER(C.c_int32)]),
     "aios_request_submit": (C.c_int, [_P, _P, C.c_int32, C.POINTER(Sampling), C.c_int32, C.c_int32, C.POINTER(_P)]),
     "aios_request_poll": (C.c_int, [_P, _P, C.c_int32, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
@@ -268,6 +270,18 @@ class Engine:
                                  _ptr(nw) if nw is not None else None, eps, _ptr(y)))
         return y
 
+    def sample_logits(self, logits: np.ndarray, sampling: Sampling, counter: int = 0, mask: np.ndarray | None = None):
+        """One run of the on-device sampler chain on host logits (aios_sample_logits): returns (token, candidate ids
+        best first, (K, n after top-p, n after min-p))."""
+        lg = np.ascontiguousarray(logits, dtype=np.float32)
+        mk = np.ascontiguousarray(mask, dtype=np.uint8) if mask is not None else None
+        tok = C.c_int32(0)
+        cand = np.empty(128, dtype=np.int32)
+        counts = np.zeros(3, dtype=np.int32)
+        _check(lib().aios_sample_logits(self.h, _ptr(lg), lg.size, _ptr(mk) if mk is not None else None,
+                                        C.byref(sampling), int(counter), C.byref(tok), _ptr(cand), _ptr(counts)))
+        return tok.value, cand[: counts[0]].copy(), tuple(int(c) for c in counts)
+
     def bench_gemv(self, qtype: int, n_rows: int, k: int, n_copies: int, iters: int) -> float:
         ms = C.c_float(0)
         _check(lib().aios_bench_gemv(self.h, qtype, n_rows, k, n_copies, iters, C.byref(ms)))
@@ -420,6 +434,14 @@ class Seq:
         sp = sampling if sampling is not None else Sampling()
         _check(lib().aios_seq_step(self.h, C.byref(sp), C.byref(t)))
         return t.value
+
+    def set_mask(self, mask: np.ndarray | None):
+        """Logit mask for the sampler: packed bits (bit i of byte i//8 = token i allowed); None clears it."""
+        if mask is None:
+            _check(lib().aios_seq_set_mask(self.h, None, 0))
+            return
+        mk = np.ascontiguousarray(mask, dtype=np.uint8)
+        _check(lib().aios_seq_set_mask(self.h, _ptr(mk), mk.size))
 
     def logits(self) -> np.ndarray:
         out = np.empty(self.model.info.n_vocab, dtype=np.float32)

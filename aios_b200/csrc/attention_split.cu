@@ -111,6 +111,7 @@ __global__ void __launch_bounds__(AS_THREADS, 1) attn_split_kernel(const AttnPar
 
     unsigned long long *tr = (blockIdx.x == 0 && threadIdx.x == 0) ? p.trace : nullptr;
     trace_mark(tr, 0);
+    if (tr) tr[3] = 2ull;  // launch kind: attention
     // the successor only prefetches weights until this grid has completed: let it start now
     asm volatile("griddepcontrol.launch_dependents;");
 
@@ -339,6 +340,11 @@ __global__ void __launch_bounds__(AS_THREADS, 1) attn_split_kernel(const AttnPar
         p.out[(size_t)h * HD + part_id * DPC + d] = (float)s;
     }
     trace_mark(tr, 4);
+    if (p.trace && threadIdx.x == 0) {  // [7]: when the last CTA of the launch finished
+        unsigned long long now;
+        asm volatile("mov.u64 %0, %globaltimer;" : "=l"(now));
+        atomicMax(p.trace + 7, now);
+    }
 }
 
 static size_t as_smem(int n_ctx, int hd, int split) {

@@ -466,6 +466,14 @@ int aios_seq_decode_static(aios_seq *s, int32_t max_tokens, int32_t *out_tokens,
         return (int)AIOS_OK;
     });
 }
+int aios_seq_set_mask(aios_seq *s, const uint8_t *mask_bits, int32_t n_bytes) {
+    return guarded([&] {
+        if (!s || (mask_bits && n_bytes <= 0)) return fail(AIOS_E_INVAL, "bad argument");
+        std::lock_guard<std::mutex> lk(s->impl.m->eng->mu);
+        s->impl.set_mask(mask_bits, n_bytes);
+        return (int)AIOS_OK;
+    });
+}
 int aios_seq_logits(aios_seq *s, float *logits_out) {
     return guarded([&] {
         if (!s || !logits_out) return fail(AIOS_E_INVAL, "bad argument");
@@ -656,6 +664,43 @@ int aios_matmul(aios_engine *e, int32_t type, const void *w_blocks, int64_t n_ro
         launch_gemm_q(dm.w, img.as<uint8_t>(), n_tok, dy.as<float>(), n_rows, EPI_STORE, E.stream);
         CUDA_CHECK(cudaMemcpyAsync(y, dy.p, dy.bytes, cudaMemcpyDeviceToHost, E.stream));
         CUDA_CHECK(cudaStreamSynchronize(E.stream));
+        return (int)AIOS_OK;
+    });
+}
+
+int aios_sample_logits(aios_engine *e, const float *logits, int32_t n_vocab, const uint8_t *mask_bits, const aios_sampling *sp,
+                       uint64_t counter, int32_t *token, int32_t *cand, int32_t *counts) {
+    return guarded([&] {
+        if (!e || !logits || n_vocab <= 0 || !token) return fail(AIOS_E_INVAL, "bad argument");
+        if (counter > 0x7fffffffull) return fail(AIOS_E_RANGE, "counter beyond 2^31-1");
+        aios_sampling d{};
+        if (sp) d = *sp;
+        std::lock_guard<std::mutex> lk(e->impl.mu);
+        Engine &E = e->impl;
+        E.make_current();
+        const size_t mb = ((size_t)n_vocab + 7) / 8;
+        DevBuf dl((size_t)n_vocab * 4), dm(mask_bits ? mb : 0), st(64), outs((128 + 3 + 4) * 4);
+        int32_t *o = outs.as<int32_t>();  // [0] token slot (out_tokens), [1..129) cand, [129..132) counts
+        int32_t hdr[4] = {(int32_t)counter, 0, 0, 0};  // pos (the draw's counter), step, cur_token
+        CUDA_CHECK(cudaMemcpyAsync(st.p, hdr, sizeof(hdr), cudaMemcpyHostToDevice, E.stream));
+        CUDA_CHECK(cudaMemcpyAsync(dl.p, logits, (size_t)n_vocab * 4, cudaMemcpyHostToDevice, E.stream));
+        if (mask_bits) CUDA_CHECK(cudaMemcpyAsync(dm.p, mask_bits, mb, cudaMemcpyHostToDevice, E.stream));
+        CUDA_CHECK(cudaMemsetAsync(outs.p, 0xff, outs.bytes, E.stream));
+        SampleParams s{};
+        s.logits = dl.as<float>(); s.n_vocab = n_vocab;
+        s.temperature = d.temperature; s.top_k = d.top_k; s.top_p = d.top_p; s.min_p = d.min_p; s.seed = d.seed;
+        s.pos_ptr = st.as<int32_t>(); s.step_ptr = st.as<int32_t>() + 1; s.cur_token = st.as<int32_t>() + 2;
+        s.out_tokens = o; s.out_cap = 1;
+        s.mask = mask_bits ? dm.as<uint8_t>() : nullptr;
+        s.cand_out = o + 1; s.counts_out = o + 129;
+        launch_sample(s, E.stream);
+        CUDA_CHECK(cudaGetLastError());
+        int32_t host[132];
+        CUDA_CHECK(cudaMemcpyAsync(host, outs.p, sizeof(host), cudaMemcpyDeviceToHost, E.stream));
+        CUDA_CHECK(cudaStreamSynchronize(E.stream));
+        *token = host[0];
+        if (cand) memcpy(cand, host + 1, 128 * 4);
+        if (counts) memcpy(counts, host + 129, 3 * 4);
         return (int)AIOS_OK;
     });
 }

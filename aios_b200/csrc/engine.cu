@@ -408,6 +408,7 @@ void Seq::launch_sample_kernel(const aios_sampling &sp, cudaStream_t st) {
     s.temperature = sp.temperature; s.top_k = sp.top_k; s.top_p = sp.top_p; s.min_p = sp.min_p; s.seed = sp.seed;
     s.pos_ptr = &sd->pos; s.step_ptr = &sd->step; s.cur_token = &sd->cur_token;
     s.out_tokens = out_tokens.as<int32_t>(); s.out_cap = m->hp.n_ctx;
+    s.mask = mask_on ? mask.as<uint8_t>() : nullptr;
     TIMED(2, launch_sample(s, st));
 }
 
@@ -439,7 +440,7 @@ static bool same_sampling(const aios_sampling &a, const aios_sampling &b) {
 }
 
 void Seq::ensure_graph(const aios_sampling &sp) {
-    if (graph && same_sampling(sp, graph_sampling)) return;
+    if (graph && same_sampling(sp, graph_sampling) && graph_mask == mask_on) return;
     if (graph) { cudaGraphExecDestroy(graph); graph = nullptr; }
     cudaStream_t st = m->eng->stream;
     cudaGraph_t g = nullptr;
@@ -459,6 +460,7 @@ void Seq::ensure_graph(const aios_sampling &sp) {
     cudaGraphDestroy(g);
     CUDA_CHECK(e);
     graph_sampling = sp;
+    graph_mask = mask_on;
 }
 
 // One prompt chunk of T <= 32 tokens at positions pos0 .. pos0+T-1.  Same arithmetic as T token passes (the logits and
@@ -793,7 +795,7 @@ void Seq::build_pfd() {
 bool Seq::use_pfd(const aios_sampling &sp) const {
     // opt-in until it beats the per-op path (AIOS_ENGINE_USE_PFD); AIOS_ENGINE_NO_PFD always wins
     const int f = m->eng->flags;
-    return pfd_grid > 0 && !(sp.temperature > 0.f) && (f & AIOS_ENGINE_USE_PFD) && !(f & AIOS_ENGINE_NO_PFD);
+    return pfd_grid > 0 && !mask_on && !(sp.temperature > 0.f) && (f & AIOS_ENGINE_USE_PFD) && !(f & AIOS_ENGINE_NO_PFD);
 }
 
 // n greedy tokens after the current position; device state (pos, step) must already be set
@@ -853,6 +855,19 @@ int Seq::decode_static(int max_tokens, int32_t *out) {
     CUDA_CHECK(cudaGetLastError());
     n_past += steps;
     return steps;
+}
+
+// Logit mask for the sampler: bit i of byte i/8 set = token i may be sampled.  It stays in force (for greedy and
+// stochastic sampling alike) until replaced or cleared; JSON mode uploads the grammar's allowed set before every step.
+void Seq::set_mask(const uint8_t *bits, int n_bytes) {
+    if (!bits) { mask_on = false; return; }
+    const int need = (m->hp.n_vocab + 7) / 8;
+    if (n_bytes < need) throw std::invalid_argument("mask shorter than n_vocab bits");
+    m->eng->make_current();
+    if (!mask.p) mask = DevBuf((size_t)need);
+    CUDA_CHECK(cudaMemcpyAsync(mask.p, bits, (size_t)need, cudaMemcpyHostToDevice, m->eng->stream));
+    CUDA_CHECK(cudaStreamSynchronize(m->eng->stream));  // the caller's buffer is free again on return
+    mask_on = true;
 }
 
 void Seq::read_logits(float *out) {

@@ -115,9 +115,12 @@ struct Seq {
     // prompt chunks (prefill_chunk): activations of up to 32 tokens side by side, their quantised images, positions
     DevBuf cx, cqkv, catt, ch, cgu, cimg, cpos;
     DevBuf trace;
+    DevBuf mask;           // optional logit mask (n_vocab bits), see set_mask
+    bool mask_on = false;
     unsigned long long *trace_base = nullptr;  // non-null only inside trace_decode
     cudaGraphExec_t graph = nullptr;
     aios_sampling graph_sampling{};
+    bool graph_mask = false;
     int kernels_per_step = 0;
     // persistent fused decode (pfd.cu): phase table + global exchange buffers; pfd_grid == 0 -> not usable
     DevBuf pfd_phases, pfd_att_max, pfd_att_sum, pfd_att_acc, pfd_counters, pfd_timing;
@@ -138,6 +141,7 @@ struct Seq {
     void snapshot();
     void restore();
     void read_logits(float *out);
+    void set_mask(const uint8_t *bits, int n_bytes);  // null: sample from every token again
 
    private:
     void launch_token_pass(bool from_prompt, int prompt_idx, int pos_value, bool want_logits, cudaStream_t st, int *n_launch);

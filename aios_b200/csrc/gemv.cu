@@ -146,6 +146,7 @@ __device__ __forceinline__ void gemv_db_body(const GemvParams &p, int seg, uint8
     constexpr int PU = Regs::ITS * 32;
     unsigned long long *tr = (blockIdx.x == 0 && threadIdx.x == 0) ? p.trace : nullptr;
     trace_mark(tr, 0);
+    if (tr) tr[3] = 1ull;  // launch kind: GEMV
     const WPlanes &W = p.seg[seg];
     const WPlanes &W1 = p.seg[p.epi == EPI_SWIGLU ? 1 : seg];
     const int cta_local = (int)blockIdx.x - p.cta_begin[seg];

@@ -42,7 +42,7 @@ struct GemvParams {
     float eps;
     unsigned long long *argmax_key;  // if non-null (EPI_STORE, 1 segment): running packed (value,index) max
     // timeline of CTA 0 (null = off; gemv_db_kernel): [0] entry [1] dependency wait over [2] activations ready
-    // [4] CTA 0 done [7] last CTA done
+    // [3] launch kind (1 = GEMV, 2 = attention) [4] CTA 0 done [7] last CTA done
     unsigned long long *trace;
     RopeKv rope;
     // ready-made activation image in global memory (quant_rows_kernel, gemm_q.cu), in this launch's shared-memory
@@ -109,6 +109,9 @@ struct SampleParams {
     int32_t *cur_token;      // device: sampled token (input of the next step)
     int32_t *out_tokens;     // device array
     int32_t out_cap;
+    const uint8_t *mask;     // optional: bit i of byte i/8 set = token i may be sampled (JSON mode); null = all
+    int32_t *cand_out;       // optional (tests): the K candidate ids, best first
+    int32_t *counts_out;     // optional (tests): {K, n after top-p, n after min-p}
 };
 void launch_sample(const SampleParams &p, cudaStream_t st);
 

@@ -123,48 +123,58 @@ def recorded_traffic() -> float | None:
         return None
 
 
-def cpu_reference_tok_s(path: str, n_prompt: int, max_decode: int, budget_s: float = 15.0, threads: int = 0):
-    """Times the CPU restatement of the llama.cpp CPU path (oracle, AVX2 dot kernels) on host cores: greedy decode
-    tokens until `budget_s` seconds of CPU work are spent (at least 8, at most `max_decode` tokens)."""
+def host_threads() -> int:
+    """Threads the CPU arm may use: the cores this process is allowed on.  (torchrun injects OMP_NUM_THREADS=1 into its
+    ranks, which would silently time the CPU path on one core; the oracle's pool is sized explicitly instead.)"""
+    try:
+        return max(1, len(os.sched_getaffinity(0)))
+    except AttributeError:
+        return max(1, os.cpu_count() or 1)
+
+
+def oracle_window(path: str, arch: str, n_prompt: int, n_gen: int):
+    """CPU restatement of the llama.cpp CPU path (oracle, AVX2 integer dots, all host threads) on the bench's own
+    window: feeds the n_prompt-token prompt position by position, then decodes n_gen greedy tokens.  Returns
+    (tokens, forward passes per second, threads, seconds, forward passes)."""
     from oracle import oracle as orc
 
     orc.build()
-    m = orc.OracleModel(path, n_ctx=max(64, n_prompt + max_decode + 1), simd=True, threads=threads)
-    cores = orc.lib().oracle_num_threads()
-    prompt = gs.synthetic_prompt("mistral-7b", n_prompt, SEED)
-    m.eval(prompt)  # prefill (also pages the file in)
-    toks = np.array([1], np.int32)
+    threads = host_threads()
+    m = orc.OracleModel(path, n_ctx=n_prompt + n_gen + 8, simd=True, threads=threads)
+    prompt = gs.synthetic_prompt(arch, n_prompt, SEED)
     t0 = time.perf_counter()
-    pos, n = n_prompt, 0
-    while n < max_decode and (n < 8 or time.perf_counter() - t0 < budget_s):
-        logits = m.eval(toks, n_past=pos)
-        toks = np.array([int(np.argmax(logits))], np.int32)
-        pos += 1
-        n += 1
+    toks, _ = m.greedy(prompt, n_gen)
     dt = time.perf_counter() - t0
     m.close()
-    return n / dt, cores, dt, n
+    passes = n_prompt + n_gen - 1  # greedy() does not feed the last token it returns
+    return toks, passes / dt, orc.lib().oracle_num_threads(), dt, passes
 
 
 def run_reference(args, rank: int, world: int):
+    """The reference arm: the reference's CPU path for this workload.  llama.cpp itself is an un-vendored, un-pinned
+    dependency of the reference and is not on this box, so this times the oracle (CPU restatement, AVX2 dots) with all
+    the host threads it can use.  Same GGUF, same 384-token prompt (fed untimed, like the GPU arm's prefill); a step
+    is a bounded sample of the GPU arm's step: the first `--ref-tokens-per-step` greedy tokens of the 128-token
+    window, restarted at position 384 every step."""
     if rank != 0:
         return
     path = ensure_model(args.arch, args.ftype, True)
     from oracle import oracle as orc
 
     orc.build()
-    n_tok = args.ref_tokens_per_step
-    m = orc.OracleModel(path, n_ctx=64 + (args.steps + args.warmup) * n_tok + 8, simd=True)
+    threads = host_threads()
+    n_tok = min(args.ref_tokens_per_step, args.gen)
+    m = orc.OracleModel(path, n_ctx=args.prompt + args.gen + 8, simd=True, threads=threads)
     cores = orc.lib().oracle_num_threads()
-    prompt = gs.synthetic_prompt(args.arch, 8, SEED)
-    m.eval(prompt)
-    pos = len(prompt)
-    tok = np.array([1], np.int32)
+    prompt = gs.synthetic_prompt(args.arch, args.prompt, SEED)
+    logits0 = m.eval(prompt)  # untimed: positions 0..prompt-1 (the GPU arm's prefill is untimed too)
+    first = int(np.argmax(logits0))
 
     def step():
-        nonlocal pos, tok
-        for _ in range(n_tok):
-            lg = m.eval(tok, n_past=pos)
+        tok = np.array([first], np.int32)
+        pos = args.prompt
+        for _ in range(n_tok):  # decode step: feed the token at `pos`, arg-max the next one
+            lg = m.eval(tok, n_past=pos)  # rows >= prompt of the KV cache are simply overwritten each step
             tok = np.array([int(np.argmax(lg))], np.int32)
             pos += 1
 
@@ -175,20 +185,52 @@ def run_reference(args, rank: int, world: int):
         step()
     dt = time.perf_counter() - t0
     val = args.steps * n_tok / dt
-    sample = (f"{args.steps} steps x {n_tok} greedy decode tokens at context {len(prompt)}..{pos} on the same seeded "
-              f"{args.arch} {args.ftype} GGUF (bounded sample of the 128-token step)")
+    sample = (f"{args.steps} steps x the first {n_tok} of the {args.gen} greedy decode tokens at context {args.prompt}.."
+              f"{args.prompt + n_tok} (same GGUF, same {args.prompt}-token prompt fed untimed); CPU restatement with AVX2 "
+              f"integer dots on {cores} threads, not llama.cpp (un-vendored by the reference, unavailable on this box)")
     line = {
         "impl": "reference", "metric": METRIC, "value": val, "unit": "tok/s", "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": dt / args.steps * 1e3, "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": "int8 x q4/q6 integer dots, f32 accumulate", "data": "synthetic",
-        "config": {"workload": f"{args.arch} {args.ftype} batch-1 greedy decode (CPU restatement of the llama.cpp CPU path; "
-                               "real llama.cpp is not vendored by the reference and unavailable here)",
-                   "tokens_per_step": n_tok},
+        "vs_baseline": None, "dtype": "int8 x q4/q6 integer dots, f32/f64 accumulate", "data": "synthetic",
+        "config": {"workload": f"{args.arch} {args.ftype} batch-1 greedy decode, {args.prompt}-token prompt + "
+                               f"{args.gen} generated = {args.prompt + args.gen}-token context (BASELINE.json configs[1])",
+                   "tokens_per_step": n_tok, "window": f"positions {args.prompt}..{args.prompt + n_tok}", "seed": SEED},
         "cpu_baseline": {"value": val, "unit": "tok/s", "cores": cores, "kind": "port", "sample": sample},
         "e2e": {"value": val, "unit": "tok/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
     print(json.dumps(line), flush=True)
+
+
+def in_graph_breakdown(seq, n_runs: int = 4):
+    """Per-token time of each launch kind INSIDE the token pass, from the %globaltimer marks the kernels themselves take
+    (aios_seq_trace_decode: same launch order and programmatic-dependent-launch attributes as the captured graph).
+    A launch's share is completion-to-completion: from the moment the previous launch's last CTA finished to the moment
+    its own last CTA finished — hand-over, dependency wait, activation prologue and weight stream included — so the
+    shares of all launches add up to the token's span and never exceed it.
+    Returns dict(us_token, us_gemv, us_attn, us_other, n_gemv, n_attn)."""
+    acc = {"us_token": 0.0, "us_gemv": 0.0, "us_attn": 0.0, "us_other": 0.0}
+    n_gemv = n_attn = 0
+    for _ in range(n_runs):
+        seq.restore()
+        tr = seq.trace_decode().astype(np.int64)
+        done = np.maximum(tr[:, 7], tr[:, 4])
+        kind = tr[:, 3]
+        traced = tr[:, 0] > 0
+        idx = np.nonzero(traced)[0]
+        if idx.size < 2:
+            continue
+        prev = tr[idx[0], 0]  # the first traced launch's entry opens the token
+        n_gemv = int((kind[idx] == 1).sum())
+        n_attn = int((kind[idx] == 2).sum())
+        for i in idx:
+            d = max(0, int(done[i] - prev)) / 1e3
+            prev = max(prev, int(done[i]))
+            acc["us_gemv" if kind[i] == 1 else "us_attn" if kind[i] == 2 else "us_other"] += d
+        acc["us_token"] += (prev - tr[idx[0], 0]) / 1e3
+    out = {k: v / n_runs for k, v in acc.items()}
+    out.update(n_gemv=n_gemv, n_attn=n_attn)
+    return out
 
 
 def main():
@@ -202,7 +244,8 @@ def main():
     ap.add_argument("--prompt", type=int, default=384)
     ap.add_argument("--gen", type=int, default=128)
     ap.add_argument("--ref-tokens-per-step", type=int, default=16)
-    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the oracle run (parity gate + cpu_baseline)")
+    ap.add_argument("--parity-tokens", type=int, default=16)
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -244,6 +287,24 @@ def main():
     seq_e2e.snapshot()
     last_tok = np.ascontiguousarray(prompt[-1:], dtype=np.int32)
 
+    # parity gate, before anything is timed: the first tokens of this very run against the oracle on the same GGUF and
+    # prompt (rank 0; the same CPU run is the cpu_baseline sample).  A mismatch aborts the bench.
+    parity = None
+    cpu = None
+    if rank == 0 and not args.no_cpu_baseline:
+        n_chk = min(args.parity_tokens, args.gen)
+        want, cpu_rate, cores, cpu_dt, cpu_passes = oracle_window(path, args.arch, args.prompt, n_chk)
+        got = seq.decode(n_chk)
+        seq.restore()
+        if not np.array_equal(got, want):
+            raise SystemExit(f"bench.py: PARITY FAILURE — first {n_chk} greedy tokens differ from the oracle: {got} vs {want}")
+        parity = n_chk
+        cpu = {"value": cpu_rate, "unit": "tok/s", "cores": cores, "kind": "port",
+               "sample": f"{cpu_passes} single-token forward passes on the same GGUF: the {args.prompt} prompt positions and the "
+                         f"first {n_chk - 1} generated tokens, contexts 1..{args.prompt + n_chk - 1} ({cpu_dt:.1f} s of CPU work); "
+                         "CPU restatement with AVX2 integer dots, not llama.cpp (unavailable on this box)"}
+    barrier()
+
     for _ in range(max(args.warmup, 3)):
         seq.restore()
         seq.bench_decode(args.gen)
@@ -283,34 +344,33 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     dev_ms_max, e2e_ms_max, wall_ms_max = [float(v) for v in t.tolist()]
 
-    # roofline leg: per-launch CUDA events around every kernel of a few tokens
+    # roofline legs.  (1) in-graph: the kernels' own %globaltimer marks inside the token pass; (2) isolated: a CUDA-event
+    # pair around every launch of a few eagerly launched tokens (stand-alone rate, ~3 us of event overhead per launch).
+    ig = in_graph_breakdown(seq)
     seq.restore()
     prof = seq.profile_decode(16)
     n_gemv = int(prof.reserved[2])
     emb_row = gs.tensor_nbytes((1, info.n_embd), gs.Q4_K if args.ftype == "Q4_K_M" else gs.Q8_0)
-    norm_bytes = (2 * info.n_layer + 1) * info.n_embd * 4
     gemv_bytes_per_token = info.weight_bytes_per_token - emb_row  # matrices + the norm vectors their prologues read
     peak, peak_src = measured_peaks()
-    gemv_gbs = gemv_bytes_per_token * prof.n_tokens / (prof.ms_gemv * 1e-3) / 1e9
     n_past_mean = args.prompt + (args.gen - 1) / 2.0
     bytes_per_token = info.weight_bytes_per_token + info.kv_bytes_per_position * n_past_mean
     total_tokens = world * args.steps * args.gen
     value = total_tokens / (dev_ms_max * 1e-3)
     e2e_value = total_tokens / (e2e_ms_max * 1e-3)
+    us_token = dev_ms_max * 1e3 / (args.steps * args.gen)
+    gemv_gbs = gemv_bytes_per_token / (ig["us_gemv"] * 1e-6) / 1e9 if ig["us_gemv"] > 0 else 0.0
+    iso_gbs = gemv_bytes_per_token * prof.n_tokens / (prof.ms_gemv * 1e-3) / 1e9
 
     if rank == 0:
-        cpu = None
-        if world == 1 and not args.no_cpu_baseline:
-            v, cores, dt, n_cpu = cpu_reference_tok_s(path, 8, 512)
-            cpu = {"value": v, "unit": "tok/s", "cores": cores, "kind": "port",
-                   "sample": f"{n_cpu} greedy decode tokens after an 8-token prompt on the same GGUF ({dt:.1f} s of CPU work); "
-                             "CPU restatement with AVX2 integer dots, not llama.cpp (unavailable on this box)"}
+        # the dominant kernel's in-graph time must fit inside the token it is part of
+        fits = ig["us_gemv"] <= us_token * 1.05 and ig["us_token"] <= us_token * 1.25
         traffic = recorded_traffic()
         line = {
             "metric": METRIC, "value": value, "unit": "tok/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": dev_ms_max / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "int8 x q4/q6 integer dots, f32/f64 accumulate",
-            "data": "synthetic",
+            "data": "synthetic", "parity_checked": bool(parity), "parity_tokens": parity,
             "config": {"workload": f"{args.arch} {args.ftype} batch-1 greedy decode, {args.prompt}-token prompt + "
                                    f"{args.gen} generated = {n_ctx}-token context (BASELINE.json configs[1])",
                        "tokens_per_step": args.gen, "l2": "inputs larger than L2 (4.29 GB weights per token vs 126 MB)",
@@ -319,19 +379,28 @@ def main():
                        "wall_ms_per_step": wall_ms_max / args.steps},
             "roofline": {"bound": "hbm", "achieved": gemv_gbs, "peak": peak, "unit": "GB/s", "frac": gemv_gbs / peak,
                          "traffic": traffic, "peak_source": peak_src,
-                         "kernel": "gemv_db_kernel / gemv_db_mixed_kernel (fused norm + act-quant + dequant-GEMV + epilogue)", "launches_per_token": n_gemv // prof.n_tokens,
+                         "kernel": "gemv_db_kernel / gemv_db_mixed_kernel (fused norm + act-quant + dequant-GEMV + epilogue)",
+                         "method": "in-graph: algorithmic bytes of the GEMV launches of one token / their summed "
+                                   "completion-to-completion time from the kernels' own %globaltimer marks (hand-over, "
+                                   "dependency wait and activation prologue included)",
+                         "launches_per_token": ig["n_gemv"],
                          "algorithmic_bytes_per_token": gemv_bytes_per_token,
-                         "avg_launch_us": prof.ms_gemv * 1e3 / max(1, n_gemv),
-                         "whole_token_frac_of_peak": bytes_per_token * value / world / 1e9 / peak,
-                         "attention_ms_per_token": prof.reserved[0] / prof.n_tokens,
-                         "other_ms_per_token": prof.reserved[1] / prof.n_tokens},
+                         "avg_launch_us": ig["us_gemv"] / max(1, ig["n_gemv"]),
+                         "in_graph_us_per_token": {"gemv": ig["us_gemv"], "attention": ig["us_attn"], "other": ig["us_other"],
+                                                   "traced_token": ig["us_token"], "graph_token": us_token},
+                         "kernel_time_fits_in_token": bool(fits),
+                         "isolated": {"achieved": iso_gbs, "frac": iso_gbs / peak, "avg_launch_us": prof.ms_gemv * 1e3 / max(1, n_gemv),
+                                      "attention_ms_per_token": prof.reserved[0] / prof.n_tokens,
+                                      "other_ms_per_token": prof.reserved[1] / prof.n_tokens,
+                                      "method": "CUDA-event pair around every launch of 16 eagerly launched tokens"},
+                         "whole_token_frac_of_peak": bytes_per_token * value / world / 1e9 / peak},
             "e2e": {"value": e2e_value, "unit": "tok/s", "h2d_bytes_per_step": 4, "d2h_bytes_per_step": 4 * args.gen,
                     "api": "aios_seq_prefill(last prompt token, from host memory) + aios_seq_step per token "
                            "(one C-ABI call, one 4-byte D2H and one sync per token)"},
             "gpu_launches": launches,
             "clocks": clocks,
         }
-        if cpu:
+        if cpu and world == 1:
             line["cpu_baseline"] = cpu
         print(json.dumps(line), flush=True)
     seq.free()

@@ -199,6 +199,13 @@ int aios_seq_step(aios_seq *s, const aios_sampling *sp, int32_t *token_out);
  * Set-up: the first call on a device looks the array's device address up once (cudaGetSymbolAddress, with that
  * device current) and remembers it; make that first call before starting any stream capture. */
 int aios_seq_decode_static(aios_seq *s, int32_t max_tokens, int32_t *out_tokens, int32_t *n_out);
+/* Logit mask for this sequence's sampler (greedy or stochastic): bit i of byte i/8 of mask_bits set = token i may be
+ * sampled; n_bytes >= ceil(n_vocab / 8).  It applies to every later step until replaced, or cleared with
+ * mask_bits = NULL.  This is the device-side half of JSON mode: unary Infer always asks for response_format
+ * json_object (runtime/src/inference.rs:119-121), llama-server enforces it with a grammar that masks logits before its
+ * sampler chain; here the host advances the grammar and uploads the allowed set (n_vocab / 8 bytes) per step, and the
+ * on-device sampler applies it — the logits themselves never leave the GPU.  H2D: n_vocab / 8 bytes; D2H: 0. */
+int aios_seq_set_mask(aios_seq *s, const uint8_t *mask_bits, int32_t n_bytes);
 /* copy the kept logits (n_vocab floats) to the host */
 int aios_seq_logits(aios_seq *s, float *logits_out);
 /* remember / return to the current position and its logits (prompt caching, benchmark replays).
@@ -244,6 +251,12 @@ int aios_matvec(aios_engine *e, int32_t ggml_type, const void *w_blocks, int64_t
  * n_tok calls of aios_matvec, bit for bit.  Q4_K and Q8_0 weights (AIOS_E_UNSUPPORTED otherwise); host in, host out. */
 int aios_matmul(aios_engine *e, int32_t ggml_type, const void *w_blocks, int64_t n_rows, int64_t k, const float *x,
                 int32_t n_tok, const float *norm_w, float rms_eps, float *y);
+/* one run of the on-device sampler chain on host logits (parity hook for oracle_sample): mask_bits may be NULL;
+ * `counter` is the draw's counter (a sequence uses the position of the last token fed, n_past - 1).  Outputs: *token,
+ * cand[128] (candidate ids, best first; -1 beyond K), counts[3] = {K, n after top-p, n after min-p}; cand / counts may
+ * be NULL. */
+int aios_sample_logits(aios_engine *e, const float *logits, int32_t n_vocab, const uint8_t *mask_bits, const aios_sampling *sp,
+                       uint64_t counter, int32_t *token, int32_t *cand, int32_t *counts);
 /* logits of the last of n tokens fed at position n_past into a scratch sequence */
 int aios_forward_logits(aios_model *m, const int32_t *tokens, int32_t n, int32_t n_past, float *logits_out);
 /* read back one layer's KV rows [pos0, pos0+n) as fp16 bit patterns: k_out/v_out[n][n_head_kv*head_dim] */

@@ -787,6 +787,80 @@ int oracle_greedy(oracle_model *m, const int32_t *prompt, int n_prompt, int n_ge
     return 0;
 }
 
+/* ---------------------------------------------------------------- sampler chain
+ * llama-server's default chain, of which the reference sets only `temperature` and `max_tokens`
+ * (runtime/src/inference.rs:103-122): top-k -> top-p -> min-p -> temperature -> soft-max -> draw.
+ * llama.cpp's own draw (std::mt19937 + std::discrete_distribution) is neither specified nor stable across
+ * standard libraries; the draw here is an inverse-CDF walk over the surviving candidates with a splitmix64
+ * uniform keyed by (seed, counter).  Every float step is a single rounded f32 operation in a fixed order
+ * (this file is built with -ffp-contract=off), so a GPU can reproduce the candidate set, both cut-offs and
+ * the drawn token bit for bit.
+ *
+ *   candidates  = allowed tokens (mask bit set, or all when mask == NULL) sorted by (logit descending, index
+ *                 ascending); K = min(top_k > 0 ? top_k : 128, 128, #allowed)      [128 = candidate cap]
+ *   p_i         = expf(l_i - l_0), sum = p_0 + p_1 + ... (left to right)
+ *   top-p       : n = smallest i+1 with (p_0/sum + ... + p_i/sum) >= top_p          (top_p >= 1: off)
+ *   min-p       : n = first i in [1, n) with p_i < min_p * p_0, if any               (min_p <= 0: off)
+ *   temperature : w_i = expf((l_i - l_0) / temperature), i < n; sum2 left to right
+ *   draw        : u = uniform(seed, counter) * sum2; first i with u < w_0 + ... + w_i (else n - 1)
+ * Returns the token; cand[0..K) = sorted candidate ids, counts[3] = {K, n after top-p, n after min-p}.
+ * temperature <= 0 is greedy (arg-max over the allowed tokens, lowest index wins). */
+float oracle_uniform(uint64_t seed, uint64_t ctr) {
+    uint64_t z = seed + 0x9E3779B97F4A7C15ull * (ctr + 1);
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    z ^= z >> 31;
+    return (float)(z >> 40) * (1.0f / 16777216.0f);
+}
+
+#define ORACLE_SAMPLE_MAX_K 128
+int oracle_sample(const float *logits, int n_vocab, const uint8_t *mask, float temperature, int top_k, float top_p,
+                  float min_p, uint64_t seed, uint64_t counter, int32_t *cand, int32_t *counts) {
+    int K = top_k > 0 ? top_k : ORACLE_SAMPLE_MAX_K;
+    if (K > ORACLE_SAMPLE_MAX_K) K = ORACLE_SAMPLE_MAX_K;
+    if (!(temperature > 0.f)) K = 1;
+    int idx[ORACLE_SAMPLE_MAX_K];
+    float val[ORACLE_SAMPLE_MAX_K];
+    int n = 0;
+    /* insertion into a sorted list of at most K: (logit descending, index ascending) */
+    for (int i = 0; i < n_vocab; i++) {
+        if (mask && !((mask[i >> 3] >> (i & 7)) & 1)) continue;
+        const float v = logits[i];
+        if (n == K && !(v > val[n - 1])) continue; /* ties keep the earlier index */
+        int j = n < K ? n : K - 1;
+        while (j > 0 && v > val[j - 1]) { val[j] = val[j - 1]; idx[j] = idx[j - 1]; j--; }
+        val[j] = v; idx[j] = i;
+        if (n < K) n++;
+    }
+    if (n == 0) return -1;
+    K = n;
+    if (cand) for (int i = 0; i < K; i++) cand[i] = idx[i];
+    if (counts) counts[0] = counts[1] = counts[2] = K;
+    if (!(temperature > 0.f)) return idx[0];
+    float p[ORACLE_SAMPLE_MAX_K];
+    float sum = 0.f;
+    for (int i = 0; i < K; i++) { p[i] = oracle_expf(val[i] - val[0]); sum = sum + p[i]; }
+    n = K;
+    if (top_p < 1.f) {
+        float c = 0.f;
+        for (int i = 0; i < K; i++) { c = c + p[i] / sum; if (c >= top_p) { n = i + 1; break; } }
+    }
+    if (counts) counts[1] = n;
+    if (min_p > 0.f) {
+        int n2 = 1;
+        while (n2 < n && p[n2] >= min_p * p[0]) n2++;
+        n = n2;
+    }
+    if (counts) counts[2] = n;
+    float sum2 = 0.f;
+    for (int i = 0; i < n; i++) { p[i] = oracle_expf((val[i] - val[0]) / temperature); sum2 = sum2 + p[i]; }
+    const float u = oracle_uniform(seed, counter) * sum2;
+    float c = 0.f;
+    int pick = n - 1;
+    for (int i = 0; i < n; i++) { c = c + p[i]; if (u < c) { pick = i; break; } }
+    return idx[pick];
+}
+
 const uint16_t *oracle_k_cache(const oracle_model *m) { return m->k_cache; }
 const uint16_t *oracle_v_cache(const oracle_model *m) { return m->v_cache; }
 int oracle_num_threads(void) {

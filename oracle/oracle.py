@@ -57,6 +57,11 @@ def lib():
         L.oracle_greedy.argtypes = [C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_void_p, C.c_void_p]
         L.oracle_rope_table.argtypes = [C.c_int, C.c_int, C.c_float, C.c_void_p, C.c_void_p]
         L.oracle_set_simd.argtypes = [C.c_int]
+        L.oracle_sample.restype = C.c_int
+        L.oracle_sample.argtypes = [C.c_void_p, C.c_int, C.c_void_p, C.c_float, C.c_int, C.c_float, C.c_float,
+                                    C.c_uint64, C.c_uint64, C.c_void_p, C.c_void_p]
+        L.oracle_uniform.restype = C.c_float
+        L.oracle_uniform.argtypes = [C.c_uint64, C.c_uint64]
         L.oracle_set_threads.argtypes = [C.c_int]
         L.oracle_num_threads.restype = C.c_int
         L.oracle_f2h.restype = C.c_uint16
@@ -105,6 +110,19 @@ def matvec(qtype: int, w_blocks: np.ndarray, n_rows: int, k: int, x: np.ndarray,
     lib().oracle_set_simd(0)
     assert rc == 0
     return y
+
+
+def sample(logits: np.ndarray, temperature: float, top_k: int = 40, top_p: float = 0.95, min_p: float = 0.05,
+           seed: int = 0, counter: int = 0, mask: np.ndarray | None = None):
+    """The sampler chain (oracle_sample): returns (token, candidate ids sorted, (K, n after top-p, n after min-p)).
+    `mask` = packed bits, bit i of byte i//8 set when token i is allowed."""
+    lg = np.ascontiguousarray(logits, np.float32)
+    cand = np.full(128, -1, np.int32)
+    counts = np.zeros(3, np.int32)
+    mk = None if mask is None else np.ascontiguousarray(mask, np.uint8)
+    tok = lib().oracle_sample(_ptr(lg), lg.size, None if mk is None else _ptr(mk), float(temperature), int(top_k),
+                              float(top_p), float(min_p), int(seed), int(counter), _ptr(cand), _ptr(counts))
+    return int(tok), cand[:counts[0]].copy(), tuple(int(c) for c in counts)
 
 
 def rope_table(pos: int, n_rot: int, freq_base: float):

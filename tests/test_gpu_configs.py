@@ -6,9 +6,11 @@ engine must produce the same 128 tokens and bit-identical logits at the end.  Th
 whose matrices take the default double-buffered GEMV kernel for K = 2048 and the single-image fallback for
 K = 5632 (ffn_down) in the same pass.
 
-configs[1] (Mistral-7B, the bench workload) is covered at full size by size-independent properties: the decode is
-deterministic, a chunked decode equals a one-shot decode, the sequence snapshot/restore replays identically, and the
-queued-request path returns the same tokens as the synchronous one.
+configs[1] (Mistral-7B Q4_K_M, the bench workload) is compared with the oracle directly — a 40-token prompt, 16
+greedy tokens and the final logits, bit for bit — and covered at full size by size-independent properties: the decode
+is deterministic, a chunked decode equals a one-shot decode, the sequence snapshot/restore replays identically, and
+the queued-request path returns the same tokens as the synchronous one.  (bench.py repeats the oracle comparison on its
+own 384-token prompt before it times anything.)
 """
 import numpy as np
 import pytest
@@ -35,6 +37,32 @@ def test_config0_tinyllama_128_prompt_128_greedy(engine, oracle, tmp_models):
             # decode feeds every token it samples: the kept logits are those after all 256 tokens — bit for bit
             assert seq.n_past == 256
             assert np.array_equal(seq.logits().view(np.uint32), ref_logits.view(np.uint32))
+        finally:
+            seq.free()
+    finally:
+        m.unload()
+
+
+def test_config1_mistral7b_matches_oracle(engine, oracle):
+    """The benchmarked model against the oracle at Mistral-7B size: every matrix shape of the headline number (K = 4096
+    and 14336, Q4_K and Q6_K, the mixed q/k/v launch, 32 layers of GQA-4 attention with head_dim 128)."""
+    import bench
+    path = bench.ensure_model("mistral-7b", "Q4_K_M", True)
+    prompt = gs.synthetic_prompt("mistral-7b", 40, bench.SEED)
+    om = oracle.OracleModel(path, n_ctx=64, simd=True, threads=bench.host_threads())
+    ref, margins = om.greedy(prompt, 16)
+    ref_logits = om.eval(np.concatenate([prompt, ref]).astype(np.int32))  # after all 56 tokens were fed
+    om.close()
+    m = engine.load_model("m7o", path, n_ctx=64)
+    try:
+        seq = m.new_seq()
+        try:
+            seq.prefill(prompt)
+            got = seq.decode(16)
+            print(f"min top-1/top-2 margin over 16 tokens: {margins.min():.3e}")
+            assert np.array_equal(got, ref)
+            assert seq.n_past == 56
+            assert np.array_equal(seq.logits().view(np.uint32), ref_logits.view(np.uint32))  # bit for bit
         finally:
             seq.free()
     finally:
