@@ -382,100 +382,121 @@ static float vec_dot_f32(int64_t n, const float *x, const float *y) {
 }
 
 /* ---------------------------------------------------------------- AVX2 dot kernels (timed CPU baseline)
- * Same integer arithmetic as the generic kernels above; only the float summation order
- * differs (as it does between ggml's own generic/AVX2 kernels).  Validated against the
- * generic versions in tests/.  Selected with oracle_set_simd(1). */
+ * The integer sub-block dots (exact in any order) are vectorised; everything that rounds — the one f32 term per
+ * 64-weight unit (32-weight block for Q8_0) and the double sum of the terms — is the generic kernels' code, operation
+ * by operation.  The results are therefore BIT-IDENTICAL to the generic kernels (tests/test_cpu.py checks this on
+ * every type), which is what lets the fast path serve as the parity oracle at Mistral-7B size.
+ * (Round 1's AVX2 kernels accumulated per-block f32 partial sums like ggml's own AVX2 path; on a 32-layer random-init
+ * model that last-bit difference grows to ~0.4 of the logit std, so they could not pin anything.)
+ * Selected with oracle_set_simd(1). */
 static int g_simd = 0;
 void oracle_set_simd(int on) { g_simd = on; }
 #if defined(__AVX2__)
 #include <immintrin.h>
-static inline float hsum8(__m256 v) {
-    __m128 lo = _mm256_castps256_ps128(v), hi = _mm256_extractf128_ps(v, 1);
-    lo = _mm_add_ps(lo, hi);
-    lo = _mm_add_ps(lo, _mm_movehl_ps(lo, lo));
-    lo = _mm_add_ss(lo, _mm_movehdup_ps(lo));
-    return _mm_cvtss_f32(lo);
-}
 static inline int hsum8_i32(__m256i v) {
     __m128i s = _mm_add_epi32(_mm256_castsi256_si128(v), _mm256_extracti128_si256(v, 1));
     s = _mm_add_epi32(s, _mm_shuffle_epi32(s, 0x4e));
     s = _mm_add_epi32(s, _mm_shuffle_epi32(s, 0xb1));
     return _mm_cvtsi128_si32(s);
 }
-/* u8 x i8 -> i32 lanes (8 lanes, each the sum of 4 products) */
+/* u8 x i8 -> i32 lanes (8 lanes, each the sum of 4 products; |pair sums| <= 2*128*127 < 2^15: no saturation) */
 static inline __m256i dot_u8_i8(__m256i u, __m256i s) {
     const __m256i p16 = _mm256_maddubs_epi16(u, s);
     return _mm256_madd_epi16(p16, _mm256_set1_epi16(1));
 }
+/* horizontal sums of eight 8-lane vectors at once: returns lanes {sum(v0), ..., sum(v7)} */
+static inline __m256i hsum8x8(__m256i v0, __m256i v1, __m256i v2, __m256i v3, __m256i v4, __m256i v5, __m256i v6, __m256i v7) {
+    const __m256i g0 = _mm256_hadd_epi32(_mm256_hadd_epi32(v0, v1), _mm256_hadd_epi32(v2, v3)); /* [s0..s3 lo | s0..s3 hi] */
+    const __m256i g1 = _mm256_hadd_epi32(_mm256_hadd_epi32(v4, v5), _mm256_hadd_epi32(v6, v7));
+    const __m128i a = _mm_add_epi32(_mm256_castsi256_si128(g0), _mm256_extracti128_si256(g0, 1));
+    const __m128i b = _mm_add_epi32(_mm256_castsi256_si128(g1), _mm256_extracti128_si256(g1, 1));
+    return _mm256_set_m128i(b, a);
+}
 static float vec_dot_q4_K_q8_K_avx2(int64_t n, const block_q4_K *x, const block_q8_K *y) {
     const int64_t nb = n / QK_K;
     const __m256i m4 = _mm256_set1_epi8(0xF);
-    float acc = 0, accm = 0;
+    double acc = 0.0;
     for (int64_t i = 0; i < nb; i++) {
-        uint8_t sc[8], mn[8];
-        for (int j = 0; j < 8; j++) get_scale_min_k4(j, x[i].scales, &sc[j], &mn[j]);
-        int summ = 0;
-        for (int j = 0; j < 8; j++) summ += mn[j] * (y[i].bsums[2 * j] + y[i].bsums[2 * j + 1]);
-        __m256i sumi = _mm256_setzero_si256();
+        const float d = h2f(x[i].d), dmin = h2f(x[i].dmin), d8 = y[i].d;
+        const float fd = d * d8, fm = dmin * d8;
+        __m256i v[8];
         for (int p = 0; p < 4; p++) {
             const __m256i q4 = _mm256_loadu_si256((const __m256i *)(x[i].qs + 32 * p));
-            const __m256i lo = _mm256_and_si256(q4, m4);
-            const __m256i hi = _mm256_and_si256(_mm256_srli_epi16(q4, 4), m4);
             const __m256i a0 = _mm256_loadu_si256((const __m256i *)(y[i].qs + 64 * p));
             const __m256i a1 = _mm256_loadu_si256((const __m256i *)(y[i].qs + 64 * p + 32));
-            sumi = _mm256_add_epi32(sumi, _mm256_mullo_epi32(dot_u8_i8(lo, a0), _mm256_set1_epi32(sc[2 * p])));
-            sumi = _mm256_add_epi32(sumi, _mm256_mullo_epi32(dot_u8_i8(hi, a1), _mm256_set1_epi32(sc[2 * p + 1])));
+            v[2 * p] = dot_u8_i8(_mm256_and_si256(q4, m4), a0);
+            v[2 * p + 1] = dot_u8_i8(_mm256_and_si256(_mm256_srli_epi16(q4, 4), m4), a1);
         }
-        acc += (h2f(x[i].d) * y[i].d) * (float)hsum8_i32(sumi);
-        accm += (h2f(x[i].dmin) * y[i].d) * (float)summ;
+        int32_t dots[8]; /* dots[2p] = low-nibble dot of unit p, dots[2p+1] = high-nibble dot */
+        _mm256_storeu_si256((__m256i *)dots, hsum8x8(v[0], v[1], v[2], v[3], v[4], v[5], v[6], v[7]));
+        for (int p = 0; p < 4; p++) {
+            uint8_t sc_lo, m_lo, sc_hi, m_hi;
+            get_scale_min_k4(2 * p, x[i].scales, &sc_lo, &m_lo);
+            get_scale_min_k4(2 * p + 1, x[i].scales, &sc_hi, &m_hi);
+            const int bs_lo = y[i].bsums[4 * p] + y[i].bsums[4 * p + 1];
+            const int bs_hi = y[i].bsums[4 * p + 2] + y[i].bsums[4 * p + 3];
+            const int isum = sc_lo * dots[2 * p] + sc_hi * dots[2 * p + 1];
+            const int msum = m_lo * bs_lo + m_hi * bs_hi;
+            const float term = fmaf(fd, (float)isum, -(fm * (float)msum));
+            acc += (double)term;
+        }
     }
-    return acc - accm;
+    return (float)acc;
 }
 static float vec_dot_q6_K_q8_K_avx2(int64_t n, const block_q6_K *x, const block_q8_K *y) {
     const int64_t nb = n / QK_K;
     const __m256i m4 = _mm256_set1_epi8(0xF), m2 = _mm256_set1_epi8(0x30);
-    float acc = 0;
+    double acc = 0.0;
     for (int64_t i = 0; i < nb; i++) {
-        int32_t tot = 0;
+        const float fd = h2f(x[i].d) * y[i].d;
         for (int h = 0; h < 2; h++) {
             const __m256i qla = _mm256_loadu_si256((const __m256i *)(x[i].ql + 64 * h));
             const __m256i qlb = _mm256_loadu_si256((const __m256i *)(x[i].ql + 64 * h + 32));
             const __m256i qh = _mm256_loadu_si256((const __m256i *)(x[i].qh + 32 * h));
-            __m256i q[4];
+            __m256i q[4], v[4];
             q[0] = _mm256_or_si256(_mm256_and_si256(qla, m4), _mm256_and_si256(_mm256_slli_epi16(qh, 4), m2));
             q[1] = _mm256_or_si256(_mm256_and_si256(qlb, m4), _mm256_and_si256(_mm256_slli_epi16(qh, 2), m2));
             q[2] = _mm256_or_si256(_mm256_and_si256(_mm256_srli_epi16(qla, 4), m4), _mm256_and_si256(qh, m2));
             q[3] = _mm256_or_si256(_mm256_and_si256(_mm256_srli_epi16(qlb, 4), m4), _mm256_and_si256(_mm256_srli_epi16(qh, 2), m2));
+            for (int g = 0; g < 4; g++)  /* 8 lanes: lanes 0-3 = first 16 weights of the 32-group, 4-7 = second 16 */
+                v[g] = dot_u8_i8(q[g], _mm256_loadu_si256((const __m256i *)(y[i].qs + 128 * h + 32 * g)));
+            /* [d0(g=0..3) | d1(g=0..3)]: d0 = dot of the first 16 (t = 0), d1 = of the second 16 (t = 1) */
+            int32_t dd[8];
+            _mm256_storeu_si256((__m256i *)dd, _mm256_hadd_epi32(_mm256_hadd_epi32(v[0], v[1]), _mm256_hadd_epi32(v[2], v[3])));
+            int isum0 = 0, isum1 = 0; /* units (h, t = 0) and (h, t = 1) */
             for (int g = 0; g < 4; g++) {
-                const __m256i a = _mm256_loadu_si256((const __m256i *)(y[i].qs + 128 * h + 32 * g));
-                const __m256i d32 = dot_u8_i8(q[g], a); /* 8 lanes: lanes 0-3 = first 16, 4-7 = second 16 */
-                const __m128i l = _mm256_castsi256_si128(d32), u = _mm256_extracti128_si256(d32, 1);
-                __m128i sl = _mm_add_epi32(l, _mm_shuffle_epi32(l, 0x4e));
-                sl = _mm_add_epi32(sl, _mm_shuffle_epi32(sl, 0xb1));
-                __m128i su = _mm_add_epi32(u, _mm_shuffle_epi32(u, 0x4e));
-                su = _mm_add_epi32(su, _mm_shuffle_epi32(su, 0xb1));
                 const int is = 8 * h + 2 * g;
-                const int d0 = _mm_cvtsi128_si32(sl) - 32 * y[i].bsums[is];
-                const int d1 = _mm_cvtsi128_si32(su) - 32 * y[i].bsums[is + 1];
-                tot += x[i].scales[is] * d0 + x[i].scales[is + 1] * d1;
+                isum0 += x[i].scales[is] * (dd[g] - 32 * y[i].bsums[is]);
+                isum1 += x[i].scales[is + 1] * (dd[4 + g] - 32 * y[i].bsums[is + 1]);
             }
+            acc += (double)(fd * (float)isum0);
+            acc += (double)(fd * (float)isum1);
         }
-        acc += (h2f(x[i].d) * y[i].d) * (float)tot;
     }
-    return acc;
+    return (float)acc;
 }
 static float vec_dot_q8_0_q8_0_avx2(int64_t n, const block_q8_0 *x, const block_q8_0 *y) {
     const int64_t nb = n / QK8_0;
-    __m256 acc = _mm256_setzero_ps();
-    for (int64_t ib = 0; ib < nb; ib++) {
+    double acc = 0.0;
+    int64_t ib = 0;
+    for (; ib + 8 <= nb; ib += 8) {
+        __m256i v[8];
+        for (int j = 0; j < 8; j++) {
+            const __m256i qx = _mm256_loadu_si256((const __m256i *)x[ib + j].qs);
+            const __m256i qy = _mm256_loadu_si256((const __m256i *)y[ib + j].qs);
+            v[j] = dot_u8_i8(_mm256_sign_epi8(qx, qx), _mm256_sign_epi8(qy, qx));
+        }
+        int32_t sums[8];
+        _mm256_storeu_si256((__m256i *)sums, hsum8x8(v[0], v[1], v[2], v[3], v[4], v[5], v[6], v[7]));
+        for (int j = 0; j < 8; j++) acc += (double)((float)sums[j] * (h2f(x[ib + j].d) * h2f(y[ib + j].d)));
+    }
+    for (; ib < nb; ib++) {
         const __m256i qx = _mm256_loadu_si256((const __m256i *)x[ib].qs);
         const __m256i qy = _mm256_loadu_si256((const __m256i *)y[ib].qs);
-        const __m256i ax = _mm256_sign_epi8(qx, qx);
-        const __m256i sy = _mm256_sign_epi8(qy, qx);
-        const __m256 p = _mm256_cvtepi32_ps(dot_u8_i8(ax, sy));
-        acc = _mm256_add_ps(acc, _mm256_mul_ps(p, _mm256_set1_ps(h2f(x[ib].d) * h2f(y[ib].d))));
+        const int sumi = hsum8_i32(dot_u8_i8(_mm256_sign_epi8(qx, qx), _mm256_sign_epi8(qy, qx)));
+        acc += (double)((float)sumi * (h2f(x[ib].d) * h2f(y[ib].d)));
     }
-    return hsum8(acc);
+    return (float)acc;
 }
 #define HAVE_AVX2_DOTS 1
 #else
