@@ -60,6 +60,21 @@ __device__ __forceinline__ uint4 ldg_stream(const void *p) {
                  : "l"(p));
     return r;
 }
+// L2 eviction policy for streamed weights: every weight byte is used once per token, so it is marked evict-first and
+// does not push the activations, the KV rows and the next launch's first weights out of L2.  0 = no hint.
+__device__ __forceinline__ uint64_t l2_policy(bool evict_first) {
+    uint64_t pol = 0;
+    if (evict_first) asm volatile("createpolicy.fractional.L2::evict_first.b64 %0, 1.0;" : "=l"(pol));
+    return pol;
+}
+__device__ __forceinline__ uint4 ldg_stream(const void *p, uint64_t pol) {
+    if (pol == 0) return ldg_stream(p);
+    uint4 r;
+    asm volatile("ld.global.nc.L1::no_allocate.L2::cache_hint.v4.u32 {%0,%1,%2,%3}, [%4], %5;"
+                 : "=r"(r.x), "=r"(r.y), "=r"(r.z), "=r"(r.w)
+                 : "l"(p), "l"(pol));
+    return r;
+}
 __device__ __forceinline__ uint32_t ldg_stream_u32(const void *p) {
     uint32_t r;
     asm volatile("ld.global.nc.L1::no_allocate.u32 %0, [%1];" : "=r"(r) : "l"(p));

@@ -49,6 +49,7 @@ Engine::Engine(const aios_engine_opts &o) : device(o.device), max_batch(o.max_ba
     }
     n_sms = prop.multiProcessorCount;
     CUDA_CHECK(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
+    if (const char *e = getenv("AIOS_EVICT_FIRST")) evict_first = atoi(e) != 0;
     // function attributes are per-device settings: every engine sets them for its own device
     gemv_init();
     attn_split_init();
@@ -295,6 +296,18 @@ void Seq::reset() {
     CUDA_CHECK(cudaMemcpy(state.p, &s, sizeof(s), cudaMemcpyHostToDevice));
 }
 
+// ---- the token pass as a list of launches
+namespace {
+struct PassLaunch {
+    int kind;  // 0 GEMV, 1 attention
+    GemvParams g{};
+    AttnParams a{};
+    int grid = 0;
+    bool pdl = false;
+};
+
+}  // namespace
+
 void Seq::launch_token_pass(bool from_prompt, int prompt_idx, int pos_value, bool want_logits, cudaStream_t st, int *n_launch) {
     const HParams &hp = m->hp;
     SeqState *sd = state.as<SeqState>();
@@ -306,11 +319,19 @@ void Seq::launch_token_pass(bool from_prompt, int prompt_idx, int pos_value, boo
                      from_prompt ? &sd->pos : nullptr, pos_value, from_prompt ? &sd->cur_token : nullptr, st));
     launches++;
     const int QD = hp.n_head * hp.head_dim, KVD = hp.n_head_kv * hp.head_dim;
-    auto trace_slot = [&]() { return trace_base && launches < 4096 ? trace_base + (size_t)launches * 8 : nullptr; };
     const int amode = (m->eng->flags & AIOS_ENGINE_ATTN_CLUSTER) ? 2 : 0;
     // with the split attention kernel, RoPE + f16 rounding + KV append move into the q/k/v GEMV's epilogue
     // (EPI_QKV_ROPE): the attention kernel then starts on final data, with no dependent table loads of its own
     const bool rope_in_gemv = amode == 0 && attn_split_usable(hp.n_ctx, hp.head_dim) && !(m->eng->flags & AIOS_ENGINE_NO_ROPE_EPILOGUE);
+    std::vector<PassLaunch> ls;
+    ls.reserve((size_t)hp.n_layer * 6 + 2);
+    auto add_gemv = [&](const GemvParams &p, bool use_pdl) {
+        PassLaunch L;
+        L.kind = 0; L.g = p; L.pdl = use_pdl;
+        L.g.evict_first = m->eng->evict_first ? 1 : 0;
+        L.grid = gemv_plan_grid(L.g, n_sms);
+        ls.push_back(L);
+    };
     for (int il = 0; il < hp.n_layer; il++) {
         const Layer &L = m->layers[il];
         bool kv_ready = false;
@@ -331,21 +352,19 @@ void Seq::launch_token_pass(bool from_prompt, int prompt_idx, int pos_value, boo
                 p.rope.n_rot = hp.n_rot; p.rope.hd = hp.head_dim; p.rope.kvd = KVD;
                 kv_ready = true;
             }
-            p.trace = trace_slot();
-            TIMED(0, launch_gemv(p, gemv_plan_grid(p, n_sms), st, pdl));
-            launches++;
+            add_gemv(p, pdl);
             if (!same) {
                 GemvParams v{};
                 v.n_seg = 1; v.epi = EPI_STORE; v.k = hp.n_embd;
                 v.seg[0] = L.wv.w; v.out[0] = qkv.as<float>() + QD + KVD;
                 v.x = x.as<float>(); v.norm_w = L.attn_norm.as<float>(); v.eps = hp.rms_eps;
-                v.trace = trace_slot();
-                TIMED(0, launch_gemv(v, gemv_plan_grid(v, n_sms), st, pdl));
-                launches++;
+                add_gemv(v, pdl);
             }
         }
         {   // RoPE + KV write + flash-decode
-            AttnParams a{};
+            PassLaunch A;
+            A.kind = 1; A.pdl = pdl;
+            AttnParams &a = A.a;
             a.qkv = qkv.as<float>(); a.out = att.as<float>();
             a.k_cache = m->k_cache(slot, il); a.v_cache = m->v_cache(slot, il);
             a.rope_cos = m->rope_cos.as<float>(); a.rope_sin = m->rope_sin.as<float>();
@@ -354,47 +373,49 @@ void Seq::launch_token_pass(bool from_prompt, int prompt_idx, int pos_value, boo
             a.n_head = hp.n_head; a.n_kv = hp.n_head_kv; a.hd = hp.head_dim; a.n_rot = hp.n_rot;
             a.n_split = m->attn_splits; a.n_ctx = hp.n_ctx;
             a.scale = 1.0f / sqrtf((float)hp.head_dim);
-            a.trace = trace_slot();
             a.kv_ready = kv_ready ? 1 : 0;
-            TIMED(1, launch_attn_decode(a, st, pdl, amode));
-            launches++;
+            ls.push_back(A);
         }
         {   // attention output projection + residual add
             GemvParams p{};
             p.n_seg = 1; p.epi = EPI_ADD; p.k = QD;
             p.seg[0] = L.wo.w; p.out[0] = x.as<float>(); p.x = att.as<float>();
-            p.trace = trace_slot();
-            TIMED(0, launch_gemv(p, gemv_plan_grid(p, n_sms), st, pdl));
-            launches++;
+            add_gemv(p, pdl);
         }
         {   // RMSNorm + gate/up + SwiGLU
             GemvParams p{};
             p.n_seg = 2; p.epi = EPI_SWIGLU; p.k = hp.n_embd;
             p.seg[0] = L.w_gate.w; p.seg[1] = L.w_up.w; p.out[0] = h.as<float>();
             p.x = x.as<float>(); p.norm_w = L.ffn_norm.as<float>(); p.eps = hp.rms_eps;
-            p.trace = trace_slot();
-            TIMED(0, launch_gemv(p, gemv_plan_grid(p, n_sms), st, pdl));
-            launches++;
+            add_gemv(p, pdl);
         }
         {   // down projection + residual add
             GemvParams p{};
             p.n_seg = 1; p.epi = EPI_ADD; p.k = hp.n_ff;
             p.seg[0] = L.w_down.w; p.out[0] = x.as<float>(); p.x = h.as<float>();
-            p.trace = trace_slot();
-            TIMED(0, launch_gemv(p, gemv_plan_grid(p, n_sms), st, pdl));
-            launches++;
+            add_gemv(p, pdl);
         }
     }
     if (want_logits) {
         // the lm_head epilogue keeps the packed (value, index) arg-max of the logits it writes
-        CUDA_CHECK(cudaMemsetAsync(&sd->argmax_key, 0, sizeof(unsigned long long), st));
         GemvParams p{};
         p.n_seg = 1; p.epi = EPI_STORE; p.k = hp.n_embd;
         p.seg[0] = m->output.w; p.out[0] = logits.as<float>();
         p.x = x.as<float>(); p.norm_w = m->output_norm.as<float>(); p.eps = hp.rms_eps;
         p.argmax_key = &sd->argmax_key;
-        p.trace = trace_slot();
-        TIMED(0, launch_gemv(p, gemv_plan_grid(p, n_sms), st, false));
+        add_gemv(p, false);
+    }
+    for (size_t i = 0; i < ls.size(); i++) {
+        PassLaunch &L = ls[i];
+        unsigned long long *tr = trace_base && launches < 4096 ? trace_base + (size_t)launches * 8 : nullptr;
+        if (L.kind == 0) {
+            if (L.g.argmax_key) CUDA_CHECK(cudaMemsetAsync(&sd->argmax_key, 0, sizeof(unsigned long long), st));
+            L.g.trace = tr;
+            TIMED(0, launch_gemv(L.g, L.grid, st, L.pdl));
+        } else {
+            L.a.trace = tr;
+            TIMED(1, launch_attn_decode(L.a, st, L.pdl, amode));
+        }
         launches++;
     }
     if (n_launch) *n_launch += launches;

@@ -38,6 +38,9 @@ struct Engine {
     int n_sms = 148;
     int max_batch = 1;
     int flags = 0;
+    // streamed weights carry the L2 evict-first policy (bytes used once should not push out activations, KV rows or
+    // the next launch's first weights); AIOS_EVICT_FIRST=0/1 overrides for A/B runs
+    bool evict_first = true;
     cudaStream_t stream = nullptr;
     std::mutex mu;  // serialises use of the stream by API calls
     explicit Engine(const aios_engine_opts &o);

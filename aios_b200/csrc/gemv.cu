@@ -65,11 +65,12 @@ __global__ void __launch_bounds__(GEMV_THREADS, 1) gemv_kernel(const GemvParams 
     // so that HBM is busy during the dependency wait and the activation prologue.
     PassRegs<TYPE> g;
     RowPtrs rp[GEMV_R];
+    const uint64_t pol = l2_policy(p.evict_first != 0);
     const bool have_work = row_first < N;
     if (have_work) {
         ptrs(row_first, rp);
-        if (full) load_pass<TYPE, true>(g, rp, 0, nu);
-        else load_pass<TYPE, false>(g, rp, 0, nu);
+        if (full) load_pass<TYPE, true>(g, rp, 0, nu, pol);
+        else load_pass<TYPE, false>(g, rp, 0, nu, pol);
     }
     // programmatic dependent launch: everything above overlapped the previous kernel's tail
     asm volatile("griddepcontrol.wait;" ::: "memory");
@@ -92,8 +93,8 @@ __global__ void __launch_bounds__(GEMV_THREADS, 1) gemv_kernel(const GemvParams 
         if (row0 != row_first) ptrs(row0, rp);
         for (int u0 = 0; u0 < nu; u0 += PASS_UNITS) {
             if (row0 != row_first || u0 != 0) {
-                if (full) load_pass<TYPE, true>(g, rp, u0, nu);
-                else load_pass<TYPE, false>(g, rp, u0, nu);
+                if (full) load_pass<TYPE, true>(g, rp, u0, nu, pol);
+                else load_pass<TYPE, false>(g, rp, u0, nu, pol);
             }
             if (full) compute_pass<TYPE, true>(g, u0, nu, p.k, s, acc);
             else compute_pass<TYPE, false>(g, u0, nu, p.k, s, acc);
@@ -173,9 +174,10 @@ __device__ __forceinline__ void gemv_db_body(const GemvParams &p, int seg, uint8
     int lrow = row_first, lu = 0;
     RowPtrs lrp[GEMV_R];
     if (lrow < N) ptrs(lrow, lrp);
+    const uint64_t pol = l2_policy(p.evict_first != 0);
     auto load_next = [&](Regs &g) {
         if (lrow < N) {
-            load_pass<TYPE, true>(g, lrp, lu, nu);
+            load_pass<TYPE, true>(g, lrp, lu, nu, pol);
             lu += PU;
             if (lu >= nu) {
                 lu = 0;

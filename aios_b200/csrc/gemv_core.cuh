@@ -324,7 +324,7 @@ __device__ __forceinline__ int dp4a_us(uint32_t a, uint32_t b, int c) {
 
 // FULL: the pass is known to be entirely in range (no per-lane predicates)
 template <int TYPE, bool FULL, typename Regs>
-__device__ __forceinline__ void load_pass(Regs &g, const RowPtrs (&rp)[GEMV_R], int u0, int nu) {
+__device__ __forceinline__ void load_pass(Regs &g, const RowPtrs (&rp)[GEMV_R], int u0, int nu, uint64_t pol) {
     const int lane = threadIdx.x & 31;
     constexpr int ITS = Regs::ITS;
 #pragma unroll
@@ -333,16 +333,16 @@ __device__ __forceinline__ void load_pass(Regs &g, const RowPtrs (&rp)[GEMV_R], 
         if (FULL || u < nu) {
 #pragma unroll
             for (int r = 0; r < GEMV_R; r++) {
-                g.a[r][it] = ldg_stream(rp[r].p[0] + (size_t)u * 16);
-                g.b[r][it] = ldg_stream(rp[r].p[1] + (size_t)u * 16);
+                g.a[r][it] = ldg_stream(rp[r].p[0] + (size_t)u * 16, pol);
+                g.b[r][it] = ldg_stream(rp[r].p[1] + (size_t)u * 16, pol);
                 if (TYPE == T_Q4_K || TYPE == T_Q5_K) {
-                    g.c[r][it] = ldg_stream(rp[r].p[2] + (size_t)(u >> 2) * 16);
+                    g.c[r][it] = ldg_stream(rp[r].p[2] + (size_t)(u >> 2) * 16, pol);
                     if (TYPE == T_Q5_K) {
                         const uint2 h = *reinterpret_cast<const uint2 *>(rp[r].p[3] + (size_t)u * 8);
                         g.e[r][it] = h.x; g.f[r][it] = h.y;
                     }
                 } else if (TYPE == T_Q6_K) {
-                    g.c[r][it] = ldg_stream(rp[r].p[2] + (size_t)u * 16);
+                    g.c[r][it] = ldg_stream(rp[r].p[2] + (size_t)u * 16, pol);
                     g.e[r][it] = ldg_stream_u32(rp[r].p[3] + (size_t)u * 4);
                     g.f[r][it] = ldg_stream_u16(rp[r].p[4] + (size_t)(u >> 2) * 2);
                 } else {

@@ -48,6 +48,7 @@ struct GemvParams {
     // ready-made activation image in global memory (quant_rows_kernel, gemm_q.cu), in this launch's shared-memory
     // image layout: the prologue becomes a copy and x / norm_w are not read
     const uint8_t *x_image;
+    int32_t evict_first;    // stream this launch's weights with the L2 evict-first policy
 };
 
 // fills cta_begin[] and returns the grid size; n_sms from the device

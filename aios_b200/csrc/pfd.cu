@@ -154,11 +154,12 @@ __device__ __forceinline__ void loader_advance(const PfdParams &p, Loader &L) {
 
 __device__ __forceinline__ void issue_load(const Loader &L, AnyRegs &g) {
     const int u0 = L.chunk * 64;
+    const uint64_t pol = l2_policy(false);
     switch (L.type) {
-        case T_Q4_K: load_pass<T_Q4_K, false>(g, L.rp, u0, L.nu); break;
-        case T_Q5_K: load_pass<T_Q5_K, false>(g, L.rp, u0, L.nu); break;
-        case T_Q6_K: load_pass<T_Q6_K, false>(g, L.rp, u0, L.nu); break;
-        default: load_pass<T_Q8_0, false>(g, L.rp, u0, L.nu); break;
+        case T_Q4_K: load_pass<T_Q4_K, false>(g, L.rp, u0, L.nu, pol); break;
+        case T_Q5_K: load_pass<T_Q5_K, false>(g, L.rp, u0, L.nu, pol); break;
+        case T_Q6_K: load_pass<T_Q6_K, false>(g, L.rp, u0, L.nu, pol); break;
+        default: load_pass<T_Q8_0, false>(g, L.rp, u0, L.nu, pol); break;
     }
 }
 
