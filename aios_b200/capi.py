@@ -105,6 +105,7 @@ SYMBOLS = {
     "aios_sample_logits": (C.c_int, [_P, _P, C.c_int32, _P, C.POINTER(Sampling), C.c_uint64, C.POINTER(C.c_int32), _P, _P]),
     "aios_generate": (C.c_int, [_P, _P, C.c_int32, C.POINTER(Sampling), C.c_int32, _P, C.POINTER(C.c_int32)]),
     "aios_request_submit": (C.c_int, [_P, _P, C.c_int32, C.POINTER(Sampling), C.c_int32, C.c_int32, C.POINTER(_P)]),
+    "aios_request_submit_masked": (C.c_int, [_P, _P, C.c_int32, C.POINTER(Sampling), C.c_int32, C.c_int32, _P, _P, C.POINTER(_P)]),
     "aios_request_poll": (C.c_int, [_P, _P, C.c_int32, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
     "aios_request_wait": (C.c_int, [_P, C.c_int32, C.POINTER(C.c_int32)]),
     "aios_request_cancel": (C.c_int, [_P]),
@@ -325,14 +326,33 @@ class Model:
     def new_seq(self) -> "Seq":
         return Seq(self)
 
-    def submit(self, prompt, max_tokens: int, sampling: Sampling | None = None, stop_at_eog: bool = False) -> "Request":
-        """Queue a generation on the engine's scheduler thread (aios_request_submit); returns at once."""
+    def submit(self, prompt, max_tokens: int, sampling: Sampling | None = None, stop_at_eog: bool = False,
+               mask_cb=None) -> "Request":
+        """Queue a generation on the engine's scheduler thread (aios_request_submit); returns at once.
+        ``mask_cb(last_token, mask) -> int`` (optional): called by the scheduler before every step of this request with
+        the token sampled in the previous step (-1 first) and a zeroed uint8 array of ceil(n_vocab / 8) bytes to fill
+        with the allowed set of the next token; returns 0 (mask written), 1 (no restriction), 2 (finish now)."""
         toks = np.ascontiguousarray(prompt, dtype=np.int32)
         sp = sampling if sampling is not None else Sampling()
         h = _P()
-        _check(lib().aios_request_submit(self.h, _ptr(toks), toks.size, C.byref(sp), max_tokens,
-                                         REQ_STOP_AT_EOG if stop_at_eog else 0, C.byref(h)))
-        return Request(h, self)
+        flags = REQ_STOP_AT_EOG if stop_at_eog else 0
+        if mask_cb is None:
+            _check(lib().aios_request_submit(self.h, _ptr(toks), toks.size, C.byref(sp), max_tokens, flags, C.byref(h)))
+            return Request(h, self)
+
+        def tramp(_user, last_token, mask_ptr, n_bytes):
+            try:
+                arr = np.ctypeslib.as_array(mask_ptr, shape=(n_bytes,))
+                return int(mask_cb(int(last_token), arr))
+            except Exception:  # never unwind into the scheduler thread
+                return -1
+
+        cfun = MASK_CB(tramp)
+        _check(lib().aios_request_submit_masked(self.h, _ptr(toks), toks.size, C.byref(sp), max_tokens, flags,
+                                                C.cast(cfun, _P), None, C.byref(h)))
+        r = Request(h, self)
+        r._keep = cfun  # the C callback must outlive the request
+        return r
 
     def forward_logits(self, tokens, n_past: int = 0) -> np.ndarray:
         toks = np.ascontiguousarray(tokens, dtype=np.int32)
@@ -350,6 +370,7 @@ class Model:
 
 
 REQ_STOP_AT_EOG = 1
+MASK_CB = C.CFUNCTYPE(C.c_int, C.c_void_p, C.c_int32, C.POINTER(C.c_uint8), C.c_int32)
 
 
 class Request:

@@ -64,6 +64,7 @@ __global__ void __launch_bounds__(ATT_THREADS) attn_decode_kernel(const AttnPara
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int rep = p.n_head / p.n_kv;
     const int kvd = p.n_kv * HD;
+    const int kvs = p.kv_stride;  // cache row stride
     const int n_past = *p.n_past_ptr;
     const int n_kv_pos = n_past + 1;  // including the new token
     const int per = (n_kv_pos + ATT_CLUSTER - 1) / ATT_CLUSTER;
@@ -82,8 +83,8 @@ __global__ void __launch_bounds__(ATT_THREADS) attn_decode_kernel(const AttnPara
     if (n_past >= j0 && n_past < j1) {
         const float *kraw = p.qkv + (size_t)p.n_head * HD + (size_t)g * HD;
         const float *vraw = p.qkv + (size_t)p.n_head * HD + (size_t)kvd + (size_t)g * HD;
-        uint16_t *kc = p.k_cache + (size_t)n_past * kvd + (size_t)g * HD;
-        uint16_t *vc = p.v_cache + (size_t)n_past * kvd + (size_t)g * HD;
+        uint16_t *kc = p.k_cache + (size_t)n_past * kvs + (size_t)g * HD;
+        uint16_t *vc = p.v_cache + (size_t)n_past * kvs + (size_t)g * HD;
         for (int i = threadIdx.x; i < HD / 2; i += ATT_THREADS) {
             float x0 = kraw[2 * i], x1 = kraw[2 * i + 1];
             if (2 * i < p.n_rot) {
@@ -131,7 +132,7 @@ __global__ void __launch_bounds__(ATT_THREADS) attn_decode_kernel(const AttnPara
 #pragma unroll
         for (int t = 0; t < ATT_BATCH; t++) {
             const int j = min(jb + t, j1 - 1);
-            load_row<EPL>(p.k_cache + (size_t)j * kvd + (size_t)g * HD + lane * EPL, kf[t]);
+            load_row<EPL>(p.k_cache + (size_t)j * kvs + (size_t)g * HD + lane * EPL, kf[t]);
         }
 #pragma unroll
         for (int t = 0; t < ATT_BATCH; t++) {
@@ -210,7 +211,7 @@ __global__ void __launch_bounds__(ATT_THREADS) attn_decode_kernel(const AttnPara
 #pragma unroll
         for (int t = 0; t < ATT_BATCH; t++) {
             const int j = min(jb + t, j1 - 1);
-            load_row<EPL>(p.v_cache + (size_t)j * kvd + (size_t)g * HD + lane * EPL, vf[t]);
+            load_row<EPL>(p.v_cache + (size_t)j * kvs + (size_t)g * HD + lane * EPL, vf[t]);
         }
 #pragma unroll
         for (int t = 0; t < ATT_BATCH; t++) {

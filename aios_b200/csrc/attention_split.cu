@@ -86,16 +86,28 @@ __device__ __forceinline__ int butterfly_index(int lane) {
 
 // dynamic smem: sc[n_ctx] f32 | part[AS_WARPS][DPC] f64 | knew[HD] f16 | vnew[HD] f16
 template <int HD, int SPLIT>
-__global__ void __launch_bounds__(AS_THREADS, 1) attn_split_kernel(const AttnParams p) {
+__global__ void __launch_bounds__(AS_THREADS, 1) attn_split_kernel(const AttnParams p_in) {
     constexpr int LPR = HD / 8, RPW = 32 / LPR;       // K: lanes per row, rows per warp-load
     constexpr int DPC = HD / SPLIT;                   // output dims of this CTA
     constexpr int VL = DPC / 8, RPV = 32 / VL;        // V: lanes per row slice, rows per warp-load
     static_assert(DPC % 8 == 0 && VL >= 1 && VL <= 4 && LPR >= 8, "unsupported head-dim split");
     const int h = blockIdx.x / SPLIT, part_id = blockIdx.x % SPLIT;
+    // batched decode: blockIdx.y = lane; every lane has its own q/k/v slice, output slice, position and KV range
+    AttnParams p = p_in;
+    if (p_in.n_lanes > 0) {
+        const int l = blockIdx.y;
+        p.qkv = p_in.qkv + (size_t)l * p_in.lane_qkv_stride;
+        p.out = p_in.out + (size_t)l * p_in.lane_out_stride;
+        p.n_past_ptr = p_in.lane_pos + l;
+        uint16_t *base = p_in.lane_kv[l];
+        p.k_cache = base + (reinterpret_cast<uintptr_t>(p_in.k_cache) >> 1);
+        p.v_cache = base + (reinterpret_cast<uintptr_t>(p_in.v_cache) >> 1);
+    }
     const int rep = p.n_head / p.n_kv;
     const int g = h / rep;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int kvd = p.n_kv * HD;
+    const int kvd = p.n_kv * HD;      // width of a raw k / v projection
+    const int kvs = p.kv_stride;      // cache row stride
 
     extern __shared__ __align__(16) uint8_t dyn[];
     const int sc_cap = (p.n_ctx + 3) & ~3;
@@ -126,12 +138,12 @@ __global__ void __launch_bounds__(AS_THREADS, 1) attn_split_kernel(const AttnPar
         for (int c = lo * LPR + threadIdx.x; c < hi * LPR; c += AS_THREADS) {
             const int j = c / LPR, ch = c % LPR;
             const uint32_t dst = (uint32_t)__cvta_generic_to_shared(kst + (size_t)j * HD + ch * 8);
-            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(p.k_cache + (size_t)j * kvd + head_off + ch * 8) : "memory");
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(p.k_cache + (size_t)j * kvs + head_off + ch * 8) : "memory");
         }
         for (int c = lo * VL + threadIdx.x; c < hi * VL; c += AS_THREADS) {
             const int j = c / VL, ch = c % VL;
             const uint32_t dst = (uint32_t)__cvta_generic_to_shared(vst + (size_t)j * DPC + ch * 8);
-            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(p.v_cache + (size_t)j * kvd + head_off + part_id * DPC + ch * 8) : "memory");
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(dst), "l"(p.v_cache + (size_t)j * kvs + head_off + part_id * DPC + ch * 8) : "memory");
         }
         asm volatile("cp.async.commit_group;" ::: "memory");
     };
@@ -163,7 +175,7 @@ __global__ void __launch_bounds__(AS_THREADS, 1) attn_split_kernel(const AttnPar
     for (int t = 0; t < AS_BATCH; t++) {
         const int j = warp * RPW + t * kstep + ksub;
         kk[0][t] = make_uint4(0, 0, 0, 0);
-        if (j >= n_stage && j < n_cached) kk[0][t] = __ldcg(reinterpret_cast<const uint4 *>(kbase + (size_t)j * kvd));
+        if (j >= n_stage && j < n_cached) kk[0][t] = __ldcg(reinterpret_cast<const uint4 *>(kbase + (size_t)j * kvs));
     }
 
     // ---- new token's k (roped) and v, rounded to f16; one CTA of the kv group appends the cache rows
@@ -184,8 +196,8 @@ __global__ void __launch_bounds__(AS_THREADS, 1) attn_split_kernel(const AttnPar
             knew[2 * i] = k0; knew[2 * i + 1] = k1;
             vnew[2 * i] = v0; vnew[2 * i + 1] = v1;
             if (writer) {
-                uint16_t *kc = p.k_cache + (size_t)n_past * kvd + (size_t)g * HD;
-                uint16_t *vc = p.v_cache + (size_t)n_past * kvd + (size_t)g * HD;
+                uint16_t *kc = p.k_cache + (size_t)n_past * kvs + (size_t)g * HD;
+                uint16_t *vc = p.v_cache + (size_t)n_past * kvs + (size_t)g * HD;
                 kc[2 * i] = k0; kc[2 * i + 1] = k1;
                 vc[2 * i] = v0; vc[2 * i + 1] = v1;
             }
@@ -222,7 +234,7 @@ __global__ void __launch_bounds__(AS_THREADS, 1) attn_split_kernel(const AttnPar
             const int j = jb + t * kstep + ksub;
             dst[t] = make_uint4(0, 0, 0, 0);
             if (j < n_stage) dst[t] = *reinterpret_cast<const uint4 *>(kst + (size_t)j * HD + kdl);
-            else if (j < n_cached) dst[t] = __ldcg(reinterpret_cast<const uint4 *>(kbase + (size_t)j * kvd));
+            else if (j < n_cached) dst[t] = __ldcg(reinterpret_cast<const uint4 *>(kbase + (size_t)j * kvs));
         }
     };
     if (n_stage > 0) {  // the first batch was requested before the staged rows had landed
@@ -281,7 +293,7 @@ __global__ void __launch_bounds__(AS_THREADS, 1) attn_split_kernel(const AttnPar
             const int j = jb + t * vstep + vsub;
             vv[t] = make_uint4(0, 0, 0, 0);
             if (j < n_stage) vv[t] = *reinterpret_cast<const uint4 *>(vst + (size_t)j * DPC + (lane % VL) * 8);
-            else if (j < n_cached) vv[t] = __ldcg(reinterpret_cast<const uint4 *>(vbase + (size_t)j * kvd));
+            else if (j < n_cached) vv[t] = __ldcg(reinterpret_cast<const uint4 *>(vbase + (size_t)j * kvs));
         }
     };
     vload(warp * RPV);
@@ -375,7 +387,7 @@ void launch_attn_decode_split(const AttnParams &p_in, cudaStream_t st, bool pdl)
     AttnParams p = p_in;
     p.stage_cap = p.kv_ready ? std::min(p.n_ctx, AS_STAGE_ROWS) : 0;
     cudaLaunchConfig_t cfg{};
-    cfg.gridDim = dim3(p.n_head * AS_SPLIT);
+    cfg.gridDim = dim3(p.n_head * AS_SPLIT, p.n_lanes > 0 ? p.n_lanes : 1);
     cfg.blockDim = dim3(AS_THREADS);
     cfg.dynamicSmemBytes = as_smem(p.n_ctx, p.hd, AS_SPLIT) + (size_t)p.stage_cap * (p.hd + p.hd / AS_SPLIT) * 2;
     cfg.stream = st;

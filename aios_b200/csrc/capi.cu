@@ -2,6 +2,7 @@
 // all C++ exceptions and turns them into an AIOS_E_* code + thread-local message.
 #include <string.h>
 
+#include <algorithm>
 #include <atomic>
 #include <chrono>
 #include <condition_variable>
@@ -24,6 +25,8 @@ struct aios_request {
     std::vector<int32_t> prompt;
     aios_sampling sp{};
     int32_t max_tokens = 0, flags = 0;
+    aios_mask_cb mask_cb = nullptr;   // optional: the allowed-token set of the next step (JSON mode)
+    void *mask_user = nullptr;
     std::mutex mu;
     std::condition_variable cv;
     std::vector<int32_t> out;   // generated tokens so far
@@ -31,11 +34,14 @@ struct aios_request {
     bool done = false, cancel = false, orphan = false;
     int err = AIOS_OK;
     std::string msg;
+    // scheduler-side state (touched by the scheduler thread only)
+    int generated = 0;
+    int32_t last_token = -1;
 };
 
 struct aios_engine {
     Engine impl;
-    // scheduler thread: requests of all models of this engine, first come first served (one GPU stream)
+    // scheduler thread: continuous batching over the requests of all models of this engine (one GPU stream)
     std::thread worker;
     std::mutex qmu;
     std::condition_variable qcv;
@@ -45,7 +51,6 @@ struct aios_engine {
     ~aios_engine();
     void ensure_worker();
     void run();
-    void serve(aios_request *r);
 };
 // host-only: the tokenizer of one GGUF file; either owns its file (aios_vocab_open) or borrows the model's
 struct aios_vocab {
@@ -66,7 +71,9 @@ struct aios_model {
         return vocab_.get();
     }
     aios_engine *owner = nullptr;
-    std::unique_ptr<Seq> req_seq;        // the KV slot queued requests run in (created on first use)
+    // the scheduler's batch of this model: up to 64 requests decode together (created on first use)
+    std::unique_ptr<Batch> batch;
+    std::vector<aios_request *> lane_req;  // lane -> request
     std::atomic<int> inflight{0};        // queued or running requests
     aios_model(Engine *e, const char *n, const char *p, int c) : impl(e, n, p, c) {}
 };
@@ -89,73 +96,172 @@ static void finish_request(aios_request *r, int err, const std::string &msg) {
     if (orphan) delete r;  // the owner freed it while it was queued or running
 }
 
-void aios_engine::serve(aios_request *r) {
-    int err = AIOS_OK;
-    std::string msg;
+static void error_of(const std::exception_ptr &ep, int *err, std::string *msg) {
     try {
-        impl.make_current();
-        Model &M = r->m->impl;
-        const Tokenizer *tok = (r->flags & AIOS_REQ_STOP_AT_EOG) ? &r->m->vocab()->tok : nullptr;
-        {
-            std::lock_guard<std::mutex> lk(impl.mu);
-            if (!r->m->req_seq) r->m->req_seq.reset(new Seq(&M, true));  // a hidden slot, not one of the caller's
-            r->m->req_seq->reset();
-            r->m->req_seq->prefill(r->prompt.data(), (int)r->prompt.size());
-        }
-        Seq &s = *r->m->req_seq;
-        int left = r->max_tokens;
-        int32_t buf[16];
-        while (left > 0) {
-            {
-                std::lock_guard<std::mutex> lk(r->mu);
-                if (r->cancel) break;
-            }
-            int n;
-            {
-                std::lock_guard<std::mutex> lk(impl.mu);  // other API calls of this engine interleave between chunks
-                n = s.decode(r->sp, std::min(left, 16), buf);
-            }
-            if (n <= 0) break;  // context full
-            left -= n;
-            int keep = n;
-            bool stop = false;
-            if (tok)
-                for (int i = 0; i < n; i++)
-                    if (tok->is_eog(buf[i])) { keep = i; stop = true; break; }
-            {
-                std::lock_guard<std::mutex> lk(r->mu);
-                r->out.insert(r->out.end(), buf, buf + keep);
-            }
-            r->cv.notify_all();
-            if (stop) break;
-        }
+        std::rethrow_exception(ep);
     } catch (const GgufError &e) {
-        err = e.code; msg = e.what();
+        *err = e.code; *msg = e.what();
     } catch (const CudaError &e) {
         cudaGetLastError();
-        err = AIOS_E_CUDA; msg = e.what();
+        *err = AIOS_E_CUDA; *msg = e.what();
     } catch (const std::exception &e) {
-        err = AIOS_E_STATE; msg = e.what();
+        *err = AIOS_E_STATE; *msg = e.what();
+    } catch (...) {
+        *err = AIOS_E_STATE; *msg = "unknown error";
     }
-    finish_request(r, err, msg);
 }
 
+// Continuous batching: every pass of the loop (1) admits waiting requests into free lanes of their model's batch —
+// the prompt is prefilled into the lane's sequence — and (2) runs ONE decode step for every model that has live lanes:
+// each lane samples a token and feeds it, all lanes of a model through the same weight stream.  Finished, cancelled and
+// failed requests leave their lane between steps; the next waiting request takes it in the following pass.
 void aios_engine::run() {
-    for (;;) {
-        aios_request *r;
-        {
-            std::unique_lock<std::mutex> lk(qmu);
-            qcv.wait(lk, [&] { return stop || !queue.empty(); });
-            if (queue.empty()) return;  // stop requested and nothing left
-            r = queue.front();
-            queue.pop_front();
-            if (stop) {
-                lk.unlock();
-                finish_request(r, AIOS_E_STATE, "engine destroyed before the request ran");
-                continue;
+    std::deque<aios_request *> waiting;   // submitted, not yet in a lane (first come first served per model)
+    std::vector<aios_model *> live;       // models with lanes in use
+    auto fail_all = [&](const std::string &why) {
+        for (aios_request *r : waiting) finish_request(r, AIOS_E_STATE, why);
+        waiting.clear();
+        for (aios_model *m : live) {
+            std::lock_guard<std::mutex> lk(impl.mu);
+            while (m->batch && m->batch->n > 0) {
+                aios_request *r = m->lane_req[(size_t)m->batch->n - 1];
+                try { m->batch->retire(m->batch->n - 1); } catch (...) { m->batch->n--; }
+                finish_request(r, AIOS_E_STATE, why);
             }
         }
-        serve(r);
+        live.clear();
+    };
+    for (;;) {
+        {
+            std::unique_lock<std::mutex> lk(qmu);
+            if (waiting.empty() && live.empty()) qcv.wait(lk, [&] { return stop || !queue.empty(); });
+            while (!queue.empty()) { waiting.push_back(queue.front()); queue.pop_front(); }
+            if (stop) {
+                lk.unlock();
+                fail_all("engine destroyed before the request finished");
+                return;
+            }
+        }
+        // ---- (1) admission
+        for (auto it = waiting.begin(); it != waiting.end();) {
+            aios_request *r = *it;
+            aios_model *m = r->m;
+            bool cancelled;
+            {
+                std::lock_guard<std::mutex> lk(r->mu);
+                cancelled = r->cancel;
+            }
+            if (cancelled || r->max_tokens <= 0) {
+                it = waiting.erase(it);
+                finish_request(r, AIOS_OK, "");
+                continue;
+            }
+            int err = AIOS_OK;
+            std::string msg;
+            bool admitted = false;
+            try {
+                std::lock_guard<std::mutex> lk(impl.mu);
+                impl.make_current();
+                if (!m->batch) {
+                    m->batch.reset(new Batch(&m->impl));
+                    m->lane_req.assign((size_t)m->batch->capacity(), nullptr);
+                }
+                Batch &b = *m->batch;
+                // a lane is free and the KV pool can back prompt + generation (pages are only counted when capped)
+                const size_t need = ((size_t)(r->prompt.size() + (size_t)r->max_tokens) * m->impl.kv_pos_bytes() + m->impl.kv_pool.page_bytes - 1) /
+                                    m->impl.kv_pool.page_bytes;
+                if (b.n < b.capacity() && m->impl.kv_pool.pages_available() >= need) {
+                    const int lane = b.admit(r->prompt.data(), (int)r->prompt.size(), r->sp);
+                    m->lane_req[(size_t)lane] = r;
+                    r->generated = 0;
+                    r->last_token = -1;
+                    admitted = true;
+                    if (std::find(live.begin(), live.end(), m) == live.end()) live.push_back(m);
+                }
+            } catch (...) {
+                error_of(std::current_exception(), &err, &msg);
+            }
+            if (err != AIOS_OK) {
+                it = waiting.erase(it);
+                finish_request(r, err, msg);
+            } else if (admitted) {
+                it = waiting.erase(it);
+            } else {
+                ++it;
+            }
+        }
+        // ---- (2) one step per model with live lanes
+        for (size_t mi = 0; mi < live.size();) {
+            aios_model *m = live[mi];
+            Batch &b = *m->batch;
+            int err = AIOS_OK;
+            std::string msg;
+            std::vector<uint8_t> mask_buf;
+            try {
+                std::lock_guard<std::mutex> lk(impl.mu);  // synchronous API calls of this engine interleave between steps
+                impl.make_current();
+                // cancelled lanes leave before the step; masked lanes get this step's allowed set
+                for (int lane = b.n - 1; lane >= 0; lane--) {
+                    aios_request *r = m->lane_req[(size_t)lane];
+                    bool cancelled;
+                    {
+                        std::lock_guard<std::mutex> rl(r->mu);
+                        cancelled = r->cancel;
+                    }
+                    int cb_rc = 1;
+                    if (!cancelled && r->mask_cb) {
+                        mask_buf.assign(b.mask_bytes, 0);
+                        cb_rc = r->mask_cb(r->mask_user, r->last_token, mask_buf.data(), (int32_t)((m->impl.hp.n_vocab + 7) / 8));
+                    }
+                    if (cancelled || cb_rc == 2 || cb_rc < 0) {
+                        b.retire(lane);
+                        m->lane_req[(size_t)lane] = m->lane_req[(size_t)b.n];  // the former last lane moved here
+                        m->lane_req[(size_t)b.n] = nullptr;
+                        finish_request(r, cb_rc < 0 ? AIOS_E_STATE : AIOS_OK, cb_rc < 0 ? "the mask callback failed" : "");
+                        continue;
+                    }
+                    if (r->mask_cb) b.set_mask(lane, cb_rc == 0 ? mask_buf.data() : nullptr);
+                }
+                if (b.n > 0) b.step();
+                const Tokenizer *tok = nullptr;
+                for (int lane = b.n - 1; lane >= 0; lane--) {
+                    aios_request *r = m->lane_req[(size_t)lane];
+                    const int32_t t = b.h_tok[lane];
+                    r->generated++;
+                    r->last_token = t;
+                    bool finished = r->generated >= r->max_tokens;
+                    bool keep = true;
+                    if (r->flags & AIOS_REQ_STOP_AT_EOG) {
+                        if (!tok) tok = &m->vocab()->tok;
+                        if (tok->is_eog(t)) { keep = false; finished = true; }
+                    }
+                    if (keep) {
+                        std::lock_guard<std::mutex> rl(r->mu);
+                        r->out.push_back(t);
+                    }
+                    r->cv.notify_all();
+                    if (finished) {
+                        b.retire(lane);
+                        m->lane_req[(size_t)lane] = m->lane_req[(size_t)b.n];
+                        m->lane_req[(size_t)b.n] = nullptr;
+                        finish_request(r, AIOS_OK, "");
+                    }
+                }
+            } catch (...) {
+                error_of(std::current_exception(), &err, &msg);
+            }
+            if (err != AIOS_OK) {  // a failed step fails every request of the batch
+                std::lock_guard<std::mutex> lk(impl.mu);
+                while (b.n > 0) {
+                    aios_request *r = m->lane_req[(size_t)b.n - 1];
+                    m->lane_req[(size_t)b.n - 1] = nullptr;
+                    try { b.retire(b.n - 1); } catch (...) { b.n--; }
+                    finish_request(r, err, msg);
+                }
+            }
+            if (b.n == 0) live.erase(live.begin() + (long)mi);
+            else mi++;
+        }
     }
 }
 
@@ -244,10 +350,13 @@ int aios_model_unload(aios_model *m) {
     return guarded([&] {
         if (!m) return fail(AIOS_E_INVAL, "null model");
         if (m->inflight.load() > 0) return fail(AIOS_E_STATE, "model still has queued or running requests");
-        m->scratch.reset();
-        m->req_seq.reset();
-        for (bool u : m->impl.slot_used)
-            if (u) return fail(AIOS_E_STATE, "model still has live sequences");
+        {
+            std::lock_guard<std::mutex> lk(m->impl.eng->mu);
+            m->impl.eng->make_current();
+            m->scratch.reset();
+            m->batch.reset();
+        }
+        if (m->impl.live_seqs > 0) return fail(AIOS_E_STATE, "model still has live sequences");
         delete m;
         return AIOS_OK;
     });
@@ -264,7 +373,8 @@ int aios_model_info_get(const aios_model *m, aios_model_info *o) {
         o->head_dim = M.hp.head_dim; o->n_ff = M.hp.n_ff; o->n_vocab = M.hp.n_vocab; o->n_ctx = M.hp.n_ctx;
         o->n_rot = M.hp.n_rot; o->file_type = M.hp.file_type; o->n_tensors = (int32_t)M.file->tensors().size();
         o->max_batch = M.eng->max_batch; o->rms_eps = M.hp.rms_eps; o->rope_freq_base = M.hp.rope_freq_base;
-        o->file_bytes = (int64_t)M.file->file_bytes(); o->weight_bytes = M.weight_bytes; o->kv_bytes = (int64_t)M.kv.bytes;
+        o->file_bytes = (int64_t)M.file->file_bytes(); o->weight_bytes = M.weight_bytes;
+        o->kv_bytes = (int64_t)(const_cast<Model &>(M).kv_pool.pages_in_use() * M.kv_pool.page_bytes);
         o->weight_bytes_per_token = M.weight_bytes_per_token;
         o->kv_bytes_per_position = (int64_t)M.hp.n_layer * 2 * M.hp.n_head_kv * M.hp.head_dim * 2;
         return AIOS_OK;
@@ -498,8 +608,16 @@ int aios_generate(aios_model *m, const int32_t *prompt, int32_t n_prompt, const 
     });
 }
 
+int aios_request_submit_masked(aios_model *m, const int32_t *tokens, int32_t n, const aios_sampling *sp, int32_t max_tokens,
+                               int32_t flags, aios_mask_cb cb, void *user, aios_request **out);
+
 int aios_request_submit(aios_model *m, const int32_t *tokens, int32_t n, const aios_sampling *sp, int32_t max_tokens,
                         int32_t flags, aios_request **out) {
+    return aios_request_submit_masked(m, tokens, n, sp, max_tokens, flags, nullptr, nullptr, out);
+}
+
+int aios_request_submit_masked(aios_model *m, const int32_t *tokens, int32_t n, const aios_sampling *sp, int32_t max_tokens,
+                               int32_t flags, aios_mask_cb cb, void *user, aios_request **out) {
     return guarded([&] {
         if (!m || !tokens || n <= 0 || !out || max_tokens < 0) return fail(AIOS_E_INVAL, "bad argument");
         if (!m->owner) return fail(AIOS_E_STATE, "model has no engine");
@@ -512,6 +630,8 @@ int aios_request_submit(aios_model *m, const int32_t *tokens, int32_t n, const a
         if (sp) r->sp = *sp;
         r->max_tokens = std::min(max_tokens, m->impl.hp.n_ctx - n);
         r->flags = flags;
+        r->mask_cb = cb;
+        r->mask_user = user;
         m->inflight.fetch_add(1);
         aios_engine *e = m->owner;
         {
@@ -645,14 +765,14 @@ int aios_matmul(aios_engine *e, int32_t type, const void *w_blocks, int64_t n_ro
                 const float *norm_w, float rms_eps, float *y) {
     return guarded([&] {
         if (!e || !w_blocks || !x || !y || n_rows <= 0 || k <= 0 || n_tok <= 0) return fail(AIOS_E_INVAL, "bad argument");
-        if (!gemm_q_usable(type, (int)k)) return fail(AIOS_E_UNSUPPORTED, "aios_matmul: Q4_K / Q8_0 weights, k a multiple of 256");
-        if (n_tok > 32) return fail(AIOS_E_RANGE, "aios_matmul: at most 32 tokens per call");
+        if (!gemm_q_usable(type, (int)k)) return fail(AIOS_E_UNSUPPORTED, "aios_matmul: Q4_K / Q6_K / Q8_0 weights, k a multiple of 256");
+        if (n_tok > GEMM_MAX_TOKENS) return fail(AIOS_E_RANGE, "aios_matmul: at most 64 tokens per call");
         std::lock_guard<std::mutex> lk(e->impl.mu);
         Engine &E = e->impl;
         E.make_current();
         DevMatrix dm;
         make_dev_matrix(E, type, w_blocks, n_rows, k, dm);
-        const int T8 = (n_tok + 7) / 8 * 8;
+        const int T8 = gemm_pad_tokens(n_tok);
         DevBuf dx((size_t)T8 * k * 4), dy((size_t)n_tok * n_rows * 4), dn, img(gemm_images_bytes((int)k, T8));
         CUDA_CHECK(cudaMemsetAsync(dx.p, 0, dx.bytes, E.stream));  // padding tokens: zeros
         CUDA_CHECK(cudaMemcpyAsync(dx.p, x, (size_t)n_tok * k * 4, cudaMemcpyHostToDevice, E.stream));
@@ -727,9 +847,12 @@ int aios_seq_read_kv(aios_seq *s, int32_t layer, int32_t pos0, int32_t n, uint16
         if (layer < 0 || layer >= M.hp.n_layer || pos0 < 0 || n < 0 || pos0 + n > M.hp.n_ctx) return fail(AIOS_E_INVAL, "range");
         std::lock_guard<std::mutex> lk(M.eng->mu);
         M.eng->make_current();
-        const size_t kvd = (size_t)M.hp.n_head_kv * M.hp.head_dim;
-        CUDA_CHECK(cudaMemcpy(k_out, M.k_cache(s->impl.slot, layer) + (size_t)pos0 * kvd, (size_t)n * kvd * 2, cudaMemcpyDeviceToHost));
-        CUDA_CHECK(cudaMemcpy(v_out, M.v_cache(s->impl.slot, layer) + (size_t)pos0 * kvd, (size_t)n * kvd * 2, cudaMemcpyDeviceToHost));
+        if (n == 0) return (int)AIOS_OK;
+        if (pos0 + n > s->impl.n_past) return fail(AIOS_E_INVAL, "rows beyond the sequence's position");
+        // rows of one layer are kv_pos_bytes apart (position-major pages): strided copy
+        const size_t kvd = M.kvd(), pitch = M.kv_pos_bytes();
+        CUDA_CHECK(cudaMemcpy2D(k_out, kvd * 2, s->impl.k_cache(layer) + (size_t)pos0 * M.kv_pos_elems(), pitch, kvd * 2, (size_t)n, cudaMemcpyDeviceToHost));
+        CUDA_CHECK(cudaMemcpy2D(v_out, kvd * 2, s->impl.v_cache(layer) + (size_t)pos0 * M.kv_pos_elems(), pitch, kvd * 2, (size_t)n, cudaMemcpyDeviceToHost));
         return (int)AIOS_OK;
     });
 }

@@ -211,22 +211,15 @@ Model::Model(Engine *e, const std::string &name_, const std::string &path_, int 
         CUDA_CHECK(cudaMemcpy(rope_cos.p, c.data(), c.size() * 4, cudaMemcpyHostToDevice));
         CUDA_CHECK(cudaMemcpy(rope_sin.p, s.data(), s.size() * 4, cudaMemcpyHostToDevice));
     }
-    const size_t n_slots = (size_t)e->max_batch + HIDDEN_SLOTS;
-    kv = DevBuf(n_slots * hp.n_layer * 2 * kv_layer_elems() * 2);
-    CUDA_CHECK(cudaMemsetAsync(kv.p, 0, kv.bytes, st));
-    CUDA_CHECK(cudaStreamSynchronize(st));
-    slot_used.assign(n_slots, false);
+    {   // KV pages of 8 MB (64 positions of Mistral-7B, 372 of TinyLlama); AIOS_KV_POOL_MB caps the pool
+        size_t cap = 0;
+        if (const char *c = getenv("AIOS_KV_POOL_MB")) cap = (size_t)atoll(c) << 20;
+        kv_pool.init(e->device, 8u << 20, cap);
+    }
     attn_splits = std::max(1, std::min(32, (2 * e->n_sms) / std::max(1, hp.n_head_kv)));
 }
 
 Model::~Model() {}
-
-uint16_t *Model::k_cache(int slot, int layer) const {
-    return kv.as<uint16_t>() + (((size_t)slot * hp.n_layer + layer) * 2 + 0) * kv_layer_elems();
-}
-uint16_t *Model::v_cache(int slot, int layer) const {
-    return kv.as<uint16_t>() + (((size_t)slot * hp.n_layer + layer) * 2 + 1) * kv_layer_elems();
-}
 
 // ---------------------------------------------------------------- Seq
 struct KernelTimer {  // per-launch CUDA events (profile_decode only)
@@ -244,19 +237,20 @@ struct KernelTimer {  // per-launch CUDA events (profile_decode only)
 };
 #define TIMED(kind, stmt) do { if (timer) timer->begin(kind); stmt; if (timer) timer->end(); } while (0)
 
-Seq::Seq(Model *m_, bool internal) : m(m_), slot(-1) {
+Seq::Seq(Model *m_, bool internal_) : m(m_), internal(internal_) {
     m->eng->make_current();
     {
-        // caller-visible sequences own slots [0, max_batch); the library's own live in the hidden slots behind them
         std::lock_guard<std::mutex> lk(m->mu);
-        const size_t lo = internal ? (size_t)m->eng->max_batch : 0;
-        const size_t hi = internal ? m->slot_used.size() : (size_t)m->eng->max_batch;
-        for (size_t i = lo; i < hi; i++)
-            if (!m->slot_used[i]) { slot = (int)i; m->slot_used[i] = true; break; }
+        if (!internal && m->user_seqs >= m->eng->max_batch) throw std::runtime_error("no free KV slot (engine max_batch reached)");
+        if (!internal) m->user_seqs++;
+        m->live_seqs++;
     }
-    if (slot < 0) throw std::runtime_error(internal ? "no free internal KV slot" : "no free KV slot (engine max_batch reached)");
     const HParams &hp = m->hp;
     try {
+        kv.init(&m->kv_pool, (size_t)hp.n_ctx * m->kv_pos_bytes());
+        // a caller's sequence owns its whole context from the start (it may later be driven by the allocation-free
+        // aios_seq_decode_static); the library's own sequences grow page by page
+        if (!internal) kv.ensure((size_t)hp.n_ctx * m->kv_pos_bytes());
         state = DevBuf(sizeof(SeqState));
         x = DevBuf((size_t)hp.n_embd * 4);
         qkv = DevBuf((size_t)(hp.n_head + 2 * hp.n_head_kv) * hp.head_dim * 4);
@@ -278,20 +272,33 @@ Seq::Seq(Model *m_, bool internal) : m(m_), slot(-1) {
         build_pfd();
     } catch (...) {
         std::lock_guard<std::mutex> lk(m->mu);
-        m->slot_used[slot] = false;
+        if (!internal) m->user_seqs--;
+        m->live_seqs--;
         throw;
     }
 }
 
 Seq::~Seq() {
     if (graph) cudaGraphExecDestroy(graph);
+    cudaStreamSynchronize(m->eng->stream);  // nothing in flight may still touch the pages that are about to be unmapped
     std::lock_guard<std::mutex> lk(m->mu);
-    if (slot >= 0) m->slot_used[slot] = false;
+    if (!internal) m->user_seqs--;
+    m->live_seqs--;
+}
+
+void Seq::ensure_kv(int n_positions) {
+    if (!internal) return;  // fully mapped at creation
+    const int n = std::min(n_positions, m->hp.n_ctx);
+    kv.ensure((size_t)n * m->kv_pos_bytes());
 }
 
 void Seq::reset() {
     n_past = 0;
     have_logits = false;
+    if (internal && !kv.pages.empty()) {  // give the pages back (all but the first, which the next request will need anyway)
+        CUDA_CHECK(cudaStreamSynchronize(m->eng->stream));
+        kv.trim(1);
+    }
     SeqState s{-1, 0, 0, 0, 0ull};
     CUDA_CHECK(cudaMemcpy(state.p, &s, sizeof(s), cudaMemcpyHostToDevice));
 }
@@ -348,8 +355,8 @@ void Seq::launch_token_pass(bool from_prompt, int prompt_idx, int pos_value, boo
                 p.epi = EPI_QKV_ROPE;
                 p.rope.cos = m->rope_cos.as<float>(); p.rope.sin = m->rope_sin.as<float>();
                 p.rope.n_past_ptr = &sd->pos;
-                p.rope.k_cache = m->k_cache(slot, il); p.rope.v_cache = m->v_cache(slot, il);
-                p.rope.n_rot = hp.n_rot; p.rope.hd = hp.head_dim; p.rope.kvd = KVD;
+                p.rope.k_cache = k_cache(il); p.rope.v_cache = v_cache(il);
+                p.rope.n_rot = hp.n_rot; p.rope.hd = hp.head_dim; p.rope.kvd = KVD; p.rope.kv_stride = (int32_t)m->kv_pos_elems();
                 kv_ready = true;
             }
             add_gemv(p, pdl);
@@ -366,7 +373,7 @@ void Seq::launch_token_pass(bool from_prompt, int prompt_idx, int pos_value, boo
             A.kind = 1; A.pdl = pdl;
             AttnParams &a = A.a;
             a.qkv = qkv.as<float>(); a.out = att.as<float>();
-            a.k_cache = m->k_cache(slot, il); a.v_cache = m->v_cache(slot, il);
+            a.k_cache = k_cache(il); a.v_cache = v_cache(il); a.kv_stride = (int32_t)m->kv_pos_elems();
             a.rope_cos = m->rope_cos.as<float>(); a.rope_sin = m->rope_sin.as<float>();
             a.n_past_ptr = &sd->pos;
             a.scratch = attn_scratch.as<float>(); a.counters = attn_counters.as<uint32_t>();
@@ -439,12 +446,13 @@ void Seq::prefill(const int32_t *tokens, int n) {
     for (int i = 0; i < n; i++)
         if (tokens[i] < 0 || tokens[i] >= m->hp.n_vocab) throw std::invalid_argument("token id out of range");
     m->eng->make_current();
+    ensure_kv(n_past + n);
     cudaStream_t st = m->eng->stream;
     CUDA_CHECK(cudaMemcpyAsync(prompt.p, tokens, (size_t)n * 4, cudaMemcpyHostToDevice, st));
     if (n >= 4 && !(m->eng->flags & AIOS_ENGINE_NO_GEMM)) {
-        // prompt chunks of up to 32 tokens: every Q4_K / Q8_0 matrix is streamed once per chunk (gemm_q.cu)
-        for (int i = 0; i < n; i += 32) {
-            const int T = std::min(32, n - i);
+        // prompt chunks of up to 64 tokens: every matrix is streamed once per chunk (gemm_q.cu)
+        for (int i = 0; i < n; i += GEMM_MAX_TOKENS) {
+            const int T = std::min((int)GEMM_MAX_TOKENS, n - i);
             prefill_chunk(i, T, n_past + i, i + T == n, st);
         }
     } else {
@@ -484,60 +492,75 @@ void Seq::ensure_graph(const aios_sampling &sp) {
     graph_mask = mask_on;
 }
 
-// One prompt chunk of T <= 32 tokens at positions pos0 .. pos0+T-1.  Same arithmetic as T token passes (the logits and
-// the KV rows come out bit-identical); what changes is the weight traffic: every Q4_K / Q8_0 matrix is streamed once
-// for the whole chunk by the tensor-core GEMM (gemm_q.cu).  Matrices of other types (Q6_K, Q5_K) and attention still
-// go token by token through the decode kernels.
+// One prompt chunk of T <= 64 tokens at positions pos0 .. pos0+T-1.  Same arithmetic as T token passes (the logits and
+// the KV rows come out bit-identical); what changes is the weight traffic: every matrix is streamed once for the whole
+// chunk by the multi-token GEMM (gemm_q.cu; q/k/v and gate/up as segments of one launch).  Attention still goes token
+// by token through the decode kernel (each token sees the rows before it).  Matrices of other types (Q5_K) fall back
+// to the GEMV, token by token.
 void Seq::prefill_chunk(int idx0, int T, int pos0, bool want_logits, cudaStream_t st) {
     const HParams &hp = m->hp;
+    constexpr int CH = GEMM_MAX_TOKENS;
     const int E = hp.n_embd, FF = hp.n_ff, QD = hp.n_head * hp.head_dim, KVD = hp.n_head_kv * hp.head_dim;
-    const int LQ = QD + 2 * KVD, T8 = (T + 7) / 8 * 8, n_sms = m->eng->n_sms;
+    const int LQ = QD + 2 * KVD, Tp = gemm_pad_tokens(T), n_sms = m->eng->n_sms;
     SeqState *sd = state.as<SeqState>();
-    if (!cx.p) {  // first chunk of this sequence: room for 32 tokens side by side
-        cx = DevBuf((size_t)32 * E * 4); cqkv = DevBuf((size_t)32 * LQ * 4); catt = DevBuf((size_t)32 * QD * 4);
-        ch = DevBuf((size_t)32 * FF * 4); cgu = DevBuf((size_t)32 * 2 * FF * 4);
-        cimg = DevBuf(gemm_images_bytes(std::max(std::max(E, QD), FF), 32)); cpos = DevBuf(32 * 4);
+    if (!cx.p) {  // first chunk of this sequence: room for CH tokens side by side
+        cx = DevBuf((size_t)CH * E * 4); cqkv = DevBuf((size_t)CH * LQ * 4); catt = DevBuf((size_t)CH * QD * 4);
+        ch = DevBuf((size_t)CH * FF * 4); cgu = DevBuf((size_t)CH * 2 * FF * 4);
+        cimg = DevBuf(2 * gemm_images_bytes(std::max(std::max(E, QD), FF), CH)); cpos = DevBuf(CH * 4);
         CUDA_CHECK(cudaMemsetAsync(cx.p, 0, cx.bytes, st)); CUDA_CHECK(cudaMemsetAsync(catt.p, 0, catt.bytes, st));
         CUDA_CHECK(cudaMemsetAsync(ch.p, 0, ch.bytes, st));  // rows of padding tokens stay zero (finite images)
     }
     float *X = cx.as<float>(), *QKV = cqkv.as<float>(), *ATT = catt.as<float>(), *H = ch.as<float>(), *GU = cgu.as<float>();
-    uint8_t *IMG = cimg.as<uint8_t>();
+    uint8_t *IMG[2] = {cimg.as<uint8_t>(), cimg.as<uint8_t>() + cimg.bytes / 2};
     int32_t *POS = cpos.as<int32_t>();
     const int32_t *toks = prompt.as<int32_t>() + idx0;
-    for (int t = 0; t < T; t++)  // the last token also leaves its position / id in the sequence state
-        launch_embed_row(m->tok_embd_type, m->tok_embd_raw.p, m->tok_embd_row_bytes, E, toks + t, X + (size_t)t * E,
-                         t == T - 1 ? &sd->pos : POS + t, pos0 + t, t == T - 1 ? &sd->cur_token : nullptr, st);
-    CUDA_CHECK(cudaMemcpyAsync(POS + (T - 1), &sd->pos, 4, cudaMemcpyDeviceToDevice, st));
-
+    launch_embed_rows(m->tok_embd_type, m->tok_embd_raw.p, m->tok_embd_row_bytes, E, toks, T, X, E, st);
+    {   // positions of the chunk's tokens; the last token also leaves its position / id in the sequence state
+        std::vector<int32_t> hp_pos((size_t)T);
+        for (int t = 0; t < T; t++) hp_pos[(size_t)t] = pos0 + t;
+        CUDA_CHECK(cudaMemcpyAsync(POS, hp_pos.data(), (size_t)T * 4, cudaMemcpyHostToDevice, st));
+        CUDA_CHECK(cudaStreamSynchronize(st));  // hp_pos is a stack buffer
+        CUDA_CHECK(cudaMemcpyAsync(&sd->pos, POS + (T - 1), 4, cudaMemcpyDeviceToDevice, st));
+        CUDA_CHECK(cudaMemcpyAsync(&sd->cur_token, toks + (T - 1), 4, cudaMemcpyDeviceToDevice, st));
+    }
+    auto perm_class = [](int type) { return type == T_Q6_K ? 1 : type == T_Q8_0 ? 2 : 0; };
     auto gemv1 = [&](const WPlanes &w, const float *xin, const float *norm, float *out, int epi) {
         GemvParams p{};
         p.n_seg = 1; p.epi = epi; p.k = w.k; p.seg[0] = w; p.out[0] = out; p.x = xin; p.norm_w = norm; p.eps = hp.rms_eps;
+        p.evict_first = m->eng->evict_first ? 1 : 0;
         launch_gemv(p, gemv_plan_grid(p, n_sms), st, false);
     };
-    // Y[t] (=|+=) W . act(in[t]) for all tokens of the chunk; `img_type` remembers which image permutation IMG holds
-    auto matmul = [&](const WPlanes &w, const float *in, int64_t ldin, const float *norm, float *out, int64_t ldo, int epi,
-                      int &img_type) {
-        if (gemm_q_usable(w.type, w.k)) {
-            const int perm_class = w.type == T_Q8_0 ? T_Q8_0 : T_Q4_K;
-            if (img_type != perm_class) {
-                launch_quant_rows(w.type, in, ldin, norm, hp.rms_eps, w.k, T8, IMG, st);
-                img_type = perm_class;
+    // Y[t] (=|+=) W . act(in[t]) for all tokens of the chunk and every matrix of the group (they share the input)
+    auto matmul = [&](std::initializer_list<const WPlanes *> ws, std::initializer_list<float *> outs, const float *in, int64_t ldin,
+                      const float *norm, int64_t ldo, int epi) {
+        GemmMulti g{};
+        g.T = T; g.epi = epi; g.ldo = ldo;
+        uint8_t *img_of_class[3] = {nullptr, nullptr, nullptr};
+        int n_bufs = 0;
+        auto o = outs.begin();
+        for (const WPlanes *w : ws) {
+            float *out = *o++;
+            const int pc = perm_class(w->type);
+            if (!gemm_q_usable(w->type, w->k) || (!img_of_class[pc] && n_bufs >= 2)) {
+                for (int t = 0; t < T; t++) gemv1(*w, in + (size_t)t * ldin, norm, out + (size_t)t * ldo, epi);
+                continue;
             }
-            launch_gemm_q(w, IMG, T, out, ldo, epi, st);
-        } else {
-            for (int t = 0; t < T; t++) gemv1(w, in + (size_t)t * ldin, norm, out + (size_t)t * ldo, epi);
+            if (!img_of_class[pc]) {
+                img_of_class[pc] = IMG[n_bufs++];
+                launch_quant_rows(w->type, in, ldin, norm, hp.rms_eps, w->k, Tp, img_of_class[pc], st);
+            }
+            g.seg[g.n_seg] = *w; g.out[g.n_seg] = out; g.images[g.n_seg] = img_of_class[pc];
+            g.n_seg++;
         }
+        if (g.n_seg) launch_gemm_multi(g, st);
     };
     for (int il = 0; il < hp.n_layer; il++) {
         const Layer &L = m->layers[il];
-        int img = -1;
-        matmul(L.wq.w, X, E, L.attn_norm.as<float>(), QKV, LQ, EPI_STORE, img);
-        matmul(L.wk.w, X, E, L.attn_norm.as<float>(), QKV + QD, LQ, EPI_STORE, img);
-        matmul(L.wv.w, X, E, L.attn_norm.as<float>(), QKV + QD + KVD, LQ, EPI_STORE, img);
+        matmul({&L.wq.w, &L.wk.w, &L.wv.w}, {QKV, QKV + QD, QKV + QD + KVD}, X, E, L.attn_norm.as<float>(), LQ, EPI_STORE);
         for (int t = 0; t < T; t++) {  // RoPE + KV append + attention, token by token (each sees the rows before it)
             AttnParams a{};
             a.qkv = QKV + (size_t)t * LQ; a.out = ATT + (size_t)t * QD;
-            a.k_cache = m->k_cache(slot, il); a.v_cache = m->v_cache(slot, il);
+            a.k_cache = k_cache(il); a.v_cache = v_cache(il); a.kv_stride = (int32_t)m->kv_pos_elems();
             a.rope_cos = m->rope_cos.as<float>(); a.rope_sin = m->rope_sin.as<float>();
             a.n_past_ptr = POS + t;
             a.scratch = attn_scratch.as<float>(); a.counters = attn_counters.as<uint32_t>();
@@ -546,14 +569,10 @@ void Seq::prefill_chunk(int idx0, int T, int pos0, bool want_logits, cudaStream_
             a.scale = 1.0f / sqrtf((float)hp.head_dim);
             launch_attn_decode(a, st, false, (m->eng->flags & AIOS_ENGINE_ATTN_CLUSTER) ? 2 : 0);
         }
-        img = -1;
-        matmul(L.wo.w, ATT, QD, nullptr, X, E, EPI_ADD, img);
-        img = -1;
-        matmul(L.w_gate.w, X, E, L.ffn_norm.as<float>(), GU, 2 * FF, EPI_STORE, img);
-        matmul(L.w_up.w, X, E, L.ffn_norm.as<float>(), GU + FF, 2 * FF, EPI_STORE, img);
+        matmul({&L.wo.w}, {X}, ATT, QD, nullptr, E, EPI_ADD);
+        matmul({&L.w_gate.w, &L.w_up.w}, {GU, GU + FF}, X, E, L.ffn_norm.as<float>(), 2 * FF, EPI_STORE);
         launch_swiglu_rows(GU, 2 * FF, FF, T, H, FF, st);
-        img = -1;
-        matmul(L.w_down.w, H, FF, nullptr, X, E, EPI_ADD, img);
+        matmul({&L.w_down.w}, {X}, H, FF, nullptr, E, EPI_ADD);
     }
     if (want_logits) {
         CUDA_CHECK(cudaMemsetAsync(&sd->argmax_key, 0, sizeof(unsigned long long), st));
@@ -562,6 +581,7 @@ void Seq::prefill_chunk(int idx0, int T, int pos0, bool want_logits, cudaStream_
         p.seg[0] = m->output.w; p.out[0] = logits.as<float>();
         p.x = X + (size_t)(T - 1) * E; p.norm_w = m->output_norm.as<float>(); p.eps = hp.rms_eps;
         p.argmax_key = &sd->argmax_key;
+        p.evict_first = m->eng->evict_first ? 1 : 0;
         launch_gemv(p, gemv_plan_grid(p, n_sms), st, false);
     }
 }
@@ -572,6 +592,7 @@ int Seq::decode(const aios_sampling &sp, int max_tokens, int32_t *out) {
     const int steps = std::min(max_tokens, m->hp.n_ctx - n_past);
     if (steps <= 0) return 0;
     m->eng->make_current();
+    ensure_kv(n_past + steps);
     cudaStream_t st = m->eng->stream;
     const bool use_graph = !(m->eng->flags & AIOS_ENGINE_NO_GRAPH);
     int32_t hdr[2] = {n_past - 1, 0};  // pos, step
@@ -603,6 +624,7 @@ void Seq::bench_decode(int n_tokens, aios_bench_result *out) {
     const int steps = std::min(n_tokens, m->hp.n_ctx - n_past);
     if (steps <= 0) throw std::runtime_error("context is full");
     m->eng->make_current();
+    ensure_kv(n_past + steps);
     cudaStream_t st = m->eng->stream;
     aios_sampling sp{};  // greedy
     const bool fused = use_pfd(sp);
@@ -636,6 +658,7 @@ void Seq::profile_decode(int n_tokens, aios_bench_result *out) {
     const int steps = std::min(n_tokens, m->hp.n_ctx - n_past);
     if (steps <= 0) throw std::runtime_error("context is full");
     m->eng->make_current();
+    ensure_kv(n_past + steps);
     cudaStream_t st = m->eng->stream;
     aios_sampling sp{};
     int32_t hdr[2] = {n_past - 1, 0};
@@ -685,6 +708,7 @@ int Seq::trace_decode(unsigned long long *out, int cap_launches) {
     if (!have_logits) throw std::runtime_error("trace_decode needs a prefilled sequence");
     if (m->hp.n_ctx - n_past < 2) throw std::runtime_error("context is full");
     m->eng->make_current();
+    ensure_kv(n_past + 2);
     cudaStream_t st = m->eng->stream;
     aios_sampling sp{};
     int32_t hdr[2] = {n_past - 1, 0};
@@ -768,7 +792,7 @@ void Seq::build_pfd() {
         {
             PfdPhase P{};
             P.kind = PH_ATTN;
-            P.k_cache = m->k_cache(slot, il); P.v_cache = m->v_cache(slot, il);
+            P.k_cache = k_cache(il); P.v_cache = v_cache(il);
             ph.push_back(P);
         }
         gemv(L.wo.w, nullptr, xq, EPI_ADD, QD, nullptr, pfd_att_acc.as<double>(), nullptr, true, true, perm_bit(L.wo.w.type));
@@ -800,6 +824,7 @@ void Seq::build_pfd() {
     p.tok_embd_row_bytes = m->tok_embd_row_bytes; p.tok_embd_type = m->tok_embd_type; p.n_embd = hp.n_embd;
     p.rope_cos = m->rope_cos.as<float>(); p.rope_sin = m->rope_sin.as<float>();
     p.n_head = hp.n_head; p.n_kv = hp.n_head_kv; p.hd = hp.head_dim; p.n_rot = hp.n_rot;
+    p.kv_stride = (int32_t)m->kv_pos_elems();
     p.att_scale = 1.0f / sqrtf((float)hp.head_dim);
     const int n_sms = m->eng->n_sms;
     p.att_group = std::max(1, std::min(16, n_sms / hp.n_head_kv));

@@ -14,6 +14,7 @@
 #include "../../include/aios_b200.h"
 #include "gguf.h"
 #include "kernels.h"
+#include "kvpool.h"
 #include "layout.cuh"
 #include "pfd.h"
 
@@ -79,21 +80,22 @@ struct Model {
     DevMatrix output;     // output.weight (or the tied embedding) in planes layout
     DevBuf output_norm;
     DevBuf rope_cos, rope_sin;  // [n_ctx][n_rot/2], host-computed (glibc cosf/sinf, as the oracle)
-    // KV slots: max_batch for the caller's sequences (aios_seq_create, aios_generate) plus HIDDEN_SLOTS the library
-    // keeps for itself (aios_forward_logits' scratch sequence, the request scheduler's sequence), so that internal
-    // sequences never eat into the budget the caller was promised
-    static constexpr int HIDDEN_SLOTS = 2;
-    DevBuf kv;            // [max_batch + HIDDEN_SLOTS][n_layer][2][n_ctx][n_kv*hd] f16
-    std::vector<bool> slot_used;
+    // KV cache: a pool of physical pages; every sequence maps pages into its own virtual range (kvpool.h).
+    // The caller may hold max_batch sequences (aios_seq_create, aios_generate); the library's own sequences
+    // (aios_forward_logits' scratch, the request scheduler's batch lanes) are not counted against that budget.
+    KvPool kv_pool;
+    int user_seqs = 0;    // live caller-visible sequences (guarded by mu)
+    int live_seqs = 0;    // all live sequences (guarded by mu)
     int64_t weight_bytes = 0, weight_bytes_per_token = 0;
     std::mutex mu;
     int attn_splits = 16;
 
     Model(Engine *e, const std::string &name, const std::string &path, int n_ctx);
     ~Model();
-    uint16_t *k_cache(int slot, int layer) const;
-    uint16_t *v_cache(int slot, int layer) const;
-    size_t kv_layer_elems() const { return (size_t)hp.n_ctx * hp.n_head_kv * hp.head_dim; }
+    // position-major KV layout: [position][layer][K|V][n_kv*hd] f16
+    size_t kvd() const { return (size_t)hp.n_head_kv * hp.head_dim; }
+    size_t kv_pos_elems() const { return (size_t)hp.n_layer * 2 * kvd(); }   // f16 elements per position = row stride
+    size_t kv_pos_bytes() const { return kv_pos_elems() * 2; }
 
    private:
     void upload_matrix(const GgufTensor &t, DevMatrix &dst, DevBuf &staging, void *pinned, size_t pinned_bytes);
@@ -109,8 +111,12 @@ struct SeqState {  // lives in device memory
 
 struct Seq {
     Model *m;
-    int slot;
+    bool internal;   // one of the library's own sequences: KV pages are mapped as the position grows
+    KvSpace kv;      // this sequence's virtual KV range (caller-visible sequences map their whole context up front)
     int n_past = 0;  // host mirror: number of positions in the KV cache
+    uint16_t *k_cache(int layer) const { return kv.as<uint16_t>() + ((size_t)layer * 2 + 0) * m->kvd(); }
+    uint16_t *v_cache(int layer) const { return kv.as<uint16_t>() + ((size_t)layer * 2 + 1) * m->kvd(); }
+    void ensure_kv(int n_positions);  // back positions [0, n_positions) with pages
     bool have_logits = false;
     DevBuf state, x, qkv, att, h, logits, out_tokens, prompt, attn_scratch, attn_counters, snap_logits;
     int snap_n_past = -1;
@@ -154,6 +160,41 @@ struct Seq {
     void build_pfd();
     bool use_pfd(const aios_sampling &sp) const;
     void launch_pfd_tokens(int n, cudaStream_t st);
+};
+
+// ---------------------------------------------------------------- continuous batching (batch.cu)
+// Up to GEMM_MAX_TOKENS (64) sequences of one model decode together: one token per live lane per step, every weight
+// matrix streamed once per step by the multi-token GEMM (gemm_q.cu), attention per lane over the lane's own KV range,
+// one sampler CTA per lane.  The request scheduler (capi.cu) admits and retires lanes between steps.  All arithmetic
+// is the single-sequence path's, so a lane's tokens do not depend on what else is in the batch.
+struct Batch {
+    Model *m;
+    int n = 0;                          // live lanes: 0 .. n-1 (kept dense)
+    std::vector<std::unique_ptr<Seq>> seqs;  // lane i's sequence (KV range, prompt prefill); pooled, created on demand
+    std::vector<SampleLane> cfg;        // host mirror of the per-lane sampler parameters
+    DevBuf X, QKV, ATT, H, GU, LOGITS, IMG_A, IMG_B, POS, TOK, KVB, CFG, MASKS;
+    int32_t *h_tok = nullptr;           // pinned: the step's sampled tokens
+    int32_t *h_pos = nullptr;           // pinned staging for POS
+    void **h_kvb = nullptr;             // pinned staging for KVB
+    SampleLane *h_cfg = nullptr;        // pinned staging for CFG
+    bool dirty = true;                  // lane set / parameters changed: re-upload POS, KVB, CFG before the next step
+    std::vector<cudaGraphExec_t> graphs;  // captured step, indexed by n (lazily)
+    size_t mask_bytes = 0;
+
+    explicit Batch(Model *m);
+    ~Batch();
+    int capacity() const { return GEMM_MAX_TOKENS; }
+    // bring a request in: prefill its prompt into a pooled sequence, whose logits become lane n's row.  Returns the lane.
+    int admit(const int32_t *prompt, int n_prompt, const aios_sampling &sp);
+    void retire(int lane);              // the last lane moves into the hole
+    void set_mask(int lane, const uint8_t *bits);  // null: no mask; else n_vocab bits, copied
+    // one step: every live lane samples a token from its logits and feeds it.  Returns after the tokens are in h_tok.
+    void step();
+    int kernels_per_step = 0;
+
+   private:
+    void launch_step(cudaStream_t st, int *n_launch);
+    void upload_lane_state(cudaStream_t st);
 };
 
 }  // namespace aios

@@ -1,21 +1,26 @@
-// gemm_q.cu — multi-token dequant GEMM on the tensor cores: Y[T][N] = X[T][K] . dq(W[N][K])^T for T = 8..32 tokens
-// of one prompt chunk (prefill), weights streamed ONCE for all T tokens.
+// gemm_q.cu — multi-token dequant GEMM on the int8 tensor cores: Y[T][N] = X[T][K] . dq(W[N][K])^T for T = 1..64
+// tokens, weights streamed ONCE for all T tokens.  Two users:
+//   * batched decode — T = the live sequences of the continuous batcher, one token each (BASELINE.json configs[3]);
+//   * bit-exact prompt chunks — T consecutive tokens of one prompt.
 //
 // Same numbers as T calls of the GEMV (gemv.cu) — bit for bit.  The GEMV's arithmetic per 64-weight unit is
-//   term = fma(d * d8, sc_lo * dot(lo32, a) + sc_hi * dot(hi32, a'), -(dmin * d8) * (m_lo * bs + m_hi * bs'))
-// with INTEGER dots of 32 int8 pairs, and the terms are summed in double (order-free).  An integer dot does not care
-// how it is computed, so here the 32-wide dots come from `mma.sync.m16n8k32.s8` — one instruction = 16 weight rows x
-// 8 tokens x one 32-weight sub-block — and the scale arithmetic around them is the GEMV's, per (row, token) pair.
-// (Why not tcgen05 with TMEM accumulators: K-quant scales change every 32 weights, so the accumulator has to be read
-// out after every k = 32 step; a register accumulator is the natural home for that.  The integer MMA is what keeps
-// the result exact; a bf16/fp8 tensor-core path would not be bit-compatible with the decode path.)
+//   Q4_K  term = fma(d*d8, sc_lo*dot(lo32, a) + sc_hi*dot(hi32, a'), -(dmin*d8) * (m_lo*bs + m_hi*bs'))
+//   Q6_K  term = (d*d8) * sum_k sc_k * (dot(q_k16, a_k) - 32*bs_k)
+//   Q8_0  term = dot(q32, a) * (d*d8)                                    (unit = one 32-weight block)
+// with INTEGER dots, and the f32 terms are summed in double (order-free, rounded once).  An integer dot does not care
+// how it is computed, so here the sub-block dots come from `mma.sync` s8 — m16n8k32 for the 32-wide dots of Q4_K and
+// Q8_0, m16n8k16 for the 16-wide dots of Q6_K: one instruction = 16 weight rows x 8 tokens x one sub-block — and the
+// scale arithmetic around them is the GEMV's, per (row, token) pair.  This is why the path is exact and also why it is
+// ALU-bound rather than tensor-bound at T = 64: every (row, token, unit) costs ~12 scalar instructions after the MMA.
+// The tensor-bound path for long prompts is prefill_tc.cu (tcgen05, float arithmetic, stated tolerance).
 //
 // Activations: `quant_rows_kernel` builds, per token, the same Q8_K / Q8_0 image the GEMV prologue builds in shared
-// memory (gemv_core.cuh quant_slab, optional RMSNorm first) — in global memory, once per chunk, instead of once per
-// CTA.  The GEMM stages the images of all T tokens block by block (256 weights) through shared memory.
+// memory (gemv_core.cuh quant_slab, optional RMSNorm first) — in global memory, once per launch group, instead of once
+// per CTA.  The GEMM stages the images of all T tokens block by block (256 weights) through shared memory.
 //
-// Q4_K and Q8_0 weights (sub-blocks of 32).  Q6_K (sub-blocks of 16) is not built yet: the engine runs those
-// matrices token by token through the GEMV.
+// A CTA owns 32 weight rows (two m16 row groups) of ONE segment and all T tokens: warp (rg, tg) takes row group rg and
+// token group tg (8*NT tokens).  Matrices that share an input ride in one launch as segments (q/k/v — also when
+// attn_v is Q6_K next to Q4_K q/k — and gate/up): the type is CTA-uniform.
 #define GEMV_CORE_WARPS 8
 #include "gemv_core.cuh"
 
@@ -44,118 +49,147 @@ void launch_quant_rows(int weight_type, const float *x, int64_t ldx, const float
 size_t gemm_images_bytes(int k, int T) { return gemm_image_stride(k) * (size_t)T; }
 
 // ---------------------------------------------------------------- the GEMM
-constexpr int GEMM_WARPS = 2, GEMM_THREADS = GEMM_WARPS * 32, GEMM_ROWS = GEMM_WARPS * 16;
-constexpr int GEMM_TOK_STRIDE = 17;  // uint4 per token in the staged chunk: 16 used + 1 pad (bank spread over tokens)
+constexpr int GEMM_RG = 2;                  // m16 row groups per CTA
+constexpr int GEMM_ROWS = GEMM_RG * 16;     // weight rows per CTA
+constexpr int GEMM_TOK_STRIDE = 17;         // uint4 per token in the staged block: 16 used + 1 pad (bank spread over tokens)
+constexpr int GEMM_STAGES = 3;
 
-__device__ __forceinline__ void mma_s8(int (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
+__device__ __forceinline__ void mma_s8_k32(int (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
     asm volatile(
         "mma.sync.aligned.m16n8k32.row.col.s32.s8.s8.s32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%10,%10,%10,%10};"
         : "=r"(c[0]), "=r"(c[1]), "=r"(c[2]), "=r"(c[3])
         : "r"(a0), "r"(a1), "r"(a2), "r"(a3), "r"(b0), "r"(b1), "r"(0));
 }
+__device__ __forceinline__ void mma_s8_k16(int (&c)[4], uint32_t a0, uint32_t a1, uint32_t b0) {
+    asm volatile(
+        "mma.sync.aligned.m16n8k16.row.col.s32.s8.s8.s32 {%0,%1,%2,%3}, {%4,%5}, {%6}, {%7,%7,%7,%7};"
+        : "=r"(c[0]), "=r"(c[1]), "=r"(c[2]), "=r"(c[3])
+        : "r"(a0), "r"(a1), "r"(b0), "r"(0));
+}
 __device__ __forceinline__ void cp16(void *smem_dst, const void *gsrc) {
     const uint32_t d = (uint32_t)__cvta_generic_to_shared(smem_dst);
     asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(d), "l"(gsrc) : "memory");
 }
+__device__ __forceinline__ void cp4(void *smem_dst, const void *gsrc) {
+    const uint32_t d = (uint32_t)__cvta_generic_to_shared(smem_dst);
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d), "l"(gsrc) : "memory");
+}
 
-struct GemmSmem {  // one staged 256-weight block of all T token images
-    uint4 *act;    // [T][GEMM_TOK_STRIDE]
-    int32_t *bs;   // Q4_K: [T][8] 32-wide q8 sums
-    float *d8;     // Q4_K: [T] ; Q8_0: [T][8]
+// one staged 256-weight block of all T token images
+//   act [T][GEMM_TOK_STRIDE] uint4 : Q4_K / Q6_K: entry 4u+kk = activation bytes a_kk of unit u; Q8_0: entry 2u+kk
+//   aux [T][32] bytes              : Q4_K: 8 x i32 32-wide q8 sums; Q6_K: 16 x i16 16-wide sums; Q8_0: 8 x f32 d8
+//   d8  [T] f32                    : Q4_K / Q6_K block scale
+__host__ __device__ inline size_t gemm_img_bytes(int T) { return (size_t)T * (GEMM_TOK_STRIDE * 16 + 32 + 4); }
+struct ImgSmem {
+    uint4 *act;
+    uint8_t *aux;
+    float *d8;
 };
-__host__ __device__ inline size_t gemm_chunk_bytes(int T) { return (size_t)T * (GEMM_TOK_STRIDE * 16 + 32 + 32); }
-__device__ __forceinline__ GemmSmem gemm_carve(uint8_t *base, int T) {
-    GemmSmem s;
+__device__ __forceinline__ ImgSmem img_carve(uint8_t *base, int T) {
+    ImgSmem s;
     s.act = reinterpret_cast<uint4 *>(base);
-    s.bs = reinterpret_cast<int32_t *>(base + (size_t)T * GEMM_TOK_STRIDE * 16);
+    s.aux = base + (size_t)T * GEMM_TOK_STRIDE * 16;
     s.d8 = reinterpret_cast<float *>(base + (size_t)T * (GEMM_TOK_STRIDE * 16 + 32));
     return s;
 }
 
 // copy block b of every token's image into a staging buffer (cp.async, all threads)
 template <int TYPE>
-__device__ __forceinline__ void gemm_stage(const GemmSmem &s, const uint8_t *images, size_t img_stride, int k, int T, int b) {
+__device__ __forceinline__ void stage_images(const ImgSmem &s, const uint8_t *images, size_t img_stride, int k, int T, int b, int nthreads) {
     const int U = TYPE == T_Q8_0 ? k / 32 : k / 64;
-    for (int idx = threadIdx.x; idx < T * 16; idx += GEMM_THREADS) {
+    for (int idx = threadIdx.x; idx < T * 16; idx += nthreads) {
         const int t = idx >> 4, e = idx & 15;
         const uint4 *act = reinterpret_cast<const uint4 *>(images + (size_t)t * img_stride);
         const uint4 *src = TYPE == T_Q8_0 ? act + (size_t)(e & 1) * U + 8 * b + (e >> 1)   // [blk][kk]
                                           : act + (size_t)(e & 3) * U + 4 * b + (e >> 2);  // [unit][kk]
         cp16(s.act + t * GEMM_TOK_STRIDE + e, src);
     }
-    for (int idx = threadIdx.x; idx < T * 2; idx += GEMM_THREADS) {
+    for (int idx = threadIdx.x; idx < T * 2; idx += nthreads) {
         const int t = idx >> 1, h = idx & 1;
         const uint8_t *aux = images + (size_t)t * img_stride + k;
-        if (TYPE == T_Q8_0) cp16(s.d8 + t * 8 + h * 4, aux + k / 8 + (size_t)(8 * b + h * 4) * 4);
-        else cp16(s.bs + t * 8 + h * 4, aux + (size_t)(8 * b + h * 4) * 4);
+        // Q8_0: eight f32 block scales (behind the k/8 aux bytes); K-quants: the block's 32 bytes of sub-block sums
+        if (TYPE == T_Q8_0) cp16(s.aux + t * 32 + h * 16, aux + k / 8 + (size_t)(8 * b + h * 4) * 4);
+        else cp16(s.aux + t * 32 + h * 16, aux + (size_t)b * 32 + h * 16);
     }
     if (TYPE != T_Q8_0) {
-        for (int t = threadIdx.x; t < T; t += GEMM_THREADS) {
+        for (int t = threadIdx.x; t < T; t += nthreads) {
             const uint8_t *aux = images + (size_t)t * img_stride + k;
-            const uint32_t d = (uint32_t)__cvta_generic_to_shared(s.d8 + t);
-            asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d), "l"(aux + k / 8 + (size_t)b * 4) : "memory");
+            cp4(s.d8 + t, aux + k / 8 + (size_t)b * 4);
         }
     }
-    asm volatile("cp.async.commit_group;" ::: "memory");
 }
-
-struct GemmParams {
-    WPlanes w;
-    const uint8_t *images;  // T activation images (quant_rows_kernel), stride gemm_image_stride(k)
-    float *out;             // [T][ldo]
-    int64_t ldo;
-    int32_t T, epi;         // epi: EPI_STORE or EPI_ADD
-};
 
 // Weight side of a stage: the 256-weight block b of GEMM_ROWS rows, copied plane by plane with 16-byte cp.async
 // (a row's bytes of one block are contiguous inside a plane), padded per row so that the fragment reads of the eight
 // row groups of a warp fall into different banks.
 //   Q4_K: qa[rows][5] uint4 (4 units + pad) | qb[rows][5] | meta[rows] uint4
-//   Q8_0: qa[rows][9] uint4 (8 blocks + pad) | qb[rows][9] | d[rows][8] f16
-template <int TYPE> struct GemmA;
-template <> struct GemmA<T_Q4_K> {
-    static constexpr int RS = 5;
-    static constexpr size_t bytes = (size_t)GEMM_ROWS * (2 * RS + 1) * 16;
-};
-template <> struct GemmA<T_Q8_0> {
-    static constexpr int RS = 9;
-    static constexpr size_t bytes = (size_t)GEMM_ROWS * (2 * RS + 1) * 16;
-};
+//   Q8_0: qa[rows][9] uint4 (8 blocks + pad) | qb[rows][9] | d[rows] uint4 (8 x f16)
+//   Q6_K: la[rows][5] | lb[rows][5] | hh[rows][5] | sc[rows] uint4 (4 units x 4 i8) | d[rows] u32 (the aligned word
+//         holding the f16 block scale)
+template <int TYPE> struct TileA;
+template <> struct TileA<T_Q4_K> { static constexpr int RS = 5; static constexpr size_t bytes = (size_t)GEMM_ROWS * (2 * RS + 1) * 16; };
+template <> struct TileA<T_Q8_0> { static constexpr int RS = 9; static constexpr size_t bytes = (size_t)GEMM_ROWS * (2 * RS + 1) * 16; };
+template <> struct TileA<T_Q6_K> { static constexpr int RS = 5; static constexpr size_t bytes = (size_t)GEMM_ROWS * (3 * RS + 1) * 16 + GEMM_ROWS * 4; };
+constexpr size_t GEMM_A_BYTES = TileA<T_Q8_0>::bytes;  // the largest: one stage layout for every type
+static_assert(TileA<T_Q6_K>::bytes <= GEMM_A_BYTES && TileA<T_Q4_K>::bytes <= GEMM_A_BYTES, "stage layout");
 
 template <int TYPE>
-__device__ __forceinline__ void gemm_stage_a(uint8_t *sa, const WPlanes &w, int row0, int b) {
-    constexpr int RS = GemmA<TYPE>::RS, UPB = TYPE == T_Q8_0 ? 8 : 4;  // units (blocks of 32) per 256-weight block
+__device__ __forceinline__ void stage_weights(uint8_t *sa, const WPlanes &w, int row0, int b, int nthreads) {
+    constexpr int RS = TileA<TYPE>::RS, UPB = TYPE == T_Q8_0 ? 8 : 4;  // units per 256-weight block
     const size_t U = (size_t)w.k / (TYPE == T_Q8_0 ? 32 : 64), nb = (size_t)w.k / 256;
-    uint4 *qa = reinterpret_cast<uint4 *>(sa), *qb = qa + GEMM_ROWS * RS, *ex = qb + GEMM_ROWS * RS;
-    for (int idx = threadIdx.x; idx < GEMM_ROWS * UPB; idx += GEMM_THREADS) {
+    uint4 *p0 = reinterpret_cast<uint4 *>(sa), *p1 = p0 + GEMM_ROWS * RS;
+    for (int idx = threadIdx.x; idx < GEMM_ROWS * UPB; idx += nthreads) {
         const int r = idx / UPB, u = idx % UPB;
         const size_t row = (size_t)min(row0 + r, w.n_rows - 1);
-        cp16(qa + r * RS + u, w.p[0] + (row * U + (size_t)UPB * b + u) * 16);
-        cp16(qb + r * RS + u, w.p[1] + (row * U + (size_t)UPB * b + u) * 16);
+        cp16(p0 + r * RS + u, w.p[0] + (row * U + (size_t)UPB * b + u) * 16);
+        cp16(p1 + r * RS + u, w.p[1] + (row * U + (size_t)UPB * b + u) * 16);
+        if (TYPE == T_Q6_K) cp16(p1 + GEMM_ROWS * RS + r * RS + u, w.p[2] + (row * U + (size_t)UPB * b + u) * 16);
     }
-    for (int r = threadIdx.x; r < GEMM_ROWS; r += GEMM_THREADS) {
-        const size_t row = (size_t)min(row0 + r, w.n_rows - 1);
-        if (TYPE == T_Q8_0) cp16(ex + r, w.p[2] + (row * U + (size_t)8 * b) * 2);   // eight f16 scales = 16 bytes
-        else cp16(ex + r, w.p[2] + (row * nb + b) * 16);                            // META of the block
+    if (TYPE == T_Q6_K) {
+        uint4 *sc = p1 + 2 * GEMM_ROWS * RS;
+        uint32_t *dd = reinterpret_cast<uint32_t *>(sc + GEMM_ROWS);
+        for (int r = threadIdx.x; r < GEMM_ROWS; r += nthreads) {
+            const size_t row = (size_t)min(row0 + r, w.n_rows - 1);
+            cp16(sc + r, w.p[3] + (row * U + (size_t)4 * b) * 4);   // 4 units x 4 scales
+            // the f16 block scale: 2 bytes at a 2-byte-aligned address -> copy the aligned 4-byte word that holds it
+            const uintptr_t dsrc = reinterpret_cast<uintptr_t>(w.p[4] + (row * nb + b) * 2);
+            cp4(dd + r, reinterpret_cast<const void *>(dsrc & ~(uintptr_t)3));
+        }
+    } else {
+        uint4 *ex = p1 + GEMM_ROWS * RS;
+        for (int r = threadIdx.x; r < GEMM_ROWS; r += nthreads) {
+            const size_t row = (size_t)min(row0 + r, w.n_rows - 1);
+            if (TYPE == T_Q8_0) cp16(ex + r, w.p[2] + (row * U + (size_t)8 * b) * 2);   // eight f16 scales = 16 bytes
+            else cp16(ex + r, w.p[2] + (row * nb + b) * 16);                            // META of the block
+        }
     }
 }
 
-// grid = ceil(N / GEMM_ROWS); warp w of a CTA owns rows [GEMM_ROWS*cta + 16*w, +16) for the whole K and all T = 8*NT
-// tokens.  Thread (g = lane/4, q = lane%4) ends up with the sums of rows g and g+8 for tokens 8j+2q, 8j+2q+1, j < NT.
-// Three-stage cp.async pipeline over the 256-weight blocks of K: weights and activation images of block b+2 are in
-// flight while block b is multiplied.
-template <int TYPE, int NT>
-__global__ void __launch_bounds__(GEMM_THREADS) gemm_q_kernel(const GemmParams p) {
-    extern __shared__ __align__(16) uint8_t smem[];
-    constexpr int T = 8 * NT, RS = GemmA<TYPE>::RS, STAGES = 3;
-    const size_t stage_bytes = GemmA<TYPE>::bytes + gemm_chunk_bytes(T);
+struct GemmParams {
+    int32_t n_seg;           // 1..3 matrices sharing the same input tokens
+    int32_t T, epi;          // epi: EPI_STORE or EPI_ADD
+    int32_t tile_begin[4];   // segment i owns CTAs [tile_begin[i], tile_begin[i+1])
+    WPlanes seg[3];
+    float *out[3];           // [T][ldo]
+    const uint8_t *images[3];  // T activation images in the permutation of the segment's type, stride gemm_image_stride(k)
+    int64_t ldo;
+};
+
+// the k-loop of one CTA for weight type TYPE
+template <int TYPE, int NT, int TW>
+__device__ __forceinline__ void gemm_body(const GemmParams &p, int seg, uint8_t *smem) {
+    constexpr int T = 8 * NT * TW, RS = TileA<TYPE>::RS, NTHREADS = GEMM_RG * TW * 32;
+    const size_t stage_bytes = GEMM_A_BYTES + gemm_img_bytes(T);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int rg = warp % GEMM_RG, tg = warp / GEMM_RG;
     const int g = lane >> 2, q = lane & 3;
-    const int k = p.w.k, N = p.w.n_rows;
+    const WPlanes &W = p.seg[seg];
+    const int k = W.k, N = W.n_rows;
     const int nb = k / 256;
     const size_t img_stride = gemm_image_stride(k);
-    const int row0 = blockIdx.x * GEMM_ROWS;
-    const int ra = warp * 16 + g, rb = ra + 8;  // my two rows inside the CTA's tile
+    const int row0 = ((int)blockIdx.x - p.tile_begin[seg]) * GEMM_ROWS;
+    const int ra = rg * 16 + g, rb = ra + 8;  // my two rows inside the CTA's tile
+    const int tok0 = tg * 8 * NT;             // first token of my token group
 
     double acc[NT][4];
 #pragma unroll
@@ -164,9 +198,10 @@ __global__ void __launch_bounds__(GEMM_THREADS) gemm_q_kernel(const GemmParams p
         for (int e = 0; e < 4; e++) acc[j][e] = 0.0;
 
     auto stage = [&](int b) {
-        uint8_t *base = smem + (size_t)(b % STAGES) * stage_bytes;
-        gemm_stage_a<TYPE>(base, p.w, row0, b);
-        gemm_stage<TYPE>(gemm_carve(base + GemmA<TYPE>::bytes, T), p.images, img_stride, k, T, b);  // commits the group
+        uint8_t *base = smem + (size_t)(b % GEMM_STAGES) * stage_bytes;
+        stage_weights<TYPE>(base, W, row0, b, NTHREADS);
+        stage_images<TYPE>(img_carve(base + GEMM_A_BYTES, T), p.images[seg], img_stride, k, T, b, NTHREADS);
+        asm volatile("cp.async.commit_group;" ::: "memory");
     };
     stage(0);
     if (nb > 1) stage(1);
@@ -180,31 +215,35 @@ __global__ void __launch_bounds__(GEMM_THREADS) gemm_q_kernel(const GemmParams p
             asm volatile("cp.async.wait_group 0;" ::: "memory");
         }
         __syncthreads();
-        const uint8_t *base = smem + (size_t)(b % STAGES) * stage_bytes;
-        const uint4 *qa = reinterpret_cast<const uint4 *>(base), *qb = qa + GEMM_ROWS * RS, *ex = qb + GEMM_ROWS * RS;
-        const GemmSmem s = gemm_carve(const_cast<uint8_t *>(base) + GemmA<TYPE>::bytes, T);
+        const uint8_t *base = smem + (size_t)(b % GEMM_STAGES) * stage_bytes;
+        const uint4 *p0 = reinterpret_cast<const uint4 *>(base), *p1 = p0 + GEMM_ROWS * RS;
+        const ImgSmem s = img_carve(const_cast<uint8_t *>(base) + GEMM_A_BYTES, T);
         if (TYPE == T_Q8_0) {
+            const uint4 *ex = p1 + GEMM_ROWS * RS;
             const __half *dha = reinterpret_cast<const __half *>(ex + ra), *dhb = reinterpret_cast<const __half *>(ex + rb);
 #pragma unroll 2
             for (int u = 0; u < 8; u++) {
-                const uint32_t a0 = reinterpret_cast<const uint32_t *>(qa + ra * RS + u)[q];
-                const uint32_t a1 = reinterpret_cast<const uint32_t *>(qa + rb * RS + u)[q];
-                const uint32_t a2 = reinterpret_cast<const uint32_t *>(qb + ra * RS + u)[q];
-                const uint32_t a3 = reinterpret_cast<const uint32_t *>(qb + rb * RS + u)[q];
+                const uint32_t a0 = reinterpret_cast<const uint32_t *>(p0 + ra * RS + u)[q];
+                const uint32_t a1 = reinterpret_cast<const uint32_t *>(p0 + rb * RS + u)[q];
+                const uint32_t a2 = reinterpret_cast<const uint32_t *>(p1 + ra * RS + u)[q];
+                const uint32_t a3 = reinterpret_cast<const uint32_t *>(p1 + rb * RS + u)[q];
                 const float dwa = __half2float(dha[u]), dwb = __half2float(dhb[u]);
 #pragma unroll
                 for (int j = 0; j < NT; j++) {
-                    const uint32_t *bt = reinterpret_cast<const uint32_t *>(s.act + (8 * j + g) * GEMM_TOK_STRIDE + u * 2);
+                    const int tb = tok0 + 8 * j;
+                    const uint32_t *bt = reinterpret_cast<const uint32_t *>(s.act + (tb + g) * GEMM_TOK_STRIDE + u * 2);
                     int c[4];
-                    mma_s8(c, a0, a1, a2, a3, bt[q], bt[4 + q]);
-                    const float d0 = s.d8[(8 * j + 2 * q) * 8 + u], d1 = s.d8[(8 * j + 2 * q + 1) * 8 + u];
+                    mma_s8_k32(c, a0, a1, a2, a3, bt[q], bt[4 + q]);
+                    const float d0 = reinterpret_cast<const float *>(s.aux + (tb + 2 * q) * 32)[u];
+                    const float d1 = reinterpret_cast<const float *>(s.aux + (tb + 2 * q + 1) * 32)[u];
                     acc[j][0] += (double)__fmul_rn((float)c[0], __fmul_rn(dwa, d0));
                     acc[j][1] += (double)__fmul_rn((float)c[1], __fmul_rn(dwa, d1));
                     acc[j][2] += (double)__fmul_rn((float)c[2], __fmul_rn(dwb, d0));
                     acc[j][3] += (double)__fmul_rn((float)c[3], __fmul_rn(dwb, d1));
                 }
             }
-        } else {  // Q4_K
+        } else if (TYPE == T_Q4_K) {
+            const uint4 *ex = p1 + GEMM_ROWS * RS;
             const uint4 mta = ex[ra], mtb = ex[rb];
             const uint32_t dda = __byte_perm(__byte_perm(mta.x, mta.y, 0x0073), __byte_perm(mta.z, mta.w, 0x0073), 0x5410);
             const uint32_t ddb = __byte_perm(__byte_perm(mtb.x, mtb.y, 0x0073), __byte_perm(mtb.z, mtb.w, 0x0073), 0x5410);
@@ -213,23 +252,24 @@ __global__ void __launch_bounds__(GEMM_THREADS) gemm_q_kernel(const GemmParams p
             const uint32_t mwa[4] = {mta.x, mta.y, mta.z, mta.w}, mwb[4] = {mtb.x, mtb.y, mtb.z, mtb.w};
 #pragma unroll
             for (int u = 0; u < 4; u++) {
-                const uint32_t qa0 = reinterpret_cast<const uint32_t *>(qa + ra * RS + u)[q];
-                const uint32_t qa1 = reinterpret_cast<const uint32_t *>(qa + rb * RS + u)[q];
-                const uint32_t qb0 = reinterpret_cast<const uint32_t *>(qb + ra * RS + u)[q];
-                const uint32_t qb1 = reinterpret_cast<const uint32_t *>(qb + rb * RS + u)[q];
+                const uint32_t qa0 = reinterpret_cast<const uint32_t *>(p0 + ra * RS + u)[q];
+                const uint32_t qa1 = reinterpret_cast<const uint32_t *>(p0 + rb * RS + u)[q];
+                const uint32_t qb0 = reinterpret_cast<const uint32_t *>(p1 + ra * RS + u)[q];
+                const uint32_t qb1 = reinterpret_cast<const uint32_t *>(p1 + rb * RS + u)[q];
                 const int sa_lo = mwa[u] & 63, sa_hi = (mwa[u] >> 6) & 63, ma_lo = (mwa[u] >> 12) & 63, ma_hi = (mwa[u] >> 18) & 63;
                 const int sb_lo = mwb[u] & 63, sb_hi = (mwb[u] >> 6) & 63, mb_lo = (mwb[u] >> 12) & 63, mb_hi = (mwb[u] >> 18) & 63;
 #pragma unroll
                 for (int j = 0; j < NT; j++) {
-                    const uint32_t *bt = reinterpret_cast<const uint32_t *>(s.act + (8 * j + g) * GEMM_TOK_STRIDE + u * 4);
+                    const int tb = tok0 + 8 * j;
+                    const uint32_t *bt = reinterpret_cast<const uint32_t *>(s.act + (tb + g) * GEMM_TOK_STRIDE + u * 4);
                     int lo[4], hi[4];
-                    mma_s8(lo, qa0 & 0x0F0F0F0Fu, qa1 & 0x0F0F0F0Fu, qb0 & 0x0F0F0F0Fu, qb1 & 0x0F0F0F0Fu, bt[q], bt[4 + q]);
-                    mma_s8(hi, (qa0 >> 4) & 0x0F0F0F0Fu, (qa1 >> 4) & 0x0F0F0F0Fu, (qb0 >> 4) & 0x0F0F0F0Fu,
-                           (qb1 >> 4) & 0x0F0F0F0Fu, bt[8 + q], bt[12 + q]);
+                    mma_s8_k32(lo, qa0 & 0x0F0F0F0Fu, qa1 & 0x0F0F0F0Fu, qb0 & 0x0F0F0F0Fu, qb1 & 0x0F0F0F0Fu, bt[q], bt[4 + q]);
+                    mma_s8_k32(hi, (qa0 >> 4) & 0x0F0F0F0Fu, (qa1 >> 4) & 0x0F0F0F0Fu, (qb0 >> 4) & 0x0F0F0F0Fu,
+                               (qb1 >> 4) & 0x0F0F0F0Fu, bt[8 + q], bt[12 + q]);
 #pragma unroll
                     for (int e = 0; e < 2; e++) {  // my two tokens of this n-block
-                        const int t = 8 * j + 2 * q + e;
-                        const int2 bs = *reinterpret_cast<const int2 *>(s.bs + t * 8 + 2 * u);
+                        const int t = tb + 2 * q + e;
+                        const int2 bs = *reinterpret_cast<const int2 *>(s.aux + t * 32 + u * 8);
                         const float d8 = s.d8[t];
                         const int isa = sa_lo * lo[e] + sa_hi * hi[e], msa = ma_lo * bs.x + ma_hi * bs.y;
                         const int isb = sb_lo * lo[2 + e] + sb_hi * hi[2 + e], msb = mb_lo * bs.x + mb_hi * bs.y;
@@ -238,25 +278,88 @@ __global__ void __launch_bounds__(GEMM_THREADS) gemm_q_kernel(const GemmParams p
                     }
                 }
             }
+        } else {  // Q6_K
+            const uint4 *p2 = p1 + GEMM_ROWS * RS;
+            const uint4 *sc = p2 + GEMM_ROWS * RS;
+            const uint32_t *dd = reinterpret_cast<const uint32_t *>(sc + GEMM_ROWS);
+            // the block scale sits in the low or the high half of its aligned word
+            const uintptr_t da_addr = reinterpret_cast<uintptr_t>(W.p[4]) + ((size_t)min(row0 + ra, N - 1) * nb + b) * 2;
+            const uintptr_t db_addr = reinterpret_cast<uintptr_t>(W.p[4]) + ((size_t)min(row0 + rb, N - 1) * nb + b) * 2;
+            const float dwa = h2f_bits((uint16_t)(dd[ra] >> (8 * (da_addr & 2))));
+            const float dwb = h2f_bits((uint16_t)(dd[rb] >> (8 * (db_addr & 2))));
+            const uint32_t *sca = reinterpret_cast<const uint32_t *>(sc + ra), *scb = reinterpret_cast<const uint32_t *>(sc + rb);
+#pragma unroll
+            for (int u = 0; u < 4; u++) {
+                const uint32_t la_a = reinterpret_cast<const uint32_t *>(p0 + ra * RS + u)[q], la_b = reinterpret_cast<const uint32_t *>(p0 + rb * RS + u)[q];
+                const uint32_t lb_a = reinterpret_cast<const uint32_t *>(p1 + ra * RS + u)[q], lb_b = reinterpret_cast<const uint32_t *>(p1 + rb * RS + u)[q];
+                const uint32_t hh_a = reinterpret_cast<const uint32_t *>(p2 + ra * RS + u)[q], hh_b = reinterpret_cast<const uint32_t *>(p2 + rb * RS + u)[q];
+                uint32_t qa[4], qb[4];  // the four 16-weight sub-blocks of the unit (6-bit values, 0..63)
+                qa[0] = (la_a & 0x0F0F0F0Fu) | ((hh_a << 4) & 0x30303030u);
+                qa[1] = (lb_a & 0x0F0F0F0Fu) | ((hh_a << 2) & 0x30303030u);
+                qa[2] = ((la_a >> 4) & 0x0F0F0F0Fu) | (hh_a & 0x30303030u);
+                qa[3] = ((lb_a >> 4) & 0x0F0F0F0Fu) | ((hh_a >> 2) & 0x30303030u);
+                qb[0] = (la_b & 0x0F0F0F0Fu) | ((hh_b << 4) & 0x30303030u);
+                qb[1] = (lb_b & 0x0F0F0F0Fu) | ((hh_b << 2) & 0x30303030u);
+                qb[2] = ((la_b >> 4) & 0x0F0F0F0Fu) | (hh_b & 0x30303030u);
+                qb[3] = ((lb_b >> 4) & 0x0F0F0F0Fu) | ((hh_b >> 2) & 0x30303030u);
+                const uint32_t swa = sca[u], swb = scb[u];
+                int sa[4], sb[4];
+#pragma unroll
+                for (int kk = 0; kk < 4; kk++) {
+                    sa[kk] = (int)(int8_t)((swa >> (8 * kk)) & 0xff);
+                    sb[kk] = (int)(int8_t)((swb >> (8 * kk)) & 0xff);
+                }
+#pragma unroll
+                for (int j = 0; j < NT; j++) {
+                    const int tb = tok0 + 8 * j;
+                    const uint32_t *bt = reinterpret_cast<const uint32_t *>(s.act + (tb + g) * GEMM_TOK_STRIDE + u * 4);
+                    int dk[4][4];
+#pragma unroll
+                    for (int kk = 0; kk < 4; kk++) mma_s8_k16(dk[kk], qa[kk], qb[kk], bt[4 * kk + q]);
+#pragma unroll
+                    for (int e = 0; e < 2; e++) {
+                        const int t = tb + 2 * q + e;
+                        const uint2 bsp = *reinterpret_cast<const uint2 *>(s.aux + t * 32 + u * 8);  // four i16 16-wide sums
+                        const int b0 = (int)(int16_t)(bsp.x & 0xffff), b1 = (int)(int16_t)(bsp.x >> 16);
+                        const int b2 = (int)(int16_t)(bsp.y & 0xffff), b3 = (int)(int16_t)(bsp.y >> 16);
+                        const float d8 = s.d8[t];
+                        const int isa = sa[0] * (dk[0][e] - 32 * b0) + sa[1] * (dk[1][e] - 32 * b1) + sa[2] * (dk[2][e] - 32 * b2) + sa[3] * (dk[3][e] - 32 * b3);
+                        const int isb = sb[0] * (dk[0][2 + e] - 32 * b0) + sb[1] * (dk[1][2 + e] - 32 * b1) + sb[2] * (dk[2][2 + e] - 32 * b2) + sb[3] * (dk[3][2 + e] - 32 * b3);
+                        acc[j][e] += (double)__fmul_rn(__fmul_rn(dwa, d8), (float)isa);
+                        acc[j][2 + e] += (double)__fmul_rn(__fmul_rn(dwb, d8), (float)isb);
+                    }
+                }
+            }
         }
         __syncthreads();  // everyone is done with this stage before it is refilled
     }
     const int row_a = row0 + ra, row_b = row0 + rb;
+    float *out = p.out[seg];
 #pragma unroll
     for (int j = 0; j < NT; j++)
 #pragma unroll
         for (int e = 0; e < 4; e++) {
-            const int row = (e & 2) ? row_b : row_a, t = 8 * j + 2 * q + (e & 1);
+            const int row = (e & 2) ? row_b : row_a, t = tok0 + 8 * j + 2 * q + (e & 1);
             if (row < N && t < p.T) {
-                float *o = p.out + (size_t)t * p.ldo + row;
+                float *o = out + (size_t)t * p.ldo + row;
                 const float v = (float)acc[j][e];
                 *o = p.epi == EPI_ADD ? __fadd_rn(*o, v) : v;
             }
         }
 }
 
-template <int TYPE>
-static size_t gemm_smem_bytes(int T) { return 3 * (GemmA<TYPE>::bytes + gemm_chunk_bytes(T)); }
+template <int NT, int TW>
+__global__ void __launch_bounds__(GEMM_RG * TW * 32) gemm_q_kernel(const GemmParams p) {
+    extern __shared__ __align__(16) uint8_t smem[];
+    int seg = 0;
+    while (seg + 1 < p.n_seg && (int)blockIdx.x >= p.tile_begin[seg + 1]) seg++;
+    const int type = p.seg[seg].type;  // CTA-uniform
+    if (type == T_Q4_K) gemm_body<T_Q4_K, NT, TW>(p, seg, smem);
+    else if (type == T_Q6_K) gemm_body<T_Q6_K, NT, TW>(p, seg, smem);
+    else gemm_body<T_Q8_0, NT, TW>(p, seg, smem);
+}
+
+static size_t gemm_smem_bytes(int T) { return GEMM_STAGES * (GEMM_A_BYTES + gemm_img_bytes(T)); }
 
 // h[t][i] = silu(gate[t][i]) * up[t][i] for a chunk: gu[t] = gate[ff] | up[ff].  Same expression, operation by
 // operation, as the GEMV's fused SwiGLU epilogue.
@@ -273,30 +376,49 @@ void launch_swiglu_rows(const float *gu, int64_t ldgu, int ff, int T, float *h, 
     CUDA_CHECK(cudaGetLastError());
 }
 
-bool gemm_q_usable(int type, int k) { return (type == T_Q4_K || type == T_Q8_0) && k % 256 == 0; }
+bool gemm_q_usable(int type, int k) { return (type == T_Q4_K || type == T_Q6_K || type == T_Q8_0) && k % 256 == 0; }
 
-// T in 1..32: the images of tokens T..8*NT-1 (padding) must exist (any finite contents); their outputs are not stored.
-void launch_gemm_q(const WPlanes &w, const uint8_t *images, int T, float *out, int64_t ldo, int epi, cudaStream_t st) {
-    if (!gemm_q_usable(w.type, w.k)) throw CudaError("launch_gemm_q: only Q4_K / Q8_0 weights");
-    if (T < 1 || T > 32) throw CudaError("launch_gemm_q: 1..32 tokens per call");
+// images of tokens T..pad(T)-1 (padding) must exist (any finite contents); their outputs are not stored.
+int gemm_pad_tokens(int T) { return T <= 32 ? (T + 7) / 8 * 8 : GEMM_MAX_TOKENS; }
+
+void launch_gemm_multi(const GemmMulti &m, cudaStream_t st) {
+    if (m.T < 1 || m.T > GEMM_MAX_TOKENS) throw CudaError("launch_gemm: 1..64 tokens per call");
+    if (m.n_seg < 1 || m.n_seg > 3) throw CudaError("launch_gemm: 1..3 segments");
     GemmParams p{};
-    p.w = w; p.images = images; p.out = out; p.ldo = ldo; p.T = T; p.epi = epi;
-    const int nt = (T + 7) / 8;
-    const dim3 grid((w.n_rows + GEMM_ROWS - 1) / GEMM_ROWS);
-    const size_t smem = w.type == T_Q4_K ? gemm_smem_bytes<T_Q4_K>(8 * nt) : gemm_smem_bytes<T_Q8_0>(8 * nt);
-#define GEMM_LAUNCH(TY, NTV)                                                                                          \
+    p.n_seg = m.n_seg; p.T = m.T; p.epi = m.epi; p.ldo = m.ldo;
+    int tiles = 0;
+    for (int i = 0; i < m.n_seg; i++) {
+        if (!gemm_q_usable(m.seg[i].type, m.seg[i].k)) throw CudaError("launch_gemm: Q4_K / Q6_K / Q8_0 weights only");
+        if (m.seg[i].k != m.seg[0].k) throw CudaError("launch_gemm: segments must share K");
+        p.seg[i] = m.seg[i]; p.out[i] = m.out[i]; p.images[i] = m.images[i];
+        p.tile_begin[i] = tiles;
+        tiles += (m.seg[i].n_rows + GEMM_ROWS - 1) / GEMM_ROWS;
+    }
+    for (int i = m.n_seg; i < 4; i++) p.tile_begin[i] = tiles;
+    const int Tp = gemm_pad_tokens(m.T);
+    const size_t smem = gemm_smem_bytes(Tp);
+#define GEMM_LAUNCH(NTV, TWV)                                                                                         \
     do {                                                                                                              \
         static PerDeviceOnce once;                                                                                    \
-        once.run([] { CUDA_CHECK(cudaFuncSetAttribute(gemm_q_kernel<TY, NTV>, cudaFuncAttributeMaxDynamicSharedMemorySize, 96 * 1024)); }); \
-        gemm_q_kernel<TY, NTV><<<grid, GEMM_THREADS, smem, st>>>(p);                                                  \
+        once.run([] { CUDA_CHECK(cudaFuncSetAttribute(gemm_q_kernel<NTV, TWV>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024)); }); \
+        gemm_q_kernel<NTV, TWV><<<tiles, GEMM_RG * TWV * 32, smem, st>>>(p);                                          \
     } while (0)
-    if (w.type == T_Q4_K) {
-        if (nt == 1) GEMM_LAUNCH(T_Q4_K, 1); else if (nt == 2) GEMM_LAUNCH(T_Q4_K, 2); else if (nt == 3) GEMM_LAUNCH(T_Q4_K, 3); else GEMM_LAUNCH(T_Q4_K, 4);
-    } else {
-        if (nt == 1) GEMM_LAUNCH(T_Q8_0, 1); else if (nt == 2) GEMM_LAUNCH(T_Q8_0, 2); else if (nt == 3) GEMM_LAUNCH(T_Q8_0, 3); else GEMM_LAUNCH(T_Q8_0, 4);
+    switch (Tp) {
+        case 8: GEMM_LAUNCH(1, 1); break;
+        case 16: GEMM_LAUNCH(2, 1); break;
+        case 24: GEMM_LAUNCH(3, 1); break;
+        case 32: GEMM_LAUNCH(4, 1); break;
+        default: GEMM_LAUNCH(4, 2); break;
     }
 #undef GEMM_LAUNCH
     CUDA_CHECK(cudaGetLastError());
+}
+
+void launch_gemm_q(const WPlanes &w, const uint8_t *images, int T, float *out, int64_t ldo, int epi, cudaStream_t st) {
+    GemmMulti m{};
+    m.n_seg = 1; m.T = T; m.epi = epi; m.ldo = ldo;
+    m.seg[0] = w; m.out[0] = out; m.images[0] = images;
+    launch_gemm_multi(m, st);
 }
 
 }  // namespace aios

@@ -507,7 +507,7 @@ __device__ __forceinline__ void qkv_rope_store(const GemvParams &p, int seg, int
     if (seg == 0) {
         *reinterpret_cast<float2 *>(p.out[0] + row0) = make_float2(h2f_bits(ha), h2f_bits(hb));
     } else {
-        uint16_t *dst = (seg == 1 ? r.k_cache : r.v_cache) + (size_t)n_past * r.kvd + row0;
+        uint16_t *dst = (seg == 1 ? r.k_cache : r.v_cache) + (size_t)n_past * r.kv_stride + row0;
         *reinterpret_cast<uint32_t *>(dst) = (uint32_t)ha | ((uint32_t)hb << 16);
     }
 }

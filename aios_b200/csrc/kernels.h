@@ -11,6 +11,9 @@ namespace aios {
 void launch_dequantize(int type, const void *d_blocks, int64_t n, float *d_out, cudaStream_t st);
 void launch_embed_row(int type, const void *d_table, int64_t row_bytes, int k, const int32_t *d_tok, float *d_x,
                       int32_t *d_pos, int pos_value, int32_t *d_cur_token, cudaStream_t st);
+// T rows at once: x[t] = embedding row of d_toks[t] (row stride ldx floats)
+void launch_embed_rows(int type, const void *d_table, int64_t row_bytes, int k, const int32_t *d_toks, int T, float *d_x,
+                       int64_t ldx, cudaStream_t st);
 void launch_repack(int type, const void *d_raw, int64_t n_rows, int k, uint8_t *const planes[5], cudaStream_t st);
 
 // ---- gemv.cu : fused [RMSNorm] -> activation quantisation -> dequant+GEMV -> epilogue
@@ -26,8 +29,8 @@ enum GemvEpilogue : int {
 struct RopeKv {              // EPI_QKV_ROPE only
     const float *cos, *sin;  // [n_ctx][n_rot/2]
     const int32_t *n_past_ptr;
-    uint16_t *k_cache, *v_cache;  // this layer, this sequence: [n_ctx][kvd] f16
-    int32_t n_rot, hd, kvd, pad;
+    uint16_t *k_cache, *v_cache;  // this layer, this sequence: row of position j at + j * kv_stride (f16 elements)
+    int32_t n_rot, hd, kvd, kv_stride;
 };
 
 struct GemvParams {
@@ -58,14 +61,27 @@ void launch_gemv(const GemvParams &p, int grid, cudaStream_t st, bool pdl = fals
 bool gemv_can_mix(const GemvParams &p);  // may Q4_K and Q6_K segments of p ride in one launch?
 void gemv_init();  // one-time function attributes (dynamic smem)
 
-// ---- gemm_q.cu : multi-token (prompt chunk) dequant GEMM on int8 tensor cores, bit-identical to T GEMV calls
-// per-token Q8_K / Q8_0 activation images in global memory (optionally RMS-normed first); x row stride ldx floats
+// ---- gemm_q.cu : multi-token (batched decode / prompt chunk) dequant GEMM on int8 tensor cores, bit-identical to T
+// GEMV calls.  Per-token Q8_K / Q8_0 activation images in global memory (optionally RMS-normed first); x row stride
+// ldx floats.
+constexpr int GEMM_MAX_TOKENS = 64;
 void launch_quant_rows(int weight_type, const float *x, int64_t ldx, const float *norm_w, float eps, int k, int T,
                        uint8_t *images, cudaStream_t st);
-size_t gemm_images_bytes(int k, int T);  // allocate for T rounded up to a multiple of 8
-bool gemm_q_usable(int type, int k);     // Q4_K / Q8_0
-// out[t][row] (row stride ldo floats) = or += dot, t < T <= 32; epi = EPI_STORE or EPI_ADD
+size_t gemm_images_bytes(int k, int T);  // allocate for gemm_pad_tokens(T) tokens
+int gemm_pad_tokens(int T);              // tokens whose images must exist for a T-token launch: T rounded up to 8 (64 above 32)
+bool gemm_q_usable(int type, int k);     // Q4_K / Q6_K / Q8_0
+// out[t][row] (row stride ldo floats) = or += dot, t < T <= 64; epi = EPI_STORE or EPI_ADD
 void launch_gemm_q(const WPlanes &w, const uint8_t *images, int T, float *out, int64_t ldo, int epi, cudaStream_t st);
+// 1..3 matrices that share the input tokens in ONE launch (q/k/v, gate/up): images[i] = the image set in the
+// permutation of seg[i]'s type (Q4_K/Q5_K, Q6_K and Q8_0 weights read differently ordered images)
+struct GemmMulti {
+    int32_t n_seg, T, epi;
+    WPlanes seg[3];
+    float *out[3];
+    const uint8_t *images[3];
+    int64_t ldo;
+};
+void launch_gemm_multi(const GemmMulti &m, cudaStream_t st);
 // h[t][0..ff) = silu(gu[t][0..ff)) * gu[t][ff..2ff)
 void launch_swiglu_rows(const float *gu, int64_t ldgu, int ff, int T, float *h, int64_t ldh, cudaStream_t st);
 
@@ -73,8 +89,9 @@ void launch_swiglu_rows(const float *gu, int64_t ldgu, int ff, int T, float *h, 
 struct AttnParams {
     const float *qkv;        // [n_head*hd + 2*n_kv*hd] raw projections of the new token
     float *out;              // [n_head*hd]
-    uint16_t *k_cache;       // this layer: [n_ctx][n_kv*hd] f16
+    uint16_t *k_cache;       // this layer: row of position j = [n_kv*hd] f16 at + j * kv_stride
     uint16_t *v_cache;
+    int32_t kv_stride;       // f16 elements between the rows of consecutive positions (position-major KV pages)
     const float *rope_cos;   // [n_ctx][hd/2]
     const float *rope_sin;
     const int32_t *n_past_ptr;  // device: number of cached positions before this token
@@ -87,6 +104,14 @@ struct AttnParams {
     // (EPI_QKV_ROPE): qkv holds the final q only, every position comes from the cache
     int32_t kv_ready;
     int32_t stage_cap;  // set by launch_attn_decode_split: cache rows staged in shared memory (kv_ready launches)
+    // Batched decode (split kernel only): n_lanes > 0 -> blockIdx.y = lane, one new token per live sequence.  Lane l
+    // reads qkv + l * lane_qkv_stride, writes out + l * lane_out_stride, is at position lane_pos[l] and keeps its KV
+    // rows in its own range: k_cache / v_cache above are then OFFSETS (this layer's K and V rows inside a position,
+    // i.e. pointers relative to null) added to lane_kv[l].
+    int32_t n_lanes;
+    int64_t lane_qkv_stride, lane_out_stride;
+    const int32_t *lane_pos;
+    uint16_t *const *lane_kv;
 };
 // mode: 0 = pick (split kernel when usable, else cluster); 2 = cluster kernel
 void launch_attn_decode(const AttnParams &p, cudaStream_t st, bool pdl = false, int mode = 0);
@@ -115,5 +140,21 @@ struct SampleParams {
     int32_t *counts_out;     // optional (tests): {K, n after top-p, n after min-p}
 };
 void launch_sample(const SampleParams &p, cudaStream_t st);
+// batched decode: one CTA per lane; lane l samples from logits + l * n_vocab with its own parameters
+struct SampleLane {
+    float temperature;
+    int32_t top_k;
+    float top_p, min_p;
+    uint64_t seed;
+    const uint8_t *mask;   // device pointer or null
+};
+struct SampleBatchParams {
+    const float *logits;      // [n_lanes][n_vocab]
+    int32_t n_vocab;
+    const SampleLane *lanes;  // device array
+    int32_t *pos;             // device [n_lanes]: position of the last token fed; incremented
+    int32_t *tok;             // device [n_lanes]: sampled token (input of the forward pass that follows)
+};
+void launch_sample_batch(const SampleBatchParams &p, int n_lanes, cudaStream_t st);
 
 }  // namespace aios

@@ -423,6 +423,7 @@ __device__ void pfd_attention(const PfdParams &p, const PfdPhase &P, const PfdSm
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int rep = p.n_head / p.n_kv;
     const int kvd = p.n_kv * HD;
+    const int kvs = p.kv_stride;  // cache row stride
     const int n_kv_pos = pos + 1;
     const int per = (n_kv_pos + grp - 1) / grp;
     const int j0 = min(n_kv_pos, rank * per), j1 = min(n_kv_pos, j0 + per);
@@ -440,8 +441,8 @@ __device__ void pfd_attention(const PfdParams &p, const PfdPhase &P, const PfdSm
     if (pos >= j0 && pos < j1) {
         const float *kraw = qkv + (size_t)p.n_head * HD + (size_t)g * HD;
         const float *vraw = qkv + (size_t)p.n_head * HD + (size_t)kvd + (size_t)g * HD;
-        uint16_t *kc = P.k_cache + (size_t)pos * kvd + (size_t)g * HD;
-        uint16_t *vc = P.v_cache + (size_t)pos * kvd + (size_t)g * HD;
+        uint16_t *kc = P.k_cache + (size_t)pos * kvs + (size_t)g * HD;
+        uint16_t *vc = P.v_cache + (size_t)pos * kvs + (size_t)g * HD;
         for (int i = threadIdx.x; i < HD / 2; i += PFD_THREADS) {
             float x0 = __ldcg(kraw + 2 * i), x1 = __ldcg(kraw + 2 * i + 1);
             if (2 * i < p.n_rot) {
@@ -488,7 +489,7 @@ __device__ void pfd_attention(const PfdParams &p, const PfdPhase &P, const PfdSm
 #pragma unroll
         for (int t = 0; t < PFD_ATT_BATCH; t++) {
             const int j = min(jb + t, j1 - 1);
-            att_load_row<EPL>(P.k_cache + (size_t)j * kvd + (size_t)g * HD + lane * EPL, kf[t]);
+            att_load_row<EPL>(P.k_cache + (size_t)j * kvs + (size_t)g * HD + lane * EPL, kf[t]);
         }
 #pragma unroll
         for (int t = 0; t < PFD_ATT_BATCH; t++) {
@@ -563,7 +564,7 @@ __device__ void pfd_attention(const PfdParams &p, const PfdPhase &P, const PfdSm
 #pragma unroll
         for (int t = 0; t < PFD_ATT_BATCH; t++) {
             const int j = min(jb + t, j1 - 1);
-            att_load_row<EPL>(P.v_cache + (size_t)j * kvd + (size_t)g * HD + lane * EPL, vf[t]);
+            att_load_row<EPL>(P.v_cache + (size_t)j * kvs + (size_t)g * HD + lane * EPL, vf[t]);
         }
 #pragma unroll
         for (int t = 0; t < PFD_ATT_BATCH; t++) {

@@ -52,6 +52,7 @@ struct PfdParams {
     int32_t n_embd;
     const float *rope_cos, *rope_sin;
     int32_t n_head, n_kv, hd, n_rot;
+    int32_t kv_stride;       // f16 elements between the cache rows of consecutive positions
     float att_scale;
     int32_t att_group;       // CTAs per kv-head
     int32_t att_per_cap;     // max cached positions per CTA

@@ -70,7 +70,7 @@ __device__ __forceinline__ float rng_uniform(uint64_t seed, uint64_t ctr) {
 
 __device__ __forceinline__ bool allowed(const uint8_t *mask, int i) { return !mask || ((mask[i >> 3] >> (i & 7)) & 1); }
 
-__global__ void __launch_bounds__(SAMP_THREADS) sample_kernel(const SampleParams p) {
+__device__ __forceinline__ void sample_body(const SampleParams &p) {
     __shared__ unsigned long long sh[32];
     __shared__ unsigned long long top[SAMP_MAX_K], sorted[SAMP_MAX_K];
     __shared__ float prob[SAMP_MAX_K], wgt[SAMP_MAX_K];
@@ -229,6 +229,31 @@ __global__ void __launch_bounds__(SAMP_THREADS) sample_kernel(const SampleParams
     if (p.cand_out && tid < K) p.cand_out[tid] = key_index(sorted[tid]);
 }
 
+__global__ void __launch_bounds__(SAMP_THREADS) sample_kernel(const SampleParams p) { sample_body(p); }
+
+// one CTA per lane of the continuous batcher: the lane's own parameters, logits row, position and token slot
+__global__ void __launch_bounds__(SAMP_THREADS) sample_batch_kernel(const SampleBatchParams b) {
+    const int l = blockIdx.x;
+    const SampleLane L = b.lanes[l];
+    __shared__ int32_t step_dummy;
+    if (threadIdx.x == 0) step_dummy = 0;
+    __syncthreads();
+    SampleParams p{};
+    p.logits = b.logits + (size_t)l * b.n_vocab;
+    p.n_vocab = b.n_vocab;
+    p.temperature = L.temperature; p.top_k = L.top_k; p.top_p = L.top_p; p.min_p = L.min_p; p.seed = L.seed;
+    p.pos_ptr = b.pos + l;
+    p.step_ptr = &step_dummy;
+    p.cur_token = b.tok + l;
+    p.out_tokens = b.tok + l;  // step 0 of a 1-slot array: the same word
+    p.out_cap = 1;
+    p.mask = L.mask;
+    sample_body(p);
+}
+
 void launch_sample(const SampleParams &p, cudaStream_t st) { sample_kernel<<<1, SAMP_THREADS, 0, st>>>(p); }
+void launch_sample_batch(const SampleBatchParams &p, int n_lanes, cudaStream_t st) {
+    sample_batch_kernel<<<n_lanes, SAMP_THREADS, 0, st>>>(p);
+}
 
 }  // namespace aios

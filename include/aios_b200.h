@@ -220,14 +220,29 @@ int aios_generate(aios_model *m, const int32_t *prompt, int32_t n_prompt, const 
 
 /* ---- queued requests: what concurrent tonic handlers need (SURVEY.md §8b "Threading": the reference lets Infer calls
  *      run in parallel against llama-server, runtime/src/main.rs:50-51, grpc_service.rs:86-141).  submit / poll /
- *      wait / cancel / free are thread-safe and submit / poll / cancel never block on the GPU: one scheduler thread
- *      per engine runs the requests first come first served in a KV slot of their model (the model needs one free
- *      slot, see aios_engine_opts.max_batch), in chunks of 16 tokens between which other calls on the engine interleave.
+ *      wait / cancel / free are thread-safe and submit / poll / cancel never block on the GPU.  One scheduler thread
+ *      per engine does CONTINUOUS BATCHING: up to 64 requests of a model decode together, one token per request per
+ *      step, every weight matrix streamed once per step for all of them; requests join and leave between steps, and
+ *      synchronous calls on the engine interleave between steps as well.  A request's tokens do not depend on what
+ *      else is in the batch (same arithmetic as the single-sequence path, bit for bit).  KV memory comes from the
+ *      model's page pool as the request grows; the library's batch lanes do not count against max_batch.
  *      The prompt is copied on submit.  max_tokens is clipped to the context. */
 typedef struct aios_request aios_request;
 #define AIOS_REQ_STOP_AT_EOG 1  /* stop at (and do not return) the first end-of-generation token, see aios_token_is_eog */
 int aios_request_submit(aios_model *m, const int32_t *tokens, int32_t n, const aios_sampling *sp, int32_t max_tokens,
                         int32_t flags, aios_request **out);
+/* Same, with a per-step logit mask (JSON mode through the queue: unary Infer always asks for json_object,
+ * runtime/src/inference.rs:119-121).  Before every decode step of this request the scheduler thread calls
+ * cb(user, last_token, mask_out, n_bytes): last_token = the token sampled in the previous step (-1 before the first);
+ * the callback advances its grammar by that token and writes the allowed set of the NEXT token into mask_out
+ * (n_bytes = ceil(n_vocab / 8), zeroed on entry; bit i of byte i/8 = token i allowed).  Return 0: mask written;
+ * 1: no restriction for this step; 2: the output is complete, finish the request without sampling; < 0: fail the
+ * request.  The mask goes to the device (n_vocab / 8 bytes H2D) and is applied by the on-device sampler; logits never
+ * leave the GPU.  The callback runs on the scheduler thread between steps: keep it short, do not call back into the
+ * engine from it. */
+typedef int (*aios_mask_cb)(void *user, int32_t last_token, uint8_t *mask_out, int32_t n_bytes);
+int aios_request_submit_masked(aios_model *m, const int32_t *tokens, int32_t n, const aios_sampling *sp, int32_t max_tokens,
+                               int32_t flags, aios_mask_cb cb, void *user, aios_request **out);
 /* take up to cap new tokens; *done = 1 once the request has finished AND everything was taken.  A request that
  * failed returns its error code (message in aios_last_error) from the poll that would have set *done. */
 int aios_request_poll(aios_request *r, int32_t *out_tokens, int32_t cap, int32_t *n_out, int32_t *done);
@@ -246,9 +261,10 @@ int aios_dequantize(aios_engine *e, int32_t ggml_type, const void *blocks, int64
  * integer block dots): host in, host out.  If norm_w != NULL, x is RMS-normed first. */
 int aios_matvec(aios_engine *e, int32_t ggml_type, const void *w_blocks, int64_t n_rows, int64_t k,
                 const float *x, const float *norm_w, float rms_eps, float *y);
-/* Y[n_tok][n_rows] = X[n_tok][k] . W[n_rows,k]^T for a chunk of 1..32 tokens through the tensor-core kernel
- * (gemm_q.cu: int8 MMA on the 32-weight sub-block dots, weights streamed once for all tokens).  Same numerics as
- * n_tok calls of aios_matvec, bit for bit.  Q4_K and Q8_0 weights (AIOS_E_UNSUPPORTED otherwise); host in, host out. */
+/* Y[n_tok][n_rows] = X[n_tok][k] . W[n_rows,k]^T for 1..64 tokens through the multi-token kernel (gemm_q.cu: int8 MMA
+ * on the sub-block dots, weights streamed once for all tokens — batched decode and bit-exact prompt chunks).  Same
+ * numerics as n_tok calls of aios_matvec, bit for bit.  Q4_K, Q6_K and Q8_0 weights (AIOS_E_UNSUPPORTED otherwise);
+ * host in, host out. */
 int aios_matmul(aios_engine *e, int32_t ggml_type, const void *w_blocks, int64_t n_rows, int64_t k, const float *x,
                 int32_t n_tok, const float *norm_w, float rms_eps, float *y);
 /* one run of the on-device sampler chain on host logits (parity hook for oracle_sample): mask_bits may be NULL;

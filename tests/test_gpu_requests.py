@@ -99,3 +99,93 @@ def test_request_argument_errors(model):
     r = model.submit(p, 100)
     assert r.result().size == 6
     r.free()
+
+
+def test_64_concurrent_requests_equal_one_by_one(engine, tmp_models):
+    """Continuous batching (BASELINE.json configs[3]: 64 concurrent agent requests per GPU): 64 requests submitted at
+    once decode together — one token per request per step through the multi-token GEMM — and every one of them must
+    return exactly the tokens the same prompt gives alone, greedy, bit for bit.  Prompts and lengths differ, so requests
+    join and leave the batch at different steps."""
+    m = engine.load_model("b64", tmp_models("tiny-gqa4", "Q4_K_M"), n_ctx=192)
+    try:
+        rng = np.random.default_rng(5)
+        prompts = [gs.synthetic_prompt("tiny-gqa4", int(rng.integers(3, 60)), 1000 + i) for i in range(64)]
+        n_gen = [int(rng.integers(1, 90)) for _ in range(64)]
+        want = [m.generate(p, n) for p, n in zip(prompts, n_gen)]
+        reqs = [m.submit(p, n) for p, n in zip(prompts, n_gen)]
+        got = [r.result() for r in reqs]
+        for r in reqs:
+            r.free()
+        for i, (g, w) in enumerate(zip(got, want)):
+            assert np.array_equal(g, w), (i, len(prompts[i]), n_gen[i])
+        # more requests than lanes: the rest wait for a lane and still match
+        more = [m.submit(prompts[i % 64], n_gen[i % 64]) for i in range(100)]
+        for i, r in enumerate(more):
+            assert np.array_equal(r.result(), want[i % 64]), i
+            r.free()
+    finally:
+        m.unload()
+
+
+@pytest.mark.parametrize("ftype", ["Q4_K_M", "Q8_0"])
+def test_batched_stochastic_requests_equal_sequential(engine, tmp_models, ftype):
+    """Sampling in the batch is per lane (own parameters, seed, position counter): a request drawn with temperature 0.8
+    gives the same tokens inside a batch of 24 as alone."""
+    arch = "tiny-gqa4" if ftype == "Q4_K_M" else "tiny"
+    m = engine.load_model("bs", tmp_models(arch, ftype), n_ctx=128)
+    try:
+        prompts = [gs.synthetic_prompt(arch, 4 + i, 50 + i) for i in range(24)]
+        sps = [capi.make_sampling(0.8 if i % 3 else 0.0, 40, 0.95, 0.05, seed=7 + i) for i in range(24)]
+        want = [m.generate(p, 40, sp) for p, sp in zip(prompts, sps)]
+        reqs = [m.submit(p, 40, sp) for p, sp in zip(prompts, sps)]
+        for i, r in enumerate(reqs):
+            assert np.array_equal(r.result(), want[i]), i
+            r.free()
+    finally:
+        m.unload()
+
+
+def test_masked_request_applies_the_callback_mask_on_the_device(engine, tmp_models):
+    """aios_request_submit_masked: the scheduler asks the callback for the allowed set before every step and the
+    on-device sampler honours it; the callback sees every sampled token and can end the request."""
+    m = engine.load_model("mk", tmp_models("tiny-gqa4", "Q4_K_M"), n_ctx=128)
+    try:
+        V = m.info.n_vocab
+        prompt = gs.synthetic_prompt("tiny-gqa4", 9, 3)
+        seen = []
+
+        def cb(last_token, mask):
+            seen.append(last_token)
+            if len(seen) > 20:
+                return 2  # "the object is closed"
+            if len(seen) % 4 == 0:
+                return 1  # an unrestricted step
+            mask[:] = 0x55 if len(seen) % 2 else 0xAA  # even ids / odd ids
+            return 0
+
+        r = m.submit(prompt, 64, capi.make_sampling(0.7, 40, 0.95, 0.05, seed=3), mask_cb=cb)
+        toks = r.result()
+        r.free()
+        assert len(toks) == 20 and seen[0] == -1 and seen[1:] == [int(t) for t in toks]
+        for i, t in enumerate(toks):
+            step = i + 1
+            if step % 4 == 0:
+                continue
+            assert t % 2 == (0 if step % 2 else 1), (i, t)
+        # the same masks applied step by step on a plain sequence give the same tokens
+        s = m.new_seq()
+        try:
+            s.prefill(prompt)
+            sp = capi.make_sampling(0.7, 40, 0.95, 0.05, seed=3)
+            again = []
+            for step in range(1, 21):
+                if step % 4 == 0:
+                    s.set_mask(None)
+                else:
+                    s.set_mask(np.full((V + 7) // 8, 0x55 if step % 2 else 0xAA, np.uint8))
+                again.append(s.step(sp))
+            assert again == [int(t) for t in toks]
+        finally:
+            s.free()
+    finally:
+        m.unload()
