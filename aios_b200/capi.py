@@ -61,6 +61,12 @@ class Sampling(C.Structure):
                 ("seed", C.c_uint64)]
 
 
+class BatchBench(C.Structure):
+    _fields_ = [("ms_decode", C.c_float), ("ms_prefill", C.c_float), ("n_lanes", C.c_int32), ("n_steps_timed", C.c_int32),
+                ("kernel_launches", C.c_int32), ("n_past_begin", C.c_int32), ("n_past_end", C.c_int32),
+                ("reserved", C.c_int32)]
+
+
 class BenchResult(C.Structure):
     _fields_ = [("ms_total", C.c_float), ("n_tokens", C.c_int32), ("kernel_launches", C.c_int32),
                 ("n_past_begin", C.c_int32), ("n_past_end", C.c_int32), ("ms_gemv", C.c_float),
@@ -122,6 +128,7 @@ SYMBOLS = {
     "aios_seq_phase_timing": (C.c_int, [_P, _P, C.c_int32, C.POINTER(C.c_int32)]),
     "aios_seq_snapshot": (C.c_int, [_P]),
     "aios_seq_restore": (C.c_int, [_P]),
+    "aios_bench_batch_decode": (C.c_int, [_P, C.c_int32, _P, C.c_int32, C.c_int32, _P, C.POINTER(BatchBench)]),
     "aios_bench_gemv": (C.c_int, [_P, C.c_int32, C.c_int64, C.c_int64, C.c_int32, C.c_int32, C.POINTER(C.c_float)]),
 }
 
@@ -353,6 +360,15 @@ class Model:
         r = Request(h, self)
         r._keep = cfun  # the C callback must outlive the request
         return r
+
+    def bench_batch_decode(self, prompts: np.ndarray, n_steps: int, want_tokens: bool = True):
+        """aios_bench_batch_decode: prompts[n_lanes][n_prompt] -> (BatchBench, tokens[n_lanes][n_steps] or None)."""
+        pr = np.ascontiguousarray(prompts, dtype=np.int32)
+        out = np.empty((pr.shape[0], n_steps), dtype=np.int32) if want_tokens else None
+        r = BatchBench()
+        _check(lib().aios_bench_batch_decode(self.h, pr.shape[0], _ptr(pr), pr.shape[1], n_steps,
+                                             _ptr(out) if out is not None else None, C.byref(r)))
+        return r, out
 
     def forward_logits(self, tokens, n_past: int = 0) -> np.ndarray:
         toks = np.ascontiguousarray(tokens, dtype=np.int32)

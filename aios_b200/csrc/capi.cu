@@ -927,6 +927,51 @@ int aios_seq_restore(aios_seq *s) {
     });
 }
 
+int aios_bench_batch_decode(aios_model *m, int32_t n_lanes, const int32_t *prompts, int32_t n_prompt, int32_t n_steps,
+                            int32_t *out_tokens, aios_batch_bench *out) {
+    return guarded([&] {
+        if (!m || !prompts || !out || n_lanes <= 0 || n_lanes > GEMM_MAX_TOKENS || n_prompt <= 0 || n_steps <= 0)
+            return fail(AIOS_E_INVAL, "bad argument");
+        if (n_prompt + n_steps > m->impl.hp.n_ctx) return fail(AIOS_E_STATE, "prompt + steps do not fit in the context");
+        for (int64_t i = 0; i < (int64_t)n_lanes * n_prompt; i++)
+            if (prompts[i] < 0 || prompts[i] >= m->impl.hp.n_vocab) return fail(AIOS_E_INVAL, "token id out of range");
+        Engine &E = *m->impl.eng;
+        std::lock_guard<std::mutex> lk(E.mu);
+        E.make_current();
+        Batch b(&m->impl);  // a private batch: the scheduler's own lanes are untouched
+        aios_sampling greedy{};
+        cudaEvent_t e0, e1, e2;
+        CUDA_CHECK(cudaEventCreate(&e0));
+        CUDA_CHECK(cudaEventCreate(&e1));
+        CUDA_CHECK(cudaEventCreate(&e2));
+        CUDA_CHECK(cudaEventRecord(e0, E.stream));
+        for (int l = 0; l < n_lanes; l++) b.admit(prompts + (size_t)l * n_prompt, n_prompt, greedy);
+        CUDA_CHECK(cudaEventRecord(e1, E.stream));
+        b.step();  // untimed: captures the step's graph for this lane count
+        if (out_tokens)
+            for (int l = 0; l < n_lanes; l++) out_tokens[(size_t)l * n_steps] = b.h_tok[l];
+        CUDA_CHECK(cudaEventRecord(e1, E.stream));
+        for (int s = 1; s < n_steps; s++) {
+            b.step();
+            if (out_tokens)
+                for (int l = 0; l < n_lanes; l++) out_tokens[(size_t)l * n_steps + s] = b.h_tok[l];
+        }
+        CUDA_CHECK(cudaEventRecord(e2, E.stream));
+        CUDA_CHECK(cudaEventSynchronize(e2));
+        memset(out, 0, sizeof(*out));
+        CUDA_CHECK(cudaEventElapsedTime(&out->ms_decode, e1, e2));
+        CUDA_CHECK(cudaEventElapsedTime(&out->ms_prefill, e0, e1));
+        cudaEventDestroy(e0); cudaEventDestroy(e1); cudaEventDestroy(e2);
+        out->n_lanes = n_lanes;
+        out->n_steps_timed = n_steps - 1;
+        out->kernel_launches = b.kernels_per_step * (n_steps - 1);
+        out->n_past_begin = n_prompt + 1;
+        out->n_past_end = n_prompt + n_steps;
+        while (b.n > 0) b.retire(b.n - 1);
+        return (int)AIOS_OK;
+    });
+}
+
 int aios_bench_gemv(aios_engine *e, int32_t type, int64_t n_rows, int64_t k, int32_t n_copies, int32_t iters,
                     float *ms_per_launch) {
     return guarded([&] {

@@ -202,6 +202,44 @@ def run_reference(args, rank: int, world: int):
     print(json.dumps(line), flush=True)
 
 
+def bench_config4(eng, model, arch: str, ftype: str, peak: float, n_lanes: int = 64, n_prompt: int = 128, n_gen: int = 128):
+    """BASELINE.json configs[3]: batched decode, 64 concurrent requests on one GPU (one token per request per step, all
+    through one weight stream).  Device-timed steps (CUDA events, every step's tokens copied to the host like in the
+    scheduler) plus the same load end to end through aios_request_submit / poll (prefill included)."""
+    info = model.info
+    rng_prompts = np.stack([gs.synthetic_prompt(arch, n_prompt, SEED + 100 + i) for i in range(n_lanes)])
+    model.bench_batch_decode(rng_prompts[:, :8], 4, want_tokens=False)  # warm-up: buffers, graphs of this lane count
+    r, toks = model.bench_batch_decode(rng_prompts, n_gen)
+    # parity spot check: two lanes against the single-sequence path
+    for lane in (0, n_lanes - 1):
+        alone = model.generate(rng_prompts[lane], n_gen)
+        if not np.array_equal(alone, toks[lane]):
+            raise SystemExit(f"bench.py: PARITY FAILURE — batched lane {lane} differs from the single-sequence path")
+    steps_s = r.n_steps_timed / (r.ms_decode * 1e-3)
+    tok_s = steps_s * n_lanes
+    n_past_mean = (r.n_past_begin + r.n_past_end) / 2.0
+    bytes_step = info.weight_bytes_per_token + n_lanes * info.kv_bytes_per_position * n_past_mean
+    # end to end: submit, wait, read every token back through the request API (host buffers in, host buffers out)
+    t0 = time.perf_counter()
+    reqs = [model.submit(rng_prompts[i], n_gen) for i in range(n_lanes)]
+    got = [q.result(600000) for q in reqs]
+    dt = time.perf_counter() - t0
+    for q in reqs:
+        q.free()
+    if not all(np.array_equal(g, t) for g, t in zip(got, toks)):
+        raise SystemExit("bench.py: PARITY FAILURE — queued requests differ from the batched decode hook")
+    return {"workload": f"{arch} {ftype} batched greedy decode, {n_lanes} concurrent requests x ({n_prompt}-token prompt + {n_gen} "
+                        "generated) on one GPU (BASELINE.json configs[3])",
+            "value": tok_s, "unit": "tok/s", "ms_per_step": r.ms_decode / r.n_steps_timed, "steps_timed": r.n_steps_timed,
+            "lanes": n_lanes, "gpu_launches": r.kernel_launches, "bytes_per_step": bytes_step,
+            "roofline_tok_s": n_lanes * peak * 1e9 / bytes_step, "frac_of_hbm_roofline": tok_s / (n_lanes * peak * 1e9 / bytes_step),
+            "prefill_ms": r.ms_prefill,
+            "e2e": {"value": n_lanes * n_gen / dt, "unit": "tok/s generated, prompt prefill included in the time",
+                    "seconds": dt, "api": "aios_request_submit x64 + aios_request_wait / poll",
+                    "h2d_bytes_per_step": int(rng_prompts.nbytes), "d2h_bytes_per_step": n_lanes * n_gen * 4},
+            "parity_checked": True}
+
+
 def in_graph_breakdown(seq, n_runs: int = 4):
     """Per-token time of each launch kind INSIDE the token pass, from the %globaltimer marks the kernels themselves take
     (aios_seq_trace_decode: same launch order and programmatic-dependent-launch attributes as the captured graph).
@@ -246,6 +284,7 @@ def main():
     ap.add_argument("--ref-tokens-per-step", type=int, default=16)
     ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the oracle run (parity gate + cpu_baseline)")
     ap.add_argument("--parity-tokens", type=int, default=16)
+    ap.add_argument("--no-subrecords", action="store_true", help="headline measurement only (no config3 / config4 sub-records)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -362,6 +401,16 @@ def main():
     gemv_gbs = gemv_bytes_per_token / (ig["us_gemv"] * 1e-6) / 1e9 if ig["us_gemv"] > 0 else 0.0
     iso_gbs = gemv_bytes_per_token * prof.n_tokens / (prof.ms_gemv * 1e-3) / 1e9
 
+    config4 = None
+    if rank == 0 and world == 1 and not args.no_subrecords:
+        config4 = {"mistral-7b": bench_config4(eng, model, args.arch, args.ftype, peak)}
+        tl_path = ensure_model("tinyllama-1.1b", "Q4_K_M", True)
+        tl = eng.load_model("bench-tl", tl_path, n_ctx=512)
+        try:
+            config4["tinyllama-1.1b"] = bench_config4(eng, tl, "tinyllama-1.1b", "Q4_K_M", peak)
+        finally:
+            tl.unload()
+
     if rank == 0:
         # the dominant kernel's in-graph time must fit inside the token it is part of
         fits = ig["us_gemv"] <= us_token * 1.05 and ig["us_token"] <= us_token * 1.25
@@ -402,6 +451,8 @@ def main():
         }
         if cpu and world == 1:
             line["cpu_baseline"] = cpu
+        if config4:
+            line["config4"] = config4
         print(json.dumps(line), flush=True)
     seq.free()
     seq_e2e.free()

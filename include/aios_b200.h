@@ -308,6 +308,21 @@ int aios_seq_trace_decode(aios_seq *s, uint64_t *out, int32_t cap_launches, int3
  * fused launch: out[n_phases][4] = phase start, after the activation prologue, after the compute loop, after the grid
  * barrier.  *n_phases returns the phase count; cap = capacity of out in phases. */
 int aios_seq_phase_timing(aios_seq *s, uint64_t *out, int32_t cap, int32_t *n_phases);
+/* batched decode as the continuous batcher runs it (bench.py configs[3]): n_lanes sequences are admitted with their
+ * n_prompt-token prompts (prompts[n_lanes][n_prompt]), then n_steps greedy steps run — one token per lane per step, the
+ * first step untimed (it captures the step's CUDA graph), the others timed with CUDA events on the engine's stream,
+ * each step's sampled tokens copied to the host and synchronised like in the scheduler.  out_tokens[n_lanes][n_steps]
+ * (may be NULL) receives every lane's tokens.  ms_prefill includes the first step. */
+typedef struct aios_batch_bench {
+    float ms_decode;         /* CUDA-event time of the timed steps                            */
+    float ms_prefill;        /* admission: the prompts' prefill + the untimed first step      */
+    int32_t n_lanes, n_steps_timed;
+    int32_t kernel_launches; /* kernel nodes executed inside the timed steps                  */
+    int32_t n_past_begin, n_past_end;  /* positions in every lane's cache at the first / after the last timed step */
+    int32_t reserved;
+} aios_batch_bench;
+int aios_bench_batch_decode(aios_model *m, int32_t n_lanes, const int32_t *prompts, int32_t n_prompt, int32_t n_steps,
+                            int32_t *out_tokens, aios_batch_bench *out);
 /* time ONE GEMV launch shape in isolation (roofline leg): type/n_rows/k on random weights,
  * `iters` launches over `n_copies` distinct weight copies (so the working set exceeds L2) */
 int aios_bench_gemv(aios_engine *e, int32_t ggml_type, int64_t n_rows, int64_t k, int32_t n_copies,

@@ -10,6 +10,6 @@ timeout 600 python bench.py --steps 5 --warmup 3 > gpurun_out/bench.json 2> gpur
 timeout 600 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/bench_reference.json 2> gpurun_out/bench_reference.err
 tail -3 gpurun_out/pytest.log; cat gpurun_out/smoke.log | tail -2; cat gpurun_out/bench.json | head -c 1500
 # launch list of the same short bench command (cold-cache, serialised: compare SHARES)
-timeout 600 python bench.py --steps 1 --warmup 3 --gen 2 --no-cpu-baseline > gpurun_out/ncu_plain.log 2>&1 && \
+timeout 600 python bench.py --steps 1 --warmup 3 --gen 2 --no-cpu-baseline --no-subrecords > gpurun_out/ncu_plain.log 2>&1 && \
 timeout 900 ncu --metrics gpu__time_duration.sum --clock-control none -k regex:'gemv|attn|sample|embed|gemm|quant' -s 2000 -c 400 --csv \
-    --log-file gpurun_out/launches.csv python bench.py --steps 1 --warmup 3 --gen 2 --no-cpu-baseline > gpurun_out/ncu.log 2>&1
+    --log-file gpurun_out/launches.csv python bench.py --steps 1 --warmup 3 --gen 2 --no-cpu-baseline --no-subrecords > gpurun_out/ncu.log 2>&1
