@@ -313,7 +313,7 @@ def main():
     path = ensure_model(args.arch, args.ftype, writer=(local_rank == 0))
     barrier()
     n_ctx = args.prompt + args.gen
-    eng = capi.Engine(device=local_rank, max_batch=2)
+    eng = capi.Engine(device=local_rank, max_batch=3)  # seq, seq_e2e, and a temporary one for the parity spot checks
     model = eng.load_model("bench", path, n_ctx=n_ctx)
     info = model.info
     seq = model.new_seq()
