@@ -119,6 +119,7 @@ SYMBOLS = {
     "aios_dequantize": (C.c_int, [_P, C.c_int32, _P, C.c_int64, _P]),
     "aios_matvec": (C.c_int, [_P, C.c_int32, _P, C.c_int64, C.c_int64, _P, _P, C.c_float, _P]),
     "aios_matmul": (C.c_int, [_P, C.c_int32, _P, C.c_int64, C.c_int64, _P, C.c_int32, _P, C.c_float, _P]),
+    "aios_matmul_tc": (C.c_int, [_P, C.c_int32, _P, C.c_int64, C.c_int64, _P, C.c_int32, _P, C.c_float, _P]),
     "aios_forward_logits": (C.c_int, [_P, _P, C.c_int32, C.c_int32, _P]),
     "aios_seq_read_kv": (C.c_int, [_P, C.c_int32, C.c_int32, C.c_int32, _P, _P]),
     "aios_seq_read_activation": (C.c_int, [_P, C.c_int32, _P, C.c_int64]),
@@ -276,6 +277,17 @@ class Engine:
         nw = np.ascontiguousarray(norm_w, dtype=np.float32) if norm_w is not None else None
         _check(lib().aios_matmul(self.h, qtype, _ptr(w), n_rows, k, _ptr(x), x.shape[0],
                                  _ptr(nw) if nw is not None else None, eps, _ptr(y)))
+        return y
+
+    def matmul_tc(self, qtype: int, w_blocks: np.ndarray, n_rows: int, k: int, x: np.ndarray, norm_w=None,
+                  eps: float = 1e-5) -> np.ndarray:
+        """Y[T][n_rows] through the tcgen05 prefill GEMM (aios_matmul_tc): float arithmetic, stated tolerance."""
+        w = np.ascontiguousarray(w_blocks, dtype=np.uint8).reshape(-1)
+        x = np.ascontiguousarray(x, dtype=np.float32).reshape(-1, k)
+        y = np.empty((x.shape[0], n_rows), dtype=np.float32)
+        nw = np.ascontiguousarray(norm_w, dtype=np.float32) if norm_w is not None else None
+        _check(lib().aios_matmul_tc(self.h, qtype, _ptr(w), n_rows, k, _ptr(x), x.shape[0],
+                                    _ptr(nw) if nw is not None else None, eps, _ptr(y)))
         return y
 
     def sample_logits(self, logits: np.ndarray, sampling: Sampling, counter: int = 0, mask: np.ndarray | None = None):

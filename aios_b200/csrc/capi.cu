@@ -12,6 +12,9 @@
 #include <thread>
 #include <vector>
 
+#include <cuda_fp16.h>
+#include <cuda_profiler_api.h>
+
 #include "../../include/aios_b200.h"
 #include "common.cuh"
 #include "engine.h"
@@ -825,6 +828,31 @@ int aios_sample_logits(aios_engine *e, const float *logits, int32_t n_vocab, con
     });
 }
 
+int aios_matmul_tc(aios_engine *e, int32_t type, const void *w_blocks, int64_t n_rows, int64_t k, const float *x, int32_t n_tok,
+                   const float *norm_w, float rms_eps, float *y) {
+    return guarded([&] {
+        if (!e || !w_blocks || !x || !y || n_rows <= 0 || k <= 0 || n_tok <= 0) return fail(AIOS_E_INVAL, "bad argument");
+        if (!prefill_tc_usable(type, (int)k)) return fail(AIOS_E_UNSUPPORTED, "aios_matmul_tc: Q4_K / Q6_K / Q8_0 weights, k a multiple of 256");
+        std::lock_guard<std::mutex> lk(e->impl.mu);
+        Engine &E = e->impl;
+        E.make_current();
+        DevMatrix dm;
+        make_dev_matrix(E, type, w_blocks, n_rows, k, dm);
+        DevBuf dx((size_t)n_tok * k * 4), dh((size_t)n_tok * k * 2), dy((size_t)n_tok * n_rows * 4), dn;
+        CUDA_CHECK(cudaMemcpyAsync(dx.p, x, (size_t)n_tok * k * 4, cudaMemcpyHostToDevice, E.stream));
+        if (norm_w) {
+            dn = DevBuf((size_t)k * 4);
+            CUDA_CHECK(cudaMemcpyAsync(dn.p, norm_w, (size_t)k * 4, cudaMemcpyHostToDevice, E.stream));
+        }
+        launch_rows_to_f16(dx.as<float>(), k, norm_w ? dn.as<float>() : nullptr, rms_eps, (int)k, n_tok, dh.as<__half>(), E.stream);
+        launch_prefill_tc(dm.w, dh.as<__half>(), n_tok, dy.as<float>(), n_rows, EPI_STORE, E.n_sms, E.stream);
+        CUDA_CHECK(cudaMemcpyAsync(y, dy.p, dy.bytes, cudaMemcpyDeviceToHost, E.stream));
+        CUDA_CHECK(cudaStreamSynchronize(E.stream));
+        CUDA_CHECK(cudaGetLastError());
+        return (int)AIOS_OK;
+    });
+}
+
 int aios_forward_logits(aios_model *m, const int32_t *tokens, int32_t n, int32_t n_past, float *logits_out) {
     return guarded([&] {
         if (!m || !tokens || n <= 0 || !logits_out || n_past < 0) return fail(AIOS_E_INVAL, "bad argument");
@@ -951,6 +979,8 @@ int aios_bench_batch_decode(aios_model *m, int32_t n_lanes, const int32_t *promp
         if (out_tokens)
             for (int l = 0; l < n_lanes; l++) out_tokens[(size_t)l * n_steps] = b.h_tok[l];
         CUDA_CHECK(cudaEventRecord(e1, E.stream));
+        const bool prof = getenv("AIOS_PROFILE_STEPS") != nullptr;  // ncu --profile-from-start off: the timed steps only
+        if (prof) cudaProfilerStart();
         for (int s = 1; s < n_steps; s++) {
             b.step();
             if (out_tokens)
@@ -958,6 +988,7 @@ int aios_bench_batch_decode(aios_model *m, int32_t n_lanes, const int32_t *promp
         }
         CUDA_CHECK(cudaEventRecord(e2, E.stream));
         CUDA_CHECK(cudaEventSynchronize(e2));
+        if (prof) cudaProfilerStop();
         memset(out, 0, sizeof(*out));
         CUDA_CHECK(cudaEventElapsedTime(&out->ms_decode, e1, e2));
         CUDA_CHECK(cudaEventElapsedTime(&out->ms_prefill, e0, e1));

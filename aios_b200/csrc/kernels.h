@@ -1,5 +1,6 @@
 // kernels.h — host-callable launchers of the CUDA kernels (internal; not part of the C ABI).
 #pragma once
+#include <cuda_fp16.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -84,6 +85,16 @@ struct GemmMulti {
 void launch_gemm_multi(const GemmMulti &m, cudaStream_t st);
 // h[t][0..ff) = silu(gu[t][0..ff)) * gu[t][ff..2ff)
 void launch_swiglu_rows(const float *gu, int64_t ldgu, int ff, int T, float *h, int64_t ldh, cudaStream_t st);
+
+// ---- prefill_tc.cu : the prefill GEMM on tcgen05 tensor cores (TMEM accumulators, TMA-staged f16 activations, weights
+// dequantised into shared memory); f16 x f16 products, f32 accumulation — a stated tolerance, not the bit-exact path
+bool prefill_tc_usable(int type, int k);  // Q4_K / Q6_K / Q8_0
+// out[t][row] (row stride ldo floats) = or += sum_k xh[t][k] * dq(w)[row][k], t < T; xh = f16 [T][k] in this GPU's memory
+void launch_prefill_tc(const WPlanes &w, const __half *xh, int T, float *out, int64_t ldo, int epi, int n_sms, cudaStream_t st);
+// xh[t] = f16(rmsnorm(x[t]) * norm_w) (norm_w null: plain conversion); x row stride ldx floats
+void launch_rows_to_f16(const float *x, int64_t ldx, const float *norm_w, float eps, int k, int T, __half *xh, cudaStream_t st);
+// hh[t][i] = f16(silu(gu[t][i]) * gu[t][ff+i])
+void launch_swiglu_rows_f16(const float *gu, int64_t ldgu, int ff, int T, __half *hh, cudaStream_t st);
 
 // ---- attention.cu : RoPE + KV write + flash-decode over the f16 KV cache (one new token)
 struct AttnParams {
