@@ -24,6 +24,7 @@ ENGINE_USE_PFD = 8
 ENGINE_ATTN_CLUSTER = 64
 ENGINE_NO_ROPE_EPILOGUE = 256
 ENGINE_NO_GEMM = 1024
+ENGINE_EXACT_PREFILL = 2048
 
 
 class AiosError(RuntimeError):

@@ -187,6 +187,10 @@ Model::Model(Engine *e, const std::string &name_, const std::string &path_, int 
         weight_bytes_per_token += (int64_t)hp.n_embd * 4;
         const GgufTensor *out = f.find("output.weight");
         upload_matrix(out ? *out : te, output, staging, pinned, pinned_bytes);  // tied embeddings when absent
+        tc_ok = true;
+        for (const Layer &L : layers)
+            for (const DevMatrix *dm : {&L.wq, &L.wk, &L.wv, &L.wo, &L.w_gate, &L.w_up, &L.w_down})
+                tc_ok = tc_ok && prefill_tc_usable(dm->w.type, dm->w.k);
     } catch (...) {
         cudaFreeHost(pinned);
         throw;
@@ -449,7 +453,14 @@ void Seq::prefill(const int32_t *tokens, int n) {
     ensure_kv(n_past + n);
     cudaStream_t st = m->eng->stream;
     CUDA_CHECK(cudaMemcpyAsync(prompt.p, tokens, (size_t)n * 4, cudaMemcpyHostToDevice, st));
-    if (n >= 4 && !(m->eng->flags & AIOS_ENGINE_NO_GEMM)) {
+    constexpr int TC_MIN_TOKENS = 256, TC_MAX_TOKENS = 4096;
+    if (n >= TC_MIN_TOKENS && m->tc_ok && !(m->eng->flags & (AIOS_ENGINE_EXACT_PREFILL | AIOS_ENGINE_NO_GEMM))) {
+        // long prompts: the tcgen05 GEMM + flash attention (float arithmetic, stated tolerance)
+        for (int i = 0; i < n; i += TC_MAX_TOKENS) {
+            const int T = std::min(TC_MAX_TOKENS, n - i);
+            prefill_tc(i, T, n_past + i, i + T == n, st);
+        }
+    } else if (n >= 4 && !(m->eng->flags & AIOS_ENGINE_NO_GEMM)) {
         // prompt chunks of up to 64 tokens: every matrix is streamed once per chunk (gemm_q.cu)
         for (int i = 0; i < n; i += GEMM_MAX_TOKENS) {
             const int T = std::min((int)GEMM_MAX_TOKENS, n - i);
@@ -574,6 +585,61 @@ void Seq::prefill_chunk(int idx0, int T, int pos0, bool want_logits, cudaStream_
         launch_swiglu_rows(GU, 2 * FF, FF, T, H, FF, st);
         matmul({&L.w_down.w}, {X}, H, FF, nullptr, E, EPI_ADD);
     }
+    if (want_logits) {
+        CUDA_CHECK(cudaMemsetAsync(&sd->argmax_key, 0, sizeof(unsigned long long), st));
+        GemvParams p{};
+        p.n_seg = 1; p.epi = EPI_STORE; p.k = E;
+        p.seg[0] = m->output.w; p.out[0] = logits.as<float>();
+        p.x = X + (size_t)(T - 1) * E; p.norm_w = m->output_norm.as<float>(); p.eps = hp.rms_eps;
+        p.argmax_key = &sd->argmax_key;
+        p.evict_first = m->eng->evict_first ? 1 : 0;
+        launch_gemv(p, gemv_plan_grid(p, n_sms), st, false);
+    }
+}
+
+// One prompt chunk of T tokens on the tensor-core path: every matrix product through the tcgen05 GEMM (prefill_tc.cu),
+// RoPE + KV append for all T rows at once, causal flash attention over the KV range (attention_prefill.cu).  The
+// residual stream stays f32; GEMM inputs are f16.  The last token's logits come from the exact lm_head GEMV.
+void Seq::prefill_tc(int idx0, int T, int pos0, bool want_logits, cudaStream_t st) {
+    const HParams &hp = m->hp;
+    const int E = hp.n_embd, FF = hp.n_ff, QD = hp.n_head * hp.head_dim, KVD = hp.n_head_kv * hp.head_dim, LQ = QD + 2 * KVD;
+    const int n_sms = m->eng->n_sms;
+    TcScratch &S = m->tc;
+    if (S.cap < T) {
+        CUDA_CHECK(cudaStreamSynchronize(st));
+        S = TcScratch{};
+        S.X = DevBuf((size_t)T * E * 4); S.Xh = DevBuf((size_t)T * std::max(E, QD) * 2); S.QKV = DevBuf((size_t)T * LQ * 4);
+        S.Qh = DevBuf((size_t)T * QD * 2); S.ATTh = DevBuf((size_t)T * QD * 2); S.GU = DevBuf((size_t)T * 2 * FF * 4);
+        S.Hh = DevBuf((size_t)T * FF * 2);
+        S.cap = T;
+    }
+    SeqState *sd = state.as<SeqState>();
+    float *X = S.X.as<float>(), *QKV = S.QKV.as<float>(), *GU = S.GU.as<float>();
+    __half *Xh = S.Xh.as<__half>(), *Qh = S.Qh.as<__half>(), *ATTh = S.ATTh.as<__half>(), *Hh = S.Hh.as<__half>();
+    const int32_t *toks = prompt.as<int32_t>() + idx0;
+    launch_embed_rows(m->tok_embd_type, m->tok_embd_raw.p, m->tok_embd_row_bytes, E, toks, T, X, E, st);
+    const int kvs = (int)m->kv_pos_elems();
+    for (int il = 0; il < hp.n_layer; il++) {
+        const Layer &L = m->layers[il];
+        launch_rows_to_f16(X, E, L.attn_norm.as<float>(), hp.rms_eps, E, T, Xh, st);
+        launch_prefill_tc(L.wq.w, Xh, T, QKV, LQ, EPI_STORE, n_sms, st);
+        launch_prefill_tc(L.wk.w, Xh, T, QKV + QD, LQ, EPI_STORE, n_sms, st);
+        launch_prefill_tc(L.wv.w, Xh, T, QKV + QD + KVD, LQ, EPI_STORE, n_sms, st);
+        launch_rope_kv_rows(QKV, Qh, k_cache(il), v_cache(il), m->rope_cos.as<float>(), m->rope_sin.as<float>(), T, pos0, hp.n_head,
+                            hp.n_head_kv, hp.head_dim, hp.n_rot, kvs, st);
+        launch_attn_prefill(Qh, ATTh, k_cache(il), v_cache(il), T, pos0, hp.n_head, hp.n_head_kv, hp.head_dim, kvs, st);
+        launch_prefill_tc(L.wo.w, ATTh, T, X, E, EPI_ADD, n_sms, st);
+        launch_rows_to_f16(X, E, L.ffn_norm.as<float>(), hp.rms_eps, E, T, Xh, st);
+        launch_prefill_tc(L.w_gate.w, Xh, T, GU, 2 * FF, EPI_STORE, n_sms, st);
+        launch_prefill_tc(L.w_up.w, Xh, T, GU + FF, 2 * FF, EPI_STORE, n_sms, st);
+        launch_swiglu_rows_f16(GU, 2 * FF, FF, T, Hh, st);
+        launch_prefill_tc(L.w_down.w, Hh, T, X, E, EPI_ADD, n_sms, st);
+    }
+    // the sequence state after the chunk: position and id of its last token
+    const int32_t last_pos = pos0 + T - 1;
+    CUDA_CHECK(cudaMemcpyAsync(&sd->pos, &last_pos, 4, cudaMemcpyHostToDevice, st));
+    CUDA_CHECK(cudaMemcpyAsync(&sd->cur_token, toks + (T - 1), 4, cudaMemcpyDeviceToDevice, st));
+    CUDA_CHECK(cudaStreamSynchronize(st));  // last_pos is a stack variable
     if (want_logits) {
         CUDA_CHECK(cudaMemsetAsync(&sd->argmax_key, 0, sizeof(unsigned long long), st));
         GemvParams p{};

@@ -68,6 +68,13 @@ struct HParams {
 
 struct Seq;
 
+// activations of one prompt chunk on the tensor-core prefill path (prefill_tc.cu): f32 residual stream and projections,
+// f16 GEMM inputs.  One per model, used under the engine lock, grown to the longest chunk seen.
+struct TcScratch {
+    int cap = 0;  // tokens
+    DevBuf X, Xh, QKV, Qh, ATTh, GU, Hh;
+};
+
 struct Model {
     Engine *eng;
     std::string name, arch, path;
@@ -84,6 +91,8 @@ struct Model {
     // The caller may hold max_batch sequences (aios_seq_create, aios_generate); the library's own sequences
     // (aios_forward_logits' scratch, the request scheduler's batch lanes) are not counted against that budget.
     KvPool kv_pool;
+    TcScratch tc;
+    bool tc_ok = false;   // every matrix has a type the tensor-core prefill GEMM reads (Q4_K / Q6_K / Q8_0)
     int user_seqs = 0;    // live caller-visible sequences (guarded by mu)
     int live_seqs = 0;    // all live sequences (guarded by mu)
     int64_t weight_bytes = 0, weight_bytes_per_token = 0;
@@ -156,6 +165,7 @@ struct Seq {
     void launch_token_pass(bool from_prompt, int prompt_idx, int pos_value, bool want_logits, cudaStream_t st, int *n_launch);
     void launch_sample_kernel(const aios_sampling &sp, cudaStream_t st);
     void prefill_chunk(int idx0, int T, int pos0, bool want_logits, cudaStream_t st);  // tokens prompt[idx0 .. idx0+T)
+    void prefill_tc(int idx0, int T, int pos0, bool want_logits, cudaStream_t st);     // the same on the tensor-core path
     void ensure_graph(const aios_sampling &sp);
     void build_pfd();
     bool use_pfd(const aios_sampling &sp) const;

@@ -96,6 +96,13 @@ void launch_rows_to_f16(const float *x, int64_t ldx, const float *norm_w, float 
 // hh[t][i] = f16(silu(gu[t][i]) * gu[t][ff+i])
 void launch_swiglu_rows_f16(const float *gu, int64_t ldgu, int ff, int T, __half *hh, cudaStream_t st);
 
+// ---- attention_prefill.cu : RoPE + KV append for T tokens, and causal flash attention over the KV range (tensor-core
+// prefill path; f16 operands, f32 soft-max and accumulation)
+void launch_rope_kv_rows(const float *qkv, __half *qh, uint16_t *k_cache, uint16_t *v_cache, const float *cos, const float *sin, int T,
+                         int pos0, int n_head, int n_kv, int hd, int n_rot, int kv_stride, cudaStream_t st);
+void launch_attn_prefill(const __half *qh, __half *out, const uint16_t *k_cache, const uint16_t *v_cache, int T, int pos0, int n_head,
+                         int n_kv, int hd, int kv_stride, cudaStream_t st);
+
 // ---- attention.cu : RoPE + KV write + flash-decode over the f16 KV cache (one new token)
 struct AttnParams {
     const float *qkv;        // [n_head*hd + 2*n_kv*hd] raw projections of the new token

@@ -184,20 +184,31 @@ __device__ __forceinline__ void dequant_row_stage(const WPlanes &w, int64_t row,
         const uint32_t mw = (pq & 2) ? ((pq & 1) ? mt.w : mt.z) : ((pq & 1) ? mt.y : mt.x);
         const uint32_t ddm = __byte_perm(__byte_perm(mt.x, mt.y, 0x0073), __byte_perm(mt.z, mt.w, 0x0073), 0x5410);
         const float2 dd = __half22float2(*reinterpret_cast<const __half2 *>(&ddm));  // (d, dmin)
-        // w = (d*sc)*q - dmin*m per 32-weight sub-block, in f16: scale and offset rounded once each
-        const __half2 s_lo = __float2half2_rn(__fmul_rn(dd.x, (float)(mw & 63)));
-        const __half2 s_hi = __float2half2_rn(__fmul_rn(dd.x, (float)((mw >> 6) & 63)));
-        const __half2 m_lo = __float2half2_rn(-__fmul_rn(dd.y, (float)((mw >> 12) & 63)));
-        const __half2 m_hi = __float2half2_rn(-__fmul_rn(dd.y, (float)((mw >> 18) & 63)));
-        auto nib = [](const uint4 &q, int hi) {
-            return hi ? make_uint4((q.x >> 4) & 0x0F0F0F0Fu, (q.y >> 4) & 0x0F0F0F0Fu, (q.z >> 4) & 0x0F0F0F0Fu, (q.w >> 4) & 0x0F0F0F0Fu)
-                      : make_uint4(q.x & 0x0F0F0F0Fu, q.y & 0x0F0F0F0Fu, q.z & 0x0F0F0F0Fu, q.w & 0x0F0F0F0Fu);
+        // w = (d*sc)*q - dmin*m per 32-weight sub-block: scale and offset stay f32 (q - dmin*m cancels, so an f16 scale
+        // would cost ~10x the error), one rounding to f16 at the end
+        const float s_lo = __fmul_rn(dd.x, (float)(mw & 63)), s_hi = __fmul_rn(dd.x, (float)((mw >> 6) & 63));
+        const float m_lo = -__fmul_rn(dd.y, (float)((mw >> 12) & 63)), m_hi = -__fmul_rn(dd.y, (float)((mw >> 18) & 63));
+        auto deq16 = [&](const uint4 &q, int hi, float sc, float mn, int c) {  // 16 nibbles -> chunks c, c+1
+            const uint32_t wds[4] = {q.x, q.y, q.z, q.w};
+            uint32_t o[8];
+#pragma unroll
+            for (int i = 0; i < 4; i++) {
+                const uint32_t n4 = hi ? (wds[i] >> 4) & 0x0F0F0F0Fu : wds[i] & 0x0F0F0F0Fu;
+#pragma unroll
+                for (int pr = 0; pr < 2; pr++) {
+                    const uint32_t h = h2_sub(bytes_to_h2_1024(n4, pr), H1024);  // exact 0..15
+                    const float2 f = __half22float2(*reinterpret_cast<const __half2 *>(&h));
+                    const __half2 r2 = __floats2half2_rn(__fmaf_rn(f.x, sc, mn), __fmaf_rn(f.y, sc, mn));
+                    o[2 * i + pr] = *reinterpret_cast<const uint32_t *>(&r2);
+                }
+            }
+            store_chunk(a_tile, r, c, make_uint4(o[0], o[1], o[2], o[3]));
+            store_chunk(a_tile, r, c + 1, make_uint4(o[4], o[5], o[6], o[7]));
         };
-        uint4 c0, c1;
-        bytes16_to_chunks<true>(nib(qa, 0), H1024, s_lo, m_lo, c0, c1); store_chunk(a_tile, r, 0, c0); store_chunk(a_tile, r, 1, c1);
-        bytes16_to_chunks<true>(nib(qb, 0), H1024, s_lo, m_lo, c0, c1); store_chunk(a_tile, r, 2, c0); store_chunk(a_tile, r, 3, c1);
-        bytes16_to_chunks<true>(nib(qa, 1), H1024, s_hi, m_hi, c0, c1); store_chunk(a_tile, r, 4, c0); store_chunk(a_tile, r, 5, c1);
-        bytes16_to_chunks<true>(nib(qb, 1), H1024, s_hi, m_hi, c0, c1); store_chunk(a_tile, r, 6, c0); store_chunk(a_tile, r, 7, c1);
+        deq16(qa, 0, s_lo, m_lo, 0);
+        deq16(qb, 0, s_lo, m_lo, 2);
+        deq16(qa, 1, s_hi, m_hi, 4);
+        deq16(qb, 1, s_hi, m_hi, 6);
     } else {  // Q6_K
         // 64 weights [64*kb, +64) = half hh = (kb >> 1) & 1 of block b = kb >> 2, sub-blocks k0 = 2*(kb & 1) and k0 + 1 of
         // BOTH units t = 0, 1: order in K is (t0,k0) (t1,k0) (t0,k0+1) (t1,k0+1), 16 weights each

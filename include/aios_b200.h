@@ -65,6 +65,8 @@ typedef struct aios_engine_opts {
 #define AIOS_ENGINE_USE_PFD 8  /* greedy decode through the persistent fused decode kernel (pfd.cu) */
 #define AIOS_ENGINE_ATTN_CLUSTER 64 /* decode attention: the cluster / DSMEM kernel (attention.cu) at every context length */
 #define AIOS_ENGINE_NO_ROPE_EPILOGUE 256/* RoPE / KV append in the attention kernel instead of the q/k/v GEMV's epilogue */
+#define AIOS_ENGINE_EXACT_PREFILL 2048 /* prompts of every length through the bit-exact integer path (64-token chunks,
+                                           gemm_q.cu); default: prompts of 256+ tokens take the tcgen05 float path (prefill_tc.cu) */
 #define AIOS_ENGINE_NO_GEMM 1024 /* prefill token by token through the decode kernels instead of prompt chunks through the tensor-core GEMM */
 /* (bits 16, 32, 128 and 512 selected round-1 experiments — L2 prefetch, per-head attention, TMA-ring GEMV, producer-side
  * quantisation — that measured slower than the default path and were removed; their profiles are under profiles/r01_*.

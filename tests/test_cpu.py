@@ -228,3 +228,18 @@ def test_replica_bookkeeping_world_size_2_gloo():
     assert res[0][1] == [0, 2, 4, 6] and res[1][1] == [1, 3, 5]
     for r in res:
         assert r[2] == 128.0 * 7 and r[3] == 150.0 and abs(r[4] - 128.0 * 7 / 0.150) < 1e-6
+
+
+@pytest.mark.parametrize("arch,ftype", [("tiny-gqa4", "Q4_K_M"), ("tiny", "Q8_0")])
+def test_oracle_against_exact_math_numpy_reference(oracle, tmp_models, arch, ftype):
+    """A second independent pin of the oracle's model math (the first is the committed HF fp32 fixture): an exact f64
+    numpy forward pass of the dequantised model (oracle/ref_llama.py — its own RoPE, attention and SwiGLU code) must
+    agree with the oracle at every position up to the oracle's activation-quantisation noise."""
+    from oracle import ref_llama
+    path = tmp_models(arch, ftype)
+    prompt = gs.synthetic_prompt(arch, 48, 3)
+    hp, w = ref_llama.load_weights(path, oracle)
+    exact = ref_llama.forward_logits(hp, w, prompt)
+    got = oracle.OracleModel(path, n_ctx=64).eval_all(prompt)
+    assert np.abs(got - exact).max() / exact.std() < 0.15
+    assert np.corrcoef(got[-1], exact[-1])[0, 1] > 0.999

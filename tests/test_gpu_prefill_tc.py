@@ -51,3 +51,56 @@ def test_matmul_tc_with_rmsnorm(engine, oracle):
     xn = xn / np.sqrt((xn ** 2).mean(axis=1, keepdims=True) + 1e-5) * nw
     exact = xn @ oracle.dequantize(qt, w).reshape(n, k).astype(np.float64).T
     assert np.abs(got - exact).max() / np.sqrt(np.mean(exact ** 2)) < 2e-3
+
+
+@pytest.mark.parametrize("arch,ftype", [("tiny-gqa4", "Q4_K_M"), ("tiny", "Q8_0"), ("tiny-mha32", "Q4_K_M")])
+def test_tc_prefill_logits_against_exact_math(oracle, tmp_models, arch, ftype):
+    """Whole path: a 300-token prompt through the tensor-core prefill (tcgen05 GEMMs, RoPE / KV append for all rows, causal
+    flash attention) against an exact f64 forward pass of the dequantised model (oracle/ref_llama.py).
+    Stated tolerance: the last token's logits within 2e-2 of the logit std (f16 operands; measured a few 1e-3).  The
+    bit-exact integer path differs from the same reference by its activation-quantisation noise (~1e-1 of the std),
+    so the float path is the CLOSER of the two to exact arithmetic; the test prints both."""
+    from aios_b200 import capi
+    from oracle import ref_llama
+    path = tmp_models(arch, ftype)
+    prompt = gs.synthetic_prompt(arch, 300, 77)
+    hp, w = ref_llama.load_weights(path, oracle)
+    exact = ref_llama.forward_logits(hp, w, prompt)[-1]
+    sd = exact.std()
+    eng_tc = capi.Engine(device=0, max_batch=1)
+    eng_ex = capi.Engine(device=0, max_batch=1, flags=capi.ENGINE_EXACT_PREFILL)
+    try:
+        m_tc, m_ex = eng_tc.load_model("tc", path, n_ctx=512), eng_ex.load_model("ex", path, n_ctx=512)
+        try:
+            s_tc, s_ex = m_tc.new_seq(), m_ex.new_seq()
+            try:
+                s_tc.prefill(prompt)
+                s_ex.prefill(prompt)
+                l_tc, l_ex = s_tc.logits().astype(np.float64), s_ex.logits().astype(np.float64)
+                e_tc, e_ex = np.abs(l_tc - exact).max() / sd, np.abs(l_ex - exact).max() / sd
+                print(f"{arch} {ftype}: max |logit - exact| / std: tensor-core path {e_tc:.2e}, integer path {e_ex:.2e}")
+                assert e_tc < 2e-2
+                # the KV rows the two paths wrote agree to f16 rounding of slightly different f32 values
+                k1, v1 = s_tc.read_kv(0, 0, 300)
+                k2, v2 = s_ex.read_kv(0, 0, 300)
+                kd = np.abs(k1.view(np.float16).astype(np.float32) - k2.view(np.float16).astype(np.float32)).max()
+                assert kd < 0.1 * np.abs(k2.view(np.float16).astype(np.float32)).std() + 1e-3
+                # decode continues from either cache; report how long the greedy continuations agree
+                a, b = s_tc.decode(32), s_ex.decode(32)
+                agree = int(np.argmax(np.concatenate([a != b, [True]])))
+                print(f"greedy continuation: first {agree} of 32 tokens identical")
+                # a second chunk on top of a cached prefix (positions 300..): attention sees the cached rows
+                more = gs.synthetic_prompt(arch, 280, 78)[: 512 - 300 - 32 - 1]
+                s_tc.reset(); s_tc.prefill(np.concatenate([prompt[:40]]))      # exact (short), then a long chunk at position 40
+                s_tc.prefill(np.concatenate([prompt[40:], more[:100]]))
+                full = ref_llama.forward_logits(hp, w, np.concatenate([prompt, more[:100]]))[-1]
+                assert np.abs(s_tc.logits().astype(np.float64) - full).max() / full.std() < 1.5e-1  # exact prefix: Q8 noise
+            finally:
+                s_tc.free()
+                s_ex.free()
+        finally:
+            m_tc.unload()
+            m_ex.unload()
+    finally:
+        eng_tc.close()
+        eng_ex.close()
