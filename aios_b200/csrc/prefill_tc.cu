@@ -8,7 +8,7 @@
 // Numerics (stated, not bit-exact): weights are rounded to f16 after dequantisation (relative error 2^-12), activations
 // to f16, products are exact, accumulation is f32 over the whole K in TMEM.  This is NOT the llama.cpp CPU arithmetic
 // the decode path reproduces bit for bit (activations there are Q8-quantised, which is ~10x noisier than f16): the
-// tolerance against an exact f64 product of the dequantised weights is 2e-3 of the output's rms
+// tolerance against an exact f64 product of the dequantised weights is 4e-3 (max) / 8e-4 (rms) of the output's rms
 // (tests/test_gpu_prefill_tc.py).  The engine takes this path for long prompts; the bit-exact chunked path
 // (gemm_q.cu) stays available (AIOS_ENGINE_EXACT_PREFILL) and is what short prompts use.
 //

@@ -270,8 +270,8 @@ int aios_matvec(aios_engine *e, int32_t ggml_type, const void *w_blocks, int64_t
 int aios_matmul(aios_engine *e, int32_t ggml_type, const void *w_blocks, int64_t n_rows, int64_t k, const float *x,
                 int32_t n_tok, const float *norm_w, float rms_eps, float *y);
 /* the same product through the prefill path's tensor-core GEMM (prefill_tc.cu: tcgen05 / TMEM, f16 operands, f32
- * accumulation): any n_tok >= 1; Q4_K, Q6_K and Q8_0 weights.  Float arithmetic with a stated tolerance — 2e-3 of the
- * output's rms against an exact product of the dequantised weights — not the bit-exact integer path of aios_matmul. */
+ * accumulation): any n_tok >= 1; Q4_K, Q6_K and Q8_0 weights.  Float arithmetic with a stated tolerance — max error 4e-3,
+ * rms error 8e-4 of the output's rms against an exact product of the dequantised weights — not the bit-exact integer path of aios_matmul. */
 int aios_matmul_tc(aios_engine *e, int32_t ggml_type, const void *w_blocks, int64_t n_rows, int64_t k, const float *x,
                    int32_t n_tok, const float *norm_w, float rms_eps, float *y);
 /* one run of the on-device sampler chain on host logits (parity hook for oracle_sample): mask_bits may be NULL;
