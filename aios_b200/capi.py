@@ -130,6 +130,7 @@ SYMBOLS = {
     "aios_seq_phase_timing": (C.c_int, [_P, _P, C.c_int32, C.POINTER(C.c_int32)]),
     "aios_seq_snapshot": (C.c_int, [_P]),
     "aios_seq_restore": (C.c_int, [_P]),
+    "aios_seq_bench_prefill": (C.c_int, [_P, _P, C.c_int32, C.c_int32, C.POINTER(C.c_float)]),
     "aios_bench_batch_decode": (C.c_int, [_P, C.c_int32, _P, C.c_int32, C.c_int32, _P, C.POINTER(BatchBench)]),
     "aios_bench_gemv": (C.c_int, [_P, C.c_int32, C.c_int64, C.c_int64, C.c_int32, C.c_int32, C.POINTER(C.c_float)]),
 }
@@ -509,6 +510,13 @@ class Seq:
         out = np.empty(n, dtype=np.float32)
         _check(lib().aios_seq_read_activation(self.h, which, _ptr(out), n))
         return out
+
+    def bench_prefill(self, tokens, iters: int = 3) -> float:
+        """ms per prefill of `tokens` from position 0 (aios_seq_bench_prefill, CUDA events)."""
+        toks = np.ascontiguousarray(tokens, dtype=np.int32)
+        ms = C.c_float(0)
+        _check(lib().aios_seq_bench_prefill(self.h, _ptr(toks), toks.size, iters, C.byref(ms)))
+        return ms.value
 
     def profile_decode(self, n_tokens: int) -> BenchResult:
         r = BenchResult()

@@ -955,6 +955,41 @@ int aios_seq_restore(aios_seq *s) {
     });
 }
 
+int aios_seq_bench_prefill(aios_seq *s, const int32_t *tokens, int32_t n, int32_t iters, float *ms_per_prefill) {
+    return guarded([&] {
+        if (!s || !tokens || n <= 0 || iters <= 0 || !ms_per_prefill) return fail(AIOS_E_INVAL, "bad argument");
+        Seq &q = s->impl;
+        if (n > q.m->hp.n_ctx) return fail(AIOS_E_STATE, "prompt does not fit in the context");
+        std::lock_guard<std::mutex> lk(q.m->eng->mu);
+        q.m->eng->make_current();
+        cudaStream_t st = q.m->eng->stream;
+        q.reset();
+        q.prefill(tokens, n);  // warm-up: scratch buffers, tensor maps, function attributes
+        cudaEvent_t e0, e1;
+        CUDA_CHECK(cudaEventCreate(&e0));
+        CUDA_CHECK(cudaEventCreate(&e1));
+        float total = 0.f;
+        const bool prof = getenv("AIOS_PROFILE_STEPS") != nullptr;
+        for (int i = 0; i < iters; i++) {
+            q.reset();
+            CUDA_CHECK(cudaStreamSynchronize(st));
+            if (prof && i == 0) cudaProfilerStart();
+            CUDA_CHECK(cudaEventRecord(e0, st));
+            q.prefill(tokens, n);
+            CUDA_CHECK(cudaEventRecord(e1, st));
+            CUDA_CHECK(cudaEventSynchronize(e1));
+            if (prof && i == 0) cudaProfilerStop();
+            float ms = 0.f;
+            CUDA_CHECK(cudaEventElapsedTime(&ms, e0, e1));
+            total += ms;
+        }
+        cudaEventDestroy(e0);
+        cudaEventDestroy(e1);
+        *ms_per_prefill = total / (float)iters;
+        return (int)AIOS_OK;
+    });
+}
+
 int aios_bench_batch_decode(aios_model *m, int32_t n_lanes, const int32_t *prompts, int32_t n_prompt, int32_t n_steps,
                             int32_t *out_tokens, aios_batch_bench *out) {
     return guarded([&] {

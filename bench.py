@@ -240,6 +240,59 @@ def bench_config4(eng, model, arch: str, ftype: str, peak: float, n_lanes: int =
             "parity_checked": True}
 
 
+def measured_tensor_peak() -> tuple[float, str]:
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        return float(json.load(open(p))["bf16_tflops_sustained"]), "measured (MEASURED_PEAKS.json bf16_tflops_sustained)"
+    except Exception:
+        return 1400.0, "fallback (B200_PROFILING.md ~1.4 PFLOP/s sustained)"
+
+
+def bench_config3(device: int, n_prompt: int = 4096, iters: int = 3):
+    """BASELINE.json configs[2]: Mistral-7B Q8_0, prefill of a 4096-token prompt through the tensor-core path (tcgen05 /
+    TMEM dequant GEMM + causal flash attention).  tok/s and achieved / measured-sustained bf16 TFLOP/s (SURVEY.md §8d:
+    2 * 6.979e9 * T mat-mul + 4 * n_head * hd * T^2 / 2 causal attention FLOPs)."""
+    from aios_b200 import capi
+    arch, ftype = "mistral-7b", "Q8_0"
+    path = ensure_model(arch, ftype, True)
+    eng = capi.Engine(device=device, max_batch=1)  # default flags: prompts of 256+ tokens take the tensor-core path
+    try:
+        m = eng.load_model("bench-q8", path, n_ctx=n_prompt + 8)
+        try:
+            info = m.info
+            a = gs.ARCHS[arch]
+            prompt = gs.synthetic_prompt(arch, n_prompt, SEED + 3)
+            s = m.new_seq()
+            try:
+                ms = s.bench_prefill(prompt, iters)
+                # end to end through the C ABI: token ids from host memory in, the last token's logits back to the host
+                s.reset()
+                t0 = time.perf_counter()
+                s.prefill(prompt)
+                lg = s.logits()
+                e2e_s = time.perf_counter() - t0
+                finite = bool(np.isfinite(lg).all())
+            finally:
+                s.free()
+            per_tok_mm = 2.0 * a.n_layer * (a.n_embd * (a.n_head * a.head_dim + 2 * a.n_head_kv * a.head_dim) + a.n_head * a.head_dim * a.n_embd + 3 * a.n_embd * a.n_ff)
+            flop = per_tok_mm * n_prompt + 4.0 * a.n_layer * a.n_head * a.head_dim * n_prompt * n_prompt / 2.0
+            peak, src = measured_tensor_peak()
+            tflops = flop / (ms * 1e-3) / 1e12
+            return {"workload": f"{arch} {ftype} prefill of a {n_prompt}-token prompt (BASELINE.json configs[2]), tensor-core path: "
+                                "tcgen05 / TMEM dequant GEMM, TMA-staged f16 activations, causal flash attention",
+                    "value": n_prompt / (ms * 1e-3), "unit": "tok/s", "ms_per_prefill": ms, "iters": iters,
+                    "flop_per_prefill": flop, "roofline": {"bound": "tensor", "achieved": tflops, "peak": peak, "unit": "TFLOP/s",
+                                                           "frac": tflops / peak, "peak_source": src},
+                    "roofline_tok_s": n_prompt / (flop / (peak * 1e12)),
+                    "e2e": {"value": n_prompt / e2e_s, "unit": "tok/s", "h2d_bytes_per_step": 4 * n_prompt,
+                            "d2h_bytes_per_step": 4 * info.n_vocab, "api": "aios_seq_prefill (host token ids) + aios_seq_logits"},
+                    "numerics": "f16 operands, f32 accumulation; stated tolerance in tests/test_gpu_prefill_tc.py", "logits_finite": finite}
+        finally:
+            m.unload()
+    finally:
+        eng.close()
+
+
 def in_graph_breakdown(seq, n_runs: int = 4):
     """Per-token time of each launch kind INSIDE the token pass, from the %globaltimer marks the kernels themselves take
     (aios_seq_trace_decode: same launch order and programmatic-dependent-launch attributes as the captured graph).
@@ -313,7 +366,9 @@ def main():
     path = ensure_model(args.arch, args.ftype, writer=(local_rank == 0))
     barrier()
     n_ctx = args.prompt + args.gen
-    eng = capi.Engine(device=local_rank, max_batch=3)  # seq, seq_e2e, and a temporary one for the parity spot checks
+    # seq, seq_e2e, and a temporary sequence for the parity spot checks; the 384-token prompt goes through the bit-exact
+    # integer prefill so that the decode that follows can be checked against the oracle token by token
+    eng = capi.Engine(device=local_rank, max_batch=3, flags=capi.ENGINE_EXACT_PREFILL)
     model = eng.load_model("bench", path, n_ctx=n_ctx)
     info = model.info
     seq = model.new_seq()
@@ -411,6 +466,12 @@ def main():
         finally:
             tl.unload()
 
+    config3 = None
+    if rank == 0 and world == 1 and not args.no_subrecords:
+        seq.free(); seq_e2e.free(); model.unload(); eng.close()
+        seq = seq_e2e = model = eng = None
+        config3 = bench_config3(local_rank)
+
     if rank == 0:
         # the dominant kernel's in-graph time must fit inside the token it is part of
         fits = ig["us_gemv"] <= us_token * 1.05 and ig["us_token"] <= us_token * 1.25
@@ -453,11 +514,14 @@ def main():
             line["cpu_baseline"] = cpu
         if config4:
             line["config4"] = config4
+        if config3:
+            line["config3"] = config3
         print(json.dumps(line), flush=True)
-    seq.free()
-    seq_e2e.free()
-    model.unload()
-    eng.close()
+    if eng is not None:
+        seq.free()
+        seq_e2e.free()
+        model.unload()
+        eng.close()
     if world > 1:
         dist.destroy_process_group()
 

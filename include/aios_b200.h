@@ -315,6 +315,10 @@ int aios_seq_trace_decode(aios_seq *s, uint64_t *out, int32_t cap_launches, int3
  * fused launch: out[n_phases][4] = phase start, after the activation prologue, after the compute loop, after the grid
  * barrier.  *n_phases returns the phase count; cap = capacity of out in phases. */
 int aios_seq_phase_timing(aios_seq *s, uint64_t *out, int32_t cap, int32_t *n_phases);
+/* prefill of an n-token prompt from position 0 (bench.py configs[2]): the sequence is reset, one untimed prefill warms
+ * the path up, then `iters` prefills are timed with CUDA events on the engine's stream (token ids already on the host
+ * side of the call: the 4n-byte H2D is inside the timed region, like in aios_seq_prefill).  The sequence ends prefilled. */
+int aios_seq_bench_prefill(aios_seq *s, const int32_t *tokens, int32_t n, int32_t iters, float *ms_per_prefill);
 /* batched decode as the continuous batcher runs it (bench.py configs[3]): n_lanes sequences are admitted with their
  * n_prompt-token prompts (prompts[n_lanes][n_prompt]), then n_steps greedy steps run — one token per lane per step, the
  * first step untimed (it captures the step's CUDA graph), the others timed with CUDA events on the engine's stream,
