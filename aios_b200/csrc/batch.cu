@@ -147,38 +147,36 @@ void Batch::launch_step(cudaStream_t st, int *n_launch) {
         launch_gemm_multi(g, st);
         launches++;
     };
-    const bool split_ok = attn_split_usable(hp.n_ctx, hp.head_dim);
+    const bool batch_ok = attn_batch_usable(hp.n_head, hp.n_head_kv, hp.n_ctx, hp.head_dim);
     for (int il = 0; il < hp.n_layer; il++) {
         const Layer &L = m->layers[il];
         matmul({&L.wq.w, &L.wk.w, &L.wv.w}, {qkv, qkv + QD, qkv + QD + KVD}, x, E, L.attn_norm.as<float>(), LQ, EPI_STORE);
-        {   // RoPE + KV append + attention, every lane over its own KV range
-            AttnParams a{};
+        if (batch_ok) {   // RoPE + KV append + attention: one CTA per (lane, kv head), every lane over its own KV range
+            AttnBatchParams a{};
             a.qkv = qkv; a.out = att;
             a.rope_cos = m->rope_cos.as<float>(); a.rope_sin = m->rope_sin.as<float>();
-            a.n_head = hp.n_head; a.n_kv = hp.n_head_kv; a.hd = hp.head_dim; a.n_rot = hp.n_rot;
-            a.n_split = m->attn_splits; a.n_ctx = hp.n_ctx;
+            a.lane_pos = POS.as<int32_t>(); a.lane_kv = KVB.as<uint16_t *>();
+            a.k_off = (int64_t)(((size_t)il * 2 + 0) * m->kvd()); a.v_off = (int64_t)(((size_t)il * 2 + 1) * m->kvd());
+            a.lane_qkv_stride = LQ; a.lane_out_stride = QD;
+            a.n_head = hp.n_head; a.n_kv = hp.n_head_kv; a.hd = hp.head_dim; a.n_rot = hp.n_rot; a.n_ctx = hp.n_ctx;
+            a.kv_stride = (int32_t)m->kv_pos_elems(); a.kv_ready = 0;
             a.scale = 1.0f / sqrtf((float)hp.head_dim);
-            a.kv_stride = (int32_t)m->kv_pos_elems();
-            a.kv_ready = 0;
-            if (split_ok) {
-                // this layer's K / V rows inside a position block, as byte offsets carried in the pointer fields
-                a.k_cache = reinterpret_cast<uint16_t *>((uintptr_t)(((size_t)il * 2 + 0) * m->kvd() * 2));
-                a.v_cache = reinterpret_cast<uint16_t *>((uintptr_t)(((size_t)il * 2 + 1) * m->kvd() * 2));
-                a.n_lanes = T; a.lane_qkv_stride = LQ; a.lane_out_stride = QD;
-                a.lane_pos = POS.as<int32_t>(); a.lane_kv = KVB.as<uint16_t *>();
-                launch_attn_decode_split(a, st, false);
+            launch_attn_batch(a, T, st);
+            launches++;
+        } else {  // very long contexts: the cluster kernel, lane by lane
+            for (int l = 0; l < T; l++) {
+                AttnParams b{};
+                Seq &s = *seqs[(size_t)l];
+                b.qkv = qkv + (size_t)l * LQ; b.out = att + (size_t)l * QD;
+                b.k_cache = s.k_cache(il); b.v_cache = s.v_cache(il); b.kv_stride = (int32_t)m->kv_pos_elems();
+                b.rope_cos = m->rope_cos.as<float>(); b.rope_sin = m->rope_sin.as<float>();
+                b.n_past_ptr = POS.as<int32_t>() + l;
+                b.scratch = s.attn_scratch.as<float>(); b.counters = s.attn_counters.as<uint32_t>();
+                b.n_head = hp.n_head; b.n_kv = hp.n_head_kv; b.hd = hp.head_dim; b.n_rot = hp.n_rot;
+                b.n_split = m->attn_splits; b.n_ctx = hp.n_ctx;
+                b.scale = 1.0f / sqrtf((float)hp.head_dim);
+                launch_attn_decode(b, st, false, 2);
                 launches++;
-            } else {  // long contexts: the cluster kernel, lane by lane
-                for (int l = 0; l < T; l++) {
-                    AttnParams b = a;
-                    Seq &s = *seqs[(size_t)l];
-                    b.qkv = qkv + (size_t)l * LQ; b.out = att + (size_t)l * QD;
-                    b.k_cache = s.k_cache(il); b.v_cache = s.v_cache(il);
-                    b.n_past_ptr = POS.as<int32_t>() + l;
-                    b.scratch = s.attn_scratch.as<float>(); b.counters = s.attn_counters.as<uint32_t>();
-                    launch_attn_decode(b, st, false, 2);
-                    launches++;
-                }
             }
         }
         matmul({&L.wo.w}, {x}, att, QD, nullptr, E, EPI_ADD);
@@ -197,7 +195,7 @@ void Batch::step() {
     cudaStream_t st = m->eng->stream;
     for (int i = 0; i < n; i++) seqs[(size_t)i]->ensure_kv(seqs[(size_t)i]->n_past + 1);  // the token fed this step
     if (dirty) { upload_lane_state(st); dirty = false; }
-    const bool use_graph = !(m->eng->flags & AIOS_ENGINE_NO_GRAPH) && attn_split_usable(m->hp.n_ctx, m->hp.head_dim);
+    const bool use_graph = !(m->eng->flags & AIOS_ENGINE_NO_GRAPH);
     if (use_graph) {
         cudaGraphExec_t &ge = graphs[(size_t)n];
         if (!ge) {

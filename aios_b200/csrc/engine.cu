@@ -516,7 +516,7 @@ void Seq::prefill_chunk(int idx0, int T, int pos0, bool want_logits, cudaStream_
     SeqState *sd = state.as<SeqState>();
     if (!cx.p) {  // first chunk of this sequence: room for CH tokens side by side
         cx = DevBuf((size_t)CH * E * 4); cqkv = DevBuf((size_t)CH * LQ * 4); catt = DevBuf((size_t)CH * QD * 4);
-        ch = DevBuf((size_t)CH * FF * 4); cgu = DevBuf((size_t)CH * 2 * FF * 4);
+        ch = DevBuf((size_t)CH * FF * 4); cgu = DevBuf((size_t)CH * 2 * FF * 4); cqh = DevBuf((size_t)CH * QD * 2);
         cimg = DevBuf(2 * gemm_images_bytes(std::max(std::max(E, QD), FF), CH)); cpos = DevBuf(CH * 4);
         CUDA_CHECK(cudaMemsetAsync(cx.p, 0, cx.bytes, st)); CUDA_CHECK(cudaMemsetAsync(catt.p, 0, catt.bytes, st));
         CUDA_CHECK(cudaMemsetAsync(ch.p, 0, ch.bytes, st));  // rows of padding tokens stay zero (finite images)
@@ -568,6 +568,21 @@ void Seq::prefill_chunk(int idx0, int T, int pos0, bool want_logits, cudaStream_
     for (int il = 0; il < hp.n_layer; il++) {
         const Layer &L = m->layers[il];
         matmul({&L.wq.w, &L.wk.w, &L.wv.w}, {QKV, QKV + QD, QKV + QD + KVD}, X, E, L.attn_norm.as<float>(), LQ, EPI_STORE);
+        if (attn_batch_usable(hp.n_head, hp.n_head_kv, hp.n_ctx, hp.head_dim)) {
+            // RoPE + KV append for all T rows first (token t must see the rows of the tokens before it), then attention
+            // with one CTA per (token, kv head); same operations as the single-token kernels, bit for bit
+            launch_rope_kv_rows(QKV, cqh.as<__half>(), k_cache(il), v_cache(il), m->rope_cos.as<float>(), m->rope_sin.as<float>(), T,
+                                pos0, hp.n_head, hp.n_head_kv, hp.head_dim, hp.n_rot, (int)m->kv_pos_elems(), st);
+            AttnBatchParams a{};
+            a.qh = cqh.as<__half>(); a.out = ATT;
+            a.lane_pos = POS; a.lane_kv = nullptr; a.kv_base = kv.as<uint16_t>();
+            a.k_off = (int64_t)(((size_t)il * 2 + 0) * m->kvd()); a.v_off = (int64_t)(((size_t)il * 2 + 1) * m->kvd());
+            a.lane_out_stride = QD;
+            a.n_head = hp.n_head; a.n_kv = hp.n_head_kv; a.hd = hp.head_dim; a.n_rot = hp.n_rot; a.n_ctx = hp.n_ctx;
+            a.kv_stride = (int32_t)m->kv_pos_elems(); a.kv_ready = 1;
+            a.scale = 1.0f / sqrtf((float)hp.head_dim);
+            launch_attn_batch(a, T, st);
+        } else
         for (int t = 0; t < T; t++) {  // RoPE + KV append + attention, token by token (each sees the rows before it)
             AttnParams a{};
             a.qkv = QKV + (size_t)t * LQ; a.out = ATT + (size_t)t * QD;

@@ -131,7 +131,7 @@ struct Seq {
     int snap_n_past = -1;
     struct KernelTimer *timer = nullptr;  // non-null only inside profile_decode
     // prompt chunks (prefill_chunk): activations of up to 32 tokens side by side, their quantised images, positions
-    DevBuf cx, cqkv, catt, ch, cgu, cimg, cpos;
+    DevBuf cx, cqkv, catt, ch, cgu, cimg, cpos, cqh;
     DevBuf trace;
     DevBuf mask;           // optional logit mask (n_vocab bits), see set_mask
     bool mask_on = false;

@@ -140,6 +140,23 @@ void launch_attn_decode_split(const AttnParams &p, cudaStream_t st, bool pdl);
 void attn_init();  // one-time function attributes (dynamic smem)
 size_t attn_scratch_floats(int n_head, int n_split, int hd);
 
+// ---- attention_batch.cu : decode attention for many (sequence, token) lanes at once, one CTA per (lane, kv head)
+struct AttnBatchParams {
+    const float *qkv;          // kv_ready = 0: [lane] raw q|k|v projections, lane stride lane_qkv_stride floats
+    const __half *qh;          // kv_ready = 1: [lane][n_head*hd] q, roped and rounded
+    float *out;                // [lane] attention output, lane stride lane_out_stride floats
+    const float *rope_cos, *rope_sin;
+    const int32_t *lane_pos;   // device [lanes]: cached positions before the lane's token (= its position)
+    uint16_t *const *lane_kv;  // device [lanes]: base of each lane's KV range, or null: every lane uses kv_base
+    uint16_t *kv_base;
+    int64_t k_off, v_off;      // this layer's K / V rows inside a position block (f16 elements)
+    int64_t lane_qkv_stride, lane_out_stride;
+    int32_t n_head, n_kv, hd, n_rot, n_ctx, kv_stride, kv_ready;
+    float scale;
+};
+bool attn_batch_usable(int n_head, int n_kv, int n_ctx, int hd);
+void launch_attn_batch(const AttnBatchParams &p, int n_lanes, cudaStream_t st);
+
 // ---- sampler.cu
 struct SampleParams {
     const float *logits;
