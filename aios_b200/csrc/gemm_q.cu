@@ -49,10 +49,9 @@ void launch_quant_rows(int weight_type, const float *x, int64_t ldx, const float
 size_t gemm_images_bytes(int k, int T) { return gemm_image_stride(k) * (size_t)T; }
 
 // ---------------------------------------------------------------- the GEMM
-constexpr int GEMM_RG = 2;                  // m16 row groups per CTA
-constexpr int GEMM_ROWS = GEMM_RG * 16;     // weight rows per CTA
+constexpr int GEMM_MAX_ROWS = 32;           // weight rows per CTA: 16 * RG, RG = 1 or 2 m16 row groups (template parameter)
 constexpr int GEMM_TOK_STRIDE = 17;         // uint4 per token in the staged block: 16 used + 1 pad (bank spread over tokens)
-constexpr int GEMM_STAGES = 3;
+constexpr int GEMM_STAGES = 2;
 
 __device__ __forceinline__ void mma_s8_k32(int (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
     asm volatile(
@@ -127,13 +126,13 @@ __device__ __forceinline__ void stage_images(const ImgSmem &s, const uint8_t *im
 //   Q6_K: la[rows][5] | lb[rows][5] | hh[rows][5] | sc[rows] uint4 (4 units x 4 i8) | d[rows] u32 (the aligned word
 //         holding the f16 block scale)
 template <int TYPE> struct TileA;
-template <> struct TileA<T_Q4_K> { static constexpr int RS = 5; static constexpr size_t bytes = (size_t)GEMM_ROWS * (2 * RS + 1) * 16; };
-template <> struct TileA<T_Q8_0> { static constexpr int RS = 9; static constexpr size_t bytes = (size_t)GEMM_ROWS * (2 * RS + 1) * 16; };
-template <> struct TileA<T_Q6_K> { static constexpr int RS = 5; static constexpr size_t bytes = (size_t)GEMM_ROWS * (3 * RS + 1) * 16 + GEMM_ROWS * 4; };
+template <> struct TileA<T_Q4_K> { static constexpr int RS = 5; static constexpr size_t bytes = (size_t)GEMM_MAX_ROWS * (2 * RS + 1) * 16; };
+template <> struct TileA<T_Q8_0> { static constexpr int RS = 9; static constexpr size_t bytes = (size_t)GEMM_MAX_ROWS * (2 * RS + 1) * 16; };
+template <> struct TileA<T_Q6_K> { static constexpr int RS = 5; static constexpr size_t bytes = (size_t)GEMM_MAX_ROWS * (3 * RS + 1) * 16 + GEMM_MAX_ROWS * 4; };
 constexpr size_t GEMM_A_BYTES = TileA<T_Q8_0>::bytes;  // the largest: one stage layout for every type
 static_assert(TileA<T_Q6_K>::bytes <= GEMM_A_BYTES && TileA<T_Q4_K>::bytes <= GEMM_A_BYTES, "stage layout");
 
-template <int TYPE>
+template <int TYPE, int GEMM_ROWS>
 __device__ __forceinline__ void stage_weights(uint8_t *sa, const WPlanes &w, int row0, int b, int nthreads) {
     constexpr int RS = TileA<TYPE>::RS, UPB = TYPE == T_Q8_0 ? 8 : 4;  // units per 256-weight block
     const size_t U = (size_t)w.k / (TYPE == T_Q8_0 ? 32 : 64), nb = (size_t)w.k / 256;
@@ -176,8 +175,9 @@ struct GemmParams {
 };
 
 // the k-loop of one CTA for weight type TYPE
-template <int TYPE, int NT, int TW>
+template <int TYPE, int NT, int TW, int GEMM_RG>
 __device__ __forceinline__ void gemm_body(const GemmParams &p, int seg, uint8_t *smem) {
+    constexpr int GEMM_ROWS = GEMM_RG * 16;
     constexpr int T = 8 * NT * TW, RS = TileA<TYPE>::RS, NTHREADS = GEMM_RG * TW * 32;
     const size_t stage_bytes = GEMM_A_BYTES + gemm_img_bytes(T);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -199,17 +199,14 @@ __device__ __forceinline__ void gemm_body(const GemmParams &p, int seg, uint8_t 
 
     auto stage = [&](int b) {
         uint8_t *base = smem + (size_t)(b % GEMM_STAGES) * stage_bytes;
-        stage_weights<TYPE>(base, W, row0, b, NTHREADS);
+        stage_weights<TYPE, GEMM_ROWS>(base, W, row0, b, NTHREADS);
         stage_images<TYPE>(img_carve(base + GEMM_A_BYTES, T), p.images[seg], img_stride, k, T, b, NTHREADS);
         asm volatile("cp.async.commit_group;" ::: "memory");
     };
     stage(0);
-    if (nb > 1) stage(1);
     for (int b = 0; b < nb; b++) {
-        if (b + 2 < nb) {
-            stage(b + 2);
-            asm volatile("cp.async.wait_group 2;" ::: "memory");
-        } else if (b + 1 < nb) {
+        if (b + 1 < nb) {  // the next block's copies fly while this one is multiplied
+            stage(b + 1);
             asm volatile("cp.async.wait_group 1;" ::: "memory");
         } else {
             asm volatile("cp.async.wait_group 0;" ::: "memory");
@@ -348,15 +345,15 @@ __device__ __forceinline__ void gemm_body(const GemmParams &p, int seg, uint8_t 
         }
 }
 
-template <int NT, int TW>
+template <int NT, int TW, int GEMM_RG>
 __global__ void __launch_bounds__(GEMM_RG * TW * 32) gemm_q_kernel(const GemmParams p) {
     extern __shared__ __align__(16) uint8_t smem[];
     int seg = 0;
     while (seg + 1 < p.n_seg && (int)blockIdx.x >= p.tile_begin[seg + 1]) seg++;
     const int type = p.seg[seg].type;  // CTA-uniform
-    if (type == T_Q4_K) gemm_body<T_Q4_K, NT, TW>(p, seg, smem);
-    else if (type == T_Q6_K) gemm_body<T_Q6_K, NT, TW>(p, seg, smem);
-    else gemm_body<T_Q8_0, NT, TW>(p, seg, smem);
+    if (type == T_Q4_K) gemm_body<T_Q4_K, NT, TW, GEMM_RG>(p, seg, smem);
+    else if (type == T_Q6_K) gemm_body<T_Q6_K, NT, TW, GEMM_RG>(p, seg, smem);
+    else gemm_body<T_Q8_0, NT, TW, GEMM_RG>(p, seg, smem);
 }
 
 static size_t gemm_smem_bytes(int T) { return GEMM_STAGES * (GEMM_A_BYTES + gemm_img_bytes(T)); }
@@ -381,35 +378,49 @@ bool gemm_q_usable(int type, int k) { return (type == T_Q4_K || type == T_Q6_K |
 // images of tokens T..pad(T)-1 (padding) must exist (any finite contents); their outputs are not stored.
 int gemm_pad_tokens(int T) { return T <= 32 ? (T + 7) / 8 * 8 : GEMM_MAX_TOKENS; }
 
+static int n_sms_hint() {
+    int dev = 0, n = 148;
+    if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&n, cudaDevAttrMultiProcessorCount, dev);
+    return n;
+}
+
 void launch_gemm_multi(const GemmMulti &m, cudaStream_t st) {
     if (m.T < 1 || m.T > GEMM_MAX_TOKENS) throw CudaError("launch_gemm: 1..64 tokens per call");
     if (m.n_seg < 1 || m.n_seg > 3) throw CudaError("launch_gemm: 1..3 segments");
     GemmParams p{};
     p.n_seg = m.n_seg; p.T = m.T; p.epi = m.epi; p.ldo = m.ldo;
+    int64_t total_rows = 0;
+    for (int i = 0; i < m.n_seg; i++) total_rows += m.seg[i].n_rows;
+    // 32-row CTAs when that still gives the machine >= 2 CTAs per SM, else 16-row CTAs (twice as many)
+    const int rg = (total_rows / 32 >= 2 * n_sms_hint()) ? 2 : 1;
+    const int rows_per_cta = 16 * rg;
     int tiles = 0;
     for (int i = 0; i < m.n_seg; i++) {
         if (!gemm_q_usable(m.seg[i].type, m.seg[i].k)) throw CudaError("launch_gemm: Q4_K / Q6_K / Q8_0 weights only");
         if (m.seg[i].k != m.seg[0].k) throw CudaError("launch_gemm: segments must share K");
         p.seg[i] = m.seg[i]; p.out[i] = m.out[i]; p.images[i] = m.images[i];
         p.tile_begin[i] = tiles;
-        tiles += (m.seg[i].n_rows + GEMM_ROWS - 1) / GEMM_ROWS;
+        tiles += (m.seg[i].n_rows + rows_per_cta - 1) / rows_per_cta;
     }
     for (int i = m.n_seg; i < 4; i++) p.tile_begin[i] = tiles;
     const int Tp = gemm_pad_tokens(m.T);
     const size_t smem = gemm_smem_bytes(Tp);
-#define GEMM_LAUNCH(NTV, TWV)                                                                                         \
+#define GEMM_LAUNCH(NTV, TWV, RGV)                                                                                    \
     do {                                                                                                              \
         static PerDeviceOnce once;                                                                                    \
-        once.run([] { CUDA_CHECK(cudaFuncSetAttribute(gemm_q_kernel<NTV, TWV>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024)); }); \
-        gemm_q_kernel<NTV, TWV><<<tiles, GEMM_RG * TWV * 32, smem, st>>>(p);                                          \
+        once.run([] { CUDA_CHECK(cudaFuncSetAttribute(gemm_q_kernel<NTV, TWV, RGV>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024)); }); \
+        gemm_q_kernel<NTV, TWV, RGV><<<tiles, RGV * TWV * 32, smem, st>>>(p);                                         \
     } while (0)
+#define GEMM_LAUNCH_RG(NTV, TWV) do { if (rg == 2) GEMM_LAUNCH(NTV, TWV, 2); else GEMM_LAUNCH(NTV, TWV, 1); } while (0)
+    // tokens per warp = 8 * NT; token groups per CTA = TW: more, smaller warps keep more of them in flight per SM
     switch (Tp) {
-        case 8: GEMM_LAUNCH(1, 1); break;
-        case 16: GEMM_LAUNCH(2, 1); break;
-        case 24: GEMM_LAUNCH(3, 1); break;
-        case 32: GEMM_LAUNCH(4, 1); break;
-        default: GEMM_LAUNCH(4, 2); break;
+        case 8: GEMM_LAUNCH_RG(1, 1); break;
+        case 16: GEMM_LAUNCH_RG(1, 2); break;
+        case 24: GEMM_LAUNCH_RG(1, 3); break;
+        case 32: GEMM_LAUNCH_RG(2, 2); break;
+        default: GEMM_LAUNCH_RG(2, 4); break;
     }
+#undef GEMM_LAUNCH_RG
 #undef GEMM_LAUNCH
     CUDA_CHECK(cudaGetLastError());
 }
