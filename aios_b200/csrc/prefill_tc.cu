@@ -151,18 +151,50 @@ __device__ __forceinline__ void bytes16_to_chunks(const uint4 &q, uint32_t offse
     c1 = make_uint4(o[4], o[5], o[6], o[7]);
 }
 
+// The quantised bytes of one (row, 64-weight stage): requested one stage AHEAD of their use, so that the L2 / HBM
+// latency of stage kb+1 hides behind the conversion of stage kb (the loads do not depend on the stage's smem slot).
+struct RawStage {
+    uint4 v[6];
+    uint32_t s[2];
+    unsigned short d;
+};
+template <int TYPE>
+__device__ __forceinline__ void load_raw_stage(const WPlanes &w, int64_t row, int kb, RawStage &R) {
+    if (TYPE == T_Q8_0) {
+        const int64_t u = row * (w.k / 32) + 2 * kb;
+        R.v[0] = __ldg(reinterpret_cast<const uint4 *>(w.p[0] + u * 16));
+        R.v[1] = __ldg(reinterpret_cast<const uint4 *>(w.p[1] + u * 16));
+        R.v[2] = __ldg(reinterpret_cast<const uint4 *>(w.p[0] + (u + 1) * 16));
+        R.v[3] = __ldg(reinterpret_cast<const uint4 *>(w.p[1] + (u + 1) * 16));
+        R.s[0] = __ldg(reinterpret_cast<const uint32_t *>(w.p[2] + u * 2));  // two f16 scales (u is even: 4-byte aligned)
+    } else if (TYPE == T_Q4_K) {
+        const int64_t u = row * (w.k / 64) + kb;
+        R.v[0] = __ldg(reinterpret_cast<const uint4 *>(w.p[0] + u * 16));
+        R.v[1] = __ldg(reinterpret_cast<const uint4 *>(w.p[1] + u * 16));
+        R.v[2] = __ldg(reinterpret_cast<const uint4 *>(w.p[2] + (row * (w.k / 256) + (kb >> 2)) * 16));
+    } else {
+        const int b = kb >> 2, hh = (kb >> 1) & 1;
+        const int64_t u = row * (w.k / 64) + 4 * b + 2 * hh;
+#pragma unroll
+        for (int t = 0; t < 2; t++) {
+            R.v[3 * t + 0] = __ldg(reinterpret_cast<const uint4 *>(w.p[0] + (u + t) * 16));
+            R.v[3 * t + 1] = __ldg(reinterpret_cast<const uint4 *>(w.p[1] + (u + t) * 16));
+            R.v[3 * t + 2] = __ldg(reinterpret_cast<const uint4 *>(w.p[2] + (u + t) * 16));
+            R.s[t] = __ldg(reinterpret_cast<const uint32_t *>(w.p[3] + (u + t) * 4));
+        }
+        R.d = __ldg(reinterpret_cast<const unsigned short *>(w.p[4] + (row * (w.k / 256) + b) * 2));
+    }
+}
+
 // one thread = one weight row: dequantise the 64 weights [64*kb, 64*kb+64) of `row` into row r of the A tile
 template <int TYPE>
-__device__ __forceinline__ void dequant_row_stage(const WPlanes &w, int64_t row, int kb, uint8_t *a_tile, int r) {
+__device__ __forceinline__ void dequant_row_stage(const RawStage &R, int kb, uint8_t *a_tile, int r) {
     const uint32_t H1024 = 0x64006400u;  // half2(1024, 1024)
     if (TYPE == T_Q8_0) {
-        const int64_t U8 = w.k / 32;
 #pragma unroll
         for (int blk = 0; blk < 2; blk++) {
-            const int64_t u = row * U8 + 2 * kb + blk;
-            uint4 qa = __ldg(reinterpret_cast<const uint4 *>(w.p[0] + u * 16));
-            uint4 qb = __ldg(reinterpret_cast<const uint4 *>(w.p[1] + u * 16));
-            const __half d = __ushort_as_half(__ldg(reinterpret_cast<const unsigned short *>(w.p[2] + u * 2)));
+            uint4 qa = R.v[2 * blk], qb = R.v[2 * blk + 1];
+            const __half d = __ushort_as_half((unsigned short)(R.s[0] >> (16 * blk)));
             const __half2 s = __half2half2(d), z = __half2half2(__ushort_as_half((unsigned short)0));
             // signed bytes: b ^ 0x80 is the value + 128 as an unsigned byte -> subtract 1024 + 128
             qa.x ^= 0x80808080u; qa.y ^= 0x80808080u; qa.z ^= 0x80808080u; qa.w ^= 0x80808080u;
@@ -175,11 +207,7 @@ __device__ __forceinline__ void dequant_row_stage(const WPlanes &w, int64_t row,
         }
     } else if (TYPE == T_Q4_K) {
         // unit kb of the row: k 0-15 QSa low nibbles, 16-31 QSb low, 32-47 QSa high, 48-63 QSb high (layout.cuh)
-        const int64_t U = w.k / 64, nb = w.k / 256;
-        const int64_t u = row * U + kb;
-        const uint4 qa = __ldg(reinterpret_cast<const uint4 *>(w.p[0] + u * 16));
-        const uint4 qb = __ldg(reinterpret_cast<const uint4 *>(w.p[1] + u * 16));
-        const uint4 mt = __ldg(reinterpret_cast<const uint4 *>(w.p[2] + (row * nb + (kb >> 2)) * 16));
+        const uint4 qa = R.v[0], qb = R.v[1], mt = R.v[2];
         const int pq = kb & 3;
         const uint32_t mw = (pq & 2) ? ((pq & 1) ? mt.w : mt.z) : ((pq & 1) ? mt.y : mt.x);
         const uint32_t ddm = __byte_perm(__byte_perm(mt.x, mt.y, 0x0073), __byte_perm(mt.z, mt.w, 0x0073), 0x5410);
@@ -212,17 +240,13 @@ __device__ __forceinline__ void dequant_row_stage(const WPlanes &w, int64_t row,
     } else {  // Q6_K
         // 64 weights [64*kb, +64) = half hh = (kb >> 1) & 1 of block b = kb >> 2, sub-blocks k0 = 2*(kb & 1) and k0 + 1 of
         // BOTH units t = 0, 1: order in K is (t0,k0) (t1,k0) (t0,k0+1) (t1,k0+1), 16 weights each
-        const int64_t U = w.k / 64, nb = w.k / 256;
-        const int b = kb >> 2, hh = (kb >> 1) & 1, k0 = 2 * (kb & 1);
-        const __half d = __ushort_as_half(__ldg(reinterpret_cast<const unsigned short *>(w.p[4] + (row * nb + b) * 2)));
+        const int k0 = 2 * (kb & 1);
+        const __half d = __ushort_as_half(R.d);
         const float df = __half2float(d);
 #pragma unroll
         for (int t = 0; t < 2; t++) {
-            const int64_t u = row * U + 4 * b + 2 * hh + t;
-            const uint4 la = __ldg(reinterpret_cast<const uint4 *>(w.p[0] + u * 16));
-            const uint4 lb = __ldg(reinterpret_cast<const uint4 *>(w.p[1] + u * 16));
-            const uint4 qh = __ldg(reinterpret_cast<const uint4 *>(w.p[2] + u * 16));
-            const uint32_t scw = __ldg(reinterpret_cast<const uint32_t *>(w.p[3] + u * 4));
+            const uint4 la = R.v[3 * t], lb = R.v[3 * t + 1], qh = R.v[3 * t + 2];
+            const uint32_t scw = R.s[t];
             const uint32_t LA[4] = {la.x, la.y, la.z, la.w}, LB[4] = {lb.x, lb.y, lb.z, lb.w}, QH[4] = {qh.x, qh.y, qh.z, qh.w};
             uint4 v0, v1;  // 6-bit values of sub-blocks k0 and k0 + 1
             uint32_t *p0 = &v0.x, *p1 = &v1.x;
@@ -333,13 +357,21 @@ __global__ void __launch_bounds__(TC_THREADS, 1) prefill_tc_kernel(const __grid_
         for (int tile = blockIdx.x; tile < n_tiles_total; tile += gridDim.x) {
             const int m_blk = tile / p.n_tiles;
             const int64_t row = min(m_blk * TC_BM + r, p.w.n_rows - 1);  // rows beyond N repeat the last one (never stored)
-            for (int kb = 0; kb < n_kb; kb++, it++) {
+            RawStage ra, rb;  // ping-pong: the stage being converted and the one in flight
+            load_raw_stage<TYPE>(p.w, row, 0, ra);
+            auto do_stage = [&](const RawStage &cur, RawStage &nxt, int kb) {
                 const int s = it % TC_STAGES;
+                if (kb + 1 < n_kb) load_raw_stage<TYPE>(p.w, row, kb + 1, nxt);  // one stage ahead
                 mbar_wait(&empty[s], ((it / TC_STAGES) & 1) ^ 1);
-                dequant_row_stage<TYPE>(p.w, row, kb, smem + s * TC_STAGE_BYTES, r);
+                dequant_row_stage<TYPE>(cur, kb, smem + s * TC_STAGE_BYTES, r);
                 fence_proxy_async();  // generic-proxy stores -> visible to the tensor core's async-proxy reads
                 __syncwarp();
                 if (lane == 0) mbar_arrive(&full[s]);
+                it++;
+            };
+            for (int kb = 0; kb < n_kb; kb += 2) {  // K is a multiple of 256: n_kb is even
+                do_stage(ra, rb, kb);
+                do_stage(rb, ra, kb + 1);
             }
         }
     } else if (warp >= 8) {
