@@ -113,6 +113,10 @@ SYMBOLS = {
     "aios_generate": (C.c_int, [_P, _P, C.c_int32, C.POINTER(Sampling), C.c_int32, _P, C.POINTER(C.c_int32)]),
     "aios_request_submit": (C.c_int, [_P, _P, C.c_int32, C.POINTER(Sampling), C.c_int32, C.c_int32, C.POINTER(_P)]),
     "aios_request_submit_masked": (C.c_int, [_P, _P, C.c_int32, C.POINTER(Sampling), C.c_int32, C.c_int32, _P, _P, C.POINTER(_P)]),
+    "aios_json_grammar_create": (C.c_int, [_P, C.POINTER(_P)]),
+    "aios_json_grammar_free": (None, [_P]),
+    "aios_json_grammar_complete": (C.c_int, [_P, C.POINTER(C.c_int32)]),
+    "aios_json_grammar_mask_cb": (C.c_int, [_P, C.c_int32, _P, C.c_int32]),
     "aios_request_poll": (C.c_int, [_P, _P, C.c_int32, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]),
     "aios_request_wait": (C.c_int, [_P, C.c_int32, C.POINTER(C.c_int32)]),
     "aios_request_cancel": (C.c_int, [_P]),
@@ -241,6 +245,33 @@ class Vocab:
         return bool(r.value)
 
 
+class JsonGrammar:
+    """JSON-object grammar over a vocabulary (aios_json_grammar): the allowed-token mask of every step, computed in C++.
+    One per request; pass it to ``Model.submit(json_grammar=...)`` and free it afterwards."""
+
+    def __init__(self, vocab: Vocab):
+        self.h = _P()
+        self._vocab = vocab
+        _check(lib().aios_json_grammar_create(vocab.h, C.byref(self.h)))
+
+    def step(self, last_token: int, n_vocab: int):
+        """-> (rc, mask): advance by last_token (-1 first) and return the allowed set (the call the scheduler makes)."""
+        mask = np.zeros((n_vocab + 7) // 8, np.uint8)
+        rc = lib().aios_json_grammar_mask_cb(self.h, int(last_token), _ptr(mask), mask.size)
+        return rc, mask
+
+    @property
+    def complete(self) -> bool:
+        c = C.c_int32(0)
+        _check(lib().aios_json_grammar_complete(self.h, C.byref(c)))
+        return bool(c.value)
+
+    def free(self):
+        if self.h:
+            lib().aios_json_grammar_free(self.h)
+            self.h = _P()
+
+
 class Engine:
     def __init__(self, device: int = 0, max_batch: int = 1, flags: int = 0):
         self.h = _P()
@@ -348,7 +379,7 @@ class Model:
         return Seq(self)
 
     def submit(self, prompt, max_tokens: int, sampling: Sampling | None = None, stop_at_eog: bool = False,
-               mask_cb=None) -> "Request":
+               mask_cb=None, json_grammar: "JsonGrammar | None" = None) -> "Request":
         """Queue a generation on the engine's scheduler thread (aios_request_submit); returns at once.
         ``mask_cb(last_token, mask) -> int`` (optional): called by the scheduler before every step of this request with
         the token sampled in the previous step (-1 first) and a zeroed uint8 array of ceil(n_vocab / 8) bytes to fill
@@ -357,6 +388,13 @@ class Model:
         sp = sampling if sampling is not None else Sampling()
         h = _P()
         flags = REQ_STOP_AT_EOG if stop_at_eog else 0
+        if json_grammar is not None:  # the C++ grammar drives the mask: no Python on the scheduler thread
+            cb = C.cast(lib().aios_json_grammar_mask_cb, _P)
+            _check(lib().aios_request_submit_masked(self.h, _ptr(toks), toks.size, C.byref(sp), max_tokens, flags, cb,
+                                                    json_grammar.h, C.byref(h)))
+            r = Request(h, self)
+            r._keep = json_grammar
+            return r
         if mask_cb is None:
             _check(lib().aios_request_submit(self.h, _ptr(toks), toks.size, C.byref(sp), max_tokens, flags, C.byref(h)))
             return Request(h, self)

@@ -18,6 +18,7 @@
 #include "../../include/aios_b200.h"
 #include "common.cuh"
 #include "engine.h"
+#include "json_mask.h"
 #include "tokenizer.h"
 
 using namespace aios;
@@ -59,6 +60,13 @@ struct aios_engine {
 struct aios_vocab {
     std::unique_ptr<GgufFile> own;
     Tokenizer tok;
+    std::mutex json_mu;
+    std::shared_ptr<JsonTables> json_tables;  // built on first use (aios_json_grammar_create)
+    std::shared_ptr<JsonTables> json() {
+        std::lock_guard<std::mutex> lk(json_mu);
+        if (!json_tables) json_tables = std::make_shared<JsonTables>(tok);
+        return json_tables;
+    }
     explicit aios_vocab(const char *path) : own(new GgufFile(path)), tok(*own) {}
     explicit aios_vocab(const GgufFile &f) : tok(f) {}
 };
@@ -512,6 +520,32 @@ int aios_token_is_eog(aios_vocab *v, int32_t id, int32_t *is_eog) {
         *is_eog = v->tok.is_eog(id) ? 1 : 0;
         return (int)AIOS_OK;
     });
+}
+
+struct aios_json_grammar { JsonMasker impl; explicit aios_json_grammar(std::shared_ptr<JsonTables> t) : impl(std::move(t)) {} };
+
+int aios_json_grammar_create(aios_vocab *v, aios_json_grammar **out) {
+    return guarded([&] {
+        if (!v || !out) return fail(AIOS_E_INVAL, "null argument");
+        if (v->tok.n_tokens() == 0) return fail(AIOS_E_STATE, "the GGUF file carries no tokenizer.ggml.tokens");
+        *out = new aios_json_grammar(v->json());
+        return (int)AIOS_OK;
+    });
+}
+void aios_json_grammar_free(aios_json_grammar *g) { delete g; }
+int aios_json_grammar_complete(aios_json_grammar *g, int32_t *complete) {
+    if (!g || !complete) return fail(AIOS_E_INVAL, "null argument");
+    *complete = g->impl.state.complete() ? 1 : 0;
+    return AIOS_OK;
+}
+// aios_mask_cb: user = the aios_json_grammar of this request
+int aios_json_grammar_mask_cb(void *user, int32_t last_token, uint8_t *mask_out, int32_t n_bytes) {
+    if (!user || !mask_out) return -1;
+    try {
+        return static_cast<aios_json_grammar *>(user)->impl.step(last_token, mask_out, n_bytes);
+    } catch (...) {
+        return -1;
+    }
 }
 
 int aios_seq_create(aios_model *m, aios_seq **out) {

@@ -186,9 +186,28 @@ class InferenceEngine:
         return pieces
 
     def _generate_json(self, lm, p: InferParams):
-        """-> (completion tokens, n_prompt).  Stops when the JSON object closes, at max_tokens, or when nothing fits."""
+        """-> (completion tokens, n_prompt).  Stops when the JSON object closes, at max_tokens, or when nothing fits.
+
+        On the real engine the request goes through the scheduler like any other (it shares the batch with whatever
+        else is running): the JSON grammar runs in C++ on the scheduler thread (aios_json_grammar_mask_cb), the allowed
+        set goes to the GPU as a bit mask (n_vocab / 8 bytes per step) and the on-device sampler applies it — the
+        logits never leave the GPU and no Python runs per token.  The host chain below is what scripted test models
+        (no engine) use."""
         from .json_grammar import JsonPrefix
         tokens, max_tokens, sampling = self._prepare(lm, p)
+        model = getattr(lm, "model", None)
+        if model is not None and hasattr(model, "submit") and hasattr(lm.vocab, "h"):
+            from ..capi import JsonGrammar
+            g = JsonGrammar(lm.vocab)
+            try:
+                req = model.submit(tokens, max_tokens, sampling, json_grammar=g)
+                try:
+                    out = req.result(120000)
+                finally:
+                    req.free()
+            finally:
+                g.free()
+            return np.asarray(out, np.int32), int(tokens.size)
         pieces = self._pieces(lm)
         rng = np.random.default_rng(sampling.seed & 0xFFFFFFFF)
         temp, top_k, top_p, min_p = float(sampling.temperature), int(sampling.top_k), float(sampling.top_p), float(sampling.min_p)

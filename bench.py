@@ -293,6 +293,43 @@ def bench_config3(device: int, n_prompt: int = 4096, iters: int = 3):
         eng.close()
 
 
+def bench_served(model, arch: str, n_prompt: int = 256, n_gen: int = 128, reps: int = 3):
+    """What one agent call costs: unary Infer semantics through the C ABI's request queue — JSON mode (the reference
+    always asks for response_format json_object, runtime/src/inference.rs:119-121), temperature 0.3, a 256-token prompt,
+    128 generated tokens.  The grammar runs in C++ on the scheduler thread, its mask goes to the GPU every step
+    (n_vocab / 8 bytes H2D), the sampled token comes back (4 B D2H).  Decode rate = tokens after the first / time after
+    the first token (the prompt's prefill is reported separately)."""
+    from aios_b200 import capi
+    vocab = model.vocab()
+    prompt = gs.synthetic_prompt(arch, n_prompt, SEED + 9)
+    rates, ttft, n_out = [], [], 0
+    for rep in range(reps + 1):
+        g = capi.JsonGrammar(vocab)
+        t0 = time.perf_counter()
+        r = model.submit(prompt, n_gen, capi.make_sampling(0.3, 40, 0.95, 0.05, seed=SEED + rep), json_grammar=g)
+        t_first, n = None, 0
+        while True:
+            r.wait(60000)
+            toks, done = r.poll(4096)
+            if toks.size and t_first is None:
+                t_first, n_first = time.perf_counter(), int(toks.size)
+            n += int(toks.size)
+            if done:
+                break
+        t1 = time.perf_counter()
+        r.free()
+        g.free()
+        if rep and t_first is not None and n > n_first:
+            rates.append((n - n_first) / (t1 - t_first))
+            ttft.append(t_first - t0)
+            n_out = n
+    return {"workload": f"unary Infer as served: JSON mode (device logit mask), temperature 0.3, {n_prompt}-token prompt, up to {n_gen} "
+                        "tokens, one request at a time through aios_request_submit_masked",
+            "value": float(np.median(rates)) if rates else None, "unit": "tok/s", "tokens_generated": n_out,
+            "seconds_to_first_token": float(np.median(ttft)) if ttft else None,
+            "h2d_bytes_per_token": (model.info.n_vocab + 7) // 8, "d2h_bytes_per_token": 4}
+
+
 def in_graph_breakdown(seq, n_runs: int = 4):
     """Per-token time of each launch kind INSIDE the token pass, from the %globaltimer marks the kernels themselves take
     (aios_seq_trace_decode: same launch order and programmatic-dependent-launch attributes as the captured graph).
@@ -456,8 +493,10 @@ def main():
     gemv_gbs = gemv_bytes_per_token / (ig["us_gemv"] * 1e-6) / 1e9 if ig["us_gemv"] > 0 else 0.0
     iso_gbs = gemv_bytes_per_token * prof.n_tokens / (prof.ms_gemv * 1e-3) / 1e9
 
-    config4 = None
+    config4 = served = None
     if rank == 0 and world == 1 and not args.no_subrecords:
+        served = bench_served(model, args.arch)
+        served["fraction_of_greedy_value"] = served["value"] / value if served.get("value") else None
         config4 = {"mistral-7b": bench_config4(eng, model, args.arch, args.ftype, peak)}
         tl_path = ensure_model("tinyllama-1.1b", "Q4_K_M", True)
         tl = eng.load_model("bench-tl", tl_path, n_ctx=512)
@@ -516,6 +555,8 @@ def main():
             line["config4"] = config4
         if config3:
             line["config3"] = config3
+        if served:
+            line["served"] = served
         print(json.dumps(line), flush=True)
     if eng is not None:
         seq.free()

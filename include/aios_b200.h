@@ -245,6 +245,16 @@ int aios_request_submit(aios_model *m, const int32_t *tokens, int32_t n, const a
 typedef int (*aios_mask_cb)(void *user, int32_t last_token, uint8_t *mask_out, int32_t n_bytes);
 int aios_request_submit_masked(aios_model *m, const int32_t *tokens, int32_t n, const aios_sampling *sp, int32_t max_tokens,
                                int32_t flags, aios_mask_cb cb, void *user, aios_request **out);
+/* JSON mode without any host code per token on the caller's side: a JSON-object grammar (root ::= object, RFC 8259 as
+ * llama.cpp's json.gbnf restricts it) over a vocabulary.  One grammar per request: create it, submit with
+ * cb = aios_json_grammar_mask_cb and user = the grammar, free it after the request.  The callback advances the grammar
+ * by every sampled token, allows exactly the tokens whose bytes keep the text a prefix of one JSON object, and ends
+ * the request (return 2) when the object closes or nothing fits. */
+typedef struct aios_json_grammar aios_json_grammar;
+int aios_json_grammar_create(aios_vocab *v, aios_json_grammar **out);
+void aios_json_grammar_free(aios_json_grammar *g);
+int aios_json_grammar_complete(aios_json_grammar *g, int32_t *complete);
+int aios_json_grammar_mask_cb(void *user, int32_t last_token, uint8_t *mask_out, int32_t n_bytes);
 /* take up to cap new tokens; *done = 1 once the request has finished AND everything was taken.  A request that
  * failed returns its error code (message in aios_last_error) from the poll that would have set *done. */
 int aios_request_poll(aios_request *r, int32_t *out_tokens, int32_t cap, int32_t *n_out, int32_t *done);

@@ -98,3 +98,42 @@ def test_constrained_generation_only_emits_json_prefixes(vocab_gguf):  # noqa: F
     # unconstrained sampling from the same logits is junk: the constraint is what made the difference
     junk = lm.vocab.detokenize(np.argsort(-lm.seq.logits())[:8])
     assert not is_json_object_prefix(junk)
+
+
+def test_cpp_grammar_mask_equals_python_acceptor(vocab_gguf):  # noqa: F811
+    """The C++ JSON grammar (csrc/json_mask.cpp — what the scheduler thread calls per decode step) must allow exactly the
+    tokens the Python acceptor (runtime/json_grammar.py) accepts, state after state along random JSON-valid walks, and
+    report completion at the same step."""
+    from aios_b200 import capi
+    from aios_b200.runtime.json_grammar import JsonPrefix
+    vocab = capi.Vocab.open(vocab_gguf)
+    n = vocab.info.n_tokens
+    pieces = [vocab.detokenize([i]) for i in range(n)]
+    rng = np.random.default_rng(11)
+    for walk in range(6):
+        g = capi.JsonGrammar(vocab)
+        st = JsonPrefix()
+        last = -1
+        for step in range(60):
+            rc, mask = g.step(last, n)
+            if st.complete:
+                assert rc == 2 and g.complete
+                break
+            want = np.array([bool(pieces[i]) and st.accepts(pieces[i]) for i in range(n)])
+            got = np.unpackbits(mask, bitorder="little")[:n].astype(bool)
+            assert np.array_equal(got, want), (walk, step, np.nonzero(got != want)[0][:5])
+            assert rc == (0 if want.any() else 2)
+            if not want.any():
+                break
+            # prefer closing tokens now and then so that walks end
+            allowed = np.nonzero(want)[0]
+            closers = [i for i in allowed if pieces[i].strip() in (b"}", b'"', b"]", b'"}')]
+            last = int(rng.choice(closers)) if closers and rng.random() < 0.4 else int(rng.choice(allowed))
+            assert st.feed(pieces[last])
+        g.free()
+    # a token the grammar did not allow is an error, not a silent state change
+    g = capi.JsonGrammar(vocab)
+    g.step(-1, n)
+    bad = next(i for i in range(n) if pieces[i] and not JsonPrefix().accepts(pieces[i]))
+    assert g.step(bad, n)[0] == -1
+    g.free()
