@@ -35,6 +35,7 @@ Batch::Batch(Model *m_) : m(m_) {
     CUDA_CHECK(cudaMallocHost(&h_cfg, (size_t)C * sizeof(SampleLane)));
     seqs.resize((size_t)C);
     cfg.resize((size_t)C);
+    in_seq.assign((size_t)C, 0);
     graphs.assign((size_t)C + 1, nullptr);
 }
 
@@ -51,9 +52,8 @@ int Batch::admit(const int32_t *prompt, int n_prompt, const aios_sampling &sp) {
     Seq &s = *seqs[(size_t)lane];
     s.reset();
     s.prefill(prompt, n_prompt);  // (synchronises) the last prompt token's logits are in s.logits
-    cudaStream_t st = m->eng->stream;
-    CUDA_CHECK(cudaMemcpyAsync(LOGITS.as<float>() + (size_t)lane * m->hp.n_vocab, s.logits.p, (size_t)m->hp.n_vocab * 4,
-                               cudaMemcpyDeviceToDevice, st));
+    s.ext_mask = nullptr;
+    in_seq[(size_t)lane] = 1;     // ... and stay there until the lane takes part in a batched step
     SampleLane &c = cfg[(size_t)lane];
     c.temperature = sp.temperature; c.top_k = sp.top_k; c.top_p = sp.top_p; c.min_p = sp.min_p; c.seed = sp.seed;
     c.mask = nullptr;
@@ -71,8 +71,10 @@ void Batch::retire(int lane) {
         std::swap(seqs[(size_t)lane], seqs[(size_t)last]);
         const bool had_mask = cfg[(size_t)last].mask != nullptr;
         cfg[(size_t)lane] = cfg[(size_t)last];
-        CUDA_CHECK(cudaMemcpyAsync(LOGITS.as<float>() + (size_t)lane * m->hp.n_vocab, LOGITS.as<float>() + (size_t)last * m->hp.n_vocab,
-                                   (size_t)m->hp.n_vocab * 4, cudaMemcpyDeviceToDevice, st));
+        in_seq[(size_t)lane] = in_seq[(size_t)last];
+        if (!in_seq[(size_t)last])
+            CUDA_CHECK(cudaMemcpyAsync(LOGITS.as<float>() + (size_t)lane * m->hp.n_vocab, LOGITS.as<float>() + (size_t)last * m->hp.n_vocab,
+                                       (size_t)m->hp.n_vocab * 4, cudaMemcpyDeviceToDevice, st));
         if (had_mask) {
             CUDA_CHECK(cudaMemcpyAsync(MASKS.as<uint8_t>() + (size_t)lane * mask_bytes, MASKS.as<uint8_t>() + (size_t)last * mask_bytes,
                                        mask_bytes, cudaMemcpyDeviceToDevice, st));
@@ -193,7 +195,32 @@ void Batch::step() {
     if (n <= 0) return;
     m->eng->make_current();
     cudaStream_t st = m->eng->stream;
-    for (int i = 0; i < n; i++) seqs[(size_t)i]->ensure_kv(seqs[(size_t)i]->n_past + 1);  // the token fed this step
+    const size_t row_bytes = (size_t)m->hp.n_vocab * 4;
+    if (n <= SMALL_BATCH) {
+        // few lanes: every lane through the single-sequence token pass (its own CUDA graph of GEMV kernels), which
+        // streams the weights once per lane but without the multi-token kernel's per-(row, token) overhead
+        for (int i = 0; i < n; i++) {
+            Seq &s = *seqs[(size_t)i];
+            if (!in_seq[(size_t)i]) {
+                CUDA_CHECK(cudaMemcpyAsync(s.logits.p, LOGITS.as<float>() + (size_t)i * m->hp.n_vocab, row_bytes, cudaMemcpyDeviceToDevice, st));
+                in_seq[(size_t)i] = 1;
+            }
+            const SampleLane &c = cfg[(size_t)i];
+            aios_sampling sp{c.temperature, c.top_k, c.top_p, c.min_p, c.seed};
+            s.ext_mask = c.mask;
+            s.have_logits = true;
+            if (s.decode(sp, 1, &h_tok[i]) != 1) throw std::runtime_error("context is full");
+        }
+        return;
+    }
+    for (int i = 0; i < n; i++) {
+        if (in_seq[(size_t)i]) {  // joins the batched steps: its logits move into its LOGITS row
+            CUDA_CHECK(cudaMemcpyAsync(LOGITS.as<float>() + (size_t)i * m->hp.n_vocab, seqs[(size_t)i]->logits.p, row_bytes, cudaMemcpyDeviceToDevice, st));
+            in_seq[(size_t)i] = 0;
+            dirty = true;
+        }
+        seqs[(size_t)i]->ensure_kv(seqs[(size_t)i]->n_past + 1);  // the token fed this step
+    }
     if (dirty) { upload_lane_state(st); dirty = false; }
     const bool use_graph = !(m->eng->flags & AIOS_ENGINE_NO_GRAPH);
     if (use_graph) {

@@ -440,7 +440,7 @@ void Seq::launch_sample_kernel(const aios_sampling &sp, cudaStream_t st) {
     s.temperature = sp.temperature; s.top_k = sp.top_k; s.top_p = sp.top_p; s.min_p = sp.min_p; s.seed = sp.seed;
     s.pos_ptr = &sd->pos; s.step_ptr = &sd->step; s.cur_token = &sd->cur_token;
     s.out_tokens = out_tokens.as<int32_t>(); s.out_cap = m->hp.n_ctx;
-    s.mask = mask_on ? mask.as<uint8_t>() : nullptr;
+    s.mask = ext_mask ? ext_mask : (mask_on ? mask.as<uint8_t>() : nullptr);
     TIMED(2, launch_sample(s, st));
 }
 
@@ -480,7 +480,7 @@ static bool same_sampling(const aios_sampling &a, const aios_sampling &b) {
 }
 
 void Seq::ensure_graph(const aios_sampling &sp) {
-    if (graph && same_sampling(sp, graph_sampling) && graph_mask == mask_on) return;
+    if (graph && same_sampling(sp, graph_sampling) && graph_mask == mask_on && graph_mask_ptr == ext_mask) return;
     if (graph) { cudaGraphExecDestroy(graph); graph = nullptr; }
     cudaStream_t st = m->eng->stream;
     cudaGraph_t g = nullptr;
@@ -501,6 +501,7 @@ void Seq::ensure_graph(const aios_sampling &sp) {
     CUDA_CHECK(e);
     graph_sampling = sp;
     graph_mask = mask_on;
+    graph_mask_ptr = ext_mask;
 }
 
 // One prompt chunk of T <= 64 tokens at positions pos0 .. pos0+T-1.  Same arithmetic as T token passes (the logits and
@@ -922,7 +923,7 @@ void Seq::build_pfd() {
 bool Seq::use_pfd(const aios_sampling &sp) const {
     // opt-in until it beats the per-op path (AIOS_ENGINE_USE_PFD); AIOS_ENGINE_NO_PFD always wins
     const int f = m->eng->flags;
-    return pfd_grid > 0 && !mask_on && !(sp.temperature > 0.f) && (f & AIOS_ENGINE_USE_PFD) && !(f & AIOS_ENGINE_NO_PFD);
+    return pfd_grid > 0 && !mask_on && !ext_mask && !(sp.temperature > 0.f) && (f & AIOS_ENGINE_USE_PFD) && !(f & AIOS_ENGINE_NO_PFD);
 }
 
 // n greedy tokens after the current position; device state (pos, step) must already be set

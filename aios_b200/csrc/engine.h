@@ -135,9 +135,11 @@ struct Seq {
     DevBuf trace;
     DevBuf mask;           // optional logit mask (n_vocab bits), see set_mask
     bool mask_on = false;
+    const uint8_t *ext_mask = nullptr;  // a mask owned by someone else (the batcher's lane mask); wins over `mask`
     unsigned long long *trace_base = nullptr;  // non-null only inside trace_decode
     cudaGraphExec_t graph = nullptr;
     aios_sampling graph_sampling{};
+    const uint8_t *graph_mask_ptr = nullptr;
     bool graph_mask = false;
     int kernels_per_step = 0;
     // persistent fused decode (pfd.cu): phase table + global exchange buffers; pfd_grid == 0 -> not usable
@@ -182,6 +184,10 @@ struct Batch {
     int n = 0;                          // live lanes: 0 .. n-1 (kept dense)
     std::vector<std::unique_ptr<Seq>> seqs;  // lane i's sequence (KV range, prompt prefill); pooled, created on demand
     std::vector<SampleLane> cfg;        // host mirror of the per-lane sampler parameters
+    // where a lane's current logits live: its own sequence's buffer (after its prefill, and while the batch is small
+    // enough that every lane runs the single-sequence token pass) or its row of LOGITS (batched steps)
+    std::vector<char> in_seq;
+    static constexpr int SMALL_BATCH = 3;  // up to this many lanes, one GEMV token pass per lane beats the multi-token GEMM
     DevBuf X, QKV, ATT, H, GU, LOGITS, IMG_A, IMG_B, POS, TOK, KVB, CFG, MASKS;
     int32_t *h_tok = nullptr;           // pinned: the step's sampled tokens
     int32_t *h_pos = nullptr;           // pinned staging for POS
