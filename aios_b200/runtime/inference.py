@@ -11,9 +11,9 @@ tokenizer, prefill, the decode loop, the sampler chain (top-k 40, top-p 0.95, mi
 
 Differences, on purpose: ``stream_infer`` really streams (the reference buffers the whole SSE body first,
 inference.rs:261).  JSON mode (``response_format: json_object``, :119-121): requests with
-``json_mode`` are sampled under ``json_grammar.JsonPrefix`` — the candidates come back to the host every step
-(128 KB of logits) and only pieces that keep the text a prefix of one JSON object survive; the sampler chain
-(top-k 40, top-p, min-p, temperature) then runs on the survivors.
+``json_mode`` go through the request queue with a JSON-object grammar (csrc/json_mask.cpp) whose allowed-token mask
+the on-device sampler applies every step — n_vocab / 8 bytes down, 4 bytes up per token, no Python per token.
+Models without an engine behind them (scripted test doubles) keep the host-side chain over ``json_grammar.JsonPrefix``.
 
 There is no CPU fallback: ``EngineBackend`` needs libaios_b200.so and a B200.
 """
@@ -86,9 +86,19 @@ class LoadedModel:
         self.seq = self.model.new_seq()  # for direct (non-queued) use: tests, prompt caching
         self.lock = threading.Lock()
 
-    def submit(self, tokens, max_tokens: int, sampling):
-        """Queue a generation on the engine's scheduler; stops at the first end-of-generation token."""
-        return self.model.submit(tokens, max_tokens, sampling, stop_at_eog=True)
+    def submit(self, tokens, max_tokens: int, sampling, json_mode: bool = False):
+        """Queue a generation on the engine's scheduler; stops at the first end-of-generation token.  json_mode: the
+        request carries a JSON-object grammar whose per-step mask the on-device sampler applies."""
+        if not json_mode:
+            return self.model.submit(tokens, max_tokens, sampling, stop_at_eog=True)
+        from ..capi import JsonGrammar
+        g = JsonGrammar(self.vocab)
+        try:
+            req = self.model.submit(tokens, max_tokens, sampling, json_grammar=g)
+        except Exception:
+            g.free()
+            raise
+        return _GrammarRequest(req, g)
 
     def close(self):
         with self.lock:
@@ -96,25 +106,79 @@ class LoadedModel:
             self.model.unload()
 
 
-class EngineBackend:
-    """``Backend`` of ModelManager on the real engine: one ``aios_engine`` per process / GPU."""
+class _GrammarRequest:
+    """A queued JSON-mode request: frees its grammar with the request."""
 
-    def __init__(self, device: int = 0, flags: int = 0):
+    def __init__(self, req, grammar):
+        self._req, self._g = req, grammar
+
+    def __getattr__(self, name):
+        return getattr(self._req, name)
+
+    def free(self):
+        self._req.free()
+        if self._g is not None:
+            self._g.free()
+            self._g = None
+
+
+class EngineBackend:
+    """``Backend`` of ModelManager on the real engine: one ``aios_engine`` per GPU of this process.
+
+    ``devices``: CUDA ordinals to serve on; default = ``AIOS_GPUS`` ("0,2,3" or "all") if set, else ``[device]``.
+    With several devices LoadModel puts one full replica of the model on every GPU and each request goes to the
+    least-loaded replica (``aios_b200.replicas.ReplicaSet``; SURVEY.md §8e: replicas only, no collective)."""
+
+    def __init__(self, device: int = 0, flags: int = 0, devices: Optional[list] = None):
         from .. import capi
         self.capi = capi
-        # KV slots per model: one for the scheduler's queued requests, one for direct use, one spare
-        self.engine = capi.Engine(device=device, max_batch=3, flags=flags)
+        if devices is None:
+            env = os.environ.get("AIOS_GPUS", "").strip()
+            if env.lower() == "all":
+                devices = list(range(capi.device_count()))
+            elif env:
+                devices = [int(x) for x in env.split(",") if x.strip()]
+            else:
+                devices = [device]
+        self.devices = list(devices)
+        # caller-visible sequences per model: one for direct use (tests, prompt caching) and a spare; the scheduler's
+        # batch lanes and the scratch sequence are not counted
+        self.engines = [capi.Engine(device=d, max_batch=2, flags=flags) for d in self.devices]
+        self.engine = self.engines[0]
+        self._sets: list = []
 
-    def load(self, name: str, path: str, context_length: int) -> LoadedModel:
+    def load(self, name: str, path: str, context_length: int):
         if not os.path.isfile(path):
             raise FileNotFoundError(f"model file {path} not found")
-        return LoadedModel(self.engine, name, path, context_length)
+        from ..replicas import ReplicaSet
+        loaded = []
+        try:
+            for e in self.engines:
+                loaded.append(LoadedModel(e, name, path, context_length))
+        except Exception:
+            for lm in loaded:
+                lm.close()
+            raise
+        rs = ReplicaSet(loaded, self.devices)
+        self._sets.append(rs)
+        return rs
 
-    def unload(self, handle: LoadedModel) -> None:
+    def unload(self, handle) -> None:
+        if handle in self._sets:
+            self._sets.remove(handle)
         handle.close()
 
-    def alive(self, handle: LoadedModel) -> bool:
-        return bool(handle.model.h)
+    def alive(self, handle) -> bool:
+        return all(bool(r.model.h) for r in handle.replicas)
+
+    def gpu_load(self) -> dict:
+        """device -> (models resident, requests in flight), for HealthCheck."""
+        out = {d: [0, 0] for d in self.devices}
+        for rs in self._sets:
+            for d, n in rs.load().items():
+                out[d][0] += 1
+                out[d][1] += n
+        return out
 
     def close(self):
         self.engine.close()
@@ -143,8 +207,8 @@ class InferenceEngine:
         """Yields (new completion tokens without the end-of-generation token, n_prompt, finished)."""
         tokens, max_tokens, sampling = self._prepare(lm, p)
         if hasattr(lm, "submit"):
-            # the engine's own scheduler thread (aios_request_*): handlers of concurrent RPCs queue up there, like
-            # concurrent HTTP requests did on llama-server's slot, and none of them blocks another one's polling
+            # the engine's own scheduler thread (aios_request_*): concurrent RPCs are batched there (continuous
+            # batching, one token per request per step); with several GPUs the least-loaded replica takes the request
             req = lm.submit(tokens, max_tokens, sampling)
             try:
                 while True:
@@ -195,18 +259,12 @@ class InferenceEngine:
         (no engine) use."""
         from .json_grammar import JsonPrefix
         tokens, max_tokens, sampling = self._prepare(lm, p)
-        model = getattr(lm, "model", None)
-        if model is not None and hasattr(model, "submit") and hasattr(lm.vocab, "h"):
-            from ..capi import JsonGrammar
-            g = JsonGrammar(lm.vocab)
+        if getattr(lm, "model", None) is not None and hasattr(lm, "submit") and hasattr(lm.vocab, "h"):
+            req = lm.submit(tokens, max_tokens, sampling, json_mode=True)
             try:
-                req = model.submit(tokens, max_tokens, sampling, json_grammar=g)
-                try:
-                    out = req.result(120000)
-                finally:
-                    req.free()
+                out = req.result(120000)
             finally:
-                g.free()
+                req.free()
             return np.asarray(out, np.int32), int(tokens.size)
         pieces = self._pieces(lm)
         rng = np.random.default_rng(sampling.seed & 0xFFFFFFFF)

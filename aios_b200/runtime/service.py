@@ -158,6 +158,10 @@ class AIRuntimeService:
         details = {"loaded_models": str(loaded), "total_models": str(total)}
         for m in models:
             details[f"model:{m.model_name}"] = f"status={m.status} port={m.port}"
+        gpu_load = getattr(self.model_manager.backend, "gpu_load", None)
+        if gpu_load:  # one engine per GPU: resident replicas and requests in flight on each
+            for dev, (n_models, n_req) in sorted(gpu_load().items()):
+                details[f"gpu:{dev}"] = f"models={n_models} inflight={n_req}"
         log.info("gRPC HealthCheck loaded=%d total=%d uptime=%d", loaded, total, uptime)
         return pb.HealthStatus(healthy=True, service="aios-runtime",
                                message=f"{loaded}/{total} models loaded, uptime {uptime}s", uptime_seconds=uptime,
@@ -253,6 +257,9 @@ def main(argv=None):
     ap = argparse.ArgumentParser(description="aios-runtime drop-in on the B200 engine")
     ap.add_argument("--addr", default=LISTEN_ADDR)
     ap.add_argument("--device", type=int, default=int(os.environ.get("LOCAL_RANK", "0")))
+    ap.add_argument("--gpus", default=None, help='CUDA ordinals to serve on, e.g. "0,1,2,3" or "all" (default: $AIOS_GPUS, '
+                                                 "else --device): one engine and one replica of every model per GPU, "
+                                                 "requests go to the least-loaded replica")
     ap.add_argument("--model-dir", default=None)
     ap.add_argument("--openai-http", action="store_true",
                     help="serve every loaded model on its port (8080, 8081, ...) with the OpenAI-compatible HTTP API")
@@ -260,6 +267,8 @@ def main(argv=None):
     logging.basicConfig(level=logging.INFO, format="%(asctime)s %(levelname)s %(message)s")
     from .inference import EngineBackend
     log.info("aiOS AI Runtime starting...")
+    if args.gpus:
+        os.environ["AIOS_GPUS"] = args.gpus
     srv = RuntimeServer(EngineBackend(device=args.device), addr=args.addr, model_dir=args.model_dir,
                         openai_http=args.openai_http).start()
     try:

@@ -243,3 +243,41 @@ def test_oracle_against_exact_math_numpy_reference(oracle, tmp_models, arch, fty
     got = oracle.OracleModel(path, n_ctx=64).eval_all(prompt)
     assert np.abs(got - exact).max() / exact.std() < 0.15
     assert np.corrcoef(got[-1], exact[-1])[0, 1] > 0.999
+
+
+def test_replica_set_dispatches_to_the_least_loaded_replica():
+    """Multi-GPU service: one replica of a model per GPU, every request to the replica with the fewest
+    requests in flight, ties in turn; a finished request gives its count back."""
+    from aios_b200.replicas import ReplicaSet
+
+    class FakeReq:
+        def __init__(self, tag):
+            self.tag, self.freed = tag, False
+
+        def free(self):
+            self.freed = True
+
+    class FakeReplica:
+        def __init__(self, i):
+            self.name, self.vocab, self.n_ctx, self.i, self.closed = "m", object(), 128, i, False
+
+        def submit(self, tokens, max_tokens, sampling, json_mode=False):
+            return FakeReq((self.i, json_mode))
+
+        def close(self):
+            self.closed = True
+
+    rs = ReplicaSet([FakeReplica(i) for i in range(4)], devices=[0, 1, 2, 3])
+    reqs = [rs.submit([1], 4, None) for _ in range(8)]
+    assert sorted(r.tag[0] for r in reqs) == [0, 0, 1, 1, 2, 2, 3, 3]      # spread evenly
+    assert rs.load() == {0: 2, 1: 2, 2: 2, 3: 2}
+    for r in reqs:
+        if r.device in (1, 2):
+            r.free()
+    assert rs.load() == {0: 2, 1: 0, 2: 0, 3: 2}
+    nxt = [rs.submit([1], 4, None, json_mode=True) for _ in range(4)]
+    assert sorted(r.device for r in nxt) == [1, 1, 2, 2] and all(r.tag[1] for r in nxt)  # the idle GPUs take the new work
+    reqs[0].free(); reqs[0].free()                                           # double free gives the count back once
+    assert rs.load()[reqs[0].device] == 1
+    rs.close()
+    assert all(r.closed for r in rs.replicas)

@@ -100,3 +100,31 @@ def test_two_engines_on_two_devices(oracle, tmp_models):
     finally:
         for e in engines:
             e.close()
+
+
+def test_service_backend_replicates_models_and_spreads_requests(tmp_models):
+    """The multi-GPU service: EngineBackend with several devices loads one replica of a model per GPU and concurrent
+    requests land on different devices (least-loaded dispatch); HealthCheck-style load report per GPU."""
+    n_dev = capi.device_count()
+    if n_dev < 2:
+        pytest.skip("needs two GPUs")
+    from aios_b200.runtime.inference import EngineBackend
+    path = tmp_models("tiny-gqa4", "Q4_K_M")
+    be = EngineBackend(devices=[0, 1])
+    try:
+        rs = be.load("m", path, 128)
+        prompt = gs.synthetic_prompt("tiny-gqa4", 12, 4)
+        want = rs.replicas[0].model.generate(prompt, 24)
+        a = rs.submit(prompt, 24, capi.make_sampling(0.0))
+        b = rs.submit(prompt, 24, capi.make_sampling(0.0))
+        assert {a.device, b.device} == {0, 1}
+        assert be.gpu_load() == {0: [1, 1], 1: [1, 1]}
+        ra, rb = a.result(), b.result()
+        a.free(); b.free()
+        # stop_at_eog may cut at an end-of-generation token: compare the common prefix
+        assert np.array_equal(ra, want[: len(ra)]) and np.array_equal(rb, want[: len(rb)])
+        assert be.gpu_load() == {0: [1, 0], 1: [1, 0]}
+        be.unload(rs)
+    finally:
+        for e in be.engines:
+            e.close()
