@@ -27,6 +27,7 @@ import time
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
+os.environ.setdefault("OMP_WAIT_POLICY", "PASSIVE")  # the oracle's OpenMP team must not spin against other busy threads
 
 import numpy as np  # noqa: E402
 
@@ -422,7 +423,9 @@ def main():
     # prompt (rank 0; the same CPU run is the cpu_baseline sample).  A mismatch aborts the bench.
     parity = None
     cpu = None
-    if rank == 0 and not args.no_cpu_baseline:
+    # (single-GPU runs only: under torchrun the other ranks would spin in the barrier on the cores the oracle needs;
+    # every rank runs the same code on the same file, and the driver's N = 1 run gates it)
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
         n_chk = min(args.parity_tokens, args.gen)
         want, cpu_rate, cores, cpu_dt, cpu_passes = oracle_window(path, args.arch, args.prompt, n_chk)
         got = seq.decode(n_chk)
