@@ -74,6 +74,12 @@ class BenchResult(C.Structure):
                 ("reserved", C.c_float * 3)]
 
 
+class TpBench(C.Structure):
+    _fields_ = [("ms_total", C.c_float), ("n_tokens", C.c_int32), ("n_ranks", C.c_int32), ("kernel_launches", C.c_int32),
+                ("n_past_begin", C.c_int32), ("n_past_end", C.c_int32), ("n_allreduce_per_token", C.c_int32),
+                ("us_per_allreduce", C.c_float)]
+
+
 TOK_ADD_SPECIAL, TOK_PARSE_SPECIAL, TOK_RENDER_SPECIAL, TOK_STRIP_SPACE = 1, 2, 4, 8
 
 # every symbol include/aios_b200.h declares: name -> (restype, argtypes)
@@ -137,6 +143,14 @@ SYMBOLS = {
     "aios_seq_bench_prefill": (C.c_int, [_P, _P, C.c_int32, C.c_int32, C.POINTER(C.c_float)]),
     "aios_bench_batch_decode": (C.c_int, [_P, C.c_int32, _P, C.c_int32, C.c_int32, _P, C.POINTER(BatchBench)]),
     "aios_bench_gemv": (C.c_int, [_P, C.c_int32, C.c_int64, C.c_int64, C.c_int32, C.c_int32, C.POINTER(C.c_float)]),
+    "aios_tp_model_load": (C.c_int, [_P, C.c_int32, C.c_char_p, C.c_char_p, C.c_int32, C.c_int32, C.POINTER(_P)]),
+    "aios_tp_model_unload": (C.c_int, [_P]),
+    "aios_tp_model_info": (C.c_int, [_P, C.POINTER(ModelInfo)]),
+    "aios_tp_reset": (C.c_int, [_P]),
+    "aios_tp_prefill": (C.c_int, [_P, _P, C.c_int32]),
+    "aios_tp_decode": (C.c_int, [_P, C.POINTER(Sampling), C.c_int32, _P, C.POINTER(C.c_int32)]),
+    "aios_tp_get_logits": (C.c_int, [_P, _P, C.c_int32]),
+    "aios_tp_bench_decode": (C.c_int, [_P, C.c_int32, C.POINTER(TpBench)]),
 }
 
 _lib = None
@@ -583,4 +597,51 @@ class Seq:
     def bench_decode(self, n_tokens: int) -> BenchResult:
         r = BenchResult()
         _check(lib().aios_seq_bench_decode(self.h, n_tokens, C.byref(r)))
+        return r
+
+
+class TpModel:
+    """One model split over several GPUs of this node (aios_tp_*): row/K-split projections, NCCL all-reduce of the
+    f64 partial sums, every rank sampling the same token from the gathered logits."""
+
+    def __init__(self, devices, name: str, path: str, n_ctx: int = 0, flags: int = 0):
+        devs = np.ascontiguousarray(devices, dtype=np.int32)
+        self.h = _P()
+        _check(lib().aios_tp_model_load(_ptr(devs), devs.size, name.encode(), path.encode(), n_ctx, flags, C.byref(self.h)))
+        self.info = ModelInfo()
+        _check(lib().aios_tp_model_info(self.h, C.byref(self.info)))
+        self.n_ranks = int(devs.size)
+
+    def unload(self):
+        if self.h:
+            _check(lib().aios_tp_model_unload(self.h))
+            self.h = _P()
+
+    def reset(self):
+        _check(lib().aios_tp_reset(self.h))
+
+    def prefill(self, tokens):
+        toks = np.ascontiguousarray(tokens, dtype=np.int32)
+        _check(lib().aios_tp_prefill(self.h, _ptr(toks), toks.size))
+
+    def decode(self, max_tokens: int, sampling: Sampling | None = None) -> np.ndarray:
+        out = np.empty(max(max_tokens, 1), dtype=np.int32)
+        n = C.c_int32(0)
+        sp = sampling if sampling is not None else Sampling()
+        _check(lib().aios_tp_decode(self.h, C.byref(sp), max_tokens, _ptr(out), C.byref(n)))
+        return out[: n.value].copy()
+
+    def logits(self) -> np.ndarray:
+        out = np.empty(self.info.n_vocab, dtype=np.float32)
+        _check(lib().aios_tp_get_logits(self.h, _ptr(out), out.size))
+        return out
+
+    def generate(self, prompt, max_tokens: int, sampling: Sampling | None = None) -> np.ndarray:
+        self.reset()
+        self.prefill(prompt)
+        return self.decode(max_tokens, sampling)
+
+    def bench_decode(self, n_tokens: int) -> TpBench:
+        r = TpBench()
+        _check(lib().aios_tp_bench_decode(self.h, n_tokens, C.byref(r)))
         return r

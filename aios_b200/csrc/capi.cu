@@ -20,6 +20,7 @@
 #include "engine.h"
 #include "json_mask.h"
 #include "tokenizer.h"
+#include "tp.h"
 
 using namespace aios;
 
@@ -318,6 +319,13 @@ static int guarded(F &&f) {
         return fail(AIOS_E_STATE, "unknown error");
     }
 }
+
+// ---------------------------------------------------------------- tensor parallelism (tp.cu)
+struct aios_tp_model {
+    std::unique_ptr<aios::TpModel> impl;
+    std::mutex mu;
+};
+
 
 extern "C" {
 
@@ -1118,6 +1126,74 @@ int aios_bench_gemv(aios_engine *e, int32_t type, int64_t n_rows, int64_t k, int
         cudaEventDestroy(e0);
         cudaEventDestroy(e1);
         *ms_per_launch = ms / (float)iters;
+        return (int)AIOS_OK;
+    });
+}
+
+// ---- tensor parallelism
+int aios_tp_model_load(const int32_t *devices, int32_t n_devices, const char *name, const char *gguf_path, int32_t n_ctx,
+                       int32_t engine_flags, aios_tp_model **out) {
+    return guarded([&] {
+        if (!devices || !name || !gguf_path || !out) return fail(AIOS_E_INVAL, "null argument");
+        if (n_devices < 2 || n_devices > 8) return fail(AIOS_E_INVAL, "tensor parallelism takes 2 to 8 devices");
+        std::vector<int> devs(devices, devices + n_devices);
+        std::unique_ptr<aios_tp_model> m(new aios_tp_model());
+        m->impl.reset(new aios::TpModel(devs, name, gguf_path, n_ctx, engine_flags));
+        *out = m.release();
+        return (int)AIOS_OK;
+    });
+}
+int aios_tp_model_unload(aios_tp_model *m) {
+    return guarded([&] {
+        delete m;
+        return (int)AIOS_OK;
+    });
+}
+int aios_tp_model_info(const aios_tp_model *m, aios_model_info *out) {
+    return guarded([&] {
+        if (!m || !out) return fail(AIOS_E_INVAL, "null argument");
+        m->impl->info(out);
+        return (int)AIOS_OK;
+    });
+}
+int aios_tp_reset(aios_tp_model *m) {
+    return guarded([&] {
+        if (!m) return fail(AIOS_E_INVAL, "null argument");
+        std::lock_guard<std::mutex> lk(m->mu);
+        m->impl->reset();
+        return (int)AIOS_OK;
+    });
+}
+int aios_tp_prefill(aios_tp_model *m, const int32_t *tokens, int32_t n_tokens) {
+    return guarded([&] {
+        if (!m || (!tokens && n_tokens > 0)) return fail(AIOS_E_INVAL, "null argument");
+        std::lock_guard<std::mutex> lk(m->mu);
+        m->impl->prefill(tokens, n_tokens);
+        return (int)AIOS_OK;
+    });
+}
+int aios_tp_decode(aios_tp_model *m, const aios_sampling *sp, int32_t max_tokens, int32_t *out_tokens, int32_t *n_out) {
+    return guarded([&] {
+        if (!m || !sp || !out_tokens || !n_out) return fail(AIOS_E_INVAL, "null argument");
+        std::lock_guard<std::mutex> lk(m->mu);
+        *n_out = m->impl->decode(*sp, max_tokens, out_tokens);
+        return (int)AIOS_OK;
+    });
+}
+int aios_tp_get_logits(aios_tp_model *m, float *out, int32_t n) {
+    return guarded([&] {
+        if (!m || !out) return fail(AIOS_E_INVAL, "null argument");
+        if (n != m->impl->n_vocab()) return fail(AIOS_E_RANGE, "n must equal n_vocab");
+        std::lock_guard<std::mutex> lk(m->mu);
+        m->impl->read_logits(out);
+        return (int)AIOS_OK;
+    });
+}
+int aios_tp_bench_decode(aios_tp_model *m, int32_t n_tokens, aios_tp_bench *out) {
+    return guarded([&] {
+        if (!m || !out) return fail(AIOS_E_INVAL, "null argument");
+        std::lock_guard<std::mutex> lk(m->mu);
+        m->impl->bench_decode(n_tokens, out);
         return (int)AIOS_OK;
     });
 }

@@ -77,20 +77,36 @@ static void alloc_planes(int type, int64_t n_rows, int64_t k, DevMatrix &dst) {
     dst.w.k = (int32_t)k;
 }
 
-void Model::upload_matrix(const GgufTensor &t, DevMatrix &dst, DevBuf &staging, void *pinned, size_t pinned_bytes) {
+void Model::upload_matrix(const GgufTensor &t, DevMatrix &dst, DevBuf &staging, void *pinned, size_t pinned_bytes, int64_t row0,
+                          int64_t n_rows, int64_t k0, int64_t k_len) {
     if (!is_quant_matrix_type(t.type))
         throw GgufError(AIOS_E_FORMAT, "tensor '" + t.name + "': matrix type " + std::to_string(t.type) +
                                            " is not supported (Q4_K, Q5_K, Q6_K, Q8_0 are)");
     if (t.n_dims != 2) throw GgufError(AIOS_E_FORMAT, "tensor '" + t.name + "' is not a matrix");
-    const int64_t k = t.ne[0], n = t.ne[1];
-    if (k % 256) throw GgufError(AIOS_E_FORMAT, "tensor '" + t.name + "': K must be a multiple of 256");
+    const int64_t K = t.ne[0], N = t.ne[1];
+    if (K % 256) throw GgufError(AIOS_E_FORMAT, "tensor '" + t.name + "': K must be a multiple of 256");
+    const int64_t n = n_rows < 0 ? N : n_rows, k = k_len < 0 ? K : k_len;
+    if (row0 < 0 || row0 + n > N || k0 < 0 || k0 + k > K || k % 256 || k0 % 256)
+        throw GgufError(AIOS_E_FORMAT, "tensor '" + t.name + "': bad shard (quant blocks run along K: K slices are cut at multiples of 256)");
+    // the slice as a contiguous [n][k] tensor of the same type: whole rows are contiguous in the file, a K slice is a
+    // contiguous run of blocks inside every row
+    const size_t be = (size_t)type_block_elems(t.type), bb = (size_t)type_block_bytes(t.type);
+    const size_t row_bytes_full = (size_t)K / be * bb, row_bytes = (size_t)k / be * bb, nbytes = (size_t)n * row_bytes;
+    std::vector<uint8_t> gathered;
+    const uint8_t *src = t.data + (size_t)row0 * row_bytes_full;
+    if (k != K) {
+        gathered.resize(nbytes);
+        for (int64_t r = 0; r < n; r++)
+            memcpy(gathered.data() + (size_t)r * row_bytes, t.data + (size_t)(row0 + r) * row_bytes_full + (size_t)k0 / be * bb, row_bytes);
+        src = gathered.data();
+    }
     alloc_planes(t.type, n, k, dst);
-    dst.src_bytes = t.nbytes;
-    if (staging.bytes < t.nbytes) staging = DevBuf(t.nbytes);
+    dst.src_bytes = nbytes;
+    if (staging.bytes < nbytes) staging = DevBuf(nbytes);
     cudaStream_t st = eng->stream;
-    for (size_t off = 0; off < t.nbytes; off += pinned_bytes) {
-        const size_t c = std::min(pinned_bytes, (size_t)t.nbytes - off);
-        memcpy(pinned, t.data + off, c);
+    for (size_t off = 0; off < nbytes; off += pinned_bytes) {
+        const size_t c = std::min(pinned_bytes, nbytes - off);
+        memcpy(pinned, src + off, c);
         CUDA_CHECK(cudaMemcpyAsync(staging.as<uint8_t>() + off, pinned, c, cudaMemcpyHostToDevice, st));
         CUDA_CHECK(cudaStreamSynchronize(st));
     }
@@ -100,7 +116,7 @@ void Model::upload_matrix(const GgufTensor &t, DevMatrix &dst, DevBuf &staging, 
     CUDA_CHECK(cudaGetLastError());
     CUDA_CHECK(cudaStreamSynchronize(st));
     weight_bytes += (int64_t)dst.storage.bytes;
-    weight_bytes_per_token += (int64_t)t.nbytes;
+    weight_bytes_per_token += (int64_t)nbytes;
 }
 
 static DevBuf upload_f32(const GgufTensor &t, int64_t expect, cudaStream_t st) {
@@ -112,7 +128,8 @@ static DevBuf upload_f32(const GgufTensor &t, int64_t expect, cudaStream_t st) {
     return b;
 }
 
-Model::Model(Engine *e, const std::string &name_, const std::string &path_, int n_ctx) : eng(e), name(name_), path(path_) {
+Model::Model(Engine *e, const std::string &name_, const std::string &path_, int n_ctx, int tp_rank_, int tp_size_)
+    : eng(e), name(name_), path(path_), tp_rank(tp_rank_), tp_size(tp_size_) {
     e->make_current();
     file.reset(new GgufFile(path));
     const GgufFile &f = *file;
@@ -141,6 +158,17 @@ Model::Model(Engine *e, const std::string &name_, const std::string &path_, int 
     const GgufTensor &te = f.require("token_embd.weight");
     hp.n_vocab = (int)te.ne[1];
     if (te.ne[0] != hp.n_embd) throw GgufError(AIOS_E_FORMAT, "token_embd.weight has the wrong width");
+    // full-model sizes (the GGUF tensors' shapes) and this shard's share of them
+    const int QD_full = hp.n_head * hp.head_dim, KVD_full = hp.n_head_kv * hp.head_dim, FF_full = hp.n_ff;
+    vocab_local = hp.n_vocab;
+    if (tp_size > 1) {
+        if (tp_rank < 0 || tp_rank >= tp_size) throw GgufError(AIOS_E_INVAL, "bad tensor-parallel rank");
+        if (hp.n_head_kv % tp_size || hp.n_ff % tp_size || hp.n_vocab % tp_size || (QD_full / tp_size) % 256 || (FF_full / tp_size) % 256)
+            throw GgufError(AIOS_E_FORMAT, "model cannot be split " + std::to_string(tp_size) + " ways: kv heads, FF and vocabulary "
+                            "must divide, and the K slices of attn_output / ffn_down must be multiples of 256");
+        hp.n_head /= tp_size; hp.n_head_kv /= tp_size; hp.n_ff /= tp_size;
+        vocab_local = hp.n_vocab / tp_size;
+    }
 
     cudaStream_t st = e->stream;
     const size_t pinned_bytes = 64u << 20;
@@ -161,7 +189,6 @@ Model::Model(Engine *e, const std::string &name_, const std::string &path_, int 
         weight_bytes += (int64_t)te.nbytes;
         weight_bytes_per_token += tok_embd_row_bytes;
 
-        const int QD = hp.n_head * hp.head_dim, KVD = hp.n_head_kv * hp.head_dim;
         layers.resize(hp.n_layer);
         for (int i = 0; i < hp.n_layer; i++) {
             const std::string p = "blk." + std::to_string(i) + ".";
@@ -169,16 +196,19 @@ Model::Model(Engine *e, const std::string &name_, const std::string &path_, int 
             L.attn_norm = upload_f32(f.require(p + "attn_norm.weight"), hp.n_embd, st);
             L.ffn_norm = upload_f32(f.require(p + "ffn_norm.weight"), hp.n_embd, st);
             weight_bytes_per_token += 2 * (int64_t)hp.n_embd * 4;
-            struct { const char *n; DevMatrix *d; int64_t rows, cols; } ms[] = {
-                {"attn_q.weight", &L.wq, QD, hp.n_embd},      {"attn_k.weight", &L.wk, KVD, hp.n_embd},
-                {"attn_v.weight", &L.wv, KVD, hp.n_embd},     {"attn_output.weight", &L.wo, hp.n_embd, QD},
-                {"ffn_gate.weight", &L.w_gate, hp.n_ff, hp.n_embd}, {"ffn_up.weight", &L.w_up, hp.n_ff, hp.n_embd},
-                {"ffn_down.weight", &L.w_down, hp.n_embd, hp.n_ff}};
+            // rows / cols = the tensor's full shape; split: 1 = this rank's rows (column-parallel), 2 = this rank's K slice
+            struct { const char *n; DevMatrix *d; int64_t rows, cols; int split; } ms[] = {
+                {"attn_q.weight", &L.wq, QD_full, hp.n_embd, 1},      {"attn_k.weight", &L.wk, KVD_full, hp.n_embd, 1},
+                {"attn_v.weight", &L.wv, KVD_full, hp.n_embd, 1},     {"attn_output.weight", &L.wo, hp.n_embd, QD_full, 2},
+                {"ffn_gate.weight", &L.w_gate, FF_full, hp.n_embd, 1}, {"ffn_up.weight", &L.w_up, FF_full, hp.n_embd, 1},
+                {"ffn_down.weight", &L.w_down, hp.n_embd, FF_full, 2}};
             for (auto &m : ms) {
                 const GgufTensor &t = f.require(p + m.n);
                 if (t.ne[0] != m.cols || t.ne[1] != m.rows)
                     throw GgufError(AIOS_E_FORMAT, "tensor '" + t.name + "' has unexpected shape");
-                upload_matrix(t, *m.d, staging, pinned, pinned_bytes);
+                if (tp_size == 1) upload_matrix(t, *m.d, staging, pinned, pinned_bytes);
+                else if (m.split == 1) upload_matrix(t, *m.d, staging, pinned, pinned_bytes, tp_rank * (m.rows / tp_size), m.rows / tp_size);
+                else upload_matrix(t, *m.d, staging, pinned, pinned_bytes, 0, -1, tp_rank * (m.cols / tp_size), m.cols / tp_size);
             }
             if (L.w_gate.w.type != L.w_up.w.type)
                 throw GgufError(AIOS_E_FORMAT, "ffn_gate and ffn_up of layer " + std::to_string(i) + " differ in type");
@@ -186,7 +216,8 @@ Model::Model(Engine *e, const std::string &name_, const std::string &path_, int 
         output_norm = upload_f32(f.require("output_norm.weight"), hp.n_embd, st);
         weight_bytes_per_token += (int64_t)hp.n_embd * 4;
         const GgufTensor *out = f.find("output.weight");
-        upload_matrix(out ? *out : te, output, staging, pinned, pinned_bytes);  // tied embeddings when absent
+        if (tp_size == 1) upload_matrix(out ? *out : te, output, staging, pinned, pinned_bytes);  // tied embeddings when absent
+        else upload_matrix(out ? *out : te, output, staging, pinned, pinned_bytes, (int64_t)tp_rank * vocab_local, vocab_local);
         tc_ok = true;
         for (const Layer &L : layers)
             for (const DevMatrix *dm : {&L.wq, &L.wk, &L.wv, &L.wo, &L.w_gate, &L.w_up, &L.w_down})
@@ -272,8 +303,9 @@ Seq::Seq(Model *m_, bool internal_) : m(m_), internal(internal_) {
         pfd_counters = DevBuf(((size_t)hp.n_head_kv + 16) * sizeof(unsigned));  // [n_kv] group barriers, then the grid barrier
         CUDA_CHECK(cudaMemset(pfd_att_acc.p, 0, pfd_att_acc.bytes));
         CUDA_CHECK(cudaMemset(pfd_counters.p, 0, pfd_counters.bytes));
+        if (m->tp_size > 1) tp_part64 = DevBuf((size_t)hp.n_embd * sizeof(double));
         reset();
-        build_pfd();
+        if (m->tp_size == 1) build_pfd();
     } catch (...) {
         std::lock_guard<std::mutex> lk(m->mu);
         if (!internal) m->user_seqs--;
@@ -307,38 +339,34 @@ void Seq::reset() {
     CUDA_CHECK(cudaMemcpy(state.p, &s, sizeof(s), cudaMemcpyHostToDevice));
 }
 
-// ---- the token pass as a list of launches
-namespace {
-struct PassLaunch {
-    int kind;  // 0 GEMV, 1 attention
-    GemvParams g{};
-    AttnParams a{};
-    int grid = 0;
-    bool pdl = false;
-};
-
-}  // namespace
-
-void Seq::launch_token_pass(bool from_prompt, int prompt_idx, int pos_value, bool want_logits, cudaStream_t st, int *n_launch) {
+// ---- the token pass as a list of launches (PassLaunch: engine.h)
+void Seq::launch_embed(bool from_prompt, int prompt_idx, int pos_value, cudaStream_t st) {
     const HParams &hp = m->hp;
     SeqState *sd = state.as<SeqState>();
-    const int n_sms = m->eng->n_sms;
-    int launches = 0;
-    const bool pdl = !(m->eng->flags & AIOS_ENGINE_NO_PDL);
     const int32_t *tok_ptr = from_prompt ? prompt.as<int32_t>() + prompt_idx : &sd->cur_token;
     TIMED(2, launch_embed_row(m->tok_embd_type, m->tok_embd_raw.p, m->tok_embd_row_bytes, hp.n_embd, tok_ptr, x.as<float>(),
                      from_prompt ? &sd->pos : nullptr, pos_value, from_prompt ? &sd->cur_token : nullptr, st));
-    launches++;
+}
+
+// With a tensor-parallel shard (m->tp_size > 1) hp holds the LOCAL head / FF counts, the K-split projections
+// (attn_output, ffn_down) store their unrounded double sums into tp_part64 and are marked reduce_after: the driver
+// (tp.cu) all-reduces the partials and adds them to x; the lm_head writes this rank's slice of the logits.
+void Seq::build_token_pass(bool want_logits, std::vector<PassLaunch> &ls) {
+    const HParams &hp = m->hp;
+    SeqState *sd = state.as<SeqState>();
+    const int n_sms = m->eng->n_sms;
+    const bool pdl = !(m->eng->flags & AIOS_ENGINE_NO_PDL);
+    const bool tp = m->tp_size > 1;
     const int QD = hp.n_head * hp.head_dim, KVD = hp.n_head_kv * hp.head_dim;
     const int amode = (m->eng->flags & AIOS_ENGINE_ATTN_CLUSTER) ? 2 : 0;
     // with the split attention kernel, RoPE + f16 rounding + KV append move into the q/k/v GEMV's epilogue
     // (EPI_QKV_ROPE): the attention kernel then starts on final data, with no dependent table loads of its own
     const bool rope_in_gemv = amode == 0 && attn_split_usable(hp.n_ctx, hp.head_dim) && !(m->eng->flags & AIOS_ENGINE_NO_ROPE_EPILOGUE);
-    std::vector<PassLaunch> ls;
+    ls.clear();
     ls.reserve((size_t)hp.n_layer * 6 + 2);
-    auto add_gemv = [&](const GemvParams &p, bool use_pdl) {
+    auto add_gemv = [&](const GemvParams &p, bool use_pdl, bool reduce_after = false) {
         PassLaunch L;
-        L.kind = 0; L.g = p; L.pdl = use_pdl;
+        L.kind = 0; L.g = p; L.pdl = use_pdl; L.reduce_after = reduce_after;
         L.g.evict_first = m->eng->evict_first ? 1 : 0;
         L.grid = gemv_plan_grid(L.g, n_sms);
         ls.push_back(L);
@@ -389,46 +417,60 @@ void Seq::launch_token_pass(bool from_prompt, int prompt_idx, int pos_value, boo
         }
         {   // attention output projection + residual add
             GemvParams p{};
-            p.n_seg = 1; p.epi = EPI_ADD; p.k = QD;
-            p.seg[0] = L.wo.w; p.out[0] = x.as<float>(); p.x = att.as<float>();
-            add_gemv(p, pdl);
+            p.n_seg = 1; p.epi = tp ? EPI_STORE_F64 : EPI_ADD; p.k = QD;
+            p.seg[0] = L.wo.w; p.out[0] = tp ? tp_part64.as<float>() : x.as<float>(); p.x = att.as<float>();
+            add_gemv(p, pdl, tp);
         }
-        {   // RMSNorm + gate/up + SwiGLU
+        {   // RMSNorm + gate/up + SwiGLU (after an all-reduce the previous launch on the stream is not a PDL primary)
             GemvParams p{};
             p.n_seg = 2; p.epi = EPI_SWIGLU; p.k = hp.n_embd;
             p.seg[0] = L.w_gate.w; p.seg[1] = L.w_up.w; p.out[0] = h.as<float>();
             p.x = x.as<float>(); p.norm_w = L.ffn_norm.as<float>(); p.eps = hp.rms_eps;
-            add_gemv(p, pdl);
+            add_gemv(p, pdl && !tp);
         }
         {   // down projection + residual add
             GemvParams p{};
-            p.n_seg = 1; p.epi = EPI_ADD; p.k = hp.n_ff;
-            p.seg[0] = L.w_down.w; p.out[0] = x.as<float>(); p.x = h.as<float>();
-            add_gemv(p, pdl);
+            p.n_seg = 1; p.epi = tp ? EPI_STORE_F64 : EPI_ADD; p.k = hp.n_ff;
+            p.seg[0] = L.w_down.w; p.out[0] = tp ? tp_part64.as<float>() : x.as<float>(); p.x = h.as<float>();
+            add_gemv(p, pdl, tp);
         }
     }
     if (want_logits) {
         // the lm_head epilogue keeps the packed (value, index) arg-max of the logits it writes
         GemvParams p{};
         p.n_seg = 1; p.epi = EPI_STORE; p.k = hp.n_embd;
-        p.seg[0] = m->output.w; p.out[0] = logits.as<float>();
+        p.seg[0] = m->output.w; p.out[0] = logits.as<float>() + (size_t)m->tp_rank * m->vocab_local;
         p.x = x.as<float>(); p.norm_w = m->output_norm.as<float>(); p.eps = hp.rms_eps;
-        p.argmax_key = &sd->argmax_key;
+        p.argmax_key = tp ? nullptr : &sd->argmax_key;
         add_gemv(p, false);
     }
-    for (size_t i = 0; i < ls.size(); i++) {
-        PassLaunch &L = ls[i];
-        unsigned long long *tr = trace_base && launches < 4096 ? trace_base + (size_t)launches * 8 : nullptr;
-        if (L.kind == 0) {
-            if (L.g.argmax_key) CUDA_CHECK(cudaMemsetAsync(&sd->argmax_key, 0, sizeof(unsigned long long), st));
-            L.g.trace = tr;
-            TIMED(0, launch_gemv(L.g, L.grid, st, L.pdl));
-        } else {
-            L.a.trace = tr;
-            TIMED(1, launch_attn_decode(L.a, st, L.pdl, amode));
-        }
-        launches++;
+    if (tp)  // the first launch of a layer follows the all-reduce's add kernel, which is no PDL primary either
+        for (size_t i = 1; i < ls.size(); i++)
+            if (ls[i - 1].reduce_after) ls[i].pdl = false;
+}
+
+void Seq::launch_pass_item(PassLaunch &L, cudaStream_t st, int launch_index) {
+    SeqState *sd = state.as<SeqState>();
+    unsigned long long *tr = trace_base && launch_index < 4096 ? trace_base + (size_t)launch_index * 8 : nullptr;
+    if (L.kind == 0) {
+        if (L.g.argmax_key) CUDA_CHECK(cudaMemsetAsync(&sd->argmax_key, 0, sizeof(unsigned long long), st));
+        L.g.trace = tr;
+        TIMED(0, launch_gemv(L.g, L.grid, st, L.pdl));
+    } else {
+        L.a.trace = tr;
+        const int amode = (m->eng->flags & AIOS_ENGINE_ATTN_CLUSTER) ? 2 : 0;
+        TIMED(1, launch_attn_decode(L.a, st, L.pdl, amode));
     }
+}
+
+void Seq::launch_token_pass(bool from_prompt, int prompt_idx, int pos_value, bool want_logits, cudaStream_t st, int *n_launch) {
+    if (m->tp_size > 1) throw std::logic_error("a tensor-parallel shard is driven by its group (tp.cu)");
+    int launches = 0;
+    launch_embed(from_prompt, prompt_idx, pos_value, st);
+    launches++;
+    std::vector<PassLaunch> ls;
+    build_token_pass(want_logits, ls);
+    for (size_t i = 0; i < ls.size(); i++) launch_pass_item(ls[i], st, launches++);
     if (n_launch) *n_launch += launches;
 }
 

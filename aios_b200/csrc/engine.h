@@ -99,7 +99,12 @@ struct Model {
     std::mutex mu;
     int attn_splits = 16;
 
-    Model(Engine *e, const std::string &name, const std::string &path, int n_ctx);
+    // tp_size > 1: this is shard tp_rank of a tensor-parallel model (tp.cu): q/k/v, gate/up and the lm_head hold this
+    // rank's rows (heads / FF columns / vocabulary slice), attn_output and ffn_down this rank's K slice; hp holds the
+    // LOCAL head and FF counts, n_embd and n_vocab stay global
+    Model(Engine *e, const std::string &name, const std::string &path, int n_ctx, int tp_rank = 0, int tp_size = 1);
+    int tp_rank = 0, tp_size = 1;
+    int vocab_local = 0;  // rows of the lm_head held here (= n_vocab without tensor parallelism)
     ~Model();
     // position-major KV layout: [position][layer][K|V][n_kv*hd] f16
     size_t kvd() const { return (size_t)hp.n_head_kv * hp.head_dim; }
@@ -107,7 +112,9 @@ struct Model {
     size_t kv_pos_bytes() const { return kv_pos_elems() * 2; }
 
    private:
-    void upload_matrix(const GgufTensor &t, DevMatrix &dst, DevBuf &staging, void *pinned, size_t pinned_bytes);
+    // rows [row0, row0 + n_rows) x weights [k0, k0 + k_len) of the tensor (n_rows < 0: all rows, k_len < 0: the whole K)
+    void upload_matrix(const GgufTensor &t, DevMatrix &dst, DevBuf &staging, void *pinned, size_t pinned_bytes, int64_t row0 = 0,
+                       int64_t n_rows = -1, int64_t k0 = 0, int64_t k_len = -1);
 };
 
 struct SeqState {  // lives in device memory
@@ -116,6 +123,16 @@ struct SeqState {  // lives in device memory
     int32_t cur_token;  // token fed at `pos`
     int32_t pad;
     unsigned long long argmax_key;
+};
+
+// one launch of the token pass (Seq::build_token_pass)
+struct PassLaunch {
+    int kind = 0;  // 0 GEMV, 1 attention
+    GemvParams g{};
+    AttnParams a{};
+    int grid = 0;
+    bool pdl = false;
+    bool reduce_after = false;  // tensor parallel: g.out[0] holds f64 partial sums to all-reduce and add to x
 };
 
 struct Seq {
@@ -162,10 +179,15 @@ struct Seq {
     void restore();
     void read_logits(float *out);
     void set_mask(const uint8_t *bits, int n_bytes);  // null: sample from every token again
+    // the token pass in pieces, for the tensor-parallel driver (tp.cu), which runs the ranks' lists in lockstep
+    DevBuf tp_part64;  // [n_embd] doubles, tensor-parallel shards only
+    void launch_embed(bool from_prompt, int prompt_idx, int pos_value, cudaStream_t st);
+    void build_token_pass(bool want_logits, std::vector<PassLaunch> &ls);
+    void launch_pass_item(PassLaunch &L, cudaStream_t st, int launch_index);
+    void launch_sample_kernel(const aios_sampling &sp, cudaStream_t st);
 
    private:
     void launch_token_pass(bool from_prompt, int prompt_idx, int pos_value, bool want_logits, cudaStream_t st, int *n_launch);
-    void launch_sample_kernel(const aios_sampling &sp, cudaStream_t st);
     void prefill_chunk(int idx0, int T, int pos0, bool want_logits, cudaStream_t st);  // tokens prompt[idx0 .. idx0+T)
     void prefill_tc(int idx0, int T, int pos0, bool want_logits, cudaStream_t st);     // the same on the tensor-core path
     void ensure_graph(const aios_sampling &sp);

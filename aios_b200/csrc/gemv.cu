@@ -109,7 +109,8 @@ __global__ void __launch_bounds__(GEMV_THREADS, 1) gemv_kernel(const GemvParams 
             const int row = row0 + (lane >> 4);
             if (row < N) {
                 const float v = (float)tot;
-                if (p.epi == EPI_ADD) out[row] = __fadd_rn(out[row], v);
+                if (p.epi == EPI_STORE_F64) reinterpret_cast<double *>(out)[row] = tot;
+                else if (p.epi == EPI_ADD) out[row] = __fadd_rn(out[row], v);
                 else out[row] = v;
                 if (p.argmax_key) {
                     const unsigned long long key = argmax_key(v, row);
@@ -220,7 +221,8 @@ __device__ __forceinline__ void gemv_db_body(const GemvParams &p, int seg, uint8
                 const int row = crow + (lane >> 4);
                 if (row < N) {
                     const float v = (float)tot;
-                    if (p.epi == EPI_ADD) out[row] = __fadd_rn(out[row], v);
+                    if (p.epi == EPI_STORE_F64) reinterpret_cast<double *>(out)[row] = tot;
+                    else if (p.epi == EPI_ADD) out[row] = __fadd_rn(out[row], v);
                     else out[row] = v;
                     if (p.argmax_key) {
                         const unsigned long long key = argmax_key(v, row);

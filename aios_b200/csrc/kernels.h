@@ -25,6 +25,9 @@ enum GemvEpilogue : int {
     // segments = (attn_q, attn_k, attn_v): RoPE + f16 rounding in the epilogue; q -> out[0] (f32 holding f16 values),
     // k and v -> row *n_past_ptr of the layer's KV cache.  Attention then reads every position from the cache.
     EPI_QKV_ROPE = 3,
+    // out[n] (a double array) = the row's double sum, unrounded: the partial of a K-split matrix whose other parts live on
+    // other GPUs (tensor parallelism): the f64 partials are all-reduced and rounded to f32 once, like the unsplit sum
+    EPI_STORE_F64 = 4,
 };
 
 struct RopeKv {              // EPI_QKV_ROPE only

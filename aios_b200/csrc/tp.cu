@@ -1,0 +1,367 @@
+// tp.cu — tensor parallelism for models that need more than one GPU (BASELINE.json configs[4]:
+// Llama-3-70B at TP 2/4/8).  The reference's hardware table lists 70B-class local models
+// (docs/HARDWARE.md:135-138); north_star asks for 2/4/8-way tensor parallelism with NCCL all-reduce over NVLink.
+//
+// Megatron-style split inside ONE process (one engine, one stream and one NCCL communicator per GPU, driven by the
+// calling thread): attn_q/k/v, ffn_gate/up and the lm_head are split by rows (heads / FF columns / vocabulary slice),
+// attn_output and ffn_down by K at multiples of 256 (quant blocks run along K).  Every rank holds the replicated
+// residual stream; per layer two all-reduces (after attn_output and after ffn_down) and, per token, one all-gather of
+// the logits slices.
+//
+// How the order-free double sum crosses ranks: a K-split GEMV stores its rows' UNROUNDED double sums (EPI_STORE_F64);
+// the f64 partials are all-reduced (ncclDouble, ncclSum) and rounded to f32 once, then added to the residual — the same
+// set of f32 terms as the unsplit sum, so the result is the single-GPU result bit for bit (up to the usual ~1e-7
+// chance per value that a double sum's association moves the final rounding).  Every rank then samples from the same
+// full logits with the same deterministic sampler: no broadcast of the token is needed.
+//
+// This is the plain-NCCL baseline (2 x n_layer latency-bound all-reduces of n_embd doubles per token, launched eagerly,
+// no CUDA graph); the fused one-shot all-reduce in the attn_output / ffn_down epilogue is the next step.
+#include <dlfcn.h>
+#include <math.h>
+#include <nccl.h>
+#include <string.h>
+
+#include <mutex>
+
+#include <algorithm>
+#include <memory>
+#include <vector>
+
+#include "common.cuh"
+#include "engine.h"
+#include "tp.h"
+
+namespace aios {
+
+namespace {
+struct Nccl {
+    ncclResult_t (*CommInitAll)(ncclComm_t *, int, const int *) = nullptr;
+    ncclResult_t (*CommDestroy)(ncclComm_t) = nullptr;
+    ncclResult_t (*AllReduce)(const void *, void *, size_t, ncclDataType_t, ncclRedOp_t, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*AllGather)(const void *, void *, size_t, ncclDataType_t, ncclComm_t, cudaStream_t) = nullptr;
+    ncclResult_t (*GroupStart)() = nullptr;
+    ncclResult_t (*GroupEnd)() = nullptr;
+    const char *(*GetErrorString)(ncclResult_t) = nullptr;
+};
+// libnccl is opened on first use: the library itself has no link-time dependency on it (single-GPU users never load it)
+const Nccl &nccl() {
+    static Nccl n;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void *h = dlopen("libnccl.so.2", RTLD_NOW | RTLD_GLOBAL);
+        if (!h) h = dlopen("libnccl.so", RTLD_NOW | RTLD_GLOBAL);
+        if (!h) throw CudaError(std::string("tensor parallelism needs NCCL: ") + dlerror());
+        auto get = [&](const char *name, void *slot) {
+            void *f = dlsym(h, name);
+            if (!f) throw CudaError(std::string("NCCL symbol missing: ") + name);
+            memcpy(slot, &f, sizeof(f));
+        };
+        get("ncclCommInitAll", &n.CommInitAll); get("ncclCommDestroy", &n.CommDestroy); get("ncclAllReduce", &n.AllReduce);
+        get("ncclAllGather", &n.AllGather); get("ncclGroupStart", &n.GroupStart); get("ncclGroupEnd", &n.GroupEnd);
+        get("ncclGetErrorString", &n.GetErrorString);
+    });
+    return n;
+}
+void nccl_check(ncclResult_t r, const char *what) {
+    if (r != ncclSuccess) throw CudaError(std::string(what) + ": " + nccl().GetErrorString(r));
+}
+
+// x[i] += (float) part[i]   (the all-reduced f64 partial sums of a K-split projection, rounded once)
+__global__ void add_f64_kernel(float *x, const double *part, int n) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) x[i] = __fadd_rn(x[i], (float)part[i]);
+}
+}  // namespace
+
+struct TpRank {
+    std::unique_ptr<Engine> eng;
+    std::unique_ptr<Model> model;
+    std::unique_ptr<Seq> seq;
+    ncclComm_t comm = nullptr;
+};
+
+struct TpModelImpl {
+    std::vector<TpRank> ranks;
+    int n = 0;
+    int n_past = 0;
+    bool have_logits = false;
+    // all-reduce timing (rank 0's stream), filled when timing is on
+    bool timing = false;
+    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ar_events;
+
+    ~TpModelImpl() {
+        for (auto &r : ranks) {
+            if (r.eng) cudaSetDevice(r.eng->device);
+            r.seq.reset();
+            r.model.reset();
+            if (r.comm) nccl().CommDestroy(r.comm);
+            r.eng.reset();
+        }
+        for (auto &e : ar_events) { cudaEventDestroy(e.first); cudaEventDestroy(e.second); }
+    }
+    const HParams &hp() const { return ranks[0].model->hp; }
+    void all_reduce_add_to_x();
+    // one token through every rank's shard in lockstep; launches counts rank 0's kernels (collectives included)
+    void token_pass(bool from_prompt, int prompt_idx, int pos_value, bool want_logits, int *launches);
+    void sample_all(const aios_sampling &sp);
+    void sync_all();
+    void set_pos_step();
+    std::vector<std::vector<PassLaunch>> lists;  // per rank; [0] without, rebuilt when want_logits changes
+    int lists_logits = -1;
+};
+
+void TpModelImpl::sync_all() {
+    for (auto &r : ranks) {
+        r.eng->make_current();
+        CUDA_CHECK(cudaStreamSynchronize(r.eng->stream));
+        CUDA_CHECK(cudaGetLastError());
+    }
+}
+
+// part64 of every rank: all-reduce (sum of doubles), then x += (float) sum on every rank
+void TpModelImpl::all_reduce_add_to_x() {
+    const int E = hp().n_embd;
+    cudaEvent_t e0 = nullptr, e1 = nullptr;
+    if (timing) {
+        ranks[0].eng->make_current();
+        CUDA_CHECK(cudaEventCreate(&e0));
+        CUDA_CHECK(cudaEventCreate(&e1));
+        CUDA_CHECK(cudaEventRecord(e0, ranks[0].eng->stream));
+    }
+    nccl_check(nccl().GroupStart(), "ncclGroupStart");
+    for (auto &r : ranks)
+        nccl_check(nccl().AllReduce(r.seq->tp_part64.p, r.seq->tp_part64.p, (size_t)E, ncclDouble, ncclSum, r.comm, r.eng->stream), "ncclAllReduce");
+    nccl_check(nccl().GroupEnd(), "ncclGroupEnd");
+    if (timing) {
+        ranks[0].eng->make_current();
+        CUDA_CHECK(cudaEventRecord(e1, ranks[0].eng->stream));
+        ar_events.emplace_back(e0, e1);
+    }
+    for (auto &r : ranks) {
+        r.eng->make_current();
+        add_f64_kernel<<<(E + 255) / 256, 256, 0, r.eng->stream>>>(r.seq->x.as<float>(), r.seq->tp_part64.as<double>(), E);
+    }
+}
+
+void TpModelImpl::token_pass(bool from_prompt, int prompt_idx, int pos_value, bool want_logits, int *launches) {
+    if (lists_logits != (int)want_logits) {
+        lists.resize((size_t)n);
+        for (int r = 0; r < n; r++) ranks[(size_t)r].seq->build_token_pass(want_logits, lists[(size_t)r]);
+        lists_logits = (int)want_logits;
+    }
+    int li = 0;
+    for (auto &r : ranks) {
+        r.eng->make_current();
+        r.seq->launch_embed(from_prompt, prompt_idx, pos_value, r.eng->stream);
+    }
+    li++;
+    const size_t n_items = lists[0].size();
+    for (size_t i = 0; i < n_items; i++) {
+        for (int r = 0; r < n; r++) {
+            TpRank &R = ranks[(size_t)r];
+            R.eng->make_current();
+            R.seq->launch_pass_item(lists[(size_t)r][i], R.eng->stream, li);
+        }
+        li++;
+        if (lists[0][i].reduce_after) {
+            all_reduce_add_to_x();
+            li += 2;
+        }
+    }
+    if (want_logits) {  // every rank gets every slice of the logits (in place: rank r's slice already sits at r * vocab_local)
+        const size_t vl = (size_t)ranks[0].model->vocab_local;
+        nccl_check(nccl().GroupStart(), "ncclGroupStart");
+        for (int r = 0; r < n; r++) {
+            TpRank &R = ranks[(size_t)r];
+            float *lg = R.seq->logits.as<float>();
+            nccl_check(nccl().AllGather(lg + (size_t)r * vl, lg, vl, ncclFloat, R.comm, R.eng->stream), "ncclAllGather");
+        }
+        nccl_check(nccl().GroupEnd(), "ncclGroupEnd");
+        li++;
+    }
+    if (launches) *launches += li;
+}
+
+// the sampler reads pos (position of the last fed token) and step (index into out_tokens) from the device state
+void TpModelImpl::set_pos_step() {
+    const int32_t hdr[2] = {n_past - 1, 0};
+    for (auto &r : ranks) {
+        r.eng->make_current();
+        CUDA_CHECK(cudaMemcpyAsync(r.seq->state.p, hdr, sizeof(hdr), cudaMemcpyHostToDevice, r.eng->stream));
+    }
+}
+
+void TpModelImpl::sample_all(const aios_sampling &sp) {
+    for (auto &r : ranks) {
+        r.eng->make_current();
+        r.seq->launch_sample_kernel(sp, r.eng->stream);
+    }
+}
+
+// ---------------------------------------------------------------- TpModel
+TpModel::TpModel(const std::vector<int> &devices, const std::string &name, const std::string &path, int n_ctx, int flags) {
+    const int n = (int)devices.size();
+    if (n < 2 || n > 8) throw std::invalid_argument("tensor parallelism takes 2 to 8 devices");
+    for (int i = 0; i < n; i++)
+        for (int j = 0; j < i; j++)
+            if (devices[(size_t)i] == devices[(size_t)j]) throw std::invalid_argument("tensor-parallel devices must be distinct");
+    impl.reset(new TpModelImpl());
+    impl->n = n;
+    impl->ranks.resize((size_t)n);
+    for (int r = 0; r < n; r++) {
+        aios_engine_opts o{};
+        o.device = devices[(size_t)r];
+        o.max_batch = 1;
+        o.flags = flags;
+        TpRank &R = impl->ranks[(size_t)r];
+        R.eng.reset(new Engine(o));
+        R.model.reset(new Model(R.eng.get(), name, path, n_ctx, r, n));
+        R.seq.reset(new Seq(R.model.get(), /*internal=*/false));
+    }
+    std::vector<ncclComm_t> comms((size_t)n);
+    nccl_check(nccl().CommInitAll(comms.data(), n, devices.data()), "ncclCommInitAll");
+    for (int r = 0; r < n; r++) impl->ranks[(size_t)r].comm = comms[(size_t)r];
+}
+TpModel::~TpModel() = default;
+
+int TpModel::n_ranks() const { return impl->n; }
+int TpModel::n_vocab() const { return impl->hp().n_vocab; }
+int TpModel::n_ctx() const { return impl->hp().n_ctx; }
+int TpModel::n_past() const { return impl->n_past; }
+void TpModel::info(aios_model_info *o) const {
+    memset(o, 0, sizeof(*o));
+    Model &M = *impl->ranks[0].model;
+    strncpy(o->name, M.name.c_str(), sizeof(o->name) - 1);
+    strncpy(o->arch, M.arch.c_str(), sizeof(o->arch) - 1);
+    const int n = impl->n;
+    o->n_layer = M.hp.n_layer; o->n_embd = M.hp.n_embd; o->n_head = M.hp.n_head * n; o->n_head_kv = M.hp.n_head_kv * n;
+    o->head_dim = M.hp.head_dim; o->n_ff = M.hp.n_ff * n; o->n_vocab = M.hp.n_vocab; o->n_ctx = M.hp.n_ctx;
+    o->n_rot = M.hp.n_rot; o->file_type = M.hp.file_type; o->n_tensors = (int32_t)M.file->tensors().size();
+    o->max_batch = 1; o->rms_eps = M.hp.rms_eps; o->rope_freq_base = M.hp.rope_freq_base;
+    o->file_bytes = (int64_t)M.file->file_bytes(); o->weight_bytes = M.weight_bytes;
+    o->kv_bytes = (int64_t)(M.kv_pool.pages_in_use() * M.kv_pool.page_bytes);
+    o->weight_bytes_per_token = M.weight_bytes_per_token;
+    o->kv_bytes_per_position = (int64_t)M.kv_pos_bytes();
+}
+
+void TpModel::reset() {
+    for (auto &r : impl->ranks) {
+        r.eng->make_current();
+        r.seq->reset();
+    }
+    impl->n_past = 0;
+    impl->have_logits = false;
+}
+
+void TpModel::prefill(const int32_t *tokens, int n) {
+    if (n <= 0) return;
+    const HParams &hp = impl->hp();
+    if (impl->n_past + n > hp.n_ctx) throw std::runtime_error("prefill would exceed the context length");
+    for (int i = 0; i < n; i++)
+        if (tokens[i] < 0 || tokens[i] >= hp.n_vocab) throw std::invalid_argument("token id out of range");
+    for (auto &r : impl->ranks) {
+        r.eng->make_current();
+        CUDA_CHECK(cudaMemcpyAsync(r.seq->prompt.p, tokens, (size_t)n * 4, cudaMemcpyHostToDevice, r.eng->stream));
+    }
+    for (int i = 0; i < n; i++) impl->token_pass(true, i, impl->n_past + i, i == n - 1, nullptr);
+    impl->sync_all();
+    impl->n_past += n;
+    impl->have_logits = true;
+}
+
+int TpModel::decode(const aios_sampling &sp, int max_tokens, int32_t *out) {
+    if (!impl->have_logits) throw std::runtime_error("decode needs a prefill first");
+    const HParams &hp = impl->hp();
+    const int room = hp.n_ctx - impl->n_past;
+    const int n = std::min(max_tokens, room);
+    if (n <= 0) return 0;
+    impl->set_pos_step();
+    for (int i = 0; i < n; i++) {
+        impl->sample_all(sp);  // token -> state.cur_token, pos++, out_tokens[step++]
+        impl->token_pass(false, 0, 0, true, nullptr);
+    }
+    impl->sync_all();
+    TpRank &R0 = impl->ranks[0];
+    R0.eng->make_current();
+    CUDA_CHECK(cudaMemcpy(out, R0.seq->out_tokens.p, (size_t)n * 4, cudaMemcpyDeviceToHost));
+    impl->n_past += n;
+    return n;
+}
+
+void TpModel::read_logits(float *out) {
+    if (!impl->have_logits) throw std::runtime_error("no logits yet");
+    TpRank &R0 = impl->ranks[0];
+    R0.eng->make_current();
+    CUDA_CHECK(cudaMemcpy(out, R0.seq->logits.p, (size_t)impl->hp().n_vocab * 4, cudaMemcpyDeviceToHost));
+}
+
+void TpModel::bench_decode(int n_tokens, aios_tp_bench *out) {
+    if (!impl->have_logits) throw std::runtime_error("bench needs a prefill first");
+    memset(out, 0, sizeof(*out));
+    const HParams &hp = impl->hp();
+    n_tokens = std::min(n_tokens, hp.n_ctx - impl->n_past - 2);
+    if (n_tokens <= 0) throw std::runtime_error("no room left in the context");
+    aios_sampling greedy{};
+    greedy.temperature = 0.f;
+    impl->set_pos_step();
+    for (int i = 0; i < 2; i++) {  // warm-up
+        impl->sample_all(greedy);
+        impl->token_pass(false, 0, 0, true, nullptr);
+    }
+    impl->sync_all();
+    impl->n_past += 2;
+    out->n_past_begin = impl->n_past;
+    TpRank &R0 = impl->ranks[0];
+    // pass 1: the whole region, nothing else on the streams
+    R0.eng->make_current();
+    cudaEvent_t a, b;
+    CUDA_CHECK(cudaEventCreate(&a));
+    CUDA_CHECK(cudaEventCreate(&b));
+    int launches = 0;
+    impl->sync_all();
+    R0.eng->make_current();
+    CUDA_CHECK(cudaEventRecord(a, R0.eng->stream));
+    for (int i = 0; i < n_tokens; i++) {
+        impl->sample_all(greedy);
+        launches++;
+        impl->token_pass(false, 0, 0, true, &launches);
+    }
+    R0.eng->make_current();
+    CUDA_CHECK(cudaEventRecord(b, R0.eng->stream));
+    impl->sync_all();
+    R0.eng->make_current();
+    CUDA_CHECK(cudaEventElapsedTime(&out->ms_total, a, b));
+    impl->n_past += n_tokens;
+    out->n_tokens = n_tokens;
+    out->kernel_launches = launches;
+    out->n_ranks = impl->n;
+    // pass 2 (a few tokens): an event pair around every all-reduce on rank 0's stream
+    const int n_timed = std::min(8, hp.n_ctx - impl->n_past);
+    if (n_timed > 0) {
+        impl->timing = true;
+        for (int i = 0; i < n_timed; i++) {
+            impl->sample_all(greedy);
+            impl->token_pass(false, 0, 0, true, nullptr);
+        }
+        impl->sync_all();
+        impl->timing = false;
+        impl->n_past += n_timed;
+        R0.eng->make_current();
+        double ms = 0;
+        for (auto &e : impl->ar_events) {
+            float t = 0;
+            CUDA_CHECK(cudaEventElapsedTime(&t, e.first, e.second));
+            ms += t;
+            cudaEventDestroy(e.first);
+            cudaEventDestroy(e.second);
+        }
+        out->n_allreduce_per_token = (int32_t)(impl->ar_events.size() / (size_t)n_timed);
+        out->us_per_allreduce = impl->ar_events.empty() ? 0.f : (float)(ms * 1e3 / (double)impl->ar_events.size());
+        impl->ar_events.clear();
+    }
+    out->n_past_end = impl->n_past;
+    cudaEventDestroy(a);
+    cudaEventDestroy(b);
+}
+
+}  // namespace aios

@@ -54,6 +54,8 @@ ARCHS = {
     "tiny-gqa4": Arch("tiny-gqa4", 3, 512, 8, 2, 64, 1024, 1000, 10000.0, 1e-5, 512),
     # multi-head attention with 32 kv heads (Llama-2-7B's head layout on a small width)
     "tiny-mha32": Arch("tiny-mha32", 2, 2048, 32, 32, 64, 512, 512, 10000.0, 1e-5, 512),
+    # splits four ways (tensor-parallel tests): 4 kv heads, n_head*head_dim / 4 and FF / 4 multiples of 256
+    "tiny-tp4": Arch("tiny-tp4", 2, 1024, 16, 4, 64, 1024, 512, 10000.0, 1e-5, 512),
     # SURVEY.md Appendix B shapes
     "tinyllama-1.1b": Arch("tinyllama-1.1b", 22, 2048, 32, 4, 64, 5632, 32000, 10000.0, 1e-5, 2048),
     "mistral-7b": Arch("mistral-7b", 32, 4096, 32, 8, 128, 14336, 32000, 1000000.0, 1e-5, 32768),

@@ -349,6 +349,36 @@ int aios_bench_batch_decode(aios_model *m, int32_t n_lanes, const int32_t *promp
 int aios_bench_gemv(aios_engine *e, int32_t ggml_type, int64_t n_rows, int64_t k, int32_t n_copies,
                     int32_t iters, float *ms_per_launch);
 
+/* ---- tensor parallelism: one model split over 2..8 GPUs of this node --------------------------------------------
+ * (BASELINE.json configs[4], Llama-3-70B at TP 2/4/8.  The reference's hardware table lists
+ *  70B-class local models, docs/HARDWARE.md:135-138; llama-server's counterpart is --tensor-split / --split-mode row.)
+ * attn_q/k/v, ffn_gate/up and the lm_head are split by rows, attn_output and ffn_down along K; per layer two NCCL
+ * all-reduces of the projections' f64 partial sums (so the tokens are those of the unsplit model), per token one
+ * all-gather of the logits.  libnccl.so.2 is opened on the first aios_tp_model_load; the library does not link to it.
+ * One process drives all the shards; calls on one aios_tp_model must not overlap.  The model must split evenly:
+ * n_head_kv, n_ff and n_vocab divisible by n_devices, and n_head*head_dim / n_devices and n_ff / n_devices
+ * multiples of 256 (AIOS_E_FORMAT otherwise). */
+typedef struct aios_tp_model aios_tp_model;
+int aios_tp_model_load(const int32_t *devices, int32_t n_devices, const char *name, const char *gguf_path, int32_t n_ctx,
+                       int32_t engine_flags, aios_tp_model **out);
+int aios_tp_model_unload(aios_tp_model *m);
+int aios_tp_model_info(const aios_tp_model *m, aios_model_info *out);   /* weight_bytes: one shard's           */
+int aios_tp_reset(aios_tp_model *m);
+int aios_tp_prefill(aios_tp_model *m, const int32_t *tokens, int32_t n_tokens);
+int aios_tp_decode(aios_tp_model *m, const aios_sampling *sp, int32_t max_tokens, int32_t *out_tokens, int32_t *n_out);
+int aios_tp_get_logits(aios_tp_model *m, float *out, int32_t n);
+/* n_tokens greedy steps timed with CUDA events on rank 0's stream (every rank runs the same launches and the
+ * collectives keep them in step), then 8 more with an event pair around every all-reduce */
+typedef struct aios_tp_bench {
+    float ms_total;
+    int32_t n_tokens, n_ranks;
+    int32_t kernel_launches;        /* rank 0: kernels + collectives inside the timed region     */
+    int32_t n_past_begin, n_past_end;
+    int32_t n_allreduce_per_token;
+    float us_per_allreduce;         /* average, n_embd doubles each                              */
+} aios_tp_bench;
+int aios_tp_bench_decode(aios_tp_model *m, int32_t n_tokens, aios_tp_bench *out);
+
 #ifdef __cplusplus
 }
 #endif

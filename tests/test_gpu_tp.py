@@ -1,0 +1,77 @@
+"""Tensor parallelism (aios_tp_*): a model split over 2 / 4 GPUs must produce the unsplit model's logits and tokens.
+
+The K-split projections all-reduce f64 partial sums and round once, so the comparison is bit for bit (against the
+oracle, which is also what the single-GPU engine is pinned to).  Skipped on boxes with fewer GPUs.
+(BASELINE.json configs[4]; reference: docs/HARDWARE.md:135-138 lists the 70B-class models this exists for.)
+"""
+import numpy as np
+import pytest
+
+from aios_b200 import capi
+from aios_b200 import gguf_synth as gs
+
+pytestmark = pytest.mark.gpu
+
+
+def _need_gpus(n):
+    if capi.device_count() < n:
+        pytest.skip(f"needs {n} GPUs")
+
+
+@pytest.mark.parametrize("arch,ftype,n_dev", [("tiny-gqa4", "Q4_K_M", 2), ("tiny-gqa4", "Q8_0", 2), ("tiny-tp4", "Q4_K_M", 4),
+                                             ("tiny-tp4", "Q6_K", 2)])
+def test_tp_matches_oracle(oracle, tmp_models, arch, ftype, n_dev):
+    _need_gpus(n_dev)
+    path = tmp_models(arch, ftype)
+    prompt = gs.synthetic_prompt(arch, 24, 5)
+    om = oracle.OracleModel(path, n_ctx=128)
+    ref_logits = om.eval(prompt)
+    ref, _ = om.greedy(prompt, 24)
+    tp = capi.TpModel(list(range(n_dev)), "tp", path, n_ctx=128)
+    try:
+        assert tp.info.n_head == gs.ARCHS[arch].n_head and tp.info.n_ff == gs.ARCHS[arch].n_ff
+        tp.reset()
+        tp.prefill(prompt)
+        assert np.array_equal(tp.logits().view(np.uint32), ref_logits.view(np.uint32))
+        assert np.array_equal(tp.decode(24), ref)
+        # a second request on the same shards, prompt fed in two pieces
+        tp.reset()
+        tp.prefill(prompt[:10])
+        tp.prefill(prompt[10:])
+        assert np.array_equal(tp.decode(24), ref)
+    finally:
+        tp.unload()
+
+
+def test_tp_stochastic_matches_single_gpu(tmp_models):
+    """Every rank draws from the same logits with the same counter-based generator: the split model's sampled tokens
+    are the single-GPU engine's."""
+    _need_gpus(2)
+    path = tmp_models("tiny-gqa4", "Q4_K_M")
+    prompt = gs.synthetic_prompt("tiny-gqa4", 12, 9)
+    sp = capi.make_sampling(temperature=0.9, top_k=50, top_p=0.9, min_p=0.02, seed=1234)
+    eng = capi.Engine(device=0)
+    try:
+        m = eng.load_model("one", path, n_ctx=128)
+        want = m.generate(prompt, 32, sp)
+        m.unload()
+    finally:
+        eng.close()
+    tp = capi.TpModel([0, 1], "tp", path, n_ctx=128)
+    try:
+        assert np.array_equal(tp.generate(prompt, 32, sp), want)
+        b = tp.bench_decode(16)
+        assert b.n_ranks == 2 and b.n_tokens == 16 and b.n_allreduce_per_token == 2 * gs.ARCHS["tiny-gqa4"].n_layer
+        assert b.us_per_allreduce > 0 and b.ms_total > 0
+    finally:
+        tp.unload()
+
+
+def test_tp_rejects_uneven_split(tmp_models):
+    _need_gpus(2)
+    path = tmp_models("tiny", "Q4_K_M")  # n_head * head_dim = 256: half of it is no multiple of 256
+    with pytest.raises(capi.AiosError) as ei:
+        capi.TpModel([0, 1], "bad", path, n_ctx=64)
+    assert ei.value.code == capi.E_FORMAT
+    with pytest.raises(capi.AiosError):
+        capi.TpModel([0, 0], "dup", path, n_ctx=64)
