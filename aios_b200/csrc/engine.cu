@@ -364,9 +364,16 @@ void Seq::build_token_pass(bool want_logits, std::vector<PassLaunch> &ls) {
     const bool rope_in_gemv = amode == 0 && attn_split_usable(hp.n_ctx, hp.head_dim) && !(m->eng->flags & AIOS_ENGINE_NO_ROPE_EPILOGUE);
     ls.clear();
     ls.reserve((size_t)hp.n_layer * 6 + 2);
+    int n_reduce = 0;
     auto add_gemv = [&](const GemvParams &p, bool use_pdl, bool reduce_after = false) {
         PassLaunch L;
         L.kind = 0; L.g = p; L.pdl = use_pdl; L.reduce_after = reduce_after;
+        if (reduce_after && tp_push.n > 0) {
+            L.g.epi = EPI_PUSH_F64;
+            L.g.push = tp_push;
+            L.g.push.index = n_reduce;
+        }
+        if (reduce_after) n_reduce++;
         L.g.evict_first = m->eng->evict_first ? 1 : 0;
         L.grid = gemv_plan_grid(L.g, n_sms);
         ls.push_back(L);

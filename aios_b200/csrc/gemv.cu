@@ -26,6 +26,29 @@
 
 namespace aios {
 
+// ---- EPI_PUSH_F64 (tensor parallelism, tp.cu): the row's double sum goes to every rank's receive slab; when the whole
+// grid has stored, its last CTA raises this rank's arrival flag on every rank.  Plain stores and a release store over
+// NVLink peer mappings; the consumer (tp_wait_add_kernel) acquires the flags and reads the slabs past L1.
+__device__ __forceinline__ unsigned tp_push_epoch(const GemvParams &p) {
+    return __ldcg(p.push.tick) * (unsigned)p.push.per_token + (unsigned)p.push.index;
+}
+__device__ __forceinline__ void tp_push_store(const GemvParams &p, int row, int n_rows, double tot, unsigned ep) {
+    const size_t off = (size_t)(ep & 1u) * (size_t)n_rows + (size_t)row;
+    for (int r = 0; r < p.push.n; r++) p.push.dst[r][off] = tot;
+}
+__device__ __forceinline__ void tp_push_signal(const GemvParams &p, unsigned ep) {
+    __threadfence_system();  // this thread's slab stores are visible system-wide before the CTA counts itself done
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        const unsigned old = atomicAdd(p.push.done, 1u);
+        if (old == gridDim.x - 1) {
+            *p.push.done = 0u;  // the next launch on this GPU starts counting from zero
+            __threadfence_system();
+            for (int r = 0; r < p.push.n; r++) asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p.push.flag[r]), "r"(ep) : "memory");
+        }
+    }
+}
+
 template <int TYPE>
 __global__ void __launch_bounds__(GEMV_THREADS, 1) gemv_kernel(const GemvParams p) {
     extern __shared__ __align__(16) uint8_t smem[];
@@ -88,6 +111,7 @@ __global__ void __launch_bounds__(GEMV_THREADS, 1) gemv_kernel(const GemvParams 
     float *out = p.out[seg];
     unsigned long long best = 0ull;
     const int rope_pos = p.epi == EPI_QKV_ROPE ? __ldcg(p.rope.n_past_ptr) : 0;
+    const unsigned push_ep = p.epi == EPI_PUSH_F64 ? tp_push_epoch(p) : 0u;
     for (int row0 = row_first; row0 < N; row0 += row_step) {
         double acc[GEMV_R] = {0.0, 0.0};
         if (row0 != row_first) ptrs(row0, rp);
@@ -109,7 +133,8 @@ __global__ void __launch_bounds__(GEMV_THREADS, 1) gemv_kernel(const GemvParams 
             const int row = row0 + (lane >> 4);
             if (row < N) {
                 const float v = (float)tot;
-                if (p.epi == EPI_STORE_F64) reinterpret_cast<double *>(out)[row] = tot;
+                if (p.epi == EPI_PUSH_F64) tp_push_store(p, row, N, tot, push_ep);
+                else if (p.epi == EPI_STORE_F64) reinterpret_cast<double *>(out)[row] = tot;
                 else if (p.epi == EPI_ADD) out[row] = __fadd_rn(out[row], v);
                 else out[row] = v;
                 if (p.argmax_key) {
@@ -124,6 +149,7 @@ __global__ void __launch_bounds__(GEMV_THREADS, 1) gemv_kernel(const GemvParams 
         best = other > best ? other : best;
         if (lane == 0 && best) atomicMax(p.argmax_key, best);
     }
+    if (p.epi == EPI_PUSH_F64) tp_push_signal(p, push_ep);
 }
 
 // ---------------------------------------------------------------- double-buffered variant
@@ -204,6 +230,7 @@ __device__ __forceinline__ void gemv_db_body(const GemvParams &p, int seg, uint8
     float *out = p.out[seg];
     unsigned long long best = 0ull;
     const int rope_pos = p.epi == EPI_QKV_ROPE ? __ldcg(p.rope.n_past_ptr) : 0;
+    const unsigned push_ep = p.epi == EPI_PUSH_F64 ? tp_push_epoch(p) : 0u;
     int crow = row_first, cu = 0;  // compute cursor
     double acc[GEMV_R] = {0.0, 0.0};
     auto step = [&](Regs &g) {
@@ -221,7 +248,8 @@ __device__ __forceinline__ void gemv_db_body(const GemvParams &p, int seg, uint8
                 const int row = crow + (lane >> 4);
                 if (row < N) {
                     const float v = (float)tot;
-                    if (p.epi == EPI_STORE_F64) reinterpret_cast<double *>(out)[row] = tot;
+                    if (p.epi == EPI_PUSH_F64) tp_push_store(p, row, N, tot, push_ep);
+                    else if (p.epi == EPI_STORE_F64) reinterpret_cast<double *>(out)[row] = tot;
                     else if (p.epi == EPI_ADD) out[row] = __fadd_rn(out[row], v);
                     else out[row] = v;
                     if (p.argmax_key) {
@@ -252,6 +280,7 @@ __device__ __forceinline__ void gemv_db_body(const GemvParams &p, int seg, uint8
         best = other > best ? other : best;
         if (lane == 0 && best) atomicMax(p.argmax_key, best);
     }
+    if (p.epi == EPI_PUSH_F64) tp_push_signal(p, push_ep);
 }
 
 __device__ __forceinline__ int gemv_my_segment(const GemvParams &p) {

@@ -28,6 +28,21 @@ enum GemvEpilogue : int {
     // out[n] (a double array) = the row's double sum, unrounded: the partial of a K-split matrix whose other parts live on
     // other GPUs (tensor parallelism): the f64 partials are all-reduced and rounded to f32 once, like the unsplit sum
     EPI_STORE_F64 = 4,
+    // the same partial sums, pushed straight into every rank's receive slab over NVLink (plain peer stores), followed by
+    // an arrival flag from the launch's last CTA: the all-reduce's transport rides in the GEMV (TpPush; tp.cu)
+    EPI_PUSH_F64 = 5,
+};
+
+// EPI_PUSH_F64: where this rank's partials go.  An all-reduce has an epoch = *tick * per_token + index (tick: the
+// device-side count of token passes started, so that a captured launch needs no per-call arguments); slabs are double
+// buffered by the epoch's parity, flags carry the epoch of the last complete push.
+constexpr int TP_MAX_RANKS = 8;
+struct TpPush {
+    double *dst[TP_MAX_RANKS];     // rank r's slab for THIS rank's partials: [2][n_rows] doubles (r = own rank included)
+    unsigned *flag[TP_MAX_RANKS];  // rank r's arrival flag for this rank
+    unsigned *done;                // this GPU's finished-CTA counter (zero between launches)
+    const unsigned *tick;
+    int32_t n, per_token, index;
 };
 
 struct RopeKv {              // EPI_QKV_ROPE only
@@ -56,6 +71,7 @@ struct GemvParams {
     // image layout: the prologue becomes a copy and x / norm_w are not read
     const uint8_t *x_image;
     int32_t evict_first;    // stream this launch's weights with the L2 evict-first policy
+    TpPush push;            // EPI_PUSH_F64 only
 };
 
 // fills cta_begin[] and returns the grid size; n_sms from the device

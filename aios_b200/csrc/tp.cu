@@ -71,6 +71,39 @@ __global__ void add_f64_kernel(float *x, const double *part, int n) {
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < n) x[i] = __fadd_rn(x[i], (float)part[i]);
 }
+
+// ---- the push all-reduce's other half (the first half is the GEMV's EPI_PUSH_F64 epilogue, gemv.cu)
+__global__ void tp_tick_kernel(unsigned *tick) { *tick = *tick + 1u; }
+
+// wait until every rank's partials of this epoch have landed in this GPU's slabs, then x[i] += (float) sum over ranks
+// (rank order, the same on every GPU: every rank computes the same residual stream bit for bit).
+// slabs: [n][2][E] doubles; flags: one per source rank, 32 words apart.  A peer that never arrives (a failed launch on
+// another GPU) must not hang this one: after ~2 s the kernel gives up and raises *err, which the host checks.
+__global__ void tp_wait_add_kernel(float *x, const double *slabs, const unsigned *flags, const unsigned *tick, int per_token,
+                                   int index, int n, int E, unsigned *err) {
+    const unsigned ep = __ldcg(tick) * (unsigned)per_token + (unsigned)index;
+    if ((int)threadIdx.x < n) {
+        const unsigned *f = flags + threadIdx.x * 32;
+        const long long t0 = clock64();
+        for (;;) {
+            unsigned v;
+            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(f) : "memory");
+            if ((int)(v - ep) >= 0) break;
+            if (clock64() - t0 > 4000000000ll) {
+                atomicExch(err, 1u);
+                break;
+            }
+        }
+    }
+    __syncthreads();
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < E) {
+        const double *s = slabs + (size_t)(ep & 1u) * E + i;
+        double tot = __ldcg(s);
+        for (int r = 1; r < n; r++) tot += __ldcg(s + (size_t)r * 2 * E);
+        x[i] = __fadd_rn(x[i], (float)tot);
+    }
+}
 }  // namespace
 
 struct TpRank {
@@ -78,6 +111,10 @@ struct TpRank {
     std::unique_ptr<Model> model;
     std::unique_ptr<Seq> seq;
     ncclComm_t comm = nullptr;
+    // push all-reduce: this GPU's receive slabs [n][2][E] doubles, then n flags (32 words apart), done, tick, err
+    DevBuf xchg;
+    double *slabs = nullptr;
+    unsigned *flags = nullptr, *done = nullptr, *tick = nullptr, *err = nullptr;
 };
 
 struct TpModelImpl {
@@ -85,6 +122,9 @@ struct TpModelImpl {
     int n = 0;
     int n_past = 0;
     bool have_logits = false;
+    bool push = false;  // the all-reduce rides in the GEMV epilogue over peer mappings (else: ncclAllReduce)
+    void setup_push();
+    void check_push_errors();
     // all-reduce timing (rank 0's stream), filled when timing is on
     bool timing = false;
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ar_events;
@@ -93,6 +133,7 @@ struct TpModelImpl {
         for (auto &r : ranks) {
             if (r.eng) cudaSetDevice(r.eng->device);
             r.seq.reset();
+            r.xchg = DevBuf();
             r.model.reset();
             if (r.comm) nccl().CommDestroy(r.comm);
             r.eng.reset();
@@ -100,7 +141,7 @@ struct TpModelImpl {
         for (auto &e : ar_events) { cudaEventDestroy(e.first); cudaEventDestroy(e.second); }
     }
     const HParams &hp() const { return ranks[0].model->hp; }
-    void all_reduce_add_to_x();
+    void all_reduce_add_to_x(int reduce_index);
     // one token through every rank's shard in lockstep; launches counts rank 0's kernels (collectives included)
     void token_pass(bool from_prompt, int prompt_idx, int pos_value, bool want_logits, int *launches);
     void sample_all(const aios_sampling &sp);
@@ -119,7 +160,7 @@ void TpModelImpl::sync_all() {
 }
 
 // part64 of every rank: all-reduce (sum of doubles), then x += (float) sum on every rank
-void TpModelImpl::all_reduce_add_to_x() {
+void TpModelImpl::all_reduce_add_to_x(int reduce_index) {
     const int E = hp().n_embd;
     cudaEvent_t e0 = nullptr, e1 = nullptr;
     if (timing) {
@@ -128,18 +169,86 @@ void TpModelImpl::all_reduce_add_to_x() {
         CUDA_CHECK(cudaEventCreate(&e1));
         CUDA_CHECK(cudaEventRecord(e0, ranks[0].eng->stream));
     }
-    nccl_check(nccl().GroupStart(), "ncclGroupStart");
-    for (auto &r : ranks)
-        nccl_check(nccl().AllReduce(r.seq->tp_part64.p, r.seq->tp_part64.p, (size_t)E, ncclDouble, ncclSum, r.comm, r.eng->stream), "ncclAllReduce");
-    nccl_check(nccl().GroupEnd(), "ncclGroupEnd");
+    if (push) {
+        const int per_token = 2 * hp().n_layer;
+        for (auto &r : ranks) {
+            r.eng->make_current();
+            tp_wait_add_kernel<<<(E + 255) / 256, 256, 0, r.eng->stream>>>(r.seq->x.as<float>(), r.slabs, r.flags, r.tick, per_token,
+                                                                          reduce_index, n, E, r.err);
+        }
+    } else {
+        nccl_check(nccl().GroupStart(), "ncclGroupStart");
+        for (auto &r : ranks)
+            nccl_check(nccl().AllReduce(r.seq->tp_part64.p, r.seq->tp_part64.p, (size_t)E, ncclDouble, ncclSum, r.comm, r.eng->stream), "ncclAllReduce");
+        nccl_check(nccl().GroupEnd(), "ncclGroupEnd");
+    }
     if (timing) {
         ranks[0].eng->make_current();
         CUDA_CHECK(cudaEventRecord(e1, ranks[0].eng->stream));
         ar_events.emplace_back(e0, e1);
     }
+    if (!push)
+        for (auto &r : ranks) {
+            r.eng->make_current();
+            add_f64_kernel<<<(E + 255) / 256, 256, 0, r.eng->stream>>>(r.seq->x.as<float>(), r.seq->tp_part64.as<double>(), E);
+        }
+}
+
+// Peer mappings between every pair of shards, the receive slabs, and the push descriptors of every rank's sequence.
+// Without full peer access (or with AIOS_TP_ALLREDUCE=nccl) the group stays on ncclAllReduce.
+void TpModelImpl::setup_push() {
+    const char *mode = getenv("AIOS_TP_ALLREDUCE");
+    if (mode && !strcmp(mode, "nccl")) return;
+    for (int a = 0; a < n; a++)
+        for (int b = 0; b < n; b++) {
+            if (a == b) continue;
+            int can = 0;
+            CUDA_CHECK(cudaDeviceCanAccessPeer(&can, ranks[(size_t)a].eng->device, ranks[(size_t)b].eng->device));
+            if (!can) return;
+        }
+    for (int a = 0; a < n; a++) {
+        ranks[(size_t)a].eng->make_current();
+        for (int b = 0; b < n; b++) {
+            if (a == b) continue;
+            const cudaError_t e = cudaDeviceEnablePeerAccess(ranks[(size_t)b].eng->device, 0);
+            if (e == cudaErrorPeerAccessAlreadyEnabled) cudaGetLastError();
+            else CUDA_CHECK(e);
+        }
+    }
+    const int E = hp().n_embd;
+    const size_t slab_bytes = (size_t)n * 2 * E * sizeof(double);
     for (auto &r : ranks) {
         r.eng->make_current();
-        add_f64_kernel<<<(E + 255) / 256, 256, 0, r.eng->stream>>>(r.seq->x.as<float>(), r.seq->tp_part64.as<double>(), E);
+        r.xchg = DevBuf(slab_bytes + ((size_t)n * 32 + 96) * sizeof(unsigned));
+        CUDA_CHECK(cudaMemset(r.xchg.p, 0, r.xchg.bytes));
+        r.slabs = r.xchg.as<double>();
+        r.flags = reinterpret_cast<unsigned *>(r.xchg.as<uint8_t>() + slab_bytes);
+        r.done = r.flags + (size_t)n * 32;
+        r.tick = r.done + 32;
+        r.err = r.tick + 32;
+    }
+    for (int a = 0; a < n; a++) {
+        TpPush &P = ranks[(size_t)a].seq->tp_push;
+        P = TpPush{};
+        for (int b = 0; b < n; b++) {
+            P.dst[b] = ranks[(size_t)b].slabs + (size_t)a * 2 * E;  // rank b's slab for rank a's partials
+            P.flag[b] = ranks[(size_t)b].flags + (size_t)a * 32;
+        }
+        P.done = ranks[(size_t)a].done;
+        P.tick = ranks[(size_t)a].tick;
+        P.n = n;
+        P.per_token = 2 * hp().n_layer;
+    }
+    push = true;
+}
+
+void TpModelImpl::check_push_errors() {
+    if (!push) return;
+    for (auto &r : ranks) {
+        r.eng->make_current();
+        unsigned e = 0;
+        CUDA_CHECK(cudaMemcpy(&e, r.err, sizeof(e), cudaMemcpyDeviceToHost));
+        if (e) throw CudaError("tensor-parallel all-reduce: a peer's partial sums never arrived");
     }
 }
 
@@ -149,12 +258,13 @@ void TpModelImpl::token_pass(bool from_prompt, int prompt_idx, int pos_value, bo
         for (int r = 0; r < n; r++) ranks[(size_t)r].seq->build_token_pass(want_logits, lists[(size_t)r]);
         lists_logits = (int)want_logits;
     }
-    int li = 0;
+    int li = 0, n_reduce = 0;
     for (auto &r : ranks) {
         r.eng->make_current();
+        if (push) tp_tick_kernel<<<1, 1, 0, r.eng->stream>>>(r.tick);
         r.seq->launch_embed(from_prompt, prompt_idx, pos_value, r.eng->stream);
     }
-    li++;
+    li += push ? 2 : 1;
     const size_t n_items = lists[0].size();
     for (size_t i = 0; i < n_items; i++) {
         for (int r = 0; r < n; r++) {
@@ -164,8 +274,8 @@ void TpModelImpl::token_pass(bool from_prompt, int prompt_idx, int pos_value, bo
         }
         li++;
         if (lists[0][i].reduce_after) {
-            all_reduce_add_to_x();
-            li += 2;
+            all_reduce_add_to_x(n_reduce++);
+            li += push ? 1 : 2;
         }
     }
     if (want_logits) {  // every rank gets every slice of the logits (in place: rank r's slice already sits at r * vocab_local)
@@ -221,6 +331,7 @@ TpModel::TpModel(const std::vector<int> &devices, const std::string &name, const
     std::vector<ncclComm_t> comms((size_t)n);
     nccl_check(nccl().CommInitAll(comms.data(), n, devices.data()), "ncclCommInitAll");
     for (int r = 0; r < n; r++) impl->ranks[(size_t)r].comm = comms[(size_t)r];
+    impl->setup_push();
 }
 TpModel::~TpModel() = default;
 
@@ -265,6 +376,7 @@ void TpModel::prefill(const int32_t *tokens, int n) {
     }
     for (int i = 0; i < n; i++) impl->token_pass(true, i, impl->n_past + i, i == n - 1, nullptr);
     impl->sync_all();
+    impl->check_push_errors();
     impl->n_past += n;
     impl->have_logits = true;
 }
@@ -281,6 +393,7 @@ int TpModel::decode(const aios_sampling &sp, int max_tokens, int32_t *out) {
         impl->token_pass(false, 0, 0, true, nullptr);
     }
     impl->sync_all();
+    impl->check_push_errors();
     TpRank &R0 = impl->ranks[0];
     R0.eng->make_current();
     CUDA_CHECK(cudaMemcpy(out, R0.seq->out_tokens.p, (size_t)n * 4, cudaMemcpyDeviceToHost));
@@ -335,6 +448,7 @@ void TpModel::bench_decode(int n_tokens, aios_tp_bench *out) {
     out->n_tokens = n_tokens;
     out->kernel_launches = launches;
     out->n_ranks = impl->n;
+    out->allreduce_kind = impl->push ? 1 : 0;
     // pass 2 (a few tokens): an event pair around every all-reduce on rank 0's stream
     const int n_timed = std::min(8, hp.n_ctx - impl->n_past);
     if (n_timed > 0) {

@@ -352,9 +352,13 @@ int aios_bench_gemv(aios_engine *e, int32_t ggml_type, int64_t n_rows, int64_t k
 /* ---- tensor parallelism: one model split over 2..8 GPUs of this node --------------------------------------------
  * (BASELINE.json configs[4], Llama-3-70B at TP 2/4/8.  The reference's hardware table lists
  *  70B-class local models, docs/HARDWARE.md:135-138; llama-server's counterpart is --tensor-split / --split-mode row.)
- * attn_q/k/v, ffn_gate/up and the lm_head are split by rows, attn_output and ffn_down along K; per layer two NCCL
+ * attn_q/k/v, ffn_gate/up and the lm_head are split by rows, attn_output and ffn_down along K; per layer two
  * all-reduces of the projections' f64 partial sums (so the tokens are those of the unsplit model), per token one
- * all-gather of the logits.  libnccl.so.2 is opened on the first aios_tp_model_load; the library does not link to it.
+ * all-gather of the logits.  With peer access between all the devices the all-reduce rides in the GEMV: its epilogue
+ * stores the partials into every GPU's receive slab over NVLink and raises an arrival flag, and one small kernel per
+ * GPU waits for the flags and adds the sum to the residual; otherwise (or with AIOS_TP_ALLREDUCE=nccl in the
+ * environment) it is ncclAllReduce.  libnccl.so.2 is opened on the first aios_tp_model_load (communicators, the logits
+ * all-gather, the fallback); the library does not link to it.
  * One process drives all the shards; calls on one aios_tp_model must not overlap.  The model must split evenly:
  * n_head_kv, n_ff and n_vocab divisible by n_devices, and n_head*head_dim / n_devices and n_ff / n_devices
  * multiples of 256 (AIOS_E_FORMAT otherwise). */
@@ -376,6 +380,9 @@ typedef struct aios_tp_bench {
     int32_t n_past_begin, n_past_end;
     int32_t n_allreduce_per_token;
     float us_per_allreduce;         /* average, n_embd doubles each                              */
+    int32_t allreduce_kind;         /* 1: partial sums pushed to the peers from the GEMV epilogue over NVLink
+                                     *    (peer stores + arrival flags); 0: ncclAllReduce             */
+    int32_t reserved;
 } aios_tp_bench;
 int aios_tp_bench_decode(aios_tp_model *m, int32_t n_tokens, aios_tp_bench *out);
 

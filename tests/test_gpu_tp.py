@@ -19,9 +19,11 @@ def _need_gpus(n):
 
 
 @pytest.mark.parametrize("arch,ftype,n_dev", [("tiny-gqa4", "Q4_K_M", 2), ("tiny-gqa4", "Q8_0", 2), ("tiny-tp4", "Q4_K_M", 4),
-                                             ("tiny-tp4", "Q6_K", 2)])
-def test_tp_matches_oracle(oracle, tmp_models, arch, ftype, n_dev):
+                                             ("tiny-tp4", "Q8_0", 2)])
+@pytest.mark.parametrize("allreduce", ["push", "nccl"])
+def test_tp_matches_oracle(oracle, tmp_models, monkeypatch, arch, ftype, n_dev, allreduce):
     _need_gpus(n_dev)
+    monkeypatch.setenv("AIOS_TP_ALLREDUCE", allreduce)
     path = tmp_models(arch, ftype)
     prompt = gs.synthetic_prompt(arch, 24, 5)
     om = oracle.OracleModel(path, n_ctx=128)
@@ -61,6 +63,7 @@ def test_tp_stochastic_matches_single_gpu(tmp_models):
     try:
         assert np.array_equal(tp.generate(prompt, 32, sp), want)
         b = tp.bench_decode(16)
+        assert b.allreduce_kind == 1  # two GPUs of one box see each other: the fused all-reduce is the default
         assert b.n_ranks == 2 and b.n_tokens == 16 and b.n_allreduce_per_token == 2 * gs.ARCHS["tiny-gqa4"].n_layer
         assert b.us_per_allreduce > 0 and b.ms_total > 0
     finally:
