@@ -77,7 +77,7 @@ class BenchResult(C.Structure):
 class TpBench(C.Structure):
     _fields_ = [("ms_total", C.c_float), ("n_tokens", C.c_int32), ("n_ranks", C.c_int32), ("kernel_launches", C.c_int32),
                 ("n_past_begin", C.c_int32), ("n_past_end", C.c_int32), ("n_allreduce_per_token", C.c_int32),
-                ("us_per_allreduce", C.c_float), ("allreduce_kind", C.c_int32), ("reserved", C.c_int32)]
+                ("us_per_allreduce", C.c_float), ("allreduce_kind", C.c_int32), ("graphs", C.c_int32)]
 
 
 TOK_ADD_SPECIAL, TOK_PARSE_SPECIAL, TOK_RENDER_SPECIAL, TOK_STRIP_SPACE = 1, 2, 4, 8

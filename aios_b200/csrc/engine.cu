@@ -450,6 +450,10 @@ void Seq::build_token_pass(bool want_logits, std::vector<PassLaunch> &ls) {
         p.x = x.as<float>(); p.norm_w = m->output_norm.as<float>(); p.eps = hp.rms_eps;
         p.argmax_key = tp ? nullptr : &sd->argmax_key;
         add_gemv(p, false);
+        if (tp && tp_push_logits.n > 0) {
+            ls.back().g.epi = EPI_PUSH_F32;
+            ls.back().g.push = tp_push_logits;
+        }
     }
     if (tp)  // the first launch of a layer follows the all-reduce's add kernel, which is no PDL primary either
         for (size_t i = 1; i < ls.size(); i++)

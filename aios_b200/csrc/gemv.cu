@@ -36,6 +36,9 @@ __device__ __forceinline__ void tp_push_store(const GemvParams &p, int row, int 
     const size_t off = (size_t)(ep & 1u) * (size_t)n_rows + (size_t)row;
     for (int r = 0; r < p.push.n; r++) p.push.dst[r][off] = tot;
 }
+__device__ __forceinline__ void tp_push_store_f32(const GemvParams &p, int row, float v) {
+    for (int r = 0; r < p.push.n; r++) reinterpret_cast<float *>(p.push.dst[r])[row] = v;
+}
 __device__ __forceinline__ void tp_push_signal(const GemvParams &p, unsigned ep) {
     __threadfence_system();  // this thread's slab stores are visible system-wide before the CTA counts itself done
     __syncthreads();
@@ -111,7 +114,7 @@ __global__ void __launch_bounds__(GEMV_THREADS, 1) gemv_kernel(const GemvParams 
     float *out = p.out[seg];
     unsigned long long best = 0ull;
     const int rope_pos = p.epi == EPI_QKV_ROPE ? __ldcg(p.rope.n_past_ptr) : 0;
-    const unsigned push_ep = p.epi == EPI_PUSH_F64 ? tp_push_epoch(p) : 0u;
+    const unsigned push_ep = p.epi >= EPI_PUSH_F64 ? tp_push_epoch(p) : 0u;
     for (int row0 = row_first; row0 < N; row0 += row_step) {
         double acc[GEMV_R] = {0.0, 0.0};
         if (row0 != row_first) ptrs(row0, rp);
@@ -134,6 +137,7 @@ __global__ void __launch_bounds__(GEMV_THREADS, 1) gemv_kernel(const GemvParams 
             if (row < N) {
                 const float v = (float)tot;
                 if (p.epi == EPI_PUSH_F64) tp_push_store(p, row, N, tot, push_ep);
+                else if (p.epi == EPI_PUSH_F32) tp_push_store_f32(p, row, v);
                 else if (p.epi == EPI_STORE_F64) reinterpret_cast<double *>(out)[row] = tot;
                 else if (p.epi == EPI_ADD) out[row] = __fadd_rn(out[row], v);
                 else out[row] = v;
@@ -149,7 +153,7 @@ __global__ void __launch_bounds__(GEMV_THREADS, 1) gemv_kernel(const GemvParams 
         best = other > best ? other : best;
         if (lane == 0 && best) atomicMax(p.argmax_key, best);
     }
-    if (p.epi == EPI_PUSH_F64) tp_push_signal(p, push_ep);
+    if (p.epi >= EPI_PUSH_F64) tp_push_signal(p, push_ep);
 }
 
 // ---------------------------------------------------------------- double-buffered variant
@@ -230,7 +234,7 @@ __device__ __forceinline__ void gemv_db_body(const GemvParams &p, int seg, uint8
     float *out = p.out[seg];
     unsigned long long best = 0ull;
     const int rope_pos = p.epi == EPI_QKV_ROPE ? __ldcg(p.rope.n_past_ptr) : 0;
-    const unsigned push_ep = p.epi == EPI_PUSH_F64 ? tp_push_epoch(p) : 0u;
+    const unsigned push_ep = p.epi >= EPI_PUSH_F64 ? tp_push_epoch(p) : 0u;
     int crow = row_first, cu = 0;  // compute cursor
     double acc[GEMV_R] = {0.0, 0.0};
     auto step = [&](Regs &g) {
@@ -249,6 +253,7 @@ __device__ __forceinline__ void gemv_db_body(const GemvParams &p, int seg, uint8
                 if (row < N) {
                     const float v = (float)tot;
                     if (p.epi == EPI_PUSH_F64) tp_push_store(p, row, N, tot, push_ep);
+                    else if (p.epi == EPI_PUSH_F32) tp_push_store_f32(p, row, v);
                     else if (p.epi == EPI_STORE_F64) reinterpret_cast<double *>(out)[row] = tot;
                     else if (p.epi == EPI_ADD) out[row] = __fadd_rn(out[row], v);
                     else out[row] = v;
@@ -280,7 +285,7 @@ __device__ __forceinline__ void gemv_db_body(const GemvParams &p, int seg, uint8
         best = other > best ? other : best;
         if (lane == 0 && best) atomicMax(p.argmax_key, best);
     }
-    if (p.epi == EPI_PUSH_F64) tp_push_signal(p, push_ep);
+    if (p.epi >= EPI_PUSH_F64) tp_push_signal(p, push_ep);
 }
 
 __device__ __forceinline__ int gemv_my_segment(const GemvParams &p) {

@@ -31,6 +31,9 @@ enum GemvEpilogue : int {
     // the same partial sums, pushed straight into every rank's receive slab over NVLink (plain peer stores), followed by
     // an arrival flag from the launch's last CTA: the all-reduce's transport rides in the GEMV (TpPush; tp.cu)
     EPI_PUSH_F64 = 5,
+    // out[n] = dot on every rank: this rank's slice of the logits stored into every rank's logits buffer (push.dst as
+    // float pointers, already offset to this rank's slice; no double buffering: see tp.cu), then the arrival flag
+    EPI_PUSH_F32 = 6,
 };
 
 // EPI_PUSH_F64: where this rank's partials go.  An all-reduce has an epoch = *tick * per_token + index (tick: the

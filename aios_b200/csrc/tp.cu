@@ -104,6 +104,24 @@ __global__ void tp_wait_add_kernel(float *x, const double *slabs, const unsigned
         x[i] = __fadd_rn(x[i], (float)tot);
     }
 }
+
+// every rank's slice of this token's logits has landed in this GPU's logits buffer (EPI_PUSH_F32): one CTA, n waiters
+__global__ void tp_wait_logits_kernel(const unsigned *flags, const unsigned *tick, int n, unsigned *err) {
+    const unsigned ep = __ldcg(tick);
+    if ((int)threadIdx.x < n) {
+        const unsigned *f = flags + threadIdx.x * 32;
+        const long long t0 = clock64();
+        for (;;) {
+            unsigned v;
+            asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(f) : "memory");
+            if ((int)(v - ep) >= 0) break;
+            if (clock64() - t0 > 4000000000ll) {
+                atomicExch(err, 1u);
+                break;
+            }
+        }
+    }
+}
 }  // namespace
 
 struct TpRank {
@@ -114,7 +132,8 @@ struct TpRank {
     // push all-reduce: this GPU's receive slabs [n][2][E] doubles, then n flags (32 words apart), done, tick, err
     DevBuf xchg;
     double *slabs = nullptr;
-    unsigned *flags = nullptr, *done = nullptr, *tick = nullptr, *err = nullptr;
+    unsigned *flags = nullptr, *lflags = nullptr, *done = nullptr, *tick = nullptr, *err = nullptr;
+    cudaGraphExec_t graph = nullptr;  // one decode step: sample, tick, embed, the layers, lm_head, logits wait
 };
 
 struct TpModelImpl {
@@ -125,6 +144,14 @@ struct TpModelImpl {
     bool push = false;  // the all-reduce rides in the GEMV epilogue over peer mappings (else: ncclAllReduce)
     void setup_push();
     void check_push_errors();
+    // push mode: one CUDA graph per rank holds a whole decode step (no host-side collective call is left in it)
+    bool use_graphs = false;
+    bool graphs_built = false;
+    aios_sampling graph_sp{};
+    int graph_launches = 0;  // kernels inside one rank's graph
+    void rank_step(int r, const aios_sampling &sp, int *launches);
+    void ensure_graphs(const aios_sampling &sp);
+    void decode_steps(const aios_sampling &sp, int n_steps, int *launches);
     // all-reduce timing (rank 0's stream), filled when timing is on
     bool timing = false;
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> ar_events;
@@ -132,6 +159,7 @@ struct TpModelImpl {
     ~TpModelImpl() {
         for (auto &r : ranks) {
             if (r.eng) cudaSetDevice(r.eng->device);
+            if (r.graph) cudaGraphExecDestroy(r.graph);
             r.seq.reset();
             r.xchg = DevBuf();
             r.model.reset();
@@ -219,11 +247,12 @@ void TpModelImpl::setup_push() {
     const size_t slab_bytes = (size_t)n * 2 * E * sizeof(double);
     for (auto &r : ranks) {
         r.eng->make_current();
-        r.xchg = DevBuf(slab_bytes + ((size_t)n * 32 + 96) * sizeof(unsigned));
+        r.xchg = DevBuf(slab_bytes + ((size_t)n * 64 + 96) * sizeof(unsigned));
         CUDA_CHECK(cudaMemset(r.xchg.p, 0, r.xchg.bytes));
         r.slabs = r.xchg.as<double>();
         r.flags = reinterpret_cast<unsigned *>(r.xchg.as<uint8_t>() + slab_bytes);
-        r.done = r.flags + (size_t)n * 32;
+        r.lflags = r.flags + (size_t)n * 32;
+        r.done = r.lflags + (size_t)n * 32;
         r.tick = r.done + 32;
         r.err = r.tick + 32;
     }
@@ -238,8 +267,24 @@ void TpModelImpl::setup_push() {
         P.tick = ranks[(size_t)a].tick;
         P.n = n;
         P.per_token = 2 * hp().n_layer;
+        // the lm_head's slice of the logits: straight into every rank's logits buffer.  No double buffering needed: a
+        // rank samples from its logits before its next token pass, and nobody reaches the next lm_head without that
+        // rank's contributions to the token's all-reduces.
+        TpPush &L = ranks[(size_t)a].seq->tp_push_logits;
+        L = TpPush{};
+        const size_t vl = (size_t)ranks[0].model->vocab_local;
+        for (int b = 0; b < n; b++) {
+            L.dst[b] = reinterpret_cast<double *>(ranks[(size_t)b].seq->logits.as<float>() + (size_t)a * vl);
+            L.flag[b] = ranks[(size_t)b].lflags + (size_t)a * 32;
+        }
+        L.done = ranks[(size_t)a].done;
+        L.tick = ranks[(size_t)a].tick;
+        L.n = n;
+        L.per_token = 1;
+        L.index = 0;
     }
     push = true;
+    use_graphs = !(ranks[0].eng->flags & AIOS_ENGINE_NO_GRAPH);
 }
 
 void TpModelImpl::check_push_errors() {
@@ -278,7 +323,13 @@ void TpModelImpl::token_pass(bool from_prompt, int prompt_idx, int pos_value, bo
             li += push ? 1 : 2;
         }
     }
-    if (want_logits) {  // every rank gets every slice of the logits (in place: rank r's slice already sits at r * vocab_local)
+    if (want_logits && push) {
+        for (auto &R : ranks) {
+            R.eng->make_current();
+            tp_wait_logits_kernel<<<1, 32, 0, R.eng->stream>>>(R.lflags, R.tick, n, R.err);
+        }
+        li++;
+    } else if (want_logits) {  // every rank gets every slice of the logits (in place: rank r's slice already sits at r * vocab_local)
         const size_t vl = (size_t)ranks[0].model->vocab_local;
         nccl_check(nccl().GroupStart(), "ncclGroupStart");
         for (int r = 0; r < n; r++) {
@@ -298,6 +349,78 @@ void TpModelImpl::set_pos_step() {
     for (auto &r : ranks) {
         r.eng->make_current();
         CUDA_CHECK(cudaMemcpyAsync(r.seq->state.p, hdr, sizeof(hdr), cudaMemcpyHostToDevice, r.eng->stream));
+    }
+}
+
+// one decode step of ONE rank, in stream order (push mode only: the ranks meet through flags, not through the host)
+void TpModelImpl::rank_step(int r, const aios_sampling &sp, int *launches) {
+    TpRank &R = ranks[(size_t)r];
+    R.eng->make_current();
+    cudaStream_t st = R.eng->stream;
+    const int E = hp().n_embd, per_token = 2 * hp().n_layer;
+    int li = 0, n_reduce = 0;
+    R.seq->launch_sample_kernel(sp, st);
+    tp_tick_kernel<<<1, 1, 0, st>>>(R.tick);
+    R.seq->launch_embed(false, 0, 0, st);
+    li += 3;
+    for (PassLaunch &L : lists[(size_t)r]) {
+        R.seq->launch_pass_item(L, st, li++);
+        if (L.reduce_after) {
+            tp_wait_add_kernel<<<(E + 255) / 256, 256, 0, st>>>(R.seq->x.as<float>(), R.slabs, R.flags, R.tick, per_token, n_reduce++, n, E, R.err);
+            li++;
+        }
+    }
+    tp_wait_logits_kernel<<<1, 32, 0, st>>>(R.lflags, R.tick, n, R.err);
+    li++;
+    if (launches) *launches = li;
+}
+
+void TpModelImpl::ensure_graphs(const aios_sampling &sp) {
+    if (graphs_built && !memcmp(&sp, &graph_sp, sizeof(sp))) return;
+    if (lists_logits != 1) {
+        lists.resize((size_t)n);
+        for (int r = 0; r < n; r++) ranks[(size_t)r].seq->build_token_pass(true, lists[(size_t)r]);
+        lists_logits = 1;
+    }
+    sync_all();
+    for (int r = 0; r < n; r++) {
+        TpRank &R = ranks[(size_t)r];
+        R.eng->make_current();
+        if (R.graph) { cudaGraphExecDestroy(R.graph); R.graph = nullptr; }
+        cudaGraph_t g = nullptr;
+        CUDA_CHECK(cudaStreamBeginCapture(R.eng->stream, cudaStreamCaptureModeThreadLocal));
+        try {
+            rank_step(r, sp, &graph_launches);
+        } catch (...) {
+            cudaStreamEndCapture(R.eng->stream, &g);
+            if (g) cudaGraphDestroy(g);
+            throw;
+        }
+        CUDA_CHECK(cudaStreamEndCapture(R.eng->stream, &g));
+        const cudaError_t e = cudaGraphInstantiate(&R.graph, g, 0);
+        cudaGraphDestroy(g);
+        CUDA_CHECK(e);
+    }
+    graph_sp = sp;
+    graphs_built = true;
+}
+
+// n_steps x (sample the next token from the logits, feed it); asynchronous
+void TpModelImpl::decode_steps(const aios_sampling &sp, int n_steps, int *launches) {
+    if (use_graphs && !timing) {
+        ensure_graphs(sp);
+        for (int i = 0; i < n_steps; i++)
+            for (auto &R : ranks) {
+                R.eng->make_current();
+                CUDA_CHECK(cudaGraphLaunch(R.graph, R.eng->stream));
+            }
+        if (launches) *launches += n_steps * graph_launches;
+        return;
+    }
+    for (int i = 0; i < n_steps; i++) {
+        sample_all(sp);
+        if (launches) (*launches)++;
+        token_pass(false, 0, 0, true, launches);
     }
 }
 
@@ -388,10 +511,7 @@ int TpModel::decode(const aios_sampling &sp, int max_tokens, int32_t *out) {
     const int n = std::min(max_tokens, room);
     if (n <= 0) return 0;
     impl->set_pos_step();
-    for (int i = 0; i < n; i++) {
-        impl->sample_all(sp);  // token -> state.cur_token, pos++, out_tokens[step++]
-        impl->token_pass(false, 0, 0, true, nullptr);
-    }
+    impl->decode_steps(sp, n, nullptr);  // per step: token -> state.cur_token, pos++, out_tokens[step++], then the pass
     impl->sync_all();
     impl->check_push_errors();
     TpRank &R0 = impl->ranks[0];
@@ -417,10 +537,7 @@ void TpModel::bench_decode(int n_tokens, aios_tp_bench *out) {
     aios_sampling greedy{};
     greedy.temperature = 0.f;
     impl->set_pos_step();
-    for (int i = 0; i < 2; i++) {  // warm-up
-        impl->sample_all(greedy);
-        impl->token_pass(false, 0, 0, true, nullptr);
-    }
+    impl->decode_steps(greedy, 2, nullptr);  // warm-up (captures the graphs)
     impl->sync_all();
     impl->n_past += 2;
     out->n_past_begin = impl->n_past;
@@ -434,11 +551,7 @@ void TpModel::bench_decode(int n_tokens, aios_tp_bench *out) {
     impl->sync_all();
     R0.eng->make_current();
     CUDA_CHECK(cudaEventRecord(a, R0.eng->stream));
-    for (int i = 0; i < n_tokens; i++) {
-        impl->sample_all(greedy);
-        launches++;
-        impl->token_pass(false, 0, 0, true, &launches);
-    }
+    impl->decode_steps(greedy, n_tokens, &launches);
     R0.eng->make_current();
     CUDA_CHECK(cudaEventRecord(b, R0.eng->stream));
     impl->sync_all();
@@ -449,14 +562,12 @@ void TpModel::bench_decode(int n_tokens, aios_tp_bench *out) {
     out->kernel_launches = launches;
     out->n_ranks = impl->n;
     out->allreduce_kind = impl->push ? 1 : 0;
+    out->graphs = impl->use_graphs ? 1 : 0;
     // pass 2 (a few tokens): an event pair around every all-reduce on rank 0's stream
     const int n_timed = std::min(8, hp.n_ctx - impl->n_past);
     if (n_timed > 0) {
-        impl->timing = true;
-        for (int i = 0; i < n_timed; i++) {
-            impl->sample_all(greedy);
-            impl->token_pass(false, 0, 0, true, nullptr);
-        }
+        impl->timing = true;  // launched kernel by kernel
+        impl->decode_steps(greedy, n_timed, nullptr);
         impl->sync_all();
         impl->timing = false;
         impl->n_past += n_timed;

@@ -382,7 +382,7 @@ typedef struct aios_tp_bench {
     float us_per_allreduce;         /* average, n_embd doubles each                              */
     int32_t allreduce_kind;         /* 1: partial sums pushed to the peers from the GEMV epilogue over NVLink
                                      *    (peer stores + arrival flags); 0: ncclAllReduce             */
-    int32_t reserved;
+    int32_t graphs;                 /* 1: each rank replays one CUDA graph per token (push mode)   */
 } aios_tp_bench;
 int aios_tp_bench_decode(aios_tp_model *m, int32_t n_tokens, aios_tp_bench *out);
 

@@ -44,7 +44,7 @@ tp.prefill(gs.synthetic_prompt(arch, ctx // 2, 11))
 r = tp.bench_decode(n_tokens)
 rec = {"arch": arch, "ftype": ftype, "tp": n_gpus, "ctx": ctx, "n_tokens": r.n_tokens, "ms_per_token": r.ms_total / r.n_tokens,
        "tok_per_s": 1e3 * r.n_tokens / r.ms_total, "launches_per_token": r.kernel_launches / r.n_tokens,
-       "allreduce": "push" if r.allreduce_kind else "nccl", "allreduce_per_token": r.n_allreduce_per_token, "us_per_allreduce": r.us_per_allreduce,
+       "allreduce": "push" if r.allreduce_kind else "nccl", "graphs": bool(r.graphs), "allreduce_per_token": r.n_allreduce_per_token, "us_per_allreduce": r.us_per_allreduce,
        "allreduce_share": r.n_allreduce_per_token * r.us_per_allreduce * 1e-3 / (r.ms_total / r.n_tokens),
        "n_past": [r.n_past_begin, r.n_past_end], "weight_gb_per_rank": tp.info.weight_bytes / 1e9,
        "repeatable": bool(np.array_equal(first, again)), "write_s": round(t_write, 1), "load_s": round(t_load, 1)}

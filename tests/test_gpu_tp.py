@@ -20,16 +20,17 @@ def _need_gpus(n):
 
 @pytest.mark.parametrize("arch,ftype,n_dev", [("tiny-gqa4", "Q4_K_M", 2), ("tiny-gqa4", "Q8_0", 2), ("tiny-tp4", "Q4_K_M", 4),
                                              ("tiny-tp4", "Q8_0", 2)])
-@pytest.mark.parametrize("allreduce", ["push", "nccl"])
+@pytest.mark.parametrize("allreduce", ["push", "push-eager", "nccl"])
 def test_tp_matches_oracle(oracle, tmp_models, monkeypatch, arch, ftype, n_dev, allreduce):
     _need_gpus(n_dev)
-    monkeypatch.setenv("AIOS_TP_ALLREDUCE", allreduce)
+    monkeypatch.setenv("AIOS_TP_ALLREDUCE", allreduce.split("-")[0])
+    flags = capi.ENGINE_NO_GRAPH if allreduce.endswith("eager") else 0
     path = tmp_models(arch, ftype)
     prompt = gs.synthetic_prompt(arch, 24, 5)
     om = oracle.OracleModel(path, n_ctx=128)
     ref_logits = om.eval(prompt)
     ref, _ = om.greedy(prompt, 24)
-    tp = capi.TpModel(list(range(n_dev)), "tp", path, n_ctx=128)
+    tp = capi.TpModel(list(range(n_dev)), "tp", path, n_ctx=128, flags=flags)
     try:
         assert tp.info.n_head == gs.ARCHS[arch].n_head and tp.info.n_ff == gs.ARCHS[arch].n_ff
         tp.reset()
