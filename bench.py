@@ -362,6 +362,97 @@ def in_graph_breakdown(seq, n_runs: int = 4):
     return out
 
 
+def run_tp(args):
+    """BASELINE.json configs[4]: one model split over --tp GPUs of this node (one process drives every shard).
+
+    value = device-timed greedy decode tok/s from position prompt to prompt + gen; e2e = the same tokens through
+    aios_tp_prefill (last prompt token from host memory) + aios_tp_decode (tokens back to a host buffer).  The first
+    greedy tokens are printed (`first_tokens`) so that runs at different TP degrees — and the single-GPU engine, where
+    the model fits — can be compared: the split does not change the tokens (f64 partial sums, rounded once)."""
+    import hashlib
+    import shutil
+
+    from aios_b200 import capi
+
+    n = args.tp
+    arch, ftype = args.tp_arch, args.ftype
+    a = gs.ARCHS[arch]
+    path = model_path(arch, ftype)
+    if not os.path.exists(path):
+        approx = (a.n_layer * (2 * a.n_embd * a.n_head * a.head_dim + 2 * a.n_embd * a.n_head_kv * a.head_dim + 3 * a.n_embd * a.n_ff)
+                  + 2 * a.n_vocab * a.n_embd) * 0.6
+        free = shutil.disk_usage(os.path.dirname(path)).free
+        if free < approx * 1.15:
+            print(json.dumps({"metric": f"{arch} {ftype} decode tok/s (bs1, TP-{n})", "unavailable":
+                              f"the synthetic GGUF needs ~{approx / 1e9:.0f} GB, {free / 1e9:.0f} GB free"}), flush=True)
+            return
+    path = ensure_model(arch, ftype, True)
+    n_ctx = args.prompt + args.gen + 16  # bench_decode: 2 untimed tokens, the timed window, 8 tokens with per-all-reduce events
+    t0 = time.perf_counter()
+    tp = capi.TpModel(list(range(n)), "bench-tp", path, n_ctx=n_ctx)
+    load_s = time.perf_counter() - t0
+    info = tp.info
+    prompt = gs.synthetic_prompt(arch, args.prompt, SEED)
+    first = tp.generate(prompt[:32], 16)
+    again = tp.generate(prompt[:32], 16)
+    for _ in range(max(args.warmup, 3)):
+        tp.reset()
+        tp.prefill(prompt[:8])
+        tp.bench_decode(8)
+    peak, peak_src = measured_peaks()
+    sampler = ClockSampler(0)
+    sampler.start()
+    dev_ms, launches, tokens, ar_us = 0.0, 0, 0, []
+    kind = graphs = None
+    for _ in range(args.steps):
+        tp.reset()
+        tp.prefill(prompt)  # untimed; token by token through the decode pass (no tensor-parallel prefill GEMM yet)
+        r = tp.bench_decode(args.gen)
+        dev_ms += r.ms_total
+        launches += r.kernel_launches
+        tokens += r.n_tokens
+        ar_us.append(r.us_per_allreduce)
+        kind, graphs = r.allreduce_kind, r.graphs
+    clocks = sampler.stop()
+    last_tok = np.ascontiguousarray(prompt[-1:], dtype=np.int32)
+    e2e_tokens, e2e_ms = 0, 0.0
+    for _ in range(args.steps):
+        tp.reset()
+        tp.prefill(prompt[:-1])
+        t0 = time.perf_counter()
+        tp.prefill(last_tok)
+        e2e_tokens += tp.decode(args.gen).size
+        e2e_ms += (time.perf_counter() - t0) * 1e3
+    value = tokens / (dev_ms * 1e-3)
+    ms_token = dev_ms / tokens
+    rank_bytes = info.weight_bytes_per_token  # one shard's algorithmic weight bytes per token
+    line = {
+        "metric": f"{arch} {ftype} decode tok/s (bs1, TP-{n})", "value": value, "unit": "tok/s", "n_gpus": n, "steps": args.steps,
+        "warmup": max(args.warmup, 3), "ms_per_step": dev_ms / args.steps, "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "int8 x q4/q5/q6 integer dots, f32 terms summed in f64 across ranks", "data": "synthetic",
+        "config": {"workload": f"{arch} {ftype} batch-1 greedy decode split {n} ways (BASELINE.json configs[4]), "
+                               f"{args.gen} tokens per step from position {args.prompt + 2}", "parallelism": f"tp{n}, one process",
+                   "l2": f"inputs larger than L2 ({rank_bytes / 1e9:.1f} GB of weights per rank per token)",
+                   "allreduce": "partial sums pushed from the GEMV epilogue over NVLink peer mappings + arrival flags"
+                                if kind else "ncclAllReduce (f64) per projection",
+                   "cuda_graph_per_rank": bool(graphs), "allreduces_per_token": 2 * info.n_layer,
+                   "us_per_allreduce": float(np.mean(ar_us)), "load_s": round(load_s, 1), "seed": SEED},
+        "roofline": {"bound": "hbm", "achieved": rank_bytes / (ms_token * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
+                     "frac": rank_bytes / (ms_token * 1e-3) / 1e9 / peak, "traffic": None, "peak_source": peak_src,
+                     "method": "one rank's algorithmic weight bytes per token / device time per token (every rank streams "
+                               "its shard concurrently; attention, all-reduce waits and the sampler are inside)",
+                     "algorithmic_bytes_per_token_per_rank": rank_bytes},
+        "e2e": {"value": e2e_tokens / (e2e_ms * 1e-3), "unit": "tok/s", "h2d_bytes_per_step": 4, "d2h_bytes_per_step": 4 * args.gen,
+                "api": "aios_tp_prefill(last prompt token, host memory) + aios_tp_decode(gen tokens to a host buffer)"},
+        "gpu_launches": launches, "clocks": clocks, "repeatable": bool(np.array_equal(first, again)),
+        "first_tokens": [int(t) for t in first], "first_tokens_sha1": hashlib.sha1(first.tobytes()).hexdigest()[:12],
+    }
+    print(json.dumps(line), flush=True)
+    tp.unload()
+    if not args.keep_model and os.path.getsize(path) > 8e9:
+        os.remove(path)
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -376,7 +467,13 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the oracle run (parity gate + cpu_baseline)")
     ap.add_argument("--parity-tokens", type=int, default=16)
     ap.add_argument("--no-subrecords", action="store_true", help="headline measurement only (no config3 / config4 sub-records)")
+    ap.add_argument("--tp", type=int, default=0, help="tensor-parallel decode of --tp-arch over this many GPUs (one process)")
+    ap.add_argument("--tp-arch", default="llama3-70b")
+    ap.add_argument("--keep-model", action="store_true", help="leave the large synthetic GGUF in place for the next run")
     args = ap.parse_args()
+    if args.tp:
+        run_tp(args)
+        return
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
