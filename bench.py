@@ -372,6 +372,8 @@ def run_tp(args):
     import hashlib
     import shutil
 
+    os.environ["NCCL_DEBUG"] = "WARN"  # NCCL's version banner goes to stdout, where the JSON line belongs
+
     from aios_b200 import capi
 
     n = args.tp
