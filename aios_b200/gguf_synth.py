@@ -193,12 +193,15 @@ class SynthInfo:
 
 def write_synthetic_gguf(path: str, arch: Arch | str, ftype: str = "Q4_K_M", seed: int = 0xA105,
                          w_std: float = 0.02, with_vocab: bool = True, vocab: list | None = None,
-                         chat_template: str | None = None, tokenizer_model: str = "llama") -> SynthInfo:
+                         chat_template: str | None = None, tokenizer_model: str = "llama", tied: bool = False) -> SynthInfo:
     """``vocab`` = [(piece, score, token_type)] replaces the generated placeholder vocabulary (padded with unused
-    entries up to ``arch.n_vocab``); ``chat_template`` is stored as ``tokenizer.chat_template``."""
+    entries up to ``arch.n_vocab``); ``chat_template`` is stored as ``tokenizer.chat_template``; ``tied`` leaves
+    ``output.weight`` out (the lm_head is then ``token_embd.weight``, as in files with tied embeddings)."""
     if isinstance(arch, str):
         arch = ARCHS[arch]
     plan = tensor_plan(arch, ftype)
+    if tied:
+        plan = [t for t in plan if t[0] != "output.weight"]
     kvs = [
         _kv("general.architecture", _STR, "llama"),
         _kv("general.name", _STR, f"synthetic-{arch.name}-{ftype}-seed{seed}"),

@@ -85,37 +85,78 @@ class LoadedModel:
         self.n_ctx = self.model.info.n_ctx
         self.seq = self.model.new_seq()  # for direct (non-queued) use: tests, prompt caching
         self.lock = threading.Lock()
+        self._live: set = set()  # queued / running requests that have not been freed yet
+        self._mu = threading.Lock()
+        self.closing = False
 
     def submit(self, tokens, max_tokens: int, sampling, json_mode: bool = False):
         """Queue a generation on the engine's scheduler; stops at the first end-of-generation token.  json_mode: the
         request carries a JSON-object grammar whose per-step mask the on-device sampler applies."""
-        if not json_mode:
-            return self.model.submit(tokens, max_tokens, sampling, stop_at_eog=True)
-        from ..capi import JsonGrammar
-        g = JsonGrammar(self.vocab)
-        try:
-            req = self.model.submit(tokens, max_tokens, sampling, json_grammar=g)
-        except Exception:
-            g.free()
-            raise
-        return _GrammarRequest(req, g)
+        with self._mu:
+            if self.closing:
+                raise RuntimeError(f"model '{self.name}' is unloading")
+            g = None
+            if json_mode:
+                from ..capi import JsonGrammar
+                g = JsonGrammar(self.vocab)
+            try:
+                if g is None:
+                    req = self.model.submit(tokens, max_tokens, sampling, stop_at_eog=True)
+                else:
+                    req = self.model.submit(tokens, max_tokens, sampling, json_grammar=g)
+            except Exception:
+                if g is not None:
+                    g.free()
+                raise
+            live = _LiveRequest(req, g, self)
+            self._live.add(live)
+            return live
 
-    def close(self):
+    def close(self, drain_timeout_s: float = 10.0):
+        """Unload.  A request that is still queued or running is cancelled first and the unload waits until the
+        engine's scheduler has retired it (the reference's unload SIGTERMs the child and waits 10 s,
+        model_manager.rs:285-345): an UnloadModel that races an Infer must free the model, not leave it in HBM."""
+        from ..capi import AiosError, E_STATE
+        with self._mu:
+            self.closing = True
+            live = list(self._live)
+        for r in live:
+            try:
+                r.cancel()
+            except Exception:
+                pass
+        deadline = time.monotonic() + drain_timeout_s
         with self.lock:
-            self.seq.free()
-            self.model.unload()
+            if self.seq is not None:
+                self.seq.free()
+                self.seq = None
+            while True:
+                try:
+                    self.model.unload()
+                    return
+                except AiosError as e:
+                    if e.code != E_STATE or time.monotonic() >= deadline:
+                        with self._mu:
+                            self.closing = False  # still loaded: the caller may retry the unload
+                        raise
+                    time.sleep(0.005)
 
 
-class _GrammarRequest:
-    """A queued JSON-mode request: frees its grammar with the request."""
+class _LiveRequest:
+    """A queued request as the runtime holds it: known to its model until freed (so that an unload can cancel it), and
+    freeing its JSON grammar, if it has one, with it."""
 
-    def __init__(self, req, grammar):
-        self._req, self._g = req, grammar
+    def __init__(self, req, grammar, owner):
+        self._req, self._g, self._owner = req, grammar, owner
 
     def __getattr__(self, name):
         return getattr(self._req, name)
 
     def free(self):
+        owner, self._owner = self._owner, None
+        if owner is not None:
+            with owner._mu:
+                owner._live.discard(self)
         self._req.free()
         if self._g is not None:
             self._g.free()

@@ -63,6 +63,7 @@ class ManagedModel:
     gpu_layers: int = 0
     threads: int = DEFAULT_THREADS
     handle: Any = None
+    restarts: int = 0  # consecutive automatic restarts that have not yet produced a healthy model
     http: Any = None  # the model's OpenAI-compatible endpoint on `port`, when the manager was given an http_factory
     loaded_evt: threading.Event = field(default_factory=threading.Event, repr=False)
 
@@ -101,8 +102,23 @@ def model_to_status(m: ManagedModel) -> ModelStatusRecord:
     return ModelStatusRecord(m.name, str(m.status), int(m.port), m.loaded_at, m.last_used, m.request_count)
 
 
+MAX_RESTARTS = 3  # consecutive failed restarts after which a model is left in its error state
+
+
 class ModelManager:
-    def __init__(self, backend: Backend, model_dir: Optional[str] = None, http_factory=None):
+    def __init__(self, backend: Backend, model_dir: Optional[str] = None, http_factory=None,
+                 idle_unload_minutes: Optional[float] = None, idle_exempt: tuple = ("tinyllama",),
+                 auto_restart: bool = True):
+        # idle_unload_minutes: config/default-config.toml:26 (`idle_unload_minutes = 5`) and
+        # docs/phases/04-AI-RUNTIME.md:208 ("unload tactical models after idle timeout"); None reads
+        # AIOS_IDLE_UNLOAD_MINUTES, 0 = never.  Models whose lower-cased name contains one of `idle_exempt` stay (the
+        # operational model must always be there, 04-AI-RUNTIME.md:206).  auto_restart: 04-AI-RUNTIME.md:210 /
+        # model_manager.rs:391-392 ("Automatic restart can be added later"): a model whose handle died is reloaded.
+        if idle_unload_minutes is None:
+            idle_unload_minutes = float(os.environ.get("AIOS_IDLE_UNLOAD_MINUTES", "0") or 0)
+        self.idle_unload_ms = int(idle_unload_minutes * 60_000)
+        self.idle_exempt = tuple(s.lower() for s in idle_exempt)
+        self.auto_restart = auto_restart
         # http_factory(name, handle, port) -> object with .close(): serves the loaded model on its port the way the
         # llama-server child did; None = the port stays a pseudo-port
         self.http_factory = http_factory
@@ -173,19 +189,31 @@ class ModelManager:
 
     # ------------------------------------------------------------------ unload (model_manager.rs:285-345)
     def unload_model(self, name: str) -> None:
+        """The reference kills the child, which always frees the model.  Here the backend cancels and drains what is
+        in flight before it unloads; if that fails the entry stays, in its error state and with its handle, so that
+        the unload can be retried (nothing is left unreachable in HBM)."""
         with self.lock:
             model = self.models.get(name)
             if model is None:
                 raise KeyError(f"Model '{name}' not found")
             model.status = ModelState(ModelState.UNLOADING)
-            handle, model.handle = model.handle, None
+            handle = model.handle
             http, model.http = model.http, None
-            del self.models[name]
         log.info("Unloading model %s", name)
-        if http is not None:
-            http.close()
-        if handle is not None:
-            self.backend.unload(handle)
+        try:
+            if http is not None:
+                http.close()
+            if handle is not None:
+                self.backend.unload(handle)
+        except Exception as e:
+            with self.lock:
+                model.status = ModelState(ModelState.ERROR, f"unload failed: {e}")
+            log.error("Model %s failed to unload: %s", name, e)
+            raise
+        with self.lock:
+            model.handle = None
+            if self.models.get(name) is model:
+                del self.models[name]
         log.info("Model %s unloaded", name)
 
     # ------------------------------------------------------------------ list / get (model_manager.rs:352-376)
@@ -218,7 +246,11 @@ class ModelManager:
     # ------------------------------------------------------------------ health (model_manager.rs:393-447)
     def health_check_all(self) -> None:
         """Reference: child liveness + GET /health per model, flipping Ready <-> Error.  Here: ask the backend
-        whether the handle is still usable (a sticky CUDA error is the in-process version of a dead child)."""
+        whether the handle is still usable (a sticky CUDA error is the in-process version of a dead child).  On top of
+        the reference, the two behaviours its phase document promises for this loop (04-AI-RUNTIME.md:246-250):
+        a dead model is restarted, and a model idle for longer than the timeout is unloaded."""
+        restart, idle = [], []
+        now = now_epoch_ms()
         with self.lock:
             for m in self.models.values():
                 if m.status.kind in (ModelState.LOADING, ModelState.UNLOADING) or m.handle is None:
@@ -232,9 +264,63 @@ class ModelManager:
                 if ok and m.status.kind == ModelState.ERROR:
                     log.info("Model %s recovered", m.name)
                     m.status = ModelState(ModelState.READY)
+                    m.restarts = 0
                 elif not ok and m.status.kind != ModelState.ERROR:
                     log.warning("Model %s health check failed: %s", m.name, why)
                     m.status = ModelState(ModelState.ERROR, why)
+                if not ok and self.auto_restart and m.restarts < MAX_RESTARTS:
+                    restart.append(m)
+                elif ok and m.status.ready and self.idle_unload_ms > 0 and now - m.last_used >= self.idle_unload_ms \
+                        and not any(x in m.name.lower() for x in self.idle_exempt) and not self._busy(m.handle):
+                    idle.append(m.name)
+        for m in restart:
+            self._restart(m)
+        for name in idle:
+            log.info("Model %s idle for %d min: unloading", name, self.idle_unload_ms // 60_000)
+            try:
+                self.unload_model(name)
+            except Exception as e:  # stays in the table in its error state
+                log.warning("idle unload of %s failed: %s", name, e)
+
+    @staticmethod
+    def _busy(handle) -> bool:
+        load = getattr(handle, "load", None)
+        try:
+            return bool(load and sum(load().values()) > 0)
+        except Exception:
+            return False
+
+    def _restart(self, m: ManagedModel) -> None:
+        """Crash recovery: drop what is left of the dead handle and load the same file again on the same port."""
+        m.restarts += 1
+        log.warning("Restarting model %s (attempt %d of %d)", m.name, m.restarts, MAX_RESTARTS)
+        with self.lock:
+            if self.models.get(m.name) is not m:
+                return
+            old, m.handle = m.handle, None
+            m.status = ModelState(ModelState.LOADING)
+        try:
+            self.backend.unload(old)
+        except Exception as e:
+            log.warning("could not release the dead handle of %s: %s", m.name, e)
+        try:
+            handle = self.backend.load(m.name, m.path, m.context_length)
+        except Exception as e:
+            with self.lock:
+                m.status = ModelState(ModelState.ERROR, f"restart failed: {e}")
+            log.error("Model %s failed to restart: %s", m.name, e)
+            return
+        with self.lock:
+            if self.models.get(m.name) is not m or m.status.kind == ModelState.UNLOADING:
+                self.backend.unload(handle)
+                return
+            m.handle = handle
+            if m.http is not None and hasattr(m.http, "handle"):
+                m.http.handle = handle  # the model's HTTP endpoint keeps its port and serves the new handle
+            m.status = ModelState(ModelState.READY)
+            m.loaded_at = now_epoch_ms()
+            m.restarts = 0
+        log.info("Model %s restarted", m.name)
 
     # ------------------------------------------------------------------ level routing (model_manager.rs:462-518)
     LEVELS = {

@@ -215,13 +215,14 @@ class RuntimeServer:
 
     def __init__(self, backend, addr: str = LISTEN_ADDR, model_dir: Optional[str] = None, max_workers: int = 16,
                  health_interval_s: float = HEALTH_CHECK_INTERVAL_S, inference_engine: Optional[InferenceEngine] = None,
-                 openai_http: bool = False):
+                 openai_http: bool = False, idle_unload_minutes: Optional[float] = None, auto_restart: bool = True):
         engine = inference_engine or InferenceEngine()
         factory = None
         if openai_http:  # every loaded model also answers OpenAI-compatible HTTP on its ModelStatus.port
             from .openai_http import OpenAIServer
             factory = lambda name, handle, port: OpenAIServer(handle, name, port, engine).start()  # noqa: E731
-        self.manager = ModelManager(backend, model_dir, http_factory=factory)
+        self.manager = ModelManager(backend, model_dir, http_factory=factory, idle_unload_minutes=idle_unload_minutes,
+                                    auto_restart=auto_restart)
         self.service = AIRuntimeService(self.manager, engine)
         self.server = grpc.server(futures.ThreadPoolExecutor(max_workers=max_workers))
         self.server.add_generic_rpc_handlers((generic_handler(self.service),))
@@ -263,6 +264,12 @@ def main(argv=None):
     ap.add_argument("--model-dir", default=None)
     ap.add_argument("--openai-http", action="store_true",
                     help="serve every loaded model on its port (8080, 8081, ...) with the OpenAI-compatible HTTP API")
+    ap.add_argument("--idle-unload-minutes", type=float, default=None,
+                    help="unload a model that has not been used for this long (config/default-config.toml: "
+                         "idle_unload_minutes; default $AIOS_IDLE_UNLOAD_MINUTES, 0 = never); models whose name "
+                         'contains "tinyllama" (the operational model) stay')
+    ap.add_argument("--no-auto-restart", action="store_true", help="flag a dead model as errored and leave it (the "
+                                                                   "reference's behaviour) instead of reloading it")
     args = ap.parse_args(argv)
     logging.basicConfig(level=logging.INFO, format="%(asctime)s %(levelname)s %(message)s")
     from .inference import EngineBackend
@@ -270,7 +277,8 @@ def main(argv=None):
     if args.gpus:
         os.environ["AIOS_GPUS"] = args.gpus
     srv = RuntimeServer(EngineBackend(device=args.device), addr=args.addr, model_dir=args.model_dir,
-                        openai_http=args.openai_http).start()
+                        openai_http=args.openai_http, idle_unload_minutes=args.idle_unload_minutes,
+                        auto_restart=not args.no_auto_restart).start()
     try:
         srv.server.wait_for_termination()
     except KeyboardInterrupt:

@@ -257,7 +257,7 @@ def test_model_to_status_conversion():
 
 def test_load_unload_lifecycle(vocab_gguf, tmp_path):
     be = FakeBackend()
-    mgr = ModelManager(be, os.path.dirname(vocab_gguf))
+    mgr = ModelManager(be, os.path.dirname(vocab_gguf), auto_restart=False)  # the reference's own behaviour
     t0 = now_epoch_ms()
     st = mgr.load_model(LoadRequest(model_name=os.path.basename(vocab_gguf)))  # empty path -> model_dir/name
     assert st.status == "ready" and st.port == BASE_PORT and st.request_count == 0
@@ -445,3 +445,84 @@ def test_reference_client_stub_talks_to_the_server(server, vocab_gguf):
         assert r.model_used == "mistral-7b-test" and r.tokens_used > 8
         assert stub.HealthCheck(common_pb2.Empty()).details["loaded_models"] == "1"
         assert [c.done for c in stub.StreamInfer(runtime_pb2.InferRequest(prompt="hi", max_tokens=4))][-1] is True
+
+
+# ------------------------------------------------------------------ lifecycle extras the reference's docs promise
+def test_failed_unload_keeps_the_model_for_a_retry(vocab_gguf):
+    """An unload that the backend refuses must not orphan the model (its weights would stay in HBM, unreachable):
+    the entry stays, in its error state, and a second UnloadModel goes through."""
+    class Stubborn(FakeBackend):
+        refuse = True
+
+        def unload(self, handle):
+            if self.refuse:
+                raise RuntimeError("model still has queued or running requests")
+            super().unload(handle)
+
+    be = Stubborn()
+    mgr = ModelManager(be, model_dir=os.path.dirname(vocab_gguf))
+    mgr.load_model(LoadRequest("tinyllama-1.1b-chat", model_path=vocab_gguf))
+    with pytest.raises(RuntimeError, match="queued or running"):
+        mgr.unload_model("tinyllama-1.1b-chat")
+    st = mgr.list_models()[0]
+    assert st.status.startswith("error: unload failed") and mgr.models["tinyllama-1.1b-chat"].handle is not None
+    assert mgr.model_port("tinyllama-1.1b-chat") is None  # not routable meanwhile
+    be.refuse = False
+    mgr.unload_model("tinyllama-1.1b-chat")
+    assert mgr.list_models() == [] and be.unloaded[0].closed
+
+
+def test_idle_unload_spares_the_operational_model(vocab_gguf):
+    """config/default-config.toml:26 `idle_unload_minutes`, docs/phases/04-AI-RUNTIME.md:208: tactical models leave
+    after the idle timeout; the operational model (name contains "tinyllama") stays; a busy model stays."""
+    be = FakeBackend()
+    mgr = ModelManager(be, model_dir=os.path.dirname(vocab_gguf), idle_unload_minutes=5)
+    for name in ("tinyllama-1.1b-chat", "mistral-7b-instruct", "qwen3-14b"):
+        mgr.load_model(LoadRequest(name, model_path=vocab_gguf))
+    old = now_epoch_ms() - 6 * 60_000
+    for m in mgr.models.values():
+        m.last_used = old
+    mgr.models["qwen3-14b"].handle.load = lambda: {0: 1}  # one request in flight
+    mgr.health_check_all()
+    assert sorted(mgr.models) == ["qwen3-14b", "tinyllama-1.1b-chat"]
+    assert [h.name for h in be.unloaded] == ["mistral-7b-instruct"]
+    mgr.models["qwen3-14b"].handle.load = lambda: {0: 0}
+    mgr.get_model("qwen3-14b")  # a use stamps last_used (model_manager.rs:357-365)
+    mgr.health_check_all()
+    assert "qwen3-14b" in mgr.models
+    # off by default, as in the reference (which never unloads on its own)
+    assert ModelManager(FakeBackend(), model_dir="/tmp").idle_unload_ms == 0
+
+
+def test_dead_model_is_restarted(vocab_gguf):
+    """docs/phases/04-AI-RUNTIME.md:210 / model_manager.rs:391-392: a model whose backend handle died is loaded again
+    from the same file, keeps its port and request count, and goes back to ready; when the file is gone it stays in
+    its error state after MAX_RESTARTS attempts."""
+    from aios_b200.runtime.model_manager import MAX_RESTARTS
+    be = FakeBackend()
+    mgr = ModelManager(be, model_dir=os.path.dirname(vocab_gguf))
+    st = mgr.load_model(LoadRequest("mistral-7b", model_path=vocab_gguf))
+    mgr.model_port("mistral-7b")
+    first = mgr.models["mistral-7b"].handle
+    be.dead.add("mistral-7b")
+    real_alive = be.alive
+    be.alive = lambda h: h is not first and real_alive(h) or (h is not first)
+    mgr.health_check_all()
+    m = mgr.models["mistral-7b"]
+    assert m.status.ready and m.handle is not first and first.closed and m.port == st.port and m.request_count == 1
+    assert m.restarts == 0 and len(be.loaded) == 2
+    # a model that cannot come back
+    be.alive = lambda h: False
+    m.path = "/nonexistent/model.gguf"
+    for _ in range(MAX_RESTARTS + 2):
+        mgr.health_check_all()
+        mgr.models["mistral-7b"].handle = mgr.models["mistral-7b"].handle or object()  # keep it checkable
+    m = mgr.models["mistral-7b"]
+    assert str(m.status).startswith("error: ") and m.restarts == MAX_RESTARTS
+    # without auto_restart the reference's behaviour: flagged, left alone
+    be2 = FakeBackend()
+    mgr2 = ModelManager(be2, model_dir=os.path.dirname(vocab_gguf), auto_restart=False)
+    mgr2.load_model(LoadRequest("mistral-7b", model_path=vocab_gguf))
+    be2.dead.add("mistral-7b")
+    mgr2.health_check_all()
+    assert str(mgr2.models["mistral-7b"].status).startswith("error: ") and len(be2.loaded) == 1

@@ -98,3 +98,27 @@ def test_config1_mistral7b_full_size_properties(engine):
         assert info.kv_bytes_per_position == gs.kv_bytes_per_position("mistral-7b") == 131072
     finally:
         m.unload()
+
+
+def test_tied_embeddings_match_oracle(oracle, tmp_path):
+    """Files without `output.weight` use `token_embd.weight` as the lm_head (real-file compatibility,
+    §8f-4): logits and greedy tokens against the oracle, which takes the same branch (oracle/aios_oracle.c)."""
+    from aios_b200 import capi
+
+    path = str(tmp_path / "tied.gguf")
+    info = gs.write_synthetic_gguf(path, "tiny-gqa4", "Q4_K_M", 11, tied=True)
+    assert "output.weight" not in info.tensors
+    prompt = gs.synthetic_prompt("tiny-gqa4", 20, 3)
+    om = oracle.OracleModel(path, n_ctx=128)
+    ref_logits = om.eval(prompt)
+    ref, _ = om.greedy(prompt, 24)
+    eng = capi.Engine(device=0)
+    try:
+        m = eng.load_model("tied", path, n_ctx=128)
+        try:
+            assert np.array_equal(m.forward_logits(prompt).view(np.uint32), ref_logits.view(np.uint32))
+            assert np.array_equal(m.generate(prompt, 24), ref)
+        finally:
+            m.unload()
+    finally:
+        eng.close()
