@@ -483,8 +483,8 @@ int aios_model_meta_str(aios_model *m, const char *key, char *buf, int32_t cap, 
 
 static int need_vocab(const Tokenizer &t) {
     if (t.n_tokens() == 0) return fail(AIOS_E_STATE, "the GGUF file carries no tokenizer.ggml.tokens");
-    if (t.model() != "llama")
-        return fail(AIOS_E_UNSUPPORTED, "tokenizer.ggml.model '" + t.model() + "' is not supported (only 'llama' / SentencePiece)");
+    if (t.model() != "llama" && t.model() != "gpt2")
+        return fail(AIOS_E_UNSUPPORTED, "tokenizer.ggml.model '" + t.model() + "' is not supported ('llama' = SentencePiece and 'gpt2' = byte-level BPE are)");
     return (int)AIOS_OK;
 }
 

@@ -7,8 +7,151 @@
 #include <queue>
 
 #include "gguf.h"
+#include "unicode_tables.h"
 
 namespace aios {
+
+// ---------------------------------------------------------------- Unicode helpers for the BPE pre-tokenizer
+namespace {
+bool in_ranges(const uint32_t (*tab)[2], int n, uint32_t cp) {
+    int lo = 0, hi = n - 1;
+    while (lo <= hi) {
+        const int mid = (lo + hi) / 2;
+        if (cp < tab[mid][0]) hi = mid - 1;
+        else if (cp > tab[mid][1]) lo = mid + 1;
+        else return true;
+    }
+    return false;
+}
+enum CpClass : uint8_t { C_OTHER = 0, C_LETTER = 1, C_NUMBER = 2, C_SPACE = 3 };
+CpClass classify(uint32_t cp) {
+    if (cp < 128) {
+        if ((cp >= 'a' && cp <= 'z') || (cp >= 'A' && cp <= 'Z')) return C_LETTER;
+        if (cp >= '0' && cp <= '9') return C_NUMBER;
+        if (cp == ' ' || (cp >= 9 && cp <= 13)) return C_SPACE;
+        return C_OTHER;
+    }
+    if (in_ranges(UNI_LETTER, UNI_LETTER_N, cp)) return C_LETTER;
+    if (in_ranges(UNI_NUMBER, UNI_NUMBER_N, cp)) return C_NUMBER;
+    if (in_ranges(UNI_SPACE, UNI_SPACE_N, cp)) return C_SPACE;
+    return C_OTHER;
+}
+
+struct Cp {
+    uint32_t cp;
+    uint32_t off;  // byte offset in the text
+    CpClass cls;
+};
+// decode UTF-8 leniently: an invalid byte is one code point of class OTHER (it still goes through the byte map)
+std::vector<Cp> decode_utf8(const std::string &t, size_t off, size_t len) {
+    std::vector<Cp> out;
+    out.reserve(len);
+    const size_t end = off + len;
+    for (size_t i = off; i < end;) {
+        const unsigned char c = (unsigned char)t[i];
+        uint32_t cp = c;
+        size_t n = 1;
+        if (c >= 0xC2 && c <= 0xDF) n = 2, cp = c & 0x1F;
+        else if (c >= 0xE0 && c <= 0xEF) n = 3, cp = c & 0x0F;
+        else if (c >= 0xF0 && c <= 0xF4) n = 4, cp = c & 0x07;
+        bool ok = n > 1 && i + n <= end;
+        for (size_t k = 1; ok && k < n; k++) {
+            const unsigned char cc = (unsigned char)t[i + k];
+            if ((cc & 0xC0) != 0x80) ok = false;
+            else cp = (cp << 6) | (cc & 0x3F);
+        }
+        if (n > 1 && !ok) {
+            out.push_back({0xFFFFFFFFu, (uint32_t)i, C_OTHER});
+            i += 1;
+            continue;
+        }
+        out.push_back({cp, (uint32_t)i, n == 1 ? classify(cp) : classify(cp)});
+        i += n;
+    }
+    return out;
+}
+inline bool is_nl(uint32_t cp) { return cp == '\r' || cp == '\n'; }
+inline uint32_t ascii_lower(uint32_t cp) { return cp >= 'A' && cp <= 'Z' ? cp + 32 : cp; }
+
+// Length in code points of the pre-token that starts at i.
+//   Llama-3: (?i:'s|'t|'re|'ve|'m|'ll|'d)|[^\r\n\p{L}\p{N}]?\p{L}+|\p{N}{1,3}| ?[^\s\p{L}\p{N}]+[\r\n]*|\s*[\r\n]+|\s+(?!\S)|\s+
+//   GPT-2:   's|'t|'re|'ve|'m|'ll|'d| ?\p{L}+| ?\p{N}+| ?[^\s\p{L}\p{N}]+|\s+(?!\S)|\s+
+// Alternatives are tried in order at each position (leftmost alternative wins, each quantifier greedy with
+// backtracking) — written out case by case.
+size_t pretoken_len(const std::vector<Cp> &c, size_t i, int pre) {
+    const size_t n = c.size();
+    const bool l3 = pre == 1;
+    // contractions
+    if (c[i].cp == '\'' && i + 1 < n) {
+        const uint32_t a = l3 ? ascii_lower(c[i + 1].cp) : c[i + 1].cp;
+        if (a == 's' || a == 't' || a == 'm' || a == 'd') return 2;
+        if (i + 2 < n) {
+            const uint32_t b = l3 ? ascii_lower(c[i + 2].cp) : c[i + 2].cp;
+            if ((a == 'r' && b == 'e') || (a == 'v' && b == 'e') || (a == 'l' && b == 'l')) return 3;
+        }
+    }
+    auto run = [&](size_t j, CpClass k) {
+        while (j < n && c[j].cls == k) j++;
+        return j;
+    };
+    if (l3) {
+        // [^\r\n\p{L}\p{N}]?\p{L}+
+        if (c[i].cls != C_LETTER && c[i].cls != C_NUMBER && !is_nl(c[i].cp) && i + 1 < n && c[i + 1].cls == C_LETTER)
+            return run(i + 1, C_LETTER) - i;
+        if (c[i].cls == C_LETTER) return run(i, C_LETTER) - i;
+        // \p{N}{1,3}
+        if (c[i].cls == C_NUMBER) return std::min(run(i, C_NUMBER), i + 3) - i;
+        // ' ?[^\s\p{L}\p{N}]+[\r\n]*'
+        {
+            size_t j = i;
+            if (c[j].cp == ' ' && j + 1 < n && c[j + 1].cls == C_OTHER) j++;
+            if (c[j].cls == C_OTHER) {
+                j = run(j, C_OTHER);
+                while (j < n && is_nl(c[j].cp)) j++;
+                return j - i;
+            }
+        }
+    } else {
+        // ' ?\p{L}+', ' ?\p{N}+', ' ?[^\s\p{L}\p{N}]+'
+        size_t j = i;
+        if (c[j].cp == ' ' && j + 1 < n && c[j + 1].cls != C_SPACE) j++;
+        if (c[j].cls != C_SPACE) return run(j, c[j].cls) - i;
+    }
+    // only whitespace can be here
+    if (c[i].cls != C_SPACE) return 1;
+    const size_t e = run(i, C_SPACE);
+    if (l3) {  // \s*[\r\n]+ : up to and including the last newline of the run
+        size_t last = n;
+        for (size_t j = i; j < e; j++)
+            if (is_nl(c[j].cp)) last = j;
+        if (last != n) return last + 1 - i;
+    }
+    // \s+(?!\S): leave the last blank to the word that follows, unless the run is a single one or ends the text
+    if (e == n) return e - i;
+    if (e - i > 1) return e - 1 - i;
+    return e - i;  // \s+
+}
+
+// GPT-2's byte -> printable code point map (bytes_to_unicode): printable Latin-1 stays, the rest moves to U+0100...
+struct ByteMap {
+    std::string enc[256];                          // UTF-8 of the mapped character
+    std::unordered_map<uint32_t, uint8_t> dec;     // mapped code point -> byte
+    ByteMap() {
+        int extra = 0;
+        for (int b = 0; b < 256; b++) {
+            const bool keep = (b >= 33 && b <= 126) || (b >= 161 && b <= 172) || (b >= 174 && b <= 255);
+            const uint32_t cp = keep ? (uint32_t)b : 256u + (uint32_t)extra++;
+            if (cp < 0x80) enc[b] = std::string(1, (char)cp);
+            else enc[b] = {(char)(0xC0 | (cp >> 6)), (char)(0x80 | (cp & 0x3F))};
+            dec.emplace(cp, (uint8_t)b);
+        }
+    }
+};
+const ByteMap &byte_map() {
+    static const ByteMap m;
+    return m;
+}
+}  // namespace
 
 static const char kSpace[] = "\xE2\x96\x81";  // U+2581, SentencePiece's visible space
 
@@ -30,6 +173,23 @@ Tokenizer::Tokenizer(const GgufFile &f) {
     unk_ = (int32_t)f.get_u("tokenizer.ggml.unknown_token_id", 0);
     add_bos_ = f.has("tokenizer.ggml.add_bos_token") ? f.get_u("tokenizer.ggml.add_bos_token", 1) != 0 : true;
     add_space_prefix_ = f.has("tokenizer.ggml.add_space_prefix") ? f.get_u("tokenizer.ggml.add_space_prefix", 1) != 0 : true;
+
+    bpe_ = model_ == "gpt2";
+    if (bpe_) {
+        const std::string pre = f.get_s("tokenizer.ggml.pre", "default");
+        if (pre == "llama-bpe" || pre == "llama3" || pre == "llama-v3") {
+            pre_ = 1;
+            ignore_merges_ = true;  // a pre-token that is itself a piece is taken whole
+            if (!f.has("tokenizer.ggml.add_bos_token")) add_bos_ = true;
+        } else {
+            pre_ = 0;  // GPT-2's pattern (also the fallback for pre-tokenizers this build does not know)
+            if (!f.has("tokenizer.ggml.add_bos_token")) add_bos_ = false;
+        }
+        add_space_prefix_ = false;
+        const std::vector<std::string> merges = f.get_str_array("tokenizer.ggml.merges");
+        merge_rank_.reserve(merges.size() * 2);
+        for (size_t i = 0; i < merges.size(); i++) merge_rank_.emplace(merges[i], (int32_t)i);
+    }
 
     index_.reserve(pieces_.size() * 2);
     for (int i = 0; i < 256; i++) byte_ids_[i] = -1;
@@ -125,6 +285,80 @@ void Tokenizer::encode_spm(const std::string &text, std::vector<int32_t> &out) c
     for (int i = 0; i >= 0; i = sym[i].next) emit_symbol(text.substr(sym[i].off, sym[i].len), out);
 }
 
+// one pre-token, already in mapped characters: merge adjacent symbols by rank until no listed pair is left
+void Tokenizer::bpe_word(const std::string &w, std::vector<int32_t> &out) const {
+    if (ignore_merges_) {
+        auto it = index_.find(w);
+        if (it != index_.end()) {
+            out.push_back(it->second);
+            return;
+        }
+    }
+    std::vector<Symbol> sym;
+    for (size_t off = 0; off < w.size();) {
+        const size_t n = std::min(utf8_len((unsigned char)w[off]), w.size() - off);
+        sym.push_back({(int)sym.size() - 1, (int)sym.size() + 1, off, n});
+        off += n;
+    }
+    sym.back().next = -1;
+    struct Pair {
+        int left, right, rank;
+        size_t llen, rlen;
+        bool operator<(const Pair &o) const { return rank > o.rank || (rank == o.rank && left > o.left); }  // min-heap
+    };
+    std::priority_queue<Pair> work;
+    std::string key;
+    auto try_add = [&](int l, int r) {
+        if (l < 0 || r < 0) return;
+        key.assign(w, sym[l].off, sym[l].len);
+        key += ' ';
+        key.append(w, sym[r].off, sym[r].len);
+        auto it = merge_rank_.find(key);
+        if (it != merge_rank_.end()) work.push({l, r, it->second, sym[l].len, sym[r].len});
+    };
+    for (int i = 1; i < (int)sym.size(); i++) try_add(i - 1, i);
+    while (!work.empty()) {
+        const Pair b = work.top();
+        work.pop();
+        Symbol &l = sym[b.left], &r = sym[b.right];
+        if (l.len != b.llen || r.len != b.rlen || l.next != b.right) continue;  // stale entry
+        l.len += r.len;
+        r.len = 0;
+        l.next = r.next;
+        if (r.next >= 0) sym[r.next].prev = b.left;
+        try_add(l.prev, b.left);
+        try_add(b.left, l.next);
+    }
+    for (int i = 0; i >= 0; i = sym[i].next) {
+        const std::string piece = w.substr(sym[i].off, sym[i].len);
+        auto it = index_.find(piece);
+        if (it != index_.end()) {
+            out.push_back(it->second);
+            continue;
+        }
+        for (size_t off = 0; off < piece.size();) {  // no such piece: one token per byte (mapped character)
+            const size_t n = std::min(utf8_len((unsigned char)piece[off]), piece.size() - off);
+            auto b = index_.find(piece.substr(off, n));
+            out.push_back(b != index_.end() ? b->second : unk_);
+            off += n;
+        }
+    }
+}
+
+void Tokenizer::encode_bpe(const std::string &text, std::vector<int32_t> &out) const {
+    const std::vector<Cp> cps = decode_utf8(text, 0, text.size());
+    const ByteMap &bm = byte_map();
+    std::string w;
+    for (size_t i = 0; i < cps.size();) {
+        const size_t len = pretoken_len(cps, i, pre_);
+        const size_t b0 = cps[i].off, b1 = i + len < cps.size() ? cps[i + len].off : text.size();
+        w.clear();
+        for (size_t b = b0; b < b1; b++) w += bm.enc[(unsigned char)text[b]];
+        bpe_word(w, out);
+        i += len;
+    }
+}
+
 std::vector<int32_t> Tokenizer::encode(const std::string &text, bool add_special, bool parse_special) const {
     std::vector<int32_t> out;
     if (add_special && add_bos_ && bos_ >= 0) out.push_back(bos_);
@@ -160,6 +394,11 @@ std::vector<int32_t> Tokenizer::encode(const std::string &text, bool add_special
             continue;
         }
         if (fr.len == 0) continue;
+        if (bpe_) {
+            encode_bpe(text.substr(fr.off, fr.len), out);
+            prev_special = false;
+            continue;
+        }
         std::string s;
         s.reserve(fr.len * 3 + 3);
         if (add_space_prefix_ && prev_special) s += kSpace;
@@ -191,6 +430,15 @@ std::string Tokenizer::piece_text(int32_t id, bool render_special) const {
         default: {
             std::string s;
             s.reserve(p.size());
+            if (bpe_) {  // mapped characters back to bytes (user-defined pieces are literal text)
+                if (type(id) == TOK_USER_DEFINED) return p;
+                const ByteMap &bm = byte_map();
+                for (const Cp &c : decode_utf8(p, 0, p.size())) {
+                    auto it = bm.dec.find(c.cp);
+                    if (it != bm.dec.end()) s += (char)it->second;
+                }
+                return s;
+            }
             for (size_t i = 0; i < p.size();) {
                 if (p.compare(i, 3, kSpace) == 0) { s += ' '; i += 3; }
                 else s += p[i++];

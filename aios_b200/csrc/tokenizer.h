@@ -5,8 +5,11 @@
 // (runtime/src/inference.rs:363-376) and llama-server renders them with the model's chat
 // template and encodes the text.  llama.cpp is not vendored, so this is written from the
 // published algorithms [upstream-knowledge]: SentencePiece-style greedy bigram merging by
-// score with <0xNN> byte fallback ("llama" vocabularies: TinyLlama, Mistral), special-token
-// partitioning, and recognition of the common chat formats by their marker strings.
+// score with <0xNN> byte fallback ("llama" vocabularies: TinyLlama, Mistral); byte-level BPE
+// ("gpt2" vocabularies: Llama-3) — regex pre-tokenizer (the Llama-3 and GPT-2 patterns, matched by
+// a hand-written scanner over Unicode categories), GPT-2's byte <-> printable-character map, merges
+// by rank from tokenizer.ggml.merges; special-token partitioning; and recognition of the common
+// chat formats by their marker strings (how llama.cpp's llama_chat_apply_template picks one too).
 #pragma once
 #include <stdint.h>
 
@@ -52,6 +55,8 @@ class Tokenizer {
    private:
     void encode_spm(const std::string &text, std::vector<int32_t> &out) const;
     void emit_symbol(const std::string &s, std::vector<int32_t> &out) const;
+    void encode_bpe(const std::string &text, std::vector<int32_t> &out) const;
+    void bpe_word(const std::string &mapped, std::vector<int32_t> &out) const;
 
     std::string model_;
     std::vector<std::string> pieces_;
@@ -63,6 +68,10 @@ class Tokenizer {
     int32_t byte_ids_[256];
     int32_t bos_ = -1, eos_ = -1, unk_ = 0;
     bool add_bos_ = true, add_space_prefix_ = true;
+    // byte-level BPE
+    bool bpe_ = false, ignore_merges_ = false;
+    int pre_ = 0;  // 0: GPT-2 pattern, 1: Llama-3 pattern
+    std::unordered_map<std::string, int32_t> merge_rank_;  // "left right" -> rank
     ChatFormat format_ = CHAT_CHATML;
 };
 

@@ -193,10 +193,13 @@ class SynthInfo:
 
 def write_synthetic_gguf(path: str, arch: Arch | str, ftype: str = "Q4_K_M", seed: int = 0xA105,
                          w_std: float = 0.02, with_vocab: bool = True, vocab: list | None = None,
-                         chat_template: str | None = None, tokenizer_model: str = "llama", tied: bool = False) -> SynthInfo:
+                         chat_template: str | None = None, tokenizer_model: str = "llama", tied: bool = False,
+                         merges: list | None = None, tokenizer_pre: str | None = None,
+                         bos_id: int = 1, eos_id: int = 2) -> SynthInfo:
     """``vocab`` = [(piece, score, token_type)] replaces the generated placeholder vocabulary (padded with unused
     entries up to ``arch.n_vocab``); ``chat_template`` is stored as ``tokenizer.chat_template``; ``tied`` leaves
-    ``output.weight`` out (the lm_head is then ``token_embd.weight``, as in files with tied embeddings)."""
+    ``output.weight`` out (the lm_head is then ``token_embd.weight``, as in files with tied embeddings); ``merges``
+    (["left right", ...]) and ``tokenizer_pre`` are the byte-level-BPE keys ``tokenizer.ggml.merges`` / ``.pre``."""
     if isinstance(arch, str):
         arch = ARCHS[arch]
     plan = tensor_plan(arch, ftype)
@@ -218,9 +221,13 @@ def write_synthetic_gguf(path: str, arch: Arch | str, ftype: str = "Q4_K_M", see
         _kv("llama.rope.dimension_count", _U32, arch.head_dim),
         _kv("llama.rope.freq_base", _F32, arch.rope_freq_base),
         _kv("tokenizer.ggml.model", _STR, tokenizer_model),
-        _kv("tokenizer.ggml.bos_token_id", _U32, 1),
-        _kv("tokenizer.ggml.eos_token_id", _U32, 2),
+        _kv("tokenizer.ggml.bos_token_id", _U32, bos_id),
+        _kv("tokenizer.ggml.eos_token_id", _U32, eos_id),
     ]
+    if merges is not None:
+        kvs.append(_kv("tokenizer.ggml.merges", _ARR, (_STR, list(merges))))
+    if tokenizer_pre is not None:
+        kvs.append(_kv("tokenizer.ggml.pre", _STR, tokenizer_pre))
     if chat_template is not None:
         kvs.append(_kv("tokenizer.chat_template", _STR, chat_template))
     if vocab is not None:

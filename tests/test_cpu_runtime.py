@@ -188,12 +188,64 @@ def test_vocab_open_errors(tmp_path):
     with pytest.raises(capi.AiosError) as e:
         capi.Vocab.open(str(tmp_path / "missing.gguf"))
     assert e.value.code == capi.E_IO
-    p = tmp_path / "bpe.gguf"
-    gguf_synth.write_synthetic_gguf(str(p), "tiny", tokenizer_model="gpt2")
+    p = tmp_path / "wordpiece.gguf"
+    gguf_synth.write_synthetic_gguf(str(p), "tiny", tokenizer_model="bert")
     v = capi.Vocab.open(str(p))
     with pytest.raises(capi.AiosError) as e:
         v.tokenize("hello")
     assert e.value.code == capi.E_UNSUPPORTED
+
+
+# ------------------------------------------------------------------ byte-level BPE ("gpt2" vocabularies: Llama-3)
+@pytest.fixture(scope="module")
+def bpe_golden():
+    with open(os.path.join(HERE, "golden", "bpe_vocab.json"), encoding="utf-8") as f:
+        return json.load(f)
+
+
+def _bpe_gguf(tmp_path, g, pre, template=None):
+    n_sp = g["n_special"]
+    vocab = [(p, 0.0, 3 if i < n_sp else 1) for i, p in enumerate(g["vocab"])]
+    arch = dataclasses.replace(gguf_synth.ARCHS["tiny"], n_vocab=len(vocab) + 6)
+    path = str(tmp_path / f"bpe-{pre}.gguf")
+    gguf_synth.write_synthetic_gguf(path, arch, vocab=vocab, tokenizer_model="gpt2", merges=g["merges"],
+                                    tokenizer_pre=pre, bos_id=0, eos_id=1, chat_template=template)
+    return path
+
+
+@pytest.mark.parametrize("pre,cases", [("llama-bpe", "cases_llama3"), ("gpt-2", "cases_gpt2")])
+def test_bpe_ids_match_hf_tokenizers(bpe_golden, tmp_path, pre, cases):
+    """Every golden case (contractions in both cases, digit runs, blank / newline runs, CRLF, Unicode letters, numbers
+    and spaces, emoji, text that no merge covers) encodes to the ids HF `tokenizers` produced, and decodes back."""
+    v = capi.Vocab.open(_bpe_gguf(tmp_path, bpe_golden, pre))
+    assert len(bpe_golden[cases]) >= 30
+    for text, want in bpe_golden[cases]:
+        got = v.tokenize(text, add_special=False)
+        assert got.tolist() == want, (text, got.tolist(), want)
+        assert v.detokenize(got).decode("utf-8") == text
+    # BOS: Llama-3 vocabularies get one, plain GPT-2 ones do not; special strings become their ids when asked to
+    ids = v.tokenize("Hello", add_special=True)
+    assert (ids[0] == 0) == (pre == "llama-bpe")
+    sp = v.tokenize("<|eot_id|>Hello<|end_of_text|>", add_special=False, parse_special=True)
+    assert sp[0] == 2 and sp[-1] == 1 and v.is_eog(2) and v.is_eog(1)
+    assert v.detokenize(sp, render_special=True).decode() == "<|eot_id|>Hello<|end_of_text|>"
+    assert v.detokenize(sp).decode() == "Hello"
+    # bytes that are not UTF-8 still round-trip (byte-level vocabulary)
+    raw = b"ok \xff\xfe \xc3 end"
+    assert v.detokenize(v.tokenize(raw, add_special=False)) == raw
+
+
+def test_llama3_chat_prompt(bpe_golden, tmp_path):
+    """Llama-3's chat format, picked by the template's marker string, rendered for {system, user}
+    (runtime/src/inference.rs:363-376) and tokenised with the header markers as single ids."""
+    v = capi.Vocab.open(_bpe_gguf(tmp_path, bpe_golden, "llama-bpe",
+                                  template="{% for m in messages %}<|start_header_id|>{{ m['role'] }}<|end_header_id|>…"))
+    text = v.chat_prompt("Be brief.", "Hi")
+    assert text == ("<|start_header_id|>system<|end_header_id|>\n\nBe brief.<|eot_id|>"
+                    "<|start_header_id|>user<|end_header_id|>\n\nHi<|eot_id|>"
+                    "<|start_header_id|>assistant<|end_header_id|>\n\n")
+    ids = v.tokenize(text, add_special=True, parse_special=True).tolist()
+    assert ids[0] == 0 and ids[1] == 3 and ids.count(3) == 3 and ids.count(4) == 3 and ids.count(2) == 2
 
 
 # ------------------------------------------------------------------ model_manager.rs:556-712 restated
