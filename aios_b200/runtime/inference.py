@@ -163,16 +163,72 @@ class _LiveRequest:
             self._g = None
 
 
+class _TpSeq:
+    """The sequence interface the inference layer drives (reset / prefill / decode / logits) on a tensor-parallel model."""
+
+    def __init__(self, tp):
+        self.tp = tp
+
+    def reset(self):
+        self.tp.reset()
+
+    def prefill(self, tokens):
+        self.tp.prefill(tokens)
+
+    def decode(self, max_tokens: int, sampling=None):
+        return self.tp.decode(max_tokens, sampling)
+
+    def logits(self):
+        return self.tp.logits()
+
+
+class TpLoaded:
+    """A model split over several GPUs (``aios_tp_*``: 70B-class models, docs/HARDWARE.md:135-138).  One request at
+    a time under ``lock`` (the tensor-parallel group has no request scheduler yet); same attributes as LoadedModel
+    otherwise, so Infer / StreamInfer / the HTTP endpoint run on it unchanged."""
+
+    def __init__(self, capi, devices: list, name: str, path: str, context_length: int, flags: int = 0):
+        self.name, self.devices = name, list(devices)
+        self.tp = capi.TpModel(self.devices, name, path, context_length, flags)
+        self.vocab = capi.Vocab.open(path)
+        self.n_ctx = self.tp.info.n_ctx
+        self.seq = _TpSeq(self.tp)
+        self.lock = threading.Lock()
+        self.model = None
+        self.replicas = []
+
+    def load(self) -> dict:
+        busy = 1 if self.lock.locked() else 0
+        return {d: busy for d in self.devices}
+
+    def alive(self) -> bool:
+        return bool(self.tp.h)
+
+    def close(self):
+        with self.lock:  # waits for the request that is running, like the reference's SIGTERM + wait
+            self.tp.unload()
+            self.vocab.close()
+
+
 class EngineBackend:
     """``Backend`` of ModelManager on the real engine: one ``aios_engine`` per GPU of this process.
+
+    ``tp`` (default ``AIOS_TP``, 0 = off): models whose lower-cased name contains one of ``tp_models`` (default
+    ``AIOS_TP_MODELS`` or "70b") are not replicated but split ``tp`` ways over the first ``tp`` devices.
 
     ``devices``: CUDA ordinals to serve on; default = ``AIOS_GPUS`` ("0,2,3" or "all") if set, else ``[device]``.
     With several devices LoadModel puts one full replica of the model on every GPU and each request goes to the
     least-loaded replica (``aios_b200.replicas.ReplicaSet``; SURVEY.md §8e: replicas only, no collective)."""
 
-    def __init__(self, device: int = 0, flags: int = 0, devices: Optional[list] = None):
+    def __init__(self, device: int = 0, flags: int = 0, devices: Optional[list] = None, tp: Optional[int] = None,
+                 tp_models: Optional[tuple] = None):
         from .. import capi
         self.capi = capi
+        self.flags = flags
+        self.tp = int(os.environ.get("AIOS_TP", "0") or 0) if tp is None else int(tp)
+        if tp_models is None:
+            tp_models = tuple(x for x in os.environ.get("AIOS_TP_MODELS", "70b").lower().split(",") if x)
+        self.tp_models = tuple(x.lower() for x in tp_models)
         if devices is None:
             env = os.environ.get("AIOS_GPUS", "").strip()
             if env.lower() == "all":
@@ -191,6 +247,12 @@ class EngineBackend:
     def load(self, name: str, path: str, context_length: int):
         if not os.path.isfile(path):
             raise FileNotFoundError(f"model file {path} not found")
+        if self.tp > 1 and any(x in name.lower() for x in self.tp_models):
+            if len(self.devices) < self.tp:
+                raise RuntimeError(f"tensor parallelism {self.tp} needs {self.tp} GPUs, this backend serves {self.devices}")
+            handle = TpLoaded(self.capi, self.devices[: self.tp], name, path, context_length, self.flags)
+            self._sets.append(handle)
+            return handle
         from ..replicas import ReplicaSet
         loaded = []
         try:
@@ -210,6 +272,8 @@ class EngineBackend:
         handle.close()
 
     def alive(self, handle) -> bool:
+        if isinstance(handle, TpLoaded):
+            return handle.alive()
         return all(bool(r.model.h) for r in handle.replicas)
 
     def gpu_load(self) -> dict:
@@ -222,7 +286,8 @@ class EngineBackend:
         return out
 
     def close(self):
-        self.engine.close()
+        for e in self.engines:
+            e.close()
 
 
 class InferenceEngine:

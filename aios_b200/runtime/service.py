@@ -261,6 +261,9 @@ def main(argv=None):
     ap.add_argument("--gpus", default=None, help='CUDA ordinals to serve on, e.g. "0,1,2,3" or "all" (default: $AIOS_GPUS, '
                                                  "else --device): one engine and one replica of every model per GPU, "
                                                  "requests go to the least-loaded replica")
+    ap.add_argument("--tp", type=int, default=None,
+                    help="split 70B-class models (name contains one of $AIOS_TP_MODELS, default \"70b\") this many ways "
+                         "over the first GPUs instead of replicating them (default $AIOS_TP, 0 = off)")
     ap.add_argument("--model-dir", default=None)
     ap.add_argument("--openai-http", action="store_true",
                     help="serve every loaded model on its port (8080, 8081, ...) with the OpenAI-compatible HTTP API")
@@ -276,7 +279,7 @@ def main(argv=None):
     log.info("aiOS AI Runtime starting...")
     if args.gpus:
         os.environ["AIOS_GPUS"] = args.gpus
-    srv = RuntimeServer(EngineBackend(device=args.device), addr=args.addr, model_dir=args.model_dir,
+    srv = RuntimeServer(EngineBackend(device=args.device, tp=args.tp), addr=args.addr, model_dir=args.model_dir,
                         openai_http=args.openai_http, idle_unload_minutes=args.idle_unload_minutes,
                         auto_restart=not args.no_auto_restart).start()
     try:

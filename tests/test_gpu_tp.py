@@ -79,3 +79,46 @@ def test_tp_rejects_uneven_split(tmp_models):
     assert ei.value.code == capi.E_FORMAT
     with pytest.raises(capi.AiosError):
         capi.TpModel([0, 0], "dup", path, n_ctx=64)
+
+
+def test_runtime_serves_a_tensor_parallel_model(tmp_path):
+    """The gRPC-facing layer on a split model: a model whose name says 70b is loaded tensor-parallel by the backend
+    (`--tp 2`), Infer / StreamInfer give the text of the same file served from one GPU, HealthCheck shows both GPUs."""
+    import dataclasses
+    import json
+    import os
+
+    from aios_b200.runtime.inference import EngineBackend, InferenceEngine, InferParams, TpLoaded
+
+    _need_gpus(2)
+    with open(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "spm_vocab.json"), encoding="utf-8") as f:
+        g = json.load(f)
+    vocab = [tuple(v) for v in g["vocab"]] + [("<|im_start|>", 0.0, 3), ("<|im_end|>", 0.0, 3)]
+    n_vocab = (len(vocab) + 7) // 2 * 2
+    arch = dataclasses.replace(gs.ARCHS["tiny-gqa4"], n_vocab=n_vocab)
+    path = str(tmp_path / "llama-3-70b-synthetic.gguf")
+    gs.write_synthetic_gguf(path, arch, vocab=vocab, chat_template="<|im_start|> chatml <|im_end|>")
+    p = InferParams(prompt="Hello, world!", system_prompt="Be brief.", max_tokens=24, temperature=0.8, seed=7)
+    eng = InferenceEngine(stream_chunk_tokens=4)
+    one = EngineBackend(device=0)
+    try:
+        lm = one.load("llama-3-70b", path, 256)
+        want = eng.infer(lm, "llama-3-70b", p)
+        one.unload(lm)
+    finally:
+        one.close()
+    be = EngineBackend(devices=[0, 1], tp=2)
+    try:
+        lm = be.load("llama-3-70b", path, 256)
+        assert isinstance(lm, TpLoaded) and be.alive(lm) and be.gpu_load() == {0: [1, 0], 1: [1, 0]}
+        got = eng.infer(lm, "llama-3-70b", p)
+        assert got.text == want.text and got.tokens_used == want.tokens_used
+        chunks = list(eng.stream_infer(lm, "llama-3-70b", p))
+        assert chunks[-1] == ("", True) and "".join(t for t, _ in chunks) == want.text
+        small = be.load("tinyllama", path, 256)  # other models are still replicated, one replica per GPU
+        assert not isinstance(small, TpLoaded) and len(small.replicas) == 2
+        be.unload(small)
+        be.unload(lm)
+        assert not be.alive(lm)
+    finally:
+        be.close()
