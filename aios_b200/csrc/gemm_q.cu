@@ -16,7 +16,10 @@
 //
 // Activations: `quant_rows_kernel` builds, per token, the same Q8_K / Q8_0 image the GEMV prologue builds in shared
 // memory (gemv_core.cuh quant_slab, optional RMSNorm first) — in global memory, once per launch group, instead of once
-// per CTA.  The GEMM stages the images of all T tokens block by block (256 weights) through shared memory.
+// per CTA — and then re-files it block by block (256 weights) in exactly the layout a GEMM stage has in shared memory:
+// staged[b] = act[T][17] uint4 | aux[T][32] | d8[T], one contiguous record per block for all T tokens.  The GEMM brings
+// a block's record in with ONE bulk copy (`cp.async.bulk`, mbarrier completion) issued by one thread, where 1,200
+// 16-byte `cp.async` per stage with gathered sources used to keep the LSU busy 40 % of the time.
 //
 // A CTA owns 32 weight rows (two m16 row groups) of ONE segment and all T tokens: warp (rg, tg) takes row group rg and
 // token group tg (8*NT tokens).  Matrices that share an input ride in one launch as segments (q/k/v — also when
@@ -30,13 +33,47 @@ namespace aios {
 // grid = T, block = 256.  x row stride ldx (floats); image stride = act_image_bytes(k) rounded to 256.
 __host__ __device__ inline size_t gemm_image_stride(int k) { return (act_image_bytes(k) + 255) & ~(size_t)255; }
 
+constexpr int GEMM_TOK_STRIDE = 17;         // uint4 per token in a staged block: 16 used + 1 pad (bank spread over tokens)
+// one staged 256-weight block of all T token images
+//   act [T][GEMM_TOK_STRIDE] uint4 : Q4_K / Q6_K: entry 4u+kk = activation bytes a_kk of unit u; Q8_0: entry 2u+kk
+//   aux [T][32] bytes              : Q4_K: 8 x i32 32-wide q8 sums; Q6_K: 16 x i16 16-wide sums; Q8_0: 8 x f32 d8
+//   d8  [T] f32                    : Q4_K / Q6_K block scale
+__host__ __device__ inline size_t gemm_img_bytes(int T) { return (size_t)T * (GEMM_TOK_STRIDE * 16 + 32 + 4); }
+// the staged records follow the T per-token images
+__host__ __device__ inline size_t gemm_staged_offset(int k, int T) { return (gemm_image_stride(k) * (size_t)T + 127) & ~(size_t)127; }
+
 template <int PERM>
 __global__ void __launch_bounds__(GEMV_THREADS) quant_rows_kernel(const float *x, int64_t ldx, const float *norm_w, float eps,
                                                                    int k, uint8_t *images) {
     __shared__ double red[GEMV_WARPS];
-    const int t = blockIdx.x;
-    const ActSmem s = carve(images + (size_t)t * gemm_image_stride(k), k);
+    const int t = blockIdx.x, T = gridDim.x;
+    uint8_t *img = images + (size_t)t * gemm_image_stride(k);
+    const ActSmem s = carve(img, k);
     prep_activations<PERM>(x + (size_t)t * ldx, norm_w, eps, k, s, red);
+    // re-file this token's image into the per-block records (this CTA's own global writes, visible after the barrier)
+    __threadfence_block();
+    __syncthreads();
+    constexpr bool Q80 = PERM == PERM_Q80;
+    const int U = Q80 ? k / 32 : k / 64, nb = k / 256;
+    uint8_t *staged = images + gemm_staged_offset(k, T);
+    const size_t rec = gemm_img_bytes(T);
+    const uint4 *act = reinterpret_cast<const uint4 *>(img);
+    const uint8_t *aux = img + k;
+    for (int idx = threadIdx.x; idx < nb * 16; idx += GEMV_THREADS) {
+        const int b = idx >> 4, e = idx & 15;
+        const uint4 *src = Q80 ? act + (size_t)(e & 1) * U + 8 * b + (e >> 1) : act + (size_t)(e & 3) * U + 4 * b + (e >> 2);
+        reinterpret_cast<uint4 *>(staged + (size_t)b * rec)[t * GEMM_TOK_STRIDE + e] = *src;
+    }
+    for (int idx = threadIdx.x; idx < nb * 2; idx += GEMV_THREADS) {
+        const int b = idx >> 1, h = idx & 1;
+        const uint4 v = Q80 ? *reinterpret_cast<const uint4 *>(aux + k / 8 + (size_t)(8 * b + h * 4) * 4)
+                            : *reinterpret_cast<const uint4 *>(aux + (size_t)b * 32 + h * 16);
+        *reinterpret_cast<uint4 *>(staged + (size_t)b * rec + (size_t)T * GEMM_TOK_STRIDE * 16 + (size_t)t * 32 + h * 16) = v;
+    }
+    if (!Q80)
+        for (int b = threadIdx.x; b < nb; b += GEMV_THREADS)
+            *reinterpret_cast<float *>(staged + (size_t)b * rec + (size_t)T * (GEMM_TOK_STRIDE * 16 + 32) + (size_t)t * 4) =
+                *reinterpret_cast<const float *>(aux + k / 8 + (size_t)b * 4);
 }
 
 void launch_quant_rows(int weight_type, const float *x, int64_t ldx, const float *norm_w, float eps, int k, int T,
@@ -46,11 +83,10 @@ void launch_quant_rows(int weight_type, const float *x, int64_t ldx, const float
     else quant_rows_kernel<PERM_Q4><<<T, GEMV_THREADS, 0, st>>>(x, ldx, norm_w, eps, k, images);
     CUDA_CHECK(cudaGetLastError());
 }
-size_t gemm_images_bytes(int k, int T) { return gemm_image_stride(k) * (size_t)T; }
+size_t gemm_images_bytes(int k, int T) { return gemm_staged_offset(k, T) + (size_t)(k / 256) * gemm_img_bytes(T); }
 
 // ---------------------------------------------------------------- the GEMM
 constexpr int GEMM_MAX_ROWS = 32;           // weight rows per CTA: 16 * RG, RG = 1 or 2 m16 row groups (template parameter)
-constexpr int GEMM_TOK_STRIDE = 17;         // uint4 per token in the staged block: 16 used + 1 pad (bank spread over tokens)
 constexpr int GEMM_STAGES = 2;
 
 __device__ __forceinline__ void mma_s8_k32(int (&c)[4], uint32_t a0, uint32_t a1, uint32_t a2, uint32_t a3, uint32_t b0, uint32_t b1) {
@@ -74,11 +110,6 @@ __device__ __forceinline__ void cp4(void *smem_dst, const void *gsrc) {
     asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(d), "l"(gsrc) : "memory");
 }
 
-// one staged 256-weight block of all T token images
-//   act [T][GEMM_TOK_STRIDE] uint4 : Q4_K / Q6_K: entry 4u+kk = activation bytes a_kk of unit u; Q8_0: entry 2u+kk
-//   aux [T][32] bytes              : Q4_K: 8 x i32 32-wide q8 sums; Q6_K: 16 x i16 16-wide sums; Q8_0: 8 x f32 d8
-//   d8  [T] f32                    : Q4_K / Q6_K block scale
-__host__ __device__ inline size_t gemm_img_bytes(int T) { return (size_t)T * (GEMM_TOK_STRIDE * 16 + 32 + 4); }
 struct ImgSmem {
     uint4 *act;
     uint8_t *aux;
@@ -92,30 +123,31 @@ __device__ __forceinline__ ImgSmem img_carve(uint8_t *base, int T) {
     return s;
 }
 
-// copy block b of every token's image into a staging buffer (cp.async, all threads)
-template <int TYPE>
-__device__ __forceinline__ void stage_images(const ImgSmem &s, const uint8_t *images, size_t img_stride, int k, int T, int b, int nthreads) {
-    const int U = TYPE == T_Q8_0 ? k / 32 : k / 64;
-    for (int idx = threadIdx.x; idx < T * 16; idx += nthreads) {
-        const int t = idx >> 4, e = idx & 15;
-        const uint4 *act = reinterpret_cast<const uint4 *>(images + (size_t)t * img_stride);
-        const uint4 *src = TYPE == T_Q8_0 ? act + (size_t)(e & 1) * U + 8 * b + (e >> 1)   // [blk][kk]
-                                          : act + (size_t)(e & 3) * U + 4 * b + (e >> 2);  // [unit][kk]
-        cp16(s.act + t * GEMM_TOK_STRIDE + e, src);
-    }
-    for (int idx = threadIdx.x; idx < T * 2; idx += nthreads) {
-        const int t = idx >> 1, h = idx & 1;
-        const uint8_t *aux = images + (size_t)t * img_stride + k;
-        // Q8_0: eight f32 block scales (behind the k/8 aux bytes); K-quants: the block's 32 bytes of sub-block sums
-        if (TYPE == T_Q8_0) cp16(s.aux + t * 32 + h * 16, aux + k / 8 + (size_t)(8 * b + h * 4) * 4);
-        else cp16(s.aux + t * 32 + h * 16, aux + (size_t)b * 32 + h * 16);
-    }
-    if (TYPE != T_Q8_0) {
-        for (int t = threadIdx.x; t < T; t += nthreads) {
-            const uint8_t *aux = images + (size_t)t * img_stride + k;
-            cp4(s.d8 + t, aux + k / 8 + (size_t)b * 4);
-        }
-    }
+// ---- bulk copy of one staged record (one thread) + mbarrier completion
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t *bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "GQ_WAIT_LOOP:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra GQ_WAIT_DONE;\n"
+        "bra GQ_WAIT_LOOP;\n"
+        "GQ_WAIT_DONE:\n"
+        "}\n" ::"r"(smem_u32(bar)), "r"(parity)
+        : "memory");
+}
+// this GPU's own memory -> this CTA's shared memory (no multicast)
+__device__ __forceinline__ void bulk_g2s(void *smem_dst, const void *gsrc, uint32_t bytes, uint64_t *bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(smem_dst)),
+                 "l"(gsrc), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
 }
 
 // Weight side of a stage: the 256-weight block b of GEMM_ROWS rows, copied plane by plane with 16-byte cp.async
@@ -186,7 +218,6 @@ __device__ __forceinline__ void gemm_body(const GemmParams &p, int seg, uint8_t 
     const WPlanes &W = p.seg[seg];
     const int k = W.k, N = W.n_rows;
     const int nb = k / 256;
-    const size_t img_stride = gemm_image_stride(k);
     const int row0 = ((int)blockIdx.x - p.tile_begin[seg]) * GEMM_ROWS;
     const int ra = rg * 16 + g, rb = ra + 8;  // my two rows inside the CTA's tile
     const int tok0 = tg * 8 * NT;             // first token of my token group
@@ -197,11 +228,23 @@ __device__ __forceinline__ void gemm_body(const GemmParams &p, int seg, uint8_t 
 #pragma unroll
         for (int e = 0; e < 4; e++) acc[j][e] = 0.0;
 
+    // the images' staged records (quant_rows_kernel) sit behind the T per-token images
+    const uint8_t *staged = p.images[seg] + gemm_staged_offset(k, T);
+    const uint32_t rec_bytes = (uint32_t)gemm_img_bytes(T);
+    __shared__ __align__(8) uint64_t full[GEMM_STAGES];
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < GEMM_STAGES; i++) mbar_init(&full[i], 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    __syncthreads();
     auto stage = [&](int b) {
         uint8_t *base = smem + (size_t)(b % GEMM_STAGES) * stage_bytes;
         stage_weights<TYPE, GEMM_ROWS>(base, W, row0, b, NTHREADS);
-        stage_images<TYPE>(img_carve(base + GEMM_A_BYTES, T), p.images[seg], img_stride, k, T, b, NTHREADS);
         asm volatile("cp.async.commit_group;" ::: "memory");
+        if (threadIdx.x == 0) {  // the block's activation record: one bulk copy
+            mbar_arrive_expect_tx(&full[b % GEMM_STAGES], rec_bytes);
+            bulk_g2s(base + GEMM_A_BYTES, staged + (size_t)b * rec_bytes, rec_bytes, &full[b % GEMM_STAGES]);
+        }
     };
     stage(0);
     for (int b = 0; b < nb; b++) {
@@ -211,6 +254,7 @@ __device__ __forceinline__ void gemm_body(const GemmParams &p, int seg, uint8_t 
         } else {
             asm volatile("cp.async.wait_group 0;" ::: "memory");
         }
+        mbar_wait(&full[b % GEMM_STAGES], (uint32_t)(b / GEMM_STAGES) & 1u);
         __syncthreads();
         const uint8_t *base = smem + (size_t)(b % GEMM_STAGES) * stage_bytes;
         const uint4 *p0 = reinterpret_cast<const uint4 *>(base), *p1 = p0 + GEMM_ROWS * RS;
