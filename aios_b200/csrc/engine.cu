@@ -433,7 +433,7 @@ void Seq::build_token_pass(bool want_logits, std::vector<PassLaunch> &ls) {
             p.n_seg = 2; p.epi = EPI_SWIGLU; p.k = hp.n_embd;
             p.seg[0] = L.w_gate.w; p.seg[1] = L.w_up.w; p.out[0] = h.as<float>();
             p.x = x.as<float>(); p.norm_w = L.ffn_norm.as<float>(); p.eps = hp.rms_eps;
-            add_gemv(p, pdl && !tp);
+            add_gemv(p, pdl && (!tp || tp_pdl_wait));
         }
         {   // down projection + residual add
             GemvParams p{};
@@ -455,7 +455,7 @@ void Seq::build_token_pass(bool want_logits, std::vector<PassLaunch> &ls) {
             ls.back().g.push = tp_push_logits;
         }
     }
-    if (tp)  // the first launch of a layer follows the all-reduce's add kernel, which is no PDL primary either
+    if (tp && !tp_pdl_wait)  // the launch after an all-reduce follows NCCL's / a plain add kernel: no PDL primary
         for (size_t i = 1; i < ls.size(); i++)
             if (ls[i - 1].reduce_after) ls[i].pdl = false;
 }

@@ -182,6 +182,7 @@ struct Seq {
     // the token pass in pieces, for the tensor-parallel driver (tp.cu), which runs the ranks' lists in lockstep
     DevBuf tp_part64;  // [n_embd] doubles, tensor-parallel shards only
     TpPush tp_push{};  // n > 0: the K-split projections push their partials to the peers (EPI_PUSH_F64) instead
+    bool tp_pdl_wait = false;  // the kernel after a pushed all-reduce is a programmatic dependent of the wait kernel
     TpPush tp_push_logits{};  // ... and the lm_head its slice of the logits (EPI_PUSH_F32)
     void launch_embed(bool from_prompt, int prompt_idx, int pos_value, cudaStream_t st);
     void build_token_pass(bool want_logits, std::vector<PassLaunch> &ls);

@@ -81,6 +81,10 @@ __global__ void tp_tick_kernel(unsigned *tick) { *tick = *tick + 1u; }
 // another GPU) must not hang this one: after ~2 s the kernel gives up and raises *err, which the host checks.
 __global__ void tp_wait_add_kernel(float *x, const double *slabs, const unsigned *flags, const unsigned *tick, int per_token,
                                    int index, int n, int E, unsigned *err) {
+    // Launched as a programmatic dependent of the GEMV that pushes (its CTAs come up as the GEMV's CTAs leave, and spin
+    // on the flags instead of sitting in the launch queue), and the next GEMV is a dependent of this kernel: it may
+    // start fetching its first weights right away and blocks in its own griddepcontrol.wait until x is updated.
+    asm volatile("griddepcontrol.launch_dependents;");
     const unsigned ep = __ldcg(tick) * (unsigned)per_token + (unsigned)index;
     if ((int)threadIdx.x < n) {
         const unsigned *f = flags + threadIdx.x * 32;
@@ -95,6 +99,7 @@ __global__ void tp_wait_add_kernel(float *x, const double *slabs, const unsigned
             }
         }
     }
+    asm volatile("griddepcontrol.wait;" ::: "memory");  // this GPU's own GEMV has completely finished
     __syncthreads();
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i < E) {
@@ -122,6 +127,20 @@ __global__ void tp_wait_logits_kernel(const unsigned *flags, const unsigned *tic
         }
     }
 }
+
+void launch_wait_add(float *x, const double *slabs, const unsigned *flags, const unsigned *tick, int per_token, int index, int n,
+                     int E, unsigned *err, cudaStream_t st, bool pdl) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((unsigned)((E + 255) / 256));
+    cfg.blockDim = dim3(256);
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    CUDA_CHECK(cudaLaunchKernelEx(&cfg, tp_wait_add_kernel, x, slabs, flags, tick, per_token, index, n, E, err));
+}
 }  // namespace
 
 struct TpRank {
@@ -141,6 +160,7 @@ struct TpModelImpl {
     int n = 0;
     int n_past = 0;
     bool have_logits = false;
+    bool pdl_wait = false;  // programmatic dependent launch around the wait kernel (push mode, unless AIOS_ENGINE_NO_PDL)
     bool push = false;  // the all-reduce rides in the GEMV epilogue over peer mappings (else: ncclAllReduce)
     void setup_push();
     void check_push_errors();
@@ -201,8 +221,7 @@ void TpModelImpl::all_reduce_add_to_x(int reduce_index) {
         const int per_token = 2 * hp().n_layer;
         for (auto &r : ranks) {
             r.eng->make_current();
-            tp_wait_add_kernel<<<(E + 255) / 256, 256, 0, r.eng->stream>>>(r.seq->x.as<float>(), r.slabs, r.flags, r.tick, per_token,
-                                                                          reduce_index, n, E, r.err);
+            launch_wait_add(r.seq->x.as<float>(), r.slabs, r.flags, r.tick, per_token, reduce_index, n, E, r.err, r.eng->stream, pdl_wait);
         }
     } else {
         nccl_check(nccl().GroupStart(), "ncclGroupStart");
@@ -284,6 +303,8 @@ void TpModelImpl::setup_push() {
         L.index = 0;
     }
     push = true;
+    pdl_wait = !(ranks[0].eng->flags & AIOS_ENGINE_NO_PDL) && !getenv("AIOS_TP_NO_PDL_WAIT");
+    for (auto &r : ranks) r.seq->tp_pdl_wait = pdl_wait;
     use_graphs = !(ranks[0].eng->flags & AIOS_ENGINE_NO_GRAPH);
 }
 
@@ -366,7 +387,7 @@ void TpModelImpl::rank_step(int r, const aios_sampling &sp, int *launches) {
     for (PassLaunch &L : lists[(size_t)r]) {
         R.seq->launch_pass_item(L, st, li++);
         if (L.reduce_after) {
-            tp_wait_add_kernel<<<(E + 255) / 256, 256, 0, st>>>(R.seq->x.as<float>(), R.slabs, R.flags, R.tick, per_token, n_reduce++, n, E, R.err);
+            launch_wait_add(R.seq->x.as<float>(), R.slabs, R.flags, R.tick, per_token, n_reduce++, n, E, R.err, st, pdl_wait);
             li++;
         }
     }
