@@ -618,13 +618,14 @@ def main():
         fits = ig["us_gemv"] <= us_token * 1.05 and ig["us_token"] <= us_token * 1.25
         traffic = recorded_traffic()
         line = {
-            "metric": METRIC, "value": value, "unit": "tok/s", "n_gpus": world, "steps": args.steps,
+            "metric": METRIC if (args.arch, args.ftype) == ("mistral-7b", "Q4_K_M") and n_ctx == 512
+            else f"{args.arch} {args.ftype} decode tok/s (bs1, ctx{n_ctx})", "value": value, "unit": "tok/s", "n_gpus": world, "steps": args.steps,
             "warmup": max(args.warmup, 3), "ms_per_step": dev_ms_max / args.steps, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "int8 x q4/q6 integer dots, f32/f64 accumulate",
             "data": "synthetic", "parity_checked": bool(parity), "parity_tokens": parity,
             "config": {"workload": f"{args.arch} {args.ftype} batch-1 greedy decode, {args.prompt}-token prompt + "
                                    f"{args.gen} generated = {n_ctx}-token context (BASELINE.json configs[1])",
-                       "tokens_per_step": args.gen, "l2": "inputs larger than L2 (4.29 GB weights per token vs 126 MB)",
+                       "tokens_per_step": args.gen, "l2": f"inputs larger than L2 ({info.weight_bytes_per_token / 1e9:.2f} GB weights per token vs 126 MB)",
                        "parallelism": f"replicas x{world} (no collective)", "seed": SEED,
                        "bytes_per_token": bytes_per_token, "timing": "CUDA events on the engine stream, summed over steps",
                        "wall_ms_per_step": wall_ms_max / args.steps},
