@@ -104,6 +104,8 @@ SYMBOLS = {
     "aios_tokenize": (C.c_int, [_P, C.c_char_p, C.c_int32, C.c_int32, _P, C.c_int32, C.POINTER(C.c_int32)]),
     "aios_detokenize": (C.c_int, [_P, _P, C.c_int32, C.c_int32, _P, C.c_int32, C.POINTER(C.c_int32)]),
     "aios_chat_prompt": (C.c_int, [_P, C.c_char_p, C.c_char_p, _P, C.c_int32, C.POINTER(C.c_int32)]),
+    "aios_chat_apply_template": (C.c_int, [_P, C.POINTER(C.c_char_p), C.POINTER(C.c_char_p), C.c_int32, C.c_int32, _P, C.c_int32,
+                                          C.POINTER(C.c_int32)]),
     "aios_token_is_eog": (C.c_int, [_P, C.c_int32, C.POINTER(C.c_int32)]),
     "aios_seq_create": (C.c_int, [_P, C.POINTER(_P)]),
     "aios_seq_free": (None, [_P]),
@@ -252,6 +254,16 @@ class Vocab:
     def chat_prompt(self, system_prompt: str, user_prompt: str) -> str:
         return _bytes_out(lambda b, c, l: lib().aios_chat_prompt(
             self.h, (system_prompt or "").encode("utf-8"), user_prompt.encode("utf-8"), b, c, l)).decode("utf-8", "replace")
+
+    def apply_chat_template(self, messages, add_generation_prompt: bool = True) -> str:
+        """messages: [(role, content)] or [{"role":…, "content":…}] through the file's tokenizer.chat_template
+        (AiosError E_UNSUPPORTED if the template is outside the supported Jinja subset or raises, E_STATE without one)."""
+        pairs = [(m["role"], m["content"]) if isinstance(m, dict) else tuple(m) for m in messages]
+        n = len(pairs)
+        roles = (C.c_char_p * max(n, 1))(*[r.encode("utf-8") for r, _ in pairs])
+        contents = (C.c_char_p * max(n, 1))(*[c.encode("utf-8") for _, c in pairs])
+        gen = 1 if add_generation_prompt else 0
+        return _bytes_out(lambda buf, cap, ln: lib().aios_chat_apply_template(self.h, roles, contents, n, gen, buf, cap, ln)).decode("utf-8")
 
     def is_eog(self, token: int) -> bool:
         r = C.c_int32(0)

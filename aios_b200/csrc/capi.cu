@@ -522,6 +522,22 @@ int aios_chat_prompt(aios_vocab *v, const char *system_prompt, const char *user_
     });
 }
 
+int aios_chat_apply_template(aios_vocab *v, const char *const *roles, const char *const *contents, int32_t n_messages,
+                             int32_t add_generation_prompt, char *buf, int32_t cap, int32_t *len) {
+    return guarded([&] {
+        if (!v || !len || n_messages < 0 || (n_messages > 0 && (!roles || !contents))) return fail(AIOS_E_INVAL, "null argument");
+        if (v->tok.chat_template().empty()) return fail(AIOS_E_STATE, "the GGUF file carries no tokenizer.chat_template");
+        std::vector<std::pair<std::string, std::string>> msgs;
+        for (int32_t i = 0; i < n_messages; i++) {
+            if (!roles[i] || !contents[i]) return fail(AIOS_E_INVAL, "null message");
+            msgs.emplace_back(roles[i], contents[i]);
+        }
+        std::string out, err;
+        if (!v->tok.apply_template(msgs, add_generation_prompt != 0, &out, &err)) return fail(AIOS_E_UNSUPPORTED, "chat template: " + err);
+        return put_bytes(out, buf, cap, len);
+    });
+}
+
 int aios_token_is_eog(aios_vocab *v, int32_t id, int32_t *is_eog) {
     return guarded([&] {
         if (!v || !is_eog) return fail(AIOS_E_INVAL, "null argument");

@@ -7,6 +7,7 @@
 #include <queue>
 
 #include "gguf.h"
+#include "jinja_lite.h"
 #include "unicode_tables.h"
 
 namespace aios {
@@ -213,6 +214,7 @@ Tokenizer::Tokenizer(const GgufFile &f) {
 
     // chat format from the marker strings of tokenizer.chat_template; chatml when there is none
     const std::string t = f.get_s("tokenizer.chat_template", "");
+    template_ = t;
     auto has = [&](const char *s) { return t.find(s) != std::string::npos; };
     if (has("<|im_start|>")) format_ = CHAT_CHATML;
     else if (has("<|start_header_id|>")) format_ = CHAT_LLAMA3;
@@ -455,7 +457,30 @@ std::string Tokenizer::decode(const int32_t *ids, int32_t n, bool render_special
     return s;
 }
 
+bool Tokenizer::apply_template(const std::vector<std::pair<std::string, std::string>> &messages, bool add_generation_prompt,
+                               std::string *out, std::string *err) const {
+    if (template_.empty()) {
+        if (err) *err = "the file has no tokenizer.chat_template";
+        return false;
+    }
+    std::vector<ChatMessage> msgs;
+    for (const auto &m : messages) msgs.push_back({m.first, m.second});
+    const std::string bos_text = bos_ >= 0 && bos_ < n_tokens() ? pieces_[bos_] : std::string();
+    const std::string eos_text = eos_ >= 0 && eos_ < n_tokens() ? pieces_[eos_] : std::string();
+    if (!render_chat_template(template_, msgs, bos_text, eos_text, add_generation_prompt, out, err)) return false;
+    // the tokenizer prepends BOS itself (add_special): a BOS string the template emits first would make it two
+    if (add_bos_ && !bos_text.empty() && out->compare(0, bos_text.size(), bos_text) == 0) out->erase(0, bos_text.size());
+    return true;
+}
+
 std::string Tokenizer::chat_prompt(const std::string &system, const std::string &user) const {
+    {
+        std::vector<std::pair<std::string, std::string>> msgs;
+        if (!system.empty()) msgs.emplace_back("system", system);
+        msgs.emplace_back("user", user);
+        std::string rendered, err;
+        if (apply_template(msgs, true, &rendered, &err)) return rendered;
+    }
     std::string s;
     const std::string eos_text = eos_ >= 0 && eos_ < n_tokens() ? pieces_[eos_] : std::string("</s>");
     switch (format_) {

@@ -37,8 +37,13 @@ class Tokenizer {
     std::string decode(const int32_t *ids, int32_t n, bool render_special, bool strip_space) const;
     std::string piece_text(int32_t id, bool render_special) const;
 
-    // the {system,user} message list of inference.rs:363-376 rendered for generation
+    // the {system,user} message list of inference.rs:363-376 rendered for generation: the file's own template
+    // (jinja_lite.h) when it can be evaluated, else the format recognised by marker strings
     std::string chat_prompt(const std::string &system, const std::string &user) const;
+    // messages through tokenizer.chat_template only; false + *err when there is none or it cannot be evaluated
+    bool apply_template(const std::vector<std::pair<std::string, std::string>> &messages, bool add_generation_prompt,
+                        std::string *out, std::string *err) const;
+    const std::string &chat_template() const { return template_; }
     ChatFormat chat_format() const { return format_; }
     // end-of-generation tokens: eos plus the turn terminators present in the vocabulary
     bool is_eog(int32_t id) const;
@@ -73,6 +78,7 @@ class Tokenizer {
     int pre_ = 0;  // 0: GPT-2 pattern, 1: Llama-3 pattern
     std::unordered_map<std::string, int32_t> merge_rank_;  // "left right" -> rank
     ChatFormat format_ = CHAT_CHATML;
+    std::string template_;  // tokenizer.chat_template
 };
 
 }  // namespace aios

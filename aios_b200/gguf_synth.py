@@ -47,6 +47,10 @@ class Arch:
     n_ctx_train: int = 4096
 
 
+# the ChatML template as model cards carry it in tokenizer.chat_template
+CHATML_TEMPLATE = ("{% for message in messages %}{{'<|im_start|>' + message['role'] + '\\n' + message['content'] + '<|im_end|>' + '\\n'}}"
+                   "{% endfor %}{% if add_generation_prompt %}{{ '<|im_start|>assistant\\n' }}{% endif %}")
+
 ARCHS = {
     # tiny shapes for CPU-speed parity tests (K multiples of 256 as K-quants require)
     "tiny": Arch("tiny", 2, 256, 4, 2, 64, 512, 512, 10000.0, 1e-5, 512),

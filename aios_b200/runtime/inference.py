@@ -47,6 +47,9 @@ class InferParams:
     task_id: str = ""
     seed: Optional[int] = None  # not on the wire; tests pin it
     json_mode: bool = False     # response_format json_object: what unary Infer always asks for (inference.rs:119-121)
+    # the whole conversation, when the caller has one (the OpenAI-compatible endpoint): [(role, content)], rendered by
+    # the model's own chat template; prompt / system_prompt are then only the fallback
+    messages: Optional[list] = None
 
 
 @dataclass
@@ -298,7 +301,14 @@ class InferenceEngine:
 
     # -- what llama-server did before the forward passes: template + tokenize
     def _prepare(self, lm: LoadedModel, p: InferParams):
-        text = lm.vocab.chat_prompt(p.system_prompt, p.prompt)
+        text = None
+        if p.messages and hasattr(lm.vocab, "apply_chat_template"):
+            try:
+                text = lm.vocab.apply_chat_template(p.messages, True)
+            except Exception:  # no template in the file, outside the supported subset, or the template raised
+                text = None
+        if text is None:
+            text = lm.vocab.chat_prompt(p.system_prompt, p.prompt)
         tokens = lm.vocab.tokenize(text, add_special=True, parse_special=True)
         if tokens.size >= lm.n_ctx:
             raise RuntimeError(f"the request exceeds the available context size ({tokens.size} prompt tokens, "

@@ -39,9 +39,12 @@ def _messages_to_params(body: dict) -> InferParams:
     if not users:
         raise ValueError("no message with role 'user'")
     rf = body.get("response_format")
+    # the conversation as sent goes through the model's chat template; (system, last user turn) is the fallback
+    convo = [(str(m.get("role", "")), str(m.get("content", "") or "")) for m in msgs if isinstance(m, dict)]
     return InferParams(prompt=str(users[-1]), system_prompt=str(system or ""), max_tokens=int(body.get("max_tokens") or 0),
                        temperature=float(body.get("temperature") or 0.0), seed=body.get("seed"),
-                       json_mode=isinstance(rf, dict) and rf.get("type") == "json_object")
+                       json_mode=isinstance(rf, dict) and rf.get("type") == "json_object",
+                       messages=convo if len(convo) == len(msgs) else None)
 
 
 class OpenAIServer:

@@ -142,10 +142,18 @@ int aios_vocab_token_piece(aios_vocab *v, int32_t id, char *buf, int32_t cap, in
 /* text_len < 0: text is NUL-terminated */
 int aios_tokenize(aios_vocab *v, const char *text, int32_t text_len, int32_t flags, int32_t *out, int32_t cap, int32_t *n_out);
 int aios_detokenize(aios_vocab *v, const int32_t *tokens, int32_t n, int32_t flags, char *buf, int32_t cap, int32_t *len);
-/* [system?, user] rendered in the model's chat format (recognised from tokenizer.chat_template by its marker
- * strings: chatml, llama-2, mistral, zephyr, llama-3; chatml when there is none) and ending with the assistant
- * header, ready for aios_tokenize(ADD_SPECIAL|PARSE_SPECIAL).  system_prompt may be NULL or "". */
+/* [system?, user] (the message list of runtime/src/inference.rs:363-376) rendered for generation, ready for
+ * aios_tokenize(ADD_SPECIAL|PARSE_SPECIAL).  First the file's own tokenizer.chat_template is evaluated (a Jinja subset:
+ * csrc/jinja_lite.h); if the template uses something outside that subset or raises (Mistral's refuses a system role),
+ * the format recognised from its marker strings is used instead (chatml, llama-2, mistral, zephyr, llama-3; chatml when
+ * the file has no template).  A BOS string the template itself emits is dropped when the tokenizer adds BOS anyway.
+ * system_prompt may be NULL or "". */
 int aios_chat_prompt(aios_vocab *v, const char *system_prompt, const char *user_prompt, char *buf, int32_t cap, int32_t *len);
+/* any message list through tokenizer.chat_template only (what the OpenAI-compatible endpoint receives,
+ * api-gateway/src/openai.rs:148-165): AIOS_E_STATE if the file has no template, AIOS_E_UNSUPPORTED (message in
+ * aios_last_error) if the template is outside the supported subset or raises for these messages. */
+int aios_chat_apply_template(aios_vocab *v, const char *const *roles, const char *const *contents, int32_t n_messages,
+                             int32_t add_generation_prompt, char *buf, int32_t cap, int32_t *len);
 /* 1 if id ends generation: tokenizer.ggml.eos_token_id or a turn terminator (<|im_end|>, <|eot_id|>, ...) */
 int aios_token_is_eog(aios_vocab *v, int32_t id, int32_t *is_eog);
 

@@ -117,3 +117,18 @@ def test_runtime_server_serves_models_on_their_ports(vocab_gguf, tmp_path):  # n
             urllib.request.urlopen(f"http://127.0.0.1:{free_port}/health", timeout=2)
     finally:
         srv.stop(0)
+
+
+def test_whole_conversation_goes_through_the_chat_template(http):
+    """A multi-turn message list is rendered by the model's own tokenizer.chat_template (aios_chat_apply_template), not
+    cut down to (system, last user turn): the prompt the scripted model is fed has the length of the full rendering."""
+    url, lm = http
+    body = {"messages": [{"role": "user", "content": "a"}, {"role": "assistant", "content": "beta"},
+                         {"role": "user", "content": "c"}], "max_tokens": 64, "temperature": 0.2}
+    with _post(url, body) as r:
+        obj = json.load(r)
+    want = lm.vocab.apply_chat_template([("user", "a"), ("assistant", "beta"), ("user", "c")])
+    assert obj["usage"]["prompt_tokens"] == lm.vocab.tokenize(want, add_special=True, parse_special=True).size
+    assert obj["usage"]["prompt_tokens"] > lm.vocab.tokenize(lm.vocab.chat_prompt("", "c"), parse_special=True).size
+    assert want == ("<|im_start|>user\na<|im_end|>\n<|im_start|>assistant\nbeta<|im_end|>\n<|im_start|>user\nc<|im_end|>\n"
+                    "<|im_start|>assistant\n")

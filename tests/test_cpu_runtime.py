@@ -42,7 +42,7 @@ def vocab_gguf(tmp_path_factory, spm_golden):
     arch = dataclasses.replace(gguf_synth.ARCHS["tiny"], n_vocab=len(vocab) + 6)
     path = str(d / "tinyllama-1.1b-chat.gguf")
     gguf_synth.write_synthetic_gguf(path, arch, vocab=vocab,
-                                    chat_template="{% for m in messages %}<|im_start|>{{m.role}}…<|im_end|>{% endfor %}")
+                                    chat_template=gguf_synth.CHATML_TEMPLATE)
     return path
 
 
@@ -246,6 +246,74 @@ def test_llama3_chat_prompt(bpe_golden, tmp_path):
                     "<|start_header_id|>assistant<|end_header_id|>\n\n")
     ids = v.tokenize(text, add_special=True, parse_special=True).tolist()
     assert ids[0] == 0 and ids[1] == 3 and ids.count(3) == 3 and ids.count(4) == 3 and ids.count(2) == 2
+
+
+# ------------------------------------------------------------------ tokenizer.chat_template evaluated (jinja_lite)
+def test_chat_templates_match_jinja2(spm_golden, tmp_path):  # noqa: F811
+    """Every golden rendering (five real-world template shapes + two synthetic ones x five conversations x with/without
+    the generation prompt) matches what the jinja2 package produced; where jinja2 raised (raise_exception in the
+    template), aios_chat_apply_template answers AIOS_E_UNSUPPORTED."""
+    with open(os.path.join(HERE, "golden", "chat_templates.json"), encoding="utf-8") as f:
+        g = json.load(f)
+    vocab = [tuple(v) for v in spm_golden["vocab"]]
+    arch = dataclasses.replace(gguf_synth.ARCHS["tiny"], n_vocab=len(vocab) + 6)
+    n_ok = n_raise = 0
+    for tname, src in g["templates"].items():
+        path = str(tmp_path / f"tmpl-{tname}.gguf")
+        # add_bos_token is on (SPM default): give the template an empty-looking BOS so that nothing is stripped here
+        gguf_synth.write_synthetic_gguf(path, arch, vocab=vocab, chat_template=src)
+        v = capi.Vocab.open(path)
+        bos, eos = v.detokenize([1], render_special=True).decode(), v.detokenize([2], render_special=True).decode()
+        assert (bos, eos) == ("<s>", "</s>")
+        for case in (c for c in g["cases"] if c["template"] == tname):
+            msgs = g["conversations"][case["conversation"]]
+            want = case["expected"]
+            if want is None:
+                with pytest.raises(capi.AiosError) as e:
+                    v.apply_chat_template(msgs, case["add_generation_prompt"])
+                assert e.value.code == capi.E_UNSUPPORTED
+                n_raise += 1
+                continue
+            got = v.apply_chat_template(msgs, case["add_generation_prompt"])
+            if want.startswith("<s>"):
+                want = want[3:]  # the tokenizer adds BOS itself: a leading BOS string from the template is dropped
+            assert got == want, (tname, case["conversation"], case["add_generation_prompt"], got, want)
+            n_ok += 1
+        v.close()
+    assert n_ok >= 60 and n_raise >= 8
+
+
+def test_chat_prompt_prefers_the_files_template(spm_golden, tmp_path):  # noqa: F811
+    vocab = [tuple(v) for v in spm_golden["vocab"]]
+    arch = dataclasses.replace(gguf_synth.ARCHS["tiny"], n_vocab=len(vocab) + 6)
+
+    def vocab_with(template):
+        path = str(tmp_path / f"t{abs(hash(template))}.gguf")
+        gguf_synth.write_synthetic_gguf(path, arch, vocab=vocab, chat_template=template)
+        return capi.Vocab.open(path)
+
+    # a template nobody's marker list knows: rendered as written
+    v = vocab_with("{% for m in messages %}<{{ m.role }}>{{ m.content }}</{{ m.role }}>{% endfor %}<bot>")
+    assert v.chat_prompt("S", "U") == "<system>S</system><user>U</user><bot>"
+    assert v.chat_prompt("", "U") == "<user>U</user><bot>"
+    # Mistral's template refuses a system role: the recognised [INST] format takes over (system text inside the turn)
+    with open(os.path.join(HERE, "golden", "chat_templates.json"), encoding="utf-8") as f:
+        mistral = json.load(f)["templates"]["mistral-v0.2"]
+    v = vocab_with(mistral)
+    assert v.chat_prompt("", "U") == "[INST] U [/INST]"
+    assert v.chat_prompt("S", "U") == "[INST] S\n\nU [/INST]"
+    # outside the subset (a macro): the marker-string format again, and the direct call says why
+    v = vocab_with("{% macro f(x) %}{{ x }}{% endmacro %}<|im_start|>{{ f(messages[0].content) }}")
+    assert v.chat_prompt("", "U") == "<|im_start|>user\nU<|im_end|>\n<|im_start|>assistant\n"
+    with pytest.raises(capi.AiosError, match="macro"):
+        v.apply_chat_template([("user", "U")])
+    # no template at all
+    path = str(tmp_path / "none.gguf")
+    gguf_synth.write_synthetic_gguf(path, arch, vocab=vocab)
+    v = capi.Vocab.open(path)
+    with pytest.raises(capi.AiosError) as e:
+        v.apply_chat_template([("user", "U")])
+    assert e.value.code == capi.E_STATE
 
 
 # ------------------------------------------------------------------ model_manager.rs:556-712 restated

@@ -30,7 +30,7 @@ def chat_gguf(tmp_path_factory):
     arch = dataclasses.replace(gguf_synth.ARCHS["tiny"], n_vocab=len(vocab) + 6)
     d = tmp_path_factory.mktemp("chat")
     path = str(d / "tinyllama-1.1b-synthetic.gguf")
-    gguf_synth.write_synthetic_gguf(path, arch, vocab=vocab, chat_template="<|im_start|> chatml <|im_end|>")
+    gguf_synth.write_synthetic_gguf(path, arch, vocab=vocab, chat_template=gguf_synth.CHATML_TEMPLATE)
     return path
 
 

@@ -97,7 +97,7 @@ def test_runtime_serves_a_tensor_parallel_model(tmp_path):
     n_vocab = (len(vocab) + 7) // 2 * 2
     arch = dataclasses.replace(gs.ARCHS["tiny-gqa4"], n_vocab=n_vocab)
     path = str(tmp_path / "llama-3-70b-synthetic.gguf")
-    gs.write_synthetic_gguf(path, arch, vocab=vocab, chat_template="<|im_start|> chatml <|im_end|>")
+    gs.write_synthetic_gguf(path, arch, vocab=vocab, chat_template=gs.CHATML_TEMPLATE)
     p = InferParams(prompt="Hello, world!", system_prompt="Be brief.", max_tokens=24, temperature=0.8, seed=7)
     eng = InferenceEngine(stream_chunk_tokens=4)
     one = EngineBackend(device=0)
