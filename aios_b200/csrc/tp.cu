@@ -14,8 +14,12 @@
 // chance per value that a double sum's association moves the final rounding).  Every rank then samples from the same
 // full logits with the same deterministic sampler: no broadcast of the token is needed.
 //
-// This is the plain-NCCL baseline (2 x n_layer latency-bound all-reduces of n_embd doubles per token, launched eagerly,
-// no CUDA graph); the fused one-shot all-reduce in the attn_output / ffn_down epilogue is the next step.
+// Two transports for those partial sums.  NCCL (the reference behaviour and the fallback without peer access): the GEMV
+// stores its partials locally, ncclAllReduce(ncclDouble) + ncclAllGather per token, launched eagerly.  Push (default):
+// the GEMV's epilogue stores every row's partial straight into each rank's receive slab over the NVLink peer mapping
+// and its last CTA raises an arrival flag (EPI_PUSH_F64 / EPI_PUSH_F32, gemv.cu); a small wait kernel, chained to its
+// neighbours by programmatic dependent launch, adds the slabs to the residual.  No host-side collective is left in a
+// decode step, which is then one CUDA graph per rank.  Peer traffic is plain stores and flag loads: no TMA involved.
 #include <dlfcn.h>
 #include <math.h>
 #include <nccl.h>
