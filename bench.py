@@ -478,6 +478,8 @@ def main():
         return
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
+    if world > 1:
+        os.environ["NCCL_DEBUG"] = "WARN"  # NCCL's version banner goes to stdout, where the one JSON line belongs
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
 
     if args.impl == "reference":
