@@ -11,7 +11,8 @@
 // how it is computed, so here the sub-block dots come from `mma.sync` s8 — m16n8k32 for the 32-wide dots of Q4_K and
 // Q8_0, m16n8k16 for the 16-wide dots of Q6_K: one instruction = 16 weight rows x 8 tokens x one sub-block — and the
 // scale arithmetic around them is the GEMV's, per (row, token) pair.  This is why the path is exact and also why it is
-// ALU-bound rather than tensor-bound at T = 64: every (row, token, unit) costs ~12 scalar instructions after the MMA.
+// issue-bound rather than tensor-bound at T = 64: every (row, token, unit) costs ~12 scalar instructions after the MMA
+// (17-20 with the fragment preparation; ncu: 60-70 % of issue slots used, tensor pipe 14 %).
 // The tensor-bound path for long prompts is prefill_tc.cu (tcgen05, float arithmetic, stated tolerance).
 //
 // Activations: `quant_rows_kernel` builds, per token, the same Q8_K / Q8_0 image the GEMV prologue builds in shared
