@@ -562,16 +562,19 @@ void Seq::ensure_graph(const aios_sampling &sp) {
 // chunk by the multi-token GEMM (gemm_q.cu; q/k/v and gate/up as segments of one launch).  Attention still goes token
 // by token through the decode kernel (each token sees the rows before it).  Matrices of other types (Q5_K) fall back
 // to the GEMV, token by token.
-void Seq::prefill_chunk(int idx0, int T, int pos0, bool want_logits, cudaStream_t st) {
+void Seq::prefill_chunk(int idx0, int T, int pos0, bool want_logits, cudaStream_t st, ChunkReduce *reduce) {
     const HParams &hp = m->hp;
     constexpr int CH = GEMM_MAX_TOKENS;
     const int E = hp.n_embd, FF = hp.n_ff, QD = hp.n_head * hp.head_dim, KVD = hp.n_head_kv * hp.head_dim;
     const int LQ = QD + 2 * KVD, Tp = gemm_pad_tokens(T), n_sms = m->eng->n_sms;
     SeqState *sd = state.as<SeqState>();
+    const bool tp = m->tp_size > 1;
+    if (tp && (!reduce || want_logits)) throw std::logic_error("a tensor-parallel shard's chunks are driven by its group (tp.cu)");
     if (!cx.p) {  // first chunk of this sequence: room for CH tokens side by side
         cx = DevBuf((size_t)CH * E * 4); cqkv = DevBuf((size_t)CH * LQ * 4); catt = DevBuf((size_t)CH * QD * 4);
         ch = DevBuf((size_t)CH * FF * 4); cgu = DevBuf((size_t)CH * 2 * FF * 4); cqh = DevBuf((size_t)CH * QD * 2);
         cimg = DevBuf(2 * gemm_images_bytes(std::max(std::max(E, QD), FF), CH)); cpos = DevBuf(CH * 4);
+        if (m->tp_size > 1) cpart = DevBuf((size_t)CH * E * sizeof(double));
         CUDA_CHECK(cudaMemsetAsync(cx.p, 0, cx.bytes, st)); CUDA_CHECK(cudaMemsetAsync(catt.p, 0, catt.bytes, st));
         CUDA_CHECK(cudaMemsetAsync(ch.p, 0, ch.bytes, st));  // rows of padding tokens stay zero (finite images)
     }
@@ -616,6 +619,15 @@ void Seq::prefill_chunk(int idx0, int T, int pos0, bool want_logits, cudaStream_
             }
             g.seg[g.n_seg] = *w; g.out[g.n_seg] = out; g.images[g.n_seg] = img_of_class[pc];
             g.n_seg++;
+        }
+        if (tp && epi == EPI_ADD) {
+            // a K shard of attn_output / ffn_down: f64 partial sums, summed over the ranks, then rounded into the rows
+            if (g.n_seg != 1 || ws.size() != 1) throw CudaError("tensor-parallel chunk: the K-split matrix must take the GEMM path");
+            g.part = cpart.as<double>();
+            launch_gemm_multi(g, st);
+            reduce->all_reduce(cpart.as<double>(), (size_t)T * E, st);
+            launch_add_part_rows(g.out[0], ldo, cpart.as<double>(), E, T, st);
+            return;
         }
         if (g.n_seg) launch_gemm_multi(g, st);
     };

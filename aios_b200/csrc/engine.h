@@ -125,6 +125,13 @@ struct SeqState {  // lives in device memory
     unsigned long long argmax_key;
 };
 
+// Tensor-parallel prompt chunks: what a shard does with the f64 partial sums of a K-split projection — all-reduce them
+// over the ranks in place (tp.cu); the chunk then adds them, rounded once, to the residual rows.
+struct ChunkReduce {
+    virtual void all_reduce(double *part, size_t count, cudaStream_t st) = 0;
+    virtual ~ChunkReduce() = default;
+};
+
 // one launch of the token pass (Seq::build_token_pass)
 struct PassLaunch {
     int kind = 0;  // 0 GEMV, 1 attention
@@ -148,7 +155,7 @@ struct Seq {
     int snap_n_past = -1;
     struct KernelTimer *timer = nullptr;  // non-null only inside profile_decode
     // prompt chunks (prefill_chunk): activations of up to 32 tokens side by side, their quantised images, positions
-    DevBuf cx, cqkv, catt, ch, cgu, cimg, cpos, cqh;
+    DevBuf cx, cqkv, catt, ch, cgu, cimg, cpos, cqh, cpart;
     DevBuf trace;
     DevBuf mask;           // optional logit mask (n_vocab bits), see set_mask
     bool mask_on = false;
@@ -188,10 +195,12 @@ struct Seq {
     void build_token_pass(bool want_logits, std::vector<PassLaunch> &ls);
     void launch_pass_item(PassLaunch &L, cudaStream_t st, int launch_index);
     void launch_sample_kernel(const aios_sampling &sp, cudaStream_t st);
+    // tokens prompt[idx0 .. idx0+T) at positions pos0...; on a tensor-parallel shard `reduce` carries the K-split
+    // projections' partial sums across the ranks and want_logits must be false (the group gathers the logits itself)
+    void prefill_chunk(int idx0, int T, int pos0, bool want_logits, cudaStream_t st, ChunkReduce *reduce = nullptr);
 
    private:
     void launch_token_pass(bool from_prompt, int prompt_idx, int pos_value, bool want_logits, cudaStream_t st, int *n_launch);
-    void prefill_chunk(int idx0, int T, int pos0, bool want_logits, cudaStream_t st);  // tokens prompt[idx0 .. idx0+T)
     void prefill_tc(int idx0, int T, int pos0, bool want_logits, cudaStream_t st);     // the same on the tensor-core path
     void ensure_graph(const aios_sampling &sp);
     void build_pfd();

@@ -205,6 +205,7 @@ struct GemmParams {
     float *out[3];           // [T][ldo]
     const uint8_t *images[3];  // T activation images in the permutation of the segment's type, stride gemm_image_stride(k)
     int64_t ldo;
+    double *part;            // non-null (one segment): part[t * n_rows + row] = the unrounded double sum, out untouched
 };
 
 // the k-loop of one CTA for weight type TYPE
@@ -383,6 +384,10 @@ __device__ __forceinline__ void gemm_body(const GemmParams &p, int seg, uint8_t 
         for (int e = 0; e < 4; e++) {
             const int row = (e & 2) ? row_b : row_a, t = tok0 + 8 * j + 2 * q + (e & 1);
             if (row < N && t < p.T) {
+                if (p.part) {
+                    p.part[(size_t)t * N + row] = acc[j][e];
+                    continue;
+                }
                 float *o = out + (size_t)t * p.ldo + row;
                 const float v = (float)acc[j][e];
                 *o = p.epi == EPI_ADD ? __fadd_rn(*o, v) : v;
@@ -418,6 +423,18 @@ void launch_swiglu_rows(const float *gu, int64_t ldgu, int ff, int T, float *h, 
     CUDA_CHECK(cudaGetLastError());
 }
 
+__global__ void add_part_rows_kernel(float *x, int64_t ldx, const double *part, int n) {
+    const int t = blockIdx.y, i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) {
+        float *o = x + (size_t)t * ldx + i;
+        *o = __fadd_rn(*o, (float)part[(size_t)t * n + i]);
+    }
+}
+void launch_add_part_rows(float *x, int64_t ldx, const double *part, int n, int T, cudaStream_t st) {
+    add_part_rows_kernel<<<dim3((unsigned)((n + 255) / 256), (unsigned)T), 256, 0, st>>>(x, ldx, part, n);
+    CUDA_CHECK(cudaGetLastError());
+}
+
 bool gemm_q_usable(int type, int k) { return (type == T_Q4_K || type == T_Q6_K || type == T_Q8_0) && k % 256 == 0; }
 
 // images of tokens T..pad(T)-1 (padding) must exist (any finite contents); their outputs are not stored.
@@ -434,6 +451,8 @@ void launch_gemm_multi(const GemmMulti &m, cudaStream_t st) {
     if (m.n_seg < 1 || m.n_seg > 3) throw CudaError("launch_gemm: 1..3 segments");
     GemmParams p{};
     p.n_seg = m.n_seg; p.T = m.T; p.epi = m.epi; p.ldo = m.ldo;
+    if (m.part && m.n_seg != 1) throw CudaError("launch_gemm: partial sums need a single segment");
+    p.part = m.part;
     int64_t total_rows = 0;
     for (int i = 0; i < m.n_seg; i++) total_rows += m.seg[i].n_rows;
     // 32-row CTAs when that still gives the machine >= 2 CTAs per SM, else 16-row CTAs (twice as many)

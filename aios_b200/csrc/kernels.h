@@ -103,8 +103,13 @@ struct GemmMulti {
     float *out[3];
     const uint8_t *images[3];
     int64_t ldo;
+    // one segment, tensor-parallel K shards: instead of touching out, store the rows' unrounded double sums to
+    // part[t * n_rows + row] (the partials are all-reduced across the ranks and rounded once, like EPI_STORE_F64)
+    double *part = nullptr;
 };
 void launch_gemm_multi(const GemmMulti &m, cudaStream_t st);
+// x[t][i] += (float) part[t * n + i]   (t < T): the all-reduced partials of a K-split GEMM, rounded once
+void launch_add_part_rows(float *x, int64_t ldx, const double *part, int n, int T, cudaStream_t st);
 // h[t][0..ff) = silu(gu[t][0..ff)) * gu[t][ff..2ff)
 void launch_swiglu_rows(const float *gu, int64_t ldgu, int ff, int T, float *h, int64_t ldh, cudaStream_t st);
 

@@ -25,7 +25,9 @@
 #include <nccl.h>
 #include <string.h>
 
+#include <exception>
 #include <mutex>
+#include <thread>
 
 #include <algorithm>
 #include <memory>
@@ -196,6 +198,9 @@ struct TpModelImpl {
     void all_reduce_add_to_x(int reduce_index);
     // one token through every rank's shard in lockstep; launches counts rank 0's kernels (collectives included)
     void token_pass(bool from_prompt, int prompt_idx, int pos_value, bool want_logits, int *launches);
+    void gather_logits();
+    bool chunks_usable() const;
+    void prefill_chunks(int n_tokens);  // tokens already in every rank's prompt buffer; asynchronous on the streams
     void sample_all(const aios_sampling &sp);
     void sync_all();
     void set_pos_step();
@@ -348,24 +353,91 @@ void TpModelImpl::token_pass(bool from_prompt, int prompt_idx, int pos_value, bo
             li += push ? 1 : 2;
         }
     }
-    if (want_logits && push) {
+    if (want_logits) {
+        gather_logits();
+        li++;
+    }
+    if (launches) *launches += li;
+}
+
+// after the lm_head launches: every rank ends up with every slice of the logits
+void TpModelImpl::gather_logits() {
+    if (push) {  // the slices were pushed by the lm_head's epilogue: wait for the arrival flags
         for (auto &R : ranks) {
             R.eng->make_current();
             tp_wait_logits_kernel<<<1, 32, 0, R.eng->stream>>>(R.lflags, R.tick, n, R.err);
         }
-        li++;
-    } else if (want_logits) {  // every rank gets every slice of the logits (in place: rank r's slice already sits at r * vocab_local)
-        const size_t vl = (size_t)ranks[0].model->vocab_local;
-        nccl_check(nccl().GroupStart(), "ncclGroupStart");
-        for (int r = 0; r < n; r++) {
-            TpRank &R = ranks[(size_t)r];
-            float *lg = R.seq->logits.as<float>();
-            nccl_check(nccl().AllGather(lg + (size_t)r * vl, lg, vl, ncclFloat, R.comm, R.eng->stream), "ncclAllGather");
-        }
-        nccl_check(nccl().GroupEnd(), "ncclGroupEnd");
-        li++;
+        return;
     }
-    if (launches) *launches += li;
+    // in place: rank r's slice already sits at r * vocab_local
+    const size_t vl = (size_t)ranks[0].model->vocab_local;
+    nccl_check(nccl().GroupStart(), "ncclGroupStart");
+    for (int r = 0; r < n; r++) {
+        TpRank &R = ranks[(size_t)r];
+        float *lg = R.seq->logits.as<float>();
+        nccl_check(nccl().AllGather(lg + (size_t)r * vl, lg, vl, ncclFloat, R.comm, R.eng->stream), "ncclAllGather");
+    }
+    nccl_check(nccl().GroupEnd(), "ncclGroupEnd");
+}
+
+// Prompt chunks of up to 64 tokens (Seq::prefill_chunk on every shard: the multi-token GEMM streams each shard's
+// weights once per chunk instead of once per token).  One host thread per rank, because a chunk is a long sequence of
+// launches with an all-reduce after every K-split projection: each thread enqueues its rank's share, NCCL pairs the
+// all-reduces up on the devices ([T][n_embd] doubles each: bandwidth-sized, unlike the decode step's).
+bool TpModelImpl::chunks_usable() const {
+    if (ranks[0].eng->flags & AIOS_ENGINE_NO_GEMM) return false;
+    for (const Layer &L : ranks[0].model->layers)
+        if (!gemm_q_usable(L.wo.w.type, L.wo.w.k) || !gemm_q_usable(L.w_down.w.type, L.w_down.w.k)) return false;
+    return true;
+}
+
+void TpModelImpl::prefill_chunks(int n_tokens) {
+    struct Reduce : ChunkReduce {
+        ncclComm_t comm;
+        void all_reduce(double *part, size_t count, cudaStream_t st) override {
+            nccl_check(nccl().AllReduce(part, part, count, ncclDouble, ncclSum, comm, st), "ncclAllReduce");
+        }
+    };
+    std::vector<std::exception_ptr> errs((size_t)n);
+    std::vector<std::thread> threads;
+    for (int r = 0; r < n; r++) {
+        threads.emplace_back([&, r] {
+            try {
+                TpRank &R = ranks[(size_t)r];
+                R.eng->make_current();
+                Reduce red;
+                red.comm = R.comm;
+                for (int i = 0; i < n_tokens; i += GEMM_MAX_TOKENS) {
+                    const int T = std::min((int)GEMM_MAX_TOKENS, n_tokens - i);
+                    R.seq->prefill_chunk(i, T, n_past + i, false, R.eng->stream, &red);
+                }
+                // the last token's residual row is what the lm_head reads
+                const int last = (n_tokens - 1) % GEMM_MAX_TOKENS;
+                const size_t E = (size_t)R.model->hp.n_embd;
+                CUDA_CHECK(cudaMemcpyAsync(R.seq->x.p, R.seq->cx.as<float>() + (size_t)last * E, E * 4, cudaMemcpyDeviceToDevice, R.eng->stream));
+            } catch (...) {
+                errs[(size_t)r] = std::current_exception();
+            }
+        });
+    }
+    for (auto &t : threads) t.join();
+    for (auto &e : errs)
+        if (e) std::rethrow_exception(e);
+    // the logits of the last token: lm_head on every shard's slice, then the gather
+    if (lists_logits != 1) {
+        lists.resize((size_t)n);
+        for (int r = 0; r < n; r++) ranks[(size_t)r].seq->build_token_pass(true, lists[(size_t)r]);
+        lists_logits = 1;
+    }
+    for (int r = 0; r < n; r++) {
+        TpRank &R = ranks[(size_t)r];
+        R.eng->make_current();
+        if (push) tp_tick_kernel<<<1, 1, 0, R.eng->stream>>>(R.tick);
+        PassLaunch L = lists[(size_t)r].back();
+        L.pdl = false;
+        R.seq->launch_pass_item(L, R.eng->stream, 0);
+    }
+    gather_logits();
 }
 
 // the sampler reads pos (position of the last fed token) and step (index into out_tokens) from the device state
@@ -522,7 +594,9 @@ void TpModel::prefill(const int32_t *tokens, int n) {
         r.eng->make_current();
         CUDA_CHECK(cudaMemcpyAsync(r.seq->prompt.p, tokens, (size_t)n * 4, cudaMemcpyHostToDevice, r.eng->stream));
     }
-    for (int i = 0; i < n; i++) impl->token_pass(true, i, impl->n_past + i, i == n - 1, nullptr);
+    if (n >= 4 && impl->chunks_usable()) impl->prefill_chunks(n);
+    else
+        for (int i = 0; i < n; i++) impl->token_pass(true, i, impl->n_past + i, i == n - 1, nullptr);
     impl->sync_all();
     impl->check_push_errors();
     impl->n_past += n;

@@ -40,13 +40,16 @@ prompt = gs.synthetic_prompt(arch, 32, 7)
 first = tp.generate(prompt, 16)
 again = tp.generate(prompt, 16)
 tp.reset()
+t0 = time.time()
 tp.prefill(gs.synthetic_prompt(arch, ctx // 2, 11))
+t_prefill = time.time() - t0
 r = tp.bench_decode(n_tokens)
 rec = {"arch": arch, "ftype": ftype, "tp": n_gpus, "ctx": ctx, "n_tokens": r.n_tokens, "ms_per_token": r.ms_total / r.n_tokens,
        "tok_per_s": 1e3 * r.n_tokens / r.ms_total, "launches_per_token": r.kernel_launches / r.n_tokens,
        "allreduce": "push" if r.allreduce_kind else "nccl", "graphs": bool(r.graphs), "allreduce_per_token": r.n_allreduce_per_token, "us_per_allreduce": r.us_per_allreduce,
        "allreduce_share": r.n_allreduce_per_token * r.us_per_allreduce * 1e-3 / (r.ms_total / r.n_tokens),
        "n_past": [r.n_past_begin, r.n_past_end], "weight_gb_per_rank": tp.info.weight_bytes / 1e9,
+       "prefill_tokens": ctx // 2, "prefill_s": round(t_prefill, 3), "prefill_tok_s": round((ctx // 2) / t_prefill, 1),
        "repeatable": bool(np.array_equal(first, again)), "write_s": round(t_write, 1), "load_s": round(t_load, 1)}
 print(json.dumps(rec))
 tp.unload()
