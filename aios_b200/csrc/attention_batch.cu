@@ -44,6 +44,8 @@ template <int HD>
 __global__ void __launch_bounds__(AB_THREADS, 2) attn_batch_kernel(const AttnBatchParams p) {
     constexpr int LPR = HD / 8;          // lanes per row (8 dims = one 16-byte load per lane)
     constexpr int RPW = 32 / LPR;        // rows per warp-load: 2 (hd 128) or 4 (hd 64)
+    pdl_wait();  // the q/k/v rows (and, inside a decode step, the lane table) come from the launches before this one
+    pdl_launch_dependents();
     const int g = blockIdx.x, l = blockIdx.y;
     const int rep = p.n_head / p.n_kv;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -276,8 +278,8 @@ void launch_attn_batch(const AttnBatchParams &p, int n_lanes, cudaStream_t st) {
         CUDA_CHECK(cudaFuncSetAttribute(attn_batch_kernel<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
     });
     const dim3 grid(p.n_kv, n_lanes);
-    if (p.hd == 128) attn_batch_kernel<128><<<grid, AB_THREADS, smem, st>>>(p);
-    else attn_batch_kernel<64><<<grid, AB_THREADS, smem, st>>>(p);
+    if (p.hd == 128) launch_k(attn_batch_kernel<128>, dim3(grid), dim3(AB_THREADS), smem, st, p);
+    else launch_k(attn_batch_kernel<64>, dim3(grid), dim3(AB_THREADS), smem, st, p);
     CUDA_CHECK(cudaGetLastError());
 }
 

@@ -40,6 +40,35 @@ struct PerDeviceOnce {
     }
 };
 
+// Programmatic dependent launch for a whole sequence of launches (the batched decode step): inside a PdlScope(true)
+// launch_k gives every kernel the programmatic-stream-serialization attribute.  EVERY kernel launched that way must
+// execute pdl_wait() before it touches anything an earlier kernel of the stream wrote (the wait also carries the
+// ordering on to the kernels after it); pdl_launch_dependents() lets the next kernel's CTAs come up early.
+inline thread_local bool g_launch_pdl = false;
+struct PdlScope {
+    bool prev;
+    explicit PdlScope(bool on) : prev(g_launch_pdl) { g_launch_pdl = on; }
+    ~PdlScope() { g_launch_pdl = prev; }
+};
+#ifdef __CUDACC__
+template <typename... KArgs, typename... Args>
+inline void launch_k(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st, Args &&...args) {
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = grid;
+    cfg.blockDim = block;
+    cfg.dynamicSmemBytes = smem;
+    cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = g_launch_pdl ? 1 : 0;
+    CUDA_CHECK(cudaLaunchKernelEx(&cfg, kernel, static_cast<KArgs>(args)...));
+}
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;"); }
+#endif
+
 #ifdef __CUDACC__
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll

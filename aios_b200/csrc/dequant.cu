@@ -46,6 +46,8 @@ void launch_embed_row(int type, const void *d_table, int64_t row_bytes, int k, c
 // batched gather (continuous batching / prompt chunks): x[t][0..k) = dequant(table row toks[t]), t = blockIdx.y
 __global__ void embed_rows_kernel(int type, const uint8_t *table, int64_t row_bytes, int k, const int32_t *toks, float *x,
                                   int64_t ldx) {
+    pdl_wait();
+    pdl_launch_dependents();
     const int t = blockIdx.y;
     const uint8_t *row = table + (int64_t)toks[t] * row_bytes;
     float *xt = x + (size_t)t * ldx;
@@ -54,8 +56,8 @@ __global__ void embed_rows_kernel(int type, const uint8_t *table, int64_t row_by
 void launch_embed_rows(int type, const void *d_table, int64_t row_bytes, int k, const int32_t *d_toks, int T, float *d_x,
                        int64_t ldx, cudaStream_t st) {
     const int threads = 256;
-    embed_rows_kernel<<<dim3((k + threads - 1) / threads, T), threads, 0, st>>>(type, (const uint8_t *)d_table, row_bytes, k,
-                                                                                d_toks, d_x, ldx);
+    launch_k(embed_rows_kernel, dim3((unsigned)((k + threads - 1) / threads), (unsigned)T), dim3(threads), 0, st, type,
+             (const uint8_t *)d_table, row_bytes, k, d_toks, d_x, ldx);
 }
 
 // ---------------------------------------------------------------- natural blocks -> planes

@@ -47,6 +47,8 @@ template <int PERM>
 __global__ void __launch_bounds__(GEMV_THREADS) quant_rows_kernel(const float *x, int64_t ldx, const float *norm_w, float eps,
                                                                    int k, uint8_t *images) {
     __shared__ double red[GEMV_WARPS];
+    pdl_wait();
+    pdl_launch_dependents();
     const int t = blockIdx.x, T = gridDim.x;
     uint8_t *img = images + (size_t)t * gemm_image_stride(k);
     const ActSmem s = carve(img, k);
@@ -79,9 +81,10 @@ __global__ void __launch_bounds__(GEMV_THREADS) quant_rows_kernel(const float *x
 
 void launch_quant_rows(int weight_type, const float *x, int64_t ldx, const float *norm_w, float eps, int k, int T,
                        uint8_t *images, cudaStream_t st) {
-    if (weight_type == T_Q6_K) quant_rows_kernel<PERM_Q6><<<T, GEMV_THREADS, 0, st>>>(x, ldx, norm_w, eps, k, images);
-    else if (weight_type == T_Q8_0) quant_rows_kernel<PERM_Q80><<<T, GEMV_THREADS, 0, st>>>(x, ldx, norm_w, eps, k, images);
-    else quant_rows_kernel<PERM_Q4><<<T, GEMV_THREADS, 0, st>>>(x, ldx, norm_w, eps, k, images);
+    const dim3 grid((unsigned)T), block(GEMV_THREADS);
+    if (weight_type == T_Q6_K) launch_k(quant_rows_kernel<PERM_Q6>, grid, block, 0, st, x, ldx, norm_w, eps, k, images);
+    else if (weight_type == T_Q8_0) launch_k(quant_rows_kernel<PERM_Q80>, grid, block, 0, st, x, ldx, norm_w, eps, k, images);
+    else launch_k(quant_rows_kernel<PERM_Q4>, grid, block, 0, st, x, ldx, norm_w, eps, k, images);
     CUDA_CHECK(cudaGetLastError());
 }
 size_t gemm_images_bytes(int k, int T) { return gemm_staged_offset(k, T) + (size_t)(k / 256) * gemm_img_bytes(T); }
@@ -239,16 +242,24 @@ __device__ __forceinline__ void gemm_body(const GemmParams &p, int seg, uint8_t 
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     __syncthreads();
-    auto stage = [&](int b) {
-        uint8_t *base = smem + (size_t)(b % GEMM_STAGES) * stage_bytes;
-        stage_weights<TYPE, GEMM_ROWS>(base, W, row0, b, NTHREADS);
+    auto stage_w = [&](int b) {
+        stage_weights<TYPE, GEMM_ROWS>(smem + (size_t)(b % GEMM_STAGES) * stage_bytes, W, row0, b, NTHREADS);
         asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+    auto stage_x = [&](int b) {
         if (threadIdx.x == 0) {  // the block's activation record: one bulk copy
+            uint8_t *base = smem + (size_t)(b % GEMM_STAGES) * stage_bytes;
             mbar_arrive_expect_tx(&full[b % GEMM_STAGES], rec_bytes);
             bulk_g2s(base + GEMM_A_BYTES, staged + (size_t)b * rec_bytes, rec_bytes, &full[b % GEMM_STAGES]);
         }
     };
-    stage(0);
+    auto stage = [&](int b) { stage_w(b); stage_x(b); };
+    // the first weights do not depend on the launch before this one (programmatic dependent launch): they are on
+    // their way while that launch finishes; the activation records it writes are asked for after the wait
+    stage_w(0);
+    pdl_wait();
+    pdl_launch_dependents();
+    stage_x(0);
     for (int b = 0; b < nb; b++) {
         if (b + 1 < nb) {  // the next block's copies fly while this one is multiplied
             stage(b + 1);
@@ -411,6 +422,8 @@ static size_t gemm_smem_bytes(int T) { return GEMM_STAGES * (GEMM_A_BYTES + gemm
 // h[t][i] = silu(gate[t][i]) * up[t][i] for a chunk: gu[t] = gate[ff] | up[ff].  Same expression, operation by
 // operation, as the GEMV's fused SwiGLU epilogue.
 __global__ void swiglu_rows_kernel(const float *gu, int64_t ldgu, int ff, int T, float *h, int64_t ldh) {
+    pdl_wait();
+    pdl_launch_dependents();
     const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= (int64_t)T * ff) return;
     const int t = (int)(i / ff), c = (int)(i % ff);
@@ -419,7 +432,7 @@ __global__ void swiglu_rows_kernel(const float *gu, int64_t ldgu, int ff, int T,
 }
 void launch_swiglu_rows(const float *gu, int64_t ldgu, int ff, int T, float *h, int64_t ldh, cudaStream_t st) {
     const int64_t n = (int64_t)T * ff;
-    swiglu_rows_kernel<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(gu, ldgu, ff, T, h, ldh);
+    launch_k(swiglu_rows_kernel, dim3((unsigned)((n + 255) / 256)), dim3(256), 0, st, gu, ldgu, ff, T, h, ldh);
     CUDA_CHECK(cudaGetLastError());
 }
 
@@ -473,7 +486,7 @@ void launch_gemm_multi(const GemmMulti &m, cudaStream_t st) {
     do {                                                                                                              \
         static PerDeviceOnce once;                                                                                    \
         once.run([] { CUDA_CHECK(cudaFuncSetAttribute(gemm_q_kernel<NTV, TWV, RGV>, cudaFuncAttributeMaxDynamicSharedMemorySize, 112 * 1024)); }); \
-        gemm_q_kernel<NTV, TWV, RGV><<<tiles, RGV * TWV * 32, smem, st>>>(p);                                         \
+        launch_k(gemm_q_kernel<NTV, TWV, RGV>, dim3((unsigned)tiles), dim3(RGV * TWV * 32), smem, st, p);              \
     } while (0)
 #define GEMM_LAUNCH_RG(NTV, TWV) do { if (rg == 2) GEMM_LAUNCH(NTV, TWV, 2); else GEMM_LAUNCH(NTV, TWV, 1); } while (0)
     // tokens per warp = 8 * NT; token groups per CTA = TW: more, smaller warps keep more of them in flight per SM

@@ -233,6 +233,8 @@ __global__ void __launch_bounds__(SAMP_THREADS) sample_kernel(const SampleParams
 
 // one CTA per lane of the continuous batcher: the lane's own parameters, logits row, position and token slot
 __global__ void __launch_bounds__(SAMP_THREADS) sample_batch_kernel(const SampleBatchParams b) {
+    pdl_wait();
+    pdl_launch_dependents();
     const int l = blockIdx.x;
     const SampleLane L = b.lanes[l];
     __shared__ int32_t step_dummy;
@@ -253,7 +255,7 @@ __global__ void __launch_bounds__(SAMP_THREADS) sample_batch_kernel(const Sample
 
 void launch_sample(const SampleParams &p, cudaStream_t st) { sample_kernel<<<1, SAMP_THREADS, 0, st>>>(p); }
 void launch_sample_batch(const SampleBatchParams &p, int n_lanes, cudaStream_t st) {
-    sample_batch_kernel<<<n_lanes, SAMP_THREADS, 0, st>>>(p);
+    launch_k(sample_batch_kernel, dim3((unsigned)n_lanes), dim3(SAMP_THREADS), 0, st, p);
 }
 
 }  // namespace aios

@@ -12,7 +12,7 @@ import bench  # noqa: E402
 arch = sys.argv[1] if len(sys.argv) > 1 else "mistral-7b"
 lanes = int(sys.argv[2]) if len(sys.argv) > 2 else 64
 path = bench.ensure_model(arch, "Q4_K_M", True)
-eng = capi.Engine(0, 1, capi.ENGINE_NO_GRAPH)
+eng = capi.Engine(0, 1, capi.ENGINE_NO_GRAPH | int(os.environ.get("AIOS_PROBE_FLAGS", "0")))
 m = eng.load_model("m", path, n_ctx=512)
 prompts = np.stack([gs.synthetic_prompt(arch, 128, 7 + i) for i in range(lanes)])
 rt = ctypes.CDLL("libcudart.so.12")
