@@ -826,7 +826,7 @@ int aios_matmul(aios_engine *e, int32_t type, const void *w_blocks, int64_t n_ro
                 const float *norm_w, float rms_eps, float *y) {
     return guarded([&] {
         if (!e || !w_blocks || !x || !y || n_rows <= 0 || k <= 0 || n_tok <= 0) return fail(AIOS_E_INVAL, "bad argument");
-        if (!gemm_q_usable(type, (int)k)) return fail(AIOS_E_UNSUPPORTED, "aios_matmul: Q4_K / Q6_K / Q8_0 weights, k a multiple of 256");
+        if (!gemm_q_usable(type, (int)k)) return fail(AIOS_E_UNSUPPORTED, "aios_matmul: Q4_K / Q5_K / Q6_K / Q8_0 weights, k a multiple of 256");
         if (n_tok > GEMM_MAX_TOKENS) return fail(AIOS_E_RANGE, "aios_matmul: at most 64 tokens per call");
         std::lock_guard<std::mutex> lk(e->impl.mu);
         Engine &E = e->impl;
@@ -890,7 +890,7 @@ int aios_matmul_tc(aios_engine *e, int32_t type, const void *w_blocks, int64_t n
                    const float *norm_w, float rms_eps, float *y) {
     return guarded([&] {
         if (!e || !w_blocks || !x || !y || n_rows <= 0 || k <= 0 || n_tok <= 0) return fail(AIOS_E_INVAL, "bad argument");
-        if (!prefill_tc_usable(type, (int)k)) return fail(AIOS_E_UNSUPPORTED, "aios_matmul_tc: Q4_K / Q6_K / Q8_0 weights, k a multiple of 256");
+        if (!prefill_tc_usable(type, (int)k)) return fail(AIOS_E_UNSUPPORTED, "aios_matmul_tc: Q4_K / Q5_K / Q6_K / Q8_0 weights, k a multiple of 256");
         std::lock_guard<std::mutex> lk(e->impl.mu);
         Engine &E = e->impl;
         E.make_current();

@@ -559,9 +559,9 @@ void Seq::ensure_graph(const aios_sampling &sp) {
 
 // One prompt chunk of T <= 64 tokens at positions pos0 .. pos0+T-1.  Same arithmetic as T token passes (the logits and
 // the KV rows come out bit-identical); what changes is the weight traffic: every matrix is streamed once for the whole
-// chunk by the multi-token GEMM (gemm_q.cu; q/k/v and gate/up as segments of one launch).  Attention still goes token
-// by token through the decode kernel (each token sees the rows before it).  Matrices of other types (Q5_K) fall back
-// to the GEMV, token by token.
+// chunk by the multi-token GEMM (gemm_q.cu; q/k/v and gate/up as segments of one launch); RoPE + KV append for all
+// rows, then batched attention (one CTA per (token, kv head), each token over the rows before it).  A matrix the GEMM
+// cannot take (more than two weight-type classes in one group) falls back to the GEMV, token by token.
 void Seq::prefill_chunk(int idx0, int T, int pos0, bool want_logits, cudaStream_t st, ChunkReduce *reduce) {
     const HParams &hp = m->hp;
     constexpr int CH = GEMM_MAX_TOKENS;

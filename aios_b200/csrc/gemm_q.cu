@@ -163,10 +163,12 @@ __device__ __forceinline__ void bulk_g2s(void *smem_dst, const void *gsrc, uint3
 //         holding the f16 block scale)
 template <int TYPE> struct TileA;
 template <> struct TileA<T_Q4_K> { static constexpr int RS = 5; static constexpr size_t bytes = (size_t)GEMM_MAX_ROWS * (2 * RS + 1) * 16; };
+// Q5_K: the Q4_K tile, then qh[rows][2] uint4 (4 units x (low word, high word) of fifth bits)
+template <> struct TileA<T_Q5_K> { static constexpr int RS = 5; static constexpr size_t bytes = (size_t)GEMM_MAX_ROWS * (2 * RS + 3) * 16; };
 template <> struct TileA<T_Q8_0> { static constexpr int RS = 9; static constexpr size_t bytes = (size_t)GEMM_MAX_ROWS * (2 * RS + 1) * 16; };
 template <> struct TileA<T_Q6_K> { static constexpr int RS = 5; static constexpr size_t bytes = (size_t)GEMM_MAX_ROWS * (3 * RS + 1) * 16 + GEMM_MAX_ROWS * 4; };
 constexpr size_t GEMM_A_BYTES = TileA<T_Q8_0>::bytes;  // the largest: one stage layout for every type
-static_assert(TileA<T_Q6_K>::bytes <= GEMM_A_BYTES && TileA<T_Q4_K>::bytes <= GEMM_A_BYTES, "stage layout");
+static_assert(TileA<T_Q6_K>::bytes <= GEMM_A_BYTES && TileA<T_Q4_K>::bytes <= GEMM_A_BYTES && TileA<T_Q5_K>::bytes <= GEMM_A_BYTES, "stage layout");
 
 template <int TYPE, int GEMM_ROWS>
 __device__ __forceinline__ void stage_weights(uint8_t *sa, const WPlanes &w, int row0, int b, int nthreads) {
@@ -196,6 +198,10 @@ __device__ __forceinline__ void stage_weights(uint8_t *sa, const WPlanes &w, int
             const size_t row = (size_t)min(row0 + r, w.n_rows - 1);
             if (TYPE == T_Q8_0) cp16(ex + r, w.p[2] + (row * U + (size_t)8 * b) * 2);   // eight f16 scales = 16 bytes
             else cp16(ex + r, w.p[2] + (row * nb + b) * 16);                            // META of the block
+            if (TYPE == T_Q5_K) {  // fifth bits of the block's four units: 4 x 8 bytes
+                cp16(ex + GEMM_ROWS + 2 * r, w.p[3] + (row * U + (size_t)4 * b) * 8);
+                cp16(ex + GEMM_ROWS + 2 * r + 1, w.p[3] + (row * U + (size_t)4 * b) * 8 + 16);
+            }
         }
     }
 }
@@ -296,8 +302,9 @@ __device__ __forceinline__ void gemm_body(const GemmParams &p, int seg, uint8_t 
                     acc[j][3] += (double)__fmul_rn((float)c[3], __fmul_rn(dwb, d1));
                 }
             }
-        } else if (TYPE == T_Q4_K) {
+        } else if (TYPE == T_Q4_K || TYPE == T_Q5_K) {
             const uint4 *ex = p1 + GEMM_ROWS * RS;
+            const uint32_t *qha = reinterpret_cast<const uint32_t *>(ex + GEMM_ROWS + 2 * ra), *qhb = reinterpret_cast<const uint32_t *>(ex + GEMM_ROWS + 2 * rb);
             const uint4 mta = ex[ra], mtb = ex[rb];
             const uint32_t dda = __byte_perm(__byte_perm(mta.x, mta.y, 0x0073), __byte_perm(mta.z, mta.w, 0x0073), 0x5410);
             const uint32_t ddb = __byte_perm(__byte_perm(mtb.x, mtb.y, 0x0073), __byte_perm(mtb.z, mtb.w, 0x0073), 0x5410);
@@ -312,14 +319,24 @@ __device__ __forceinline__ void gemm_body(const GemmParams &p, int seg, uint8_t 
                 const uint32_t qb1 = reinterpret_cast<const uint32_t *>(p1 + rb * RS + u)[q];
                 const int sa_lo = mwa[u] & 63, sa_hi = (mwa[u] >> 6) & 63, ma_lo = (mwa[u] >> 12) & 63, ma_hi = (mwa[u] >> 18) & 63;
                 const int sb_lo = mwb[u] & 63, sb_hi = (mwb[u] >> 6) & 63, mb_lo = (mwb[u] >> 12) & 63, mb_hi = (mwb[u] >> 18) & 63;
+                // A fragments: low nibbles = sub-block 2u (k 0-31 of the unit), high nibbles = sub-block 2u+1
+                uint32_t al0 = qa0 & 0x0F0F0F0Fu, al1 = qa1 & 0x0F0F0F0Fu, al2 = qb0 & 0x0F0F0F0Fu, al3 = qb1 & 0x0F0F0F0Fu;
+                uint32_t ah0 = (qa0 >> 4) & 0x0F0F0F0Fu, ah1 = (qa1 >> 4) & 0x0F0F0F0Fu, ah2 = (qb0 >> 4) & 0x0F0F0F0Fu, ah3 = (qb1 >> 4) & 0x0F0F0F0Fu;
+                if (TYPE == T_Q5_K) {  // the fifth bit of element l of a sub-block is bit l of its QH5 word: my bytes are l = 4q.. and 16+4q..
+                    auto sp = [](uint32_t x4) { return ((x4 * 0x00204081u) & 0x01010101u) << 4; };  // bit j -> byte j, value 16
+                    const uint32_t ea = qha[2 * u], fa = qha[2 * u + 1], eb = qhb[2 * u], fb = qhb[2 * u + 1];
+                    al0 |= sp((ea >> (4 * q)) & 0xFu); al1 |= sp((eb >> (4 * q)) & 0xFu);
+                    al2 |= sp((ea >> (16 + 4 * q)) & 0xFu); al3 |= sp((eb >> (16 + 4 * q)) & 0xFu);
+                    ah0 |= sp((fa >> (4 * q)) & 0xFu); ah1 |= sp((fb >> (4 * q)) & 0xFu);
+                    ah2 |= sp((fa >> (16 + 4 * q)) & 0xFu); ah3 |= sp((fb >> (16 + 4 * q)) & 0xFu);
+                }
 #pragma unroll
                 for (int j = 0; j < NT; j++) {
                     const int tb = tok0 + 8 * j;
                     const uint32_t *bt = reinterpret_cast<const uint32_t *>(s.act + (tb + g) * GEMM_TOK_STRIDE + u * 4);
                     int lo[4], hi[4];
-                    mma_s8_k32(lo, qa0 & 0x0F0F0F0Fu, qa1 & 0x0F0F0F0Fu, qb0 & 0x0F0F0F0Fu, qb1 & 0x0F0F0F0Fu, bt[q], bt[4 + q]);
-                    mma_s8_k32(hi, (qa0 >> 4) & 0x0F0F0F0Fu, (qa1 >> 4) & 0x0F0F0F0Fu, (qb0 >> 4) & 0x0F0F0F0Fu,
-                               (qb1 >> 4) & 0x0F0F0F0Fu, bt[8 + q], bt[12 + q]);
+                    mma_s8_k32(lo, al0, al1, al2, al3, bt[q], bt[4 + q]);
+                    mma_s8_k32(hi, ah0, ah1, ah2, ah3, bt[8 + q], bt[12 + q]);
 #pragma unroll
                     for (int e = 0; e < 2; e++) {  // my two tokens of this n-block
                         const int t = tb + 2 * q + e;
@@ -413,6 +430,7 @@ __global__ void __launch_bounds__(GEMM_RG * TW * 32) gemm_q_kernel(const GemmPar
     while (seg + 1 < p.n_seg && (int)blockIdx.x >= p.tile_begin[seg + 1]) seg++;
     const int type = p.seg[seg].type;  // CTA-uniform
     if (type == T_Q4_K) gemm_body<T_Q4_K, NT, TW, GEMM_RG>(p, seg, smem);
+    else if (type == T_Q5_K) gemm_body<T_Q5_K, NT, TW, GEMM_RG>(p, seg, smem);
     else if (type == T_Q6_K) gemm_body<T_Q6_K, NT, TW, GEMM_RG>(p, seg, smem);
     else gemm_body<T_Q8_0, NT, TW, GEMM_RG>(p, seg, smem);
 }
@@ -448,7 +466,7 @@ void launch_add_part_rows(float *x, int64_t ldx, const double *part, int n, int 
     CUDA_CHECK(cudaGetLastError());
 }
 
-bool gemm_q_usable(int type, int k) { return (type == T_Q4_K || type == T_Q6_K || type == T_Q8_0) && k % 256 == 0; }
+bool gemm_q_usable(int type, int k) { return (type == T_Q4_K || type == T_Q5_K || type == T_Q6_K || type == T_Q8_0) && k % 256 == 0; }
 
 // images of tokens T..pad(T)-1 (padding) must exist (any finite contents); their outputs are not stored.
 int gemm_pad_tokens(int T) { return T <= 32 ? (T + 7) / 8 * 8 : GEMM_MAX_TOKENS; }

@@ -167,11 +167,15 @@ __device__ __forceinline__ void load_raw_stage(const WPlanes &w, int64_t row, in
         R.v[2] = __ldg(reinterpret_cast<const uint4 *>(w.p[0] + (u + 1) * 16));
         R.v[3] = __ldg(reinterpret_cast<const uint4 *>(w.p[1] + (u + 1) * 16));
         R.s[0] = __ldg(reinterpret_cast<const uint32_t *>(w.p[2] + u * 2));  // two f16 scales (u is even: 4-byte aligned)
-    } else if (TYPE == T_Q4_K) {
+    } else if (TYPE == T_Q4_K || TYPE == T_Q5_K) {
         const int64_t u = row * (w.k / 64) + kb;
         R.v[0] = __ldg(reinterpret_cast<const uint4 *>(w.p[0] + u * 16));
         R.v[1] = __ldg(reinterpret_cast<const uint4 *>(w.p[1] + u * 16));
         R.v[2] = __ldg(reinterpret_cast<const uint4 *>(w.p[2] + (row * (w.k / 256) + (kb >> 2)) * 16));
+        if (TYPE == T_Q5_K) {  // the fifth bits: 32 of the low sub-block, 32 of the high one
+            const uint2 h = __ldg(reinterpret_cast<const uint2 *>(w.p[3] + u * 8));
+            R.s[0] = h.x; R.s[1] = h.y;
+        }
     } else {
         const int b = kb >> 2, hh = (kb >> 1) & 1;
         const int64_t u = row * (w.k / 64) + 4 * b + 2 * hh;
@@ -205,8 +209,9 @@ __device__ __forceinline__ void dequant_row_stage(const RawStage &R, int kb, uin
             store_chunk(a_tile, r, 4 * blk + 0, c0); store_chunk(a_tile, r, 4 * blk + 1, c1);
             store_chunk(a_tile, r, 4 * blk + 2, c2); store_chunk(a_tile, r, 4 * blk + 3, c3);
         }
-    } else if (TYPE == T_Q4_K) {
-        // unit kb of the row: k 0-15 QSa low nibbles, 16-31 QSb low, 32-47 QSa high, 48-63 QSb high (layout.cuh)
+    } else if (TYPE == T_Q4_K || TYPE == T_Q5_K) {
+        // unit kb of the row: k 0-15 QSa low nibbles, 16-31 QSb low, 32-47 QSa high, 48-63 QSb high (layout.cuh);
+        // Q5_K: a fifth bit per weight from the QH5 words (bit l = element l of the sub-block)
         const uint4 qa = R.v[0], qb = R.v[1], mt = R.v[2];
         const int pq = kb & 3;
         const uint32_t mw = (pq & 2) ? ((pq & 1) ? mt.w : mt.z) : ((pq & 1) ? mt.y : mt.x);
@@ -216,12 +221,13 @@ __device__ __forceinline__ void dequant_row_stage(const RawStage &R, int kb, uin
         // would cost ~10x the error), one rounding to f16 at the end
         const float s_lo = __fmul_rn(dd.x, (float)(mw & 63)), s_hi = __fmul_rn(dd.x, (float)((mw >> 6) & 63));
         const float m_lo = -__fmul_rn(dd.y, (float)((mw >> 12) & 63)), m_hi = -__fmul_rn(dd.y, (float)((mw >> 18) & 63));
-        auto deq16 = [&](const uint4 &q, int hi, float sc, float mn, int c) {  // 16 nibbles -> chunks c, c+1
+        auto deq16 = [&](const uint4 &q, int hi, float sc, float mn, int c, uint32_t bits16) {  // 16 nibbles -> chunks c, c+1
             const uint32_t wds[4] = {q.x, q.y, q.z, q.w};
             uint32_t o[8];
 #pragma unroll
             for (int i = 0; i < 4; i++) {
-                const uint32_t n4 = hi ? (wds[i] >> 4) & 0x0F0F0F0Fu : wds[i] & 0x0F0F0F0Fu;
+                uint32_t n4 = hi ? (wds[i] >> 4) & 0x0F0F0F0Fu : wds[i] & 0x0F0F0F0Fu;
+                if (TYPE == T_Q5_K) n4 |= ((((bits16 >> (4 * i)) & 0xFu) * 0x00204081u) & 0x01010101u) << 4;  // bit j -> byte j, value 16
 #pragma unroll
                 for (int pr = 0; pr < 2; pr++) {
                     const uint32_t h = h2_sub(bytes_to_h2_1024(n4, pr), H1024);  // exact 0..15
@@ -233,10 +239,10 @@ __device__ __forceinline__ void dequant_row_stage(const RawStage &R, int kb, uin
             store_chunk(a_tile, r, c, make_uint4(o[0], o[1], o[2], o[3]));
             store_chunk(a_tile, r, c + 1, make_uint4(o[4], o[5], o[6], o[7]));
         };
-        deq16(qa, 0, s_lo, m_lo, 0);
-        deq16(qb, 0, s_lo, m_lo, 2);
-        deq16(qa, 1, s_hi, m_hi, 4);
-        deq16(qb, 1, s_hi, m_hi, 6);
+        deq16(qa, 0, s_lo, m_lo, 0, R.s[0] & 0xFFFFu);
+        deq16(qb, 0, s_lo, m_lo, 2, R.s[0] >> 16);
+        deq16(qa, 1, s_hi, m_hi, 4, R.s[1] & 0xFFFFu);
+        deq16(qb, 1, s_hi, m_hi, 6, R.s[1] >> 16);
     } else {  // Q6_K
         // 64 weights [64*kb, +64) = half hh = (kb >> 1) & 1 of block b = kb >> 2, sub-blocks k0 = 2*(kb & 1) and k0 + 1 of
         // BOTH units t = 0, 1: order in K is (t0,k0) (t1,k0) (t0,k0+1) (t1,k0+1), 16 weights each
@@ -437,11 +443,11 @@ EncodeTiledFn encode_tiled() {
 }
 }  // namespace
 
-bool prefill_tc_usable(int type, int k) { return (type == T_Q4_K || type == T_Q6_K || type == T_Q8_0) && k % 256 == 0; }
+bool prefill_tc_usable(int type, int k) { return (type == T_Q4_K || type == T_Q5_K || type == T_Q6_K || type == T_Q8_0) && k % 256 == 0; }
 
 // xh: activations as f16, [T][k] row-major (k contiguous), in THIS GPU's memory
 void launch_prefill_tc(const WPlanes &w, const __half *xh, int T, float *out, int64_t ldo, int epi, int n_sms, cudaStream_t st) {
-    if (!prefill_tc_usable(w.type, w.k)) throw CudaError("prefill_tc: Q4_K / Q6_K / Q8_0 weights, K a multiple of 256");
+    if (!prefill_tc_usable(w.type, w.k)) throw CudaError("prefill_tc: Q4_K / Q5_K / Q6_K / Q8_0 weights, K a multiple of 256");
     if (T < 1) return;
     CUtensorMap tmap;
     const cuuint64_t gdim[2] = {(cuuint64_t)w.k, (cuuint64_t)T};
@@ -464,6 +470,7 @@ void launch_prefill_tc(const WPlanes &w, const __half *xh, int T, float *out, in
         prefill_tc_kernel<TY><<<grid, TC_THREADS, TC_SMEM_BYTES, st>>>(tmap, p);                                       \
     } while (0)
     if (w.type == T_Q4_K) TC_LAUNCH(T_Q4_K);
+    else if (w.type == T_Q5_K) TC_LAUNCH(T_Q5_K);
     else if (w.type == T_Q6_K) TC_LAUNCH(T_Q6_K);
     else TC_LAUNCH(T_Q8_0);
 #undef TC_LAUNCH

@@ -66,7 +66,7 @@ ARCHS = {
     "llama3-70b": Arch("llama3-70b", 80, 8192, 64, 8, 128, 28672, 128256, 500000.0, 1e-5, 8192),
 }
 
-FTYPE_ID = {"Q4_K_M": 15, "Q8_0": 7, "F32": 0}
+FTYPE_ID = {"Q4_K_M": 15, "Q4_K_M_70B": 15, "Q8_0": 7, "F32": 0}
 
 
 def use_more_bits(i: int, n: int) -> bool:
@@ -78,9 +78,10 @@ def tensor_plan(arch: Arch, ftype: str) -> list[tuple[str, tuple[int, int] | tup
     """[(name, (rows, cols) or (n,), ggml_type)] in file order.  cols = K = quant-block axis (ne0)."""
     E, FF, V = arch.n_embd, arch.n_ff, arch.n_vocab
     QD, KVD = arch.n_head * arch.head_dim, arch.n_head_kv * arch.head_dim
-    if ftype == "Q4_K_M":
+    if ftype in ("Q4_K_M", "Q4_K_M_70B"):
         base, more = Q4_K, Q6_K
-        v70 = Q5_K if arch.n_layer >= 80 else Q4_K  # 70B-class bumps remaining attn_v to Q5_K
+        # 70B-class bumps remaining attn_v to Q5_K ("Q4_K_M_70B": that mix on any shape, for tests)
+        v70 = Q5_K if (arch.n_layer >= 80 or ftype == "Q4_K_M_70B") else Q4_K
     elif ftype == "Q8_0":
         base = more = v70 = Q8_0
     elif ftype == "F32":

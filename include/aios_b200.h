@@ -283,12 +283,12 @@ int aios_matvec(aios_engine *e, int32_t ggml_type, const void *w_blocks, int64_t
                 const float *x, const float *norm_w, float rms_eps, float *y);
 /* Y[n_tok][n_rows] = X[n_tok][k] . W[n_rows,k]^T for 1..64 tokens through the multi-token kernel (gemm_q.cu: int8 MMA
  * on the sub-block dots, weights streamed once for all tokens — batched decode and bit-exact prompt chunks).  Same
- * numerics as n_tok calls of aios_matvec, bit for bit.  Q4_K, Q6_K and Q8_0 weights (AIOS_E_UNSUPPORTED otherwise);
+ * numerics as n_tok calls of aios_matvec, bit for bit.  Q4_K, Q5_K, Q6_K and Q8_0 weights (AIOS_E_UNSUPPORTED otherwise);
  * host in, host out. */
 int aios_matmul(aios_engine *e, int32_t ggml_type, const void *w_blocks, int64_t n_rows, int64_t k, const float *x,
                 int32_t n_tok, const float *norm_w, float rms_eps, float *y);
 /* the same product through the prefill path's tensor-core GEMM (prefill_tc.cu: tcgen05 / TMEM, f16 operands, f32
- * accumulation): any n_tok >= 1; Q4_K, Q6_K and Q8_0 weights.  Float arithmetic with a stated tolerance — max error 4e-3,
+ * accumulation): any n_tok >= 1; Q4_K, Q5_K, Q6_K and Q8_0 weights.  Float arithmetic with a stated tolerance — max error 4e-3,
  * rms error 8e-4 of the output's rms against an exact product of the dequantised weights — not the bit-exact integer path of aios_matmul. */
 int aios_matmul_tc(aios_engine *e, int32_t ggml_type, const void *w_blocks, int64_t n_rows, int64_t k, const float *x,
                    int32_t n_tok, const float *norm_w, float rms_eps, float *y);

@@ -10,7 +10,7 @@ from aios_b200 import gguf_synth as gs
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.parametrize("qt", [gs.Q4_K, gs.Q6_K, gs.Q8_0])
+@pytest.mark.parametrize("qt", [gs.Q4_K, gs.Q5_K, gs.Q6_K, gs.Q8_0])
 @pytest.mark.parametrize("shape", [(16, 256, 8), (37, 512, 3), (64, 2048, 32), (130, 4096, 17), (70, 5632, 9), (48, 14336, 24),
                                    (33, 1024, 64), (95, 2048, 41), (1, 256, 1)])
 def test_matmul_equals_oracle_matvecs(engine, oracle, qt, shape):
@@ -28,7 +28,7 @@ def test_matmul_equals_oracle_matvecs(engine, oracle, qt, shape):
         assert np.array_equal(got[i].view(np.uint32), ref.view(np.uint32)), (i, np.abs(got[i] - ref).max())
 
 
-@pytest.mark.parametrize("qt", [gs.Q4_K, gs.Q6_K, gs.Q8_0])
+@pytest.mark.parametrize("qt", [gs.Q4_K, gs.Q5_K, gs.Q6_K, gs.Q8_0])
 def test_matmul_with_rmsnorm_equals_matvec(engine, qt):
     n, k, t = 96, 2048, 12
     rng = np.random.default_rng(5)
@@ -41,7 +41,7 @@ def test_matmul_with_rmsnorm_equals_matvec(engine, qt):
         assert np.array_equal(got[i].view(np.uint32), ref.view(np.uint32)), i
 
 
-@pytest.mark.parametrize("arch,ftype", [("tiny", "Q4_K_M"), ("tiny-gqa4", "Q4_K_M"), ("tiny", "Q8_0")])
+@pytest.mark.parametrize("arch,ftype", [("tiny", "Q4_K_M"), ("tiny-gqa4", "Q4_K_M"), ("tiny", "Q8_0"), ("tiny-gqa4", "Q4_K_M_70B")])
 @pytest.mark.parametrize("n_prompt", [4, 33, 70, 121])
 def test_chunked_prefill_is_bit_identical_to_token_by_token(engine, oracle, tmp_models, arch, ftype, n_prompt):
     """Seq::prefill feeds prompts in 64-token chunks through the GEMM; logits, KV rows and the continuation must be
@@ -76,9 +76,9 @@ def test_chunked_prefill_is_bit_identical_to_token_by_token(engine, oracle, tmp_
 
 
 def test_matmul_argument_errors(engine):
-    w = np.zeros(176 * 4, np.uint8)
+    w = np.zeros(4 * 256 * 4, np.uint8)
     with pytest.raises(capi.AiosError) as e:
-        engine.matmul(gs.Q5_K, w, 4, 256, np.zeros((2, 256), np.float32))
+        engine.matmul(gs.F32, w, 4, 256, np.zeros((2, 256), np.float32))  # not a quantised matrix type
     assert e.value.code == capi.E_UNSUPPORTED
     with pytest.raises(capi.AiosError) as e:
         engine.matmul(gs.Q4_K, np.zeros(144 * 4, np.uint8), 4, 256, np.zeros((65, 256), np.float32))

@@ -14,7 +14,7 @@ from aios_b200 import gguf_synth as gs
 pytestmark = pytest.mark.gpu
 
 
-@pytest.mark.parametrize("qt", [gs.Q8_0, gs.Q4_K, gs.Q6_K])
+@pytest.mark.parametrize("qt", [gs.Q8_0, gs.Q4_K, gs.Q5_K, gs.Q6_K])
 @pytest.mark.parametrize("shape", [(128, 256, 256), (128, 512, 64), (200, 1024, 300), (384, 4096, 513), (130, 14336, 40), (64, 256, 1)])
 def test_matmul_tc_within_tolerance(engine, oracle, qt, shape):
     n, k, t = shape
@@ -55,7 +55,7 @@ def test_matmul_tc_with_rmsnorm(engine, oracle):
     assert np.abs(got - exact).max() / np.sqrt(np.mean(exact ** 2)) < 4e-3
 
 
-@pytest.mark.parametrize("arch,ftype", [("tiny-gqa4", "Q4_K_M"), ("tiny", "Q8_0"), ("tiny-mha32", "Q4_K_M")])
+@pytest.mark.parametrize("arch,ftype", [("tiny-gqa4", "Q4_K_M"), ("tiny", "Q8_0"), ("tiny-mha32", "Q4_K_M"), ("tiny-gqa4", "Q4_K_M_70B")])
 def test_tc_prefill_logits_against_exact_math(oracle, tmp_models, arch, ftype):
     """Whole path: a 300-token prompt through the tensor-core prefill (tcgen05 GEMMs, RoPE / KV append for all rows, causal
     flash attention) against an exact f64 forward pass of the dequantised model (oracle/ref_llama.py).
