@@ -122,3 +122,31 @@ def test_tied_embeddings_match_oracle(oracle, tmp_path):
             m.unload()
     finally:
         eng.close()
+
+
+@pytest.mark.parametrize("name,rms_tol,corr_min,max_tol", [("exact_logits_tinyllama.npz", 0.15, 0.99, 0.8),
+                                                           ("exact_logits_mistral7b.npz", 0.25, 0.975, 1.2)])
+def test_engine_against_exact_math_at_baseline_shapes(engine, name, rms_tol, corr_min, max_tol):
+    """The CUDA path against the independent full-size pin (gguf-py dequantisers + float64 numpy forward pass,
+    scripts/make_golden_exact.py): TinyLlama-1.1B and Mistral-7B shapes, within the activation-quantisation noise that
+    separates the llama.cpp-style integer path from exact math (same bounds as the oracle's own test, tests/test_cpu.py)."""
+    import os
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", name))
+    arch, ftype, seed = str(g["arch"]), str(g["ftype"]), int(g["seed"])
+    base = "/dev/shm" if os.path.isdir("/dev/shm") and os.access("/dev/shm", os.W_OK) else "/tmp"
+    path = os.path.join(base, f"aios_pin_{arch}_{os.getpid()}.gguf")
+    try:
+        gs.write_synthetic_gguf(path, arch, ftype, seed)
+        m = engine.load_model("pin", path, n_ctx=64)
+        try:
+            got = m.forward_logits(g["prompt"])
+        finally:
+            m.unload()
+    finally:
+        if os.path.exists(path):
+            os.remove(path)
+    exact = g["logits"]
+    sd = exact.std()
+    assert np.sqrt(np.mean((got - exact) ** 2)) / sd < rms_tol
+    assert np.corrcoef(got, exact)[0, 1] > corr_min
+    assert np.abs(got - exact).max() / sd < max_tol
