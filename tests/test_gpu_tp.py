@@ -117,6 +117,9 @@ def test_runtime_serves_a_tensor_parallel_model(tmp_path):
         assert chunks[-1] == ("", True) and "".join(t for t, _ in chunks) == want.text
         small = be.load("tinyllama", path, 256)  # other models are still replicated, one replica per GPU
         assert not isinstance(small, TpLoaded) and len(small.replicas) == 2
+        # ... and requests alternate between the replicas (least loaded, ties in turn), same text from either GPU
+        texts = [eng.infer(small, "tinyllama", p).text for _ in range(4)]
+        assert texts == [want.text] * 4 and small.served == [2, 2]
         be.unload(small)
         be.unload(lm)
         assert not be.alive(lm)
