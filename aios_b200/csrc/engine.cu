@@ -50,6 +50,7 @@ Engine::Engine(const aios_engine_opts &o) : device(o.device), max_batch(o.max_ba
     n_sms = prop.multiProcessorCount;
     CUDA_CHECK(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
     if (const char *e = getenv("AIOS_EVICT_FIRST")) evict_first = atoi(e) != 0;
+    if (const char *e = getenv("AIOS_ATTN_LONG_MIN")) attn_long_min = atoi(e);
     // function attributes are per-device settings: every engine sets them for its own device
     gemv_init();
     attn_split_init();
@@ -304,6 +305,12 @@ Seq::Seq(Model *m_, bool internal_) : m(m_), internal(internal_) {
         CUDA_CHECK(cudaMemset(pfd_att_acc.p, 0, pfd_att_acc.bytes));
         CUDA_CHECK(cudaMemset(pfd_counters.p, 0, pfd_counters.bytes));
         if (m->tp_size > 1) tp_part64 = DevBuf((size_t)hp.n_embd * sizeof(double));
+        if (m->tp_size == 1 && attn_long_usable(hp.n_head, hp.n_head_kv, hp.n_ctx, hp.head_dim) &&
+            (hp.n_ctx >= m->eng->attn_long_min || !attn_split_usable(hp.n_ctx, hp.head_dim))) {
+            attn_long_n_slices = attn_long_slices(hp.n_head_kv, m->eng->n_sms);
+            attn_long_scratch = DevBuf(attn_long_scratch_bytes(hp.n_head, hp.n_head_kv, hp.n_ctx, hp.head_dim, attn_long_n_slices));
+            CUDA_CHECK(cudaMemset(attn_long_scratch.p, 0, attn_long_scratch.bytes));
+        }
         reset();
         if (m->tp_size == 1) build_pfd();
     } catch (...) {
@@ -315,7 +322,8 @@ Seq::Seq(Model *m_, bool internal_) : m(m_), internal(internal_) {
 }
 
 Seq::~Seq() {
-    if (graph) cudaGraphExecDestroy(graph);
+    for (auto &g : graphs)
+        if (g.exec) cudaGraphExecDestroy(g.exec);
     cudaStreamSynchronize(m->eng->stream);  // nothing in flight may still touch the pages that are about to be unmapped
     std::lock_guard<std::mutex> lk(m->mu);
     if (!internal) m->user_seqs--;
@@ -351,7 +359,7 @@ void Seq::launch_embed(bool from_prompt, int prompt_idx, int pos_value, cudaStre
 // With a tensor-parallel shard (m->tp_size > 1) hp holds the LOCAL head / FF counts, the K-split projections
 // (attn_output, ffn_down) store their unrounded double sums into tp_part64 and are marked reduce_after: the driver
 // (tp.cu) all-reduces the partials and adds them to x; the lm_head writes this rank's slice of the logits.
-void Seq::build_token_pass(bool want_logits, std::vector<PassLaunch> &ls) {
+void Seq::build_token_pass(bool want_logits, std::vector<PassLaunch> &ls, bool long_attn) {
     const HParams &hp = m->hp;
     SeqState *sd = state.as<SeqState>();
     const int n_sms = m->eng->n_sms;
@@ -361,7 +369,10 @@ void Seq::build_token_pass(bool want_logits, std::vector<PassLaunch> &ls) {
     const int amode = (m->eng->flags & AIOS_ENGINE_ATTN_CLUSTER) ? 2 : 0;
     // with the split attention kernel, RoPE + f16 rounding + KV append move into the q/k/v GEMV's epilogue
     // (EPI_QKV_ROPE): the attention kernel then starts on final data, with no dependent table loads of its own
-    const bool rope_in_gemv = amode == 0 && attn_split_usable(hp.n_ctx, hp.head_dim) && !(m->eng->flags & AIOS_ENGINE_NO_ROPE_EPILOGUE);
+    // (the position-split kernel of attention_long.cu takes such launches too: it is the decode attention of contexts
+    // beyond the split kernel's 4096 rows, and of long contexts below that)
+    const bool split_ok = attn_split_usable(hp.n_ctx, hp.head_dim), long_ok = attn_long_scratch.p != nullptr;
+    const bool rope_in_gemv = amode == 0 && (split_ok || long_ok) && !(m->eng->flags & AIOS_ENGINE_NO_ROPE_EPILOGUE);
     ls.clear();
     ls.reserve((size_t)hp.n_layer * 6 + 2);
     int n_reduce = 0;
@@ -420,6 +431,7 @@ void Seq::build_token_pass(bool want_logits, std::vector<PassLaunch> &ls) {
             a.n_split = m->attn_splits; a.n_ctx = hp.n_ctx;
             a.scale = 1.0f / sqrtf((float)hp.head_dim);
             a.kv_ready = kv_ready ? 1 : 0;
+            if (kv_ready && long_ok && (long_attn || !split_ok)) A.kind = 2;  // the position-split kernel
             ls.push_back(A);
         }
         {   // attention output projection + residual add
@@ -467,6 +479,8 @@ void Seq::launch_pass_item(PassLaunch &L, cudaStream_t st, int launch_index) {
         if (L.g.argmax_key) CUDA_CHECK(cudaMemsetAsync(&sd->argmax_key, 0, sizeof(unsigned long long), st));
         L.g.trace = tr;
         TIMED(0, launch_gemv(L.g, L.grid, st, L.pdl));
+    } else if (L.kind == 2) {
+        TIMED(1, launch_attn_long(L.a, attn_long_scratch.p, attn_long_n_slices, st, L.pdl));
     } else {
         L.a.trace = tr;
         const int amode = (m->eng->flags & AIOS_ENGINE_ATTN_CLUSTER) ? 2 : 0;
@@ -474,13 +488,14 @@ void Seq::launch_pass_item(PassLaunch &L, cudaStream_t st, int launch_index) {
     }
 }
 
-void Seq::launch_token_pass(bool from_prompt, int prompt_idx, int pos_value, bool want_logits, cudaStream_t st, int *n_launch) {
+void Seq::launch_token_pass(bool from_prompt, int prompt_idx, int pos_value, bool want_logits, cudaStream_t st, int *n_launch,
+                            bool long_attn) {
     if (m->tp_size > 1) throw std::logic_error("a tensor-parallel shard is driven by its group (tp.cu)");
     int launches = 0;
     launch_embed(from_prompt, prompt_idx, pos_value, st);
     launches++;
     std::vector<PassLaunch> ls;
-    build_token_pass(want_logits, ls);
+    build_token_pass(want_logits, ls, long_attn);
     for (size_t i = 0; i < ls.size(); i++) launch_pass_item(ls[i], st, launches++);
     if (n_launch) *n_launch += launches;
 }
@@ -532,9 +547,10 @@ static bool same_sampling(const aios_sampling &a, const aios_sampling &b) {
     return a.temperature == b.temperature && a.top_k == b.top_k && a.top_p == b.top_p && a.min_p == b.min_p && a.seed == b.seed;
 }
 
-void Seq::ensure_graph(const aios_sampling &sp) {
-    if (graph && same_sampling(sp, graph_sampling) && graph_mask == mask_on && graph_mask_ptr == ext_mask) return;
-    if (graph) { cudaGraphExecDestroy(graph); graph = nullptr; }
+cudaGraphExec_t Seq::ensure_graph(const aios_sampling &sp, bool long_attn) {
+    StepGraph &G = graphs[long_attn ? 1 : 0];
+    if (G.exec && same_sampling(sp, G.sampling) && G.mask == mask_on && G.mask_ptr == ext_mask) return G.exec;
+    if (G.exec) { cudaGraphExecDestroy(G.exec); G.exec = nullptr; }
     cudaStream_t st = m->eng->stream;
     cudaGraph_t g = nullptr;
     kernels_per_step = 0;
@@ -542,19 +558,20 @@ void Seq::ensure_graph(const aios_sampling &sp) {
     try {
         launch_sample_kernel(sp, st);
         kernels_per_step++;
-        launch_token_pass(false, 0, 0, true, st, &kernels_per_step);
+        launch_token_pass(false, 0, 0, true, st, &kernels_per_step, long_attn);
     } catch (...) {
         cudaStreamEndCapture(st, &g);
         if (g) cudaGraphDestroy(g);
         throw;
     }
     CUDA_CHECK(cudaStreamEndCapture(st, &g));
-    cudaError_t e = cudaGraphInstantiate(&graph, g, 0);
+    cudaError_t e = cudaGraphInstantiate(&G.exec, g, 0);
     cudaGraphDestroy(g);
     CUDA_CHECK(e);
-    graph_sampling = sp;
-    graph_mask = mask_on;
-    graph_mask_ptr = ext_mask;
+    G.sampling = sp;
+    G.mask = mask_on;
+    G.mask_ptr = ext_mask;
+    return G.exec;
 }
 
 // One prompt chunk of T <= 64 tokens at positions pos0 .. pos0+T-1.  Same arithmetic as T token passes (the logits and
@@ -747,12 +764,12 @@ int Seq::decode(const aios_sampling &sp, int max_tokens, int32_t *out) {
     if (use_pfd(sp)) {
         launch_pfd_tokens(steps, st);  // one cooperative launch for all the tokens
     } else if (use_graph) {
-        ensure_graph(sp);
-        for (int i = 0; i < steps; i++) CUDA_CHECK(cudaGraphLaunch(graph, st));
+        // step i feeds the token at position n_past + i: n_past + i + 1 rows to attend to
+        for (int i = 0; i < steps; i++) CUDA_CHECK(cudaGraphLaunch(ensure_graph(sp, want_long_attn(n_past + i + 1)), st));
     } else {
         for (int i = 0; i < steps; i++) {
             launch_sample_kernel(sp, st);
-            launch_token_pass(false, 0, 0, true, st, nullptr);
+            launch_token_pass(false, 0, 0, true, st, nullptr, want_long_attn(n_past + i + 1));
         }
     }
     CUDA_CHECK(cudaMemcpyAsync(out, out_tokens.p, (size_t)steps * 4, cudaMemcpyDeviceToHost, st));
@@ -775,7 +792,8 @@ void Seq::bench_decode(int n_tokens, aios_bench_result *out) {
     cudaStream_t st = m->eng->stream;
     aios_sampling sp{};  // greedy
     const bool fused = use_pfd(sp);
-    if (!fused) ensure_graph(sp);
+    if (!fused)
+        for (int i = 0; i < steps; i++) ensure_graph(sp, want_long_attn(n_past + i + 1));  // capture outside the timed region
     int32_t hdr[2] = {n_past - 1, 0};
     CUDA_CHECK(cudaMemcpyAsync(state.p, hdr, sizeof(hdr), cudaMemcpyHostToDevice, st));
     cudaEvent_t e0, e1;
@@ -784,7 +802,7 @@ void Seq::bench_decode(int n_tokens, aios_bench_result *out) {
     CUDA_CHECK(cudaStreamSynchronize(st));
     CUDA_CHECK(cudaEventRecord(e0, st));
     if (fused) launch_pfd_tokens(steps, st);
-    else for (int i = 0; i < steps; i++) CUDA_CHECK(cudaGraphLaunch(graph, st));
+    else for (int i = 0; i < steps; i++) CUDA_CHECK(cudaGraphLaunch(ensure_graph(sp, want_long_attn(n_past + i + 1)), st));
     CUDA_CHECK(cudaEventRecord(e1, st));
     CUDA_CHECK(cudaEventSynchronize(e1));
     float ms = 0;

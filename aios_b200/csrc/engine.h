@@ -42,6 +42,9 @@ struct Engine {
     // streamed weights carry the L2 evict-first policy (bytes used once should not push out activations, KV rows or
     // the next launch's first weights); AIOS_EVICT_FIRST=0/1 overrides for A/B runs
     bool evict_first = true;
+    // contexts of at least this many positions decode with the position-split attention (AIOS_ATTN_LONG_MIN overrides;
+    // measured crossover against the latency kernel: DESIGN.md §4)
+    int attn_long_min = 2048;
     cudaStream_t stream = nullptr;
     std::mutex mu;  // serialises use of the stream by API calls
     explicit Engine(const aios_engine_opts &o);
@@ -134,7 +137,7 @@ struct ChunkReduce {
 
 // one launch of the token pass (Seq::build_token_pass)
 struct PassLaunch {
-    int kind = 0;  // 0 GEMV, 1 attention
+    int kind = 0;  // 0 GEMV, 1 attention, 2 attention over a long context (attention_long.cu: two kernels)
     GemvParams g{};
     AttnParams a{};
     int grid = 0;
@@ -161,10 +164,17 @@ struct Seq {
     bool mask_on = false;
     const uint8_t *ext_mask = nullptr;  // a mask owned by someone else (the batcher's lane mask); wins over `mask`
     unsigned long long *trace_base = nullptr;  // non-null only inside trace_decode
-    cudaGraphExec_t graph = nullptr;
-    aios_sampling graph_sampling{};
-    const uint8_t *graph_mask_ptr = nullptr;
-    bool graph_mask = false;
+    // the captured decode step, in two variants: [0] the latency attention kernel (short contexts), [1] the
+    // position-split GQA-sharing one (attention_long.cu) that the host switches to once the context is long
+    struct StepGraph {
+        cudaGraphExec_t exec = nullptr;
+        aios_sampling sampling{};
+        const uint8_t *mask_ptr = nullptr;
+        bool mask = false;
+    } graphs[2];
+    DevBuf attn_long_scratch;  // scores / slice maxima / partial sums of attention_long.cu (null: not usable here)
+    int attn_long_n_slices = 0;
+    bool want_long_attn(int n_pos) const { return attn_long_scratch.p && n_pos >= m->eng->attn_long_min; }
     int kernels_per_step = 0;
     // persistent fused decode (pfd.cu): phase table + global exchange buffers; pfd_grid == 0 -> not usable
     DevBuf pfd_phases, pfd_att_max, pfd_att_sum, pfd_att_acc, pfd_counters, pfd_timing;
@@ -192,7 +202,7 @@ struct Seq {
     bool tp_pdl_wait = false;  // the kernel after a pushed all-reduce is a programmatic dependent of the wait kernel
     TpPush tp_push_logits{};  // ... and the lm_head its slice of the logits (EPI_PUSH_F32)
     void launch_embed(bool from_prompt, int prompt_idx, int pos_value, cudaStream_t st);
-    void build_token_pass(bool want_logits, std::vector<PassLaunch> &ls);
+    void build_token_pass(bool want_logits, std::vector<PassLaunch> &ls, bool long_attn = false);
     void launch_pass_item(PassLaunch &L, cudaStream_t st, int launch_index);
     void launch_sample_kernel(const aios_sampling &sp, cudaStream_t st);
     // tokens prompt[idx0 .. idx0+T) at positions pos0...; on a tensor-parallel shard `reduce` carries the K-split
@@ -200,9 +210,10 @@ struct Seq {
     void prefill_chunk(int idx0, int T, int pos0, bool want_logits, cudaStream_t st, ChunkReduce *reduce = nullptr);
 
    private:
-    void launch_token_pass(bool from_prompt, int prompt_idx, int pos_value, bool want_logits, cudaStream_t st, int *n_launch);
+    void launch_token_pass(bool from_prompt, int prompt_idx, int pos_value, bool want_logits, cudaStream_t st, int *n_launch,
+                           bool long_attn = false);
     void prefill_tc(int idx0, int T, int pos0, bool want_logits, cudaStream_t st);     // the same on the tensor-core path
-    void ensure_graph(const aios_sampling &sp);
+    cudaGraphExec_t ensure_graph(const aios_sampling &sp, bool long_attn);
     void build_pfd();
     bool use_pfd(const aios_sampling &sp) const;
     void launch_pfd_tokens(int n, cudaStream_t st);

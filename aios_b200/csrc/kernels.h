@@ -158,6 +158,28 @@ struct AttnParams {
     const int32_t *lane_pos;
     uint16_t *const *lane_kv;
 };
+// ---- attention_long.cu : one token over a long context — CTA = (kv head, slice of the positions), the GQA group's
+// query heads sharing every K / V row; one launch, the CTAs of a kv head meeting at two device-counter barriers.  Same
+// arithmetic, bit for bit.
+struct AttnLongParams {
+    const float *qkv;
+    float *out;
+    const uint16_t *k_cache, *v_cache;
+    int32_t kv_stride;
+    const int32_t *n_past_ptr;
+    float scale;
+    int32_t n_head, n_kv, hd, n_ctx, n_slices, chunk_cap;
+    float *smax;         // [n_head][n_slices] slice maxima
+    double *ssum;        // [n_head][n_slices] slice shares of the row sums
+    double *opart;       // [n_slices][n_head][hd] partial P.V sums
+    unsigned *counters;  // [n_kv][3]: two barrier counters and the finished-slice counter (they only ever count up)
+};
+bool attn_long_usable(int n_head, int n_kv, int n_ctx, int hd);
+int attn_long_slices(int n_kv, int n_sms);
+size_t attn_long_scratch_bytes(int n_head, int n_kv, int n_ctx, int hd, int n_slices);  // zero it once
+// a = the AttnParams of a kv_ready split launch (qkv, out, caches, n_past_ptr, shapes, scale)
+void launch_attn_long(const AttnParams &a, void *scratch, int n_slices, cudaStream_t st, bool pdl);
+
 // mode: 0 = pick (split kernel when usable, else cluster); 2 = cluster kernel
 void launch_attn_decode(const AttnParams &p, cudaStream_t st, bool pdl = false, int mode = 0);
 // one wave of independent (query head, head-dim slice) CTAs, launched with PDL (attention_split.cu)

@@ -319,3 +319,40 @@ def test_engine_variants_are_bit_identical(engine, oracle, tmp_models, flag):
         m1.unload()
         m2.unload()
         other.close()
+
+
+@pytest.mark.parametrize("arch,n_prompt,n_ctx", [("tiny-gqa4", 700, 1024), ("tiny", 37, 1024), ("tiny-mha32", 150, 1024),
+                                                 ("tiny-gqa4", 300, 5000)])
+def test_long_context_attention_is_bit_identical(oracle, tmp_models, monkeypatch, arch, n_prompt, n_ctx):
+    """attention_long.cu (CTA = kv head x slice of the positions, GQA heads sharing K / V rows, two launches) must give
+    the latency kernel's and the oracle's results bit for bit: sums of exact f16 x f16 products in double do not care
+    how the positions are cut.  AIOS_ATTN_LONG_MIN = 1 forces it from the first decoded token; the second decode call
+    crosses a slice-size boundary (slices are multiples of 32 rows).  With n_ctx beyond the latency kernel's 4096 rows
+    it is the decode attention at every position, threshold or not."""
+    path = tmp_models(arch, "Q4_K_M")
+    prompt = gs.synthetic_prompt(arch, n_prompt, 13)
+    om = oracle.OracleModel(path, n_ctx=1024)
+    ref, _ = om.greedy(prompt, 48)
+    if n_ctx <= 4096:
+        monkeypatch.setenv("AIOS_ATTN_LONG_MIN", "1")
+    for flags in (0, capi.ENGINE_NO_GRAPH):
+        eng = capi.Engine(device=0, max_batch=1, flags=flags | capi.ENGINE_EXACT_PREFILL)
+        try:
+            m = eng.load_model("long", path, n_ctx=n_ctx)
+            try:
+                s = m.new_seq()
+                s.prefill(prompt)
+                got = np.concatenate([s.decode(20), s.decode(28)])
+                assert np.array_equal(got, ref), (flags, got, ref)
+                want_logits = om.eval(np.concatenate([prompt, ref[:-1]]))
+                # the logits after feeding the 47th generated token (what the 48th was sampled from)
+                s.free()
+                s = m.new_seq()
+                s.prefill(prompt)
+                s.decode(47)
+                assert np.array_equal(s.logits().view(np.uint32), want_logits.view(np.uint32))
+                s.free()
+            finally:
+                m.unload()
+        finally:
+            eng.close()
