@@ -50,7 +50,7 @@ Engine::Engine(const aios_engine_opts &o) : device(o.device), max_batch(o.max_ba
     n_sms = prop.multiProcessorCount;
     CUDA_CHECK(cudaStreamCreateWithFlags(&stream, cudaStreamNonBlocking));
     if (const char *e = getenv("AIOS_EVICT_FIRST")) evict_first = atoi(e) != 0;
-    if (const char *e = getenv("AIOS_ATTN_LONG_MIN")) attn_long_min = atoi(e);
+    if (const char *e = getenv("AIOS_ATTN_LONG_MIN")) attn_long_min = std::max(1, std::min(4096, atoi(e)));
     // function attributes are per-device settings: every engine sets them for its own device
     gemv_init();
     attn_split_init();
@@ -371,7 +371,11 @@ void Seq::build_token_pass(bool want_logits, std::vector<PassLaunch> &ls, bool l
     // (EPI_QKV_ROPE): the attention kernel then starts on final data, with no dependent table loads of its own
     // (the position-split kernel of attention_long.cu takes such launches too: it is the decode attention of contexts
     // beyond the split kernel's 4096 rows, and of long contexts below that)
-    const bool split_ok = attn_split_usable(hp.n_ctx, hp.head_dim), long_ok = attn_long_scratch.p != nullptr;
+    // With the position-split kernel taking over at attn_long_min (<= 4096) rows, the latency kernel never sees more
+    // than that: a model loaded with a bigger n_ctx still starts on it, its shared-memory score row sized for 4096.
+    const bool long_ok = attn_long_scratch.p != nullptr;
+    const int split_ctx = long_ok ? std::min(hp.n_ctx, 4096) : hp.n_ctx;
+    const bool split_ok = attn_split_usable(split_ctx, hp.head_dim);
     const bool rope_in_gemv = amode == 0 && (split_ok || long_ok) && !(m->eng->flags & AIOS_ENGINE_NO_ROPE_EPILOGUE);
     ls.clear();
     ls.reserve((size_t)hp.n_layer * 6 + 2);
@@ -432,6 +436,7 @@ void Seq::build_token_pass(bool want_logits, std::vector<PassLaunch> &ls, bool l
             a.scale = 1.0f / sqrtf((float)hp.head_dim);
             a.kv_ready = kv_ready ? 1 : 0;
             if (kv_ready && long_ok && (long_attn || !split_ok)) A.kind = 2;  // the position-split kernel
+            else if (kv_ready && long_ok) a.n_ctx = split_ctx;
             ls.push_back(A);
         }
         {   // attention output projection + residual add
@@ -535,7 +540,7 @@ void Seq::prefill(const int32_t *tokens, int n) {
             prefill_chunk(i, T, n_past + i, i + T == n, st);
         }
     } else {
-        for (int i = 0; i < n; i++) launch_token_pass(true, i, n_past + i, i == n - 1, st, nullptr);
+        for (int i = 0; i < n; i++) launch_token_pass(true, i, n_past + i, i == n - 1, st, nullptr, want_long_attn(n_past + i + 1));
     }
     CUDA_CHECK(cudaGetLastError());
     CUDA_CHECK(cudaStreamSynchronize(st));
@@ -836,7 +841,7 @@ void Seq::profile_decode(int n_tokens, aios_bench_result *out) {
         for (int i = 0; i < steps; i++) {
             launch_sample_kernel(sp, st);
             launches++;
-            launch_token_pass(false, 0, 0, true, st, &launches);
+            launch_token_pass(false, 0, 0, true, st, &launches, want_long_attn(n_past + i + 1));
         }
         CUDA_CHECK(cudaStreamSynchronize(st));
     } catch (...) {
@@ -883,11 +888,11 @@ int Seq::trace_decode(unsigned long long *out, int cap_launches) {
     CUDA_CHECK(cudaMemsetAsync(trace.p, 0, trace.bytes, st));
     int launches = 0;
     launch_sample_kernel(sp, st);
-    launch_token_pass(false, 0, 0, true, st, nullptr);
+    launch_token_pass(false, 0, 0, true, st, nullptr, want_long_attn(n_past + 1));
     launch_sample_kernel(sp, st);
     trace_base = trace.as<unsigned long long>();
     try {
-        launch_token_pass(false, 0, 0, true, st, &launches);
+        launch_token_pass(false, 0, 0, true, st, &launches, want_long_attn(n_past + 2));
         CUDA_CHECK(cudaStreamSynchronize(st));
     } catch (...) {
         trace_base = nullptr;
