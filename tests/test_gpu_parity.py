@@ -321,21 +321,23 @@ def test_engine_variants_are_bit_identical(engine, oracle, tmp_models, flag):
         other.close()
 
 
-@pytest.mark.parametrize("arch,n_prompt,n_ctx", [("tiny-gqa4", 700, 1024), ("tiny", 37, 1024), ("tiny-mha32", 150, 1024),
-                                                 ("tiny-gqa4", 300, 5000), ("tiny", 90, 6000)])
-def test_long_context_attention_is_bit_identical(oracle, tmp_models, monkeypatch, arch, n_prompt, n_ctx):
+@pytest.mark.parametrize("arch,n_prompt,n_ctx,long_min", [("tiny-gqa4", 700, 1024, 1), ("tiny", 37, 1024, 1), ("tiny-mha32", 150, 1024, 1),
+                                                          ("tiny-gqa4", 300, 5000, None), ("tiny", 90, 6000, 1),
+                                                          ("tiny-gqa4", 300, 1024, 325), ("tiny-gqa4", 300, 5000, 325)])
+def test_long_context_attention_is_bit_identical(oracle, tmp_models, monkeypatch, arch, n_prompt, n_ctx, long_min):
     """attention_long.cu (CTA = kv head x slice of the positions, GQA heads sharing K / V rows, two launches) must give
     the latency kernel's and the oracle's results bit for bit: sums of exact f16 x f16 products in double do not care
     how the positions are cut.  AIOS_ATTN_LONG_MIN = 1 forces it from the first decoded token; the second decode call
     crosses a slice-size boundary (slices are multiples of 32 rows).  A model loaded with n_ctx beyond the latency
     kernel's 4096 rows starts on the latency kernel (sized for 4096 rows) and switches at the default threshold: the
-    (300, 5000) case runs that configuration as loaded, below the threshold."""
+    (300, 5000, default) case runs that configuration as loaded, below the threshold; a threshold of 325 makes the
+    decode calls switch kernels (and captured graphs) in mid-call."""
     path = tmp_models(arch, "Q4_K_M")
     prompt = gs.synthetic_prompt(arch, n_prompt, 13)
     om = oracle.OracleModel(path, n_ctx=1024)
     ref, _ = om.greedy(prompt, 48)
-    if n_ctx != 5000:
-        monkeypatch.setenv("AIOS_ATTN_LONG_MIN", "1")
+    if long_min is not None:
+        monkeypatch.setenv("AIOS_ATTN_LONG_MIN", str(long_min))
     for flags in (0, capi.ENGINE_NO_GRAPH):
         eng = capi.Engine(device=0, max_batch=1, flags=flags | capi.ENGINE_EXACT_PREFILL)
         try:
