@@ -80,8 +80,12 @@ __device__ __forceinline__ void al_group_barrier(unsigned *ctr, int n_ctas) {
 template <int HD>
 __global__ void __launch_bounds__(AL_THREADS) attn_long_kernel(const AttnLongParams p) {
     constexpr int LPR = HD / 8, RPW = 32 / LPR;
+    unsigned long long *tr = (blockIdx.x == 0 && blockIdx.y == 0 && threadIdx.x == 0) ? p.trace : nullptr;
+    trace_mark(tr, 0);
+    if (tr) tr[3] = 2ull;  // launch kind: attention
     pdl_launch_dependents();
     pdl_wait();
+    trace_mark(tr, 1);
     const int g = blockIdx.x, s = blockIdx.y;
     const int rep = p.n_head / p.n_kv;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -172,6 +176,7 @@ __global__ void __launch_bounds__(AL_THREADS) attn_long_kernel(const AttnLongPar
         __syncthreads();
     }
     al_group_barrier(bar + 0, p.n_slices);
+    trace_mark(tr, 2);
 
     // ---- phase B: e = expf(s - row maximum) for the slice; the slice's share of the row sums
     if ((int)threadIdx.x < rep) {
@@ -289,6 +294,12 @@ __global__ void __launch_bounds__(AL_THREADS) attn_long_kernel(const AttnLongPar
             p.out[hd_idx] = (float)t;
         }
     }
+    trace_mark(tr, 4);
+    if (p.trace && threadIdx.x == 0) {  // [7]: when the last CTA of the launch finished
+        unsigned long long now;
+        asm volatile("mov.u64 %0, %globaltimer;" : "=l"(now));
+        atomicMax(p.trace + 7, now);
+    }
 }
 
 // ---------------------------------------------------------------- host side
@@ -318,6 +329,7 @@ void launch_attn_long(const AttnParams &a, void *scratch, int n_slices, cudaStre
     p.ssum = reinterpret_cast<double *>(b); b += (size_t)a.n_head * n_slices * 8;
     p.smax = reinterpret_cast<float *>(b); b += (size_t)a.n_head * n_slices * 4;
     p.counters = reinterpret_cast<unsigned *>(b);
+    p.trace = a.trace;
     const size_t smem = al_smem_bytes(a.n_head / a.n_kv, a.n_ctx, n_slices, a.hd);
     static PerDeviceOnce once;
     once.run([] {

@@ -485,6 +485,7 @@ void Seq::launch_pass_item(PassLaunch &L, cudaStream_t st, int launch_index) {
         L.g.trace = tr;
         TIMED(0, launch_gemv(L.g, L.grid, st, L.pdl));
     } else if (L.kind == 2) {
+        L.a.trace = tr;
         TIMED(1, launch_attn_long(L.a, attn_long_scratch.p, attn_long_n_slices, st, L.pdl));
     } else {
         L.a.trace = tr;

@@ -173,6 +173,7 @@ struct AttnLongParams {
     double *ssum;        // [n_head][n_slices] slice shares of the row sums
     double *opart;       // [n_slices][n_head][hd] partial P.V sums
     unsigned *counters;  // [n_kv][3]: two barrier counters and the finished-slice counter (they only ever count up)
+    unsigned long long *trace;  // CTA (0, 0), null = off: [0] entry [1] wait over [2] scores done [3] = 2 [4] CTA done [7] last CTA done
 };
 bool attn_long_usable(int n_head, int n_kv, int n_ctx, int hd);
 int attn_long_slices(int n_kv, int n_sms);
