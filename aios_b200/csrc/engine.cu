@@ -305,7 +305,7 @@ Seq::Seq(Model *m_, bool internal_) : m(m_), internal(internal_) {
         CUDA_CHECK(cudaMemset(pfd_att_acc.p, 0, pfd_att_acc.bytes));
         CUDA_CHECK(cudaMemset(pfd_counters.p, 0, pfd_counters.bytes));
         if (m->tp_size > 1) tp_part64 = DevBuf((size_t)hp.n_embd * sizeof(double));
-        if (m->tp_size == 1 && attn_long_usable(hp.n_head, hp.n_head_kv, hp.n_ctx, hp.head_dim) &&
+        if (attn_long_usable(hp.n_head, hp.n_head_kv, hp.n_ctx, hp.head_dim) &&
             (hp.n_ctx >= m->eng->attn_long_min || !attn_split_usable(hp.n_ctx, hp.head_dim))) {
             attn_long_n_slices = attn_long_slices(hp.n_head_kv, m->eng->n_sms);
             attn_long_scratch = DevBuf(attn_long_scratch_bytes(hp.n_head, hp.n_head_kv, hp.n_ctx, hp.head_dim, attn_long_n_slices));

@@ -158,7 +158,9 @@ struct TpRank {
     DevBuf xchg;
     double *slabs = nullptr;
     unsigned *flags = nullptr, *lflags = nullptr, *done = nullptr, *tick = nullptr, *err = nullptr;
-    cudaGraphExec_t graph = nullptr;  // one decode step: sample, tick, embed, the layers, lm_head, logits wait
+    // one decode step (sample, tick, embed, the layers, lm_head, logits wait): [0] with the latency attention kernel,
+    // [1] with the position-split one (long contexts)
+    cudaGraphExec_t graph[2] = {nullptr, nullptr};
 };
 
 struct TpModelImpl {
@@ -172,11 +174,12 @@ struct TpModelImpl {
     void check_push_errors();
     // push mode: one CUDA graph per rank holds a whole decode step (no host-side collective call is left in it)
     bool use_graphs = false;
-    bool graphs_built = false;
-    aios_sampling graph_sp{};
+    bool graphs_built[2] = {false, false};
+    aios_sampling graph_sp[2] = {};
     int graph_launches = 0;  // kernels inside one rank's graph
-    void rank_step(int r, const aios_sampling &sp, int *launches);
-    void ensure_graphs(const aios_sampling &sp);
+    void rank_step(int r, const aios_sampling &sp, int *launches, bool long_attn);
+    void ensure_graphs(const aios_sampling &sp, bool long_attn);
+    bool want_long(int n_pos) const { return ranks[0].seq->want_long_attn(n_pos); }
     void decode_steps(const aios_sampling &sp, int n_steps, int *launches);
     // all-reduce timing (rank 0's stream), filled when timing is on
     bool timing = false;
@@ -185,7 +188,8 @@ struct TpModelImpl {
     ~TpModelImpl() {
         for (auto &r : ranks) {
             if (r.eng) cudaSetDevice(r.eng->device);
-            if (r.graph) cudaGraphExecDestroy(r.graph);
+            for (auto &gx : r.graph)
+                if (gx) cudaGraphExecDestroy(gx);
             r.seq.reset();
             r.xchg = DevBuf();
             r.model.reset();
@@ -197,15 +201,23 @@ struct TpModelImpl {
     const HParams &hp() const { return ranks[0].model->hp; }
     void all_reduce_add_to_x(int reduce_index);
     // one token through every rank's shard in lockstep; launches counts rank 0's kernels (collectives included)
-    void token_pass(bool from_prompt, int prompt_idx, int pos_value, bool want_logits, int *launches);
+    void token_pass(bool from_prompt, int prompt_idx, int pos_value, bool want_logits, int *launches, bool long_attn = false);
     void gather_logits();
     bool chunks_usable() const;
     void prefill_chunks(int n_tokens);  // tokens already in every rank's prompt buffer; asynchronous on the streams
     void sample_all(const aios_sampling &sp);
     void sync_all();
     void set_pos_step();
-    std::vector<std::vector<PassLaunch>> lists;  // per rank; [0] without, rebuilt when want_logits changes
-    int lists_logits = -1;
+    // the token pass as launch lists per rank, by (want_logits, long_attn); built on first use
+    std::vector<std::vector<PassLaunch>> list_cache[2][2];
+    std::vector<std::vector<PassLaunch>> &lists_for(bool want_logits, bool long_attn) {
+        auto &L = list_cache[want_logits ? 1 : 0][long_attn ? 1 : 0];
+        if (L.empty()) {
+            L.resize((size_t)n);
+            for (int r = 0; r < n; r++) ranks[(size_t)r].seq->build_token_pass(want_logits, L[(size_t)r], long_attn);
+        }
+        return L;
+    }
 };
 
 void TpModelImpl::sync_all() {
@@ -327,12 +339,8 @@ void TpModelImpl::check_push_errors() {
     }
 }
 
-void TpModelImpl::token_pass(bool from_prompt, int prompt_idx, int pos_value, bool want_logits, int *launches) {
-    if (lists_logits != (int)want_logits) {
-        lists.resize((size_t)n);
-        for (int r = 0; r < n; r++) ranks[(size_t)r].seq->build_token_pass(want_logits, lists[(size_t)r]);
-        lists_logits = (int)want_logits;
-    }
+void TpModelImpl::token_pass(bool from_prompt, int prompt_idx, int pos_value, bool want_logits, int *launches, bool long_attn) {
+    auto &lists = lists_for(want_logits, long_attn);
     int li = 0, n_reduce = 0;
     for (auto &r : ranks) {
         r.eng->make_current();
@@ -424,11 +432,7 @@ void TpModelImpl::prefill_chunks(int n_tokens) {
     for (auto &e : errs)
         if (e) std::rethrow_exception(e);
     // the logits of the last token: lm_head on every shard's slice, then the gather
-    if (lists_logits != 1) {
-        lists.resize((size_t)n);
-        for (int r = 0; r < n; r++) ranks[(size_t)r].seq->build_token_pass(true, lists[(size_t)r]);
-        lists_logits = 1;
-    }
+    auto &lists = lists_for(true, false);
     for (int r = 0; r < n; r++) {
         TpRank &R = ranks[(size_t)r];
         R.eng->make_current();
@@ -450,7 +454,7 @@ void TpModelImpl::set_pos_step() {
 }
 
 // one decode step of ONE rank, in stream order (push mode only: the ranks meet through flags, not through the host)
-void TpModelImpl::rank_step(int r, const aios_sampling &sp, int *launches) {
+void TpModelImpl::rank_step(int r, const aios_sampling &sp, int *launches, bool long_attn) {
     TpRank &R = ranks[(size_t)r];
     R.eng->make_current();
     cudaStream_t st = R.eng->stream;
@@ -460,7 +464,7 @@ void TpModelImpl::rank_step(int r, const aios_sampling &sp, int *launches) {
     tp_tick_kernel<<<1, 1, 0, st>>>(R.tick);
     R.seq->launch_embed(false, 0, 0, st);
     li += 3;
-    for (PassLaunch &L : lists[(size_t)r]) {
+    for (PassLaunch &L : lists_for(true, long_attn)[(size_t)r]) {
         R.seq->launch_pass_item(L, st, li++);
         if (L.reduce_after) {
             launch_wait_add(R.seq->x.as<float>(), R.slabs, R.flags, R.tick, per_token, n_reduce++, n, E, R.err, st, pdl_wait);
@@ -472,52 +476,52 @@ void TpModelImpl::rank_step(int r, const aios_sampling &sp, int *launches) {
     if (launches) *launches = li;
 }
 
-void TpModelImpl::ensure_graphs(const aios_sampling &sp) {
-    if (graphs_built && !memcmp(&sp, &graph_sp, sizeof(sp))) return;
-    if (lists_logits != 1) {
-        lists.resize((size_t)n);
-        for (int r = 0; r < n; r++) ranks[(size_t)r].seq->build_token_pass(true, lists[(size_t)r]);
-        lists_logits = 1;
-    }
+void TpModelImpl::ensure_graphs(const aios_sampling &sp, bool long_attn) {
+    const int v = long_attn ? 1 : 0;
+    if (graphs_built[v] && !memcmp(&sp, &graph_sp[v], sizeof(sp))) return;
+    lists_for(true, long_attn);
     sync_all();
     for (int r = 0; r < n; r++) {
         TpRank &R = ranks[(size_t)r];
         R.eng->make_current();
-        if (R.graph) { cudaGraphExecDestroy(R.graph); R.graph = nullptr; }
+        if (R.graph[v]) { cudaGraphExecDestroy(R.graph[v]); R.graph[v] = nullptr; }
         cudaGraph_t g = nullptr;
         CUDA_CHECK(cudaStreamBeginCapture(R.eng->stream, cudaStreamCaptureModeThreadLocal));
         try {
-            rank_step(r, sp, &graph_launches);
+            rank_step(r, sp, &graph_launches, long_attn);
         } catch (...) {
             cudaStreamEndCapture(R.eng->stream, &g);
             if (g) cudaGraphDestroy(g);
             throw;
         }
         CUDA_CHECK(cudaStreamEndCapture(R.eng->stream, &g));
-        const cudaError_t e = cudaGraphInstantiate(&R.graph, g, 0);
+        const cudaError_t e = cudaGraphInstantiate(&R.graph[v], g, 0);
         cudaGraphDestroy(g);
         CUDA_CHECK(e);
     }
-    graph_sp = sp;
-    graphs_built = true;
+    graph_sp[v] = sp;
+    graphs_built[v] = true;
 }
 
 // n_steps x (sample the next token from the logits, feed it); asynchronous
 void TpModelImpl::decode_steps(const aios_sampling &sp, int n_steps, int *launches) {
+    // step i feeds the token at position n_past + i: n_past + i + 1 rows to attend to (n_past is the caller's)
     if (use_graphs && !timing) {
-        ensure_graphs(sp);
-        for (int i = 0; i < n_steps; i++)
+        for (int i = 0; i < n_steps; i++) {
+            const bool la = want_long(n_past + i + 1);
+            ensure_graphs(sp, la);
             for (auto &R : ranks) {
                 R.eng->make_current();
-                CUDA_CHECK(cudaGraphLaunch(R.graph, R.eng->stream));
+                CUDA_CHECK(cudaGraphLaunch(R.graph[la ? 1 : 0], R.eng->stream));
             }
+        }
         if (launches) *launches += n_steps * graph_launches;
         return;
     }
     for (int i = 0; i < n_steps; i++) {
         sample_all(sp);
         if (launches) (*launches)++;
-        token_pass(false, 0, 0, true, launches);
+        token_pass(false, 0, 0, true, launches, want_long(n_past + i + 1));
     }
 }
 
@@ -596,7 +600,7 @@ void TpModel::prefill(const int32_t *tokens, int n) {
     }
     if (n >= 4 && impl->chunks_usable()) impl->prefill_chunks(n);
     else
-        for (int i = 0; i < n; i++) impl->token_pass(true, i, impl->n_past + i, i == n - 1, nullptr);
+        for (int i = 0; i < n; i++) impl->token_pass(true, i, impl->n_past + i, i == n - 1, nullptr, impl->want_long(impl->n_past + i + 1));
     impl->sync_all();
     impl->check_push_errors();
     impl->n_past += n;

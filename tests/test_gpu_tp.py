@@ -125,3 +125,22 @@ def test_runtime_serves_a_tensor_parallel_model(tmp_path):
         assert not be.alive(lm)
     finally:
         be.close()
+
+
+@pytest.mark.parametrize("n_ctx,long_min", [(512, 1), (512, 50), (5000, None)])
+def test_tp_long_context_attention(oracle, tmp_models, monkeypatch, n_ctx, long_min):
+    """The shards switch to the position-split attention kernel like a single GPU does (forced from the first token,
+    switched in mid-call, and a context beyond the latency kernel's 4096 rows as loaded): same tokens as the oracle."""
+    _need_gpus(2)
+    if long_min is not None:
+        monkeypatch.setenv("AIOS_ATTN_LONG_MIN", str(long_min))
+    path = tmp_models("tiny-gqa4", "Q4_K_M")
+    prompt = gs.synthetic_prompt("tiny-gqa4", 40, 21)
+    om = oracle.OracleModel(path, n_ctx=128)
+    ref, _ = om.greedy(prompt, 32)
+    for flags in (0, capi.ENGINE_NO_GRAPH):
+        tp = capi.TpModel([0, 1], "tp", path, n_ctx=n_ctx, flags=flags)
+        try:
+            assert np.array_equal(tp.generate(prompt, 32), ref)
+        finally:
+            tp.unload()
