@@ -39,7 +39,7 @@ __device__ __forceinline__ void ab_row_to_f64(const uint4 &v, double (&x)[8]) {
     x[4] = ab_h2d_lo(v.z); x[5] = ab_h2d_hi(v.z); x[6] = ab_h2d_lo(v.w); x[7] = ab_h2d_hi(v.w);
 }
 
-// dynamic smem: sc[rep][n_cap] f32 | qd[rep][HD] f64 | part[AB_WARPS][2][AB_HP][8 * LPR ... ] (see below)
+// dynamic smem: sc[min(rep, AB_HP)][n_cap] f32 (one pass of heads at a time) | qd[rep][HD] f64 | part[AB_WARPS][2][AB_HP][8 * LPR ... ] (see below)
 template <int HD>
 __global__ void __launch_bounds__(AB_THREADS, 2) attn_batch_kernel(const AttnBatchParams p) {
     constexpr int LPR = HD / 8;          // lanes per row (8 dims = one 16-byte load per lane)
@@ -58,8 +58,9 @@ __global__ void __launch_bounds__(AB_THREADS, 2) attn_batch_kernel(const AttnBat
 
     extern __shared__ __align__(16) uint8_t ab_smem[];
     const int n_cap = (p.n_ctx + 3) & ~3;
-    float *sc = reinterpret_cast<float *>(ab_smem);                               // [rep][n_cap]
-    double *qd = reinterpret_cast<double *>(ab_smem + (size_t)rep * n_cap * 4);   // [rep][HD]
+    const int sc_heads = min(rep, AB_HP);                                         // score rows of ONE pass of heads
+    float *sc = reinterpret_cast<float *>(ab_smem);                               // [sc_heads][n_cap]
+    double *qd = reinterpret_cast<double *>(ab_smem + (size_t)sc_heads * n_cap * 4);  // [rep][HD]
     double *part = qd + (size_t)rep * HD;                                         // [AB_WARPS][AB_HP][HD]
     __shared__ float sh_max[AB_WARPS][8];
     __shared__ double sh_sum[AB_WARPS][8];
@@ -153,7 +154,7 @@ __global__ void __launch_bounds__(AB_THREADS, 2) attn_batch_kernel(const AttnBat
                 for (int o = MB / 2; o > 0; o >>= 1) tot += __shfl_xor_sync(0xffffffffu, tot, o);
                 if (h < nh && j < n_pos && (lane & (MB - 1)) == 0) {
                     const float s = __fmul_rn((float)tot, p.scale);
-                    sc[(size_t)(h0 + h) * n_cap + j] = s;
+                    sc[(size_t)h * n_cap + j] = s;
                     wmax[h] = fmaxf(wmax[h], s);
                 }
             }
@@ -178,7 +179,7 @@ __global__ void __launch_bounds__(AB_THREADS, 2) attn_batch_kernel(const AttnBat
                 ps[h] = 0.0;
                 if (h < nh) {
                     const float mx = s_mx[h];
-                    float *row = sc + (size_t)(h0 + h) * n_cap;
+                    float *row = sc + (size_t)h * n_cap;
                     for (int j = threadIdx.x; j < n_pos; j += AB_THREADS) {
                         const float e = expf_det(__fsub_rn(row[j], mx));
                         row[j] = e;
@@ -222,7 +223,7 @@ __global__ void __launch_bounds__(AB_THREADS, 2) attn_batch_kernel(const AttnBat
 #pragma unroll
                     for (int h = 0; h < AB_HP; h++) {
                         if (h < nh) {
-                            const double pj = (double)__half2float(__float2half_rn(__fmul_rn(sc[(size_t)(h0 + h) * n_cap + j], inv[h])));
+                            const double pj = (double)__half2float(__float2half_rn(__fmul_rn(sc[(size_t)h * n_cap + j], inv[h])));
 #pragma unroll
                             for (int e = 0; e < 8; e++) o[h][e] = fma(vd[e], pj, o[h][e]);
                         }
@@ -260,7 +261,7 @@ __global__ void __launch_bounds__(AB_THREADS, 2) attn_batch_kernel(const AttnBat
 
 static size_t ab_smem_bytes(int rep, int n_ctx, int hd) {
     const size_t n_cap = ((size_t)n_ctx + 3) & ~(size_t)3;
-    return (size_t)rep * n_cap * 4 + (size_t)rep * hd * 8 + (size_t)AB_WARPS * AB_HP * hd * 8;
+    return (size_t)std::min(rep, AB_HP) * n_cap * 4 + (size_t)rep * hd * 8 + (size_t)AB_WARPS * AB_HP * hd * 8;
 }
 
 bool attn_batch_usable(int n_head, int n_kv, int n_ctx, int hd) {

@@ -311,6 +311,7 @@ __global__ void __launch_bounds__(GEMV_THREADS, 1) gemv_db_mixed_kernel(const Ge
     __shared__ double red[GEMV_WARPS];
     const int seg = gemv_my_segment(p);
     if (p.seg[seg].type == T_Q6_K) gemv_db_body<T_Q6_K, 2>(p, seg, smem, red);
+    else if (p.seg[seg].type == T_Q5_K) gemv_db_body<T_Q5_K, 2>(p, seg, smem, red);
     else gemv_db_body<T_Q4_K, 2>(p, seg, smem, red);
 }
 
@@ -371,15 +372,16 @@ void gemv_init() {
     });
 }
 
-// Q4_K and Q6_K matrices may share a launch (gemv_db_mixed_kernel) when K is a whole number of 2048-weight passes
+// Q4_K, Q5_K and Q6_K matrices may share a launch (gemv_db_mixed_kernel) when K is a whole number of 2048-weight passes
+// (70B-class Q4_K_M files: attn_q / attn_k Q4_K next to an attn_v of Q5_K or Q6_K)
 bool gemv_can_mix(const GemvParams &p) {
     if (g_use_db != 2 || p.epi == EPI_SWIGLU || (p.k / 64) % 32 != 0) return false;
     for (int i = 0; i < p.n_seg; i++)
-        if (p.seg[i].type != T_Q4_K && p.seg[i].type != T_Q6_K) return false;
+        if (p.seg[i].type != T_Q4_K && p.seg[i].type != T_Q5_K && p.seg[i].type != T_Q6_K) return false;
     return true;
 }
 
-// All segments of a launch must have one type, except for the Q4_K + Q6_K mix gemv_can_mix() allows.
+// All segments of a launch must have one type, except for the K-quant mixes gemv_can_mix() allows.
 void launch_gemv(const GemvParams &p_in, int grid, cudaStream_t st, bool pdl) {
     const GemvParams &p = p_in;
     const int t = p.seg[0].type;

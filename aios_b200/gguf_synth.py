@@ -56,6 +56,8 @@ ARCHS = {
     "tiny": Arch("tiny", 2, 256, 4, 2, 64, 512, 512, 10000.0, 1e-5, 512),
     "tiny1": Arch("tiny1", 1, 256, 4, 2, 64, 512, 512, 10000.0, 1e-5, 512),
     "tiny-gqa4": Arch("tiny-gqa4", 3, 512, 8, 2, 64, 1024, 1000, 10000.0, 1e-5, 512),
+    # one kv head for eight query heads (Llama-3-70B's group size): attention kernels take two passes of four heads
+    "tiny-gqa8": Arch("tiny-gqa8", 2, 512, 8, 1, 64, 1024, 512, 10000.0, 1e-5, 512),
     # multi-head attention with 32 kv heads (Llama-2-7B's head layout on a small width)
     "tiny-mha32": Arch("tiny-mha32", 2, 2048, 32, 32, 64, 512, 512, 10000.0, 1e-5, 512),
     # splits four ways (tensor-parallel tests): 4 kv heads, n_head*head_dim / 4 and FF / 4 multiples of 256

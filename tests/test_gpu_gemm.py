@@ -41,7 +41,7 @@ def test_matmul_with_rmsnorm_equals_matvec(engine, qt):
         assert np.array_equal(got[i].view(np.uint32), ref.view(np.uint32)), i
 
 
-@pytest.mark.parametrize("arch,ftype", [("tiny", "Q4_K_M"), ("tiny-gqa4", "Q4_K_M"), ("tiny", "Q8_0"), ("tiny-gqa4", "Q4_K_M_70B")])
+@pytest.mark.parametrize("arch,ftype", [("tiny", "Q4_K_M"), ("tiny-gqa4", "Q4_K_M"), ("tiny", "Q8_0"), ("tiny-gqa4", "Q4_K_M_70B"), ("tiny-gqa8", "Q4_K_M_70B")])
 @pytest.mark.parametrize("n_prompt", [4, 33, 70, 121])
 def test_chunked_prefill_is_bit_identical_to_token_by_token(engine, oracle, tmp_models, arch, ftype, n_prompt):
     """Seq::prefill feeds prompts in 64-token chunks through the GEMM; logits, KV rows and the continuation must be

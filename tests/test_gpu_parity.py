@@ -323,7 +323,8 @@ def test_engine_variants_are_bit_identical(engine, oracle, tmp_models, flag):
 
 @pytest.mark.parametrize("arch,n_prompt,n_ctx,long_min", [("tiny-gqa4", 700, 1024, 1), ("tiny", 37, 1024, 1), ("tiny-mha32", 150, 1024, 1),
                                                           ("tiny-gqa4", 300, 5000, None), ("tiny", 90, 6000, 1),
-                                                          ("tiny-gqa4", 300, 1024, 325), ("tiny-gqa4", 300, 5000, 325)])
+                                                          ("tiny-gqa4", 300, 1024, 325), ("tiny-gqa4", 300, 5000, 325),
+                                                          ("tiny-gqa8", 200, 1024, 1)])
 def test_long_context_attention_is_bit_identical(oracle, tmp_models, monkeypatch, arch, n_prompt, n_ctx, long_min):
     """attention_long.cu (CTA = kv head x slice of the positions, GQA heads sharing K / V rows, two launches) must give
     the latency kernel's and the oracle's results bit for bit: sums of exact f16 x f16 products in double do not care

@@ -101,15 +101,17 @@ def test_request_argument_errors(model):
     r.free()
 
 
-def test_64_concurrent_requests_equal_one_by_one(engine, tmp_models):
+@pytest.mark.parametrize("arch,ftype", [("tiny-gqa4", "Q4_K_M"), ("tiny-gqa8", "Q4_K_M_70B")])
+def test_64_concurrent_requests_equal_one_by_one(engine, tmp_models, arch, ftype):
     """Continuous batching (BASELINE.json configs[3]: 64 concurrent agent requests per GPU): 64 requests submitted at
     once decode together — one token per request per step through the multi-token GEMM — and every one of them must
     return exactly the tokens the same prompt gives alone, greedy, bit for bit.  Prompts and lengths differ, so requests
-    join and leave the batch at different steps."""
-    m = engine.load_model("b64", tmp_models("tiny-gqa4", "Q4_K_M"), n_ctx=192)
+    join and leave the batch at different steps.  The second model has eight query heads per kv head (two passes of the
+    batched attention kernel) and the 70B type mix (Q5_K attn_v next to Q4_K q / k in one launch)."""
+    m = engine.load_model("b64", tmp_models(arch, ftype), n_ctx=192)
     try:
         rng = np.random.default_rng(5)
-        prompts = [gs.synthetic_prompt("tiny-gqa4", int(rng.integers(3, 60)), 1000 + i) for i in range(64)]
+        prompts = [gs.synthetic_prompt(arch, int(rng.integers(3, 60)), 1000 + i) for i in range(64)]
         n_gen = [int(rng.integers(1, 90)) for _ in range(64)]
         want = [m.generate(p, n) for p, n in zip(prompts, n_gen)]
         reqs = [m.submit(p, n) for p, n in zip(prompts, n_gen)]
