@@ -343,6 +343,9 @@ void Seq::reset() {
         CUDA_CHECK(cudaStreamSynchronize(m->eng->stream));
         kv.trim(1);
     }
+    // the position-split attention's barrier counters only count up: a sequence's worth of launches fits 32 bits many
+    // times over, a pooled sequence object that serves requests for days does not — start every sequence at zero
+    if (attn_long_scratch.p) CUDA_CHECK(cudaMemsetAsync(attn_long_scratch.p, 0, attn_long_scratch.bytes, m->eng->stream));
     SeqState s{-1, 0, 0, 0, 0ull};
     CUDA_CHECK(cudaMemcpy(state.p, &s, sizeof(s), cudaMemcpyHostToDevice));
 }
